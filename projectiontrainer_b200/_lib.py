@@ -1,0 +1,62 @@
+"""ctypes binding of libpt_stage1.so (the C ABI in include/pt_stage1.h).
+
+There is deliberately no fallback: if the shared library is missing, or a call
+fails, a RuntimeError is raised.  Nothing here routes to PyTorch math.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libpt_stage1.so"
+
+PT_BF16, PT_F32, PT_I64, PT_I32 = 0, 1, 2, 3
+ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF = 0, 1, 2
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
+        ("nz", C.c_int32 * 3),
+        ("A", C.c_void_p), ("lda", C.c_int64), ("a_zs", C.c_int64 * 3), ("a_mn_major", C.c_int32),
+        ("B", C.c_void_p), ("ldb", C.c_int64), ("b_zs", C.c_int64 * 3), ("b_mn_major", C.c_int32),
+        ("C", C.c_void_p), ("c_dtype", C.c_int32), ("ldc", C.c_int64), ("c_zs", C.c_int64 * 3),
+        ("C_pre", C.c_void_p),
+        ("bias", C.c_void_p),
+        ("residual", C.c_void_p), ("r_dtype", C.c_int32), ("ldr", C.c_int64), ("r_zs", C.c_int64 * 3),
+        ("act", C.c_int32), ("alpha", C.c_float),
+        ("kg", C.c_int32), ("a_kgs", C.c_int64), ("b_kgs", C.c_int64),
+    ]
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the shared library; raise loudly if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m projectiontrainer_b200.build` "
+            "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for this path.")
+    L = C.CDLL(str(LIB_PATH))
+    L.pt_last_error.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def last_error() -> str:
+    return lib().pt_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (status {rc}): {last_error()}")
+
+
+def call(name: str, *args) -> None:
+    fn = getattr(lib(), name)
+    check(fn(*args), name)

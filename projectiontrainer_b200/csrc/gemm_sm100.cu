@@ -1,0 +1,511 @@
+// Persistent, warp-specialised bf16 GEMM for sm_100a.
+//
+//   warp 0      TMA producer   (one lane): global -> 128B-swizzled smem ring
+//   warp 1      MMA issuer     (one lane): tcgen05.mma 128 x BN x 16, f32 accumulators in TMEM
+//   warp 2      TMEM allocator
+//   warps 4..7  epilogue: tcgen05.ld -> registers -> (alpha, bias, act, residual) -> global
+//
+// Two TMEM accumulator stages let the epilogue of tile i overlap the main loop
+// of tile i+1.  Grid = min(#tiles, #SMs); each CTA walks tiles t = bid, bid+grid, ...
+// (m fastest so CTAs running together share the same B panel in L2).
+//
+// Operands may be K-major ([rows][K], box 64k x rows) or MN-major ([K][rows],
+// 64k x 64mn boxes); both land in smem in the canonical SWIZZLE_128B layouts
+// that the UMMA shared-memory descriptors name.
+#include "pt_common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace pt {
+
+constexpr int BM = 128;       // UMMA M (cta_group::1)
+constexpr int BK = 64;        // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 256;
+constexpr int kAccStride = 256;   // TMEM columns per accumulator stage
+constexpr int kTmemCols = 512;
+constexpr int kSmemBudget = 232448 - 1024 - 256;   // dyn smem minus align slack and barriers
+
+template <int BN>
+struct GemmCfg {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES_RAW = kSmemBudget / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+struct GemmDev {
+    int M, N, K;
+    int nz[3];        // batch extents used for tile enumeration
+    int kg;           // K groups (>=1)
+    int a_mn, b_mn;
+    int a_emask, b_emask;   // bit i set: tensor-map extra dim i takes a coordinate
+    int kg_slot;      // which extra dim is the K-group (-1: none)
+    int z_slot[3];    // which extra dim batch dim i maps to
+    void* C;
+    void* C_pre;
+    const float* bias;
+    const void* R;
+    long long ldc, ldr;
+    long long c_zs[3], r_zs[3];
+    int c_f32, r_f32, act;
+    float alpha;
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == PT_ACT_GELU_TANH) {
+        const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+        float u = k0 * (v + k1 * v * v * v);
+        return 0.5f * v * (1.f + tanh_fast(u));
+    } else if (act == PT_ACT_GELU_ERF) {
+        return gelu_erf_f(v);
+    }
+    return v;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const GemmDev p) {
+    using Cfg = GemmCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + STAGES;
+    uint64_t* tfull_bar = bars + 2 * STAGES;
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int mt = (p.M + BM - 1) / BM;
+    const int nt = (p.N + BN - 1) / BN;
+    const int tiles_per_z = mt * nt;
+    const int total_tiles = tiles_per_z * p.nz[0] * p.nz[1] * p.nz[2];
+    const int nkb = (p.K + BK - 1) / BK;
+    const int k_iters = nkb * p.kg;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            ptx::mbar_init(&full_bar[s], 1);
+            ptx::mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&tfull_bar[s], 1);
+            ptx::mbar_init(&tempty_bar[s], 4);
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) {
+        ptx::tmem_alloc(tmem_slot, kTmemCols);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                int zz = t / tiles_per_z, r = t - zz * tiles_per_z;
+                const int n_blk = r / mt, m_blk = r - n_blk * mt;
+                int z[3];
+                z[0] = zz % p.nz[0]; zz /= p.nz[0];
+                z[1] = zz % p.nz[1]; zz /= p.nz[1];
+                z[2] = zz;
+                int ea[3] = {0, 0, 0}, eb[3] = {0, 0, 0};
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    const int s = p.z_slot[i];
+                    if (s >= 0) {
+                        if ((p.a_emask >> s) & 1) ea[s] = z[i];
+                        if ((p.b_emask >> s) & 1) eb[s] = z[i];
+                    }
+                }
+                for (int it = 0; it < k_iters; ++it) {
+                    const int g = it / nkb, kb = it - g * nkb;
+                    if (p.kg_slot >= 0) {
+                        if ((p.a_emask >> p.kg_slot) & 1) ea[p.kg_slot] = g;
+                        if ((p.b_emask >> p.kg_slot) & 1) eb[p.kg_slot] = g;
+                    }
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                    uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
+                    uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
+                    if (!p.a_mn) {
+                        ptx::tma_load_5d(&tmA, &full_bar[stage], sa, kb * BK, m_blk * BM, ea[0],
+                                         ea[1], ea[2]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BM / 64; ++c)
+                            ptx::tma_load_5d(&tmA, &full_bar[stage], sa + c * (BK * 128),
+                                             m_blk * BM + c * 64, kb * BK, ea[0], ea[1], ea[2]);
+                    }
+                    if (!p.b_mn) {
+                        ptx::tma_load_5d(&tmB, &full_bar[stage], sb, kb * BK, n_blk * BN, eb[0],
+                                         eb[1], eb[2]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BN / 64; ++c)
+                            ptx::tma_load_5d(&tmB, &full_bar[stage], sb + c * (BK * 128),
+                                             n_blk * BN + c * 64, kb * BK, eb[0], eb[1], eb[2]);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = ptx::make_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+            // K-major: 8-row groups 1024 B apart (SBO); LBO unused with swizzle.
+            // MN-major: 64-wide MN chunks BK*128 B apart (LBO); 8-k-row groups 1024 B apart (SBO).
+            const uint32_t a_lbo = p.a_mn ? BK * 128 : 0, b_lbo = p.b_mn ? BK * 128 : 0;
+            const uint32_t a_kstep = p.a_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            const uint32_t b_kstep = p.b_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * kAccStride;
+                for (int it = 0; it < k_iters; ++it) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    const uint64_t adesc = ptx::make_smem_desc_sw128(
+                        ptx::smem_u32(smem_a + stage * Cfg::A_BYTES), a_lbo, 1024);
+                    const uint64_t bdesc = ptx::make_smem_desc_sw128(
+                        ptx::smem_u32(smem_b + stage * Cfg::B_BYTES), b_lbo, 1024);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        ptx::mma_bf16_ss(d_tmem, adesc + k * a_kstep, bdesc + k * b_kstep, idesc,
+                                         (it | k) != 0);
+                    }
+                    ptx::mma_commit(&empty_bar[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::mma_commit(&tfull_bar[acc]);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue =====================
+        const int ew = warp - 4;   // == warp % 4: the TMEM lane quarter this warp may read
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            int zz = t / tiles_per_z, r = t - zz * tiles_per_z;
+            const int n_blk = r / mt, m_blk = r - n_blk * mt;
+            const int z0 = zz % p.nz[0]; zz /= p.nz[0];
+            const int z1 = zz % p.nz[1]; zz /= p.nz[1];
+            const int z2 = zz;
+            const long long coff = z0 * p.c_zs[0] + z1 * p.c_zs[1] + z2 * p.c_zs[2];
+            const long long roff = z0 * p.r_zs[0] + z1 * p.r_zs[1] + z2 * p.r_zs[2];
+            const int row = m_blk * BM + ew * 32 + lane;
+            const bool row_ok = row < p.M;
+
+            ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + acc * kAccStride + (static_cast<uint32_t>(ew * 32) << 16);
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(taddr + c * 32, v);
+                ptx::tmem_ld_wait();
+                const int col0 = n_blk * BN + c * 32;
+                if (row_ok && col0 < p.N) {
+#pragma unroll
+                    for (int g8 = 0; g8 < 4; ++g8) {
+                        const int col = col0 + g8 * 8;
+                        if (col >= p.N) break;
+                        float f[8], pre[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g8 * 8 + j]) * p.alpha;
+                        const bool full8 = col + 8 <= p.N;
+                        if (p.bias) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (full8 || col + j < p.N) f[j] += __ldg(p.bias + col + j);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) pre[j] = f[j];
+                        if (p.act != PT_ACT_NONE) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) f[j] = apply_act(f[j], p.act);
+                        }
+                        if (p.R) {
+                            const long long ro = roff + static_cast<long long>(row) * p.ldr + col;
+                            if (p.r_f32) {
+                                const float* rp = static_cast<const float*>(p.R) + ro;
+                                if (full8) {
+                                    const float4 r0 = *reinterpret_cast<const float4*>(rp);
+                                    const float4 r1 = *reinterpret_cast<const float4*>(rp + 4);
+                                    f[0] += r0.x; f[1] += r0.y; f[2] += r0.z; f[3] += r0.w;
+                                    f[4] += r1.x; f[5] += r1.y; f[6] += r1.z; f[7] += r1.w;
+                                } else {
+                                    for (int j = 0; j < 8 && col + j < p.N; ++j) f[j] += rp[j];
+                                }
+                            } else {
+                                const __nv_bfloat16* rp = static_cast<const __nv_bfloat16*>(p.R) + ro;
+                                if (full8) {
+                                    const uint4 u = *reinterpret_cast<const uint4*>(rp);
+                                    f[0] += bf16_lo(u.x); f[1] += bf16_hi(u.x);
+                                    f[2] += bf16_lo(u.y); f[3] += bf16_hi(u.y);
+                                    f[4] += bf16_lo(u.z); f[5] += bf16_hi(u.z);
+                                    f[6] += bf16_lo(u.w); f[7] += bf16_hi(u.w);
+                                } else {
+                                    for (int j = 0; j < 8 && col + j < p.N; ++j)
+                                        f[j] += __bfloat162float(rp[j]);
+                                }
+                            }
+                        }
+                        const long long co = coff + static_cast<long long>(row) * p.ldc + col;
+                        if (p.c_f32) {
+                            float* cp = static_cast<float*>(p.C) + co;
+                            if (full8) {
+                                *reinterpret_cast<float4*>(cp) = make_float4(f[0], f[1], f[2], f[3]);
+                                *reinterpret_cast<float4*>(cp + 4) = make_float4(f[4], f[5], f[6], f[7]);
+                            } else {
+                                for (int j = 0; j < 8 && col + j < p.N; ++j) cp[j] = f[j];
+                            }
+                        } else {
+                            __nv_bfloat16* cp = static_cast<__nv_bfloat16*>(p.C) + co;
+                            if (full8) {
+                                uint4 u;
+                                u.x = pack_bf16(f[0], f[1]); u.y = pack_bf16(f[2], f[3]);
+                                u.z = pack_bf16(f[4], f[5]); u.w = pack_bf16(f[6], f[7]);
+                                *reinterpret_cast<uint4*>(cp) = u;
+                            } else {
+                                for (int j = 0; j < 8 && col + j < p.N; ++j)
+                                    cp[j] = __float2bfloat16(f[j]);
+                            }
+                        }
+                        if (p.C_pre) {
+                            __nv_bfloat16* pp = static_cast<__nv_bfloat16*>(p.C_pre) + co;
+                            if (full8) {
+                                uint4 u;
+                                u.x = pack_bf16(pre[0], pre[1]); u.y = pack_bf16(pre[2], pre[3]);
+                                u.z = pack_bf16(pre[4], pre[5]); u.w = pack_bf16(pre[6], pre[7]);
+                                *reinterpret_cast<uint4*>(pp) = u;
+                            } else {
+                                for (int j = 0; j < 8 && col + j < p.N; ++j)
+                                    pp[j] = __float2bfloat16(pre[j]);
+                            }
+                        }
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+
+// ---------------------------------------------------------------------------
+// Host side: tensor-map encoding + launch
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) !=
+            cudaSuccess || q != cudaDriverEntryPointSuccess || !sym) {
+        return nullptr;
+    }
+    fn = reinterpret_cast<EncodeTiledFn>(sym);
+    return fn;
+}
+
+// One operand = a 5-D bf16 tensor map {inner, outer, e0, e1, e2}.
+//   K-major : inner = K (box 64), outer = rows (box `rows_box`)
+//   MN-major: inner = rows (box 64), outer = K (box 64)
+static int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, int K,
+                          long long ld, const int ext[3], const long long est[3], int rows_box,
+                          const char* name) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return PT_ERR_CUDA; }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld & 7)) {
+        set_error("gemm operand %s: base must be 16B aligned and ld a multiple of 8 (ld=%lld)", name, ld);
+        return PT_ERR_INVALID;
+    }
+    cuuint64_t dims[5];
+    cuuint64_t strides[4];
+    cuuint32_t box[5] = {64, 64, 1, 1, 1};
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    if (!mn_major) {
+        dims[0] = static_cast<cuuint64_t>(K); dims[1] = static_cast<cuuint64_t>(rows);
+        box[1] = static_cast<cuuint32_t>(rows_box);
+    } else {
+        dims[0] = static_cast<cuuint64_t>(rows); dims[1] = static_cast<cuuint64_t>(K);
+    }
+    strides[0] = static_cast<cuuint64_t>(ld) * 2;
+    for (int i = 0; i < 3; ++i) {
+        if (est[i] != 0) {
+            if (est[i] & 7) {
+                set_error("gemm operand %s: batch stride %d (%lld) must be a multiple of 8", name, i, est[i]);
+                return PT_ERR_INVALID;
+            }
+            dims[2 + i] = static_cast<cuuint64_t>(ext[i]);
+            strides[1 + i] = static_cast<cuuint64_t>(est[i]) * 2;
+        } else {
+            dims[2 + i] = 1;
+            strides[1 + i] = strides[0];
+        }
+    }
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides,
+                     box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(%s) failed: CUresult %d (dims %llu %llu %llu %llu %llu, "
+                  "strides %llu %llu %llu %llu)", name, static_cast<int>(r),
+                  (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2],
+                  (unsigned long long)dims[3], (unsigned long long)dims[4],
+                  (unsigned long long)strides[0], (unsigned long long)strides[1],
+                  (unsigned long long)strides[2], (unsigned long long)strides[3]);
+        return PT_ERR_CUDA;
+    }
+    return PT_OK;
+}
+
+template <int BN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, int tiles,
+                       cudaStream_t st) {
+    using Cfg = GemmCfg<BN>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<BN>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e)); return PT_ERR_CUDA; }
+        attr_done = true;
+    }
+    int grid = tiles < num_sms() ? tiles : num_sms();
+    gemm_bf16_kernel<BN><<<grid, kGemmThreads, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+    return check_launch("gemm_bf16_kernel");
+}
+
+// Pick the N tile that wastes the least tensor-core work (ties -> larger tile).
+static int pick_bn(int M, int N, long long nbatch) {
+    const int cands[4] = {256, 192, 128, 64};
+    const int sms = num_sms();
+    double best = 1e30; int best_bn = 256;
+    const long long mt = (M + BM - 1) / BM;
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        const long long nt = (N + bn - 1) / bn;
+        const long long tiles = mt * nt * nbatch;
+        const long long waves = (tiles + sms - 1) / sms;
+        // cost ~ waves * (mainloop ∝ bn, with a fixed per-tile overhead)
+        double cost = static_cast<double>(waves) * (bn + 24.0);
+        if (cost < best * 0.999) { best = cost; best_bn = bn; }
+    }
+    return best_bn;
+}
+
+}  // namespace pt
+
+extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
+    using namespace pt;
+    PT_REQUIRE(a != nullptr, "pt_gemm_bf16: null args");
+    PT_REQUIRE(a->M > 0 && a->N > 0 && a->K > 0, "pt_gemm_bf16: M,N,K must be positive (%d,%d,%d)", a->M, a->N, a->K);
+    PT_REQUIRE(a->A && a->B && a->C, "pt_gemm_bf16: null operand");
+    PT_REQUIRE(a->nz[0] >= 1 && a->nz[1] >= 1 && a->nz[2] >= 1, "pt_gemm_bf16: batch extents must be >= 1");
+    PT_REQUIRE(a->c_dtype == PT_BF16 || a->c_dtype == PT_F32, "pt_gemm_bf16: c_dtype must be bf16 or f32");
+    const int kg = a->kg > 1 ? a->kg : 1;
+    PT_REQUIRE(kg == 1 || a->nz[2] == 1, "pt_gemm_bf16: kg > 1 requires nz[2] == 1");
+    const int cvec = a->c_dtype == PT_F32 ? 4 : 8;
+    PT_REQUIRE((a->ldc % cvec) == 0 && (reinterpret_cast<uintptr_t>(a->C) & 15) == 0,
+               "pt_gemm_bf16: C must be 16B aligned with ldc %% %d == 0 (ldc=%lld)", cvec, (long long)a->ldc);
+    for (int i = 0; i < 3; ++i)
+        PT_REQUIRE((a->c_zs[i] % cvec) == 0, "pt_gemm_bf16: c batch stride %d must be a multiple of %d", i, cvec);
+    if (a->C_pre) PT_REQUIRE(a->c_dtype == PT_BF16 || (a->ldc % 8) == 0, "pt_gemm_bf16: C_pre needs ldc %% 8 == 0");
+    if (a->residual) {
+        const int rvec = a->r_dtype == PT_F32 ? 4 : 8;
+        PT_REQUIRE(a->r_dtype == PT_BF16 || a->r_dtype == PT_F32, "pt_gemm_bf16: r_dtype must be bf16 or f32");
+        PT_REQUIRE((a->ldr % rvec) == 0 && (reinterpret_cast<uintptr_t>(a->residual) & 15) == 0,
+                   "pt_gemm_bf16: residual must be 16B aligned with ldr %% %d == 0", rvec);
+        for (int i = 0; i < 3; ++i)
+            PT_REQUIRE((a->r_zs[i] % rvec) == 0, "pt_gemm_bf16: residual batch stride %d misaligned", i);
+    }
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_GELU_ERF, "pt_gemm_bf16: bad act %d", a->act);
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+
+    GemmDev p;
+    memset(&p, 0, sizeof(p));
+    p.M = a->M; p.N = a->N; p.K = a->K;
+    p.kg = kg;
+    p.a_mn = a->a_mn_major ? 1 : 0;
+    p.b_mn = a->b_mn_major ? 1 : 0;
+    int ext[3]; long long ast[3], bst[3];
+    if (kg > 1) {
+        p.kg_slot = 0; p.z_slot[0] = 1; p.z_slot[1] = 2; p.z_slot[2] = -1;
+        ext[0] = kg; ext[1] = a->nz[0]; ext[2] = a->nz[1];
+        ast[0] = a->a_kgs; ast[1] = a->a_zs[0]; ast[2] = a->a_zs[1];
+        bst[0] = a->b_kgs; bst[1] = a->b_zs[0]; bst[2] = a->b_zs[1];
+    } else {
+        p.kg_slot = -1;
+        for (int i = 0; i < 3; ++i) { p.z_slot[i] = i; ext[i] = a->nz[i]; ast[i] = a->a_zs[i]; bst[i] = a->b_zs[i]; }
+    }
+    for (int i = 0; i < 3; ++i) {
+        p.nz[i] = a->nz[i];
+        if (ast[i] != 0) p.a_emask |= 1 << i;
+        if (bst[i] != 0) p.b_emask |= 1 << i;
+        p.c_zs[i] = a->c_zs[i]; p.r_zs[i] = a->r_zs[i];
+    }
+    p.C = a->C; p.C_pre = a->C_pre; p.bias = a->bias; p.R = a->residual;
+    p.ldc = a->ldc; p.ldr = a->ldr;
+    p.c_f32 = a->c_dtype == PT_F32; p.r_f32 = a->r_dtype == PT_F32;
+    p.act = a->act; p.alpha = a->alpha;
+
+    const long long nbatch = static_cast<long long>(a->nz[0]) * a->nz[1] * a->nz[2];
+    const int bn = pick_bn(a->M, a->N, nbatch);
+    const long long tiles_ll = static_cast<long long>((a->M + BM - 1) / BM) * ((a->N + bn - 1) / bn) * nbatch;
+    PT_REQUIRE(tiles_ll < (1ll << 31), "pt_gemm_bf16: too many tiles");
+    const int tiles = static_cast<int>(tiles_ll);
+
+    CUtensorMap ta, tb;
+    int rc = encode_operand(&ta, a->A, p.a_mn, a->M, a->K, a->lda, ext, ast, BM, "A");
+    if (rc != PT_OK) return rc;
+    rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn, "B");
+    if (rc != PT_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (bn) {
+        case 256: return launch_gemm<256>(ta, tb, p, tiles, st);
+        case 192: return launch_gemm<192>(ta, tb, p, tiles, st);
+        case 128: return launch_gemm<128>(ta, tb, p, tiles, st);
+        default:  return launch_gemm<64>(ta, tb, p, tiles, st);
+    }
+}

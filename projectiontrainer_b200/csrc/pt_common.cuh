@@ -1,0 +1,101 @@
+// Shared device/host helpers for the Stage-1 hot-path kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+
+#include "../../include/pt_stage1.h"
+
+namespace pt {
+
+// ---- error plumbing (thread-local string behind pt_last_error) -------------
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+
+#define PT_REQUIRE(cond, ...)                                   \
+    do {                                                        \
+        if (!(cond)) {                                          \
+            pt::set_error(__VA_ARGS__);                         \
+            return PT_ERR_INVALID;                              \
+        }                                                       \
+    } while (0)
+
+constexpr int kNumSMsFallback = 148;
+int num_sms();
+
+// ---- small device helpers ---------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024 (multiple of 32). `sh` needs 32 floats.
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sh[w] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    float r = (lane < nw) ? sh[lane] : 0.f;
+    r = warp_sum(r);
+    return r;
+}
+__device__ __forceinline__ float block_max(float v, float* sh) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) sh[w] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    float r = (lane < nw) ? sh[lane] : -INFINITY;
+    r = warp_max(r);
+    return r;
+}
+
+__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// tanh-GELU (SigLIP MLP, Gemma3 GeGLU): 0.5 z (1 + tanh(sqrt(2/pi)(z + 0.044715 z^3)))
+__device__ __forceinline__ float gelu_tanh_f(float z) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    float u = k0 * (z + k1 * z * z * z);
+    return 0.5f * z * (1.f + tanhf(u));
+}
+__device__ __forceinline__ float gelu_tanh_grad_f(float z) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    float u = k0 * (z + k1 * z * z * z);
+    float t = tanhf(u);
+    float du = k0 * (1.f + 3.f * k1 * z * z);
+    return 0.5f * (1.f + t) + 0.5f * z * (1.f - t * t) * du;
+}
+// exact erf-GELU (projector): 0.5 z (1 + erf(z / sqrt 2))
+__device__ __forceinline__ float gelu_erf_f(float z) {
+    return 0.5f * z * (1.f + erff(z * 0.7071067811865476f));
+}
+__device__ __forceinline__ float gelu_erf_grad_f(float z) {
+    float cdf = 0.5f * (1.f + erff(z * 0.7071067811865476f));
+    float pdf = 0.3989422804014327f * __expf(-0.5f * z * z);
+    return cdf + z * pdf;
+}
+
+}  // namespace pt

@@ -1,0 +1,122 @@
+"""tcgen05 GEMM vs torch fp32 matmul on bf16-rounded inputs (GPU only)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, dev, scale=1.0):
+    return (torch.randn(shape, device=dev, dtype=torch.float32) * scale).to(torch.bfloat16)
+
+
+def _check(out, ref, tol=2e-2, name=""):
+    out = out.float()
+    err = (out - ref).abs().max().item()
+    den = ref.abs().max().item() + 1e-6
+    assert err / den < tol, f"{name}: max err {err} vs scale {den}"
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 256, 256), (575, 1152, 1024),
+                                   (1000, 1536, 1152), (130, 64, 768), (384, 192, 2048),
+                                   (4096, 1024, 4096), (18400, 1152, 1280)])
+def test_gemm_tn(cuda_dev, M, N, K):
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(M + N + K)
+    x, w = _rand((M, K), cuda_dev), _rand((N, K), cuda_dev, 0.05)
+    ref = x.float() @ w.float().t()
+    _check(ops.linear(x, w), ref, name="bf16 out")
+    _check(ops.linear(x, w, out_dtype=torch.float32), ref, tol=1e-3, name="f32 out")
+
+
+def test_gemm_epilogues(cuda_dev):
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(0)
+    M, N, K = 700, 1152, 512
+    x, w = _rand((M, K), cuda_dev), _rand((N, K), cuda_dev, 0.05)
+    b = torch.randn(N, device=cuda_dev)
+    res = torch.randn(M, N, device=cuda_dev)
+    z = x.float() @ w.float().t() + b
+    pre = torch.empty(M, N, device=cuda_dev, dtype=torch.bfloat16)
+    y = ops.linear(x, w, bias=b, act=ops.ACT_GELU_ERF, c_pre=pre)
+    _check(y, torch.nn.functional.gelu(z), name="gelu_erf")
+    _check(pre, z, name="pre")
+    y = ops.linear(x, w, bias=b, act=ops.ACT_GELU_TANH, out_dtype=torch.float32)
+    _check(y, torch.nn.functional.gelu(z, approximate="tanh"), tol=2e-3, name="gelu_tanh")
+    y = ops.linear(x, w, bias=b, residual=res, out_dtype=torch.float32)
+    _check(y, z + res, tol=1e-3, name="residual f32")
+    acc = res.clone()
+    ops.linear(x, w, residual=acc, out=acc, alpha=0.5)
+    _check(acc, 0.5 * (z - b) + res, tol=1e-3, name="in-place accumulate")
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 256), (575, 1024, 1152), (1000, 10240, 1152),
+                                   (703, 256, 703)])
+def test_gemm_dgrad_mn_major_b(cuda_dev, M, N, K):
+    """dx[M,N] = dy[M,K] @ W[K,N] with W row-major (B operand MN-major)."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(1)
+    Kp = (K + 7) // 8 * 8
+    dy = _rand((M, Kp), cuda_dev)[:, :K]
+    w = _rand((K, N), cuda_dev, 0.05)
+    ref = dy.float() @ w.float()
+    out = torch.empty(M, N, device=cuda_dev, dtype=torch.float32)
+    ops.gemm_raw(M=M, N=N, K=K, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True,
+                 Cout=out, ldc=N)
+    _check(out, ref, tol=1e-3, name="dgrad")
+
+
+@pytest.mark.parametrize("T,N,K", [(256, 128, 256), (1000, 1152, 1024), (18400, 1152, 256),
+                                   (703, 703, 256)])
+def test_gemm_wgrad_mn_major_ab(cuda_dev, T, N, K):
+    """dw[N,K] = dy[T,N]^T @ x[T,K] (both operands MN-major, contraction over rows)."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(2)
+    Np = (N + 7) // 8 * 8
+    dy = _rand((T, Np), cuda_dev)[:, :N]
+    x = _rand((T, K), cuda_dev)
+    ref = dy.float().t() @ x.float()
+    out = torch.empty(N, K, device=cuda_dev, dtype=torch.float32)
+    ops.gemm_raw(M=N, N=K, K=T, A=dy, lda=dy.stride(0), a_mn=True, B=x, ldb=x.stride(0),
+                 b_mn=True, Cout=out, ldc=K)
+    _check(out, ref, tol=1e-3, name="wgrad")
+
+
+def test_gemm_batched_gqa_scores(cuda_dev):
+    """S[b,h,q,k] = scale * Q[b,q,h,:] . K[b,k,h//G,:]  (strided 3-D batch, broadcast kv)."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(3)
+    Bn, S, Hq, Hkv, D = 3, 703, 4, 2, 256
+    G = Hq // Hkv
+    q = _rand((Bn, S, Hq, D), cuda_dev)
+    k = _rand((Bn, S, Hkv, D), cuda_dev)
+    Sp = 704
+    out = torch.zeros(Bn, Hq, S, Sp, device=cuda_dev, dtype=torch.float32)
+    # z0 = head within group, z1 = kv head, z2 = batch
+    ops.gemm_raw(M=S, N=S, K=D, A=q, lda=Hq * D, B=k, ldb=Hkv * D, Cout=out, ldc=Sp,
+                 nz=(G, Hkv, Bn), a_zs=(D, G * D, S * Hq * D), b_zs=(0, D, S * Hkv * D),
+                 c_zs=(S * Sp, G * S * Sp, Hq * S * Sp), alpha=1.0 / 16)
+    kk = k.float().repeat_interleave(G, dim=2)
+    ref = torch.einsum("bqhd,bkhd->bhqk", q.float(), kk) / 16
+    _check(out[..., :S], ref, tol=1e-3, name="scores")
+    assert out[..., S:].abs().max().item() == 0.0
+
+
+def test_gemm_grouped_contraction(cuda_dev):
+    """dV[b,k,kvh,:] = sum_{g,q} P[b,kvh*G+g,q,k] dO[b,q,kvh*G+g,:]  (kg groups, MN-major A and B)."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(4)
+    Bn, S, Hq, Hkv, D = 2, 703, 4, 2, 256
+    G = Hq // Hkv
+    Sp = 704
+    P = torch.zeros(Bn, Hq, S, Sp, device=cuda_dev, dtype=torch.bfloat16)
+    P[..., :S] = _rand((Bn, Hq, S, S), cuda_dev, 0.1)
+    dO = _rand((Bn, S, Hq, D), cuda_dev)
+    out = torch.empty(Bn, S, Hkv, D, device=cuda_dev, dtype=torch.bfloat16)
+    ops.gemm_raw(M=S, N=D, K=S, A=P, lda=Sp, a_mn=True, B=dO, ldb=Hq * D, b_mn=True, Cout=out,
+                 ldc=Hkv * D, nz=(Hkv, Bn, 1), a_zs=(G * S * Sp, Hq * S * Sp, 0),
+                 b_zs=(G * D, S * Hq * D, 0), c_zs=(D, S * Hkv * D, 0),
+                 kg=G, a_kgs=S * Sp, b_kgs=D)
+    Pf = P[..., :S].float().view(Bn, Hkv, G, S, S)
+    dOf = dO.float().view(Bn, S, Hkv, G, D)
+    ref = torch.einsum("bhgqk,bqhgd->bkhd", Pf, dOf)
+    _check(out, ref, name="grouped")
