@@ -98,6 +98,94 @@ typedef struct {
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);
 
+
+/* ------------------------------------------------------------------------- *
+ * Bandwidth-bound kernels.  Row-group remapping: when group_rows > 0, logical
+ * row r lives at physical row (r / group_rows) * group_stride + group_row0 +
+ * r % group_rows of the strided side (used to drop token 0 of every image,
+ * ref:Stage1/projector_trainer.py:173, and to address only label rows).
+ * ------------------------------------------------------------------------- */
+
+/* f32 [B,3,H,W] -> bf16 [B*(H/p)*(W/p), 3*p*p], column order (c,py,px): the im2col of
+ * Conv2d(3,d,p,stride=p) — HF:models/siglip/modeling_siglip.py:124-130,178-180. */
+int pt_patchify(const float* pixels, void* cols_bf16, int B, int H, int W, int patch, void* stream);
+
+/* LayerNorm (biased variance), f32 in, bf16 out — HF:models/siglip/modeling_siglip.py:348,357,618. */
+int pt_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* out_bf16,
+                     int rows_out, int D, float eps, int group_rows_out, int group_rows_in,
+                     int group_row0, void* stream);
+
+/* Gemma3 RMSNorm: x * rsqrt(mean x^2 + eps) * (1 + w), fp32 inside — HF:models/gemma3/modeling_gemma3.py:138-146. */
+int pt_rmsnorm_fwd(const void* x, int x_dtype, const float* w, void* out_bf16, int rows_out, int D,
+                   float eps, int group_rows_out, int group_rows_in, int group_row0, void* stream);
+
+/* Sandwich-norm residual step of the decoder layer (HF:models/gemma3/modeling_gemma3.py:417-432):
+ *   x_out = x_in + RMS(y; w_post);   next = RMS(x_out; w_next)   (w_next/next may both be NULL) */
+int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, const float* x_in, float* x_out,
+                            const float* w_next, void* next_bf16, int rows, int D, float eps,
+                            void* stream);
+
+/* RMSNorm input gradient.  g: grad of the norm output; u: saved norm input (u_group_* remap);
+ * dst bf16: dst = du;  dst f32: dst[remap(r)] = (add ? add[remap(r)] : 0) + du. */
+int pt_rmsnorm_bwd(const void* g, int g_dtype, const void* u, int u_dtype, const float* w, void* dst,
+                   int dst_dtype, const float* add_f32, int rows, int D, float eps, int u_group_rows,
+                   int u_group_stride, int u_group_row0, int dst_group_rows, int dst_group_stride,
+                   int dst_group_row0, void* stream);
+
+/* Per-head q/k RMSNorm + rotary embedding on the fused qkv row [(hq+2hkv)*hd]; position = row % S;
+ * cos/sin are f32 [S, hd/2] — HF:models/gemma3/modeling_gemma3.py:362-368,233-263. */
+int pt_qknorm_rope_fwd(const void* qkv, const float* wq, const float* wk, const float* cos_t,
+                       const float* sin_t, void* q_out, void* k_out, int rows, int S, int hq, int hkv,
+                       int hd, float eps, void* stream);
+int pt_qknorm_rope_bwd(const void* dq, const void* dk, const void* qkv, const float* wq, const float* wk,
+                       const float* cos_t, const float* sin_t, void* d_qkv, int rows, int S, int hq,
+                       int hkv, int hd, float eps, void* stream);
+
+/* Row softmax of pre-scaled f32 scores [Z,Sq,ld] -> bf16 probabilities [Z,Sq,ld]; key k is allowed
+ * for query q iff (!causal || k <= q) && (window <= 0 || k > q - window) && keyvalid[z/heads_per_batch][k]
+ * — HF:masking_utils.py:74-99,148-159; HF:models/gemma3/modeling_gemma3.py:370-384 (SigLIP: no mask). */
+int pt_softmax_fwd(const float* scores, void* P_bf16, const uint8_t* keyvalid, int Z, int Sq, int Sk,
+                   int ld, int heads_per_batch, int causal, int window, void* stream);
+/* dS = scale * P * (dP - rowsum(P dP)) */
+int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long rows, int Sk, int ld,
+                   float scale, void* stream);
+
+/* GeGLU: act = gelu_tanh(g) * u with gu = [g | u] per row — HF:models/gemma3/modeling_gemma3.py:127-129. */
+int pt_geglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream);
+int pt_geglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, int ff, void* stream);
+
+/* dZ = dH * d/dz[0.5 z (1 + erf(z/sqrt2))] — backward of nn.GELU() in ref:Stage1/projectors.py:18. */
+int pt_gelu_erf_bwd(const void* dH, const void* Z, void* dZ, long long n, void* stream);
+
+/* Text half of the splice (ref:Stage1/projector_trainer.py:186-220): x0[b, n_img+t, :] =
+ * bf16(embed[token_ids[b,t]] * scale); attention mask / lm labels (int64, bit-exact),
+ * key-valid bytes and shifted int32 targets (HF:loss/loss_utils.py:57-60) for all S = n_img+T positions. */
+int pt_embed_splice(const int64_t* token_ids, const int64_t* labels, const void* embed_bf16, float scale,
+                    int64_t pad_id, int has_pad, int B, int T, int n_img, int h, float* x0,
+                    int64_t* attn_mask, int64_t* lm_labels, uint8_t* keyvalid, int32_t* targets,
+                    void* stream);
+
+/* Masked causal-LM cross-entropy over bf16 logits [rows, V] (HF:loss/loss_utils.py:28-67): writes
+ * lse[rows], acc2 = {sum of row losses, #valid rows}, loss = mean; then overwrites the logits with
+ * dlogits = (softmax - onehot) * gscale / n_valid (zero rows where target < 0). */
+int pt_ce_fwd_bwd(void* logits_bf16, long long ld, const int32_t* targets, int rows, int V, float* lse,
+                  float* acc2, float* loss, float gscale, void* stream);
+
+/* out[n] = sum_m x[m][n] (bias gradients). */
+int pt_colsum(const void* x_bf16, long long ld, float* out, int M, int N, void* stream);
+/* out[0] = sum g^2 */
+int pt_sumsq(const float* g, long long n, float* out, void* stream);
+/* clip_grad_norm_(max_norm) + AdamW step on a flat f32 buffer, refreshing a bf16 shadow copy
+ * (ref:Stage1/projector_trainer.py:241-243).  sumsq: device scalar from pt_sumsq of the raw grads;
+ * grad_scale multiplies grads first (1/world after an allreduce-sum).  step is 1-based. */
+int pt_clip_adamw(float* p, const float* g, float* m, float* v, void* shadow_bf16, long long n,
+                  const float* sumsq, float grad_scale, float max_norm, float lr, float beta1, float beta2,
+                  float eps, float weight_decay, int step, void* stream);
+int pt_cast_f32_bf16(const float* x, void* y_bf16, long long n, void* stream);
+/* out[r] = bf16(x[remap(r)]) — e.g. the image-token rows of dL/dX0 handed to the projector backward. */
+int pt_gather_cast_rows(const float* x, void* out_bf16, int rows_out, int D, int group_rows_out,
+                        int group_rows_in, int group_row0, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -174,10 +174,11 @@ def shifted_targets(lm_labels: np.ndarray) -> np.ndarray:
     return out
 
 
-def embed_tokens(token_ids: torch.Tensor, E: torch.Tensor, hidden: int):
+def embed_tokens(token_ids: torch.Tensor, E: torch.Tensor, hidden: int, scale_dtype=None):
     """HF:models/gemma3/modeling_gemma3.py:102-113 — embedding * sqrt(hidden), the scale being
-    rounded to the embedding dtype first."""
-    scale = torch.tensor(hidden ** 0.5, dtype=E.dtype)
+    rounded to the embedding dtype first (scale_dtype=torch.bfloat16 emulates a bf16 checkpoint
+    whose values are held in a wider tensor: sqrt(1152) = 33.94 -> 34.0)."""
+    scale = torch.tensor(hidden ** 0.5, dtype=scale_dtype or E.dtype).to(E.dtype)
     return E[token_ids] * scale
 
 
@@ -268,14 +269,14 @@ def causal_lm_loss(hidden, W: dict, cfg: GemmaCfg, lm_labels: np.ndarray):
 
 # --------------------------------------------------------------------------- whole step
 def stage1_step(pixels, token_ids, labels, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaCfg,
-                grad_accum: int = 1, want_intermediates: bool = False):
+                grad_accum: int = 1, want_intermediates: bool = False, scale_dtype=None):
     """One Stage-1 forward+backward (ref:Stage1/projector_trainer.py:152-237).
     Returns loss (unscaled, as logged) and the four projector gradients of loss/grad_accum."""
     P = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
     with torch.no_grad():
         feats = siglip_forward(pixels, Wv, vcfg)
         patch = feats[:, 1:, :]                      # ref:projector_trainer.py:173 ("discard CLS")
-        txt = embed_tokens(token_ids, Wl["embed"], lcfg.hidden)
+        txt = embed_tokens(token_ids, Wl["embed"], lcfg.hidden, scale_dtype)
     proj = projector_forward(patch, P)
     X0 = torch.cat([proj, txt.to(proj.dtype)], dim=1)
     n_img = proj.shape[1]

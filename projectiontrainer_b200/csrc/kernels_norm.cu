@@ -1,0 +1,284 @@
+// Bandwidth-bound normalisation kernels: LayerNorm (SigLIP) and the Gemma3
+// (1+w) RMSNorm family, forward and backward.  One warp per row, 128-bit loads,
+// fp32 statistics, rows re-read from L1/L2 rather than cached in registers so
+// any row length that is a multiple of 8 works.
+#include "pt_common.cuh"
+
+namespace pt {
+
+constexpr int kWarpsPerBlock = 8;
+
+struct RowMap {     // output row r  ->  input row (r / per) * stride + off + r % per
+    int per, stride, off;
+    __device__ __forceinline__ long long map(int r) const {
+        return per > 0 ? static_cast<long long>(r / per) * stride + off + r % per : r;
+    }
+};
+
+__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    const float4 b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 u = *reinterpret_cast<const uint4*>(p);
+    v[0] = bf16_lo(u.x); v[1] = bf16_hi(u.x); v[2] = bf16_lo(u.y); v[3] = bf16_hi(u.y);
+    v[4] = bf16_lo(u.z); v[5] = bf16_hi(u.z); v[6] = bf16_lo(u.w); v[7] = bf16_hi(u.w);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+    uint4 u;
+    u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
+    u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ void store8(float* p, const float (&v)[8]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+// ---- LayerNorm forward: f32 in, bf16 out; optionally drops token 0 of every image -------------
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, __nv_bfloat16* __restrict__ out, int rows_out,
+                     int D, float eps, RowMap in_map) {
+    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (r >= rows_out) return;
+    const int lane = threadIdx.x & 31;
+    const float* xr = x + in_map.map(r) * D;
+    float s = 0.f;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8]; load8(xr + i, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[j];
+    }
+    const float mean = warp_sum(s) / D;
+    float q = 0.f;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8]; load8(xr + i, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float d = v[j] - mean; q += d * d; }
+    }
+    const float rstd = rsqrtf(warp_sum(q) / D + eps);
+    __nv_bfloat16* orow = out + static_cast<long long>(r) * D;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8], g[8], b[8], o[8];
+        load8(xr + i, v); load8(gamma + i, g); load8(beta + i, b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[j] - mean) * rstd * g[j] + b[j];
+        store8(orow + i, o);
+    }
+}
+
+// ---- RMSNorm forward: out = x * rsqrt(mean x^2 + eps) * (1 + w) ------------------------------
+template <typename TIn>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+rmsnorm_fwd_kernel(const TIn* __restrict__ x, const float* __restrict__ w,
+                   __nv_bfloat16* __restrict__ out, int rows_out, int D, float eps, RowMap in_map) {
+    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (r >= rows_out) return;
+    const int lane = threadIdx.x & 31;
+    const TIn* xr = x + in_map.map(r) * D;
+    float q = 0.f;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8]; load8(xr + i, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q += v[j] * v[j];
+    }
+    const float rstd = rsqrtf(warp_sum(q) / D + eps);
+    __nv_bfloat16* orow = out + static_cast<long long>(r) * D;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8], g[8], o[8];
+        load8(xr + i, v); load8(w + i, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = v[j] * rstd * (1.f + g[j]);
+        store8(orow + i, o);
+    }
+}
+
+// ---- fused sandwich step: x_out = x_in + RMS(y; w_post); nxt = RMS(x_out; w_next) ------------
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+rmsnorm_residual_fwd_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ w_post,
+                            const float* __restrict__ x_in, float* __restrict__ x_out,
+                            const float* __restrict__ w_next, __nv_bfloat16* __restrict__ nxt,
+                            int rows, int D, float eps) {
+    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const long long base = static_cast<long long>(r) * D;
+    float q = 0.f;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8]; load8(y + base + i, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q += v[j] * v[j];
+    }
+    const float rstd = rsqrtf(warp_sum(q) / D + eps);
+    float q2 = 0.f;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8], g[8], xi[8], o[8];
+        load8(y + base + i, v); load8(w_post + i, g); load8(x_in + base + i, xi);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            // HF rounds the norm output to the activation dtype before the residual add
+            const float n = __bfloat162float(__float2bfloat16(v[j] * rstd * (1.f + g[j])));
+            o[j] = xi[j] + n;
+            q2 += o[j] * o[j];
+        }
+        store8(x_out + base + i, o);
+    }
+    if (!nxt) return;
+    const float rstd2 = rsqrtf(warp_sum(q2) / D + eps);
+    __syncwarp();
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8], g[8], o[8];
+        load8(x_out + base + i, v); load8(w_next + i, g);   // same lane wrote these addresses
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = v[j] * rstd2 * (1.f + g[j]);
+        store8(nxt + base + i, o);
+    }
+}
+
+// ---- RMSNorm backward ------------------------------------------------------------------------
+//   n = u r,  r = rsqrt(mean u^2 + eps),  out = n (1 + w)
+//   dn = g (1 + w);  du = r (dn - n mean(dn n))
+// mode 0: dst_bf16[row] = du     mode 1: dst_f32[map(row)] = add_f32[row] + du  (add may be null / alias)
+template <typename TG, typename TU>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+rmsnorm_bwd_kernel(const TG* __restrict__ g, const TU* __restrict__ u, const float* __restrict__ w,
+                   __nv_bfloat16* dst_bf16, float* dst_f32, const float* add_f32, int rows, int D,
+                   float eps, RowMap u_map, RowMap dst_map) {
+    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const TG* gr = g + static_cast<long long>(r) * D;
+    const TU* ur = u + u_map.map(r) * D;
+    float q = 0.f, dot = 0.f;
+    for (int i = lane * 8; i < D; i += 256) {
+        float gv[8], uv[8], wv[8];
+        load8(gr + i, gv); load8(ur + i, uv); load8(w + i, wv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { q += uv[j] * uv[j]; dot += gv[j] * (1.f + wv[j]) * uv[j]; }
+    }
+    q = warp_sum(q); dot = warp_sum(dot);
+    const float rstd = rsqrtf(q / D + eps);
+    const float c = dot * rstd * rstd * rstd / D;     // mean(dn n) r / ... folded: du = r dn - u c
+    const long long drow = dst_map.map(r) * D;
+    for (int i = lane * 8; i < D; i += 256) {
+        float gv[8], uv[8], wv[8], o[8];
+        load8(gr + i, gv); load8(ur + i, uv); load8(w + i, wv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * gv[j] * (1.f + wv[j]) - uv[j] * c;
+        if (dst_bf16) {
+            store8(dst_bf16 + drow + i, o);
+        } else {
+            if (add_f32) {
+                float a[8]; load8(add_f32 + drow + i, a);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] += a[j];
+            }
+            store8(dst_f32 + drow + i, o);
+        }
+    }
+}
+
+// ---- row gather + cast: f32 strided rows -> compact bf16 rows ----------------------------------
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+gather_cast_rows_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int rows_out, int D,
+                        RowMap in_map) {
+    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (r >= rows_out) return;
+    const int lane = threadIdx.x & 31;
+    const float* xr = x + in_map.map(r) * D;
+    __nv_bfloat16* orow = out + static_cast<long long>(r) * D;
+    for (int i = lane * 8; i < D; i += 256) {
+        float v[8]; load8(xr + i, v);
+        store8(orow + i, v);
+    }
+}
+
+static inline int row_blocks(int rows) { return (rows + kWarpsPerBlock - 1) / kWarpsPerBlock; }
+
+}  // namespace pt
+
+using namespace pt;
+
+extern "C" int pt_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* out_bf16,
+                                int rows_out, int D, float eps, int group_rows_out, int group_rows_in,
+                                int group_row0, void* stream) {
+    PT_REQUIRE(x && gamma && beta && out_bf16, "pt_layernorm_fwd: null pointer");
+    PT_REQUIRE(rows_out > 0 && D > 0 && D % 8 == 0, "pt_layernorm_fwd: D must be a positive multiple of 8");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    RowMap m{group_rows_out, group_rows_in, group_row0};
+    layernorm_fwd_kernel<<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, gamma, beta, static_cast<__nv_bfloat16*>(out_bf16), rows_out, D, eps, m);
+    return check_launch("layernorm_fwd");
+}
+
+extern "C" int pt_rmsnorm_fwd(const void* x, int x_dtype, const float* w, void* out_bf16, int rows_out,
+                              int D, float eps, int group_rows_out, int group_rows_in, int group_row0,
+                              void* stream) {
+    PT_REQUIRE(x && w && out_bf16, "pt_rmsnorm_fwd: null pointer");
+    PT_REQUIRE(rows_out > 0 && D > 0 && D % 8 == 0, "pt_rmsnorm_fwd: D must be a positive multiple of 8");
+    PT_REQUIRE(x_dtype == PT_BF16 || x_dtype == PT_F32, "pt_rmsnorm_fwd: x_dtype must be bf16 or f32");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    RowMap m{group_rows_out, group_rows_in, group_row0};
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    auto* o = static_cast<__nv_bfloat16*>(out_bf16);
+    if (x_dtype == PT_F32)
+        rmsnorm_fwd_kernel<float><<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, st>>>(
+            static_cast<const float*>(x), w, o, rows_out, D, eps, m);
+    else
+        rmsnorm_fwd_kernel<__nv_bfloat16><<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, st>>>(
+            static_cast<const __nv_bfloat16*>(x), w, o, rows_out, D, eps, m);
+    return check_launch("rmsnorm_fwd");
+}
+
+extern "C" int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, const float* x_in,
+                                       float* x_out, const float* w_next, void* next_bf16, int rows,
+                                       int D, float eps, void* stream) {
+    PT_REQUIRE(y_bf16 && w_post && x_in && x_out, "pt_rmsnorm_residual_fwd: null pointer");
+    PT_REQUIRE((w_next == nullptr) == (next_bf16 == nullptr), "pt_rmsnorm_residual_fwd: w_next/next mismatch");
+    PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0, "pt_rmsnorm_residual_fwd: D must be a positive multiple of 8");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    rmsnorm_residual_fwd_kernel<<<row_blocks(rows), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
+        static_cast<__nv_bfloat16*>(next_bf16), rows, D, eps);
+    return check_launch("rmsnorm_residual_fwd");
+}
+
+extern "C" int pt_rmsnorm_bwd(const void* g, int g_dtype, const void* u, int u_dtype, const float* w,
+                              void* dst, int dst_dtype, const float* add_f32, int rows, int D, float eps,
+                              int u_group_rows, int u_group_stride, int u_group_row0,
+                              int dst_group_rows, int dst_group_stride, int dst_group_row0,
+                              void* stream) {
+    PT_REQUIRE(g && u && w && dst, "pt_rmsnorm_bwd: null pointer");
+    PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0, "pt_rmsnorm_bwd: D must be a positive multiple of 8");
+    PT_REQUIRE(dst_dtype == PT_BF16 || dst_dtype == PT_F32, "pt_rmsnorm_bwd: bad dst dtype");
+    PT_REQUIRE(dst_dtype == PT_F32 || add_f32 == nullptr, "pt_rmsnorm_bwd: add only with f32 dst");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    RowMap um{u_group_rows, u_group_stride, u_group_row0};
+    RowMap dm{dst_group_rows, dst_group_stride, dst_group_row0};
+    __nv_bfloat16* db = dst_dtype == PT_BF16 ? static_cast<__nv_bfloat16*>(dst) : nullptr;
+    float* df = dst_dtype == PT_F32 ? static_cast<float*>(dst) : nullptr;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nb = row_blocks(rows), nt = kWarpsPerBlock * 32;
+#define PT_LAUNCH_RB(TG, TU)                                                                      \
+    rmsnorm_bwd_kernel<TG, TU><<<nb, nt, 0, st>>>(static_cast<const TG*>(g), static_cast<const TU*>(u), \
+                                                  w, db, df, add_f32, rows, D, eps, um, dm)
+    if (g_dtype == PT_F32 && u_dtype == PT_BF16) PT_LAUNCH_RB(float, __nv_bfloat16);
+    else if (g_dtype == PT_BF16 && u_dtype == PT_F32) PT_LAUNCH_RB(__nv_bfloat16, float);
+    else if (g_dtype == PT_BF16 && u_dtype == PT_BF16) PT_LAUNCH_RB(__nv_bfloat16, __nv_bfloat16);
+    else if (g_dtype == PT_F32 && u_dtype == PT_F32) PT_LAUNCH_RB(float, float);
+    else { set_error("pt_rmsnorm_bwd: unsupported dtype combination"); return PT_ERR_INVALID; }
+#undef PT_LAUNCH_RB
+    return check_launch("rmsnorm_bwd");
+}
+
+extern "C" int pt_gather_cast_rows(const float* x, void* out_bf16, int rows_out, int D, int group_rows_out,
+                                   int group_rows_in, int group_row0, void* stream) {
+    PT_REQUIRE(x && out_bf16 && rows_out > 0 && D > 0 && D % 8 == 0, "pt_gather_cast_rows: bad arguments");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    RowMap m{group_rows_out, group_rows_in, group_row0};
+    gather_cast_rows_kernel<<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, static_cast<__nv_bfloat16*>(out_bf16), rows_out, D, m);
+    return check_launch("gather_cast_rows");
+}

@@ -1,0 +1,431 @@
+"""Stage-1 step engine: orchestrates the sm_100a kernels (via the C ABI) for
+
+    frozen SigLIP forward -> projector fwd -> splice -> frozen Gemma3 fwd -> masked CE
+    -> input-gradient-only backward -> projector wgrads -> clip + AdamW
+
+mirroring ref:Stage1/projector_trainer.py:152-245.  torch supplies device memory and
+streams only; no torch math runs on the hot path and there is no CPU fallback.
+
+Numerics (bf16 mode = what `accelerate launch --mixed_precision bf16` gives the reference):
+bf16 GEMM operands with fp32 accumulation, fp32 residual streams, fp32 norm / softmax /
+cross-entropy internals, fp32 projector master weights, gradients and AdamW state.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import ops
+from .config import GemmaCfg, SiglipCfg
+from .ops import ACT_GELU_ERF, ACT_GELU_TANH
+
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def rope_tables(S: int, hd: int, theta: float, factor: float, device):
+    """cos/sin [S, hd/2] in fp32 (HF:models/gemma3/modeling_gemma3.py:216-230).  One-time setup
+    (inv_freq on the host as HF does), not part of the per-step path."""
+    inv = 1.0 / (theta ** (torch.arange(0, hd, 2, dtype=torch.float32) / hd)) / factor
+    ang = torch.arange(S, dtype=torch.float32)[:, None] * inv[None, :]
+    return ang.cos().to(device).contiguous(), ang.sin().to(device).contiguous()
+
+
+class PackedSiglip:
+    """Frozen SigLIP weights: bf16 matrices, fp32 vectors."""
+
+    def __init__(self, W: dict, cfg: SiglipCfg, device):
+        self.cfg = cfg
+        bf = lambda t: t.detach().to(device=device, dtype=BF16).contiguous()
+        f32 = lambda t: t.detach().to(device=device, dtype=F32).contiguous()
+        self.patch_w, self.patch_b, self.pos = bf(W["patch_w"]), f32(W["patch_b"]), f32(W["pos"])
+        self.post_g, self.post_b = f32(W["post_g"]), f32(W["post_b"])
+        self.layers = []
+        for l in range(cfg.layers):
+            p = f"l{l}."
+            self.layers.append(dict(
+                ln1_g=f32(W[p + "ln1_g"]), ln1_b=f32(W[p + "ln1_b"]),
+                ln2_g=f32(W[p + "ln2_g"]), ln2_b=f32(W[p + "ln2_b"]),
+                qkv_w=bf(W[p + "qkv_w"]), qkv_b=f32(W[p + "qkv_b"]),
+                o_w=bf(W[p + "o_w"]), o_b=f32(W[p + "o_b"]),
+                fc1_w=bf(W[p + "fc1_w"]), fc1_b=f32(W[p + "fc1_b"]),
+                fc2_w=bf(W[p + "fc2_w"]), fc2_b=f32(W[p + "fc2_b"])))
+
+
+class PackedGemma:
+    """Frozen Gemma3 text-decoder weights: bf16 matrices, fp32 norm gains."""
+
+    def __init__(self, W: dict, cfg: GemmaCfg, device):
+        self.cfg = cfg
+        bf = lambda t: t.detach().to(device=device, dtype=BF16).contiguous()
+        f32 = lambda t: t.detach().to(device=device, dtype=F32).contiguous()
+        self.embed = bf(W["embed"])
+        self.final_norm = f32(W["final_norm"])
+        # HF casts sqrt(hidden) to the embedding dtype before multiplying (modeling_gemma3.py:102-113)
+        self.embed_scale = float(torch.tensor(cfg.hidden ** 0.5, dtype=BF16).float())
+        self.layers = []
+        for l in range(cfg.layers):
+            p = f"l{l}."
+            self.layers.append(dict(
+                in_norm=f32(W[p + "in_norm"]), post_attn_norm=f32(W[p + "post_attn_norm"]),
+                pre_ffn_norm=f32(W[p + "pre_ffn_norm"]), post_ffn_norm=f32(W[p + "post_ffn_norm"]),
+                q_norm=f32(W[p + "q_norm"]), k_norm=f32(W[p + "k_norm"]),
+                qkv_w=bf(W[p + "qkv_w"]), o_w=bf(W[p + "o_w"]),
+                gu_w=bf(W[p + "gu_w"]), down_w=bf(W[p + "down_w"])))
+
+
+class ProjectorState:
+    """fp32 master weights, gradients and AdamW moments in flat buffers; bf16 shadow for GEMMs.
+
+    Layout of every flat buffer: [W1 (mid x vd) | b1 (mid) | W2 (h x mid) | b2 (h)]
+    = state_dict order model.0.weight, model.0.bias, model.2.weight, model.2.bias
+    (ref:Stage1/projectors.py:16-20)."""
+
+    KEYS = ("model.0.weight", "model.0.bias", "model.2.weight", "model.2.bias")
+
+    def __init__(self, P: dict, device):
+        shapes = [tuple(P[k].shape) for k in self.KEYS]
+        sizes = [math.prod(s) for s in shapes]
+        # keep every segment 16-byte aligned
+        offs, o = [], 0
+        for n in sizes:
+            offs.append(o)
+            o += (n + 7) // 8 * 8
+        self.n = o
+        self.shapes, self.sizes, self.offs = shapes, sizes, offs
+        self.flat = torch.zeros(o, dtype=F32, device=device)
+        self.grad = torch.zeros(o, dtype=F32, device=device)
+        self.m = torch.zeros(o, dtype=F32, device=device)
+        self.v = torch.zeros(o, dtype=F32, device=device)
+        self.shadow = torch.zeros(o, dtype=BF16, device=device)
+        for k, off, n, s in zip(self.KEYS, offs, sizes, shapes):
+            self.flat[off:off + n].view(s).copy_(P[k].detach().to(device=device, dtype=F32))
+        self.refresh_shadow()
+        self.sumsq = torch.zeros(1, dtype=F32, device=device)
+        self.step = 0
+
+    def view(self, buf, i):
+        return buf[self.offs[i]:self.offs[i] + self.sizes[i]].view(self.shapes[i])
+
+    def refresh_shadow(self):
+        ops.cast_f32_bf16(self.flat, self.shadow)
+
+    @property
+    def w1(self): return self.view(self.shadow, 0)
+    @property
+    def w2(self): return self.view(self.shadow, 2)
+    @property
+    def b1(self): return self.view(self.flat, 1)
+    @property
+    def b2(self): return self.view(self.flat, 3)
+
+    def params(self):
+        return {k: self.view(self.flat, i) for i, k in enumerate(self.KEYS)}
+
+    def grads(self):
+        return {k: self.view(self.grad, i) for i, k in enumerate(self.KEYS)}
+
+
+class Stage1Engine:
+    """One data-parallel rank of the Stage-1 step on one B200."""
+
+    def __init__(self, vis: PackedSiglip, llm: PackedGemma, proj: ProjectorState, device,
+                 grad_accum: int = 1):
+        self.vis, self.llm, self.proj = vis, llm, proj
+        self.vcfg, self.lcfg = vis.cfg, llm.cfg
+        self.device = device
+        self.grad_accum = grad_accum
+        self._ws: dict = {}
+        self._rope: dict = {}
+        self.n_img = self.vcfg.tokens - 1      # ref:projector_trainer.py:173 drops token 0
+        self.saved = None
+
+    # ------------------------------------------------------------------ workspace
+    def buf(self, name, shape, dtype):
+        key = (name, tuple(shape), dtype)
+        t = self._ws.get(key)
+        if t is None:
+            t = torch.empty(shape, dtype=dtype, device=self.device)
+            self._ws[key] = t
+        return t
+
+    def rope(self, S, full: bool):
+        key = (S, full)
+        if key not in self._rope:
+            c = self.lcfg
+            self._rope[key] = rope_tables(S, c.hd, c.theta_global if full else c.theta_local,
+                                          c.rope_factor_global if full else 1.0, self.device)
+        return self._rope[key]
+
+    # ------------------------------------------------------------------ SigLIP forward
+    def vision_forward(self, pixels: torch.Tensor, drop_first: bool = True) -> torch.Tensor:
+        """pixels f32 [B,3,H,W] -> bf16 features [B*(N-1), d] (token 0 dropped, the reference's
+        `last_hidden_state[:, 1:, :]`) or [B*N, d] with drop_first=False."""
+        c, V = self.vcfg, self.vis
+        B = pixels.shape[0]
+        N, d, H, hd = c.tokens, c.hidden, c.heads, c.hd
+        M = B * N
+        cols = self.buf("v_cols", (M, 3 * c.patch ** 2), BF16)
+        ops.patchify(pixels, c.patch, cols)
+        x = self.buf("v_x", (M, d), F32)
+        # patch-embed GEMM, epilogue adds bias and the position table (broadcast over images)
+        ops.gemm_raw(M=N, N=d, K=cols.shape[1], A=cols, lda=cols.shape[1], B=V.patch_w,
+                     ldb=cols.shape[1], Cout=x, ldc=d, nz=(B, 1, 1), a_zs=(N * cols.shape[1], 0, 0),
+                     c_zs=(N * d, 0, 0), bias=V.patch_b, residual=V.pos, ldr=d, r_zs=(0, 0, 0))
+        a = self.buf("v_a", (M, d), BF16)
+        qkv = self.buf("v_qkv", (M, 3 * d), BF16)
+        ld = _pad8(N)
+        sc = self.buf("v_scores", (B * H, N, ld), F32)
+        P = self.buf("v_P", (B * H, N, ld), BF16)
+        o = self.buf("v_o", (M, d), BF16)
+        h1 = self.buf("v_h1", (M, c.ff), BF16)
+        for L in V.layers:
+            ops.layernorm_fwd(x, L["ln1_g"], L["ln1_b"], a, c.eps)
+            ops.linear(a, L["qkv_w"], bias=L["qkv_b"], out=qkv)
+            # scores[b,h] = q k^T / sqrt(hd)
+            ops.gemm_raw(M=N, N=N, K=hd, A=qkv, lda=3 * d, B=qkv, b_off=d, ldb=3 * d, Cout=sc,
+                         ldc=ld, nz=(H, B, 1), a_zs=(hd, N * 3 * d, 0), b_zs=(hd, N * 3 * d, 0),
+                         c_zs=(N * ld, H * N * ld, 0), alpha=hd ** -0.5)
+            ops.softmax_fwd(sc, P, None, B * H, N, N, ld, H, 0, 0)
+            # o[b,:,h,:] = P[b,h] v[b,:,h,:]   (v read in place, MN-major)
+            ops.gemm_raw(M=N, N=hd, K=N, A=P, lda=ld, B=qkv, b_off=2 * d, ldb=3 * d, b_mn=True,
+                         Cout=o, ldc=d, nz=(H, B, 1), a_zs=(N * ld, H * N * ld, 0),
+                         b_zs=(hd, N * 3 * d, 0), c_zs=(hd, N * d, 0))
+            ops.linear(o, L["o_w"], bias=L["o_b"], residual=x, out=x)
+            ops.layernorm_fwd(x, L["ln2_g"], L["ln2_b"], a, c.eps)
+            ops.linear(a, L["fc1_w"], bias=L["fc1_b"], act=ACT_GELU_TANH, out=h1)
+            ops.linear(h1, L["fc2_w"], bias=L["fc2_b"], residual=x, out=x)
+        if drop_first:
+            feat = self.buf("v_feat", (B * (N - 1), d), BF16)
+            ops.layernorm_fwd(x, V.post_g, V.post_b, feat, c.eps, group=(N - 1, N, 1))
+        else:
+            feat = self.buf("v_feat_all", (M, d), BF16)
+            ops.layernorm_fwd(x, V.post_g, V.post_b, feat, c.eps)
+        return feat
+
+    # ------------------------------------------------------------------ projector forward
+    def projector_forward(self, patch: torch.Tensor, out: torch.Tensor, *, rows_per_img: int,
+                          out_batch_stride: int, save: bool = True):
+        """out[b, 0:rows_per_img, :] (f32, row stride h, image stride out_batch_stride) =
+        W2 gelu_erf(W1 patch + b1) + b2   (ref:Stage1/projectors.py:16-20)."""
+        Pj = self.proj
+        R, vd = patch.shape
+        mid, h = Pj.shapes[0][0], Pj.shapes[2][0]
+        Z = self.buf("p_Z", (R, mid), BF16) if save else None
+        Hm = self.buf("p_H", (R, mid), BF16)
+        ops.linear(patch, Pj.w1, bias=Pj.b1, act=ACT_GELU_ERF, out=Hm, c_pre=Z)
+        Bn = R // rows_per_img
+        ops.gemm_raw(M=rows_per_img, N=h, K=mid, A=Hm, lda=mid, B=Pj.w2, ldb=mid, Cout=out, ldc=h,
+                     nz=(Bn, 1, 1), a_zs=(rows_per_img * mid, 0, 0), c_zs=(out_batch_stride, 0, 0),
+                     bias=Pj.b2)
+        return Z, Hm
+
+    # ------------------------------------------------------------------ Gemma3 attention helpers
+    def _attn_geometry(self, B, S):
+        c = self.lcfg
+        G = c.hq // c.hkv
+        ld = _pad8(S)
+        QKV = (c.hq + 2 * c.hkv) * c.hd
+        return G, ld, QKV
+
+    def _scores_like(self, A, a_off, lda, a_zs, Bm, b_off, ldb, b_zs, out, B, S, alpha, b_mn=False):
+        """out[b, kvh*G+g, q, k] (f32, ld) = alpha * A_row(q) . B_row(k) over hd, batched (g, kvh, b)."""
+        c = self.lcfg
+        G, ld, _ = self._attn_geometry(B, S)
+        ops.gemm_raw(M=S, N=S, K=c.hd, A=A, a_off=a_off, lda=lda, B=Bm, b_off=b_off, ldb=ldb,
+                     Cout=out, ldc=ld, nz=(G, c.hkv, B), a_zs=a_zs, b_zs=b_zs,
+                     c_zs=(S * ld, G * S * ld, c.hq * S * ld), alpha=alpha)
+
+    # ------------------------------------------------------------------ LLM forward + loss
+    def llm_forward_loss(self, x0: torch.Tensor, keyvalid: torch.Tensor, targets: torch.Tensor,
+                         B: int, S: int, T: int, save: bool = True) -> torch.Tensor:
+        """x0 f32 [B*S, h] spliced embeddings -> device scalar loss; leaves dlogits in place and the
+        activations the input-gradient backward needs in self.saved."""
+        c, Lm = self.lcfg, self.llm
+        h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
+        M = B * S
+        G, ld, QKV = self._attn_geometry(B, S)
+        scale = c.q_scalar ** -0.5
+        sv = []
+        a = self.buf("l_a", (M, h), BF16)
+        sc = self.buf("l_scores", (B * hq, S, ld), F32)
+        attn_o = self.buf("l_attn_o", (M, hq * hd), BF16)
+        act = self.buf("l_act", (M, ff), BF16)
+        x = x0
+        ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
+        for li, L in enumerate(Lm.layers):
+            tag = f"l{li}_" if save else "l_"
+            full = c.is_full(li)
+            cos_t, sin_t = self.rope(S, full)
+            qkv = self.buf(tag + "qkv", (M, QKV), BF16)
+            q_post = self.buf(tag + "q", (M, hq * hd), BF16)
+            k_post = self.buf(tag + "k", (M, hkv * hd), BF16)
+            P = self.buf(tag + "P", (B * hq, S, ld), BF16)
+            y_attn = self.buf(tag + "ya", (M, h), BF16)
+            x1 = self.buf(tag + "x1", (M, h), F32)
+            gu = self.buf(tag + "gu", (M, 2 * ff), BF16)
+            y_mlp = self.buf(tag + "ym", (M, h), BF16)
+            x2 = self.buf(tag + "x2", (M, h), F32)
+            ops.linear(a, L["qkv_w"], out=qkv)
+            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, S, hq,
+                                hkv, hd, c.eps)
+            self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
+                              (0, hd, S * hkv * hd), sc, B, S, scale)
+            ops.softmax_fwd(sc, P, keyvalid, B * hq, S, S, ld, hq, 1, 0 if full else c.window)
+            # attn_o[b, q, head, :] = P[b, head] V[b, :, kvh, :]   (V in place inside qkv, MN-major)
+            ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, B=qkv, b_off=(hq + hkv) * hd, ldb=QKV, b_mn=True,
+                         Cout=attn_o, ldc=hq * hd, nz=(G, hkv, B),
+                         a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * QKV),
+                         c_zs=(hd, G * hd, S * hq * hd))
+            ops.linear(attn_o, L["o_w"], out=y_attn)
+            ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            ops.linear(a, L["gu_w"], out=gu)
+            ops.geglu_fwd(gu, act)
+            ops.linear(act, L["down_w"], out=y_mlp)
+            last = li == len(Lm.layers) - 1
+            ops.rmsnorm_residual_fwd(y_mlp, L["post_ffn_norm"], x1, x2,
+                                     None if last else Lm.layers[li + 1]["in_norm"],
+                                     None if last else a, c.eps)
+            sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ya=y_attn, x1=x1, gu=gu,
+                           ym=y_mlp, full=full))
+            x = x2
+        # final norm only on rows that can carry a label: positions n_img-1 .. S-2 of every sample
+        R = B * T
+        yf = self.buf("l_yf", (R, h), BF16)
+        ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(T, S, S - T - 1))
+        logits = self.buf("l_logits", (R, c.vocab), BF16)
+        ops.linear(yf, Lm.embed, out=logits)
+        tgt = self.buf("l_tgt", (R,), torch.int32)
+        # targets[b, n_img-1+t] for t in 0..T-1 -> compact [B*T] (int copy: plumbing, not arithmetic)
+        tgt.view(B, T).copy_(targets.view(B, S)[:, S - T - 1:S - 1])
+        lse = self.buf("l_lse", (R,), F32)
+        acc2 = self.buf("l_acc2", (2,), F32)
+        loss = self.buf("l_loss", (1,), F32)
+        ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.grad_accum)
+        self.saved = dict(layers=sv, x_final=x, logits=logits, B=B, S=S, T=T) if save else None
+        return loss
+
+    # ------------------------------------------------------------------ LLM backward (input grads only)
+    def llm_backward(self) -> torch.Tensor:
+        """Consumes self.saved; returns dL/dx0 as f32 [B*S, h] (weights are frozen: no wgrad GEMMs)."""
+        c, Lm, s = self.lcfg, self.llm, self.saved
+        B, S, T = s["B"], s["S"], s["T"]
+        h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
+        M, R = B * S, B * T
+        G, ld, QKV = self._attn_geometry(B, S)
+        scale = c.q_scalar ** -0.5
+        d_yf = self.buf("b_dyf", (R, h), BF16)
+        ops.linear_dgrad(s["logits"], Lm.embed, out=d_yf)          # dlogits @ E
+        dx = self.buf("b_dx", (M, h), F32)
+        dx.zero_()
+        grp = (T, S, S - T - 1)
+        ops.rmsnorm_bwd(d_yf, s["x_final"], Lm.final_norm, dx, c.eps, rows=R, u_group=grp, dst_group=grp)
+        d_y = self.buf("b_dy", (M, h), BF16)
+        d_act = self.buf("b_dact", (M, ff), BF16)
+        d_gu = self.buf("b_dgu", (M, 2 * ff), BF16)
+        d_o = self.buf("b_do", (M, hq * hd), BF16)
+        dP = self.buf("l_scores", (B * hq, S, ld), F32)            # reuse the forward score buffer
+        dS = self.buf("b_dS", (B * hq, S, ld), BF16)
+        dq = self.buf("b_dq", (M, hq * hd), BF16)
+        dk = self.buf("b_dk", (M, hkv * hd), BF16)
+        d_qkv = self.buf("b_dqkv", (M, QKV), BF16)
+        for li in range(len(Lm.layers) - 1, -1, -1):
+            L, a = Lm.layers[li], s["layers"][li]
+            cos_t, sin_t = self.rope(S, a["full"])
+            # ---- MLP branch
+            ops.rmsnorm_bwd(dx, a["ym"], L["post_ffn_norm"], d_y, c.eps)
+            ops.linear_dgrad(d_y, L["down_w"], out=d_act)
+            ops.geglu_bwd(d_act, a["gu"], d_gu)
+            ops.linear_dgrad(d_gu, L["gu_w"], out=d_y)
+            ops.rmsnorm_bwd(d_y, a["x1"], L["pre_ffn_norm"], dx, c.eps, add=dx)
+            # ---- attention branch
+            ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
+            ops.linear_dgrad(d_y, L["o_w"], out=d_o)
+            # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
+            self._scores_like(d_o, 0, hq * hd, (hd, G * hd, S * hq * hd), a["qkv"], (hq + hkv) * hd,
+                              QKV, (0, hd, S * QKV), dP, B, S, 1.0)
+            ops.softmax_bwd(a["P"], dP, dS, B * hq * S, S, ld, scale)
+            # dV[b,k,kvh,:] = sum_g P[b,kvh*G+g]^T dO[b,:,kvh*G+g,:]  -> v columns of d_qkv
+            ops.gemm_raw(M=S, N=hd, K=S, A=a["P"], lda=ld, a_mn=True, B=d_o, ldb=hq * hd, b_mn=True,
+                         Cout=d_qkv, c_off=(hq + hkv) * hd, ldc=QKV, nz=(hkv, B, 1),
+                         a_zs=(G * S * ld, hq * S * ld, 0), b_zs=(G * hd, S * hq * hd, 0),
+                         c_zs=(hd, S * QKV, 0), kg=G, a_kgs=S * ld, b_kgs=hd)
+            # dQ[b,q,head,:] = dS[b,head] K[b,:,kvh,:]
+            ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
+                         ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
+                         b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd))
+            # dK[b,k,kvh,:] = sum_g dS[b,kvh*G+g]^T Q[b,:,kvh*G+g,:]
+            ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, a_mn=True, B=a["q"], ldb=hq * hd, b_mn=True,
+                         Cout=dk, ldc=hkv * hd, nz=(hkv, B, 1), a_zs=(G * S * ld, hq * S * ld, 0),
+                         b_zs=(G * hd, S * hq * hd, 0), c_zs=(hd, S * hkv * hd, 0), kg=G,
+                         a_kgs=S * ld, b_kgs=hd)
+            ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
+                                hkv, hd, c.eps)
+            ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)
+            ops.rmsnorm_bwd(d_y, a["x_in"], L["in_norm"], dx, c.eps, add=dx)
+        return dx
+
+    # ------------------------------------------------------------------ projector backward
+    def projector_backward(self, dx: torch.Tensor, patch: torch.Tensor, Z: torch.Tensor,
+                           Hm: torch.Tensor, B: int, S: int):
+        """dL/dX0[:, :n_img] -> the four projector gradients (flat f32 buffer), no gradient to the
+        vision features (ref:Stage1/projectors.py:16-20 under autograd, projector_trainer.py:237)."""
+        Pj = self.proj
+        n_img = self.n_img
+        R = B * n_img
+        mid, h = Pj.shapes[0][0], Pj.shapes[2][0]
+        dP = self.buf("p_dP", (R, h), BF16)
+        ops.gather_cast_rows(dx, dP, group=(n_img, S, 0))
+        g = Pj.grad
+        ops.linear_wgrad(dP, Hm, out=Pj.view(g, 2))                 # dW2 = dP^T Hm
+        ops.colsum(dP, Pj.view(g, 3))                               # db2
+        dH = self.buf("p_dH", (R, mid), BF16)
+        ops.linear_dgrad(dP, Pj.w2, out=dH)                         # dH = dP W2
+        ops.gelu_erf_bwd(dH, Z, dH)                                 # dZ in place
+        ops.linear_wgrad(dH, patch, out=Pj.view(g, 0))              # dW1 = dZ^T patch
+        ops.colsum(dH, Pj.view(g, 1))                               # db1
+
+    # ------------------------------------------------------------------ optimizer
+    def optimizer_step(self, lr: float, *, weight_decay: float = 0.01, max_norm: float = 5.0,
+                       beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8,
+                       grad_scale: float = 1.0):
+        """clip_grad_norm_(5.0) + AdamW on the flat projector buffer
+        (ref:Stage1/projector_trainer.py:241-243); refreshes the bf16 shadow weights."""
+        Pj = self.proj
+        Pj.step += 1
+        ops.sumsq(Pj.grad, Pj.sumsq)
+        ops.clip_adamw(Pj.flat, Pj.grad, Pj.m, Pj.v, Pj.shadow, Pj.sumsq, grad_scale=grad_scale,
+                       max_norm=max_norm, lr=lr, beta1=beta1, beta2=beta2, eps=eps, wd=weight_decay,
+                       step=Pj.step)
+
+    # ------------------------------------------------------------------ whole step
+    def splice(self, token_ids: torch.Tensor, labels: torch.Tensor, x0: torch.Tensor, pad_id):
+        B, T = token_ids.shape
+        S = self.n_img + T
+        attn_mask = self.buf("s_mask", (B, S), torch.int64)
+        lm_labels = self.buf("s_labels", (B, S), torch.int64)
+        keyvalid = self.buf("s_kv", (B, S), torch.uint8)
+        targets = self.buf("s_tgt", (B, S), torch.int32)
+        ops.embed_splice(token_ids, labels, self.llm.embed, self.llm.embed_scale, pad_id, self.n_img,
+                         x0, attn_mask, lm_labels, keyvalid, targets)
+        return attn_mask, lm_labels, keyvalid, targets
+
+    def forward_backward(self, pixels: torch.Tensor, token_ids: torch.Tensor, labels: torch.Tensor,
+                         pad_id=0) -> torch.Tensor:
+        """Steps 1-8 of the reference loop (ref:Stage1/projector_trainer.py:157-237): returns the
+        device-resident scalar loss; projector gradients (of loss / grad_accum) land in proj.grad."""
+        B, T = token_ids.shape
+        S = self.n_img + T
+        h = self.lcfg.hidden
+        patch = self.vision_forward(pixels)
+        x0 = self.buf("x0", (B * S, h), F32)
+        Z, Hm = self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * h)
+        _, _, keyvalid, targets = self.splice(token_ids, labels, x0, pad_id)
+        loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, T)
+        dx = self.llm_backward()
+        self.projector_backward(dx, patch, Z, Hm, B, S)
+        return loss

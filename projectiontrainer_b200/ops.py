@@ -110,3 +110,130 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None) -> torch.Tensor
     gemm_raw(M=N, N=K, K=M, A=dy, lda=dy.stride(0), a_mn=True, B=x, ldb=x.stride(0), b_mn=True,
              Cout=out, ldc=out.stride(0))
     return out
+
+
+# --------------------------------------------------------------------------- bandwidth kernels
+def _i64(v):
+    return C.c_int64(int(v))
+
+
+def _f(v):
+    return C.c_float(float(v))
+
+
+def patchify(pixels: torch.Tensor, patch: int, out: torch.Tensor):
+    B, _, H, W = pixels.shape
+    _req_cuda(pixels, out)
+    _lib.call("pt_patchify", _ptr(pixels), _ptr(out), B, H, W, int(patch), _stream())
+
+
+def layernorm_fwd(x, gamma, beta, out, eps, *, group=(0, 0, 0)):
+    _req_cuda(x, out)
+    _lib.call("pt_layernorm_fwd", _ptr(x), _ptr(gamma), _ptr(beta), _ptr(out), out.shape[0],
+              x.shape[-1], _f(eps), *map(int, group), _stream())
+
+
+def rmsnorm_fwd(x, w, out, eps, *, group=(0, 0, 0)):
+    _req_cuda(x, out)
+    _lib.call("pt_rmsnorm_fwd", _ptr(x), _DT[x.dtype], _ptr(w), _ptr(out), out.shape[0],
+              x.shape[-1], _f(eps), *map(int, group), _stream())
+
+
+def rmsnorm_residual_fwd(y, w_post, x_in, x_out, w_next, nxt, eps):
+    _req_cuda(y, x_in, x_out)
+    _lib.call("pt_rmsnorm_residual_fwd", _ptr(y), _ptr(w_post), _ptr(x_in), _ptr(x_out),
+              _ptr(w_next), _ptr(nxt), y.shape[0], y.shape[1], _f(eps), _stream())
+
+
+def rmsnorm_bwd(g, u, w, dst, eps, *, add=None, rows=None, u_group=(0, 0, 0), dst_group=(0, 0, 0)):
+    _req_cuda(g, u, dst)
+    rows = g.shape[0] if rows is None else rows
+    _lib.call("pt_rmsnorm_bwd", _ptr(g), _DT[g.dtype], _ptr(u), _DT[u.dtype], _ptr(w), _ptr(dst),
+              _DT[dst.dtype], _ptr(add), int(rows), g.shape[-1], _f(eps), *map(int, u_group),
+              *map(int, dst_group), _stream())
+
+
+def qknorm_rope_fwd(qkv, wq, wk, cos_t, sin_t, q_out, k_out, S, hq, hkv, hd, eps):
+    _req_cuda(qkv, q_out, k_out)
+    _lib.call("pt_qknorm_rope_fwd", _ptr(qkv), _ptr(wq), _ptr(wk), _ptr(cos_t), _ptr(sin_t),
+              _ptr(q_out), _ptr(k_out), qkv.shape[0], int(S), hq, hkv, hd, _f(eps), _stream())
+
+
+def qknorm_rope_bwd(dq, dk, qkv, wq, wk, cos_t, sin_t, d_qkv, S, hq, hkv, hd, eps):
+    _req_cuda(dq, dk, qkv, d_qkv)
+    _lib.call("pt_qknorm_rope_bwd", _ptr(dq), _ptr(dk), _ptr(qkv), _ptr(wq), _ptr(wk), _ptr(cos_t),
+              _ptr(sin_t), _ptr(d_qkv), qkv.shape[0], int(S), hq, hkv, hd, _f(eps), _stream())
+
+
+def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window):
+    _req_cuda(scores, P, keyvalid)
+    _lib.call("pt_softmax_fwd", _ptr(scores), _ptr(P), _ptr(keyvalid), int(Z), int(Sq), int(Sk),
+              int(ld), int(heads_per_batch), int(causal), int(window), _stream())
+
+
+def softmax_bwd(P, dP, dS, rows, Sk, ld, scale):
+    _req_cuda(P, dP, dS)
+    _lib.call("pt_softmax_bwd", _ptr(P), _ptr(dP), _ptr(dS), C.c_longlong(int(rows)), int(Sk),
+              int(ld), _f(scale), _stream())
+
+
+def geglu_fwd(gu, act):
+    _req_cuda(gu, act)
+    _lib.call("pt_geglu_fwd", _ptr(gu), _ptr(act), C.c_longlong(gu.shape[0]), act.shape[1], _stream())
+
+
+def geglu_bwd(dact, gu, dgu):
+    _req_cuda(dact, gu, dgu)
+    _lib.call("pt_geglu_bwd", _ptr(dact), _ptr(gu), _ptr(dgu), C.c_longlong(gu.shape[0]),
+              dact.shape[1], _stream())
+
+
+def gelu_erf_bwd(dH, Z, dZ):
+    _req_cuda(dH, Z, dZ)
+    _lib.call("pt_gelu_erf_bwd", _ptr(dH), _ptr(Z), _ptr(dZ), C.c_longlong(dH.numel()), _stream())
+
+
+def embed_splice(token_ids, labels, embed, scale, pad_id, n_img, x0, attn_mask, lm_labels,
+                 keyvalid, targets):
+    _req_cuda(token_ids, labels, embed, x0, attn_mask, lm_labels, keyvalid, targets)
+    B, T = token_ids.shape
+    has_pad = pad_id is not None
+    _lib.call("pt_embed_splice", _ptr(token_ids), _ptr(labels), _ptr(embed), _f(scale),
+              _i64(pad_id if has_pad else 0), int(has_pad), B, T, int(n_img), embed.shape[1],
+              _ptr(x0), _ptr(attn_mask), _ptr(lm_labels), _ptr(keyvalid), _ptr(targets), _stream())
+
+
+def ce_fwd_bwd(logits, targets, lse, acc2, loss, gscale):
+    _req_cuda(logits, targets, lse, acc2, loss)
+    rows, V = logits.shape
+    _lib.call("pt_ce_fwd_bwd", _ptr(logits), C.c_longlong(logits.stride(0)), _ptr(targets), rows, V,
+              _ptr(lse), _ptr(acc2), _ptr(loss), _f(gscale), _stream())
+
+
+def colsum(x, out):
+    _req_cuda(x, out)
+    _lib.call("pt_colsum", _ptr(x), C.c_longlong(x.stride(0)), _ptr(out), x.shape[0], x.shape[1],
+              _stream())
+
+
+def sumsq(g, out):
+    _req_cuda(g, out)
+    _lib.call("pt_sumsq", _ptr(g), C.c_longlong(g.numel()), _ptr(out), _stream())
+
+
+def clip_adamw(p, g, m, v, shadow, sumsq_t, *, grad_scale, max_norm, lr, beta1, beta2, eps, wd, step):
+    _req_cuda(p, g, m, v, shadow, sumsq_t)
+    _lib.call("pt_clip_adamw", _ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(shadow),
+              C.c_longlong(p.numel()), _ptr(sumsq_t), _f(grad_scale), _f(max_norm), _f(lr),
+              _f(beta1), _f(beta2), _f(eps), _f(wd), int(step), _stream())
+
+
+def cast_f32_bf16(x, y):
+    _req_cuda(x, y)
+    _lib.call("pt_cast_f32_bf16", _ptr(x), _ptr(y), C.c_longlong(x.numel()), _stream())
+
+
+def gather_cast_rows(x, out, *, group=(0, 0, 0)):
+    _req_cuda(x, out)
+    _lib.call("pt_gather_cast_rows", _ptr(x), _ptr(out), out.shape[0], out.shape[1],
+              *map(int, group), _stream())
