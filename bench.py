@@ -1,0 +1,279 @@
+#!/usr/bin/env python
+"""Stage-1 projector-train throughput benchmark (BASELINE.json metric) — see DESIGN.md §Measurement.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --gpus N --steps K ...  # CPU reference arm (oracle port)
+
+Workload = BASELINE.json configs[2] ("config 3" in SURVEY.md): SigLIP-L/16-384 + MLP(1024->10240->1152)
++ Gemma3-1B, 128 caption tokens, batch 32 per GPU, bf16, data-parallel; synthetic CXR-shaped data,
+random-init weights.  One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "stage1_projector_train_images_per_sec"
+UNIT = "images/s"
+B_PER_GPU, T_TOK = 32, 128
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=B_PER_GPU)
+    ap.add_argument("--tokens", type=int, default=T_TOK)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile", action="store_true",
+                    help="ncu helper: 1 warm-up step + --steps steps, nothing else, no JSON value")
+    ap.add_argument("--cpu-budget-s", type=float, default=150.0)
+    return ap.parse_args()
+
+
+def workload_config(args, n):
+    return {"workload": "BASELINE.json configs[2]: Stage-1 projector training step, SigLIP-L/16-384 + "
+                        "MLP(1024->10240->1152) + Gemma3-1B, 128 caption tokens (S=575+128=703), bf16, "
+                        "data-parallel",
+            "batch_per_gpu": args.batch, "global_batch": args.batch * n, "caption_tokens": args.tokens,
+            "parallelism": f"dp{n}", "l2": "per-step working set (>30 GB of activations) >> 126 MB L2, no flush"}
+
+
+# --------------------------------------------------------------------------------------------- CPU arm
+def cpu_step_sample(budget_s: float, steps: int, warmup: int, tokens: int):
+    """Times the oracle port of the reference step on the host cores: each step = ONE image of the
+    workload (B=1, T=tokens, full-size SigLIP-L + projector + Gemma3-1B, fp32), all host threads."""
+    import torch
+    from oracle import stage1_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    cores = torch.get_num_threads()
+    vc, lc = O.SIGLIP_L, O.GEMMA3_1B
+    t0 = time.time()
+    Wv, Wl = O.init_siglip(vc), O.init_gemma(lc)
+    P = O.init_projector(vc.hidden, lc.hidden)
+    init_s = time.time() - t0
+    times = []
+    done_w = 0
+    t_start = time.time()
+    for i in range(warmup + steps):
+        px, ids, lab = O.synthetic_batch(1, tokens, vc, lc, seed=1234 + i)
+        t1 = time.time()
+        O.stage1_step(px, ids, lab, Wv, P, Wl, vc, lc)
+        dt = time.time() - t1
+        if i >= warmup:
+            times.append(dt)
+        else:
+            done_w += 1
+        if time.time() - t_start > budget_s and len(times) >= 1:
+            break
+    mean = sum(times) / len(times)
+    return dict(value=1.0 / mean, unit=UNIT, cores=cores, kind="port",
+                sample=f"{len(times)} timed step(s) of 1 image each (B=1, T={tokens}, S={575 + tokens}, fp32, "
+                       f"full-size models, oracle/stage1_oracle.py; {done_w} warm-up; weight init {init_s:.0f}s "
+                       f"not timed)"), len(times), done_w, mean
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb, k, w, mean = cpu_step_sample(args.cpu_budget_s, args.steps, min(args.warmup, 1), args.tokens)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": k, "warmup": w, "ms_per_step": mean * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, args.gpus),
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append((time.time(), ln.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, ln in self.rows:
+            if ts < t0 or ts > t1:
+                continue
+            f = [x.strip() for x in ln.split(",")]
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except Exception:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from projectiontrainer_b200 import _lib, ops
+    from projectiontrainer_b200.config import GEMMA3_1B, SIGLIP_L
+    from projectiontrainer_b200.engine import build_engine
+    from projectiontrainer_b200.flops import stage1_flops_per_image
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (impl=ours) needs a B200: there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    allreduce = (lambda g: dist.all_reduce(g)) if world > 1 else None
+
+    vc, lc = SIGLIP_L, GEMMA3_1B
+    B, T = args.batch, args.tokens
+    eng = build_engine(vc, lc, dev, seed=0, grad_accum=1)
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    px = torch.rand(B, 3, vc.image, vc.image, generator=g, device=dev) * 2 - 1
+    ids = torch.randint(3, lc.vocab, (B, T), generator=g, device=dev)
+    ids[:, 0] = 2
+    lab = ids.clone()
+    dev_batch = {"pixel_values": px, "token_ids": ids, "labels": lab}
+    host_batch = {k: v.cpu().pin_memory() for k, v in dev_batch.items()}
+    lr = 1e-4
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(batch):
+        return eng.train_step(batch, lr, pad_id=lc.pad_id, allreduce=allreduce, world_size=world)
+
+    if args.profile:
+        step(dev_batch)
+        sync()
+        n0 = _lib.launch_count
+        for _ in range(args.steps):
+            step(dev_batch)
+        sync()
+        print(json.dumps({"profile_run": True, "launches_per_step": (_lib.launch_count - n0) // args.steps}))
+        return
+    for _ in range(max(args.warmup, 3)):
+        step(dev_batch)
+    sync()
+    sampler = ClockSampler(local) if rank == 0 else None
+    # ---- device-resident timed region
+    n0 = _lib.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    t_wall0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        loss = step(dev_batch)
+    e1.record()
+    sync()
+    t_wall1 = time.time()
+    ms = e0.elapsed_time(e1)
+    launches = _lib.launch_count - n0
+    # ---- end-to-end: pinned host inputs copied in, loss read back, every step
+    for _ in range(2):
+        float(step(host_batch).item())
+    sync()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        lv = float(step(host_batch).item())
+    e3.record()
+    sync()
+    ms_e2e = e2.elapsed_time(e3)
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = t.tolist()
+
+    # ---- roofline pass for the dominant kernel (gemm_bf16_kernel): CUDA events around every launch
+    roof = None
+    if rank == 0:
+        ops.GEMM_PROFILE = []
+        step(dev_batch)
+        torch.cuda.synchronize()
+        prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
+        fl = sum(p[0] for p in prof)
+        tm = sum(p[1].elapsed_time(p[2]) for p in prof)
+        peaks = {}
+        pk = ROOT / "MEASURED_PEAKS.json"
+        which = "fallback"
+        peak = 1400.0
+        if pk.exists():
+            peaks = json.loads(pk.read_text())
+            peak, which = float(peaks.get("bf16_tflops_sustained", 1400.0)), "measured(bf16_tflops_sustained)"
+        ach = fl / (tm * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "gemm_bf16_kernel (all GEMM launches of one step)",
+                "achieved": ach, "peak": peak, "peak_source": which, "unit": "TFLOP/s", "frac": ach / peak,
+                "launches": len(prof), "flops_per_launch": fl / len(prof), "avg_launch_ms": tm / len(prof),
+                "gemm_ms_per_step": tm, "traffic": None}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    fpi = stage1_flops_per_image(vc, lc, T)["train"]
+    ips = args.steps * B * world / (ms * 1e-3)
+    ips_e2e = args.steps * B * world / (ms_e2e * 1e-3)
+    h2d = sum(v.numel() * v.element_size() for v in host_batch.values())
+    line = {"metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": workload_config(args, world),
+            "e2e": {"value": ips_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "step_tflops_per_gpu": ips / world * fpi / 1e12, "flops_per_image": fpi, "last_loss": lv}
+    if world == 1 and not args.no_cpu_baseline:
+        del eng
+        torch.cuda.empty_cache()
+        cb, *_ = cpu_step_sample(30.0, 1, 0, args.tokens)
+        line["cpu_baseline"] = cb
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

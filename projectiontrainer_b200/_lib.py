@@ -57,6 +57,13 @@ def check(rc: int, what: str) -> None:
         raise RuntimeError(f"{what} failed (status {rc}): {last_error()}")
 
 
+# kernels launched per C-ABI call (for the bench's gpu_launches claim)
+KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3}
+launch_count = 0
+
+
 def call(name: str, *args) -> None:
+    global launch_count
     fn = getattr(lib(), name)
     check(fn(*args), name)
+    launch_count += KERNELS_PER_CALL.get(name, 1)

@@ -429,3 +429,30 @@ class Stage1Engine:
         dx = self.llm_backward()
         self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
+
+    def train_step(self, batch: dict, lr: float, *, pad_id=0, weight_decay: float = 0.01,
+                   allreduce=None, world_size: int = 1) -> torch.Tensor:
+        """One optimizer step from a (host or device) batch dict with the reference's keys
+        `pixel_values`, `token_ids`, `labels` (ref:Stage1/train_projection_stage1.py:114-118).
+        Host tensors are copied in (non_blocking from pinned memory).  `allreduce(flat_grad)` sums
+        the flat gradient over ranks (NCCL); the 1/world mean is folded into the optimizer kernel.
+        Returns the device scalar loss (no host sync here)."""
+        dev = self.device
+        px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
+        ids = batch["token_ids"].to(dev, non_blocking=True)
+        lab = batch["labels"].to(dev, non_blocking=True)
+        loss = self.forward_backward(px, ids, lab, pad_id)
+        if allreduce is not None and world_size > 1:
+            allreduce(self.proj.grad)
+        self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size)
+        return loss
+
+
+def build_engine(vcfg: SiglipCfg, lcfg: GemmaCfg, device, seed: int = 0, grad_accum: int = 1,
+                 expansion: int = 10) -> Stage1Engine:
+    """Random-init engine for benchmarks and smoke tests (synthetic weights, generated on device)."""
+    from . import weights as Wt
+    vis = PackedSiglip(Wt.random_siglip(vcfg, device, seed), vcfg, device)
+    llm = PackedGemma(Wt.random_gemma(lcfg, device, seed), lcfg, device)
+    proj = ProjectorState(Wt.random_projector(vcfg.hidden, lcfg.hidden, device, expansion, seed), device)
+    return Stage1Engine(vis, llm, proj, device, grad_accum=grad_accum)

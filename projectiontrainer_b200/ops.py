@@ -15,6 +15,10 @@ from ._lib import ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmAr
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
+# When set to a list, every GEMM launch is bracketed by CUDA events on the launching stream and
+# (flops, start, end, shape) is appended (bench.py's roofline pass; never set on the timed path).
+GEMM_PROFILE = None
+
 
 def _stream() -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -69,6 +73,14 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     g.kg = int(kg)
     g.a_kgs = int(a_kgs)
     g.b_kgs = int(b_kgs)
+    if GEMM_PROFILE is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.call("pt_gemm_bf16", C.byref(g), _stream())
+        e1.record()
+        nb = int(nz[0]) * int(nz[1]) * int(nz[2])
+        GEMM_PROFILE.append((2.0 * M * N * K * nb * max(1, int(kg)), e0, e1, (M, N, K, nb, int(kg))))
+        return
     _lib.call("pt_gemm_bf16", C.byref(g), _stream())
 
 

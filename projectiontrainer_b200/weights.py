@@ -1,0 +1,106 @@
+"""Weight containers -> the flat name scheme the engine packs from.
+
+HF modules are accepted as *weight containers only*: their parameters are read once and
+repacked (fused qkv / gate-up matrices, bf16 matrices, fp32 vectors); none of their forward
+code runs on the hot path.  Unsupported architectures are rejected loudly.
+"""
+from __future__ import annotations
+
+import torch
+
+from .config import GemmaCfg, SiglipCfg, gemma_cfg_from_hf, siglip_cfg_from_hf
+
+
+def siglip_from_hf(vision_model) -> tuple[dict, SiglipCfg]:
+    """vision_model: HF SiglipVisionTransformer (`SiglipModel.vision_model` /
+    `SiglipVisionModel.vision_model`), the object ref:Stage1/projector_trainer.py:165-171 calls."""
+    cfg = siglip_cfg_from_hf(vision_model.config)
+    sd = {k: v.detach() for k, v in vision_model.state_dict().items()}
+    d = cfg.hidden
+    W = {"patch_w": sd["embeddings.patch_embedding.weight"].reshape(d, -1),
+         "patch_b": sd["embeddings.patch_embedding.bias"],
+         "pos": sd["embeddings.position_embedding.weight"],
+         "post_g": sd["post_layernorm.weight"], "post_b": sd["post_layernorm.bias"]}
+    for l in range(cfg.layers):
+        s, p = f"encoder.layers.{l}.", f"l{l}."
+        W[p + "ln1_g"], W[p + "ln1_b"] = sd[s + "layer_norm1.weight"], sd[s + "layer_norm1.bias"]
+        W[p + "ln2_g"], W[p + "ln2_b"] = sd[s + "layer_norm2.weight"], sd[s + "layer_norm2.bias"]
+        W[p + "qkv_w"] = torch.cat([sd[s + f"self_attn.{n}_proj.weight"] for n in "qkv"], 0)
+        W[p + "qkv_b"] = torch.cat([sd[s + f"self_attn.{n}_proj.bias"] for n in "qkv"], 0)
+        W[p + "o_w"], W[p + "o_b"] = sd[s + "self_attn.out_proj.weight"], sd[s + "self_attn.out_proj.bias"]
+        W[p + "fc1_w"], W[p + "fc1_b"] = sd[s + "mlp.fc1.weight"], sd[s + "mlp.fc1.bias"]
+        W[p + "fc2_w"], W[p + "fc2_b"] = sd[s + "mlp.fc2.weight"], sd[s + "mlp.fc2.bias"]
+    return W, cfg
+
+
+def gemma_from_hf(causal_lm) -> tuple[dict, GemmaCfg]:
+    """causal_lm: HF Gemma3ForCausalLM (what AutoModelForCausalLM returns for gemma3_text,
+    ref:Stage1/train_projection_stage1.py:204)."""
+    cfg = gemma_cfg_from_hf(causal_lm.config)
+    sd = {k: v.detach() for k, v in causal_lm.state_dict().items()}
+    W = {"embed": sd["model.embed_tokens.weight"], "final_norm": sd["model.norm.weight"]}
+    if "lm_head.weight" in sd and sd["lm_head.weight"].data_ptr() != sd["model.embed_tokens.weight"].data_ptr():
+        if not torch.equal(sd["lm_head.weight"], sd["model.embed_tokens.weight"]):
+            raise RuntimeError("untied lm_head is not supported (Gemma3 ties it to embed_tokens)")
+    for l in range(cfg.layers):
+        s, p = f"model.layers.{l}.", f"l{l}."
+        W[p + "in_norm"] = sd[s + "input_layernorm.weight"]
+        W[p + "post_attn_norm"] = sd[s + "post_attention_layernorm.weight"]
+        W[p + "pre_ffn_norm"] = sd[s + "pre_feedforward_layernorm.weight"]
+        W[p + "post_ffn_norm"] = sd[s + "post_feedforward_layernorm.weight"]
+        W[p + "q_norm"], W[p + "k_norm"] = sd[s + "self_attn.q_norm.weight"], sd[s + "self_attn.k_norm.weight"]
+        W[p + "qkv_w"] = torch.cat([sd[s + f"self_attn.{n}_proj.weight"] for n in "qkv"], 0)
+        W[p + "o_w"] = sd[s + "self_attn.o_proj.weight"]
+        W[p + "gu_w"] = torch.cat([sd[s + "mlp.gate_proj.weight"], sd[s + "mlp.up_proj.weight"]], 0)
+        W[p + "down_w"] = sd[s + "mlp.down_proj.weight"]
+    return W, cfg
+
+
+# ----------------------------------------------------------------------------- synthetic weights
+def _r(gen, device, *shape, std=0.02):
+    return torch.randn(*shape, generator=gen, device=device, dtype=torch.float32) * std
+
+
+def random_siglip(cfg: SiglipCfg, device, seed: int = 0) -> dict:
+    """Random-init SigLIP weights generated on `device` (benchmarks: no checkpoints, no network)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    d, f = cfg.hidden, cfg.ff
+    W = {"patch_w": _r(g, device, d, 3 * cfg.patch ** 2, std=(3 * cfg.patch ** 2) ** -0.5),
+         "patch_b": _r(g, device, d), "pos": _r(g, device, cfg.tokens, d, std=d ** -0.5),
+         "post_g": 1 + _r(g, device, d, std=0.1), "post_b": _r(g, device, d, std=0.1)}
+    for l in range(cfg.layers):
+        p = f"l{l}."
+        W[p + "ln1_g"], W[p + "ln1_b"] = 1 + _r(g, device, d, std=0.1), _r(g, device, d, std=0.1)
+        W[p + "ln2_g"], W[p + "ln2_b"] = 1 + _r(g, device, d, std=0.1), _r(g, device, d, std=0.1)
+        W[p + "qkv_w"], W[p + "qkv_b"] = _r(g, device, 3 * d, d, std=d ** -0.5), _r(g, device, 3 * d)
+        W[p + "o_w"], W[p + "o_b"] = _r(g, device, d, d, std=d ** -0.5), _r(g, device, d)
+        W[p + "fc1_w"], W[p + "fc1_b"] = _r(g, device, f, d, std=d ** -0.5), _r(g, device, f)
+        W[p + "fc2_w"], W[p + "fc2_b"] = _r(g, device, d, f, std=f ** -0.5), _r(g, device, d)
+    return W
+
+
+def random_gemma(cfg: GemmaCfg, device, seed: int = 0) -> dict:
+    g = torch.Generator(device=device).manual_seed(seed + 1)
+    h = cfg.hidden
+    W = {"embed": _r(g, device, cfg.vocab, h).to(torch.bfloat16), "final_norm": _r(g, device, h, std=0.3)}
+    for l in range(cfg.layers):
+        p = f"l{l}."
+        for n in ("in_norm", "post_attn_norm", "pre_ffn_norm", "post_ffn_norm"):
+            W[p + n] = _r(g, device, h, std=0.3)
+        W[p + "q_norm"], W[p + "k_norm"] = _r(g, device, cfg.hd, std=0.3), _r(g, device, cfg.hd, std=0.3)
+        W[p + "qkv_w"] = _r(g, device, (cfg.hq + 2 * cfg.hkv) * cfg.hd, h).to(torch.bfloat16)
+        W[p + "o_w"] = _r(g, device, h, cfg.hq * cfg.hd).to(torch.bfloat16)
+        W[p + "gu_w"] = _r(g, device, 2 * cfg.ff, h).to(torch.bfloat16)
+        W[p + "down_w"] = _r(g, device, h, cfg.ff).to(torch.bfloat16)
+    return W
+
+
+def random_projector(vision_dim: int, llm_dim: int, device, expansion: int = 10, seed: int = 0) -> dict:
+    """nn.Linear default init: U(-1/sqrt(fan_in), 1/sqrt(fan_in)) for weight and bias."""
+    g = torch.Generator(device=device).manual_seed(seed + 2)
+    mid = vision_dim * expansion
+    u = lambda *s, bound: (torch.rand(*s, generator=g, device=device) * 2 - 1) * bound
+    return {"model.0.weight": u(mid, vision_dim, bound=vision_dim ** -0.5),
+            "model.0.bias": u(mid, bound=vision_dim ** -0.5),
+            "model.2.weight": u(llm_dim, mid, bound=mid ** -0.5),
+            "model.2.bias": u(llm_dim, bound=mid ** -0.5)}
