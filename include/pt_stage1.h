@@ -58,7 +58,9 @@ int pt_device_check(void);
  * The batch index z = (z0,z1,z2) (z0 fastest).  An operand whose stride for a
  * batch dim is 0 is broadcast along it.  Alignment: A/B base pointers 16 bytes,
  * lda/ldb and all A/B batch strides multiples of 8 elements; ldc (and ldr)
- * multiples of 8 (bf16) or 4 (f32) elements with 16-byte aligned bases.
+ * multiples of 8 (bf16) or 4 (f32) elements with 16-byte aligned bases.  Output columns are produced in
+ * quads: when N % 4 != 0 the columns N .. roundup4(N)-1 of C (which exist, since ldc >= roundup4(N)) are
+ * overwritten too (with zeros when there is no bias), and bias / residual require N % 4 == 0.
  * ------------------------------------------------------------------------- */
 typedef struct {
     int32_t M, N, K;
@@ -97,6 +99,10 @@ typedef struct {
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);
+/* Kernel selection for pt_gemm_bf16: 0 = default (CTA-pair tcgen05.mma.cta_group::2 kernel),
+ * 1 = single-CTA kernel, 2 = CTA-pair kernel.  Test / profiling aid; results are identical in value
+ * up to fp32 summation order (same K order: bit-identical accumulators). */
+int pt_set_gemm_impl(int impl);
 
 
 /* ------------------------------------------------------------------------- *

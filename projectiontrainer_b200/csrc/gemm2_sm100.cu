@@ -1,0 +1,417 @@
+// CTA-pair bf16 GEMM for sm_100a: tcgen05.mma.cta_group::2 (UMMA M = 256 over two SMs of a TPC).
+//
+// One cluster of two CTAs owns a 256 x BN output tile.  CTA r of the pair stages rows
+// [128 r, 128 r + 128) of the A tile and rows [BN/2 r, BN/2 (r+1)) of the B tile, so every operand byte
+// is fetched from L2 once per PAIR (half the L2->SM traffic per flop of the single-CTA kernel, which is
+// what bounded it), and the pair's accumulator lives in both CTAs' TMEM (128 lanes x BN columns each).
+//
+//   warp 0      TMA producer (one lane, both CTAs): cp.async.bulk.tensor ... cta_group::2, bytes credited
+//               to the LEADER CTA's full barrier
+//   warp 1      MMA issuer (one lane, leader CTA only); tcgen05.commit multicast frees the smem stage /
+//               publishes the accumulator in BOTH CTAs
+//   warp 2      TMEM allocator (cta_group::2, both CTAs)
+//   warps 4..11 epilogue: tcgen05.ld -> registers -> (alpha, bias, act) -> per-warp swizzled smem
+//               staging -> coalesced 16-byte global stores (+ residual), rows of this CTA's half
+//
+// Two accumulator stages (2 x BN <= 512 TMEM columns) overlap the epilogue of tile i with the main loop
+// of tile i+1.  Persistent: cluster c walks tiles c, c + #clusters, ...; inside one batch slice the
+// tile order runs fastest along the dimension with fewer tiles, so the operand panel that is re-read
+// across concurrently running tiles is the small one and stays in L2.
+#include "pt_common.cuh"
+#include "sm100_ptx.cuh"
+#include "gemm_common.cuh"
+
+namespace pt {
+
+constexpr int kGemm2Threads = 384;     // 4 control warps + 8 epilogue warps
+constexpr int kEpiWarps = 8;
+constexpr int kEpiStageBytes = 4096;   // per epilogue warp: 32 rows x 128 B
+constexpr int kSmemTotal = 232448;
+
+template <int BN>
+struct Gemm2Cfg {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int EPI_BYTES = kEpiWarps * kEpiStageBytes;
+    static constexpr int BAR_BYTES = 512;
+    static constexpr int STAGES_RAW = (kSmemTotal - 1024 - EPI_BYTES - BAR_BYTES) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+    static constexpr int ACC_STRIDE = 256;   // TMEM columns per accumulator stage
+};
+
+// ---- epilogue helper --------------------------------------------------------------------------
+// Thread `lane` holds the raw f32 accumulators of 32 consecutive columns of row `lane` of a 32-row slab.
+// They are transposed through a per-warp XOR-swizzled smem tile (32 rows x 128 B, conflict-free both
+// ways) so that everything touching global memory is row-contiguous: in the second phase lane l owns
+// the column quad 4 (l & 7) .. +3 of rows (l >> 3) + 4 it, it = 0..7 — its bias quad is loaded once, the
+// eight residual quads are loaded up front (independent loads; C may alias R element-wise), and each
+// row segment is written as 128 contiguous bytes (f32) or 64 (bf16) by 8 neighbouring lanes.
+// Column quads are all-or-nothing (N is rounded up to a multiple of 4: see pt_gemm_bf16's contract), which
+// keeps this straight-line code small — the epilogue is instruction-issue and I-cache sensitive.
+struct EpiArgs {
+    uint8_t* C;           // byte address of element (row 0 of the slab, column col0)
+    uint8_t* Cpre;        // same position (bf16) or nullptr
+    const uint8_t* R;     // same position or nullptr
+    const float* bias;    // bias + col0 or nullptr
+    long long c_step, p_step, r_step;   // bytes per 4 rows
+    long long c_row, p_row, r_row;      // bytes per row
+    int c_f32, r_f32;
+    float alpha;
+    int rows_valid;       // rows of the slab that exist (1..32)
+    int cols_q;           // columns of the chunk to produce, multiple of 4 (4..32)
+};
+
+template <int ACT>
+__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint8_t* stg, int lane, const EpiArgs& o) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+            make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    __syncwarp();
+    const int ch = lane & 7, c = ch * 4, rsub = lane >> 3;
+    if (c < o.cols_q) {
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (o.bias) b4 = __ldg(reinterpret_cast<const float4*>(o.bias + c));
+        const int nrows = o.rows_valid - rsub;          // rows rsub, rsub + 4, ... < rows_valid
+        float4 res[8];
+        if (o.R) {
+            const uint8_t* rp = o.R + rsub * o.r_row + c * (o.r_f32 ? 4 : 2);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                res[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (it * 4 < nrows) {
+                    if (o.r_f32) {
+                        res[it] = *reinterpret_cast<const float4*>(rp);
+                    } else {
+                        const uint2 q = *reinterpret_cast<const uint2*>(rp);
+                        res[it] = make_float4(bf16_lo(q.x), bf16_hi(q.x), bf16_lo(q.y), bf16_hi(q.y));
+                    }
+                }
+                rp += o.r_step;
+            }
+        }
+        uint8_t* cp = o.C + rsub * o.c_row + c * (o.c_f32 ? 4 : 2);
+        uint8_t* pp = o.Cpre ? o.Cpre + rsub * o.p_row + c * 2 : nullptr;
+        const uint8_t* sp = stg + rsub * 128;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + rsub;
+            const float4 a = *reinterpret_cast<const float4*>(sp + it * 512 + ((ch ^ (r & 7)) << 4));
+            if (it * 4 < nrows) {
+                float x0 = fmaf(a.x, o.alpha, b4.x), x1 = fmaf(a.y, o.alpha, b4.y);
+                float x2 = fmaf(a.z, o.alpha, b4.z), x3 = fmaf(a.w, o.alpha, b4.w);
+                if (pp) {
+                    uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
+                    *reinterpret_cast<uint2*>(pp) = u;
+                }
+                if (ACT == PT_ACT_GELU_TANH) {
+                    x0 = gelu_tanh_fast_f(x0); x1 = gelu_tanh_fast_f(x1);
+                    x2 = gelu_tanh_fast_f(x2); x3 = gelu_tanh_fast_f(x3);
+                } else if (ACT == PT_ACT_GELU_ERF) {
+                    x0 = gelu_erf_f(x0); x1 = gelu_erf_f(x1); x2 = gelu_erf_f(x2); x3 = gelu_erf_f(x3);
+                }
+                if (o.R) { x0 += res[it].x; x1 += res[it].y; x2 += res[it].z; x3 += res[it].w; }
+                if (o.c_f32) {
+                    *reinterpret_cast<float4*>(cp) = make_float4(x0, x1, x2, x3);
+                } else {
+                    uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
+                    *reinterpret_cast<uint2*>(cp) = u;
+                }
+            }
+            cp += o.c_step;
+            if (pp) pp += o.p_step;
+        }
+    }
+    __syncwarp();
+}
+
+// ---- kernel ----------------------------------------------------------------------------------------
+template <int BN, int ACT>
+__global__ void __launch_bounds__(kGemm2Threads, 1)
+gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const GemmDev p) {
+    using Cfg = Gemm2Cfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    constexpr int BNH = BN / 2;                 // B rows staged by each CTA
+    constexpr int TM = 2 * BM;                  // tile rows per cluster
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;
+    uint8_t* smem_epi = smem + STAGES * Cfg::STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + Cfg::EPI_BYTES);
+    uint64_t* full_bar = bars;                       // leader's are the live ones
+    uint64_t* empty_bar = bars + STAGES;             // per CTA (multicast commit)
+    uint64_t* tfull_bar = bars + 2 * STAGES;         // per CTA (multicast commit)
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2;    // leader's are the live ones
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const bool leader = rank == 0;
+
+    const int mt = (p.M + TM - 1) / TM;
+    const int nt = (p.N + BN - 1) / BN;
+    const int tiles_per_z = mt * nt;
+    const int total_tiles = tiles_per_z * p.nz[0] * p.nz[1] * p.nz[2];
+    const int nkb = (p.K + BK - 1) / BK;
+    const int k_iters = nkb * p.kg;
+    const int cid = static_cast<int>(ptx::cluster_id_x());
+    const int ncl = static_cast<int>(ptx::num_clusters_x());
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            ptx::mbar_init(&full_bar[s], 2);      // leader's expect_tx arrive + peer's plain arrive
+            ptx::mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&tfull_bar[s], 1);
+            ptx::mbar_init(&tempty_bar[s], 2 * kEpiWarps);
+        }
+        ptx::fence_mbar_init();
+    }
+    ptx::cluster_sync_all();                      // peer barriers initialised before any remote signal
+    if (warp == 2) {
+        ptx::tmem_alloc_2sm(tmem_slot, 512);
+        ptx::tmem_relinquish_2sm();
+    }
+    ptx::tc_fence_before();
+    ptx::cluster_sync_all();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode = [&](int t, int& m_blk, int& n_blk, int (&z)[3]) {
+        int zz = t / tiles_per_z;
+        const int r = t - zz * tiles_per_z;
+        if (p.raster_n) { m_blk = r / nt; n_blk = r - m_blk * nt; }
+        else            { n_blk = r / mt; m_blk = r - n_blk * mt; }
+        z[0] = zz % p.nz[0]; zz /= p.nz[0];
+        z[1] = zz % p.nz[1]; zz /= p.nz[1];
+        z[2] = zz;
+    };
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = cid; t < total_tiles; t += ncl) {
+                int m_blk, n_blk, z[3];
+                decode(t, m_blk, n_blk, z);
+                int ea[3] = {0, 0, 0}, eb[3] = {0, 0, 0};
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    const int s = p.z_slot[i];
+                    if (s >= 0) {
+                        if ((p.a_emask >> s) & 1) ea[s] = z[i];
+                        if ((p.b_emask >> s) & 1) eb[s] = z[i];
+                    }
+                }
+                const int m0 = m_blk * TM + static_cast<int>(rank) * BM;
+                const int n0 = n_blk * BN + static_cast<int>(rank) * BNH;
+                for (int it = 0; it < k_iters; ++it) {
+                    const int g = it / nkb, kb = it - g * nkb;
+                    if (p.kg_slot >= 0) {
+                        if ((p.a_emask >> p.kg_slot) & 1) ea[p.kg_slot] = g;
+                        if ((p.b_emask >> p.kg_slot) & 1) eb[p.kg_slot] = g;
+                    }
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+                    if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+                    uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
+                    uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
+                    if (!p.a_mn) {
+                        ptx::tma_load_5d_2sm(&tmA, fb, sa, kb * BK, m0, ea[0], ea[1], ea[2]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BM / 64; ++c)
+                            ptx::tma_load_5d_2sm(&tmA, fb, sa + c * (BK * 128), m0 + c * 64, kb * BK, ea[0],
+                                                 ea[1], ea[2]);
+                    }
+                    if (!p.b_mn) {
+                        ptx::tma_load_5d_2sm(&tmB, fb, sb, kb * BK, n0, eb[0], eb[1], eb[2]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BNH / 64; ++c)
+                            ptx::tma_load_5d_2sm(&tmB, fb, sb + c * (BK * 128), n0 + c * 64, kb * BK, eb[0],
+                                                 eb[1], eb[2]);
+                    }
+                    if (!leader) ptx::mbar_arrive_cluster(fb);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (leader && lane == 0) {
+            const uint32_t idesc = ptx::make_idesc_bf16(TM, BN, p.a_mn, p.b_mn);
+            const uint32_t a_lbo = p.a_mn ? BK * 128 : 0, b_lbo = p.b_mn ? BK * 128 : 0;
+            const uint32_t a_kstep = p.a_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            const uint32_t b_kstep = p.b_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            int last_acc = -1;
+            uint32_t last_phase = 0;
+            for (int t = cid; t < total_tiles; t += ncl) {
+                ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
+                for (int it = 0; it < k_iters; ++it) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    const uint64_t adesc = ptx::make_smem_desc_sw128(
+                        ptx::smem_u32(smem_a + stage * Cfg::A_BYTES), a_lbo, 1024);
+                    const uint64_t bdesc = ptx::make_smem_desc_sw128(
+                        ptx::smem_u32(smem_b + stage * Cfg::B_BYTES), b_lbo, 1024);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        ptx::mma_bf16_ss_2sm(d_tmem, adesc + k * a_kstep, bdesc + k * b_kstep, idesc,
+                                             (it | k) != 0);
+                    }
+                    ptx::mma_commit_2sm_mc(&empty_bar[stage], 3);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::mma_commit_2sm_mc(&tfull_bar[acc], 3);
+                last_acc = acc; last_phase = acc_phase;
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            // the peer's epilogue arrives remotely on our tempty barriers: drain before teardown
+            if (last_acc >= 0) ptx::mbar_wait(&tempty_bar[last_acc], last_phase);
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue (both CTAs, rows of this CTA's half) =====================
+        const int ew = warp - 4;
+        const int q = warp & 3;                 // TMEM lane quarter this warp may read
+        const int hf = ew >> 2;                 // which half of the BN columns
+        uint8_t* stg = smem_epi + ew * kEpiStageBytes;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int t = cid; t < total_tiles; t += ncl) {
+            int m_blk, n_blk, z[3];
+            decode(t, m_blk, n_blk, z);
+            const long long coff = z[0] * p.c_zs[0] + z[1] * p.c_zs[1] + z[2] * p.c_zs[2];
+            const long long roff = z[0] * p.r_zs[0] + z[1] * p.r_zs[1] + z[2] * p.r_zs[2];
+            const int row0 = m_blk * TM + static_cast<int>(rank) * BM + q * 32;   // first row of the slab
+            const int rows_valid = min(32, p.M - row0);                            // may be <= 0
+
+            ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);
+            constexpr int NCH = BNH / 32;
+#pragma unroll 1
+            for (int c = 0; c < NCH; ++c) {
+                const int col_local = hf * BNH + c * 32;
+                const int col0 = n_blk * BN + col_local;
+                const bool live = rows_valid > 0 && col0 < p.N;       // warp-uniform
+                uint32_t v[32];
+                if (live) {
+                    ptx::tmem_ld_32x32(taddr + col_local, v);
+                    ptx::tmem_ld_wait();
+                }
+                if (c == NCH - 1) {
+                    // accumulator stage fully read by this warp: hand it back to the leader's MMA warp
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
+                }
+                if (!live) continue;
+                EpiArgs o;
+                const long long co = coff + static_cast<long long>(row0) * p.ldc + col0;
+                const int ce = p.c_f32 ? 4 : 2, re = p.r_f32 ? 4 : 2;
+                o.C = static_cast<uint8_t*>(p.C) + co * ce;
+                o.c_row = p.ldc * ce; o.c_step = 4 * o.c_row;
+                o.Cpre = p.C_pre ? static_cast<uint8_t*>(p.C_pre) + co * 2 : nullptr;
+                o.p_row = p.ldc * 2; o.p_step = 4 * o.p_row;
+                o.R = p.R ? static_cast<const uint8_t*>(p.R) +
+                                (roff + static_cast<long long>(row0) * p.ldr + col0) * re : nullptr;
+                o.r_row = p.ldr * re; o.r_step = 4 * o.r_row;
+                o.bias = p.bias ? p.bias + col0 : nullptr;
+                o.c_f32 = p.c_f32; o.r_f32 = p.r_f32; o.alpha = p.alpha;
+                o.rows_valid = rows_valid;
+                o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
+                epi_chunk<ACT>(v, stg, lane, o);
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    ptx::tc_fence_before();
+    ptx::cluster_sync_all();
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_2sm(tmem_base, 512);
+    }
+}
+
+// ---- host ----------------------------------------------------------------------------------------
+template <int BN, int ACT>
+static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, int tiles,
+                          cudaStream_t st) {
+    using Cfg = Gemm2Cfg<BN>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm2_bf16_kernel<BN, ACT>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) {
+            set_error("cudaFuncSetAttribute(gemm2<%d>): %s", BN, cudaGetErrorString(e));
+            return PT_ERR_CUDA;
+        }
+        attr_done = true;
+    }
+    const int max_clusters = num_sms() / 2;
+    const int clusters = tiles < max_clusters ? tiles : max_clusters;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(2 * clusters, 1, 1);
+    cfg.blockDim = dim3(kGemm2Threads, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_bf16_kernel<BN, ACT>, ta, tb, p);
+    if (e != cudaSuccess) {
+        set_error("gemm2_bf16_kernel<%d>: launch failed: %s", BN, cudaGetErrorString(e));
+        return PT_ERR_CUDA;
+    }
+    return PT_OK;
+}
+
+int gemm2_tiles(const GemmDev& p, int bn) {
+    const long long mt = (p.M + 2 * BM - 1) / (2 * BM), nt = (p.N + bn - 1) / bn;
+    const long long t = mt * nt * p.nz[0] * p.nz[1] * p.nz[2];
+    return t < (1ll << 31) ? static_cast<int>(t) : -1;
+}
+
+int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st) {
+    const int tiles = gemm2_tiles(p, bn);
+    if (tiles <= 0) { set_error("gemm2: bad tile count"); return PT_ERR_INVALID; }
+#define PT_G2(BN_)                                                                      \
+    case BN_:                                                                           \
+        if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, p, tiles, st); \
+        if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, p, tiles, st);   \
+        return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, p, tiles, st);
+    switch (bn) {
+        PT_G2(256) PT_G2(192) PT_G2(128) PT_G2(64)
+        default: set_error("gemm2: unsupported BN %d", bn); return PT_ERR_INVALID;
+    }
+#undef PT_G2
+}
+
+}  // namespace pt

@@ -1,0 +1,49 @@
+// Shared between the single-CTA (gemm_sm100.cu) and CTA-pair (gemm2_sm100.cu) GEMM kernels.
+#pragma once
+#include "pt_common.cuh"
+
+namespace pt {
+
+constexpr int BM = 128;       // rows of A per CTA (UMMA M = 128 for cta_group::1, 256 over a CTA pair)
+constexpr int BK = 64;        // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+
+struct GemmDev {
+    int M, N, K;
+    int nz[3];        // batch extents used for tile enumeration
+    int kg;           // K groups (>=1)
+    int a_mn, b_mn;
+    int a_emask, b_emask;   // bit i set: tensor-map extra dim i takes a coordinate
+    int kg_slot;      // which extra dim is the K-group (-1: none)
+    int z_slot[3];    // which extra dim batch dim i maps to
+    void* C;
+    void* C_pre;
+    const float* bias;
+    const void* R;
+    long long ldc, ldr;
+    long long c_zs[3], r_zs[3];
+    int c_f32, r_f32, act;
+    float alpha;
+    int raster_n;     // tile order inside one batch slice: 1 = n fastest, 0 = m fastest
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == PT_ACT_GELU_TANH) {
+        const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+        float u = k0 * (v + k1 * v * v * v);
+        return 0.5f * v * (1.f + tanh_fast(u));
+    } else if (act == PT_ACT_GELU_ERF) {
+        return gelu_erf_f(v);
+    }
+    return v;
+}
+
+
+// host helpers (gemm_sm100.cu)
+int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, int K, long long ld,
+                   const int ext[3], const long long est[3], int rows_box, const char* name);
+// CTA-pair kernel (gemm2_sm100.cu): bn in {64,128,192,256}; tensor map of B must use box rows bn/2
+int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st);
+int gemm2_tiles(const GemmDev& p, int bn);
+
+}  // namespace pt

@@ -14,12 +14,10 @@
 // that the UMMA shared-memory descriptors name.
 #include "pt_common.cuh"
 #include "sm100_ptx.cuh"
+#include "gemm_common.cuh"
 
 namespace pt {
 
-constexpr int BM = 128;       // UMMA M (cta_group::1)
-constexpr int BK = 64;        // 64 bf16 = one 128-byte swizzle row
-constexpr int UMMA_K = 16;
 constexpr int kGemmThreads = 256;
 constexpr int kAccStride = 256;   // TMEM columns per accumulator stage
 constexpr int kTmemCols = 512;
@@ -34,35 +32,6 @@ struct GemmCfg {
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 };
-
-struct GemmDev {
-    int M, N, K;
-    int nz[3];        // batch extents used for tile enumeration
-    int kg;           // K groups (>=1)
-    int a_mn, b_mn;
-    int a_emask, b_emask;   // bit i set: tensor-map extra dim i takes a coordinate
-    int kg_slot;      // which extra dim is the K-group (-1: none)
-    int z_slot[3];    // which extra dim batch dim i maps to
-    void* C;
-    void* C_pre;
-    const float* bias;
-    const void* R;
-    long long ldc, ldr;
-    long long c_zs[3], r_zs[3];
-    int c_f32, r_f32, act;
-    float alpha;
-};
-
-__device__ __forceinline__ float apply_act(float v, int act) {
-    if (act == PT_ACT_GELU_TANH) {
-        const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-        float u = k0 * (v + k1 * v * v * v);
-        return 0.5f * v * (1.f + tanh_fast(u));
-    } else if (act == PT_ACT_GELU_ERF) {
-        return gelu_erf_f(v);
-    }
-    return v;
-}
 
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -124,7 +93,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 int zz = t / tiles_per_z, r = t - zz * tiles_per_z;
-                const int n_blk = r / mt, m_blk = r - n_blk * mt;
+                const int n_blk = p.raster_n ? r % nt : r / mt;
+                const int m_blk = p.raster_n ? r / nt : r - n_blk * mt;
                 int z[3];
                 z[0] = zz % p.nz[0]; zz /= p.nz[0];
                 z[1] = zz % p.nz[1]; zz /= p.nz[1];
@@ -213,7 +183,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t acc_phase = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
             int zz = t / tiles_per_z, r = t - zz * tiles_per_z;
-            const int n_blk = r / mt, m_blk = r - n_blk * mt;
+            const int n_blk = p.raster_n ? r % nt : r / mt;
+            const int m_blk = p.raster_n ? r / nt : r - n_blk * mt;
             const int z0 = zz % p.nz[0]; zz /= p.nz[0];
             const int z1 = zz % p.nz[1]; zz /= p.nz[1];
             const int z2 = zz;
@@ -353,7 +324,7 @@ static EncodeTiledFn get_encode_fn() {
 // One operand = a 5-D bf16 tensor map {inner, outer, e0, e1, e2}.
 //   K-major : inner = K (box 64), outer = rows (box `rows_box`)
 //   MN-major: inner = rows (box 64), outer = K (box 64)
-static int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, int K,
+int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, int K,
                           long long ld, const int ext[3], const long long est[3], int rows_box,
                           const char* name) {
     EncodeTiledFn enc = get_encode_fn();
@@ -435,6 +406,26 @@ static int pick_bn(int M, int N, long long nbatch) {
     return best_bn;
 }
 
+// N tile for the CTA-pair kernel: 74 clusters, each tile 256 x bn; MN-major B needs bn/2 % 64 == 0.
+static int pick_bn2(int M, int N, long long nbatch, int b_mn) {
+    const int cands[4] = {256, 192, 128, 64};
+    const int slots = num_sms() / 2;
+    double best = 1e30; int best_bn = 256;
+    const long long mt = (M + 2 * BM - 1) / (2 * BM);
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        if (b_mn && (bn / 2) % 64 != 0) continue;
+        const long long nt = (N + bn - 1) / bn;
+        const long long tiles = mt * nt * nbatch;
+        const long long waves = (tiles + slots - 1) / slots;
+        double cost = static_cast<double>(waves) * (bn + 24.0);
+        if (cost < best * 0.999) { best = cost; best_bn = bn; }
+    }
+    return best_bn;
+}
+
+int g_gemm_impl = 0;   // 0 auto (CTA-pair kernel), 1 single-CTA kernel, 2 CTA-pair kernel
+
 }  // namespace pt
 
 extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
@@ -460,6 +451,8 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         for (int i = 0; i < 3; ++i)
             PT_REQUIRE((a->r_zs[i] % rvec) == 0, "pt_gemm_bf16: residual batch stride %d misaligned", i);
     }
+    PT_REQUIRE((a->N % 4) == 0 || (!a->bias && !a->residual && !a->C_pre),
+               "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
     PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_GELU_ERF, "pt_gemm_bf16: bad act %d", a->act);
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
 
@@ -491,21 +484,40 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     p.act = a->act; p.alpha = a->alpha;
 
     const long long nbatch = static_cast<long long>(a->nz[0]) * a->nz[1] * a->nz[2];
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CUtensorMap ta, tb;
+    if (g_gemm_impl != 1) {
+        // CTA-pair kernel (gemm2_sm100.cu): 256 x bn tiles, one per cluster of two SMs
+        const int bn = pick_bn2(a->M, a->N, nbatch, p.b_mn);
+        const long long mt = (a->M + 2 * BM - 1) / (2 * BM), nt = (a->N + bn - 1) / bn;
+        PT_REQUIRE(mt * nt * nbatch < (1ll << 31), "pt_gemm_bf16: too many tiles");
+        p.raster_n = nt <= mt;
+        int rc = encode_operand(&ta, a->A, p.a_mn, a->M, a->K, a->lda, ext, ast, BM, "A");
+        if (rc != PT_OK) return rc;
+        rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn / 2, "B");
+        if (rc != PT_OK) return rc;
+        return launch_gemm2(bn, ta, tb, p, st);
+    }
     const int bn = pick_bn(a->M, a->N, nbatch);
     const long long tiles_ll = static_cast<long long>((a->M + BM - 1) / BM) * ((a->N + bn - 1) / bn) * nbatch;
     PT_REQUIRE(tiles_ll < (1ll << 31), "pt_gemm_bf16: too many tiles");
     const int tiles = static_cast<int>(tiles_ll);
+    p.raster_n = (a->N + bn - 1) / bn <= (a->M + BM - 1) / BM;
 
-    CUtensorMap ta, tb;
     int rc = encode_operand(&ta, a->A, p.a_mn, a->M, a->K, a->lda, ext, ast, BM, "A");
     if (rc != PT_OK) return rc;
     rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn, "B");
     if (rc != PT_OK) return rc;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
     switch (bn) {
         case 256: return launch_gemm<256>(ta, tb, p, tiles, st);
         case 192: return launch_gemm<192>(ta, tb, p, tiles, st);
         case 128: return launch_gemm<128>(ta, tb, p, tiles, st);
         default:  return launch_gemm<64>(ta, tb, p, tiles, st);
     }
+}
+
+extern "C" int pt_set_gemm_impl(int impl) {
+    if (impl < 0 || impl > 2) { pt::set_error("pt_set_gemm_impl: impl must be 0 (auto), 1 or 2"); return PT_ERR_INVALID; }
+    pt::g_gemm_impl = impl;
+    return PT_OK;
 }

@@ -81,6 +81,12 @@ __device__ __forceinline__ float gelu_tanh_f(float z) {
     float u = k0 * (z + k1 * z * z * z);
     return 0.5f * z * (1.f + tanhf(u));
 }
+// same with the hardware tanh.approx (GEMM epilogues; |err| ~ 1e-3 relative, below bf16 rounding)
+__device__ __forceinline__ float gelu_tanh_fast_f(float z) {
+    const float u = 0.7978845608028654f * fmaf(0.044715f * z * z, z, z);
+    const float h = 0.5f * z;
+    return fmaf(h, tanh_fast(u), h);
+}
 __device__ __forceinline__ float gelu_tanh_grad_f(float z) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
     float u = k0 * (z + k1 * z * z * z);

@@ -84,6 +84,11 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     _lib.call("pt_gemm_bf16", C.byref(g), _stream())
 
 
+def set_gemm_impl(impl: int) -> None:
+    """0 = default (CTA-pair kernel), 1 = single-CTA kernel, 2 = CTA-pair kernel (tests / profiling)."""
+    _lib.check(_lib.lib().pt_set_gemm_impl(int(impl)), "pt_set_gemm_impl")
+
+
 def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residual=None,
            out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0) -> torch.Tensor:
     """y[M,N] = act(x[M,K] @ w[N,K]^T + bias) (+ residual).  x, w bf16 row-major 2-D."""

@@ -5,6 +5,15 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=[2, 1], ids=["cta_pair", "single_cta"])
+def gemm_impl(request):
+    """Every case runs on both tensor-core kernels behind pt_gemm_bf16 (2 = the default CTA-pair kernel)."""
+    from projectiontrainer_b200 import ops
+    ops.set_gemm_impl(request.param)
+    yield request.param
+    ops.set_gemm_impl(0)
+
+
 def _rand(shape, dev, scale=1.0):
     return (torch.randn(shape, device=dev, dtype=torch.float32) * scale).to(torch.bfloat16)
 
@@ -18,7 +27,8 @@ def _check(out, ref, tol=2e-2, name=""):
 
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 256, 256), (575, 1152, 1024),
                                    (1000, 1536, 1152), (130, 64, 768), (384, 192, 2048),
-                                   (4096, 1024, 4096), (18400, 1152, 1280)])
+                                   (4096, 1024, 4096), (18400, 1152, 1280), (22496, 1536, 1152),
+                                   (100, 40, 72), (257, 328, 8)])
 def test_gemm_tn(cuda_dev, M, N, K):
     from projectiontrainer_b200 import ops
     torch.manual_seed(M + N + K)
