@@ -60,6 +60,7 @@ struct EpiArgs {
     int c_f32, r_f32;
     float alpha;
     int rows_valid;       // rows of the slab that exist (1..32)
+    int row_lo;           // rows of the slab below this one belong to the previous (overlapped) tile
     int cols_q;           // columns of the chunk to produce, multiple of 4 (4..32)
 };
 
@@ -75,14 +76,13 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint8_t* stg,
     if (c < o.cols_q) {
         float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
         if (o.bias) b4 = __ldg(reinterpret_cast<const float4*>(o.bias + c));
-        const int nrows = o.rows_valid - rsub;          // rows rsub, rsub + 4, ... < rows_valid
         float4 res[8];
         if (o.R) {
             const uint8_t* rp = o.R + rsub * o.r_row + c * (o.r_f32 ? 4 : 2);
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
                 res[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (it * 4 < nrows) {
+                if (it * 4 + rsub >= o.row_lo && it * 4 + rsub < o.rows_valid) {
                     if (o.r_f32) {
                         res[it] = *reinterpret_cast<const float4*>(rp);
                     } else {
@@ -100,7 +100,7 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint8_t* stg,
         for (int it = 0; it < 8; ++it) {
             const int r = it * 4 + rsub;
             const float4 a = *reinterpret_cast<const float4*>(sp + it * 512 + ((ch ^ (r & 7)) << 4));
-            if (it * 4 < nrows) {
+            if (r >= o.row_lo && r < o.rows_valid) {
                 float x0 = fmaf(a.x, o.alpha, b4.x), x1 = fmaf(a.y, o.alpha, b4.y);
                 float x2 = fmaf(a.z, o.alpha, b4.z), x3 = fmaf(a.w, o.alpha, b4.w);
                 if (pp) {
@@ -217,8 +217,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         if ((p.b_emask >> s) & 1) eb[s] = z[i];
                     }
                 }
-                const int m0 = m_blk * TM + static_cast<int>(rank) * BM;
-                const int n0 = n_blk * BN + static_cast<int>(rank) * BNH;
+                const int m0 = (m_blk == mt - 1 ? p.m_last : m_blk * TM) + static_cast<int>(rank) * BM;
+                const int n0 = (n_blk == nt - 1 ? p.n_last : n_blk * BN) + static_cast<int>(rank) * BNH;
                 for (int it = 0; it < k_iters; ++it) {
                     const int g = it / nkb, kb = it - g * nkb;
                     if (p.kg_slot >= 0) {
@@ -303,8 +303,11 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             decode(t, m_blk, n_blk, z);
             const long long coff = z[0] * p.c_zs[0] + z[1] * p.c_zs[1] + z[2] * p.c_zs[2];
             const long long roff = z[0] * p.r_zs[0] + z[1] * p.r_zs[1] + z[2] * p.r_zs[2];
-            const int row0 = m_blk * TM + static_cast<int>(rank) * BM + q * 32;   // first row of the slab
+            const int tile_m = m_blk == mt - 1 ? p.m_last : m_blk * TM;
+            const int tile_n = n_blk == nt - 1 ? p.n_last : n_blk * BN;
+            const int row0 = tile_m + static_cast<int>(rank) * BM + q * 32;        // first row of the slab
             const int rows_valid = min(32, p.M - row0);                            // may be <= 0
+            const int row_lo = max(0, m_blk * TM - row0);                          // rows below: previous tile's
 
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             ptx::tc_fence_after();
@@ -313,8 +316,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll 1
             for (int c = 0; c < NCH; ++c) {
                 const int col_local = hf * BNH + c * 32;
-                const int col0 = n_blk * BN + col_local;
-                const bool live = rows_valid > 0 && col0 < p.N;       // warp-uniform
+                const int col0 = tile_n + col_local;
+                const bool live = rows_valid > row_lo && col0 < p.N && col0 >= n_blk * BN;   // warp-uniform
                 uint32_t v[32];
                 if (live) {
                     ptx::tmem_ld_32x32(taddr + col_local, v);
@@ -339,7 +342,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 o.r_row = p.ldr * re; o.r_step = 4 * o.r_row;
                 o.bias = p.bias ? p.bias + col0 : nullptr;
                 o.c_f32 = p.c_f32; o.r_f32 = p.r_f32; o.alpha = p.alpha;
-                o.rows_valid = rows_valid;
+                o.rows_valid = rows_valid; o.row_lo = row_lo;
                 o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
                 epi_chunk<ACT>(v, stg, lane, o);
             }

@@ -25,6 +25,11 @@ struct GemmDev {
     int c_f32, r_f32, act;
     float alpha;
     int raster_n;     // tile order inside one batch slice: 1 = n fastest, 0 = m fastest
+    // CTA-pair kernel: first row / column of the LAST m / n tile.  When the extent is not a multiple of the
+    // tile, the last tile is shifted back to end exactly at the edge (its loads stay in bounds: TMA boxes
+    // that are partly or wholly out of bounds were measured to stall the pipeline) and its epilogue skips
+    // the rows / columns the previous tile already produced.
+    int m_last, n_last;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {

@@ -418,7 +418,10 @@ static int pick_bn2(int M, int N, long long nbatch, int b_mn) {
         const long long nt = (N + bn - 1) / bn;
         const long long tiles = mt * nt * nbatch;
         const long long waves = (tiles + slots - 1) / slots;
-        double cost = static_cast<double>(waves) * (bn + 24.0);
+        // narrower tiles re-read A from smem more often per flop: measured ~1.4 PF/s at bn 256 but ~1.0 at 128
+        // (operand reads + TMA writes exceed the 128 B/clk smem port), hence the per-width factor
+        const double f = bn == 256 ? 1.0 : bn == 192 ? 1.15 : bn == 128 ? 1.5 : 2.5;
+        double cost = static_cast<double>(waves) * (bn * f + 16.0);
         if (cost < best * 0.999) { best = cost; best_bn = bn; }
     }
     return best_bn;
@@ -492,6 +495,9 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         const long long mt = (a->M + 2 * BM - 1) / (2 * BM), nt = (a->N + bn - 1) / bn;
         PT_REQUIRE(mt * nt * nbatch < (1ll << 31), "pt_gemm_bf16: too many tiles");
         p.raster_n = nt <= mt;
+        // (a shifted start must keep TMA's 16-byte global alignment when it is the contiguous dimension)
+        p.m_last = (a->M >= 2 * BM && (!p.a_mn || a->M % 8 == 0)) ? a->M - 2 * BM : static_cast<int>(mt - 1) * 2 * BM;
+        p.n_last = (a->N >= bn && a->N % 32 == 0) ? a->N - bn : static_cast<int>(nt - 1) * bn;
         int rc = encode_operand(&ta, a->A, p.a_mn, a->M, a->K, a->lda, ext, ast, BM, "A");
         if (rc != PT_OK) return rc;
         rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn / 2, "B");
