@@ -65,65 +65,62 @@ struct EpiArgs {
 };
 
 template <int ACT>
-__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint8_t* stg, int lane, const EpiArgs& o) {
+__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint32_t stg, int lane, const EpiArgs& o) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
-            make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-    }
+    for (int j = 0; j < 8; ++j)
+        ptx::sts128(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
     __syncwarp();
     const int ch = lane & 7, c = ch * 4, rsub = lane >> 3;
-    if (c < o.cols_q) {
-        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (o.bias) b4 = __ldg(reinterpret_cast<const float4*>(o.bias + c));
-        float4 res[8];
-        if (o.R) {
-            const uint8_t* rp = o.R + rsub * o.r_row + c * (o.r_f32 ? 4 : 2);
-#pragma unroll
-            for (int it = 0; it < 8; ++it) {
-                res[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (it * 4 + rsub >= o.row_lo && it * 4 + rsub < o.rows_valid) {
-                    if (o.r_f32) {
-                        res[it] = *reinterpret_cast<const float4*>(rp);
-                    } else {
-                        const uint2 q = *reinterpret_cast<const uint2*>(rp);
-                        res[it] = make_float4(bf16_lo(q.x), bf16_hi(q.x), bf16_lo(q.y), bf16_hi(q.y));
-                    }
-                }
-                rp += o.r_step;
-            }
-        }
-        uint8_t* cp = o.C + rsub * o.c_row + c * (o.c_f32 ? 4 : 2);
-        uint8_t* pp = o.Cpre ? o.Cpre + rsub * o.p_row + c * 2 : nullptr;
-        const uint8_t* sp = stg + rsub * 128;
+    const bool col_ok = c < o.cols_q;
+    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (o.bias && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(o.bias + c));
+    float4 res[8];
+    if (o.R) {
+        const uint8_t* rp = o.R + rsub * o.r_row + c * (o.r_f32 ? 4 : 2);
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int r = it * 4 + rsub;
-            const float4 a = *reinterpret_cast<const float4*>(sp + it * 512 + ((ch ^ (r & 7)) << 4));
-            if (r >= o.row_lo && r < o.rows_valid) {
-                float x0 = fmaf(a.x, o.alpha, b4.x), x1 = fmaf(a.y, o.alpha, b4.y);
-                float x2 = fmaf(a.z, o.alpha, b4.z), x3 = fmaf(a.w, o.alpha, b4.w);
-                if (pp) {
-                    uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
-                    *reinterpret_cast<uint2*>(pp) = u;
-                }
-                if (ACT == PT_ACT_GELU_TANH) {
-                    x0 = gelu_tanh_fast_f(x0); x1 = gelu_tanh_fast_f(x1);
-                    x2 = gelu_tanh_fast_f(x2); x3 = gelu_tanh_fast_f(x3);
-                } else if (ACT == PT_ACT_GELU_ERF) {
-                    x0 = gelu_erf_f(x0); x1 = gelu_erf_f(x1); x2 = gelu_erf_f(x2); x3 = gelu_erf_f(x3);
-                }
-                if (o.R) { x0 += res[it].x; x1 += res[it].y; x2 += res[it].z; x3 += res[it].w; }
-                if (o.c_f32) {
-                    *reinterpret_cast<float4*>(cp) = make_float4(x0, x1, x2, x3);
+            res[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (col_ok && r >= o.row_lo && r < o.rows_valid) {
+                if (o.r_f32) {
+                    res[it] = *reinterpret_cast<const float4*>(rp);
                 } else {
-                    uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
-                    *reinterpret_cast<uint2*>(cp) = u;
+                    const uint2 q = *reinterpret_cast<const uint2*>(rp);
+                    res[it] = make_float4(bf16_lo(q.x), bf16_hi(q.x), bf16_lo(q.y), bf16_hi(q.y));
                 }
             }
-            cp += o.c_step;
-            if (pp) pp += o.p_step;
+            rp += o.r_step;
         }
+    }
+    uint8_t* cp = o.C + rsub * o.c_row + c * (o.c_f32 ? 4 : 2);
+    uint8_t* pp = o.Cpre + rsub * o.p_row + c * 2;
+    const uint32_t sp = stg + rsub * 128;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + rsub;
+        const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
+        const bool ok = col_ok && r >= o.row_lo && r < o.rows_valid;
+        float x0 = fmaf(a.x, o.alpha, b4.x), x1 = fmaf(a.y, o.alpha, b4.y);
+        float x2 = fmaf(a.z, o.alpha, b4.z), x3 = fmaf(a.w, o.alpha, b4.w);
+        if (o.Cpre != nullptr) {
+            uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
+            if (ok) *reinterpret_cast<uint2*>(pp) = u;
+            pp += o.p_step;
+        }
+        if (ACT == PT_ACT_GELU_TANH) {
+            x0 = gelu_tanh_fast_f(x0); x1 = gelu_tanh_fast_f(x1);
+            x2 = gelu_tanh_fast_f(x2); x3 = gelu_tanh_fast_f(x3);
+        } else if (ACT == PT_ACT_GELU_ERF) {
+            x0 = gelu_erf_f(x0); x1 = gelu_erf_f(x1); x2 = gelu_erf_f(x2); x3 = gelu_erf_f(x3);
+        }
+        if (o.R) { x0 += res[it].x; x1 += res[it].y; x2 += res[it].z; x3 += res[it].w; }
+        if (o.c_f32) {
+            if (ok) *reinterpret_cast<float4*>(cp) = make_float4(x0, x1, x2, x3);
+        } else {
+            uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
+            if (ok) *reinterpret_cast<uint2*>(cp) = u;
+        }
+        cp += o.c_step;
     }
     __syncwarp();
 }
@@ -208,46 +205,48 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             for (int t = cid; t < total_tiles; t += ncl) {
                 int m_blk, n_blk, z[3];
                 decode(t, m_blk, n_blk, z);
-                int ea[3] = {0, 0, 0}, eb[3] = {0, 0, 0};
-#pragma unroll
-                for (int i = 0; i < 3; ++i) {
-                    const int s = p.z_slot[i];
-                    if (s >= 0) {
-                        if ((p.a_emask >> s) & 1) ea[s] = z[i];
-                        if ((p.b_emask >> s) & 1) eb[s] = z[i];
-                    }
+                // tensor-map coordinates of the three extra dims, kept in registers (no indexed local
+                // arrays in this loop: the producer is the pipeline's critical single thread)
+                const int z0 = z[0], z1 = z[1], z2 = z[2];
+                int ea0, ea1, ea2, eb0, eb1, eb2;
+                if (p.kg_slot >= 0) {          // dims: (k-group, z0, z1)
+                    ea0 = 0; ea1 = (p.a_emask & 2) ? z0 : 0; ea2 = (p.a_emask & 4) ? z1 : 0;
+                    eb0 = 0; eb1 = (p.b_emask & 2) ? z0 : 0; eb2 = (p.b_emask & 4) ? z1 : 0;
+                } else {                        // dims: (z0, z1, z2)
+                    ea0 = (p.a_emask & 1) ? z0 : 0; ea1 = (p.a_emask & 2) ? z1 : 0; ea2 = (p.a_emask & 4) ? z2 : 0;
+                    eb0 = (p.b_emask & 1) ? z0 : 0; eb1 = (p.b_emask & 2) ? z1 : 0; eb2 = (p.b_emask & 4) ? z2 : 0;
                 }
+                const bool kga = p.kg_slot >= 0 && (p.a_emask & 1), kgb = p.kg_slot >= 0 && (p.b_emask & 1);
                 const int m0 = (m_blk == mt - 1 ? p.m_last : m_blk * TM) + static_cast<int>(rank) * BM;
                 const int n0 = (n_blk == nt - 1 ? p.n_last : n_blk * BN) + static_cast<int>(rank) * BNH;
+                int g = 0, kb = 0;
                 for (int it = 0; it < k_iters; ++it) {
-                    const int g = it / nkb, kb = it - g * nkb;
-                    if (p.kg_slot >= 0) {
-                        if ((p.a_emask >> p.kg_slot) & 1) ea[p.kg_slot] = g;
-                        if ((p.b_emask >> p.kg_slot) & 1) eb[p.kg_slot] = g;
-                    }
+                    if (kga) ea0 = g;
+                    if (kgb) eb0 = g;
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
                     if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
                     uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
                     if (!p.a_mn) {
-                        ptx::tma_load_5d_2sm(&tmA, fb, sa, kb * BK, m0, ea[0], ea[1], ea[2]);
+                        ptx::tma_load_5d_2sm(&tmA, fb, sa, kb * BK, m0, ea0, ea1, ea2);
                     } else {
 #pragma unroll
                         for (int c = 0; c < BM / 64; ++c)
-                            ptx::tma_load_5d_2sm(&tmA, fb, sa + c * (BK * 128), m0 + c * 64, kb * BK, ea[0],
-                                                 ea[1], ea[2]);
+                            ptx::tma_load_5d_2sm(&tmA, fb, sa + c * (BK * 128), m0 + c * 64, kb * BK, ea0,
+                                                 ea1, ea2);
                     }
                     if (!p.b_mn) {
-                        ptx::tma_load_5d_2sm(&tmB, fb, sb, kb * BK, n0, eb[0], eb[1], eb[2]);
+                        ptx::tma_load_5d_2sm(&tmB, fb, sb, kb * BK, n0, eb0, eb1, eb2);
                     } else {
 #pragma unroll
                         for (int c = 0; c < BNH / 64; ++c)
-                            ptx::tma_load_5d_2sm(&tmB, fb, sb + c * (BK * 128), n0 + c * 64, kb * BK, eb[0],
-                                                 eb[1], eb[2]);
+                            ptx::tma_load_5d_2sm(&tmB, fb, sb + c * (BK * 128), n0 + c * 64, kb * BK, eb0,
+                                                 eb1, eb2);
                     }
                     if (!leader) ptx::mbar_arrive_cluster(fb);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (++kb == nkb) { kb = 0; ++g; }
                 }
             }
         }
@@ -295,7 +294,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int ew = warp - 4;
         const int q = warp & 3;                 // TMEM lane quarter this warp may read
         const int hf = ew >> 2;                 // which half of the BN columns
-        uint8_t* stg = smem_epi + ew * kEpiStageBytes;
+        const uint32_t stg = ptx::smem_u32(smem_epi + ew * kEpiStageBytes);
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int t = cid; t < total_tiles; t += ncl) {
