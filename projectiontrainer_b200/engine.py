@@ -111,6 +111,24 @@ class ProjectorState:
     def view(self, buf, i):
         return buf[self.offs[i]:self.offs[i] + self.sizes[i]].view(self.shapes[i])
 
+    @classmethod
+    def from_module(cls, module, device):
+        """Adopt an `MLPProjector` (ref:Stage1/projectors.py): its four fp32 parameters are re-pointed at
+        views of the flat master buffer and their `.grad` at views of the flat gradient buffer, so
+        `state_dict()`, `save_projection` and user code keep seeing live values while the fused step
+        updates them in place."""
+        sd = {k: v.detach() for k, v in module.state_dict().items()}
+        if tuple(sd.keys()) != cls.KEYS:
+            raise RuntimeError(f"unsupported projector layout {list(sd.keys())}: expected {list(cls.KEYS)} "
+                               "(Linear -> GELU -> Linear, ref:Stage1/projectors.py:16-20)")
+        st = cls(sd, device)
+        params = dict(module.named_parameters())
+        for i, k in enumerate(cls.KEYS):
+            params[k].data = st.view(st.flat, i)
+            params[k].grad = st.view(st.grad, i)
+        st.module = module
+        return st
+
     def refresh_shadow(self):
         ops.cast_f32_bf16(self.flat, self.shadow)
 
@@ -429,6 +447,26 @@ class Stage1Engine:
         dx = self.llm_backward()
         self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
+
+    @torch.no_grad()
+    def eval_loss(self, batch: dict, pad_id=0) -> torch.Tensor:
+        """Validation forward (ref:Stage1/projector_trainer.py:304-370): the same loss, no backward."""
+        dev = self.device
+        px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
+        ids = batch["token_ids"].to(dev, non_blocking=True)
+        lab = batch["labels"].to(dev, non_blocking=True)
+        B, T = ids.shape
+        S = self.n_img + T
+        patch = self.vision_forward(px)
+        x0 = self.buf("x0", (B * S, self.lcfg.hidden), F32)
+        self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * self.lcfg.hidden)
+        _, _, keyvalid, targets = self.splice(ids, lab, x0, pad_id)
+        ga, self.grad_accum = self.grad_accum, 1
+        try:
+            loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, T)
+        finally:
+            self.grad_accum = ga
+        return loss.clone()
 
     def train_step(self, batch: dict, lr: float, *, pad_id=0, weight_decay: float = 0.01,
                    allreduce=None, world_size: int = 1) -> torch.Tensor:

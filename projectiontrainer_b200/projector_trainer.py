@@ -1,0 +1,173 @@
+"""Drop-in for ref:Stage1/projector_trainer.py: same class, constructor signature, `.train()`,
+`.save_projection()`, artefact names and logged metric names.  The step body (ref lines 152-245: vision
+forward, `[:, 1:, :]` slice, projector, embed + splice, masks/labels, frozen-LLM loss, backward, clip 5.0,
+AdamW, cosine schedule) executes in `engine.Stage1Engine` on the sm_100a kernels; this file is the host
+loop around it.  Differences that are deliberate and documented in DESIGN.md: no DDP wrappers (one flat
+NCCL all-reduce of the projector gradient), one host read of the loss per step instead of two, and the
+validation pass reports the loss only (sampled generation needs the decode loop)."""
+from __future__ import annotations
+
+import json
+import logging
+import math
+import os
+import time
+
+import torch
+import torch.nn as nn
+from torch.utils.data import DataLoader
+
+from . import weights as Wt
+from .engine import PackedGemma, PackedSiglip, ProjectorState, Stage1Engine
+
+logger = logging.getLogger(__name__)
+
+
+def cosine_with_warmup(step: int, warmup: int, total: int) -> float:
+    """lr multiplier of HF `get_cosine_schedule_with_warmup` (ref:projector_trainer.py:91-95)."""
+    if step < warmup:
+        return step / max(1, warmup)
+    progress = (step - warmup) / max(1, total - warmup)
+    return max(0.0, 0.5 * (1.0 + math.cos(math.pi * progress)))
+
+
+class _ShardedLoader:
+    """What `accelerator.prepare(dataloader)` gives each process: batch i of the (identically shuffled)
+    loader goes to process i % N; short processes wrap around so that every process takes the same
+    number of optimizer steps (accelerate's even_batches)."""
+
+    def __init__(self, loader, rank, world):
+        self.loader, self.rank, self.world = loader, rank, world
+
+    def __len__(self):
+        return math.ceil(len(self.loader) / self.world)
+
+    def __iter__(self):
+        if self.world == 1:
+            yield from self.loader
+            return
+        first, mine = [], 0
+        for i, b in enumerate(self.loader):
+            if i < self.world:
+                first.append(b)
+            if i % self.world == self.rank:
+                mine += 1
+                yield b
+        if mine < len(self) and first:
+            yield first[self.rank % len(first)]
+
+
+class ProjectionTrainerStage1:
+    def __init__(self, accelerator, vision_encoder, language_model, projection_layer, processor, tokenizer,
+                 train_dataset, val_dataset=None, output_dir="./trained_projection_stage1", batch_size=8,
+                 learning_rate=1e-4, weight_decay=0.01, num_epochs=10, gradient_accumulation_steps=1,
+                 warmup_ratio=0.0, wandb_project="xray_projection_training", save_every_n_epochs=0):
+        self.accelerator = accelerator
+        self.vision_encoder, self.language_model = vision_encoder, language_model
+        self.projection_layer = projection_layer
+        self.processor, self.tokenizer = processor, tokenizer
+        self.device = accelerator.device
+        self.output_dir, self.num_epochs, self.batch_size = output_dir, num_epochs, batch_size
+        self.wandb_project, self.save_every_n_epochs = wandb_project, save_every_n_epochs
+        self.val_dataset = val_dataset
+        self.learning_rate, self.weight_decay = learning_rate, weight_decay
+        if self.device.type != "cuda":
+            raise RuntimeError("ProjectionTrainerStage1 (B200 build) needs a CUDA device: the Stage-1 step "
+                               "runs on sm_100a kernels only, there is no CPU path")
+        if accelerator.is_main_process:
+            os.makedirs(output_dir, exist_ok=True)
+
+        gen = torch.Generator().manual_seed(0)      # same shuffle on every process (accelerate syncs RNG)
+        base_loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=True, num_workers=2,
+                                 generator=gen, pin_memory=True)
+        self.val_loader = None
+        if val_dataset is not None:
+            self.val_loader = _ShardedLoader(DataLoader(val_dataset, batch_size=batch_size, shuffle=False,
+                                                        num_workers=2, pin_memory=True),
+                                             accelerator.process_index, accelerator.num_processes)
+        # schedule lengths are computed from the UNSHARDED loader, as the reference does (:82-87)
+        steps_per_epoch = math.ceil(len(base_loader) / gradient_accumulation_steps)
+        self.max_train_steps = num_epochs * steps_per_epoch
+        self.num_warmup_steps = math.ceil(warmup_ratio * self.max_train_steps)
+        self._sched_step = 0
+        self.train_loader = _ShardedLoader(base_loader, accelerator.process_index, accelerator.num_processes)
+
+        # frozen towers -> packed bf16 weights (read once; none of the HF forward code runs afterwards)
+        vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
+            PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), self.device)
+        llm = language_model if isinstance(language_model, PackedGemma) else \
+            PackedGemma(*Wt.gemma_from_hf(language_model), self.device)
+        if isinstance(projection_layer, nn.Module):
+            projection_layer.to(self.device).float()
+            projection_layer.requires_grad_(True)
+            proj = ProjectorState.from_module(projection_layer, self.device)
+        else:
+            proj = projection_layer
+        self.engine = Stage1Engine(vis, llm, proj, self.device, grad_accum=accelerator.gradient_accumulation_steps)
+        pad = getattr(tokenizer, "pad_token_id", None)
+        self.pad_id = pad
+        logger.info("Froze vision encoder and language model parameters (packed, no gradients are formed).")
+
+    # ---- schedule: accelerate's prepared scheduler ticks num_processes times per optimizer step
+    def current_lr(self) -> float:
+        return self.learning_rate * cosine_with_warmup(self._sched_step, self.num_warmup_steps, self.max_train_steps)
+
+    def train(self):
+        acc = self.accelerator
+        logger.info(f"Process {acc.process_index}: Starting Stage 1 training for {self.num_epochs} epochs on {self.device}")
+        global_step = 0
+        best_val_loss = float("inf")
+        for epoch in range(self.num_epochs):
+            epoch_train_loss = 0.0
+            n_steps = 0
+            for batch in self.train_loader:
+                lr = self.current_lr()
+                loss = self.engine.train_step(batch, lr, pad_id=self.pad_id, weight_decay=self.weight_decay,
+                                              allreduce=acc.all_reduce_sum_, world_size=acc.num_processes)
+                self._sched_step += acc.num_processes
+                global_step += 1
+                n_steps += 1
+                avg_loss_step = acc.gather(loss).mean().item()          # the one host sync of the step
+                epoch_train_loss += avg_loss_step
+                if acc.is_main_process:
+                    acc.log({"train/batch_loss": avg_loss_step, "train/learning_rate": self.current_lr(),
+                             "step": global_step}, step=global_step)
+            steps_per_epoch = math.ceil(len(self.train_loader) / acc.gradient_accumulation_steps)
+            avg_epoch = epoch_train_loss / max(1, steps_per_epoch)
+            if acc.is_main_process:
+                acc.log({"train/epoch_loss": avg_epoch, "epoch": epoch + 1}, step=global_step)
+                logger.info(f"Epoch {epoch + 1}/{self.num_epochs} completed. Avg Train Loss: {avg_epoch:.4f}")
+                if self.save_every_n_epochs > 0 and (epoch + 1) % self.save_every_n_epochs == 0:
+                    self.save_projection(epoch=epoch + 1)
+            if self.val_loader is not None:
+                val_loss, val_steps = 0.0, 0
+                for vb in self.val_loader:
+                    val_loss += self.engine.eval_loss(vb, pad_id=self.pad_id).item()
+                    val_steps += 1
+                avg_val = val_loss / val_steps if val_steps else float("inf")
+                if avg_val < best_val_loss:
+                    best_val_loss = avg_val
+                    if acc.is_main_process:
+                        self.save_projection(epoch=epoch + 1, is_best=True)
+                if acc.is_main_process:
+                    logger.info(f"Epoch {epoch + 1}/{self.num_epochs} validation loss: {avg_val:.4f} "
+                                "(last-word accuracy needs sampled generation: not computed in this build)")
+                    acc.log({"validation/loss": avg_val, "epoch": epoch + 1}, step=global_step)
+        logger.info("Stage 1 Training finished.")
+        self.save_projection(epoch=self.num_epochs)
+
+    def save_projection(self, epoch=None, is_best=False):
+        """Same files as ref:projector_trainer.py:455-521: projector_{best|epoch_N|final}.bin holding the
+        fp32 state dict (keys model.0.*, model.2.*) and projector_config.json {vision_dim, llm_dim}."""
+        if not self.accelerator.is_main_process:
+            return
+        torch.cuda.synchronize(self.device)
+        proj = self.engine.proj
+        name = "projector_best.bin" if is_best else (f"projector_epoch_{epoch}.bin" if epoch is not None
+                                                     else "projector_final.bin")
+        sd = {k: v.detach().cpu().clone() for k, v in proj.params().items()}
+        torch.save(sd, os.path.join(self.output_dir, name))
+        cfg = {"vision_dim": int(proj.shapes[0][1]), "llm_dim": int(proj.shapes[2][0])}
+        with open(os.path.join(self.output_dir, "projector_config.json"), "w") as f:
+            json.dump(cfg, f, indent=4)
+        logger.info(f"Projection layer state dict saved to {os.path.join(self.output_dir, name)}")

@@ -1,0 +1,190 @@
+"""Drop-in for ref:Stage1/train_projection_stage1.py: same flags (ref lines 139-159), same dataset item
+schema, same model-loading order; the training step itself runs on the B200 kernels.
+
+    torchrun --nproc-per-node N -m projectiontrainer_b200.train_projection_stage1 --image_root ... --train_json ...
+    python -m projectiontrainer_b200.train_projection_stage1 --synthetic 64 --disable_wandb     # no files, no weights
+
+`--synthetic N` (an addition) trains on N random CXR-shaped samples with random-init SigLIP-L/16-384 and
+Gemma3 weights — there are no checkpoints or datasets on the build / GPU boxes."""
+from __future__ import annotations
+
+import argparse
+import json
+import logging
+import os
+
+import torch
+from torch.utils.data import Dataset
+
+from .accelerator_setup import setup_accelerator_and_logging
+from .config import GEMMA3_1B, GEMMA3_4B, SIGLIP_L
+from .projector_trainer import ProjectionTrainerStage1
+from .projectors import MLPProjector
+
+logger = logging.getLogger(__name__)
+
+
+class XrayTextPairDataset(Dataset):
+    """X-ray image / caption pairs from a JSON list of {"image", "normal_caption"} records
+    (ref:train_projection_stage1.py:25-126).  Items: pixel_values f32 [3,S,S] (processor output),
+    token_ids i64 [max_length] (tokenizer padded to max_length), labels = token_ids with pad -> -100."""
+
+    def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_length=512, image_root_2=None):
+        self.image_root, self.image_root_2, self.img_size = image_root, image_root_2, img_size
+        self.processor, self.tokenizer, self.max_length = processor, tokenizer, max_length
+        self.samples = []
+        if json_file:
+            with open(json_file, "r", encoding="utf-8") as f:
+                self.samples = json.load(f)
+
+    def __len__(self):
+        return len(self.samples)
+
+    def _resolve(self, name):
+        for root in (self.image_root, self.image_root_2):
+            if root is None:
+                continue
+            p = os.path.join(root, name)
+            if os.path.isdir(p):      # a study directory: take its first image file
+                files = sorted(f for f in os.listdir(p) if f.lower().endswith((".jpg", ".jpeg", ".png")))
+                if files:
+                    return os.path.join(p, files[0])
+            if os.path.isfile(p):
+                return p
+        raise FileNotFoundError(f"Failed to find image file. Started with: {name}. Looked in: "
+                                f"{self.image_root}, {self.image_root_2}")
+
+    def __getitem__(self, idx):
+        from PIL import Image
+        sample = self.samples[idx]
+        image = Image.open(self._resolve(sample["image"])).convert("RGB").resize((self.img_size, self.img_size))
+        image_inputs = self.processor(images=image, return_tensors="pt")
+        text = self.tokenizer(sample["normal_caption"], max_length=self.max_length, padding="max_length",
+                              truncation=True, return_tensors="pt")
+        token_ids = text.input_ids.squeeze(0)
+        labels = token_ids.clone()
+        if self.tokenizer.pad_token_id is not None:
+            labels[labels == self.tokenizer.pad_token_id] = -100
+        return {"pixel_values": image_inputs.pixel_values.squeeze(0), "token_ids": token_ids, "labels": labels}
+
+
+class SyntheticXrayTextDataset(Dataset):
+    """CXR-shaped random samples: pixels ~ U(-1,1), ids[0] = BOS(2), rest ~ U{3..V-1}."""
+
+    def __init__(self, n, img_size, tokens, vocab, pad_id=0, seed=1234):
+        g = torch.Generator().manual_seed(seed)
+        self.px = torch.rand(n, 3, img_size, img_size, generator=g) * 2 - 1
+        self.ids = torch.randint(3, vocab, (n, tokens), generator=g)
+        self.ids[:, 0] = 2
+        self.pad_id = pad_id
+
+    def __len__(self):
+        return self.px.shape[0]
+
+    def __getitem__(self, i):
+        ids = self.ids[i]
+        labels = ids.clone()
+        labels[ids == self.pad_id] = -100
+        return {"pixel_values": self.px[i], "token_ids": ids, "labels": labels}
+
+
+class _Tok:
+    def __init__(self, pad, eos=1):
+        self.pad_token_id, self.eos_token_id = pad, eos
+
+
+def build_parser():
+    p = argparse.ArgumentParser(description="Train Stage 1: Vision-Language Projector Alignment (B200 build)")
+    p.add_argument("--image_root", type=str, default=None)
+    p.add_argument("--image_root_2", type=str, default=None)
+    p.add_argument("--train_json", type=str, default=None)
+    p.add_argument("--val_json", type=str, default=None)
+    p.add_argument("--train_val_split", type=float, default=0.0)
+    p.add_argument("--output_dir", type=str, default="./trained_projection_stage1")
+    p.add_argument("--vision_model_name", type=str, default="google/siglip-large-patch16-384")
+    p.add_argument("--llm_name", type=str, default="google/gemma-3-1b-it")
+    p.add_argument("--batch_size", type=int, default=4)
+    p.add_argument("--learning_rate", type=float, default=1e-4)
+    p.add_argument("--weight_decay", type=float, default=0.01)
+    p.add_argument("--num_epochs", type=int, default=10)
+    p.add_argument("--warmup_ratio", type=float, default=0.0)
+    p.add_argument("--wandb_project", type=str, default="xray_projection_training_stage1")
+    p.add_argument("--wandb_run_name", type=str, default=None)
+    p.add_argument("--wandb_log_freq", type=int, default=100)
+    p.add_argument("--disable_wandb", action="store_true")
+    p.add_argument("--gradient_accumulation_steps", type=int, default=2)
+    p.add_argument("--img_size", type=int, default=384)
+    p.add_argument("--save_every_n_epochs", type=int, default=2)
+    p.add_argument("--enable_qlora", action="store_true")
+    p.add_argument("--synthetic", type=int, default=0, help="train on N synthetic samples with random-init models")
+    p.add_argument("--synthetic_llm", choices=["1b", "4b"], default="1b")
+    p.add_argument("--max_length", type=int, default=512, help="caption tokens (the reference's dataset default)")
+    return p
+
+
+def main(argv=None):
+    args = build_parser().parse_args(argv)
+    if args.enable_qlora:
+        raise SystemExit("--enable_qlora is not supported: this build has no 4-bit (NF4) frozen-weight GEMM "
+                         "path (SURVEY.md §8f rank 4) and will not fall back to another backend")
+    accelerator = setup_accelerator_and_logging(args)
+    if args.synthetic > 0:
+        from .engine import PackedGemma, PackedSiglip
+        from . import weights as Wt
+        lc = GEMMA3_1B if args.synthetic_llm == "1b" else GEMMA3_4B
+        vc, dev = SIGLIP_L, accelerator.device
+        vision_encoder = PackedSiglip(Wt.random_siglip(vc, dev, 0), vc, dev)
+        language_model = PackedGemma(Wt.random_gemma(lc, dev, 0), lc, dev)
+        vision_dim, llm_dim = vc.hidden, lc.hidden
+        processor, tokenizer = None, _Tok(lc.pad_id)
+        T = min(args.max_length, 128)
+        train_dataset = SyntheticXrayTextDataset(args.synthetic, vc.image, T, lc.vocab, lc.pad_id)
+        val_dataset = None
+    else:
+        if not (args.image_root and args.train_json):
+            raise SystemExit("--image_root and --train_json are required (or use --synthetic N)")
+        from transformers import AutoModel, AutoModelForCausalLM, AutoProcessor, AutoTokenizer
+        processor = AutoProcessor.from_pretrained(args.vision_model_name)
+        vision_encoder = AutoModel.from_pretrained(args.vision_model_name, torch_dtype=torch.bfloat16)
+        tokenizer = AutoTokenizer.from_pretrained(args.llm_name, padding_side="left")
+        if tokenizer.pad_token is None:
+            tokenizer.pad_token = tokenizer.eos_token
+        language_model = AutoModelForCausalLM.from_pretrained(args.llm_name, torch_dtype=torch.bfloat16)
+        vision_dim = vision_encoder.config.vision_config.hidden_size
+        llm_dim = language_model.config.hidden_size
+        full = XrayTextPairDataset(args.image_root, args.train_json, processor, tokenizer, args.img_size,
+                                   max_length=args.max_length, image_root_2=args.image_root_2)
+        train_dataset, val_dataset = full, None
+        if args.val_json:
+            val_dataset = XrayTextPairDataset(args.image_root, args.val_json, processor, tokenizer, args.img_size,
+                                              max_length=args.max_length, image_root_2=args.image_root_2)
+        elif args.train_val_split > 0:
+            from sklearn.model_selection import train_test_split
+            tr, va = train_test_split(full.samples, test_size=args.train_val_split, random_state=42)
+            train_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
+                                                max_length=args.max_length, image_root_2=args.image_root_2)
+            val_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
+                                              max_length=args.max_length, image_root_2=args.image_root_2)
+            train_dataset.samples, val_dataset.samples = tr, va
+        if len(train_dataset) == 0:
+            logger.error("Training dataset is empty.")
+            return
+    projection_layer = MLPProjector(vision_dim, llm_dim)
+    trainer = ProjectionTrainerStage1(
+        accelerator=accelerator, vision_encoder=vision_encoder, language_model=language_model,
+        projection_layer=projection_layer, processor=processor, tokenizer=tokenizer,
+        train_dataset=train_dataset, val_dataset=val_dataset, output_dir=args.output_dir,
+        batch_size=args.batch_size, learning_rate=args.learning_rate, weight_decay=args.weight_decay,
+        num_epochs=args.num_epochs, gradient_accumulation_steps=args.gradient_accumulation_steps,
+        warmup_ratio=args.warmup_ratio, wandb_project=args.wandb_project,
+        save_every_n_epochs=args.save_every_n_epochs)
+    try:
+        trainer.train()
+    except Exception as e:      # the reference logs and does not re-raise (:378-389)
+        logger.error(f"Training failed: {e}", exc_info=True)
+    finally:
+        accelerator.end_training()
+
+
+if __name__ == "__main__":
+    main()

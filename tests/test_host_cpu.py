@@ -1,0 +1,123 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/pt_stage1.h declares (no
+compute calls), host logic of the drop-in trainer, and the world_size-2 gloo path of the data-parallel
+runtime (sum all-reduce of the flat gradient, loss gather, loader sharding)."""
+import ctypes
+import math
+import os
+import re
+import socket
+from pathlib import Path
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_c_abi_exports_every_declared_symbol():
+    from projectiontrainer_b200 import build
+    lib_path = build.build()
+    hdr = (ROOT / "include" / "pt_stage1.h").read_text()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(pt_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 20, names
+    lib = ctypes.CDLL(str(lib_path))
+    missing = [n for n in sorted(names) if not hasattr(lib, n)]
+    assert not missing, f"declared in pt_stage1.h but not exported: {missing}"
+    lib.pt_last_error.restype = ctypes.c_char_p
+    assert lib.pt_version() >= 100
+
+
+def test_compute_entry_fails_loudly_without_a_b200():
+    """No CPU fallback: on a box without an sm_100 device a compute entry returns PT_ERR_CUDA."""
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    from projectiontrainer_b200 import _lib
+    L = _lib.lib()
+    assert L.pt_device_check() == -2
+    assert b"no CPU path" in L.pt_last_error() or b"CUDA" in L.pt_last_error()
+    from projectiontrainer_b200 import ops
+    with pytest.raises(RuntimeError):
+        ops.linear(torch.zeros(8, 8, dtype=torch.bfloat16), torch.zeros(8, 8, dtype=torch.bfloat16))
+
+
+def test_projector_module_layout_matches_reference():
+    from projectiontrainer_b200.projectors import MLPProjector
+    m = MLPProjector(32, 48)
+    assert list(m.state_dict().keys()) == ["model.0.weight", "model.0.bias", "model.2.weight", "model.2.bias"]
+    assert m.model[0].in_features == 32 and m.model[0].out_features == 320 and m.model[2].out_features == 48
+    assert all(p.dtype == torch.float32 for p in m.parameters())
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 4, 32))          # CPU tensors: no fallback path
+
+
+def test_cosine_schedule_matches_oracle_and_hf_formula():
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200.projector_trainer import cosine_with_warmup
+    for warm, total in [(0, 10), (3, 10), (2, 3), (5, 5), (0, 1)]:
+        for s in range(total + 3):
+            assert abs(cosine_with_warmup(s, warm, total) * 1e-3 - O.cosine_lr(s, 1e-3, warm, total)) < 1e-15
+
+
+def test_sharded_loader_even_batches():
+    from projectiontrainer_b200.projector_trainer import _ShardedLoader
+    batches = list(range(7))
+    for world in (1, 2, 3, 4):
+        seen = [list(_ShardedLoader(batches, r, world)) for r in range(world)]
+        assert all(len(s) == math.ceil(7 / world) for s in seen)       # same step count on every rank
+        assert set(sum(seen, [])) == set(batches)                       # every batch is consumed
+
+
+def test_config_rejects_unsupported_models():
+    from projectiontrainer_b200.config import gemma_cfg_from_hf
+
+    class C:
+        model_type = "qwen3"
+    with pytest.raises(RuntimeError):
+        gemma_cfg_from_hf(C())
+
+
+def test_flops_model_matches_survey():
+    from projectiontrainer_b200.config import GEMMA3_1B, SIGLIP_L
+    from projectiontrainer_b200.flops import stage1_flops_per_image
+    f = stage1_flops_per_image(SIGLIP_L, GEMMA3_1B, 128)
+    assert abs(f["train"] / 1e9 - 2637.1) < 0.5 and abs(f["vision"] / 1e9 - 381.4) < 0.2
+
+
+# ------------------------------------------------------------------------------ world_size 2 (gloo)
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank_main(rank, world, port, out):
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    from projectiontrainer_b200.accelerator_setup import Stage1Accelerator
+    acc = Stage1Accelerator(gradient_accumulation_steps=2, device="cpu", backend="gloo")
+    assert acc.num_processes == world and acc.process_index == rank and acc.is_main_process == (rank == 0)
+    g = torch.full((1000,), float(rank + 1))
+    acc.all_reduce_sum_(g)                                   # the path's one exchange: SUM, mean folded later
+    mean = g / world
+    losses = acc.gather(torch.tensor(10.0 + rank))
+    out.put((rank, float(mean[0]), losses.tolist()))
+    acc.wait_for_everyone()
+    acc.end_training()
+
+
+def test_two_process_allreduce_and_gather_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rank_main, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, mean, losses in res:
+        assert mean == 1.5                      # mean over ranks of per-rank gradients (DDP semantics)
+        assert losses == [10.0, 11.0]
