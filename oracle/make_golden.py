@@ -45,7 +45,7 @@ CASES = {
                      dict(vocab=512, hidden=64, ff=128, layers=6, hq=4, hkv=2, hd=16, window=8,
                           q_scalar=16.0, rope_factor_global=8.0), 3, 12, True, 2, 2, 0.0),
     "tiny_nopad_mqa": (dict(hidden=64, ff=128, layers=1, heads=4, image=48, patch=16),
-                       dict(vocab=300, hidden=48, ff=96, layers=7, hq=4, hkv=1, hd=32, window=5,
+                       dict(vocab=304, hidden=48, ff=96, layers=7, hq=4, hkv=1, hd=32, window=5,
                             q_scalar=32.0), 2, 9, False, 1, 3, 0.34),
     "config1_full": ({}, {}, 2, 64, True, 2, 1, 0.0),
 }

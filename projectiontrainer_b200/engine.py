@@ -315,7 +315,7 @@ class Stage1Engine:
         R = B * T
         yf = self.buf("l_yf", (R, h), BF16)
         ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(T, S, S - T - 1))
-        logits = self.buf("l_logits", (R, c.vocab), BF16)
+        logits = self.buf("l_logits", (R, _pad8(c.vocab)), BF16)[:, :c.vocab]    # row stride padded to 16 B
         ops.linear(yf, Lm.embed, out=logits)
         tgt = self.buf("l_tgt", (R,), torch.int32)
         # targets[b, n_img-1+t] for t in 0..T-1 -> compact [B*T] (int copy: plumbing, not arithmetic)
