@@ -156,6 +156,12 @@ int pt_softmax_fwd(const float* scores, void* P_bf16, const uint8_t* keyvalid, i
 int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long rows, int Sk, int ld,
                    float scale, void* stream);
 
+/* Fused non-causal attention forward of the SigLIP tower (HF:models/siglip/modeling_siglip.py:293-306):
+ * out[b, q, h*hd .. ] = softmax(q k^T * scale) v, with q/k/v read in place from the fused activation
+ * qkv [B*N, 3*H*hd] (column blocks q | k | v, head h at columns h*hd) and out [B*N, H*hd], both bf16.
+ * tcgen05 kernel with K/V resident in shared memory; requires hd == 64 and N <= 576. */
+int pt_attn_siglip_fwd(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale, void* stream);
+
 /* GeGLU: act = gelu_tanh(g) * u with gu = [g | u] per row — HF:models/gemma3/modeling_gemma3.py:127-129. */
 int pt_geglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream);
 int pt_geglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, int ff, void* stream);

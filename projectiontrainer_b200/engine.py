@@ -197,22 +197,27 @@ class Stage1Engine:
         a = self.buf("v_a", (M, d), BF16)
         qkv = self.buf("v_qkv", (M, 3 * d), BF16)
         ld = _pad8(N)
-        sc = self.buf("v_scores", (B * H, N, ld), F32)
-        P = self.buf("v_P", (B * H, N, ld), BF16)
+        fused = hd == 64 and N <= 576      # tcgen05 fused attention kernel; other geometries: GEMM + softmax + GEMM
+        if not fused:
+            sc = self.buf("v_scores", (B * H, N, ld), F32)
+            P = self.buf("v_P", (B * H, N, ld), BF16)
         o = self.buf("v_o", (M, d), BF16)
         h1 = self.buf("v_h1", (M, c.ff), BF16)
         for L in V.layers:
             ops.layernorm_fwd(x, L["ln1_g"], L["ln1_b"], a, c.eps)
             ops.linear(a, L["qkv_w"], bias=L["qkv_b"], out=qkv)
-            # scores[b,h] = q k^T / sqrt(hd)
-            ops.gemm_raw(M=N, N=N, K=hd, A=qkv, lda=3 * d, B=qkv, b_off=d, ldb=3 * d, Cout=sc,
-                         ldc=ld, nz=(H, B, 1), a_zs=(hd, N * 3 * d, 0), b_zs=(hd, N * 3 * d, 0),
-                         c_zs=(N * ld, H * N * ld, 0), alpha=hd ** -0.5)
-            ops.softmax_fwd(sc, P, None, B * H, N, N, ld, H, 0, 0)
-            # o[b,:,h,:] = P[b,h] v[b,:,h,:]   (v read in place, MN-major)
-            ops.gemm_raw(M=N, N=hd, K=N, A=P, lda=ld, B=qkv, b_off=2 * d, ldb=3 * d, b_mn=True,
-                         Cout=o, ldc=d, nz=(H, B, 1), a_zs=(N * ld, H * N * ld, 0),
-                         b_zs=(hd, N * 3 * d, 0), c_zs=(hd, N * d, 0))
+            if fused:
+                ops.attn_siglip_fwd(qkv, o, B, N, H, hd, hd ** -0.5)
+            else:
+                # scores[b,h] = q k^T / sqrt(hd)
+                ops.gemm_raw(M=N, N=N, K=hd, A=qkv, lda=3 * d, B=qkv, b_off=d, ldb=3 * d, Cout=sc,
+                             ldc=ld, nz=(H, B, 1), a_zs=(hd, N * 3 * d, 0), b_zs=(hd, N * 3 * d, 0),
+                             c_zs=(N * ld, H * N * ld, 0), alpha=hd ** -0.5)
+                ops.softmax_fwd(sc, P, None, B * H, N, N, ld, H, 0, 0)
+                # o[b,:,h,:] = P[b,h] v[b,:,h,:]   (v read in place, MN-major)
+                ops.gemm_raw(M=N, N=hd, K=N, A=P, lda=ld, B=qkv, b_off=2 * d, ldb=3 * d, b_mn=True,
+                             Cout=o, ldc=d, nz=(H, B, 1), a_zs=(N * ld, H * N * ld, 0),
+                             b_zs=(hd, N * 3 * d, 0), c_zs=(hd, N * d, 0))
             ops.linear(o, L["o_w"], bias=L["o_b"], residual=x, out=x)
             ops.layernorm_fwd(x, L["ln2_g"], L["ln2_b"], a, c.eps)
             ops.linear(a, L["fc1_w"], bias=L["fc1_b"], act=ACT_GELU_TANH, out=h1)

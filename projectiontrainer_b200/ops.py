@@ -182,6 +182,12 @@ def qknorm_rope_bwd(dq, dk, qkv, wq, wk, cos_t, sin_t, d_qkv, S, hq, hkv, hd, ep
               _ptr(sin_t), _ptr(d_qkv), qkv.shape[0], int(S), hq, hkv, hd, _f(eps), _stream())
 
 
+def attn_siglip_fwd(qkv, out, B, N, H, hd, scale):
+    """Fused non-causal attention over the fused qkv activation [B*N, 3*H*hd] -> out [B*N, H*hd]."""
+    _req_cuda(qkv, out)
+    _lib.call("pt_attn_siglip_fwd", _ptr(qkv), _ptr(out), int(B), int(N), int(H), int(hd), _f(scale), _stream())
+
+
 def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window):
     _req_cuda(scores, P, keyvalid)
     _lib.call("pt_softmax_fwd", _ptr(scores), _ptr(P), _ptr(keyvalid), int(Z), int(Sq), int(Sk),
