@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--profile", action="store_true",
                     help="ncu helper: 1 warm-up step + --steps steps, nothing else, no JSON value")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0)
+    ap.add_argument("--graph", type=int, default=1, help="replay forward+backward as a CUDA graph (0 = eager launches)")
     return ap.parse_args()
 
 
@@ -47,7 +48,7 @@ def workload_config(args, n):
                         "MLP(1024->10240->1152) + Gemma3-1B, 128 caption tokens (S=575+128=703), bf16, "
                         "data-parallel",
             "batch_per_gpu": args.batch, "global_batch": args.batch * n, "caption_tokens": args.tokens,
-            "parallelism": f"dp{n}", "l2": "per-step working set (>30 GB of activations) >> 126 MB L2, no flush"}
+            "parallelism": f"dp{n}", "cuda_graph": bool(args.graph), "l2": "per-step working set (>30 GB of activations) >> 126 MB L2, no flush"}
 
 
 # --------------------------------------------------------------------------------------------- CPU arm
@@ -163,6 +164,7 @@ def run_ours(args):
     vc, lc = SIGLIP_L, GEMMA3_1B
     B, T = args.batch, args.tokens
     eng = build_engine(vc, lc, dev, seed=0, grad_accum=1)
+    eng.use_graph = bool(args.graph) and not args.profile
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     px = torch.rand(B, 3, vc.image, vc.image, generator=g, device=dev) * 2 - 1
     ids = torch.randint(3, lc.vocab, (B, T), generator=g, device=dev)
@@ -227,6 +229,7 @@ def run_ours(args):
     roof = None
     if rank == 0:
         ops.GEMM_PROFILE = []
+        eng.use_graph = False
         step(dev_batch)
         torch.cuda.synchronize()
         prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None

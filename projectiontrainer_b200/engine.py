@@ -13,10 +13,11 @@ cross-entropy internals, fp32 projector master weights, gradients and AdamW stat
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 
-from . import ops
+from . import _lib, ops
 from .config import GemmaCfg, SiglipCfg
 from .ops import ACT_GELU_ERF, ACT_GELU_TANH
 
@@ -161,6 +162,9 @@ class Stage1Engine:
         self._rope: dict = {}
         self.n_img = self.vcfg.tokens - 1      # ref:projector_trainer.py:173 drops token 0
         self.saved = None
+        # CUDA-graph replay of forward+backward (launch-bound inner loop: ~900 launches per step)
+        self.use_graph = os.environ.get("PT_STAGE1_GRAPH", "1") != "0"
+        self._graphs: dict = {}
 
     # ------------------------------------------------------------------ workspace
     def buf(self, name, shape, dtype):
@@ -453,6 +457,38 @@ class Stage1Engine:
         self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
 
+    def _graphed_forward_backward(self, batch: dict, pad_id) -> torch.Tensor:
+        """forward_backward through a CUDA graph keyed on the batch geometry: inputs are copied into
+        static device buffers, the first call per geometry runs eagerly (sizes the workspaces), the
+        second captures, later calls replay.  The all-reduce and the optimizer stay outside the graph
+        (lr and the step count change every step)."""
+        pv, ti, lb = batch["pixel_values"], batch["token_ids"], batch["labels"]
+        key = (tuple(pv.shape), tuple(ti.shape), pad_id)
+        g = self._graphs.get(key)
+        if g is None:
+            g = dict(px=torch.empty(pv.shape, dtype=F32, device=self.device),
+                     ids=torch.empty(ti.shape, dtype=torch.int64, device=self.device),
+                     lab=torch.empty(lb.shape, dtype=torch.int64, device=self.device),
+                     graph=None, calls=0, loss=None)
+            self._graphs[key] = g
+        g["px"].copy_(pv, non_blocking=True)
+        g["ids"].copy_(ti, non_blocking=True)
+        g["lab"].copy_(lb, non_blocking=True)
+        g["calls"] += 1
+        if g["calls"] == 1:
+            n0 = _lib.launch_count
+            loss = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id)
+            g["launches"] = _lib.launch_count - n0
+            return loss
+        if g["graph"] is None:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                g["loss"] = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id)
+            g["graph"] = graph
+        g["graph"].replay()
+        _lib.launch_count += g["launches"]          # kernels inside the replayed graph
+        return g["loss"]
+
     @torch.no_grad()
     def eval_loss(self, batch: dict, pad_id=0) -> torch.Tensor:
         """Validation forward (ref:Stage1/projector_trainer.py:304-370): the same loss, no backward."""
@@ -481,10 +517,13 @@ class Stage1Engine:
         the flat gradient over ranks (NCCL); the 1/world mean is folded into the optimizer kernel.
         Returns the device scalar loss (no host sync here)."""
         dev = self.device
-        px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
-        ids = batch["token_ids"].to(dev, non_blocking=True)
-        lab = batch["labels"].to(dev, non_blocking=True)
-        loss = self.forward_backward(px, ids, lab, pad_id)
+        if self.use_graph:
+            loss = self._graphed_forward_backward(batch, pad_id)
+        else:
+            px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
+            ids = batch["token_ids"].to(dev, non_blocking=True)
+            lab = batch["labels"].to(dev, non_blocking=True)
+            loss = self.forward_backward(px, ids, lab, pad_id)
         if allreduce is not None and world_size > 1:
             allreduce(self.proj.grad)
         self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size)
