@@ -293,6 +293,51 @@ def stage1_step(pixels, token_ids, labels, Wv, P, Wl, vcfg: SiglipCfg, lcfg: Gem
     return out
 
 
+# --------------------------------------------------------------------------- inference (prefill + greedy decode)
+def last_position_logits(X0, Wl: dict, lcfg: GemmaCfg):
+    """HF Gemma3ForCausalLM.forward on inputs_embeds with an all-ones mask, logits of the last position
+    (HF:models/gemma3/modeling_gemma3.py:649-656) — what `generate` samples the next token from."""
+    B, S, _ = X0.shape
+    hidden = gemma3_hidden(X0, torch.ones(B, S, dtype=torch.int64), Wl, lcfg)
+    y = rms_norm(hidden[:, -1, :], Wl["final_norm"], lcfg.eps)
+    return (y @ Wl["embed"].T).float()
+
+
+@torch.no_grad()
+def prefill_inputs(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaCfg, scale_dtype=None):
+    """ref:Stage1/inference_stage1.py:152-168: patch features without token 0 -> projector ->
+    (optionally) prompt embeddings appended."""
+    patch = siglip_forward(pixels, Wv, vcfg)[:, 1:, :]
+    X0 = projector_forward(patch, P)
+    if prompt_ids is not None and prompt_ids.shape[1] > 0:
+        X0 = torch.cat([X0, embed_tokens(prompt_ids, Wl["embed"], lcfg.hidden, scale_dtype).to(X0.dtype)], dim=1)
+    return X0
+
+
+@torch.no_grad()
+def greedy_generate(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaCfg, max_new_tokens: int,
+                    eos_id=1, pad_id=0, scale_dtype=None):
+    """`generate(inputs_embeds=..., do_sample=False)` (ref:Stage1/inference_stage1.py:176-187) restated
+    WITHOUT a KV cache: every step re-runs the full forward over [inputs ; tokens so far].  Returns the
+    new tokens i64 [B, n] (pad after eos, early stop when all rows finished) and the last-position
+    logits of every step."""
+    X = prefill_inputs(pixels, prompt_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype)
+    B = X.shape[0]
+    done = torch.zeros(B, dtype=torch.bool)
+    toks, step_logits = [], []
+    for _ in range(max_new_tokens):
+        lg = last_position_logits(X, Wl, lcfg)
+        step_logits.append(lg)
+        nxt = lg.argmax(dim=-1)
+        nxt = torch.where(done, torch.full_like(nxt, pad_id), nxt)
+        toks.append(nxt)
+        done |= nxt == eos_id
+        if bool(done.all()):
+            break
+        X = torch.cat([X, embed_tokens(nxt[:, None], Wl["embed"], lcfg.hidden, scale_dtype).to(X.dtype)], dim=1)
+    return torch.stack(toks, dim=1), torch.stack(step_logits, dim=1)
+
+
 # --------------------------------------------------------------------------- optimiser
 def cosine_lr(step: int, base_lr: float, warmup: int, total: int) -> float:
     """HF:optimization.py get_cosine_schedule_with_warmup (ref:projector_trainer.py:91-95)."""

@@ -268,10 +268,11 @@ class Stage1Engine:
                      c_zs=(S * ld, G * S * ld, c.hq * S * ld), alpha=alpha)
 
     # ------------------------------------------------------------------ LLM forward + loss
-    def llm_forward_loss(self, x0: torch.Tensor, keyvalid: torch.Tensor, targets: torch.Tensor,
-                         B: int, S: int, T: int, save: bool = True) -> torch.Tensor:
-        """x0 f32 [B*S, h] spliced embeddings -> device scalar loss; leaves dlogits in place and the
-        activations the input-gradient backward needs in self.saved."""
+    def _llm_stack(self, x0: torch.Tensor, keyvalid, B: int, S: int, save: bool, cache=None):
+        """Decoder stack over x0 f32 [B*S, h] (HF:models/gemma3/modeling_gemma3.py:404-434 per layer).
+        Returns the final residual stream (before the final norm) and, with save=True, the per-layer
+        activations the input-gradient backward needs.  With `cache` (prefill) the rotated keys and
+        the values of every layer are also stored into the KV cache at positions 0..S-1."""
         c, Lm = self.lcfg, self.llm
         h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
         M = B * S
@@ -296,10 +297,13 @@ class Stage1Engine:
             x1 = self.buf(tag + "x1", (M, h), F32)
             gu = self.buf(tag + "gu", (M, 2 * ff), BF16)
             y_mlp = self.buf(tag + "ym", (M, h), BF16)
-            x2 = self.buf(tag + "x2", (M, h), F32)
+            x2 = self.buf(tag + ("x2" if save else f"x2_{li & 1}"), (M, h), F32)
             ops.linear(a, L["qkv_w"], out=qkv)
             ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, S, hq,
                                 hkv, hd, c.eps)
+            if cache is not None:      # KV-cache fill: device-to-device copies (plumbing, no arithmetic)
+                cache["k"][li][:, :S].copy_(k_post.view(B, S, hkv * hd))
+                cache["v"][li][:, :S].copy_(qkv.view(B, S, QKV)[:, :, (hq + hkv) * hd:])
             self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
                               (0, hd, S * hkv * hd), sc, B, S, scale)
             ops.softmax_fwd(sc, P, keyvalid, B * hq, S, S, ld, hq, 1, 0 if full else c.window)
@@ -317,9 +321,19 @@ class Stage1Engine:
             ops.rmsnorm_residual_fwd(y_mlp, L["post_ffn_norm"], x1, x2,
                                      None if last else Lm.layers[li + 1]["in_norm"],
                                      None if last else a, c.eps)
-            sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ya=y_attn, x1=x1, gu=gu,
-                           ym=y_mlp, full=full))
+            if save:
+                sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ya=y_attn, x1=x1, gu=gu,
+                               ym=y_mlp, full=full))
             x = x2
+        return x, sv
+
+    def llm_forward_loss(self, x0: torch.Tensor, keyvalid: torch.Tensor, targets: torch.Tensor,
+                         B: int, S: int, T: int, save: bool = True) -> torch.Tensor:
+        """x0 f32 [B*S, h] spliced embeddings -> device scalar loss; leaves dlogits in place and the
+        activations the input-gradient backward needs in self.saved."""
+        c, Lm = self.lcfg, self.llm
+        h = c.hidden
+        x, sv = self._llm_stack(x0, keyvalid, B, S, save)
         # final norm only on rows that can carry a label: positions n_img-1 .. S-2 of every sample
         R = B * T
         yf = self.buf("l_yf", (R, h), BF16)
@@ -508,6 +522,161 @@ class Stage1Engine:
         finally:
             self.grad_accum = ga
         return loss.clone()
+
+    # ------------------------------------------------------------------ inference: prefill + decode
+    @torch.no_grad()
+    def prefill(self, pixels: torch.Tensor, prompt_ids: torch.Tensor | None = None,
+                max_new_tokens: int = 0) -> torch.Tensor:
+        """ref:Stage1/inference_stage1.py:150-175 (and projector_trainer.py:374-392): vision forward,
+        `[:, 1:, :]`, projector, optional prompt embeddings appended, all-ones attention mask, frozen
+        Gemma3 forward; the LM head runs on the LAST position only.  Returns f32 logits [B, V] and
+        leaves a KV cache sized for `max_new_tokens` more positions in self.cache."""
+        c = self.lcfg
+        dev = self.device
+        px = pixels.to(dev, dtype=F32, non_blocking=True)
+        B = px.shape[0]
+        T = 0 if prompt_ids is None else prompt_ids.shape[1]
+        S = self.n_img + T
+        h = c.hidden
+        patch = self.vision_forward(px)
+        x0 = self.buf("x0", (B * S, h), F32)
+        self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * h, save=False)
+        if T:
+            ids = prompt_ids.to(dev, non_blocking=True)
+            self.splice(ids, ids, x0, None)          # pad_id None: every key valid (all-ones mask)
+        Smax = _pad8(S + max_new_tokens)
+        kvd = c.hkv * c.hd
+        key = (B, Smax)
+        if getattr(self, "_cache_key", None) != key:
+            self.cache = dict(k=[torch.zeros(B, Smax, kvd, dtype=BF16, device=dev) for _ in range(c.layers)],
+                              v=[torch.zeros(B, Smax, kvd, dtype=BF16, device=dev) for _ in range(c.layers)])
+            self._cache_key = key
+        self.cache.update(pos=S, B=B, Smax=Smax)
+        x, _ = self._llm_stack(x0, None, B, S, save=False, cache=self.cache)
+        return self._last_logits(x, B, S)
+
+    def _last_logits(self, x: torch.Tensor, B: int, S: int) -> torch.Tensor:
+        c, Lm = self.lcfg, self.llm
+        yf = self.buf("i_yf", (B, c.hidden), BF16)
+        ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(1, S, S - 1))
+        logits = self.buf("i_logits", (B, _pad8(c.vocab)), F32)[:, :c.vocab]
+        ops.linear(yf, Lm.embed, out=logits)
+        return logits
+
+    @torch.no_grad()
+    def decode_step(self, tokens: torch.Tensor) -> torch.Tensor:
+        """One cached decode step: tokens i64 [B] at position cache['pos'] -> f32 logits [B, V]
+        (HF generate's per-token forward; sliding layers attend to the last `window` keys only)."""
+        c, Lm, kc = self.lcfg, self.llm, self.cache
+        B, pos, Smax = kc["B"], kc["pos"], kc["Smax"]
+        if pos >= Smax:
+            raise RuntimeError("KV cache full: prefill(max_new_tokens=...) was sized too small")
+        h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
+        G = hq // hkv
+        QKV = (hq + 2 * hkv) * hd
+        kvd = hkv * hd
+        scale = c.q_scalar ** -0.5
+        ids = tokens.to(self.device).view(B, 1)
+        x = self.buf("d_x", (B, h), F32)
+        ops.embed_splice(ids, ids, Lm.embed, Lm.embed_scale, None, 0, x,
+                         self.buf("d_mask", (B, 1), torch.int64), self.buf("d_lab", (B, 1), torch.int64),
+                         self.buf("d_kv", (B, 1), torch.uint8), self.buf("d_tgt", (B, 1), torch.int32))
+        a = self.buf("d_a", (B, h), BF16)
+        qkv = self.buf("d_qkv", (B, QKV), BF16)
+        q_post = self.buf("d_q", (B, hq * hd), BF16)
+        k_post = self.buf("d_k", (B, kvd), BF16)
+        ldm = _pad8(Smax)
+        sc = self.buf("d_sc", (B * hq, ldm), F32)
+        P = self.buf("d_P", (B * hq, ldm), BF16)
+        attn_o = self.buf("d_o", (B, hq * hd), BF16)
+        y = self.buf("d_y", (B, h), BF16)
+        x1 = self.buf("d_x1", (B, h), F32)
+        gu = self.buf("d_gu", (B, 2 * ff), BF16)
+        act = self.buf("d_act", (B, ff), BF16)
+        ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
+        for li, L in enumerate(Lm.layers):
+            full = c.is_full(li)
+            cos_t, sin_t = self.rope(Smax, full)
+            ops.linear(a, L["qkv_w"], out=qkv)
+            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t[pos:pos + 1], sin_t[pos:pos + 1],
+                                q_post, k_post, 1, hq, hkv, hd, c.eps)
+            K, V = kc["k"][li], kc["v"][li]
+            K[:, pos].copy_(k_post)
+            V[:, pos].copy_(qkv[:, (hq + hkv) * hd:])
+            lo = 0 if full else max(0, pos - c.window + 1)
+            n = pos + 1 - lo
+            ld = _pad8(n)
+            # scores[b, kvh*G+g, k] = scale * q[b, kvh*G+g, :] . K[b, lo+k, kvh, :]
+            ops.gemm_raw(M=G, N=n, K=hd, A=q_post, lda=hd, B=K, b_off=lo * kvd, ldb=kvd, Cout=sc, ldc=ld,
+                         nz=(hkv, B, 1), a_zs=(G * hd, hq * hd, 0), b_zs=(hd, Smax * kvd, 0),
+                         c_zs=(G * ld, hq * ld, 0), alpha=scale)
+            ops.softmax_fwd(sc, P, None, B * hq, 1, n, ld, hq, 0, 0)
+            ops.gemm_raw(M=G, N=hd, K=n, A=P, lda=ld, B=V, b_off=lo * kvd, ldb=kvd, b_mn=True,
+                         Cout=attn_o, ldc=hd, nz=(hkv, B, 1), a_zs=(G * ld, hq * ld, 0),
+                         b_zs=(hd, Smax * kvd, 0), c_zs=(G * hd, hq * hd, 0))
+            ops.linear(attn_o, L["o_w"], out=y)
+            ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            ops.linear(a, L["gu_w"], out=gu)
+            ops.geglu_fwd(gu, act)
+            ops.linear(act, L["down_w"], out=y)
+            last = li == len(Lm.layers) - 1
+            ops.rmsnorm_residual_fwd(y, L["post_ffn_norm"], x1, x,
+                                     None if last else Lm.layers[li + 1]["in_norm"],
+                                     None if last else a, c.eps)
+        kc["pos"] = pos + 1
+        return self._last_logits(x, B, 1)
+
+    @torch.no_grad()
+    def generate(self, pixels: torch.Tensor, prompt_ids: torch.Tensor | None = None, *,
+                 max_new_tokens: int = 64, do_sample: bool = False, temperature: float = 1.0,
+                 top_p: float = 1.0, top_k: int = 50, repetition_penalty: float = 1.0,
+                 pad_token_id: int | None = 0, eos_token_id: int | None = 1,
+                 generator: torch.Generator | None = None) -> torch.Tensor:
+        """`language_model.generate(inputs_embeds=projected, attention_mask=ones, ...)` of
+        ref:Stage1/inference_stage1.py:176-187 / projector_trainer.py:386-393: returns the NEW tokens
+        only, i64 [B, n<=max_new_tokens]; finished rows are filled with pad_token_id; stops early when
+        every row has produced eos.  Token selection (HF logits processors: repetition penalty ->
+        temperature -> top-k -> top-p -> multinomial, or argmax) is control logic on a [B, V] tensor
+        and uses torch ops; all model arithmetic runs in the sm_100a kernels."""
+        logits = self.prefill(pixels, prompt_ids, max_new_tokens=max_new_tokens)
+        B = logits.shape[0]
+        dev = self.device
+        out = torch.full((B, max_new_tokens), pad_token_id if pad_token_id is not None else 0,
+                         dtype=torch.int64, device=dev)
+        done = torch.zeros(B, dtype=torch.bool, device=dev)
+        n = 0
+        for step in range(max_new_tokens):
+            sc = logits.float().clone()
+            if repetition_penalty != 1.0 and step > 0:
+                prev = out[:, :step]
+                g = sc.gather(1, prev)
+                sc.scatter_(1, prev, torch.where(g < 0, g * repetition_penalty, g / repetition_penalty))
+            if do_sample:
+                if temperature != 1.0:
+                    sc = sc / temperature
+                if top_k and top_k > 0:
+                    kth = sc.topk(min(top_k, sc.shape[1]), dim=1).values[:, -1:]
+                    sc = sc.masked_fill(sc < kth, float("-inf"))
+                if top_p < 1.0:
+                    srt, idx = sc.sort(dim=1, descending=False)
+                    cum = srt.softmax(dim=1).cumsum(dim=1)
+                    rm = cum <= (1.0 - top_p)
+                    rm[:, -1:] = False
+                    sc = sc.masked_fill(rm.scatter(1, idx, rm), float("-inf"))
+                nxt = torch.multinomial(sc.softmax(dim=1), 1, generator=generator).squeeze(1)
+            else:
+                nxt = sc.argmax(dim=1)
+            if pad_token_id is not None:
+                nxt = torch.where(done, torch.full_like(nxt, pad_token_id), nxt)
+            out[:, step] = nxt
+            n = step + 1
+            if eos_token_id is not None:
+                done |= nxt == eos_token_id
+                if bool(done.all()):
+                    break
+            if step + 1 < max_new_tokens:
+                logits = self.decode_step(nxt)
+        return out[:, :n]
 
     def train_step(self, batch: dict, lr: float, *, pad_id=0, weight_decay: float = 0.01,
                    allreduce=None, world_size: int = 1) -> torch.Tensor:

@@ -3,14 +3,16 @@
 forward, `[:, 1:, :]` slice, projector, embed + splice, masks/labels, frozen-LLM loss, backward, clip 5.0,
 AdamW, cosine schedule) executes in `engine.Stage1Engine` on the sm_100a kernels; this file is the host
 loop around it.  Differences that are deliberate and documented in DESIGN.md: no DDP wrappers (one flat
-NCCL all-reduce of the projector gradient), one host read of the loss per step instead of two, and the
-validation pass reports the loss only (sampled generation needs the decode loop)."""
+NCCL all-reduce of the projector gradient) and one host read of the loss per step instead of two.  The
+validation pass reports the loss and, when the tokenizer can decode, the sampled-generation last-word
+accuracy (prefill + KV-cached decode in the engine)."""
 from __future__ import annotations
 
 import json
 import logging
 import math
 import os
+import re
 import time
 
 import torch
@@ -21,6 +23,14 @@ from . import weights as Wt
 from .engine import PackedGemma, PackedSiglip, ProjectorState, Stage1Engine
 
 logger = logging.getLogger(__name__)
+
+
+def get_last_word(text) -> str:
+    """ref:Stage1/projector_trainer.py:132-137."""
+    if not text or not isinstance(text, str):
+        return ""
+    words = re.findall(r"\b\w+\b", text.lower())
+    return words[-1] if words else ""
 
 
 def cosine_with_warmup(step: int, warmup: int, total: int) -> float:
@@ -140,19 +150,37 @@ class ProjectionTrainerStage1:
                 if self.save_every_n_epochs > 0 and (epoch + 1) % self.save_every_n_epochs == 0:
                     self.save_projection(epoch=epoch + 1)
             if self.val_loader is not None:
-                val_loss, val_steps = 0.0, 0
+                val_loss, val_steps, total_samples, correct_last_word = 0.0, 0, 0, 0
+                can_decode = hasattr(self.tokenizer, "batch_decode")
                 for vb in self.val_loader:
                     val_loss += self.engine.eval_loss(vb, pad_id=self.pad_id).item()
                     val_steps += 1
+                    if not can_decode:
+                        continue
+                    try:    # sampled generation from the image tokens only (ref :374-409)
+                        gen = self.engine.generate(vb["pixel_values"], None, max_new_tokens=64, do_sample=True,
+                                                   pad_token_id=self.pad_id,
+                                                   eos_token_id=getattr(self.tokenizer, "eos_token_id", None))
+                        gen_texts = self.tokenizer.batch_decode(gen.cpu(), skip_special_tokens=True)
+                        ref_texts = self.tokenizer.batch_decode(vb["token_ids"].cpu().numpy(),
+                                                                skip_special_tokens=True)
+                        for r, g_ in zip(ref_texts, gen_texts):
+                            rl, gl = get_last_word(r), get_last_word(g_)
+                            correct_last_word += int(bool(rl) and bool(gl) and rl == gl)
+                            total_samples += 1
+                    except Exception as e:
+                        logger.error(f"Error during generation for accuracy calculation: {e}", exc_info=True)
                 avg_val = val_loss / val_steps if val_steps else float("inf")
+                last_word_accuracy = (correct_last_word / total_samples) * 100 if total_samples else 0.0
                 if avg_val < best_val_loss:
                     best_val_loss = avg_val
                     if acc.is_main_process:
                         self.save_projection(epoch=epoch + 1, is_best=True)
                 if acc.is_main_process:
-                    logger.info(f"Epoch {epoch + 1}/{self.num_epochs} validation loss: {avg_val:.4f} "
-                                "(last-word accuracy needs sampled generation: not computed in this build)")
-                    acc.log({"validation/loss": avg_val, "epoch": epoch + 1}, step=global_step)
+                    logger.info(f"Epoch {epoch + 1}/{self.num_epochs} validation loss: {avg_val:.4f}, last word "
+                                f"accuracy: {last_word_accuracy:.2f}% ({correct_last_word}/{total_samples})")
+                    acc.log({"validation/loss": avg_val, "validation/last_word_accuracy": last_word_accuracy,
+                             "epoch": epoch + 1}, step=global_step)
         logger.info("Stage 1 Training finished.")
         self.save_projection(epoch=self.num_epochs)
 

@@ -1,0 +1,50 @@
+"""GPU probe: BASELINE.json configs[1] (SigLIP-L forward only, B=128) and configs[4] (prefill, 575 image
+tokens + 64-token prompt, Gemma3-1B, B=64) through the engine; CUDA-event timing, JSON lines."""
+import sys, json, argparse
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch
+from projectiontrainer_b200.config import GEMMA3_1B, SIGLIP_L
+from projectiontrainer_b200.engine import build_engine
+from projectiontrainer_b200.flops import stage1_flops_per_image
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--iters", type=int, default=5)
+ap.add_argument("--decode", type=int, default=16)
+a = ap.parse_args()
+dev = torch.device("cuda:0")
+eng = build_engine(SIGLIP_L, GEMMA3_1B, dev, seed=0)
+g = torch.Generator(device=dev).manual_seed(1)
+fl = stage1_flops_per_image(SIGLIP_L, GEMMA3_1B, 128)
+
+def timed(fn, iters):
+    for _ in range(2): fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+B = 128
+px = torch.rand(B, 3, 384, 384, generator=g, device=dev) * 2 - 1
+ms = timed(lambda: eng.vision_forward(px, drop_first=False), a.iters)
+print(json.dumps({"config": "configs[1] SigLIP-L/16-384 forward, bf16, B=128", "ms": ms, "images_per_s": B / ms * 1e3,
+                  "tflops": B * fl["vision"] / ms / 1e9}), flush=True)
+B, Tp = 64, 64
+px = torch.rand(B, 3, 384, 384, generator=g, device=dev) * 2 - 1
+ids = torch.randint(3, GEMMA3_1B.vocab, (B, Tp), generator=g, device=dev)
+ms = timed(lambda: eng.prefill(px, ids, max_new_tokens=a.decode), a.iters)
+print(json.dumps({"config": "configs[4] prefill 575 image + 64 prompt tokens, Gemma3-1B, B=64 (vision + projector + LLM, "
+                  "LM head on last position)", "ms": ms, "images_per_s": B / ms * 1e3}), flush=True)
+lg = eng.prefill(px, ids, max_new_tokens=a.decode)
+nxt = lg.argmax(-1)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(a.decode - 1):
+    nxt = eng.decode_step(nxt).argmax(-1)
+e1.record(); torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / (a.decode - 1)
+print(json.dumps({"config": "cached decode step after that prefill, B=64", "ms_per_token_step": ms,
+                  "tokens_per_s": B / ms * 1e3}), flush=True)
