@@ -33,7 +33,17 @@ typedef enum {
 } pt_status;
 
 typedef enum { PT_BF16 = 0, PT_F32 = 1, PT_I64 = 2, PT_I32 = 3 } pt_dtype;
-typedef enum { PT_ACT_NONE = 0, PT_ACT_GELU_TANH = 1, PT_ACT_GELU_ERF = 2 } pt_act;
+typedef enum {
+    PT_ACT_NONE = 0, PT_ACT_GELU_TANH = 1, PT_ACT_GELU_ERF = 2,
+    /* GeGLU fused into the gate||up projection (HF:models/gemma3/modeling_gemma3.py:127-129): N = 2*ff,
+     * B = [gate rows ; up rows]; C [M,2*ff] bf16 receives the pre-activations (kept for the backward) and
+     * aux [M,ff] bf16 (row stride ld_aux) receives gelu_tanh(gate) * up.  Needs ff % 128 == 0. */
+    PT_ACT_GEGLU = 3,
+    /* Backward of the above fused into the down-projection input gradient: the accumulator is
+     * d_act [M, N = ff]; aux = the saved pre-activations [M,2*ff] bf16 (row stride ld_aux, read only);
+     * C [M,2*ff] bf16 receives [d_act * up * gelu_tanh'(gate) | d_act * gelu_tanh(gate)]. */
+    PT_ACT_GEGLU_BWD = 4
+} pt_act;
 
 const char* pt_last_error(void);
 int pt_version(void);
@@ -96,6 +106,9 @@ typedef struct {
      * share one kv-head).  kg <= 1 disables it; with kg > 1, nz[2] must be 1. */
     int32_t kg;
     int64_t a_kgs, b_kgs;
+    /* Second matrix of the PT_ACT_GEGLU / PT_ACT_GEGLU_BWD epilogues (see pt_act); NULL otherwise. */
+    void* aux;
+    int64_t ld_aux;
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);

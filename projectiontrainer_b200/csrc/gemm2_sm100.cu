@@ -125,6 +125,63 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint32_t stg,
     __syncwarp();
 }
 
+// GeGLU backward fused into the down-projection input gradient: the accumulator chunk is d_act; the saved
+// pre-activations (gate at GU, up at GU + ff) are read in the row-contiguous second-phase layout and the two
+// halves of d_gu are written at C and C + ff:  d_gate = d_act * up * gelu'(gate),  d_up = d_act * gelu(gate).
+// d_act is rounded to bf16 first (what the unfused path stores between the GEMM and geglu_bwd).
+struct EpiGbwd {
+    uint8_t* C;           // d_gu, byte address of (row 0 of the slab, gate column col0)
+    const uint8_t* GU;    // gu, same position
+    long long c_row, g_row, ff_bytes;
+    int rows_valid, row_lo, cols_q;
+};
+
+__device__ __forceinline__ void epi_chunk_gbwd(const uint32_t (&v)[32], uint32_t stg, int lane, const EpiGbwd& o) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        ptx::sts128(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncwarp();
+    const int ch = lane & 7, c = ch * 4, rsub = lane >> 3;
+    const bool col_ok = c < o.cols_q;
+    uint2 gq[8], uq[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + rsub;
+        gq[it] = make_uint2(0u, 0u); uq[it] = make_uint2(0u, 0u);
+        if (col_ok && r >= o.row_lo && r < o.rows_valid) {
+            const uint8_t* gp = o.GU + r * o.g_row + c * 2;
+            gq[it] = *reinterpret_cast<const uint2*>(gp);
+            uq[it] = *reinterpret_cast<const uint2*>(gp + o.ff_bytes);
+        }
+    }
+    const uint32_t sp = stg + rsub * 128;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + rsub;
+        const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
+        const bool ok = col_ok && r >= o.row_lo && r < o.rows_valid;
+        const float d[4] = {round_bf16(a.x), round_bf16(a.y), round_bf16(a.z), round_bf16(a.w)};
+        const float g[4] = {bf16_lo(gq[it].x), bf16_hi(gq[it].x), bf16_lo(gq[it].y), bf16_hi(gq[it].y)};
+        const float u[4] = {bf16_lo(uq[it].x), bf16_hi(uq[it].x), bf16_lo(uq[it].y), bf16_hi(uq[it].y)};
+        float dg[4], du[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float val, grad;
+            gelu_tanh_fast_both(g[j], val, grad);
+            dg[j] = d[j] * u[j] * grad;
+            du[j] = d[j] * val;
+        }
+        if (ok) {
+            uint8_t* cp = o.C + r * o.c_row + c * 2;
+            uint2 w; w.x = pack_bf16(dg[0], dg[1]); w.y = pack_bf16(dg[2], dg[3]);
+            *reinterpret_cast<uint2*>(cp) = w;
+            w.x = pack_bf16(du[0], du[1]); w.y = pack_bf16(du[2], du[3]);
+            *reinterpret_cast<uint2*>(cp + o.ff_bytes) = w;
+        }
+    }
+    __syncwarp();
+}
+
 // ---- kernel ----------------------------------------------------------------------------------------
 template <int BN, int ACT>
 __global__ void __launch_bounds__(kGemm2Threads, 1)
@@ -218,7 +275,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 }
                 const bool kga = p.kg_slot >= 0 && (p.a_emask & 1), kgb = p.kg_slot >= 0 && (p.b_emask & 1);
                 const int m0 = (m_blk == mt - 1 ? p.m_last : m_blk * TM) + static_cast<int>(rank) * BM;
-                const int n0 = (n_blk == nt - 1 ? p.n_last : n_blk * BN) + static_cast<int>(rank) * BNH;
+                // fused GeGLU: the pair's tile is [128 gate rows | the 128 up rows of the same ff range]
+                const int n0 = ACT == PT_ACT_GEGLU
+                                   ? n_blk * BNH + static_cast<int>(rank) * p.ff
+                                   : (n_blk == nt - 1 ? p.n_last : n_blk * BN) + static_cast<int>(rank) * BNH;
                 int g = 0, kb = 0;
                 for (int it = 0; it < k_iters; ++it) {
                     if (kga) ea0 = g;
@@ -312,6 +372,47 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);
             constexpr int NCH = BNH / 32;
+            if constexpr (ACT == PT_ACT_GEGLU) {
+                // accumulator columns [0,128) = gate, [128,256) = up of ff columns n_blk*128 .. +127; this warp
+                // produces two 32-column chunks: gate and up pre-activations -> C, gelu_tanh(gate)*up -> aux
+                const bool live = rows_valid > row_lo;                                   // warp-uniform
+#pragma unroll 1
+                for (int c2 = 0; c2 < 2; ++c2) {
+                    const int cg = (hf * 2 + c2) * 32;
+                    uint32_t vg[32], vu[32];
+                    if (live) {
+                        ptx::tmem_ld_32x32(taddr + cg, vg);
+                        ptx::tmem_ld_32x32(taddr + BNH + cg, vu);
+                        ptx::tmem_ld_wait();
+                    }
+                    if (c2 == 1) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
+                    }
+                    if (!live) continue;
+                    const int colg = n_blk * BNH + cg;
+                    EpiArgs o;
+                    o.Cpre = nullptr; o.R = nullptr; o.bias = nullptr;
+                    o.p_row = 0; o.p_step = 0; o.r_row = 0; o.r_step = 0;
+                    o.c_f32 = 0; o.r_f32 = 0; o.alpha = 1.f;
+                    o.rows_valid = rows_valid; o.row_lo = row_lo; o.cols_q = 32;
+                    o.c_row = p.ldc * 2; o.c_step = 4 * o.c_row;
+                    uint8_t* crow = static_cast<uint8_t*>(p.C) + (coff + static_cast<long long>(row0) * p.ldc) * 2;
+                    o.C = crow + static_cast<long long>(colg) * 2;
+                    epi_chunk<PT_ACT_NONE>(vg, stg, lane, o);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float g = round_bf16(__uint_as_float(vg[j])), u = round_bf16(__uint_as_float(vu[j]));
+                        vg[j] = __float_as_uint(gelu_tanh_fast_f(g) * u);
+                    }
+                    o.C = crow + static_cast<long long>(p.ff + colg) * 2;
+                    epi_chunk<PT_ACT_NONE>(vu, stg, lane, o);
+                    o.c_row = p.ld_aux * 2; o.c_step = 4 * o.c_row;
+                    o.C = static_cast<uint8_t*>(p.aux) + (static_cast<long long>(row0) * p.ld_aux + colg) * 2;
+                    epi_chunk<PT_ACT_NONE>(vg, stg, lane, o);
+                }
+            } else {
 #pragma unroll 1
             for (int c = 0; c < NCH; ++c) {
                 const int col_local = hf * BNH + c * 32;
@@ -329,6 +430,16 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
                 }
                 if (!live) continue;
+                if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+                    EpiGbwd o;
+                    o.c_row = p.ldc * 2; o.g_row = p.ld_aux * 2; o.ff_bytes = static_cast<long long>(p.ff) * 2;
+                    o.C = static_cast<uint8_t*>(p.C) + (static_cast<long long>(row0) * p.ldc + col0) * 2;
+                    o.GU = static_cast<const uint8_t*>(p.aux) + (static_cast<long long>(row0) * p.ld_aux + col0) * 2;
+                    o.rows_valid = rows_valid; o.row_lo = row_lo;
+                    o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
+                    epi_chunk_gbwd(v, stg, lane, o);
+                    continue;
+                }
                 EpiArgs o;
                 const long long co = coff + static_cast<long long>(row0) * p.ldc + col0;
                 const int ce = p.c_f32 ? 4 : 2, re = p.r_f32 ? 4 : 2;
@@ -345,6 +456,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
                 epi_chunk<ACT>(v, stg, lane, o);
             }
+            }   // !GEGLU
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
@@ -408,7 +520,12 @@ int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const Gem
     case BN_:                                                                           \
         if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, p, tiles, st); \
         if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, p, tiles, st);   \
+        if (p.act == PT_ACT_GEGLU_BWD) return launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, p, tiles, st); \
         return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, p, tiles, st);
+    if (p.act == PT_ACT_GEGLU) {
+        if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }
+        return launch_gemm2_t<256, PT_ACT_GEGLU>(ta, tb, p, tiles, st);
+    }
     switch (bn) {
         PT_G2(256) PT_G2(192) PT_G2(128) PT_G2(64)
         default: set_error("gemm2: unsupported BN %d", bn); return PT_ERR_INVALID;

@@ -30,6 +30,10 @@ struct GemmDev {
     // that are partly or wholly out of bounds were measured to stall the pipeline) and its epilogue skips
     // the rows / columns the previous tile already produced.
     int m_last, n_last;
+    // fused GeGLU epilogues (PT_ACT_GEGLU / PT_ACT_GEGLU_BWD): second matrix, its row stride, and ff
+    void* aux;
+    long long ld_aux;
+    int ff;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {

@@ -456,7 +456,19 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     }
     PT_REQUIRE((a->N % 4) == 0 || (!a->bias && !a->residual && !a->C_pre),
                "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
-    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_GELU_ERF, "pt_gemm_bf16: bad act %d", a->act);
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_GEGLU_BWD, "pt_gemm_bf16: bad act %d", a->act);
+    const bool geglu = a->act == PT_ACT_GEGLU, geglu_bwd = a->act == PT_ACT_GEGLU_BWD;
+    if (geglu || geglu_bwd) {
+        PT_REQUIRE(a->aux != nullptr && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0 && a->ld_aux % 8 == 0,
+                   "pt_gemm_bf16: fused GeGLU needs a 16B-aligned aux matrix with ld_aux %% 8 == 0");
+        PT_REQUIRE(a->c_dtype == PT_BF16 && !a->bias && !a->residual && !a->C_pre && a->alpha == 1.0f,
+                   "pt_gemm_bf16: fused GeGLU takes bf16 C and no bias / residual / C_pre / alpha");
+        PT_REQUIRE(a->nz[0] * a->nz[1] * a->nz[2] == 1 && kg == 1, "pt_gemm_bf16: fused GeGLU is not batched");
+        PT_REQUIRE(g_gemm_impl != 1, "pt_gemm_bf16: fused GeGLU epilogues exist in the CTA-pair kernel only");
+        const int ff = geglu ? a->N / 2 : a->N;
+        PT_REQUIRE(ff % 128 == 0 && (!geglu || a->N == 2 * ff), "pt_gemm_bf16: fused GeGLU needs ff %% 128 == 0 (ff=%d)", ff);
+        PT_REQUIRE(a->ldc >= 2 * ff && a->ld_aux >= (geglu ? ff : 2 * ff), "pt_gemm_bf16: fused GeGLU: ldc / ld_aux too small");
+    }
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
 
     GemmDev p;
@@ -485,13 +497,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     p.ldc = a->ldc; p.ldr = a->ldr;
     p.c_f32 = a->c_dtype == PT_F32; p.r_f32 = a->r_dtype == PT_F32;
     p.act = a->act; p.alpha = a->alpha;
+    p.aux = a->aux; p.ld_aux = a->ld_aux; p.ff = geglu ? a->N / 2 : a->N;
 
     const long long nbatch = static_cast<long long>(a->nz[0]) * a->nz[1] * a->nz[2];
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUtensorMap ta, tb;
     if (g_gemm_impl != 1) {
         // CTA-pair kernel (gemm2_sm100.cu): 256 x bn tiles, one per cluster of two SMs
-        const int bn = pick_bn2(a->M, a->N, nbatch, p.b_mn);
+        const int bn = geglu ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
         const long long mt = (a->M + 2 * BM - 1) / (2 * BM), nt = (a->N + bn - 1) / bn;
         PT_REQUIRE(mt * nt * nbatch < (1ll << 31), "pt_gemm_bf16: too many tiles");
         p.raster_n = nt <= mt;

@@ -165,6 +165,8 @@ class Stage1Engine:
         # CUDA-graph replay of forward+backward (launch-bound inner loop: ~900 launches per step)
         self.use_graph = os.environ.get("PT_STAGE1_GRAPH", "1") != "0"
         self._graphs: dict = {}
+        # GeGLU forward / backward fused into the gate||up and down-dgrad GEMM epilogues (needs ff % 128 == 0)
+        self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
     def buf(self, name, shape, dtype):
@@ -314,8 +316,11 @@ class Stage1Engine:
                          c_zs=(hd, G * hd, S * hq * hd))
             ops.linear(attn_o, L["o_w"], out=y_attn)
             ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
-            ops.linear(a, L["gu_w"], out=gu)
-            ops.geglu_fwd(gu, act)
+            if self.fuse_geglu:
+                ops.linear_geglu(a, L["gu_w"], gu, act)
+            else:
+                ops.linear(a, L["gu_w"], out=gu)
+                ops.geglu_fwd(gu, act)
             ops.linear(act, L["down_w"], out=y_mlp)
             last = li == len(Lm.layers) - 1
             ops.rmsnorm_residual_fwd(y_mlp, L["post_ffn_norm"], x1, x2,
@@ -379,8 +384,11 @@ class Stage1Engine:
             cos_t, sin_t = self.rope(S, a["full"])
             # ---- MLP branch
             ops.rmsnorm_bwd(dx, a["ym"], L["post_ffn_norm"], d_y, c.eps)
-            ops.linear_dgrad(d_y, L["down_w"], out=d_act)
-            ops.geglu_bwd(d_act, a["gu"], d_gu)
+            if self.fuse_geglu:
+                ops.linear_dgrad_geglu_bwd(d_y, L["down_w"], a["gu"], d_gu)
+            else:
+                ops.linear_dgrad(d_y, L["down_w"], out=d_act)
+                ops.geglu_bwd(d_act, a["gu"], d_gu)
             ops.linear_dgrad(d_gu, L["gu_w"], out=d_y)
             ops.rmsnorm_bwd(d_y, a["x1"], L["pre_ffn_norm"], dx, c.eps, add=dx)
             # ---- attention branch
@@ -616,8 +624,11 @@ class Stage1Engine:
                          b_zs=(hd, Smax * kvd, 0), c_zs=(G * hd, hq * hd, 0))
             ops.linear(attn_o, L["o_w"], out=y)
             ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
-            ops.linear(a, L["gu_w"], out=gu)
-            ops.geglu_fwd(gu, act)
+            if self.fuse_geglu:
+                ops.linear_geglu(a, L["gu_w"], gu, act)
+            else:
+                ops.linear(a, L["gu_w"], out=gu)
+                ops.geglu_fwd(gu, act)
             ops.linear(act, L["down_w"], out=y)
             last = li == len(Lm.layers) - 1
             ops.rmsnorm_residual_fwd(y, L["post_ffn_norm"], x1, x,

@@ -11,7 +11,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
+from ._lib import ACT_GEGLU, ACT_GEGLU_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
@@ -37,10 +37,10 @@ def _req_cuda(*ts):
 def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0), b_zs=(0, 0, 0),
              c_zs=(0, 0, 0), a_mn=False, b_mn=False, bias=None, residual=None, ldr=0,
              r_zs=(0, 0, 0), act=ACT_NONE, alpha=1.0, c_pre=None, kg=1, a_kgs=0, b_kgs=0,
-             a_off=0, b_off=0, c_off=0, r_off=0):
+             a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0):
     """Fully general launcher; A/B/Cout are tensors used only as base pointers
     (+ element offsets), all geometry comes from the explicit arguments."""
-    _req_cuda(A, B, Cout, bias, residual, c_pre)
+    _req_cuda(A, B, Cout, bias, residual, c_pre, aux)
     if A.dtype != torch.bfloat16 or B.dtype != torch.bfloat16:
         raise RuntimeError("gemm operands must be bf16")
     g = GemmArgs()
@@ -73,6 +73,9 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     g.kg = int(kg)
     g.a_kgs = int(a_kgs)
     g.b_kgs = int(b_kgs)
+    if aux is not None:
+        g.aux = aux.data_ptr()
+        g.ld_aux = int(ld_aux)
     if GEMM_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -115,6 +118,29 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out=None, out_dtype=torch
              ldc=out.stride(0), residual=residual,
              ldr=0 if residual is None else residual.stride(0))
     return out
+
+
+def geglu_fusable(ff: int) -> bool:
+    """The fused GeGLU GEMM epilogues tile ff in 128-column blocks (CTA-pair kernel only)."""
+    return ff % 128 == 0
+
+
+def linear_geglu(x: torch.Tensor, w_gu: torch.Tensor, gu: torch.Tensor, act: torch.Tensor):
+    """gu[M,2ff] = x @ w_gu^T (gate | up pre-activations, kept for the backward) and, in the same
+    epilogue, act[M,ff] = gelu_tanh(gate) * up   (HF:models/gemma3/modeling_gemma3.py:127-129)."""
+    M, K = x.shape
+    N = w_gu.shape[0]
+    gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w_gu, ldb=w_gu.stride(0), Cout=gu, ldc=gu.stride(0),
+             act=ACT_GEGLU, aux=act, ld_aux=act.stride(0))
+
+
+def linear_dgrad_geglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, d_gu: torch.Tensor):
+    """d_act = dy[M,h] @ w_down[h,ff] formed in TMEM only; the epilogue turns it into
+    d_gu[M,2ff] = [d_act * up * gelu_tanh'(gate) | d_act * gelu_tanh(gate)] reading the saved gu."""
+    M, N = dy.shape
+    ff = w_down.shape[1]
+    gemm_raw(M=M, N=ff, K=N, A=dy, lda=dy.stride(0), B=w_down, ldb=w_down.stride(0), b_mn=True, Cout=d_gu,
+             ldc=d_gu.stride(0), act=ACT_GEGLU_BWD, aux=gu, ld_aux=gu.stride(0))
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None) -> torch.Tensor:

@@ -130,3 +130,37 @@ def test_gemm_grouped_contraction(cuda_dev):
     dOf = dO.float().view(Bn, S, Hkv, G, D)
     ref = torch.einsum("bhgqk,bqhgd->bkhd", Pf, dOf)
     _check(out, ref, name="grouped")
+
+
+@pytest.mark.parametrize("M,ff,h", [(700, 384, 192), (22496, 6912, 1152), (64, 128, 64), (3, 256, 128)])
+def test_gemm_fused_geglu_fwd_bwd(cuda_dev, gemm_impl, M, ff, h):
+    """GeGLU fused into the gate||up epilogue and its backward fused into the down-dgrad epilogue, against
+    the unfused kernels (same bf16 rounding points) and a torch fp32 reference."""
+    from projectiontrainer_b200 import ops
+    if gemm_impl == 1:
+        pytest.skip("fused GeGLU epilogues exist in the CTA-pair kernel only")
+    torch.manual_seed(M + ff)
+    x, w_gu = _rand((M, h), cuda_dev), _rand((2 * ff, h), cuda_dev, 0.08)
+    gu = torch.empty(M, 2 * ff, device=cuda_dev, dtype=torch.bfloat16)
+    act = torch.empty(M, ff, device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_geglu(x, w_gu, gu, act)
+    gu_ref = x.float() @ w_gu.float().t()
+    _check(gu, gu_ref, name="gu")
+    g, u = gu.float()[:, :ff], gu.float()[:, ff:]
+    _check(act, torch.nn.functional.gelu(g, approximate="tanh") * u, tol=1e-2, name="act vs torch on the stored gu")
+    gu2, act2 = ops.linear(x, w_gu), torch.empty_like(act)
+    ops.geglu_fwd(gu2, act2)
+    assert torch.equal(gu2, gu)
+    _check(act, act2.float(), tol=1e-2, name="act vs unfused kernel")
+    # backward
+    dy, w_down = _rand((M, h), cuda_dev), _rand((h, ff), cuda_dev, 0.08)
+    d_gu = torch.empty(M, 2 * ff, device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_dgrad_geglu_bwd(dy, w_down, gu, d_gu)
+    d_act = ops.linear_dgrad(dy, w_down)
+    d_gu2 = torch.empty_like(d_gu)
+    ops.geglu_bwd(d_act, gu, d_gu2)
+    _check(d_gu, d_gu2.float(), tol=1e-2, name="d_gu vs unfused kernel")
+    gt = g.clone().requires_grad_(True)
+    ut = u.clone().requires_grad_(True)
+    (torch.nn.functional.gelu(gt, approximate="tanh") * ut).backward(d_act.float())
+    _check(d_gu, torch.cat([gt.grad, ut.grad], 1), tol=1e-2, name="d_gu vs torch autograd")
