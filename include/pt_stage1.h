@@ -45,6 +45,13 @@ typedef enum {
     PT_ACT_GEGLU_BWD = 4
 } pt_act;
 
+typedef enum {
+    PT_BAND_NONE = 0,
+    PT_BAND_SCORES = 1,      /* rows = queries, columns = keys (Q K^T, dO V^T): masked tiles skipped */
+    PT_BAND_K_BY_QUERY = 2,  /* rows = queries, contraction over keys (P V, dS K) */
+    PT_BAND_K_BY_KEY = 3     /* rows = keys, contraction over queries (P^T dO, dS^T Q) */
+} pt_band;
+
 const char* pt_last_error(void);
 int pt_version(void);
 /* 0 when a compute-capability 10.x device is current, PT_ERR_CUDA otherwise. */
@@ -106,6 +113,13 @@ typedef struct {
      * share one kv-head).  kg <= 1 disables it; with kg > 1, nz[2] must be 1. */
     int32_t kg;
     int64_t a_kgs, b_kgs;
+    /* Causal / sliding-window band of a self-attention product (M = K or M = N = sequence length): tiles and
+     * K blocks that only meet masked (query, key) pairs are skipped.  Their outputs are NOT written
+     * (PT_BAND_SCORES) — consumers must ignore masked positions, as pt_softmax_fwd / pt_softmax_bwd do — and
+     * the skipped K blocks must hold zeros in the probability operand (they do: the softmax kernels write 0).
+     * band_window = sliding window (key k visible to query q iff q - window < k <= q), 0 = causal only. */
+    int32_t band;             /* pt_band */
+    int32_t band_window;
     /* Second matrix of the PT_ACT_GEGLU / PT_ACT_GEGLU_BWD epilogues (see pt_act); NULL otherwise. */
     void* aux;
     int64_t ld_aux;
@@ -165,15 +179,22 @@ int pt_qknorm_rope_bwd(const void* dq, const void* dk, const void* qkv, const fl
  * — HF:masking_utils.py:74-99,148-159; HF:models/gemma3/modeling_gemma3.py:370-384 (SigLIP: no mask). */
 int pt_softmax_fwd(const float* scores, void* P_bf16, const uint8_t* keyvalid, int Z, int Sq, int Sk,
                    int ld, int heads_per_batch, int causal, int window, void* stream);
-/* dS = scale * P * (dP - rowsum(P dP)) */
+/* dS = scale * P * (dP - rowsum(P dP)).  Row r belongs to query r % Sq; with Sq > 0 the same causal / window
+ * band as the forward bounds the columns that are read (P is 0 and dP may be unwritten outside it, see
+ * pt_gemm_args.band); Sq = 0 reads whole rows. */
 int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long rows, int Sk, int ld,
-                   float scale, void* stream);
+                   float scale, int Sq, int causal, int window, void* stream);
 
 /* Fused non-causal attention forward of the SigLIP tower (HF:models/siglip/modeling_siglip.py:293-306):
  * out[b, q, h*hd .. ] = softmax(q k^T * scale) v, with q/k/v read in place from the fused activation
  * qkv [B*N, 3*H*hd] (column blocks q | k | v, head h at columns h*hd) and out [B*N, H*hd], both bf16.
- * tcgen05 kernel with K/V resident in shared memory; requires hd == 64 and N <= 576. */
+ * tcgen05 flash-style kernel (96-key K/V tiles streamed by TMA, online softmax with lazy rescale, two CTAs
+ * per SM); requires hd == 64, any N. */
 int pt_attn_siglip_fwd(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale, void* stream);
+/* First-generation kernel (K/V of a whole (image, head) resident in shared memory, one CTA per SM; N <= 576):
+ * kept as a cross-check for the tests. */
+int pt_attn_siglip_fwd_v1(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale,
+                          void* stream);
 
 /* GeGLU: act = gelu_tanh(g) * u with gu = [g | u] per row — HF:models/gemma3/modeling_gemma3.py:127-129. */
 int pt_geglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream);

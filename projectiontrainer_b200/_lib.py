@@ -12,6 +12,7 @@ PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "libpt_stage1.so"
 
 PT_BF16, PT_F32, PT_I64, PT_I32 = 0, 1, 2, 3
+BAND_NONE, BAND_SCORES, BAND_K_BY_QUERY, BAND_K_BY_KEY = 0, 1, 2, 3
 ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF, ACT_GEGLU, ACT_GEGLU_BWD = 0, 1, 2, 3, 4
 
 
@@ -27,6 +28,7 @@ class GemmArgs(C.Structure):
         ("residual", C.c_void_p), ("r_dtype", C.c_int32), ("ldr", C.c_int64), ("r_zs", C.c_int64 * 3),
         ("act", C.c_int32), ("alpha", C.c_float),
         ("kg", C.c_int32), ("a_kgs", C.c_int64), ("b_kgs", C.c_int64),
+        ("band", C.c_int32), ("band_window", C.c_int32),
         ("aux", C.c_void_p), ("ld_aux", C.c_int64),
     ]
 

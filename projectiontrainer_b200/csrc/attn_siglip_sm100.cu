@@ -255,11 +255,11 @@ attn_siglip_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 
 using namespace pt;
 
-extern "C" int pt_attn_siglip_fwd(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale,
+extern "C" int pt_attn_siglip_fwd_v1(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale,
                                   void* stream) {
-    PT_REQUIRE(qkv_bf16 && out_bf16, "pt_attn_siglip_fwd: null pointer");
-    PT_REQUIRE(hd == kAhd, "pt_attn_siglip_fwd: head_dim must be 64 (got %d)", hd);
-    PT_REQUIRE(B > 0 && H > 0 && N > 0 && N <= kAmaxKeys, "pt_attn_siglip_fwd: need 0 < N <= %d (N=%d)", kAmaxKeys, N);
+    PT_REQUIRE(qkv_bf16 && out_bf16, "pt_attn_siglip_fwd_v1: null pointer");
+    PT_REQUIRE(hd == kAhd, "pt_attn_siglip_fwd_v1: head_dim must be 64 (got %d)", hd);
+    PT_REQUIRE(B > 0 && H > 0 && N > 0 && N <= kAmaxKeys, "pt_attn_siglip_fwd_v1: need 0 < N <= %d (N=%d)", kAmaxKeys, N);
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const int d = H * kAhd;
     const int ext[3] = {B, 1, 1};

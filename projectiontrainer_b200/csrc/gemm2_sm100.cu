@@ -274,13 +274,18 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     eb0 = (p.b_emask & 1) ? z0 : 0; eb1 = (p.b_emask & 2) ? z1 : 0; eb2 = (p.b_emask & 4) ? z2 : 0;
                 }
                 const bool kga = p.kg_slot >= 0 && (p.a_emask & 1), kgb = p.kg_slot >= 0 && (p.b_emask & 1);
-                const int m0 = (m_blk == mt - 1 ? p.m_last : m_blk * TM) + static_cast<int>(rank) * BM;
+                const int tile_m = m_blk == mt - 1 ? p.m_last : m_blk * TM;
+                const int tile_n = n_blk == nt - 1 ? p.n_last : n_blk * BN;
+                int kb_lo = 0, kb_hi = nkb;
+                if (p.band && band_span(p, tile_m, tile_n, TM, BN, nkb, kb_lo, kb_hi)) continue;
+                const int tile_iters = (kb_hi - kb_lo) * p.kg;
+                const int m0 = tile_m + static_cast<int>(rank) * BM;
                 // fused GeGLU: the pair's tile is [128 gate rows | the 128 up rows of the same ff range]
                 const int n0 = ACT == PT_ACT_GEGLU
                                    ? n_blk * BNH + static_cast<int>(rank) * p.ff
-                                   : (n_blk == nt - 1 ? p.n_last : n_blk * BN) + static_cast<int>(rank) * BNH;
-                int g = 0, kb = 0;
-                for (int it = 0; it < k_iters; ++it) {
+                                   : tile_n + static_cast<int>(rank) * BNH;
+                int g = 0, kb = kb_lo;
+                for (int it = 0; it < tile_iters; ++it) {
                     if (kga) ea0 = g;
                     if (kgb) eb0 = g;
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -306,7 +311,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     }
                     if (!leader) ptx::mbar_arrive_cluster(fb);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
-                    if (++kb == nkb) { kb = 0; ++g; }
+                    if (++kb == kb_hi) { kb = kb_lo; ++g; }
                 }
             }
         }
@@ -324,10 +329,19 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             int last_acc = -1;
             uint32_t last_phase = 0;
             for (int t = cid; t < total_tiles; t += ncl) {
+                int tile_iters = k_iters;
+                if (p.band) {
+                    int m_blk, n_blk, z[3];
+                    decode(t, m_blk, n_blk, z);
+                    int kb_lo, kb_hi;
+                    if (band_span(p, m_blk == mt - 1 ? p.m_last : m_blk * TM, n_blk == nt - 1 ? p.n_last : n_blk * BN,
+                                  TM, BN, nkb, kb_lo, kb_hi)) continue;
+                    tile_iters = (kb_hi - kb_lo) * p.kg;
+                }
                 ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
-                for (int it = 0; it < k_iters; ++it) {
+                for (int it = 0; it < tile_iters; ++it) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     ptx::tc_fence_after();
                     const uint64_t adesc = ptx::make_smem_desc_sw128(
@@ -364,6 +378,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const long long roff = z[0] * p.r_zs[0] + z[1] * p.r_zs[1] + z[2] * p.r_zs[2];
             const int tile_m = m_blk == mt - 1 ? p.m_last : m_blk * TM;
             const int tile_n = n_blk == nt - 1 ? p.n_last : n_blk * BN;
+            if (p.band == PT_BAND_SCORES) {
+                int kb_lo, kb_hi;
+                if (band_span(p, tile_m, tile_n, TM, BN, nkb, kb_lo, kb_hi)) continue;
+            }
             const int row0 = tile_m + static_cast<int>(rank) * BM + q * 32;        // first row of the slab
             const int rows_valid = min(32, p.M - row0);                            // may be <= 0
             const int row_lo = max(0, m_blk * TM - row0);                          // rows below: previous tile's

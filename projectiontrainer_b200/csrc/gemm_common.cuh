@@ -34,7 +34,27 @@ struct GemmDev {
     void* aux;
     long long ld_aux;
     int ff;
+    // causal / sliding-window band of self-attention products (pt_gemm_args.band): work that only meets
+    // masked (query, key) pairs is not issued.  band_w = window (0: unbounded below).
+    int band, band_w;
 };
+
+// K-block range [lo, hi) a tile must contract over, or skip = true when the whole tile is masked.
+// Tile rows [tm, tm + TM), columns [tn, tn + BN); nkb = K blocks of BK.
+__device__ __forceinline__ bool band_span(const GemmDev& p, int tm, int tn, int TM, int BN, int nkb, int& lo, int& hi) {
+    lo = 0; hi = nkb;
+    if (p.band == PT_BAND_SCORES) {          // rows = queries, columns = keys: key k allowed iff q - W < k <= q
+        if (tn > tm + TM - 1) return true;
+        if (p.band_w > 0 && tn + BN - 1 <= tm - p.band_w) return true;
+    } else if (p.band == PT_BAND_K_BY_QUERY) {   // rows = queries, contraction over keys
+        hi = min(nkb, (tm + TM - 1) / BK + 1);
+        if (p.band_w > 0) lo = max(0, tm - p.band_w + 1) / BK;
+    } else if (p.band == PT_BAND_K_BY_KEY) {     // rows = keys, contraction over queries: k <= q < k + W
+        lo = tm / BK;
+        if (p.band_w > 0) hi = min(nkb, (tm + TM - 1 + p.band_w - 1) / BK + 1);
+    }
+    return false;
+}
 
 __device__ __forceinline__ float apply_act(float v, int act) {
     if (act == PT_ACT_GELU_TANH) {

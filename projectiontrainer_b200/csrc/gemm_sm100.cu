@@ -498,6 +498,9 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     p.c_f32 = a->c_dtype == PT_F32; p.r_f32 = a->r_dtype == PT_F32;
     p.act = a->act; p.alpha = a->alpha;
     p.aux = a->aux; p.ld_aux = a->ld_aux; p.ff = geglu ? a->N / 2 : a->N;
+    PT_REQUIRE(a->band >= PT_BAND_NONE && a->band <= PT_BAND_K_BY_KEY && a->band_window >= 0,
+               "pt_gemm_bf16: bad band %d / window %d", a->band, a->band_window);
+    p.band = a->band; p.band_w = a->band_window;     // (the single-CTA kernel ignores it: a pure work-skipping hint)
 
     const long long nbatch = static_cast<long long>(a->nz[0]) * a->nz[1] * a->nz[2];
     cudaStream_t st = static_cast<cudaStream_t>(stream);

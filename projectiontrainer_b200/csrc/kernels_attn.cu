@@ -163,6 +163,94 @@ softmax_fwd_kernel(const float* __restrict__ sc, __nv_bfloat16* __restrict__ P,
     }
 }
 
+// Same contract, rows of up to 1024 columns held in registers: one global read of the in-band scores, one write.
+// Lane l owns the column pairs 2 l + 64 i, i = 0..15.
+__global__ void __launch_bounds__(kAttnWarps * 32)
+softmax_fwd_reg_kernel(const float* __restrict__ sc, __nv_bfloat16* __restrict__ P,
+                       const uint8_t* __restrict__ keyvalid, int Z, int Sq, int Sk, int ld,
+                       int heads_per_batch, int causal, int window) {
+    const long long item = static_cast<long long>(blockIdx.x) * kAttnWarps + (threadIdx.x >> 5);
+    if (item >= static_cast<long long>(Z) * Sq) return;
+    const int z = static_cast<int>(item / Sq), qi = static_cast<int>(item - static_cast<long long>(z) * Sq);
+    const int lane = threadIdx.x & 31;
+    const float* srow = sc + item * ld;
+    __nv_bfloat16* prow = P + item * ld;
+    const uint8_t* kv = keyvalid ? keyvalid + static_cast<long long>(z / heads_per_batch) * Sk : nullptr;
+    const int k_hi = causal ? min(qi, Sk - 1) : Sk - 1;                 // inclusive
+    const int k_lo = (window > 0) ? max(0, qi - window + 1) : 0;
+    float v[16][2];
+    float m = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int k = 2 * lane + 64 * i;
+        v[i][0] = -INFINITY; v[i][1] = -INFINITY;
+        if (k + 1 >= k_lo && k <= k_hi) {
+            const float2 f = *reinterpret_cast<const float2*>(srow + k);
+            if (k >= k_lo && (!kv || kv[k])) v[i][0] = f.x;
+            if (k + 1 <= k_hi && (!kv || kv[k + 1])) v[i][1] = f.y;
+        }
+        m = fmaxf(m, fmaxf(v[i][0], v[i][1]));
+    }
+    m = warp_max(m);
+    float l = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        v[i][0] = (v[i][0] == -INFINITY) ? 0.f : __expf(v[i][0] - m);
+        v[i][1] = (v[i][1] == -INFINITY) ? 0.f : __expf(v[i][1] - m);
+        l += v[i][0] + v[i][1];
+    }
+    l = warp_sum(l);
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int k = 2 * lane + 64 * i;
+        if (k < ld) *reinterpret_cast<uint32_t*>(prow + k) = pack_bf16(v[i][0] * inv, v[i][1] * inv);
+    }
+}
+
+__global__ void __launch_bounds__(kAttnWarps * 32)
+softmax_bwd_reg_kernel(const __nv_bfloat16* __restrict__ P, const float* __restrict__ dP,
+                       __nv_bfloat16* __restrict__ dS, long long rows, int Sk, int ld, float scale,
+                       int Sq, int causal, int window) {
+    const long long item = static_cast<long long>(blockIdx.x) * kAttnWarps + (threadIdx.x >> 5);
+    if (item >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const __nv_bfloat16* prow = P + item * ld;
+    const float* drow = dP + item * ld;
+    __nv_bfloat16* orow = dS + item * ld;
+    // columns outside [k_lo, k_hi] hold P = 0 and dP is undefined there (band-skipped tiles): not read
+    const int qi = Sq > 0 ? static_cast<int>(item % Sq) : 0;
+    const int k_hi = (Sq > 0 && causal) ? min(qi, Sk - 1) : Sk - 1;
+    const int k_lo = (Sq > 0 && window > 0) ? max(0, qi - window + 1) : 0;
+    uint32_t pu[16];
+    float2 d[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int k = 2 * lane + 64 * i;
+        const bool in = k + 1 >= k_lo && k <= k_hi;
+        pu[i] = in ? *reinterpret_cast<const uint32_t*>(prow + k) : 0u;
+        d[i] = in ? *reinterpret_cast<const float2*>(drow + k) : make_float2(0.f, 0.f);
+    }
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float p0 = bf16_lo(pu[i]), p1 = bf16_hi(pu[i]);
+        d[i].x = p0 != 0.f ? d[i].x : 0.f;
+        d[i].y = p1 != 0.f ? d[i].y : 0.f;
+        dot = fmaf(p0, d[i].x, dot);
+        dot = fmaf(p1, d[i].y, dot);
+    }
+    dot = warp_sum(dot);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int k = 2 * lane + 64 * i;
+        const float p0 = bf16_lo(pu[i]), p1 = bf16_hi(pu[i]);
+        if (k < ld)
+            *reinterpret_cast<uint32_t*>(orow + k) =
+                pack_bf16(p0 != 0.f ? scale * p0 * (d[i].x - dot) : 0.f, p1 != 0.f ? scale * p1 * (d[i].y - dot) : 0.f);
+    }
+}
+
 // dS[z][q][k] = scale * P (dP - sum_k P dP); written bf16 over all ld columns (0 where P == 0).
 __global__ void __launch_bounds__(kAttnWarps * 32)
 softmax_bwd_kernel(const __nv_bfloat16* __restrict__ P, const float* __restrict__ dP,
@@ -231,18 +319,27 @@ extern "C" int pt_softmax_fwd(const float* scores, void* P_bf16, const uint8_t* 
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const long long items = static_cast<long long>(Z) * Sq;
     const int nb = static_cast<int>((items + kAttnWarps - 1) / kAttnWarps);
-    softmax_fwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        scores, static_cast<__nv_bfloat16*>(P_bf16), keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window);
+    if (ld <= 1024)
+        softmax_fwd_reg_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            scores, static_cast<__nv_bfloat16*>(P_bf16), keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window);
+    else
+        softmax_fwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            scores, static_cast<__nv_bfloat16*>(P_bf16), keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window);
     return check_launch("softmax_fwd");
 }
 
 extern "C" int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long rows, int Sk,
-                              int ld, float scale, void* stream) {
+                              int ld, float scale, int Sq, int causal, int window, void* stream) {
     PT_REQUIRE(P_bf16 && dP && dS_bf16, "pt_softmax_bwd: null pointer");
     PT_REQUIRE(rows > 0 && Sk > 0 && ld >= Sk && ld % 2 == 0, "pt_softmax_bwd: bad shape");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const int nb = static_cast<int>((rows + kAttnWarps - 1) / kAttnWarps);
-    softmax_bwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(P_bf16), dP, static_cast<__nv_bfloat16*>(dS_bf16), rows, Sk, ld, scale);
+    if (ld <= 1024)
+        softmax_bwd_reg_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(P_bf16), dP, static_cast<__nv_bfloat16*>(dS_bf16), rows, Sk, ld, scale,
+            Sq, causal, window);
+    else
+        softmax_bwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(P_bf16), dP, static_cast<__nv_bfloat16*>(dS_bf16), rows, Sk, ld, scale);
     return check_launch("softmax_bwd");
 }

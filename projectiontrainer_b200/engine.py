@@ -203,7 +203,7 @@ class Stage1Engine:
         a = self.buf("v_a", (M, d), BF16)
         qkv = self.buf("v_qkv", (M, 3 * d), BF16)
         ld = _pad8(N)
-        fused = hd == 64 and N <= 576      # tcgen05 fused attention kernel; other geometries: GEMM + softmax + GEMM
+        fused = hd == 64                    # tcgen05 fused attention kernel; other head dims: GEMM + softmax + GEMM
         if not fused:
             sc = self.buf("v_scores", (B * H, N, ld), F32)
             P = self.buf("v_P", (B * H, N, ld), BF16)
@@ -261,13 +261,14 @@ class Stage1Engine:
         QKV = (c.hq + 2 * c.hkv) * c.hd
         return G, ld, QKV
 
-    def _scores_like(self, A, a_off, lda, a_zs, Bm, b_off, ldb, b_zs, out, B, S, alpha, b_mn=False):
+    def _scores_like(self, A, a_off, lda, a_zs, Bm, b_off, ldb, b_zs, out, B, S, alpha, b_mn=False, window=0):
         """out[b, kvh*G+g, q, k] (f32, ld) = alpha * A_row(q) . B_row(k) over hd, batched (g, kvh, b)."""
         c = self.lcfg
         G, ld, _ = self._attn_geometry(B, S)
         ops.gemm_raw(M=S, N=S, K=c.hd, A=A, a_off=a_off, lda=lda, B=Bm, b_off=b_off, ldb=ldb,
                      Cout=out, ldc=ld, nz=(G, c.hkv, B), a_zs=a_zs, b_zs=b_zs,
-                     c_zs=(S * ld, G * S * ld, c.hq * S * ld), alpha=alpha)
+                     c_zs=(S * ld, G * S * ld, c.hq * S * ld), alpha=alpha, band=ops.BAND_SCORES,
+                     band_window=window)
 
     # ------------------------------------------------------------------ LLM forward + loss
     def _llm_stack(self, x0: torch.Tensor, keyvalid, B: int, S: int, save: bool, cache=None):
@@ -306,14 +307,15 @@ class Stage1Engine:
             if cache is not None:      # KV-cache fill: device-to-device copies (plumbing, no arithmetic)
                 cache["k"][li][:, :S].copy_(k_post.view(B, S, hkv * hd))
                 cache["v"][li][:, :S].copy_(qkv.view(B, S, QKV)[:, :, (hq + hkv) * hd:])
+            win = 0 if full else c.window
             self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
-                              (0, hd, S * hkv * hd), sc, B, S, scale)
-            ops.softmax_fwd(sc, P, keyvalid, B * hq, S, S, ld, hq, 1, 0 if full else c.window)
+                              (0, hd, S * hkv * hd), sc, B, S, scale, window=win)
+            ops.softmax_fwd(sc, P, keyvalid, B * hq, S, S, ld, hq, 1, win)
             # attn_o[b, q, head, :] = P[b, head] V[b, :, kvh, :]   (V in place inside qkv, MN-major)
             ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, B=qkv, b_off=(hq + hkv) * hd, ldb=QKV, b_mn=True,
                          Cout=attn_o, ldc=hq * hd, nz=(G, hkv, B),
                          a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * QKV),
-                         c_zs=(hd, G * hd, S * hq * hd))
+                         c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY, band_window=win)
             ops.linear(attn_o, L["o_w"], out=y_attn)
             ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
             if self.fuse_geglu:
@@ -395,23 +397,26 @@ class Stage1Engine:
             ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
             ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
+            win = 0 if a["full"] else c.window
             self._scores_like(d_o, 0, hq * hd, (hd, G * hd, S * hq * hd), a["qkv"], (hq + hkv) * hd,
-                              QKV, (0, hd, S * QKV), dP, B, S, 1.0)
-            ops.softmax_bwd(a["P"], dP, dS, B * hq * S, S, ld, scale)
+                              QKV, (0, hd, S * QKV), dP, B, S, 1.0, window=win)
+            ops.softmax_bwd(a["P"], dP, dS, B * hq * S, S, ld, scale, Sq=S, causal=1, window=win)
             # dV[b,k,kvh,:] = sum_g P[b,kvh*G+g]^T dO[b,:,kvh*G+g,:]  -> v columns of d_qkv
             ops.gemm_raw(M=S, N=hd, K=S, A=a["P"], lda=ld, a_mn=True, B=d_o, ldb=hq * hd, b_mn=True,
                          Cout=d_qkv, c_off=(hq + hkv) * hd, ldc=QKV, nz=(hkv, B, 1),
                          a_zs=(G * S * ld, hq * S * ld, 0), b_zs=(G * hd, S * hq * hd, 0),
-                         c_zs=(hd, S * QKV, 0), kg=G, a_kgs=S * ld, b_kgs=hd)
+                         c_zs=(hd, S * QKV, 0), kg=G, a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY,
+                         band_window=win)
             # dQ[b,q,head,:] = dS[b,head] K[b,:,kvh,:]
             ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
                          ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
-                         b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd))
+                         b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY,
+                         band_window=win)
             # dK[b,k,kvh,:] = sum_g dS[b,kvh*G+g]^T Q[b,:,kvh*G+g,:]
             ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, a_mn=True, B=a["q"], ldb=hq * hd, b_mn=True,
                          Cout=dk, ldc=hkv * hd, nz=(hkv, B, 1), a_zs=(G * S * ld, hq * S * ld, 0),
                          b_zs=(G * hd, S * hq * hd, 0), c_zs=(hd, S * hkv * hd, 0), kg=G,
-                         a_kgs=S * ld, b_kgs=hd)
+                         a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY, band_window=win)
             ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                 hkv, hd, c.eps)
             ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)

@@ -11,6 +11,7 @@ import ctypes as C
 import torch
 
 from . import _lib
+from ._lib import BAND_K_BY_KEY, BAND_K_BY_QUERY, BAND_NONE, BAND_SCORES  # noqa: F401
 from ._lib import ACT_GEGLU, ACT_GEGLU_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
@@ -37,7 +38,7 @@ def _req_cuda(*ts):
 def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0), b_zs=(0, 0, 0),
              c_zs=(0, 0, 0), a_mn=False, b_mn=False, bias=None, residual=None, ldr=0,
              r_zs=(0, 0, 0), act=ACT_NONE, alpha=1.0, c_pre=None, kg=1, a_kgs=0, b_kgs=0,
-             a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0):
+             a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0, band=0, band_window=0):
     """Fully general launcher; A/B/Cout are tensors used only as base pointers
     (+ element offsets), all geometry comes from the explicit arguments."""
     _req_cuda(A, B, Cout, bias, residual, c_pre, aux)
@@ -73,6 +74,8 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     g.kg = int(kg)
     g.a_kgs = int(a_kgs)
     g.b_kgs = int(b_kgs)
+    g.band = int(band)
+    g.band_window = int(band_window)
     if aux is not None:
         g.aux = aux.data_ptr()
         g.ld_aux = int(ld_aux)
@@ -208,10 +211,10 @@ def qknorm_rope_bwd(dq, dk, qkv, wq, wk, cos_t, sin_t, d_qkv, S, hq, hkv, hd, ep
               _ptr(sin_t), _ptr(d_qkv), qkv.shape[0], int(S), hq, hkv, hd, _f(eps), _stream())
 
 
-def attn_siglip_fwd(qkv, out, B, N, H, hd, scale):
+def attn_siglip_fwd(qkv, out, B, N, H, hd, scale, v1=False):
     """Fused non-causal attention over the fused qkv activation [B*N, 3*H*hd] -> out [B*N, H*hd]."""
     _req_cuda(qkv, out)
-    _lib.call("pt_attn_siglip_fwd", _ptr(qkv), _ptr(out), int(B), int(N), int(H), int(hd), _f(scale), _stream())
+    _lib.call("pt_attn_siglip_fwd_v1" if v1 else "pt_attn_siglip_fwd", _ptr(qkv), _ptr(out), int(B), int(N), int(H), int(hd), _f(scale), _stream())
 
 
 def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window):
@@ -220,10 +223,10 @@ def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, win
               int(ld), int(heads_per_batch), int(causal), int(window), _stream())
 
 
-def softmax_bwd(P, dP, dS, rows, Sk, ld, scale):
+def softmax_bwd(P, dP, dS, rows, Sk, ld, scale, Sq=0, causal=0, window=0):
     _req_cuda(P, dP, dS)
     _lib.call("pt_softmax_bwd", _ptr(P), _ptr(dP), _ptr(dS), C.c_longlong(int(rows)), int(Sk),
-              int(ld), _f(scale), _stream())
+              int(ld), _f(scale), int(Sq), int(causal), int(window), _stream())
 
 
 def geglu_fwd(gu, act):

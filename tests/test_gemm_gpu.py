@@ -164,3 +164,38 @@ def test_gemm_fused_geglu_fwd_bwd(cuda_dev, gemm_impl, M, ff, h):
     ut = u.clone().requires_grad_(True)
     (torch.nn.functional.gelu(gt, approximate="tanh") * ut).backward(d_act.float())
     _check(d_gu, torch.cat([gt.grad, ut.grad], 1), tol=1e-2, name="d_gu vs torch autograd")
+
+
+@pytest.mark.parametrize("S,W", [(703, 0), (703, 512), (300, 64), (1000, 100)])
+def test_gemm_attention_bands_skip_only_masked_work(cuda_dev, S, W):
+    """pt_gemm_args.band: causal / sliding-window tile and K-block skipping must not change any value a masked
+    consumer can see (scores inside the band; P V, P^T dO with P zero outside the band)."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(S + W)
+    hd, G = 64, 2
+    ld = (S + 7) // 8 * 8
+    q, k = _rand((G, S, hd), cuda_dev), _rand((S, hd), cuda_dev)
+    qi, ki = torch.arange(S, device=cuda_dev)[:, None], torch.arange(S, device=cuda_dev)[None, :]
+    allowed = (ki <= qi) & ((ki > qi - W) if W else torch.ones_like(ki <= qi))
+    # scores: batched over G, B shared
+    sc = torch.full((G, S, ld), float("nan"), device=cuda_dev)
+    ops.gemm_raw(M=S, N=S, K=hd, A=q, lda=hd, B=k, ldb=hd, Cout=sc, ldc=ld, nz=(G, 1, 1), a_zs=(S * hd, 0, 0),
+                 c_zs=(S * ld, 0, 0), alpha=0.5, band=ops.BAND_SCORES, band_window=W)
+    ref = 0.5 * torch.einsum("gqd,kd->gqk", q.float(), k.float())
+    got = sc[:, :, :S]
+    assert bool(torch.isfinite(got[:, allowed]).all())
+    _check(got[:, allowed], ref[:, allowed], tol=1e-3, name="scores in band")
+    # P (zero outside the band) times V, contraction over keys
+    P = torch.zeros(G, S, ld, device=cuda_dev, dtype=torch.bfloat16)
+    P[:, :, :S] = (torch.rand(G, S, S, device=cuda_dev) * allowed).to(torch.bfloat16)
+    v = _rand((S, hd), cuda_dev)
+    o = torch.empty(G, S, hd, device=cuda_dev, dtype=torch.bfloat16)
+    ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, B=v, ldb=hd, b_mn=True, Cout=o, ldc=hd, nz=(G, 1, 1),
+                 a_zs=(S * ld, 0, 0), c_zs=(S * hd, 0, 0), band=ops.BAND_K_BY_QUERY, band_window=W)
+    _check(o, torch.einsum("gqk,kd->gqd", P[:, :, :S].float(), v.float()), name="P V")
+    # P^T dO summed over the G heads (grouped contraction), contraction over queries
+    do = _rand((G, S, hd), cuda_dev)
+    dv = torch.empty(S, hd, device=cuda_dev, dtype=torch.bfloat16)
+    ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, a_mn=True, B=do, ldb=hd, b_mn=True, Cout=dv, ldc=hd, kg=G,
+                 a_kgs=S * ld, b_kgs=S * hd, band=ops.BAND_K_BY_KEY, band_window=W)
+    _check(dv, torch.einsum("gqk,gqd->kd", P[:, :, :S].float(), do.float()), name="P^T dO")
