@@ -164,6 +164,12 @@ int pt_rmsnorm_bwd(const void* g, int g_dtype, const void* u, int u_dtype, const
                    int dst_dtype, const float* add_f32, int rows, int D, float eps, int u_group_rows,
                    int u_group_stride, int u_group_row0, int dst_group_rows, int dst_group_stride,
                    int dst_group_row0, void* stream);
+/* Two consecutive norm backwards of the sandwich-norm layer in one pass (D <= 2560):
+ *   dx += rmsnorm_bwd(g1; u1, w1);  out2 = bf16(rmsnorm_bwd(dx; u2, w2))
+ * g1 bf16 [rows,D] (gradient of a pre-norm output), u1 f32 (the residual stream it normalised), dx f32 in/out,
+ * u2 bf16 (the branch output the preceding post-norm normalised). */
+int pt_rmsnorm_bwd_pair(const void* g1_bf16, const float* u1, const float* w1, float* dx, const void* u2_bf16,
+                        const float* w2, void* out2_bf16, int rows, int D, float eps, void* stream);
 
 /* Per-head q/k RMSNorm + rotary embedding on the fused qkv row [(hq+2hkv)*hd]; position = row % S;
  * cos/sin are f32 [S, hd/2] — HF:models/gemma3/modeling_gemma3.py:362-368,233-263. */

@@ -3,8 +3,8 @@
 //
 // The first kernel (attn_siglip_sm100.cu) keeps K/V of a whole (image, head) resident in smem, which costs
 // 224 KB and therefore one CTA (one softmax warpgroup) per SM: tensor pipe and softmax warps take turns and
-// the kernel sits at ~190 TFLOP/s.  Here K/V tiles of 96 keys stream through a 3-stage TMA ring (they are
-// L2 hits: 144 KB per (image, head), re-read once per 128-row query block), smem drops to ~104 KB and TMEM to
+// the kernel sits at ~190 TFLOP/s.  Here K/V tiles of 96 keys stream through a TMA ring (3 K stages, 2 V stages) (they are
+// L2 hits: 144 KB per (image, head), re-read once per 128-row query block), smem drops to ~109 KB and TMEM to
 // 256 columns, so TWO CTAs are co-resident per SM and one CTA's softmax overlaps the other's MMAs.
 //
 // Work item = (image, head, 128-row query block); persistent CTAs walk items.  Per item and 96-key tile j:
@@ -23,12 +23,14 @@ namespace pt {
 constexpr int kBqRows = 128;
 constexpr int kBkTile = 96;
 constexpr int kBhd = 64;
-constexpr int kBstages = 3;
+constexpr int kBkStages = 3;                          // K tile j+2 is consumed (S_{j+2}) right after PV_j is issued
+constexpr int kBvStages = 2;                          // V tile j is consumed two tiles after its load is issued
 constexpr int kBthreads = 160;                        // 4 softmax warps + 1 control warp
 constexpr int kBqBytes = kBqRows * kBhd * 2;          // 16 KB
 constexpr int kBkvBytes = kBkTile * kBhd * 2;         // 12 KB per K or V tile
 constexpr int kBpBytes = 2 * kBqRows * 128;           // two 64-column swizzle atoms (the second half used)
-constexpr int kBsmem = kBqBytes + 2 * kBstages * kBkvBytes + kBpBytes + 256 + 1024;
+constexpr int kBsmem = kBqBytes + (kBkStages + kBvStages) * kBkvBytes + kBpBytes + 256 + 1024;   // 109.25 KB
+static_assert(2 * (kBsmem + 1024) <= 232448, "two CTAs must fit one SM");
 constexpr float kLazyRescaleLog2 = 8.f;
 
 struct AttnSiglip2Dev {
@@ -45,23 +47,25 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* sQ = smem;
-    uint8_t* sK = sQ + kBqBytes;                          // kBstages tiles
-    uint8_t* sV = sK + kBstages * kBkvBytes;
-    uint8_t* sP = sV + kBstages * kBkvBytes;
+    uint8_t* sK = sQ + kBqBytes;
+    uint8_t* sV = sK + kBkStages * kBkvBytes;
+    uint8_t* sP = sV + kBvStages * kBkvBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kBpBytes);
     uint64_t* q_full = bars;                  // TMA -> MMA
-    uint64_t* kv_full = bars + 1;             // [3] TMA -> MMA
-    uint64_t* s_full = bars + 4;              // [2] MMA -> softmax
-    uint64_t* p_full = bars + 6;              // softmax (128 arrivals) -> MMA
-    uint64_t* pv_done = bars + 7;             // MMA -> softmax / control
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+    uint64_t* k_full = bars + 1;              // [3] TMA -> MMA
+    uint64_t* v_full = bars + 4;              // [2] TMA -> MMA
+    uint64_t* s_full = bars + 6;              // [2] MMA -> softmax
+    uint64_t* p_full = bars + 8;              // softmax (128 arrivals) -> MMA
+    uint64_t* pv_done = bars + 9;             // MMA -> softmax / control
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 128) {
         ptx::prefetch_tmap(&tmQ);
         ptx::prefetch_tmap(&tmKV);
         ptx::mbar_init(q_full, 1);
-        for (int s = 0; s < kBstages; ++s) ptx::mbar_init(&kv_full[s], 1);
+        for (int s = 0; s < kBkStages; ++s) ptx::mbar_init(&k_full[s], 1);
+        for (int s = 0; s < kBvStages; ++s) ptx::mbar_init(&v_full[s], 1);
         ptx::mbar_init(&s_full[0], 1); ptx::mbar_init(&s_full[1], 1);
         ptx::mbar_init(p_full, 128);
         ptx::mbar_init(pv_done, 1);
@@ -86,26 +90,35 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
         if (lane == 0) {
             const uint32_t idescS = ptx::make_idesc_bf16(kBqRows, kBkTile, 0, 0);
             const uint32_t idescO = ptx::make_idesc_bf16(kBqRows, kBhd, 0, 1);      // B = V, MN-major
-            uint32_t ph_q = 0, ph_kv = 0 /* bit s = parity of stage s */, ph_p = 0, ph_pv = 0;
+            uint32_t ph_q = 0, ph_k = 0, ph_v = 0 /* bit s = parity of stage s */, ph_p = 0, ph_pv = 0;
             for (int item = blockIdx.x; item < items; item += gridDim.x) {
                 const int b = item / (p.H * p.nqb);
                 const int r = item - b * (p.H * p.nqb);
                 const int h = r / p.nqb, qb = r - h * p.nqb;
-                auto load_kv = [&](int j) {
-                    const int s = j % kBstages;
-                    ptx::mbar_arrive_expect_tx(&kv_full[s], 2 * kBkvBytes);
-                    ptx::tma_load_5d(&tmKV, &kv_full[s], sK + s * kBkvBytes, d + h * kBhd, j * kBkTile, b, 0, 0);
-                    ptx::tma_load_5d(&tmKV, &kv_full[s], sV + s * kBkvBytes, 2 * d + h * kBhd, j * kBkTile, b, 0, 0);
+                auto load_k = [&](int j) {
+                    const int s = j % kBkStages;
+                    ptx::mbar_arrive_expect_tx(&k_full[s], kBkvBytes);
+                    ptx::tma_load_5d(&tmKV, &k_full[s], sK + s * kBkvBytes, d + h * kBhd, j * kBkTile, b, 0, 0);
                 };
-                auto wait_kv = [&](int j) {
-                    const int s = j % kBstages;
-                    ptx::mbar_wait(&kv_full[s], (ph_kv >> s) & 1u);
-                    ph_kv ^= 1u << s;
+                auto load_v = [&](int j) {
+                    const int s = j % kBvStages;
+                    ptx::mbar_arrive_expect_tx(&v_full[s], kBkvBytes);
+                    ptx::tma_load_5d(&tmKV, &v_full[s], sV + s * kBkvBytes, 2 * d + h * kBhd, j * kBkTile, b, 0, 0);
+                };
+                auto wait_k = [&](int j) {
+                    const int s = j % kBkStages;
+                    ptx::mbar_wait(&k_full[s], (ph_k >> s) & 1u);
+                    ph_k ^= 1u << s;
+                };
+                auto wait_v = [&](int j) {
+                    const int s = j % kBvStages;
+                    ptx::mbar_wait(&v_full[s], (ph_v >> s) & 1u);
+                    ph_v ^= 1u << s;
                 };
                 const uint64_t qdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ), 0, 1024);
                 auto issue_S = [&](int j) {
                     const uint64_t kdesc =
-                        ptx::make_smem_desc_sw128(ptx::smem_u32(sK + (j % kBstages) * kBkvBytes), 0, 1024);
+                        ptx::make_smem_desc_sw128(ptx::smem_u32(sK + (j % kBkStages) * kBkvBytes), 0, 1024);
 #pragma unroll
                     for (int k = 0; k < kBhd / 16; ++k)
                         ptx::mma_bf16_ss(tS[j & 1], qdesc + k * 2, kdesc + k * 2, idescS, k != 0);
@@ -115,16 +128,18 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                 // tcgen05 operations of one thread complete in order): Q and all K/V stages are free
                 ptx::mbar_arrive_expect_tx(q_full, kBqBytes);
                 ptx::tma_load_5d(&tmQ, q_full, sQ, h * kBhd, qb * kBqRows, b, 0, 0);
-                for (int j = 0; j < kBstages && j < p.nkt; ++j) load_kv(j);
+                for (int j = 0; j < kBkStages && j < p.nkt; ++j) load_k(j);
+                for (int j = 0; j < kBvStages && j < p.nkt; ++j) load_v(j);
                 ptx::mbar_wait(q_full, ph_q); ph_q ^= 1;
-                wait_kv(0);
+                wait_k(0);
                 ptx::tc_fence_after();
                 issue_S(0);
-                if (p.nkt > 1) { wait_kv(1); ptx::tc_fence_after(); issue_S(1); }
+                if (p.nkt > 1) { wait_k(1); ptx::tc_fence_after(); issue_S(1); }
                 for (int j = 0; j < p.nkt; ++j) {
                     ptx::mbar_wait(p_full, ph_p); ph_p ^= 1;
+                    wait_v(j);
                     ptx::tc_fence_after();
-                    const uint32_t vbase = ptx::smem_u32(sV + (j % kBstages) * kBkvBytes);
+                    const uint32_t vbase = ptx::smem_u32(sV + (j % kBvStages) * kBkvBytes);
 #pragma unroll
                     for (int k = 0; k < kBkTile / 16; ++k) {
                         const uint64_t pdesc = ptx::make_smem_desc_sw128(
@@ -133,9 +148,11 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                         ptx::mma_bf16_ss(tO, pdesc, vdesc, idescO, (j | k) != 0);
                     }
                     ptx::mma_commit(pv_done);
-                    if (j + 2 < p.nkt) { wait_kv(j + 2); ptx::tc_fence_after(); issue_S(j + 2); }
+                    if (j + 2 < p.nkt) { wait_k(j + 2); ptx::tc_fence_after(); issue_S(j + 2); }
                     ptx::mbar_wait(pv_done, ph_pv); ph_pv ^= 1;
-                    if (j + kBstages < p.nkt) load_kv(j + kBstages);       // stage j % 3: S_j and PV_j retired
+                    // S_j and PV_j have retired: K stage j % 3 and V stage j % 2 are free
+                    if (j + kBkStages < p.nkt) load_k(j + kBkStages);
+                    if (j + kBvStages < p.nkt) load_v(j + kBvStages);
                 }
             }
         }
@@ -159,21 +176,24 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
 #pragma unroll
                 for (int c = 0; c < 3; ++c) ptx::tmem_ld_32x32(tS[sb] + lane_off + c * 32, v[c]);
                 ptx::tmem_ld_wait();
-                float mx = -INFINITY;
-                if (kvalid == kBkTile) {
+                if (kvalid < kBkTile) {
 #pragma unroll
                     for (int c = 0; c < 3; ++c)
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[c][i]));
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 3; ++c)
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
+                        for (int i = 0; i < 32; ++i)
                             if (c * 32 + i >= kvalid) v[c][i] = __float_as_uint(-INFINITY);
-                            mx = fmaxf(mx, __uint_as_float(v[c][i]));
-                        }
                 }
+                // eight independent max chains (a single chain of 96 dependent FMNMX is pure latency)
+                float mxs[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) mxs[i] = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        mxs[i & 7] = fmaxf(mxs[i & 7], __uint_as_float(v[c][i]));
+                const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                                       fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
                 bool pv_waited = false;
                 if (j == 0) {
                     m_run = mx;
@@ -202,7 +222,7 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                 }
                 // p = exp2(s * scale*log2e - m * scale*log2e) (<= 2^8 under the lazy max), bf16 pairs
                 const float mb = m_run * p.scale_log2e;
-                float lsum = 0.f;
+                float ls[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // independent partial row sums
                 uint32_t pk[48];
 #pragma unroll
                 for (int c = 0; c < 3; ++c)
@@ -210,10 +230,10 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                     for (int i = 0; i < 16; ++i) {
                         const float e0 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i]), p.scale_log2e, -mb));
                         const float e1 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i + 1]), p.scale_log2e, -mb));
-                        lsum += e0 + e1;
+                        ls[i & 7] += e0 + e1;
                         pk[c * 16 + i] = pack_bf16(e0, e1);
                     }
-                l_run += lsum;
+                l_run += ((ls[0] + ls[1]) + (ls[2] + ls[3])) + ((ls[4] + ls[5]) + (ls[6] + ls[7]));
                 // the single P buffer is free once the previous tile's PV has retired
                 if (j > 0 && !pv_waited) { ptx::mbar_wait(pv_done, ph_pv); ph_pv ^= 1; }
                 // columns c*32 .. +31 of this row: atom (c*32)/64, 16-byte chunks ((c&1)*4 + q) ^ (row&7)

@@ -386,6 +386,21 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int rows_valid = min(32, p.M - row0);                            // may be <= 0
             const int row_lo = max(0, m_blk * TM - row0);                          // rows below: previous tile's
 
+            if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+                // pull this warp's slab of the saved gate / up pre-activations into L2 while the tile's MMAs run
+                const int pr = row0 + lane;
+                if (pr < p.M && pr >= m_blk * TM) {
+                    const uint8_t* g = static_cast<const uint8_t*>(p.aux) +
+                                       (static_cast<long long>(pr) * p.ld_aux + tile_n + hf * BNH) * 2;
+#pragma unroll
+                    for (int b = 0; b < BNH * 2; b += 128) {
+                        if (tile_n + hf * BNH + b / 2 < p.N) {
+                            ptx::prefetch_l2(g + b);
+                            ptx::prefetch_l2(g + static_cast<long long>(p.ff) * 2 + b);
+                        }
+                    }
+                }
+            }
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);

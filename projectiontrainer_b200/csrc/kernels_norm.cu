@@ -180,6 +180,72 @@ rmsnorm_bwd_kernel(const TG* __restrict__ g, const TU* __restrict__ u, const flo
     }
 }
 
+// Two consecutive norm backwards of the sandwich-norm decoder layer in one pass over the row
+// (HF:models/gemma3/modeling_gemma3.py:417-432 reversed): the gradient g1 of a PRE-norm output flows into the
+// f32 residual-stream gradient, which is immediately the incoming gradient of the preceding POST-norm:
+//     dx   += rmsnorm_bwd(g1; u1, w1)            (u1 = f32 residual stream the pre-norm read)
+//     out2  = rmsnorm_bwd(dx; u2, w2)  as bf16   (u2 = bf16 branch output the post-norm read)
+// The updated dx row stays in registers between the two (NCH chunks of 256 columns per warp).
+// One block per row, 8 columns per thread (blockDim = D / 8 rounded up to a warp): few registers, many rows
+// in flight per SM; the two (sum u^2, sum dn u) reductions go through shared memory.
+__device__ __forceinline__ void block_sum2(float& a, float& b, float (*red)[2], int lane, int warp, int nwarps) {
+    a = warp_sum(a); b = warp_sum(b);
+    if (lane == 0) { red[warp][0] = a; red[warp][1] = b; }
+    __syncthreads();
+    float x = 0.f, y = 0.f;
+    for (int w = 0; w < nwarps; ++w) { x += red[w][0]; y += red[w][1]; }
+    __syncthreads();
+    a = x; b = y;
+}
+
+__global__ void __launch_bounds__(320)
+rmsnorm_bwd_pair_kernel(const __nv_bfloat16* g1, const float* __restrict__ u1,
+                        const float* __restrict__ w1, float* dx, const __nv_bfloat16* __restrict__ u2,
+                        const float* __restrict__ w2, __nv_bfloat16* out2 /* may alias g1 */, int D, float eps) {
+    __shared__ float red[10][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const long long base = static_cast<long long>(blockIdx.x) * D;
+    const int i = threadIdx.x * 8;
+    const bool on = i < D;
+    float dn[8], uu[8], a[8], wv[8];
+    float q = 0.f, dot = 0.f;
+    if (on) {
+        float gv[8];
+        load8(g1 + base + i, gv); load8(u1 + base + i, uu); load8(w1 + i, wv); load8(dx + base + i, a);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            dn[j] = gv[j] * (1.f + wv[j]);
+            q += uu[j] * uu[j];
+            dot += dn[j] * uu[j];
+        }
+    }
+    block_sum2(q, dot, red, lane, warp, nwarps);
+    float rstd = rsqrtf(q / D + eps);
+    float cc = dot * rstd * rstd * rstd / D;
+    q = 0.f; dot = 0.f;
+    if (on) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] += rstd * dn[j] - uu[j] * cc;
+        store8(dx + base + i, a);
+        load8(u2 + base + i, uu); load8(w2 + i, wv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            dn[j] = a[j] * (1.f + wv[j]);
+            q += uu[j] * uu[j];
+            dot += dn[j] * uu[j];
+        }
+    }
+    block_sum2(q, dot, red, lane, warp, nwarps);
+    rstd = rsqrtf(q / D + eps);
+    cc = dot * rstd * rstd * rstd / D;
+    if (on) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * dn[j] - uu[j] * cc;
+        store8(out2 + base + i, o);
+    }
+}
+
 // ---- row gather + cast: f32 strided rows -> compact bf16 rows ----------------------------------
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 gather_cast_rows_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int rows_out, int D,
@@ -281,4 +347,18 @@ extern "C" int pt_gather_cast_rows(const float* x, void* out_bf16, int rows_out,
     gather_cast_rows_kernel<<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
         x, static_cast<__nv_bfloat16*>(out_bf16), rows_out, D, m);
     return check_launch("gather_cast_rows");
+}
+
+extern "C" int pt_rmsnorm_bwd_pair(const void* g1_bf16, const float* u1, const float* w1, float* dx,
+                                   const void* u2_bf16, const float* w2, void* out2_bf16, int rows, int D,
+                                   float eps, void* stream) {
+    PT_REQUIRE(g1_bf16 && u1 && w1 && dx && u2_bf16 && w2 && out2_bf16, "pt_rmsnorm_bwd_pair: null pointer");
+    PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0 && D <= 2560, "pt_rmsnorm_bwd_pair: D must be a multiple of 8, <= 2560");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const __nv_bfloat16* g1 = static_cast<const __nv_bfloat16*>(g1_bf16);
+    const __nv_bfloat16* u2 = static_cast<const __nv_bfloat16*>(u2_bf16);
+    __nv_bfloat16* o2 = static_cast<__nv_bfloat16*>(out2_bf16);
+    rmsnorm_bwd_pair_kernel<<<rows, ((D / 8 + 31) / 32) * 32, 0, st>>>(g1, u1, w1, dx, u2, w2, o2, D, eps);
+    return check_launch("rmsnorm_bwd_pair");
 }

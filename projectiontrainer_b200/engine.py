@@ -381,20 +381,25 @@ class Stage1Engine:
         dq = self.buf("b_dq", (M, hq * hd), BF16)
         dk = self.buf("b_dk", (M, hkv * hd), BF16)
         d_qkv = self.buf("b_dqkv", (M, QKV), BF16)
+        pair = h <= 2560
         for li in range(len(Lm.layers) - 1, -1, -1):
             L, a = Lm.layers[li], s["layers"][li]
             cos_t, sin_t = self.rope(S, a["full"])
             # ---- MLP branch
-            ops.rmsnorm_bwd(dx, a["ym"], L["post_ffn_norm"], d_y, c.eps)
+            if li == len(Lm.layers) - 1 or not pair:
+                ops.rmsnorm_bwd(dx, a["ym"], L["post_ffn_norm"], d_y, c.eps)
             if self.fuse_geglu:
                 ops.linear_dgrad_geglu_bwd(d_y, L["down_w"], a["gu"], d_gu)
             else:
                 ops.linear_dgrad(d_y, L["down_w"], out=d_act)
                 ops.geglu_bwd(d_act, a["gu"], d_gu)
             ops.linear_dgrad(d_gu, L["gu_w"], out=d_y)
-            ops.rmsnorm_bwd(d_y, a["x1"], L["pre_ffn_norm"], dx, c.eps, add=dx)
-            # ---- attention branch
-            ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
+            # ---- attention branch (pre-ffn norm backward + post-attention norm backward in one pass)
+            if pair:
+                ops.rmsnorm_bwd_pair(d_y, a["x1"], L["pre_ffn_norm"], dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
+            else:
+                ops.rmsnorm_bwd(d_y, a["x1"], L["pre_ffn_norm"], dx, c.eps, add=dx)
+                ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
             ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
             win = 0 if a["full"] else c.window
@@ -420,7 +425,12 @@ class Stage1Engine:
             ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                 hkv, hd, c.eps)
             ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)
-            ops.rmsnorm_bwd(d_y, a["x_in"], L["in_norm"], dx, c.eps, add=dx)
+            if pair and li > 0:     # input-norm backward + the previous layer's post-ffn norm backward
+                prev = s["layers"][li - 1]
+                ops.rmsnorm_bwd_pair(d_y, a["x_in"], L["in_norm"], dx, prev["ym"],
+                                     Lm.layers[li - 1]["post_ffn_norm"], d_y, c.eps)
+            else:
+                ops.rmsnorm_bwd(d_y, a["x_in"], L["in_norm"], dx, c.eps, add=dx)
         return dx
 
     # ------------------------------------------------------------------ projector backward

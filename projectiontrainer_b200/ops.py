@@ -199,6 +199,12 @@ def rmsnorm_bwd(g, u, w, dst, eps, *, add=None, rows=None, u_group=(0, 0, 0), ds
               *map(int, dst_group), _stream())
 
 
+def rmsnorm_bwd_pair(g1, u1, w1, dx, u2, w2, out2, eps):
+    _req_cuda(g1, u1, dx, u2, out2)
+    _lib.call("pt_rmsnorm_bwd_pair", _ptr(g1), _ptr(u1), _ptr(w1), _ptr(dx), _ptr(u2), _ptr(w2), _ptr(out2),
+              g1.shape[0], g1.shape[-1], _f(eps), _stream())
+
+
 def qknorm_rope_fwd(qkv, wq, wk, cos_t, sin_t, q_out, k_out, S, hq, hkv, hd, eps):
     _req_cuda(qkv, q_out, k_out)
     _lib.call("pt_qknorm_rope_fwd", _ptr(qkv), _ptr(wq), _ptr(wk), _ptr(cos_t), _ptr(sin_t),
