@@ -209,13 +209,18 @@ def run_ours(args):
     ms = e0.elapsed_time(e1)
     launches = _lib.launch_count - n0
     # ---- end-to-end: pinned host inputs copied in, loss read back, every step
+    # (the copy of batch i+1 is started on a side stream before step i is launched — the DataLoader-prefetch
+    #  pattern of the trainer; every step's 56.7 MB still crosses PCIe inside the timed region)
     for _ in range(2):
-        float(step(host_batch).item())
+        float(step(eng.stage_batch(host_batch)).item())
     sync()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
-    for _ in range(args.steps):
-        lv = float(step(host_batch).item())
+    staged = eng.stage_batch(host_batch)
+    for i in range(args.steps):
+        nxt = eng.stage_batch(host_batch) if i + 1 < args.steps else None
+        lv = float(step(staged).item())
+        staged = nxt
     e3.record()
     sync()
     ms_e2e = e2.elapsed_time(e3)
@@ -230,7 +235,8 @@ def run_ours(args):
     if rank == 0:
         ops.GEMM_PROFILE = []
         eng.use_graph = False
-        step(dev_batch)
+        # rank-local pass (no collective: the other ranks do not take part in it)
+        eng.train_step(dev_batch, lr, pad_id=lc.pad_id, allreduce=None, world_size=1)
         torch.cuda.synchronize()
         prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
         fl = sum(p[0] for p in prof)

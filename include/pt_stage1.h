@@ -42,7 +42,13 @@ typedef enum {
     /* Backward of the above fused into the down-projection input gradient: the accumulator is
      * d_act [M, N = ff]; aux = the saved pre-activations [M,2*ff] bf16 (row stride ld_aux, read only);
      * C [M,2*ff] bf16 receives [d_act * up * gelu_tanh'(gate) | d_act * gelu_tanh(gate)]. */
-    PT_ACT_GEGLU_BWD = 4
+    PT_ACT_GEGLU_BWD = 4,
+    /* Softmax backward fused into dP = dO V^T (HF eager attention under autograd): aux = the saved
+     * probabilities P, bf16, laid out exactly like C (rows contiguous over all batches, row stride ld_aux,
+     * c_zs multiples of ldc); bias = delta, f32, one value per C row (row index = element offset / ldc) with
+     * delta[r] = sum_k P[r,k] dP[r,k] = rowsum(dO * O) (pt_attn_delta); C (bf16) receives
+     * alpha * P * (dP - delta), exactly 0 where P == 0. */
+    PT_ACT_SOFTMAX_BWD = 5
 } pt_act;
 
 typedef enum {
@@ -190,6 +196,11 @@ int pt_softmax_fwd(const float* scores, void* P_bf16, const uint8_t* keyvalid, i
  * pt_gemm_args.band); Sq = 0 reads whole rows. */
 int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long rows, int Sk, int ld,
                    float scale, int Sq, int causal, int window, void* stream);
+
+/* delta[(b*hq + head)*S + s] = sum_d dO[b,s,head,d] * O[b,s,head,d] over dO, O bf16 [rows = B*S, hq*hd]: the
+ * row term sum_k P dP of the softmax backward, for pt_gemm_bf16's PT_ACT_SOFTMAX_BWD epilogue. */
+int pt_attn_delta(const void* dO_bf16, const void* O_bf16, float* delta, int rows, int S, int hq, int hd,
+                  void* stream);
 
 /* Fused non-causal attention forward of the SigLIP tower (HF:models/siglip/modeling_siglip.py:293-306):
  * out[b, q, h*hd .. ] = softmax(q k^T * scale) v, with q/k/v read in place from the fused activation

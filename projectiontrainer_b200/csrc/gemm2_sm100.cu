@@ -182,6 +182,53 @@ __device__ __forceinline__ void epi_chunk_gbwd(const uint32_t (&v)[32], uint32_t
     __syncwarp();
 }
 
+// Softmax backward fused into the dP = dO V^T product (HF eager attention under autograd): the accumulator
+// chunk is dP; with the saved probabilities P (same [row, column] position) and delta[row] = sum_k P dP
+// (= rowsum(dO * O), computed beforehand) the epilogue writes dS = alpha * P * (dP - delta) as bf16.
+struct EpiSbwd {
+    uint8_t* C;           // dS, byte address of (row 0 of the slab, column col0)
+    const uint8_t* P;     // saved probabilities, same position
+    const float* delta;   // delta of row 0 of the slab
+    long long c_row, p_row;
+    float alpha;
+    int rows_valid, row_lo, cols_q;
+};
+
+__device__ __forceinline__ void epi_chunk_sbwd(const uint32_t (&v)[32], uint32_t stg, int lane, const EpiSbwd& o) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        ptx::sts128(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncwarp();
+    const int ch = lane & 7, c = ch * 4, rsub = lane >> 3;
+    const bool col_ok = c < o.cols_q;
+    uint2 pq[8];
+    float dl[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + rsub;
+        pq[it] = make_uint2(0u, 0u); dl[it] = 0.f;
+        if (col_ok && r >= o.row_lo && r < o.rows_valid) {
+            pq[it] = *reinterpret_cast<const uint2*>(o.P + r * o.p_row + c * 2);
+            dl[it] = __ldg(o.delta + r);
+        }
+    }
+    const uint32_t sp = stg + rsub * 128;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + rsub;
+        const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
+        if (col_ok && r >= o.row_lo && r < o.rows_valid) {
+            const float p0 = bf16_lo(pq[it].x), p1 = bf16_hi(pq[it].x), p2 = bf16_lo(pq[it].y), p3 = bf16_hi(pq[it].y);
+            uint2 w;
+            // p == 0 marks masked positions, where the accumulator may be anything: force an exact zero
+            w.x = pack_bf16(p0 != 0.f ? o.alpha * p0 * (a.x - dl[it]) : 0.f, p1 != 0.f ? o.alpha * p1 * (a.y - dl[it]) : 0.f);
+            w.y = pack_bf16(p2 != 0.f ? o.alpha * p2 * (a.z - dl[it]) : 0.f, p3 != 0.f ? o.alpha * p3 * (a.w - dl[it]) : 0.f);
+            *reinterpret_cast<uint2*>(o.C + r * o.c_row + c * 2) = w;
+        }
+    }
+    __syncwarp();
+}
+
 // ---- kernel ----------------------------------------------------------------------------------------
 template <int BN, int ACT>
 __global__ void __launch_bounds__(kGemm2Threads, 1)
@@ -463,6 +510,20 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
                 }
                 if (!live) continue;
+                if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
+                    EpiSbwd o;
+                    const long long co = coff + static_cast<long long>(row0) * p.ldc + col0;
+                    o.c_row = p.ldc * 2; o.p_row = p.ld_aux * 2;
+                    o.C = static_cast<uint8_t*>(p.C) + co * 2;
+                    o.P = static_cast<const uint8_t*>(p.aux) +
+                          (coff / p.ldc * p.ld_aux + static_cast<long long>(row0) * p.ld_aux + col0) * 2;
+                    o.delta = p.bias + coff / p.ldc + row0;
+                    o.alpha = p.alpha;
+                    o.rows_valid = rows_valid; o.row_lo = row_lo;
+                    o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
+                    epi_chunk_sbwd(v, stg, lane, o);
+                    continue;
+                }
                 if constexpr (ACT == PT_ACT_GEGLU_BWD) {
                     EpiGbwd o;
                     o.c_row = p.ldc * 2; o.g_row = p.ld_aux * 2; o.ff_bytes = static_cast<long long>(p.ff) * 2;
@@ -554,6 +615,7 @@ int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const Gem
         if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, p, tiles, st); \
         if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, p, tiles, st);   \
         if (p.act == PT_ACT_GEGLU_BWD) return launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, p, tiles, st); \
+        if (p.act == PT_ACT_SOFTMAX_BWD) return launch_gemm2_t<BN_, PT_ACT_SOFTMAX_BWD>(ta, tb, p, tiles, st); \
         return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, p, tiles, st);
     if (p.act == PT_ACT_GEGLU) {
         if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }

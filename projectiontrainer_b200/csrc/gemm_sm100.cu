@@ -454,9 +454,9 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         for (int i = 0; i < 3; ++i)
             PT_REQUIRE((a->r_zs[i] % rvec) == 0, "pt_gemm_bf16: residual batch stride %d misaligned", i);
     }
-    PT_REQUIRE((a->N % 4) == 0 || (!a->bias && !a->residual && !a->C_pre),
+    PT_REQUIRE((a->N % 4) == 0 || ((!a->bias || a->act == PT_ACT_SOFTMAX_BWD) && !a->residual && !a->C_pre),
                "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
-    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_GEGLU_BWD, "pt_gemm_bf16: bad act %d", a->act);
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_SOFTMAX_BWD, "pt_gemm_bf16: bad act %d", a->act);
     const bool geglu = a->act == PT_ACT_GEGLU, geglu_bwd = a->act == PT_ACT_GEGLU_BWD;
     if (geglu || geglu_bwd) {
         PT_REQUIRE(a->aux != nullptr && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0 && a->ld_aux % 8 == 0,
@@ -497,6 +497,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     p.ldc = a->ldc; p.ldr = a->ldr;
     p.c_f32 = a->c_dtype == PT_F32; p.r_f32 = a->r_dtype == PT_F32;
     p.act = a->act; p.alpha = a->alpha;
+    if (a->act == PT_ACT_SOFTMAX_BWD) {
+        PT_REQUIRE(a->aux && a->bias && a->c_dtype == PT_BF16 && !a->residual && !a->C_pre && kg == 1,
+                   "pt_gemm_bf16: fused softmax backward needs aux = P, bias = delta, bf16 C, no residual / C_pre");
+        PT_REQUIRE(g_gemm_impl != 1, "pt_gemm_bf16: the fused softmax-backward epilogue exists in the CTA-pair kernel only");
+        PT_REQUIRE(a->ld_aux % 4 == 0 && (reinterpret_cast<uintptr_t>(a->aux) & 7) == 0, "pt_gemm_bf16: P misaligned");
+        for (int i = 0; i < 3; ++i)
+            PT_REQUIRE(a->c_zs[i] % a->ldc == 0, "pt_gemm_bf16: fused softmax backward needs c_zs %% ldc == 0");
+    }
     p.aux = a->aux; p.ld_aux = a->ld_aux; p.ff = geglu ? a->N / 2 : a->N;
     PT_REQUIRE(a->band >= PT_BAND_NONE && a->band <= PT_BAND_K_BY_KEY && a->band_window >= 0,
                "pt_gemm_bf16: bad band %d / window %d", a->band, a->band_window);

@@ -123,6 +123,110 @@ qknorm_rope_bwd_kernel(const __nv_bfloat16* __restrict__ dq, const __nv_bfloat16
     }
 }
 
+// Single-pass variants for head_dim <= 256 (one 4-wide slice of each half per lane): every operand is loaded
+// once and stays in registers across the reduction.
+__global__ void __launch_bounds__(kAttnWarps * 32)
+qknorm_rope_fwd_reg_kernel(const __nv_bfloat16* __restrict__ qkv, const float* __restrict__ wq,
+                           const float* __restrict__ wk, const float* __restrict__ cs,
+                           const float* __restrict__ sn, __nv_bfloat16* __restrict__ q_out,
+                           __nv_bfloat16* __restrict__ k_out, int rows, int S, int hq, int hkv, int hd, float eps) {
+    const int item = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);
+    const int nh = hq + hkv;
+    if (item >= rows * nh) return;
+    const int row = item / nh, head = item - row * nh;
+    const int lane = threadIdx.x & 31;
+    const int half = hd >> 1;
+    const int i = lane * 4;
+    const bool on = i < half;
+    const __nv_bfloat16* u = qkv + static_cast<long long>(row) * (hq + 2 * hkv) * hd + head * hd;
+    const float* w = head < hq ? wq : wk;
+    __nv_bfloat16* out = head < hq ? q_out + (static_cast<long long>(row) * hq + head) * hd
+                                   : k_out + (static_cast<long long>(row) * hkv + (head - hq)) * hd;
+    const long long tb = static_cast<long long>(row % S) * half + i;
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f), s = c, w1 = c, w2 = c;
+    if (on) {
+        ld4(u + i, a); ld4(u + half + i, b);
+        c = *reinterpret_cast<const float4*>(cs + tb);
+        s = *reinterpret_cast<const float4*>(sn + tb);
+        w1 = *reinterpret_cast<const float4*>(w + i);
+        w2 = *reinterpret_cast<const float4*>(w + half + i);
+    }
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) q += a[j] * a[j] + b[j] * b[j];
+    const float rstd = rsqrtf(warp_sum(q) / hd + eps);
+    if (on) {
+        const float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {s.x, s.y, s.z, s.w};
+        const float g1[4] = {w1.x, w1.y, w1.z, w1.w}, g2[4] = {w2.x, w2.y, w2.z, w2.w};
+        float ya[4], yb[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float n1 = a[j] * rstd * (1.f + g1[j]), n2 = b[j] * rstd * (1.f + g2[j]);
+            ya[j] = n1 * cc[j] - n2 * ss[j];
+            yb[j] = n2 * cc[j] + n1 * ss[j];
+        }
+        st4(out + i, ya); st4(out + half + i, yb);
+    }
+}
+
+__global__ void __launch_bounds__(kAttnWarps * 32)
+qknorm_rope_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dq, const __nv_bfloat16* __restrict__ dk,
+                           const __nv_bfloat16* __restrict__ qkv, const float* __restrict__ wq,
+                           const float* __restrict__ wk, const float* __restrict__ cs,
+                           const float* __restrict__ sn, __nv_bfloat16* __restrict__ d_qkv, int rows,
+                           int S, int hq, int hkv, int hd, float eps) {
+    const int item = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);
+    const int nh = hq + hkv;
+    if (item >= rows * nh) return;
+    const int row = item / nh, head = item - row * nh;
+    const int lane = threadIdx.x & 31;
+    const int half = hd >> 1;
+    const int i = lane * 4;
+    const bool on = i < half;
+    const long long off = static_cast<long long>(row) * (hq + 2 * hkv) * hd + head * hd;
+    const __nv_bfloat16* u = qkv + off;
+    __nv_bfloat16* du = d_qkv + off;
+    const float* w = head < hq ? wq : wk;
+    const __nv_bfloat16* dy = head < hq ? dq + (static_cast<long long>(row) * hq + head) * hd
+                                        : dk + (static_cast<long long>(row) * hkv + (head - hq)) * hd;
+    const long long tb = static_cast<long long>(row % S) * half + i;
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, dn1[4] = {0.f, 0.f, 0.f, 0.f}, dn2[4] = {0.f, 0.f, 0.f, 0.f};
+    if (on) {
+        float da[4], db[4];
+        ld4(u + i, a); ld4(u + half + i, b); ld4(dy + i, da); ld4(dy + half + i, db);
+        const float4 c = *reinterpret_cast<const float4*>(cs + tb);
+        const float4 s = *reinterpret_cast<const float4*>(sn + tb);
+        const float4 w1 = *reinterpret_cast<const float4*>(w + i);
+        const float4 w2 = *reinterpret_cast<const float4*>(w + half + i);
+        const float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {s.x, s.y, s.z, s.w};
+        const float g1[4] = {w1.x, w1.y, w1.z, w1.w}, g2[4] = {w2.x, w2.y, w2.z, w2.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            dn1[j] = (da[j] * cc[j] + db[j] * ss[j]) * (1.f + g1[j]);
+            dn2[j] = (db[j] * cc[j] - da[j] * ss[j]) * (1.f + g2[j]);
+        }
+    }
+    float q = 0.f, dot = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        q += a[j] * a[j] + b[j] * b[j];
+        dot += dn1[j] * a[j] + dn2[j] * b[j];
+    }
+    q = warp_sum(q); dot = warp_sum(dot);
+    const float rstd = rsqrtf(q / hd + eps);
+    const float c3 = dot * rstd * rstd * rstd / hd;
+    if (on) {
+        float oa[4], ob[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            oa[j] = rstd * dn1[j] - a[j] * c3;
+            ob[j] = rstd * dn2[j] - b[j] * c3;
+        }
+        st4(du + i, oa); st4(du + half + i, ob);
+    }
+}
+
 // ---- masked softmax over score rows -------------------------------------------------------------
 // scores f32 [Z][Sq][ld] (already scaled) -> P bf16 [Z][Sq][ld]; columns >= Sk and masked keys get 0.
 // mask: key k allowed for query q iff (!causal || k <= q) && (window <= 0 || k > q - window)
@@ -278,6 +382,27 @@ softmax_bwd_kernel(const __nv_bfloat16* __restrict__ P, const float* __restrict_
     }
 }
 
+// delta[(b*hq + head)*S + s] = sum_d dO[b,s,head,d] * O[b,s,head,d]  (= sum_k P dP of that score row).
+// One warp per (token row, head).
+__global__ void __launch_bounds__(kAttnWarps * 32)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ dO, const __nv_bfloat16* __restrict__ O,
+                  float* __restrict__ delta, int rows, int S, int hq, int hd) {
+    const int item = blockIdx.x * kAttnWarps + (threadIdx.x >> 5);
+    if (item >= rows * hq) return;
+    const int row = item / hq, head = item - row * hq;
+    const int lane = threadIdx.x & 31;
+    const long long off = (static_cast<long long>(row) * hq + head) * hd;
+    float acc = 0.f;
+    for (int i = lane * 4; i < hd; i += 128) {
+        float a[4], b[4]; ld4(dO + off + i, a); ld4(O + off + i, b);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc = fmaf(a[j], b[j], acc);
+    }
+    acc = warp_sum(acc);
+    const int b = row / S, s = row - b * S;
+    if (lane == 0) delta[(static_cast<long long>(b) * hq + head) * S + s] = acc;
+}
+
 }  // namespace pt
 
 using namespace pt;
@@ -290,9 +415,14 @@ extern "C" int pt_qknorm_rope_fwd(const void* qkv, const float* wq, const float*
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const long long items = static_cast<long long>(rows) * (hq + hkv);
     const int nb = static_cast<int>((items + kAttnWarps - 1) / kAttnWarps);
-    qknorm_rope_fwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(qkv), wq, wk, cos_t, sin_t, static_cast<__nv_bfloat16*>(q_out),
-        static_cast<__nv_bfloat16*>(k_out), rows, S, hq, hkv, hd, eps);
+    if (hd <= 256)
+        qknorm_rope_fwd_reg_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(qkv), wq, wk, cos_t, sin_t, static_cast<__nv_bfloat16*>(q_out),
+            static_cast<__nv_bfloat16*>(k_out), rows, S, hq, hkv, hd, eps);
+    else
+        qknorm_rope_fwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(qkv), wq, wk, cos_t, sin_t, static_cast<__nv_bfloat16*>(q_out),
+            static_cast<__nv_bfloat16*>(k_out), rows, S, hq, hkv, hd, eps);
     return check_launch("qknorm_rope_fwd");
 }
 
@@ -304,10 +434,16 @@ extern "C" int pt_qknorm_rope_bwd(const void* dq, const void* dk, const void* qk
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const long long items = static_cast<long long>(rows) * (hq + hkv);
     const int nb = static_cast<int>((items + kAttnWarps - 1) / kAttnWarps);
-    qknorm_rope_bwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(dq), static_cast<const __nv_bfloat16*>(dk),
-        static_cast<const __nv_bfloat16*>(qkv), wq, wk, cos_t, sin_t, static_cast<__nv_bfloat16*>(d_qkv),
-        rows, S, hq, hkv, hd, eps);
+    if (hd <= 256)
+        qknorm_rope_bwd_reg_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(dq), static_cast<const __nv_bfloat16*>(dk),
+            static_cast<const __nv_bfloat16*>(qkv), wq, wk, cos_t, sin_t, static_cast<__nv_bfloat16*>(d_qkv),
+            rows, S, hq, hkv, hd, eps);
+    else
+        qknorm_rope_bwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(dq), static_cast<const __nv_bfloat16*>(dk),
+            static_cast<const __nv_bfloat16*>(qkv), wq, wk, cos_t, sin_t, static_cast<__nv_bfloat16*>(d_qkv),
+            rows, S, hq, hkv, hd, eps);
     return check_launch("qknorm_rope_bwd");
 }
 
@@ -342,4 +478,16 @@ extern "C" int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16
         softmax_bwd_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
             static_cast<const __nv_bfloat16*>(P_bf16), dP, static_cast<__nv_bfloat16*>(dS_bf16), rows, Sk, ld, scale);
     return check_launch("softmax_bwd");
+}
+
+extern "C" int pt_attn_delta(const void* dO_bf16, const void* O_bf16, float* delta, int rows, int S, int hq, int hd,
+                             void* stream) {
+    PT_REQUIRE(dO_bf16 && O_bf16 && delta, "pt_attn_delta: null pointer");
+    PT_REQUIRE(rows > 0 && S > 0 && rows % S == 0 && hq > 0 && hd % 4 == 0, "pt_attn_delta: bad shape");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    const long long items = static_cast<long long>(rows) * hq;
+    const int nb = static_cast<int>((items + kAttnWarps - 1) / kAttnWarps);
+    attn_delta_kernel<<<nb, kAttnWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dO_bf16), static_cast<const __nv_bfloat16*>(O_bf16), delta, rows, S, hq, hd);
+    return check_launch("attn_delta");
 }

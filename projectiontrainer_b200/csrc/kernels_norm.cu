@@ -69,6 +69,47 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
     }
 }
 
+// Block-per-row variant (D <= 4096): 8 columns per thread, the row is read once and stays in registers,
+// mean and variance are reduced through shared memory.
+__global__ void __launch_bounds__(512)
+layernorm_fwd_row_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, __nv_bfloat16* __restrict__ out, int D, float eps,
+                         RowMap in_map) {
+    __shared__ float red[16];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int r = blockIdx.x;
+    const int i = threadIdx.x * 8;
+    const bool on = i < D;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (on) load8(x + in_map.map(r) * D + i, v);
+    float s = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+    s = warp_sum(s);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    float tot = 0.f;
+    for (int w = 0; w < nwarps; ++w) tot += red[w];
+    __syncthreads();
+    const float mean = tot / D;
+    float q = 0.f;
+    if (on) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float d = v[j] - mean; q += d * d; }
+    }
+    q = warp_sum(q);
+    if (lane == 0) red[warp] = q;
+    __syncthreads();
+    tot = 0.f;
+    for (int w = 0; w < nwarps; ++w) tot += red[w];
+    const float rstd = rsqrtf(tot / D + eps);
+    if (on) {
+        float g[8], b[8], o[8];
+        load8(gamma + i, g); load8(beta + i, b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[j] - mean) * rstd * g[j] + b[j];
+        store8(out + static_cast<long long>(r) * D + i, o);
+    }
+}
+
 // ---- RMSNorm forward: out = x * rsqrt(mean x^2 + eps) * (1 + w) ------------------------------
 template <typename TIn>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -131,6 +172,57 @@ rmsnorm_residual_fwd_kernel(const __nv_bfloat16* __restrict__ y, const float* __
     for (int i = lane * 8; i < D; i += 256) {
         float v[8], g[8], o[8];
         load8(x_out + base + i, v); load8(w_next + i, g);   // same lane wrote these addresses
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = v[j] * rstd2 * (1.f + g[j]);
+        store8(nxt + base + i, o);
+    }
+}
+
+// Block-per-row variant of the sandwich step (D <= 4096): every operand is read once, the row stays in registers.
+__global__ void __launch_bounds__(512)
+rmsnorm_residual_fwd_row_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ w_post,
+                                const float* x_in, float* x_out, const float* __restrict__ w_next,
+                                __nv_bfloat16* __restrict__ nxt, int D, float eps) {
+    __shared__ float red[16];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const long long base = static_cast<long long>(blockIdx.x) * D;
+    const int i = threadIdx.x * 8;
+    const bool on = i < D;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, xi[8], g[8];
+    float q = 0.f;
+    if (on) {
+        load8(y + base + i, v); load8(x_in + base + i, xi); load8(w_post + i, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q += v[j] * v[j];
+    }
+    q = warp_sum(q);
+    if (lane == 0) red[warp] = q;
+    __syncthreads();
+    float tot = 0.f;
+    for (int w = 0; w < nwarps; ++w) tot += red[w];
+    __syncthreads();
+    const float rstd = rsqrtf(tot / D + eps);
+    float q2 = 0.f;
+    if (on) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            // HF rounds the norm output to the activation dtype before the residual add
+            const float n = __bfloat162float(__float2bfloat16(v[j] * rstd * (1.f + g[j])));
+            v[j] = xi[j] + n;
+            q2 += v[j] * v[j];
+        }
+        store8(x_out + base + i, v);
+    }
+    if (!nxt) return;
+    q2 = warp_sum(q2);
+    if (lane == 0) red[warp] = q2;
+    __syncthreads();
+    tot = 0.f;
+    for (int w = 0; w < nwarps; ++w) tot += red[w];
+    const float rstd2 = rsqrtf(tot / D + eps);
+    if (on) {
+        float o[8];
+        load8(w_next + i, g);
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = v[j] * rstd2 * (1.f + g[j]);
         store8(nxt + base + i, o);
@@ -274,8 +366,12 @@ extern "C" int pt_layernorm_fwd(const float* x, const float* gamma, const float*
     PT_REQUIRE(rows_out > 0 && D > 0 && D % 8 == 0, "pt_layernorm_fwd: D must be a positive multiple of 8");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     RowMap m{group_rows_out, group_rows_in, group_row0};
-    layernorm_fwd_kernel<<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        x, gamma, beta, static_cast<__nv_bfloat16*>(out_bf16), rows_out, D, eps, m);
+    if (D <= 4096)
+        layernorm_fwd_row_kernel<<<rows_out, ((D / 8 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            x, gamma, beta, static_cast<__nv_bfloat16*>(out_bf16), D, eps, m);
+    else
+        layernorm_fwd_kernel<<<row_blocks(rows_out), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            x, gamma, beta, static_cast<__nv_bfloat16*>(out_bf16), rows_out, D, eps, m);
     return check_launch("layernorm_fwd");
 }
 
@@ -305,9 +401,14 @@ extern "C" int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, 
     PT_REQUIRE((w_next == nullptr) == (next_bf16 == nullptr), "pt_rmsnorm_residual_fwd: w_next/next mismatch");
     PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0, "pt_rmsnorm_residual_fwd: D must be a positive multiple of 8");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
-    rmsnorm_residual_fwd_kernel<<<row_blocks(rows), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
-        static_cast<__nv_bfloat16*>(next_bf16), rows, D, eps);
+    if (D <= 4096)
+        rmsnorm_residual_fwd_row_kernel<<<rows, ((D / 8 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
+            static_cast<__nv_bfloat16*>(next_bf16), D, eps);
+    else
+        rmsnorm_residual_fwd_kernel<<<row_blocks(rows), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
+            static_cast<__nv_bfloat16*>(next_bf16), rows, D, eps);
     return check_launch("rmsnorm_residual_fwd");
 }
 

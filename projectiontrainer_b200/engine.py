@@ -166,6 +166,7 @@ class Stage1Engine:
         self.use_graph = os.environ.get("PT_STAGE1_GRAPH", "1") != "0"
         self._graphs: dict = {}
         # GeGLU forward / backward fused into the gate||up and down-dgrad GEMM epilogues (needs ff % 128 == 0)
+        self.fuse_softmax_bwd = os.environ.get("PT_STAGE1_FUSE_SOFTMAX_BWD", "1") != "0"
         self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
@@ -261,14 +262,15 @@ class Stage1Engine:
         QKV = (c.hq + 2 * c.hkv) * c.hd
         return G, ld, QKV
 
-    def _scores_like(self, A, a_off, lda, a_zs, Bm, b_off, ldb, b_zs, out, B, S, alpha, b_mn=False, window=0):
+    def _scores_like(self, A, a_off, lda, a_zs, Bm, b_off, ldb, b_zs, out, B, S, alpha, b_mn=False, window=0,
+                     **epilogue):
         """out[b, kvh*G+g, q, k] (f32, ld) = alpha * A_row(q) . B_row(k) over hd, batched (g, kvh, b)."""
         c = self.lcfg
         G, ld, _ = self._attn_geometry(B, S)
         ops.gemm_raw(M=S, N=S, K=c.hd, A=A, a_off=a_off, lda=lda, B=Bm, b_off=b_off, ldb=ldb,
                      Cout=out, ldc=ld, nz=(G, c.hkv, B), a_zs=a_zs, b_zs=b_zs,
                      c_zs=(S * ld, G * S * ld, c.hq * S * ld), alpha=alpha, band=ops.BAND_SCORES,
-                     band_window=window)
+                     band_window=window, **epilogue)
 
     # ------------------------------------------------------------------ LLM forward + loss
     def _llm_stack(self, x0: torch.Tensor, keyvalid, B: int, S: int, save: bool, cache=None):
@@ -284,7 +286,6 @@ class Stage1Engine:
         sv = []
         a = self.buf("l_a", (M, h), BF16)
         sc = self.buf("l_scores", (B * hq, S, ld), F32)
-        attn_o = self.buf("l_attn_o", (M, hq * hd), BF16)
         act = self.buf("l_act", (M, ff), BF16)
         x = x0
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
@@ -296,6 +297,7 @@ class Stage1Engine:
             q_post = self.buf(tag + "q", (M, hq * hd), BF16)
             k_post = self.buf(tag + "k", (M, hkv * hd), BF16)
             P = self.buf(tag + "P", (B * hq, S, ld), BF16)
+            attn_o = self.buf(tag + "ao", (M, hq * hd), BF16)      # kept: delta = rowsum(dO * O) in the backward
             y_attn = self.buf(tag + "ya", (M, h), BF16)
             x1 = self.buf(tag + "x1", (M, h), F32)
             gu = self.buf(tag + "gu", (M, 2 * ff), BF16)
@@ -329,7 +331,7 @@ class Stage1Engine:
                                      None if last else Lm.layers[li + 1]["in_norm"],
                                      None if last else a, c.eps)
             if save:
-                sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ya=y_attn, x1=x1, gu=gu,
+                sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ao=attn_o, ya=y_attn, x1=x1, gu=gu,
                                ym=y_mlp, full=full))
             x = x2
         return x, sv
@@ -378,6 +380,7 @@ class Stage1Engine:
         d_o = self.buf("b_do", (M, hq * hd), BF16)
         dP = self.buf("l_scores", (B * hq, S, ld), F32)            # reuse the forward score buffer
         dS = self.buf("b_dS", (B * hq, S, ld), BF16)
+        delta = self.buf("b_delta", (B * hq * S,), F32)
         dq = self.buf("b_dq", (M, hq * hd), BF16)
         dk = self.buf("b_dk", (M, hkv * hd), BF16)
         d_qkv = self.buf("b_dqkv", (M, QKV), BF16)
@@ -403,9 +406,16 @@ class Stage1Engine:
             ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
             win = 0 if a["full"] else c.window
-            self._scores_like(d_o, 0, hq * hd, (hd, G * hd, S * hq * hd), a["qkv"], (hq + hkv) * hd,
-                              QKV, (0, hd, S * QKV), dP, B, S, 1.0, window=win)
-            ops.softmax_bwd(a["P"], dP, dS, B * hq * S, S, ld, scale, Sq=S, causal=1, window=win)
+            if self.fuse_softmax_bwd:
+                # dS = scale * P * (dO V^T - delta) in the GEMM epilogue, delta = rowsum(dO * O)
+                ops.attn_delta(d_o, a["ao"], delta, S, hq, hd)
+                self._scores_like(d_o, 0, hq * hd, (hd, G * hd, S * hq * hd), a["qkv"], (hq + hkv) * hd,
+                                  QKV, (0, hd, S * QKV), dS, B, S, scale, window=win,
+                                  act=ops.ACT_SOFTMAX_BWD, aux=a["P"], ld_aux=ld, bias=delta)
+            else:
+                self._scores_like(d_o, 0, hq * hd, (hd, G * hd, S * hq * hd), a["qkv"], (hq + hkv) * hd,
+                                  QKV, (0, hd, S * QKV), dP, B, S, 1.0, window=win)
+                ops.softmax_bwd(a["P"], dP, dS, B * hq * S, S, ld, scale, Sq=S, causal=1, window=win)
             # dV[b,k,kvh,:] = sum_g P[b,kvh*G+g]^T dO[b,:,kvh*G+g,:]  -> v columns of d_qkv
             ops.gemm_raw(M=S, N=hd, K=S, A=a["P"], lda=ld, a_mn=True, B=d_o, ldb=hq * hd, b_mn=True,
                          Cout=d_qkv, c_off=(hq + hkv) * hd, ldc=QKV, nz=(hkv, B, 1),
@@ -494,6 +504,32 @@ class Stage1Engine:
         self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
 
+    def stage_batch(self, batch: dict) -> dict:
+        """Start the host->device copy of a (pinned) host batch on a side stream so that it overlaps the step
+        that is running; returns a batch dict to hand to train_step later.  Two staging slots alternate (the
+        DataLoader-prefetch pattern: while step i computes, batch i+1 is copied)."""
+        if not hasattr(self, "_stage"):
+            self._stage = dict(stream=torch.cuda.Stream(device=self.device), slots=[None, None], n=0)
+        sg = self._stage
+        i = sg["n"] & 1
+        sg["n"] += 1
+        pv, ti, lb = batch["pixel_values"], batch["token_ids"], batch["labels"]
+        slot = sg["slots"][i]
+        if slot is None or slot["px"].shape != pv.shape or slot["ids"].shape != ti.shape:
+            slot = dict(px=torch.empty(pv.shape, dtype=F32, device=self.device),
+                        ids=torch.empty(ti.shape, dtype=torch.int64, device=self.device),
+                        lab=torch.empty(lb.shape, dtype=torch.int64, device=self.device),
+                        event=torch.cuda.Event(), done=torch.cuda.Event())
+            slot["done"].record()
+            sg["slots"][i] = slot
+        with torch.cuda.stream(sg["stream"]):
+            sg["stream"].wait_event(slot["done"])       # the step that consumed this slot has read it
+            slot["px"].copy_(pv, non_blocking=True)
+            slot["ids"].copy_(ti, non_blocking=True)
+            slot["lab"].copy_(lb, non_blocking=True)
+            slot["event"].record()
+        return {"pixel_values": pv, "token_ids": ti, "labels": lb, "_staged": slot}
+
     def _graphed_forward_backward(self, batch: dict, pad_id) -> torch.Tensor:
         """forward_backward through a CUDA graph keyed on the batch geometry: inputs are copied into
         static device buffers, the first call per geometry runs eagerly (sizes the workspaces), the
@@ -508,9 +544,16 @@ class Stage1Engine:
                      lab=torch.empty(lb.shape, dtype=torch.int64, device=self.device),
                      graph=None, calls=0, loss=None)
             self._graphs[key] = g
+        st = batch.get("_staged")
+        if st is not None:
+            # inputs were prefetched by stage_batch() on the copy stream: order after that copy, then D2D
+            torch.cuda.current_stream().wait_event(st["event"])
+            pv, ti, lb = st["px"], st["ids"], st["lab"]
         g["px"].copy_(pv, non_blocking=True)
         g["ids"].copy_(ti, non_blocking=True)
         g["lab"].copy_(lb, non_blocking=True)
+        if st is not None:
+            st["done"].record()                 # staging slot reusable once these copies have run
         g["calls"] += 1
         if g["calls"] == 1:
             n0 = _lib.launch_count
@@ -715,10 +758,16 @@ class Stage1Engine:
         if self.use_graph:
             loss = self._graphed_forward_backward(batch, pad_id)
         else:
+            st = batch.get("_staged")
+            if st is not None:
+                torch.cuda.current_stream().wait_event(st["event"])
+                batch = {"pixel_values": st["px"], "token_ids": st["ids"], "labels": st["lab"]}
             px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
             ids = batch["token_ids"].to(dev, non_blocking=True)
             lab = batch["labels"].to(dev, non_blocking=True)
             loss = self.forward_backward(px, ids, lab, pad_id)
+            if st is not None:
+                st["done"].record()
         if allreduce is not None and world_size > 1:
             allreduce(self.proj.grad)
         self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size)

@@ -12,7 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import BAND_K_BY_KEY, BAND_K_BY_QUERY, BAND_NONE, BAND_SCORES  # noqa: F401
-from ._lib import ACT_GEGLU, ACT_GEGLU_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
+from ._lib import ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
@@ -233,6 +233,11 @@ def softmax_bwd(P, dP, dS, rows, Sk, ld, scale, Sq=0, causal=0, window=0):
     _req_cuda(P, dP, dS)
     _lib.call("pt_softmax_bwd", _ptr(P), _ptr(dP), _ptr(dS), C.c_longlong(int(rows)), int(Sk),
               int(ld), _f(scale), int(Sq), int(causal), int(window), _stream())
+
+
+def attn_delta(dO, O, delta, S, hq, hd):
+    _req_cuda(dO, O, delta)
+    _lib.call("pt_attn_delta", _ptr(dO), _ptr(O), _ptr(delta), dO.shape[0], int(S), int(hq), int(hd), _stream())
 
 
 def geglu_fwd(gu, act):

@@ -122,6 +122,20 @@ class ProjectionTrainerStage1:
     def current_lr(self) -> float:
         return self.learning_rate * cosine_with_warmup(self._sched_step, self.num_warmup_steps, self.max_train_steps)
 
+    def _prefetched(self, loader):
+        """One-batch look-ahead: the host->device copy of batch i+1 runs on a side stream while step i
+        computes (the reference gets the same overlap from DataLoader workers + pinned memory)."""
+        it = iter(loader)
+        cur = next(it, None)
+        if cur is not None and not cur["pixel_values"].is_cuda:
+            cur = self.engine.stage_batch(cur)
+        while cur is not None:
+            nxt = next(it, None)
+            if nxt is not None and not nxt["pixel_values"].is_cuda:
+                nxt = self.engine.stage_batch(nxt)
+            yield cur
+            cur = nxt
+
     def train(self):
         acc = self.accelerator
         logger.info(f"Process {acc.process_index}: Starting Stage 1 training for {self.num_epochs} epochs on {self.device}")
@@ -130,7 +144,7 @@ class ProjectionTrainerStage1:
         for epoch in range(self.num_epochs):
             epoch_train_loss = 0.0
             n_steps = 0
-            for batch in self.train_loader:
+            for batch in self._prefetched(self.train_loader):
                 lr = self.current_lr()
                 loss = self.engine.train_step(batch, lr, pad_id=self.pad_id, weight_decay=self.weight_decay,
                                               allreduce=acc.all_reduce_sum_, world_size=acc.num_processes)

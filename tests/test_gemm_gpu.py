@@ -199,3 +199,41 @@ def test_gemm_attention_bands_skip_only_masked_work(cuda_dev, S, W):
     ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, a_mn=True, B=do, ldb=hd, b_mn=True, Cout=dv, ldc=hd, kg=G,
                  a_kgs=S * ld, b_kgs=S * hd, band=ops.BAND_K_BY_KEY, band_window=W)
     _check(dv, torch.einsum("gqk,gqd->kd", P[:, :, :S].float(), do.float()), name="P^T dO")
+
+
+@pytest.mark.parametrize("S,W", [(703, 0), (703, 512), (90, 16)])
+def test_gemm_fused_softmax_backward_epilogue(cuda_dev, gemm_impl, S, W):
+    """dS = scale * P * (dO V^T - delta) in the GEMM epilogue (delta = rowsum(dO * O)) vs torch autograd
+    through softmax(QK^T * scale) V on the same bf16-rounded tensors."""
+    from projectiontrainer_b200 import ops
+    if gemm_impl == 1:
+        pytest.skip("fused softmax-backward epilogue exists in the CTA-pair kernel only")
+    torch.manual_seed(S + W)
+    Bn, hq, hd, scale = 2, 2, 64, 0.125
+    ld = (S + 7) // 8 * 8
+    q, k, v = (_rand((Bn, S, hq, hd), cuda_dev), _rand((Bn, S, 1, hd), cuda_dev), _rand((Bn, S, 1, hd), cuda_dev))
+    qi, ki = torch.arange(S, device=cuda_dev)[:, None], torch.arange(S, device=cuda_dev)[None, :]
+    allowed = (ki <= qi) & ((ki > qi - W) if W else (ki <= qi))
+    qf = q.float().permute(0, 2, 1, 3)                               # [B, hq, S, hd]
+    kf, vf = k.float()[:, :, 0], v.float()[:, :, 0]                  # [B, S, hd]
+    sc = torch.einsum("bhqd,bkd->bhqk", qf, kf) * scale
+    Pf = torch.softmax(sc.masked_fill(~allowed, float("-inf")), dim=-1)
+    P = torch.zeros(Bn * hq, S, ld, device=cuda_dev, dtype=torch.bfloat16)
+    P[:, :, :S] = Pf.reshape(Bn * hq, S, S).to(torch.bfloat16)
+    Pb = P[:, :, :S].float().reshape(Bn, hq, S, S)
+    O = torch.einsum("bhqk,bkd->bqhd", Pb, vf).to(torch.bfloat16)    # [B, S, hq, hd]
+    dO = _rand((Bn, S, hq, hd), cuda_dev)
+    delta = torch.empty(Bn * hq * S, device=cuda_dev)
+    ops.attn_delta(dO.view(Bn * S, hq * hd), O.view(Bn * S, hq * hd), delta, S, hq, hd)
+    ref_delta = (dO.float() * O.float()).sum(-1).permute(0, 2, 1).reshape(-1)
+    _check(delta, ref_delta, tol=1e-3, name="delta")
+    dS = torch.full((Bn * hq, S, ld), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    ops.gemm_raw(M=S, N=S, K=hd, A=dO, lda=hq * hd, B=v, ldb=hd, Cout=dS, ldc=ld, nz=(hq, 1, Bn),
+                 a_zs=(hd, 0, S * hq * hd), b_zs=(0, 0, S * hd), c_zs=(S * ld, 0, hq * S * ld), alpha=scale,
+                 band=ops.BAND_SCORES, band_window=W, act=ops.ACT_SOFTMAX_BWD, aux=P, ld_aux=ld, bias=delta)
+    dP = torch.einsum("bqhd,bkd->bhqk", dO.float(), vf)
+    ref = scale * Pb * (dP - (Pb * dP).sum(-1, keepdim=True))
+    got = dS[:, :, :S].float().reshape(Bn, hq, S, S)
+    inband = allowed[None, None].expand_as(got)
+    assert bool(torch.isfinite(got[inband]).all())
+    _check(got[inband], ref[inband], tol=2e-2, name="dS in band")

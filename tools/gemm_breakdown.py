@@ -14,6 +14,7 @@ a = ap.parse_args()
 dev = torch.device("cuda:0")
 vc, lc = SIGLIP_L, GEMMA3_1B
 eng = build_engine(vc, lc, dev)
+eng.use_graph = False
 g = torch.Generator(device=dev).manual_seed(1234)
 px = torch.rand(a.B, 3, vc.image, vc.image, generator=g, device=dev) * 2 - 1
 ids = torch.randint(3, lc.vocab, (a.B, a.T), generator=g, device=dev); ids[:, 0] = 2
