@@ -1,0 +1,413 @@
+// Fused causal / sliding-window GQA attention forward for the Gemma3 decoder (head_dim 256):
+//     P = softmax(mask(Q K^T * scale)),  O = P V       HF:models/gemma3/modeling_gemma3.py:278-300,370-384
+// Replaces (band GEMM -> f32 scores in HBM -> softmax kernel -> bf16 P -> band GEMM): the scores never leave
+// TMEM.  The normalised probabilities P ARE written (bf16), because the input-gradient backward reads them
+// (dV = P^T dO, dS = P (dP - delta)); to have them normalised at the time they are produced the kernel makes
+// two passes over the key tiles of a query block:
+//     pass 0:  S_j = Q K_j^T (tcgen05.mma, TMEM)  ->  running row max m and row sum l (online, registers)
+//     pass 1:  S_j again  ->  p = exp2((s - m) c) / l  -> bf16 -> global P  and  swizzled smem -> O += P_j V_j
+// which costs one extra Q K^T (cheap: K = 256) and needs no O rescaling at all.
+//
+// Work item = (batch, kv head, block of 128 stacked query rows): the G = hq/hkv query heads that share a kv
+// head are stacked with their positions, row r <-> (position s0 + r / G, head kvh*G + r % G), by a 5-D TMA box
+// over the rotated queries [B*S, hq*hd], so one K/V tile serves all G heads.  Only key tiles inside the causal
+// (and sliding-window) band of the block are visited.  Roles: warps 0-3 softmax (thread = row), warp 4 MMA
+// issuer, warp 5 TMA producer; every hand-off is an mbarrier (TMA tx, tcgen05.commit or 128 thread arrivals).
+// TMEM: S0 [0,64) S1 [64,128) O [128,384).
+#include "pt_common.cuh"
+#include "sm100_ptx.cuh"
+#include "gemm_common.cuh"
+
+namespace pt {
+
+constexpr int kGqRows = 128;
+constexpr int kGkTile = 64;
+constexpr int kGhd = 256;
+constexpr int kGthreads = 192;
+constexpr int kGqBytes = kGqRows * kGhd * 2;        // 64 KB: 4 slabs (64 columns) of 128 rows x 128 B
+constexpr int kGkvBytes = kGkTile * kGhd * 2;       // 32 KB: 4 slabs of 64 rows x 128 B
+constexpr int kGpBytes = kGqRows * kGkTile * 2;     // 16 KB
+constexpr int kGsmem = kGqBytes + 4 * kGkvBytes + kGpBytes + 256 + 1024;
+
+struct AttnGemmaDev {
+    int B, S, hq, hkv, G, window;     // window 0 = causal only
+    int pos_per_blk, nqb;             // 128 / G query positions per block; blocks per (batch, kv head)
+    int ldp;                          // row stride of P (elements)
+    float scale_log2e;
+    const unsigned long long* kvbits; // [B][ceil(S/64)] key-valid bit masks (bit i = key 64 w + i), or null
+    int kvwords;
+    __nv_bfloat16* P;                 // [B*hq, S, ldp]
+    __nv_bfloat16* O;                 // [B*S, hq*256]
+};
+
+// keyvalid bytes [B][S] -> bit masks [B][ceil(S/64)]
+__global__ void pack_keyvalid_kernel(const uint8_t* __restrict__ kv, unsigned long long* __restrict__ bits, int B,
+                                     int S, int words) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= B * words) return;
+    const int b = idx / words, w = idx - b * words;
+    unsigned long long m = 0ull;
+    for (int i = 0; i < 64; ++i) {
+        const int k = w * 64 + i;
+        if (k < S && kv[static_cast<long long>(b) * S + k]) m |= 1ull << i;
+    }
+    bits[idx] = m;
+}
+
+__device__ __forceinline__ void gemma_item(const AttnGemmaDev& p, int item, int& b, int& kvh, int& qb, int& jlo, int& nt) {
+    const int per = p.B * p.hkv;
+    const int rev = item / per;                   // heaviest (latest) query blocks first
+    const int rem = item - rev * per;
+    qb = p.nqb - 1 - rev;
+    b = rem / p.hkv; kvh = rem - b * p.hkv;
+    const int s0 = qb * p.pos_per_blk;
+    const int s1 = min(p.S - 1, s0 + p.pos_per_blk - 1);
+    jlo = p.window > 0 ? max(0, s0 - p.window + 1) / kGkTile : 0;
+    nt = s1 / kGkTile - jlo + 1;
+}
+
+__global__ void __launch_bounds__(kGthreads, 1)
+attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const AttnGemmaDev p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + kGqBytes;                 // 2 stages
+    uint8_t* sV = sK + 2 * kGkvBytes;            // 2 stages
+    uint8_t* sP = sV + 2 * kGkvBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kGpBytes);
+    uint64_t* q_full = bars;            // TMA -> MMA
+    uint64_t* q_empty = bars + 1;       // MMA (commit after the item's last S) -> TMA
+    uint64_t* k_full = bars + 2;        // [2]
+    uint64_t* k_empty = bars + 4;       // [2] commit after S_j
+    uint64_t* v_full = bars + 6;        // [2]
+    uint64_t* v_empty = bars + 8;       // [2] commit after PV_j
+    uint64_t* s_full = bars + 10;       // [2] commit after S_j -> softmax
+    uint64_t* s_free = bars + 12;       // [2] softmax (128 arrivals) -> MMA
+    uint64_t* p_full = bars + 14;       // softmax (128 arrivals) -> MMA
+    uint64_t* pv_done = bars + 15;      // commit after PV_j -> softmax
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 128) {
+        ptx::prefetch_tmap(&tmQ); ptx::prefetch_tmap(&tmK); ptx::prefetch_tmap(&tmV);
+        ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&k_full[s], 1); ptx::mbar_init(&k_empty[s], 1);
+            ptx::mbar_init(&v_full[s], 1); ptx::mbar_init(&v_empty[s], 1);
+            ptx::mbar_init(&s_full[s], 1); ptx::mbar_init(&s_free[s], 128);
+        }
+        ptx::mbar_init(p_full, 128);
+        ptx::mbar_init(pv_done, 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 4) {
+        ptx::tmem_alloc(tmem_slot, 512);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tS[2] = {tmem_base, tmem_base + kGkTile};
+    const uint32_t tO = tmem_base + 2 * kGkTile;
+    const int items = p.B * p.hkv * p.nqb;
+
+    if (warp == 5) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            uint32_t n_item = 0, kc = 0, vc = 0;          // running counters -> stage / parity
+            for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+                int b, kvh, qb, jlo, nt;
+                gemma_item(p, item, b, kvh, qb, jlo, nt);
+                ptx::mbar_wait(q_empty, (n_item & 1) ^ 1);           // previous item's S MMAs retired
+                ptx::mbar_arrive_expect_tx(q_full, kGqBytes);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    ptx::tma_load_5d(&tmQ, q_full, sQ + c * (kGqRows * 128), c * 64, 0, qb * p.pos_per_blk, kvh, b);
+                for (int pass = 0; pass < 2; ++pass) {
+                    for (int j = 0; j < nt; ++j) {
+                        const int st = kc & 1;
+                        ptx::mbar_wait(&k_empty[st], ((kc >> 1) & 1) ^ 1);
+                        ptx::mbar_arrive_expect_tx(&k_full[st], kGkvBytes);
+#pragma unroll
+                        for (int c = 0; c < 4; ++c)
+                            ptx::tma_load_5d(&tmK, &k_full[st], sK + st * kGkvBytes + c * (kGkTile * 128), c * 64,
+                                             (jlo + j) * kGkTile, kvh, b, 0);
+                        ++kc;
+                        if (pass == 1) {
+                            const int sv = vc & 1;
+                            ptx::mbar_wait(&v_empty[sv], ((vc >> 1) & 1) ^ 1);
+                            ptx::mbar_arrive_expect_tx(&v_full[sv], kGkvBytes);
+#pragma unroll
+                            for (int c = 0; c < 4; ++c)
+                                ptx::tma_load_5d(&tmV, &v_full[sv], sV + sv * kGkvBytes + c * (kGkTile * 128), c * 64,
+                                                 (jlo + j) * kGkTile, kvh, b, 0);
+                            ++vc;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 4) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idescS = ptx::make_idesc_bf16(kGqRows, kGkTile, 0, 0);
+            const uint32_t idescO = ptx::make_idesc_bf16(kGqRows, kGhd, 0, 1);      // B = V, MN-major
+            uint32_t n_item = 0, kc = 0, vc = 0, sc = 0, pc = 0;
+            auto issue_S = [&]() {
+                const int st = kc & 1, sb = sc & 1;
+                ptx::mbar_wait(&k_full[st], (kc >> 1) & 1);
+                ptx::mbar_wait(&s_free[sb], ((sc >> 1) & 1) ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t qa = ptx::smem_u32(sQ), ka = ptx::smem_u32(sK + st * kGkvBytes);
+#pragma unroll
+                for (int k = 0; k < kGhd / 16; ++k) {
+                    const uint64_t qdesc = ptx::make_smem_desc_sw128(qa + (k >> 2) * (kGqRows * 128) + (k & 3) * 32, 0, 1024);
+                    const uint64_t kdesc = ptx::make_smem_desc_sw128(ka + (k >> 2) * (kGkTile * 128) + (k & 3) * 32, 0, 1024);
+                    ptx::mma_bf16_ss(tS[sb], qdesc, kdesc, idescS, k != 0);
+                }
+                ptx::mma_commit(&s_full[sb]);
+                ptx::mma_commit(&k_empty[st]);
+                ++kc; ++sc;
+            };
+            for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+                int b, kvh, qb, jlo, nt;
+                gemma_item(p, item, b, kvh, qb, jlo, nt);
+                ptx::mbar_wait(q_full, n_item & 1);
+                for (int j = 0; j < nt; ++j) issue_S();                  // pass 0: statistics
+                issue_S();                                                // pass 1, tile 0
+                if (nt == 1) ptx::mma_commit(q_empty);
+                for (int j = 0; j < nt; ++j) {
+                    if (j + 1 < nt) {
+                        issue_S();
+                        if (j + 2 == nt) ptx::mma_commit(q_empty);        // last S of the item issued: Q is free
+                    }
+                    const int sv = vc & 1;
+                    ptx::mbar_wait(p_full, pc & 1);
+                    ptx::mbar_wait(&v_full[sv], (vc >> 1) & 1);
+                    ptx::tc_fence_after();
+                    const uint32_t pa = ptx::smem_u32(sP), va = ptx::smem_u32(sV + sv * kGkvBytes);
+#pragma unroll
+                    for (int k = 0; k < kGkTile / 16; ++k) {
+                        const uint64_t pdesc = ptx::make_smem_desc_sw128(pa + k * 32, 0, 1024);
+                        const uint64_t vdesc = ptx::make_smem_desc_sw128(va + k * 16 * 128, kGkTile * 128, 1024);
+                        ptx::mma_bf16_ss(tO, pdesc, vdesc, idescO, (j | k) != 0);
+                    }
+                    ptx::mma_commit(pv_done);
+                    ptx::mma_commit(&v_empty[sv]);
+                    ++vc; ++pc;
+                }
+            }
+        }
+    } else {
+        // ===================== softmax warps: thread = stacked query row =====================
+        const int row = threadIdx.x;                               // TMEM lane
+        const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+        const uint32_t p_row = ptx::smem_u32(sP) + row * 128;
+        uint32_t sc = 0, pc = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            int b, kvh, qb, jlo, nt;
+            gemma_item(p, item, b, kvh, qb, jlo, nt);
+            const int s = qb * p.pos_per_blk + row / p.G;           // query position of this row
+            const int head = kvh * p.G + row % p.G;
+            const bool live = s < p.S;
+            const int k_hi = live ? s : -1;                          // visible keys: k_lo <= k <= k_hi
+            const int k_lo = p.window > 0 ? max(0, s - p.window + 1) : 0;
+            const unsigned long long* kvw = p.kvbits ? p.kvbits + static_cast<long long>(b) * p.kvwords : nullptr;
+
+            // visibility mask of the 64 keys of tile j for this row
+            auto tile_mask = [&](int j) -> unsigned long long {
+                const int k0 = (jlo + j) * kGkTile;
+                unsigned long long m = kvw ? kvw[jlo + j] : ~0ull;
+                const int hi = k_hi - k0, lo = k_lo - k0;            // visible local indices: lo <= i <= hi
+                if (hi < 0 || lo > 63) return 0ull;
+                if (hi < 63) m &= (2ull << hi) - 1ull;
+                if (lo > 0) m &= ~0ull << lo;
+                return m;
+            };
+            auto load_S = [&](uint32_t (&v)[2][32]) {
+                const int sb = sc & 1;
+                ptx::mbar_wait(&s_full[sb], (sc >> 1) & 1);
+                ptx::tc_fence_after();
+                ptx::tmem_ld_32x32(tS[sb] + lane_off, v[0]);
+                ptx::tmem_ld_32x32(tS[sb] + lane_off + 32, v[1]);
+                ptx::tmem_ld_wait();
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(&s_free[sb]);
+                ++sc;
+            };
+
+            // ---- pass 0: row max and row sum over the band
+            float m_run = -INFINITY, l_run = 0.f;
+            for (int j = 0; j < nt; ++j) {
+                uint32_t v[2][32];
+                load_S(v);
+                const unsigned long long mask = tile_mask(j);
+                if (mask == 0ull) continue;
+                float mxs[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        if (!((mask >> (c * 32 + i)) & 1ull)) v[c][i] = __float_as_uint(-INFINITY);
+                        mxs[i & 3] = fmaxf(mxs[i & 3], __uint_as_float(v[c][i]));
+                    }
+                const float m_new = fmaxf(m_run, fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])));
+                const float mb = m_new * p.scale_log2e;
+                float ls[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        ls[i & 3] += ptx::exp2_fast(fmaf(__uint_as_float(v[c][i]), p.scale_log2e, -mb));
+                const float alpha = (m_run == -INFINITY) ? 0.f : ptx::exp2_fast((m_run - m_new) * p.scale_log2e);
+                l_run = l_run * alpha + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
+                m_run = m_new;
+            }
+            const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+            const float mb = (m_run == -INFINITY ? 0.f : m_run) * p.scale_log2e;
+
+            // ---- pass 1: normalised probabilities -> global P and smem, O += P V
+            __nv_bfloat16* prow_g = p.P + ((static_cast<long long>(b) * p.hq + head) * p.S + (live ? s : 0)) * p.ldp;
+            for (int j = 0; j < nt; ++j) {
+                uint32_t v[2][32];
+                load_S(v);
+                const unsigned long long mask = tile_mask(j);
+                uint32_t pk[32];
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int i0 = c * 32 + 2 * i;
+                        float e0 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i]), p.scale_log2e, -mb)) * inv;
+                        float e1 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i + 1]), p.scale_log2e, -mb)) * inv;
+                        if (!((mask >> i0) & 1ull)) e0 = 0.f;
+                        if (!((mask >> (i0 + 1)) & 1ull)) e1 = 0.f;
+                        pk[c * 16 + i] = pack_bf16(e0, e1);
+                    }
+                if (live) {
+                    const int k0 = (jlo + j) * kGkTile;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        if (k0 + q * 8 < p.ldp)
+                            *reinterpret_cast<uint4*>(prow_g + k0 + q * 8) =
+                                make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                }
+                // the single P buffer is free once the previous tile's PV has retired
+                if (j > 0) { ptx::mbar_wait(pv_done, pc & 1); ++pc; }
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    ptx::sts128(p_row + ((q ^ (row & 7)) << 4), pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                ptx::fence_proxy_async_smem();
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(p_full);
+            }
+            // ---- epilogue: O -> bf16 -> global
+            ptx::mbar_wait(pv_done, pc & 1); ++pc;
+            ptx::tc_fence_after();
+            __nv_bfloat16* op = p.O + (static_cast<long long>(b) * p.S + (live ? s : 0)) * (p.hq * kGhd) + head * kGhd;
+#pragma unroll 1
+            for (int c = 0; c < kGhd / 32; ++c) {
+                uint32_t o[32];
+                ptx::tmem_ld_32x32(tO + lane_off + c * 32, o);
+                ptx::tmem_ld_wait();
+                if (live) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        uint4 u;
+                        u.x = pack_bf16(__uint_as_float(o[8 * q]), __uint_as_float(o[8 * q + 1]));
+                        u.y = pack_bf16(__uint_as_float(o[8 * q + 2]), __uint_as_float(o[8 * q + 3]));
+                        u.z = pack_bf16(__uint_as_float(o[8 * q + 4]), __uint_as_float(o[8 * q + 5]));
+                        u.w = pack_bf16(__uint_as_float(o[8 * q + 6]), __uint_as_float(o[8 * q + 7]));
+                        *reinterpret_cast<uint4*>(op + c * 32 + q * 8) = u;
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace pt
+
+using namespace pt;
+
+extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const uint8_t* keyvalid,
+                                 void* kvbits_ws, void* P_bf16, void* O_bf16, int B, int S, int hq, int hkv, int hd,
+                                 int window, float scale, int ldp, void* stream) {
+    PT_REQUIRE(q_rot && k_rot && qkv && P_bf16 && O_bf16, "pt_attn_gemma_fwd: null pointer");
+    PT_REQUIRE(hd == kGhd, "pt_attn_gemma_fwd: head_dim must be 256 (got %d)", hd);
+    PT_REQUIRE(B > 0 && S > 0 && hq > 0 && hkv > 0 && hq % hkv == 0 && window >= 0, "pt_attn_gemma_fwd: bad shape");
+    const int G = hq / hkv;
+    PT_REQUIRE(G <= 128 && (G & (G - 1)) == 0, "pt_attn_gemma_fwd: hq / hkv must be a power of two <= 128 (got %d)", G);
+    PT_REQUIRE(ldp >= S && ldp % 8 == 0, "pt_attn_gemma_fwd: ldp must be >= S and a multiple of 8");
+    PT_REQUIRE(keyvalid == nullptr || kvbits_ws != nullptr, "pt_attn_gemma_fwd: keyvalid needs the bit-mask workspace");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int QKV = (hq + 2 * hkv) * hd;
+    const int pos = kGqRows / G;
+    CUtensorMap tq, tk, tv;
+    {   // rotated queries [B*S, hq*hd] viewed as (hd, G, S, hkv, B); box = 64 columns x G heads x 128/G positions
+        const unsigned long long dims[5] = {(unsigned long long)hd, (unsigned long long)G, (unsigned long long)S,
+                                            (unsigned long long)hkv, (unsigned long long)B};
+        const unsigned long long str[4] = {(unsigned long long)hd * 2, (unsigned long long)hq * hd * 2,
+                                           (unsigned long long)G * hd * 2, (unsigned long long)S * hq * hd * 2};
+        const unsigned int box[5] = {64, (unsigned)G, (unsigned)pos, 1, 1};
+        int rc = encode_tiled_bf16_5d(&tq, q_rot, dims, str, box, "attn_gemma Q");
+        if (rc != PT_OK) return rc;
+    }
+    {   // rotated keys [B*S, hkv*hd] viewed as (hd, S, hkv, B, 1)
+        const unsigned long long dims[5] = {(unsigned long long)hd, (unsigned long long)S, (unsigned long long)hkv,
+                                            (unsigned long long)B, 1};
+        const unsigned long long str[4] = {(unsigned long long)hkv * hd * 2, (unsigned long long)hd * 2,
+                                           (unsigned long long)S * hkv * hd * 2, (unsigned long long)S * hkv * hd * 2 * B};
+        const unsigned int box[5] = {64, kGkTile, 1, 1, 1};
+        int rc = encode_tiled_bf16_5d(&tk, k_rot, dims, str, box, "attn_gemma K");
+        if (rc != PT_OK) return rc;
+    }
+    {   // values in place inside the fused qkv activation [B*S, QKV] at column (hq + hkv) * hd
+        const unsigned long long dims[5] = {(unsigned long long)hd, (unsigned long long)S, (unsigned long long)hkv,
+                                            (unsigned long long)B, 1};
+        const unsigned long long str[4] = {(unsigned long long)QKV * 2, (unsigned long long)hd * 2,
+                                           (unsigned long long)S * QKV * 2, (unsigned long long)S * QKV * 2 * B};
+        const unsigned int box[5] = {64, kGkTile, 1, 1, 1};
+        const __nv_bfloat16* vbase = static_cast<const __nv_bfloat16*>(qkv) + static_cast<long long>(hq + hkv) * hd;
+        int rc = encode_tiled_bf16_5d(&tv, vbase, dims, str, box, "attn_gemma V");
+        if (rc != PT_OK) return rc;
+    }
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(attn_gemma_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGsmem);
+        if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(attn_gemma): %s", cudaGetErrorString(e)); return PT_ERR_CUDA; }
+        attr_done = true;
+    }
+    AttnGemmaDev p;
+    p.B = B; p.S = S; p.hq = hq; p.hkv = hkv; p.G = G; p.window = window;
+    p.pos_per_blk = pos;
+    p.nqb = (S + pos - 1) / pos;
+    p.ldp = ldp;
+    p.scale_log2e = scale * 1.4426950408889634f;
+    p.kvwords = (S + 63) / 64;
+    p.kvbits = nullptr;
+    if (keyvalid) {
+        const int n = B * p.kvwords;
+        pack_keyvalid_kernel<<<(n + 127) / 128, 128, 0, st>>>(keyvalid, static_cast<unsigned long long*>(kvbits_ws), B, S,
+                                                               p.kvwords);
+        p.kvbits = static_cast<const unsigned long long*>(kvbits_ws);
+    }
+    p.P = static_cast<__nv_bfloat16*>(P_bf16);
+    p.O = static_cast<__nv_bfloat16*>(O_bf16);
+    const long long items = static_cast<long long>(B) * hkv * p.nqb;
+    PT_REQUIRE(items < (1ll << 31), "pt_attn_gemma_fwd: too many work items");
+    const int grid = items < num_sms() ? static_cast<int>(items) : num_sms();
+    attn_gemma_fwd_kernel<<<grid, kGthreads, kGsmem, st>>>(tq, tk, tv, p);
+    return check_launch("attn_gemma_fwd_kernel");
+}

@@ -71,6 +71,8 @@ __device__ __forceinline__ float apply_act(float v, int act) {
 // host helpers (gemm_sm100.cu)
 int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, int K, long long ld,
                    const int ext[3], const long long est[3], int rows_box, const char* name);
+int encode_tiled_bf16_5d(CUtensorMap* out, const void* base, const unsigned long long dims[5],
+                         const unsigned long long strides_bytes[4], const unsigned int box[5], const char* name);
 // CTA-pair kernel (gemm2_sm100.cu): bn in {64,128,192,256}; tensor map of B must use box rows bn/2
 int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st);
 int gemm2_tiles(const GemmDev& p, int bn);

@@ -372,6 +372,28 @@ int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, i
     return PT_OK;
 }
 
+// Generic 5-D bf16 tiled map with 128-byte swizzle (attention kernels build their own geometries).
+int encode_tiled_bf16_5d(CUtensorMap* out, const void* base, const unsigned long long dims[5],
+                         const unsigned long long strides_bytes[4], const unsigned int box[5], const char* name) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return PT_ERR_CUDA; }
+    cuuint64_t d[5], st[4];
+    cuuint32_t bx[5], es[5] = {1, 1, 1, 1, 1};
+    for (int i = 0; i < 5; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
+    for (int i = 0; i < 4; ++i) st[i] = strides_bytes[i];
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), d, st, bx, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(%s) failed: CUresult %d (dims %llu %llu %llu %llu %llu, strides %llu %llu "
+                  "%llu %llu, box %u %u %u %u %u)", name, static_cast<int>(r), dims[0], dims[1], dims[2], dims[3],
+                  dims[4], strides_bytes[0], strides_bytes[1], strides_bytes[2], strides_bytes[3], box[0], box[1],
+                  box[2], box[3], box[4]);
+        return PT_ERR_CUDA;
+    }
+    return PT_OK;
+}
+
 template <int BN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, int tiles,
                        cudaStream_t st) {

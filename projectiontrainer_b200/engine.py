@@ -166,15 +166,17 @@ class Stage1Engine:
         self.use_graph = os.environ.get("PT_STAGE1_GRAPH", "1") != "0"
         self._graphs: dict = {}
         # GeGLU forward / backward fused into the gate||up and down-dgrad GEMM epilogues (needs ff % 128 == 0)
+        self.fuse_attn_fwd = ops.attn_gemma_fusable(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
+            os.environ.get("PT_STAGE1_FUSE_ATTN_FWD", "1") != "0"
         self.fuse_softmax_bwd = os.environ.get("PT_STAGE1_FUSE_SOFTMAX_BWD", "1") != "0"
         self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
-    def buf(self, name, shape, dtype):
+    def buf(self, name, shape, dtype, zero=False):
         key = (name, tuple(shape), dtype)
         t = self._ws.get(key)
         if t is None:
-            t = torch.empty(shape, dtype=dtype, device=self.device)
+            t = (torch.zeros if zero else torch.empty)(shape, dtype=dtype, device=self.device)
             self._ws[key] = t
         return t
 
@@ -285,7 +287,8 @@ class Stage1Engine:
         scale = c.q_scalar ** -0.5
         sv = []
         a = self.buf("l_a", (M, h), BF16)
-        sc = self.buf("l_scores", (B * hq, S, ld), F32)
+        sc = None if self.fuse_attn_fwd else self.buf("l_scores", (B * hq, S, ld), F32)
+        kvbits = self.buf("l_kvbits", (B * ((S + 63) // 64),), torch.int64) if self.fuse_attn_fwd else None
         act = self.buf("l_act", (M, ff), BF16)
         x = x0
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
@@ -296,7 +299,8 @@ class Stage1Engine:
             qkv = self.buf(tag + "qkv", (M, QKV), BF16)
             q_post = self.buf(tag + "q", (M, hq * hd), BF16)
             k_post = self.buf(tag + "k", (M, hkv * hd), BF16)
-            P = self.buf(tag + "P", (B * hq, S, ld), BF16)
+            # fused attention writes P only inside the causal / window band: its buffers start zero-filled
+            P = self.buf(tag + ("Pz" if self.fuse_attn_fwd else "P"), (B * hq, S, ld), BF16, zero=self.fuse_attn_fwd)
             attn_o = self.buf(tag + "ao", (M, hq * hd), BF16)      # kept: delta = rowsum(dO * O) in the backward
             y_attn = self.buf(tag + "ya", (M, h), BF16)
             x1 = self.buf(tag + "x1", (M, h), F32)
@@ -310,14 +314,18 @@ class Stage1Engine:
                 cache["k"][li][:, :S].copy_(k_post.view(B, S, hkv * hd))
                 cache["v"][li][:, :S].copy_(qkv.view(B, S, QKV)[:, :, (hq + hkv) * hd:])
             win = 0 if full else c.window
-            self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
-                              (0, hd, S * hkv * hd), sc, B, S, scale, window=win)
-            ops.softmax_fwd(sc, P, keyvalid, B * hq, S, S, ld, hq, 1, win)
-            # attn_o[b, q, head, :] = P[b, head] V[b, :, kvh, :]   (V in place inside qkv, MN-major)
-            ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, B=qkv, b_off=(hq + hkv) * hd, ldb=QKV, b_mn=True,
-                         Cout=attn_o, ldc=hq * hd, nz=(G, hkv, B),
-                         a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * QKV),
-                         c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY, band_window=win)
+            if self.fuse_attn_fwd:
+                ops.attn_gemma_fwd(q_post, k_post, qkv, keyvalid, kvbits, P, attn_o, B, S, hq, hkv, hd, win,
+                                   scale, ld)
+            else:
+                self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
+                                  (0, hd, S * hkv * hd), sc, B, S, scale, window=win)
+                ops.softmax_fwd(sc, P, keyvalid, B * hq, S, S, ld, hq, 1, win)
+                # attn_o[b, q, head, :] = P[b, head] V[b, :, kvh, :]   (V in place inside qkv, MN-major)
+                ops.gemm_raw(M=S, N=hd, K=S, A=P, lda=ld, B=qkv, b_off=(hq + hkv) * hd, ldb=QKV, b_mn=True,
+                             Cout=attn_o, ldc=hq * hd, nz=(G, hkv, B),
+                             a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * QKV),
+                             c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY, band_window=win)
             ops.linear(attn_o, L["o_w"], out=y_attn)
             ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
             if self.fuse_geglu:
@@ -378,7 +386,7 @@ class Stage1Engine:
         d_act = self.buf("b_dact", (M, ff), BF16)
         d_gu = self.buf("b_dgu", (M, 2 * ff), BF16)
         d_o = self.buf("b_do", (M, hq * hd), BF16)
-        dP = self.buf("l_scores", (B * hq, S, ld), F32)            # reuse the forward score buffer
+        dP = None if self.fuse_softmax_bwd else self.buf("l_scores", (B * hq, S, ld), F32)
         dS = self.buf("b_dS", (B * hq, S, ld), BF16)
         delta = self.buf("b_delta", (B * hq * S,), F32)
         dq = self.buf("b_dq", (M, hq * hd), BF16)

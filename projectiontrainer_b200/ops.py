@@ -235,6 +235,18 @@ def softmax_bwd(P, dP, dS, rows, Sk, ld, scale, Sq=0, causal=0, window=0):
               int(ld), _f(scale), int(Sq), int(causal), int(window), _stream())
 
 
+def attn_gemma_fusable(hq: int, hkv: int, hd: int) -> bool:
+    G = hq // max(1, hkv)
+    return hd == 256 and hq % hkv == 0 and G <= 128 and (G & (G - 1)) == 0
+
+
+def attn_gemma_fwd(q_rot, k_rot, qkv, keyvalid, kvbits_ws, P, O, B, S, hq, hkv, hd, window, scale, ldp):
+    """Fused causal / sliding-window GQA attention forward (hd 256): writes normalised P (band only) and O."""
+    _req_cuda(q_rot, k_rot, qkv, keyvalid, kvbits_ws, P, O)
+    _lib.call("pt_attn_gemma_fwd", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(keyvalid), _ptr(kvbits_ws), _ptr(P),
+              _ptr(O), int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), int(ldp), _stream())
+
+
 def attn_delta(dO, O, delta, S, hq, hd):
     _req_cuda(dO, O, delta)
     _lib.call("pt_attn_delta", _ptr(dO), _ptr(O), _ptr(delta), dO.shape[0], int(S), int(hq), int(hd), _stream())

@@ -27,3 +27,48 @@ def test_attn_siglip_fwd(cuda_dev, B, N, H, amp, v1):
     assert err < 2e-2 * ref.abs().max().item() + 1e-3, err
     cos = torch.nn.functional.cosine_similarity(out.float().flatten(), ref.flatten(), dim=0).item()
     assert cos > 0.9995, cos
+
+
+@pytest.mark.parametrize("B,S,hq,hkv,W,pad", [(2, 200, 4, 1, 0, False), (2, 200, 4, 1, 64, True), (1, 703, 4, 1, 512, True),
+                                              (2, 300, 8, 4, 0, True), (3, 831, 8, 4, 100, False), (1, 40, 2, 2, 0, True)])
+def test_attn_gemma_fwd(cuda_dev, B, S, hq, hkv, W, pad):
+    """Fused causal / sliding-window GQA attention (hd 256) vs fp32 torch on the same bf16-rounded q/k/v: the
+    normalised P it writes inside the band (everything else must stay at the caller's zero fill) and O."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(S + hq + W)
+    hd, G = 256, hq // hkv
+    QKV = (hq + 2 * hkv) * hd
+    ld = (S + 7) // 8 * 8
+    q = (torch.randn(B * S, hq * hd, device=cuda_dev) * 1.0).to(torch.bfloat16)
+    k = (torch.randn(B * S, hkv * hd, device=cuda_dev) * 1.0).to(torch.bfloat16)
+    qkv = (torch.randn(B * S, QKV, device=cuda_dev)).to(torch.bfloat16)
+    keyvalid = torch.ones(B, S, dtype=torch.uint8, device=cuda_dev)
+    if pad:
+        for b in range(B):
+            keyvalid[b, :7 * b + 3] = 0
+        keyvalid[0, S // 2] = 0                      # an isolated masked key inside the band
+    kvbits = torch.empty(B * ((S + 63) // 64), dtype=torch.int64, device=cuda_dev)
+    P = torch.zeros(B * hq, S, ld, dtype=torch.bfloat16, device=cuda_dev)
+    O = torch.full((B * S, hq * hd), float("nan"), dtype=torch.bfloat16, device=cuda_dev)
+    scale = 1.0 / 16
+    ops.attn_gemma_fwd(q, k, qkv, keyvalid, kvbits, P, O, B, S, hq, hkv, hd, W, scale, ld)
+    torch.cuda.synchronize()
+    qf = q.float().view(B, S, hq, hd).transpose(1, 2)                                  # [B,hq,S,hd]
+    kf = k.float().view(B, S, hkv, hd).transpose(1, 2).repeat_interleave(G, dim=1)
+    vf = qkv.float().view(B, S, QKV)[:, :, (hq + hkv) * hd:].reshape(B, S, hkv, hd).transpose(1, 2).repeat_interleave(G, dim=1)
+    qi, ki = torch.arange(S, device=cuda_dev)[:, None], torch.arange(S, device=cuda_dev)[None, :]
+    allowed = (ki <= qi) & ((ki > qi - W) if W else (ki <= qi))
+    allowed = allowed[None, None] & keyvalid.bool()[:, None, None, :]
+    sc = (qf @ kf.transpose(-1, -2)) * scale
+    Pref = torch.nan_to_num(torch.softmax(sc.masked_fill(~allowed, float("-inf")), dim=-1), nan=0.0)
+    Oref = (Pref @ vf).transpose(1, 2).reshape(B * S, hq * hd)
+    Pg = P[:, :, :S].float().view(B, hq, S, S)
+    assert bool(torch.isfinite(Pg).all())
+    assert float(Pg[~allowed.expand_as(Pg)].abs().max()) == 0.0                      # masked / out of band: exactly 0
+    assert float((Pg - Pref).abs().max()) < 1e-2
+    rows_with_keys = allowed.any(-1).expand(B, hq, S).transpose(1, 2).reshape(B * S, hq)
+    live = rows_with_keys[:, :, None].expand(B * S, hq, hd).reshape(B * S, hq * hd)
+    got = O.float()
+    assert bool(torch.isfinite(got[live]).all())
+    err = (got[live] - Oref[live]).abs().max().item()
+    assert err < 2e-2 * Oref.abs().max().item() + 1e-3, err
