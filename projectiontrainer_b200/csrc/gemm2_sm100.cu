@@ -448,6 +448,17 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     }
                 }
             }
+            if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
+                // same for the saved probabilities this warp's slab will be multiplied with
+                const int pr = row0 + lane;
+                if (pr < p.M && pr >= m_blk * TM) {
+                    const uint8_t* g = static_cast<const uint8_t*>(p.aux) +
+                                       (coff / p.ldc * p.ld_aux + static_cast<long long>(pr) * p.ld_aux + tile_n + hf * BNH) * 2;
+#pragma unroll
+                    for (int b = 0; b < BNH * 2; b += 128)
+                        if (tile_n + hf * BNH + b / 2 < p.N) ptx::prefetch_l2(g + b);
+                }
+            }
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);

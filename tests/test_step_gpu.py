@@ -151,3 +151,36 @@ def test_mlp_projector_module_autograd(cuda_dev):
     assert y.dtype == torch.float32 and _cos(y, yr) > 0.9999
     for (k, p), (_, q) in zip(m.named_parameters(), ref.named_parameters()):
         assert _cos(p.grad, q.grad) > 0.999, k
+
+
+@pytest.mark.parametrize("fused", [True, False], ids=["fused_epilogues", "unfused_kernels"])
+def test_step_hd256_gqa_window_pads_vs_oracle(cuda_dev, fused, monkeypatch):
+    """The fused paths that only engage at head_dim 256 / ff % 128 == 0 (flash-style Gemma attention forward,
+    softmax backward in the dO V^T epilogue, GeGLU epilogues, attention bands) on a reduced-width decoder with the
+    4B geometry class (GQA with 2 kv heads, sliding window shorter than the sequence, linear-scaled global RoPE,
+    left pads), checked against the CPU oracle holding the same bf16-rounded matrices; the unfused kernels are
+    run on the same inputs as a second witness."""
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    if not fused:
+        for k in ("PT_STAGE1_FUSE_ATTN_FWD", "PT_STAGE1_FUSE_SOFTMAX_BWD", "PT_STAGE1_FUSE_GEGLU"):
+            monkeypatch.setenv(k, "0")
+    vkw = dict(hidden=128, ff=256, layers=2, heads=2, image=160, patch=16)          # 100 patches -> 99 image tokens
+    lkw = dict(vocab=1024, hidden=256, ff=256, layers=7, hq=4, hkv=2, hd=256, window=40, q_scalar=256.0,
+               rope_factor_global=8.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    px, ids, lab = O.synthetic_batch(3, 48, ovc, olc, left_pad=True)
+    q = lambda t: t.to(torch.bfloat16).float()
+    Wv_q = {k: (q(v) if v.dim() == 2 and k != "pos" else v) for k, v in Wv.items()}
+    Wl_q = {k: (q(v) if v.dim() == 2 else v) for k, v in Wl.items()}
+    ref = O.stage1_step(px, ids, lab, Wv_q, P, Wl_q, ovc, olc, scale_dtype=torch.bfloat16)
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev)
+    assert eng.fuse_attn_fwd == fused and eng.fuse_geglu == fused and eng.fuse_softmax_bwd == fused
+    loss = eng.forward_backward(px.to(cuda_dev), ids.to(cuda_dev), lab.to(cuda_dev), olc.pad_id)
+    torch.cuda.synchronize()
+    assert abs(loss.item() - ref["loss"]) / ref["loss"] < 1e-2
+    for k, gr in eng.proj.grads().items():
+        assert _cos(gr.cpu(), ref["grads"][k]) > 0.999, k
