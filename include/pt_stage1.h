@@ -203,12 +203,15 @@ int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long
  *                      causal / window band — the caller zero-fills P once; masked keys inside the band get 0)
  *   O[b*S + q, head*256 ..] = sum_k P V                          (bf16, [B*S, hq*256])
  * q_rot [B*S, hq*256], k_rot [B*S, hkv*256] are the outputs of pt_qknorm_rope_fwd; V is read in place from the
- * fused activation qkv [B*S, (hq+2hkv)*256].  keyvalid: optional u8 [B,S] (0 = padded key); kvbits_ws: device
- * workspace of B*ceil(S/64) u64 (required with keyvalid).  window 0 = causal only.  hq/hkv a power of two.
+ * fused activation qkv [B*S, (hq+2hkv)*256].  kvbits: optional key-padding bit masks from pt_pack_keyvalid
+ * (NULL = every key valid).  window 0 = causal only.  hq/hkv a power of two.
  * Scores and un-normalised probabilities never reach HBM (two passes over the key tiles in TMEM). */
-int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const uint8_t* keyvalid,
-                      void* kvbits_ws, void* P_bf16, void* O_bf16, int B, int S, int hq, int hkv, int hd,
-                      int window, float scale, int ldp, void* stream);
+int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const void* kvbits, void* P_bf16,
+                      void* O_bf16, int B, int S, int hq, int hkv, int hd, int window, float scale, int ldp,
+                      void* stream);
+/* keyvalid u8 [B,S] (0 = padded key, ref:Stage1/projector_trainer.py:205-208) -> u64 [B, ceil(S/64)] bit masks
+ * (bit i of word w = key 64 w + i; keys >= S are 0). */
+int pt_pack_keyvalid(const uint8_t* keyvalid, void* kvbits, int B, int S, void* stream);
 
 /* delta[(b*hq + head)*S + s] = sum_d dO[b,s,head,d] * O[b,s,head,d] over dO, O bf16 [rows = B*S, hq*hd]: the
  * row term sum_k P dP of the softmax backward, for pt_gemm_bf16's PT_ACT_SOFTMAX_BWD epilogue. */

@@ -73,16 +73,13 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* sQ = smem;
-    uint8_t* sK = sQ + kGqBytes;                 // 2 stages
-    uint8_t* sV = sK + 2 * kGkvBytes;            // 2 stages
-    uint8_t* sP = sV + 2 * kGkvBytes;
+    uint8_t* sKV = sQ + kGqBytes;                // ring of 4 K-or-V tiles (pass 0: 4 K tiles in flight)
+    uint8_t* sP = sKV + 4 * kGkvBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kGpBytes);
     uint64_t* q_full = bars;            // TMA -> MMA
     uint64_t* q_empty = bars + 1;       // MMA (commit after the item's last S) -> TMA
-    uint64_t* k_full = bars + 2;        // [2]
-    uint64_t* k_empty = bars + 4;       // [2] commit after S_j
-    uint64_t* v_full = bars + 6;        // [2]
-    uint64_t* v_empty = bars + 8;       // [2] commit after PV_j
+    uint64_t* ld_full = bars + 2;       // [4] TMA -> MMA (K or V tile in ring stage s)
+    uint64_t* ld_empty = bars + 6;      // [4] commit after the MMAs that read stage s
     uint64_t* s_full = bars + 10;       // [2] commit after S_j -> softmax
     uint64_t* s_free = bars + 12;       // [2] softmax (128 arrivals) -> MMA
     uint64_t* p_full = bars + 14;       // softmax (128 arrivals) -> MMA
@@ -93,11 +90,8 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     if (threadIdx.x == 128) {
         ptx::prefetch_tmap(&tmQ); ptx::prefetch_tmap(&tmK); ptx::prefetch_tmap(&tmV);
         ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
-        for (int s = 0; s < 2; ++s) {
-            ptx::mbar_init(&k_full[s], 1); ptx::mbar_init(&k_empty[s], 1);
-            ptx::mbar_init(&v_full[s], 1); ptx::mbar_init(&v_empty[s], 1);
-            ptx::mbar_init(&s_full[s], 1); ptx::mbar_init(&s_free[s], 128);
-        }
+        for (int s = 0; s < 4; ++s) { ptx::mbar_init(&ld_full[s], 1); ptx::mbar_init(&ld_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { ptx::mbar_init(&s_full[s], 1); ptx::mbar_init(&s_free[s], 128); }
         ptx::mbar_init(p_full, 128);
         ptx::mbar_init(pv_done, 1);
         ptx::fence_mbar_init();
@@ -117,7 +111,7 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     if (warp == 5) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            uint32_t n_item = 0, kc = 0, vc = 0;          // running counters -> stage / parity
+            uint32_t n_item = 0, lc = 0;                  // lc = tiles loaded so far -> ring stage / parity
             for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
                 int b, kvh, qb, jlo, nt;
                 gemma_item(p, item, b, kvh, qb, jlo, nt);
@@ -126,28 +120,18 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
                     ptx::tma_load_5d(&tmQ, q_full, sQ + c * (kGqRows * 128), c * 64, 0, qb * p.pos_per_blk, kvh, b);
-                for (int pass = 0; pass < 2; ++pass) {
-                    for (int j = 0; j < nt; ++j) {
-                        const int st = kc & 1;
-                        ptx::mbar_wait(&k_empty[st], ((kc >> 1) & 1) ^ 1);
-                        ptx::mbar_arrive_expect_tx(&k_full[st], kGkvBytes);
+                auto load_tile = [&](const CUtensorMap* tm, int j) {
+                    const int st = lc & 3;
+                    ptx::mbar_wait(&ld_empty[st], ((lc >> 2) & 1) ^ 1);
+                    ptx::mbar_arrive_expect_tx(&ld_full[st], kGkvBytes);
 #pragma unroll
-                        for (int c = 0; c < 4; ++c)
-                            ptx::tma_load_5d(&tmK, &k_full[st], sK + st * kGkvBytes + c * (kGkTile * 128), c * 64,
-                                             (jlo + j) * kGkTile, kvh, b, 0);
-                        ++kc;
-                        if (pass == 1) {
-                            const int sv = vc & 1;
-                            ptx::mbar_wait(&v_empty[sv], ((vc >> 1) & 1) ^ 1);
-                            ptx::mbar_arrive_expect_tx(&v_full[sv], kGkvBytes);
-#pragma unroll
-                            for (int c = 0; c < 4; ++c)
-                                ptx::tma_load_5d(&tmV, &v_full[sv], sV + sv * kGkvBytes + c * (kGkTile * 128), c * 64,
-                                                 (jlo + j) * kGkTile, kvh, b, 0);
-                            ++vc;
-                        }
-                    }
-                }
+                    for (int c = 0; c < 4; ++c)
+                        ptx::tma_load_5d(tm, &ld_full[st], sKV + st * kGkvBytes + c * (kGkTile * 128), c * 64,
+                                         (jlo + j) * kGkTile, kvh, b, 0);
+                    ++lc;
+                };
+                for (int j = 0; j < nt; ++j) load_tile(&tmK, j);                       // pass 0
+                for (int j = 0; j < nt; ++j) { load_tile(&tmK, j); load_tile(&tmV, j); }   // pass 1
             }
         }
     } else if (warp == 4) {
@@ -155,13 +139,13 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         if (lane == 0) {
             const uint32_t idescS = ptx::make_idesc_bf16(kGqRows, kGkTile, 0, 0);
             const uint32_t idescO = ptx::make_idesc_bf16(kGqRows, kGhd, 0, 1);      // B = V, MN-major
-            uint32_t n_item = 0, kc = 0, vc = 0, sc = 0, pc = 0;
-            auto issue_S = [&]() {
-                const int st = kc & 1, sb = sc & 1;
-                ptx::mbar_wait(&k_full[st], (kc >> 1) & 1);
+            uint32_t n_item = 0, base = 0 /* ring index of the item's first tile */, sc = 0, pc = 0;
+            auto issue_S = [&](uint32_t li) {              // li = ring index of the K tile
+                const int st = li & 3, sb = sc & 1;
+                ptx::mbar_wait(&ld_full[st], (li >> 2) & 1);
                 ptx::mbar_wait(&s_free[sb], ((sc >> 1) & 1) ^ 1);
                 ptx::tc_fence_after();
-                const uint32_t qa = ptx::smem_u32(sQ), ka = ptx::smem_u32(sK + st * kGkvBytes);
+                const uint32_t qa = ptx::smem_u32(sQ), ka = ptx::smem_u32(sKV + st * kGkvBytes);
 #pragma unroll
                 for (int k = 0; k < kGhd / 16; ++k) {
                     const uint64_t qdesc = ptx::make_smem_desc_sw128(qa + (k >> 2) * (kGqRows * 128) + (k & 3) * 32, 0, 1024);
@@ -169,26 +153,28 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                     ptx::mma_bf16_ss(tS[sb], qdesc, kdesc, idescS, k != 0);
                 }
                 ptx::mma_commit(&s_full[sb]);
-                ptx::mma_commit(&k_empty[st]);
-                ++kc; ++sc;
+                ptx::mma_commit(&ld_empty[st]);
+                ++sc;
             };
             for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
                 int b, kvh, qb, jlo, nt;
                 gemma_item(p, item, b, kvh, qb, jlo, nt);
                 ptx::mbar_wait(q_full, n_item & 1);
-                for (int j = 0; j < nt; ++j) issue_S();                  // pass 0: statistics
-                issue_S();                                                // pass 1, tile 0
+                for (int j = 0; j < nt; ++j) issue_S(base + j);           // pass 0: statistics
+                const uint32_t b1 = base + nt;                            // pass 1: K_j at b1 + 2j, V_j at b1 + 2j + 1
+                issue_S(b1);
                 if (nt == 1) ptx::mma_commit(q_empty);
                 for (int j = 0; j < nt; ++j) {
                     if (j + 1 < nt) {
-                        issue_S();
+                        issue_S(b1 + 2 * (j + 1));
                         if (j + 2 == nt) ptx::mma_commit(q_empty);        // last S of the item issued: Q is free
                     }
-                    const int sv = vc & 1;
+                    const uint32_t lv = b1 + 2 * j + 1;
+                    const int sv = lv & 3;
                     ptx::mbar_wait(p_full, pc & 1);
-                    ptx::mbar_wait(&v_full[sv], (vc >> 1) & 1);
+                    ptx::mbar_wait(&ld_full[sv], (lv >> 2) & 1);
                     ptx::tc_fence_after();
-                    const uint32_t pa = ptx::smem_u32(sP), va = ptx::smem_u32(sV + sv * kGkvBytes);
+                    const uint32_t pa = ptx::smem_u32(sP), va = ptx::smem_u32(sKV + sv * kGkvBytes);
 #pragma unroll
                     for (int k = 0; k < kGkTile / 16; ++k) {
                         const uint64_t pdesc = ptx::make_smem_desc_sw128(pa + k * 32, 0, 1024);
@@ -196,9 +182,10 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                         ptx::mma_bf16_ss(tO, pdesc, vdesc, idescO, (j | k) != 0);
                     }
                     ptx::mma_commit(pv_done);
-                    ptx::mma_commit(&v_empty[sv]);
-                    ++vc; ++pc;
+                    ptx::mma_commit(&ld_empty[sv]);
+                    ++pc;
                 }
+                base += 3 * nt;
             }
         }
     } else {
@@ -218,9 +205,10 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             const unsigned long long* kvw = p.kvbits ? p.kvbits + static_cast<long long>(b) * p.kvwords : nullptr;
 
             // visibility mask of the 64 keys of tile j for this row
-            auto tile_mask = [&](int j) -> unsigned long long {
+            // (the key-padding word is fetched by the caller BEFORE it waits for the S tile: an L2-latency load
+            //  right in front of its first use was the top stall of this kernel)
+            auto tile_mask = [&](int j, unsigned long long m) -> unsigned long long {
                 const int k0 = (jlo + j) * kGkTile;
-                unsigned long long m = kvw ? kvw[jlo + j] : ~0ull;
                 const int hi = k_hi - k0, lo = k_lo - k0;            // visible local indices: lo <= i <= hi
                 if (hi < 0 || lo > 63) return 0ull;
                 if (hi < 63) m &= (2ull << hi) - 1ull;
@@ -242,9 +230,10 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             // ---- pass 0: row max and row sum over the band
             float m_run = -INFINITY, l_run = 0.f;
             for (int j = 0; j < nt; ++j) {
+                const unsigned long long kw = kvw ? __ldg(kvw + jlo + j) : ~0ull;
                 uint32_t v[2][32];
                 load_S(v);
-                const unsigned long long mask = tile_mask(j);
+                const unsigned long long mask = tile_mask(j, kw);
                 if (mask == 0ull) continue;
                 float mxs[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
@@ -272,9 +261,10 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             // ---- pass 1: normalised probabilities -> global P and smem, O += P V
             __nv_bfloat16* prow_g = p.P + ((static_cast<long long>(b) * p.hq + head) * p.S + (live ? s : 0)) * p.ldp;
             for (int j = 0; j < nt; ++j) {
+                const unsigned long long kw = kvw ? __ldg(kvw + jlo + j) : ~0ull;
                 uint32_t v[2][32];
                 load_S(v);
-                const unsigned long long mask = tile_mask(j);
+                const unsigned long long mask = tile_mask(j, kw);
                 uint32_t pk[32];
 #pragma unroll
                 for (int c = 0; c < 2; ++c)
@@ -287,14 +277,6 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                         if (!((mask >> (i0 + 1)) & 1ull)) e1 = 0.f;
                         pk[c * 16 + i] = pack_bf16(e0, e1);
                     }
-                if (live) {
-                    const int k0 = (jlo + j) * kGkTile;
-#pragma unroll
-                    for (int q = 0; q < 8; ++q)
-                        if (k0 + q * 8 < p.ldp)
-                            *reinterpret_cast<uint4*>(prow_g + k0 + q * 8) =
-                                make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-                }
                 // the single P buffer is free once the previous tile's PV has retired
                 if (j > 0) { ptx::mbar_wait(pv_done, pc & 1); ++pc; }
 #pragma unroll
@@ -303,6 +285,15 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(p_full);
+                // the copy of P for the backward goes out after the hand-off (off the MMA's critical path)
+                if (live) {
+                    const int k0 = (jlo + j) * kGkTile;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        if (k0 + q * 8 < p.ldp)
+                            *reinterpret_cast<uint4*>(prow_g + k0 + q * 8) =
+                                make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                }
             }
             // ---- epilogue: O -> bf16 -> global
             ptx::mbar_wait(pv_done, pc & 1); ++pc;
@@ -340,8 +331,17 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 
 using namespace pt;
 
-extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const uint8_t* keyvalid,
-                                 void* kvbits_ws, void* P_bf16, void* O_bf16, int B, int S, int hq, int hkv, int hd,
+extern "C" int pt_pack_keyvalid(const uint8_t* keyvalid, void* kvbits, int B, int S, void* stream) {
+    PT_REQUIRE(keyvalid && kvbits && B > 0 && S > 0, "pt_pack_keyvalid: bad arguments");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    const int words = (S + 63) / 64, n = B * words;
+    pack_keyvalid_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        keyvalid, static_cast<unsigned long long*>(kvbits), B, S, words);
+    return check_launch("pack_keyvalid");
+}
+
+extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const void* kvbits,
+                                 void* P_bf16, void* O_bf16, int B, int S, int hq, int hkv, int hd,
                                  int window, float scale, int ldp, void* stream) {
     PT_REQUIRE(q_rot && k_rot && qkv && P_bf16 && O_bf16, "pt_attn_gemma_fwd: null pointer");
     PT_REQUIRE(hd == kGhd, "pt_attn_gemma_fwd: head_dim must be 256 (got %d)", hd);
@@ -349,7 +349,6 @@ extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const voi
     const int G = hq / hkv;
     PT_REQUIRE(G <= 128 && (G & (G - 1)) == 0, "pt_attn_gemma_fwd: hq / hkv must be a power of two <= 128 (got %d)", G);
     PT_REQUIRE(ldp >= S && ldp % 8 == 0, "pt_attn_gemma_fwd: ldp must be >= S and a multiple of 8");
-    PT_REQUIRE(keyvalid == nullptr || kvbits_ws != nullptr, "pt_attn_gemma_fwd: keyvalid needs the bit-mask workspace");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int QKV = (hq + 2 * hkv) * hd;
@@ -396,13 +395,7 @@ extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const voi
     p.ldp = ldp;
     p.scale_log2e = scale * 1.4426950408889634f;
     p.kvwords = (S + 63) / 64;
-    p.kvbits = nullptr;
-    if (keyvalid) {
-        const int n = B * p.kvwords;
-        pack_keyvalid_kernel<<<(n + 127) / 128, 128, 0, st>>>(keyvalid, static_cast<unsigned long long*>(kvbits_ws), B, S,
-                                                               p.kvwords);
-        p.kvbits = static_cast<const unsigned long long*>(kvbits_ws);
-    }
+    p.kvbits = static_cast<const unsigned long long*>(kvbits);
     p.P = static_cast<__nv_bfloat16*>(P_bf16);
     p.O = static_cast<__nv_bfloat16*>(O_bf16);
     const long long items = static_cast<long long>(B) * hkv * p.nqb;

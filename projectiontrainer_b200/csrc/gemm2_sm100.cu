@@ -128,7 +128,7 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint32_t stg,
 // GeGLU backward fused into the down-projection input gradient: the accumulator chunk is d_act; the saved
 // pre-activations (gate at GU, up at GU + ff) are read in the row-contiguous second-phase layout and the two
 // halves of d_gu are written at C and C + ff:  d_gate = d_act * up * gelu'(gate),  d_up = d_act * gelu(gate).
-// d_act is rounded to bf16 first (what the unfused path stores between the GEMM and geglu_bwd).
+// (d_act stays in f32: the unfused path rounds it to bf16 between the GEMM and geglu_bwd.)
 struct EpiGbwd {
     uint8_t* C;           // d_gu, byte address of (row 0 of the slab, gate column col0)
     const uint8_t* GU;    // gu, same position
@@ -160,7 +160,7 @@ __device__ __forceinline__ void epi_chunk_gbwd(const uint32_t (&v)[32], uint32_t
         const int r = it * 4 + rsub;
         const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
         const bool ok = col_ok && r >= o.row_lo && r < o.rows_valid;
-        const float d[4] = {round_bf16(a.x), round_bf16(a.y), round_bf16(a.z), round_bf16(a.w)};
+        const float d[4] = {a.x, a.y, a.z, a.w};
         const float g[4] = {bf16_lo(gq[it].x), bf16_hi(gq[it].x), bf16_lo(gq[it].y), bf16_hi(gq[it].y)};
         const float u[4] = {bf16_lo(uq[it].x), bf16_hi(uq[it].x), bf16_lo(uq[it].y), bf16_hi(uq[it].y)};
         float dg[4], du[4];

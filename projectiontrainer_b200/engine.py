@@ -288,7 +288,10 @@ class Stage1Engine:
         sv = []
         a = self.buf("l_a", (M, h), BF16)
         sc = None if self.fuse_attn_fwd else self.buf("l_scores", (B * hq, S, ld), F32)
-        kvbits = self.buf("l_kvbits", (B * ((S + 63) // 64),), torch.int64) if self.fuse_attn_fwd else None
+        kvbits = None
+        if self.fuse_attn_fwd and keyvalid is not None:
+            kvbits = self.buf("l_kvbits", (B * ((S + 63) // 64),), torch.int64)
+            ops.pack_keyvalid(keyvalid.view(B, S), kvbits)
         act = self.buf("l_act", (M, ff), BF16)
         x = x0
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
@@ -315,8 +318,7 @@ class Stage1Engine:
                 cache["v"][li][:, :S].copy_(qkv.view(B, S, QKV)[:, :, (hq + hkv) * hd:])
             win = 0 if full else c.window
             if self.fuse_attn_fwd:
-                ops.attn_gemma_fwd(q_post, k_post, qkv, keyvalid, kvbits, P, attn_o, B, S, hq, hkv, hd, win,
-                                   scale, ld)
+                ops.attn_gemma_fwd(q_post, k_post, qkv, kvbits, P, attn_o, B, S, hq, hkv, hd, win, scale, ld)
             else:
                 self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
                                   (0, hd, S * hkv * hd), sc, B, S, scale, window=win)

@@ -240,10 +240,17 @@ def attn_gemma_fusable(hq: int, hkv: int, hd: int) -> bool:
     return hd == 256 and hq % hkv == 0 and G <= 128 and (G & (G - 1)) == 0
 
 
-def attn_gemma_fwd(q_rot, k_rot, qkv, keyvalid, kvbits_ws, P, O, B, S, hq, hkv, hd, window, scale, ldp):
-    """Fused causal / sliding-window GQA attention forward (hd 256): writes normalised P (band only) and O."""
-    _req_cuda(q_rot, k_rot, qkv, keyvalid, kvbits_ws, P, O)
-    _lib.call("pt_attn_gemma_fwd", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(keyvalid), _ptr(kvbits_ws), _ptr(P),
+def pack_keyvalid(keyvalid, kvbits):
+    """u8 [B,S] key-valid flags -> u64 [B, ceil(S/64)] bit masks for attn_gemma_fwd."""
+    _req_cuda(keyvalid, kvbits)
+    _lib.call("pt_pack_keyvalid", _ptr(keyvalid), _ptr(kvbits), keyvalid.shape[0], keyvalid.shape[1], _stream())
+
+
+def attn_gemma_fwd(q_rot, k_rot, qkv, kvbits, P, O, B, S, hq, hkv, hd, window, scale, ldp):
+    """Fused causal / sliding-window GQA attention forward (hd 256): writes normalised P (band only) and O.
+    kvbits: packed key-padding masks (pack_keyvalid) or None."""
+    _req_cuda(q_rot, k_rot, qkv, kvbits, P, O)
+    _lib.call("pt_attn_gemma_fwd", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(kvbits), _ptr(P),
               _ptr(O), int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), int(ldp), _stream())
 
 

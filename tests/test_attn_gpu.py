@@ -51,7 +51,8 @@ def test_attn_gemma_fwd(cuda_dev, B, S, hq, hkv, W, pad):
     P = torch.zeros(B * hq, S, ld, dtype=torch.bfloat16, device=cuda_dev)
     O = torch.full((B * S, hq * hd), float("nan"), dtype=torch.bfloat16, device=cuda_dev)
     scale = 1.0 / 16
-    ops.attn_gemma_fwd(q, k, qkv, keyvalid, kvbits, P, O, B, S, hq, hkv, hd, W, scale, ld)
+    ops.pack_keyvalid(keyvalid, kvbits)
+    ops.attn_gemma_fwd(q, k, qkv, kvbits, P, O, B, S, hq, hkv, hd, W, scale, ld)
     torch.cuda.synchronize()
     qf = q.float().view(B, S, hq, hd).transpose(1, 2)                                  # [B,hq,S,hd]
     kf = k.float().view(B, S, hkv, hd).transpose(1, 2).repeat_interleave(G, dim=1)

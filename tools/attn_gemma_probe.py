@@ -13,13 +13,14 @@ k = torch.randn(B * S, hkv * hd, device=dev).to(torch.bfloat16)
 qkv = torch.randn(B * S, QKV, device=dev).to(torch.bfloat16)
 kv = torch.ones(B, S, dtype=torch.uint8, device=dev)
 bits = torch.empty(B * 11, dtype=torch.int64, device=dev)
+ops.pack_keyvalid(kv, bits)
 P = torch.zeros(B * hq, S, ld, dtype=torch.bfloat16, device=dev)
 O = torch.empty(B * S, hq * hd, dtype=torch.bfloat16, device=dev)
 for W in (0, 512):
-    for _ in range(3): ops.attn_gemma_fwd(q, k, qkv, kv, bits, P, O, B, S, hq, hkv, hd, W, 1 / 16, ld)
+    for _ in range(3): ops.attn_gemma_fwd(q, k, qkv, bits, P, O, B, S, hq, hkv, hd, W, 1 / 16, ld)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(20): ops.attn_gemma_fwd(q, k, qkv, kv, bits, P, O, B, S, hq, hkv, hd, W, 1 / 16, ld)
+    for _ in range(20): ops.attn_gemma_fwd(q, k, qkv, bits, P, O, B, S, hq, hkv, hd, W, 1 / 16, ld)
     e1.record(); torch.cuda.synchronize()
     print(f"window={W}: {e0.elapsed_time(e1) / 20 * 1e3:.1f} us", flush=True)
