@@ -184,3 +184,41 @@ def test_step_hd256_gqa_window_pads_vs_oracle(cuda_dev, fused, monkeypatch):
     assert abs(loss.item() - ref["loss"]) / ref["loss"] < 1e-2
     for k, gr in eng.proj.grads().items():
         assert _cos(gr.cpu(), ref["grads"][k]) > 0.999, k
+
+
+def test_train_step_graph_replay_and_staged_host_batches_match_eager(cuda_dev):
+    """`train_step` through the CUDA graph with host batches prefetched by `stage_batch` (the e2e path of
+    bench.py and of the trainer's look-ahead loop) follows the same trajectory as eager launches on device
+    batches: three optimizer steps on two alternating batches."""
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    vkw = dict(hidden=64, ff=128, layers=2, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=6, hq=2, hkv=1, hd=256, window=8, q_scalar=256.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    batches = []
+    for seed in (11, 12):
+        px, ids, lab = O.synthetic_batch(2, 10, ovc, olc, seed=seed, left_pad=True)
+        batches.append({"pixel_values": px, "token_ids": ids, "labels": lab})
+
+    def run(use_graph, staged):
+        eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                             E.ProjectorState(P, cuda_dev), cuda_dev)
+        eng.use_graph = use_graph
+        losses = []
+        for i in range(4):
+            b = batches[i & 1]
+            if staged:
+                b = eng.stage_batch({k: v.pin_memory() for k, v in b.items()})
+            else:
+                b = {k: v.to(cuda_dev) for k, v in b.items()}
+            losses.append(float(eng.train_step(b, 1e-3, pad_id=olc.pad_id).item()))
+        torch.cuda.synchronize()
+        return losses, eng.proj.flat.clone()
+
+    l0, p0 = run(False, False)
+    l1, p1 = run(True, True)
+    assert np.allclose(l0, l1, rtol=1e-5, atol=1e-6), (l0, l1)
+    assert l0[2] < l0[0]                                   # the same batch, two optimizer steps later
+    assert _cos(p0.cpu(), p1.cpu()) > 1 - 1e-6

@@ -48,3 +48,23 @@ e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / (a.decode - 1)
 print(json.dumps({"config": "cached decode step after that prefill, B=64", "ms_per_token_step": ms,
                   "tokens_per_s": B / ms * 1e3}), flush=True)
+
+# ---- BASELINE.json configs[3]: Gemma3-4B text decoder (h 2560, ff 10240, L 34, 8/4 heads x 256, window 1024,
+# linear-scaled global RoPE), MLP(1024 -> 10240 -> 2560), T=256, B=16 per GPU: one full training step
+del eng
+torch.cuda.empty_cache()
+from projectiontrainer_b200.config import GEMMA3_4B
+eng = build_engine(SIGLIP_L, GEMMA3_4B, dev, seed=0)
+B, T = 16, 256
+px = torch.rand(B, 3, 384, 384, generator=g, device=dev) * 2 - 1
+ids = torch.randint(3, GEMMA3_4B.vocab, (B, T), generator=g, device=dev); ids[:, 0] = 2
+batch = {"pixel_values": px, "token_ids": ids, "labels": ids.clone()}
+losses = []
+def step4():
+    losses.append(eng.train_step(batch, 1e-4, pad_id=GEMMA3_4B.pad_id))
+ms = timed(step4, 3)
+fl4 = stage1_flops_per_image(SIGLIP_L, GEMMA3_4B, T)["train"]
+print(json.dumps({"config": "configs[3] Stage-1 step SigLIP-L + MLP(1024->2560) + Gemma3-4B text, T=256, B=16, 1 GPU",
+                  "ms_per_step": ms, "images_per_s": B / ms * 1e3, "step_tflops": B * fl4 / ms / 1e9,
+                  "first_loss": float(losses[0]), "last_loss": float(losses[-1]),
+                  "mem_gb": torch.cuda.max_memory_allocated() / 1e9}), flush=True)
