@@ -129,6 +129,9 @@ typedef struct {
     /* Second matrix of the PT_ACT_GEGLU / PT_ACT_GEGLU_BWD epilogues (see pt_act); NULL otherwise. */
     void* aux;
     int64_t ld_aux;
+    /* Output-tile width override for the CTA-pair kernel: 0 = cost model, else 64 / 128 / 192 / 256 (a tuning
+     * hint for few-tile problems whose last wave would leave most clusters idle; results do not depend on it). */
+    int32_t bn_hint;
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);

@@ -30,6 +30,7 @@ class GemmArgs(C.Structure):
         ("kg", C.c_int32), ("a_kgs", C.c_int64), ("b_kgs", C.c_int64),
         ("band", C.c_int32), ("band_window", C.c_int32),
         ("aux", C.c_void_p), ("ld_aux", C.c_int64),
+        ("bn_hint", C.c_int32),
     ]
 
 

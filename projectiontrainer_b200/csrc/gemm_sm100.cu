@@ -537,7 +537,13 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     CUtensorMap ta, tb;
     if (g_gemm_impl != 1) {
         // CTA-pair kernel (gemm2_sm100.cu): 256 x bn tiles, one per cluster of two SMs
-        const int bn = geglu ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
+        int bn = geglu ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
+        if (!geglu && a->bn_hint != 0) {
+            PT_REQUIRE(a->bn_hint == 64 || a->bn_hint == 128 || a->bn_hint == 192 || a->bn_hint == 256,
+                       "pt_gemm_bf16: bn_hint must be 0, 64, 128, 192 or 256");
+            PT_REQUIRE(!p.b_mn || (a->bn_hint / 2) % 64 == 0, "pt_gemm_bf16: an MN-major B operand needs bn_hint 128 or 256");
+            bn = a->bn_hint;
+        }
         const long long mt = (a->M + 2 * BM - 1) / (2 * BM), nt = (a->N + bn - 1) / bn;
         PT_REQUIRE(mt * nt * nbatch < (1ll << 31), "pt_gemm_bf16: too many tiles");
         p.raster_n = nt <= mt;

@@ -168,6 +168,7 @@ class Stage1Engine:
         # GeGLU forward / backward fused into the gate||up and down-dgrad GEMM epilogues (needs ff % 128 == 0)
         self.fuse_attn_fwd = ops.attn_gemma_fusable(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_FUSE_ATTN_FWD", "1") != "0"
+        self.bn_hint_dkv = int(os.environ.get("PT_STAGE1_BN_DKV", "0"))     # tile-width hint of the dV / dK GEMMs
         self.fuse_softmax_bwd = os.environ.get("PT_STAGE1_FUSE_SOFTMAX_BWD", "1") != "0"
         self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
 
@@ -431,7 +432,7 @@ class Stage1Engine:
                          Cout=d_qkv, c_off=(hq + hkv) * hd, ldc=QKV, nz=(hkv, B, 1),
                          a_zs=(G * S * ld, hq * S * ld, 0), b_zs=(G * hd, S * hq * hd, 0),
                          c_zs=(hd, S * QKV, 0), kg=G, a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY,
-                         band_window=win)
+                         band_window=win, bn_hint=self.bn_hint_dkv)
             # dQ[b,q,head,:] = dS[b,head] K[b,:,kvh,:]
             ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
                          ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
@@ -441,7 +442,8 @@ class Stage1Engine:
             ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, a_mn=True, B=a["q"], ldb=hq * hd, b_mn=True,
                          Cout=dk, ldc=hkv * hd, nz=(hkv, B, 1), a_zs=(G * S * ld, hq * S * ld, 0),
                          b_zs=(G * hd, S * hq * hd, 0), c_zs=(hd, S * hkv * hd, 0), kg=G,
-                         a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY, band_window=win)
+                         a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY, band_window=win,
+                         bn_hint=self.bn_hint_dkv)
             ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                 hkv, hd, c.eps)
             ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)

@@ -1,5 +1,6 @@
 set -x
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/t18_tests.log
-timeout 400 python tools/bench_aux.py > gpurun_out/t18_aux.json 2> gpurun_out/t18_aux.err
-timeout 300 python bench.py --steps 10 --warmup 3 > gpurun_out/t18_bench.json 2> gpurun_out/t18_bench.err
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/t18_launches.csv python bench.py --profile --steps 1 > gpurun_out/t18_ncu.log 2>&1
+timeout 200 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/t19_smoke.log 2>&1
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t19_bench_a.json 2> gpurun_out/t19_bench_a.err
+PT_STAGE1_BN_DKV=128 timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t19_bench_b.json 2> gpurun_out/t19_bench_b.err
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t19_bench_c.json 2> gpurun_out/t19_bench_c.err
+PT_STAGE1_BN_DKV=128 timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t19_bench_d.json 2> gpurun_out/t19_bench_d.err
