@@ -40,7 +40,12 @@ CASES = {
     "infer_tiny_prompt_mqa": (dict(hidden=64, ff=128, layers=1, heads=4, image=48, patch=16),
                               dict(vocab=304, hidden=48, ff=96, layers=7, hq=4, hkv=1, hd=32, window=5,
                                    q_scalar=32.0), 2, 6, 10),
+    # Stage-2 evaluation prompt (ref:Stage2/trainer.py:594-611): [image][left-padded question], mask 0 on pads
+    "infer_tiny_leftpad_gqa": (dict(hidden=64, ff=128, layers=2, heads=2, image=64, patch=16),
+                               dict(vocab=512, hidden=64, ff=128, layers=6, hq=4, hkv=2, hd=16, window=8,
+                                    q_scalar=16.0, rope_factor_global=8.0), 3, 7, 10),
 }
+LEFT_PADS = {"infer_tiny_leftpad_gqa": [0, 2, 4]}
 
 
 @torch.no_grad()
@@ -63,6 +68,15 @@ def run_case(name: str):
     if Tp:
         inputs_embeds = torch.cat([projected, llm.get_input_embeddings()(ids[:, :Tp])], dim=1)
     attention_mask = torch.ones(inputs_embeds.shape[:2], dtype=torch.long)
+    if name in LEFT_PADS:
+        for b, k in enumerate(LEFT_PADS[name]):
+            ids[b, :k] = lc.pad_id
+        q = ids[:, :Tp]
+        # the Gemma3 branch of the reference indexes the embedding weight and applies embed_scale by hand
+        # (ref:Stage2/trainer.py:543-549); same values as the embedding layer
+        emb = llm.get_input_embeddings()
+        inputs_embeds = torch.cat([projected, emb.weight[q] * emb.embed_scale.clone().detach()], dim=1)
+        attention_mask = torch.cat([torch.ones(projected.shape[:2], dtype=torch.long), (q != lc.pad_id).long()], dim=1)
     prefill_logits = llm(inputs_embeds=inputs_embeds, attention_mask=attention_mask).logits[:, -1, :].float()
     outputs = llm.generate(inputs_embeds=inputs_embeds, attention_mask=attention_mask, max_new_tokens=new,
                            pad_token_id=lc.pad_id, eos_token_id=1, do_sample=False, temperature=None,
@@ -82,5 +96,5 @@ def run_case(name: str):
 if __name__ == "__main__":
     torch.set_num_threads(8)
     torch.manual_seed(0)
-    for n in CASES:
+    for n in ([sys.argv[1]] if len(sys.argv) > 1 else CASES):
         run_case(n)

@@ -214,14 +214,20 @@ def allowed_mask(keyvalid: torch.Tensor, S: int, window: int | None):
     return m[None, :, :] & keyvalid.bool()[:, None, :]         # [B, S, S]
 
 
-def gemma3_hidden(X0, keyvalid, W: dict, cfg: GemmaCfg):
+def gemma3_hidden(X0, keyvalid, W: dict, cfg: GemmaCfg, pos_ids=None):
     """Decoder stack without the final norm (HF:models/gemma3/modeling_gemma3.py:521-583,
-    decoder layer :404-434, attention :346-388, MLP :127-129)."""
+    decoder layer :404-434, attention :346-388, MLP :127-129).  Positions are arange(S) as in a
+    plain forward (F3); `pos_ids` i64 [B, S] gives per-sample positions instead (what `generate`
+    derives from a padded attention mask, HF:generation/utils.py prepare_inputs_for_generation)."""
     B, S, h = X0.shape
     G = cfg.hq // cfg.hkv
     dt = X0.dtype
     cos_l, sin_l = rope_tables(S, cfg.hd, cfg.theta_local, 1.0, dt)
     cos_g, sin_g = rope_tables(S, cfg.hd, cfg.theta_global, cfg.rope_factor_global, dt)
+    if pos_ids is None:
+        cos_l, sin_l, cos_g, sin_g = (t[None] for t in (cos_l, sin_l, cos_g, sin_g))
+    else:
+        cos_l, sin_l, cos_g, sin_g = (t[pos_ids] for t in (cos_l, sin_l, cos_g, sin_g))   # [B, S, hd]
     m_full = allowed_mask(keyvalid, S, None)
     m_slide = allowed_mask(keyvalid, S, cfg.window)
     x = X0
@@ -238,8 +244,8 @@ def gemma3_hidden(X0, keyvalid, W: dict, cfg: GemmaCfg):
         v = v.reshape(B, S, cfg.hkv, cfg.hd)
         q = rms_norm(q, W[p + "q_norm"], cfg.eps)
         k = rms_norm(k, W[p + "k_norm"], cfg.eps)
-        q = q * cos[None, :, None, :] + rotate_half(q) * sin[None, :, None, :]
-        k = k * cos[None, :, None, :] + rotate_half(k) * sin[None, :, None, :]
+        q = q * cos[:, :, None, :] + rotate_half(q) * sin[:, :, None, :]
+        k = k * cos[:, :, None, :] + rotate_half(k) * sin[:, :, None, :]
         q = q.transpose(1, 2)                                     # [B, hq, S, hd]
         k = k.transpose(1, 2).repeat_interleave(G, dim=1)
         v = v.transpose(1, 2).repeat_interleave(G, dim=1)
@@ -294,11 +300,23 @@ def stage1_step(pixels, token_ids, labels, Wv, P, Wl, vcfg: SiglipCfg, lcfg: Gem
 
 
 # --------------------------------------------------------------------------- inference (prefill + greedy decode)
-def last_position_logits(X0, Wl: dict, lcfg: GemmaCfg):
-    """HF Gemma3ForCausalLM.forward on inputs_embeds with an all-ones mask, logits of the last position
-    (HF:models/gemma3/modeling_gemma3.py:649-656) — what `generate` samples the next token from."""
+def generate_positions(attn: torch.Tensor) -> torch.Tensor:
+    """HF:generation/utils.py prepare_inputs_for_generation — inside `generate`, position ids come
+    from the attention mask: cumsum(mask) - 1, masked positions set to 1."""
+    pos = attn.long().cumsum(-1) - 1
+    return pos.masked_fill(attn == 0, 1)
+
+
+def last_position_logits(X0, Wl: dict, lcfg: GemmaCfg, attn=None):
+    """HF Gemma3ForCausalLM.forward on inputs_embeds, logits of the last position
+    (HF:models/gemma3/modeling_gemma3.py:649-656) — what `generate` samples the next token from.
+    `attn` None = all-ones mask (ref:Stage1/inference_stage1.py:170); a padded mask (Stage-2
+    evaluation prompt, ref:Stage2/trainer.py:594-596) also moves the positions as generate does."""
     B, S, _ = X0.shape
-    hidden = gemma3_hidden(X0, torch.ones(B, S, dtype=torch.int64), Wl, lcfg)
+    if attn is None:
+        hidden = gemma3_hidden(X0, torch.ones(B, S, dtype=torch.int64), Wl, lcfg)
+    else:
+        hidden = gemma3_hidden(X0, attn, Wl, lcfg, pos_ids=generate_positions(attn))
     y = rms_norm(hidden[:, -1, :], Wl["final_norm"], lcfg.eps)
     return (y @ Wl["embed"].T).float()
 
@@ -316,7 +334,7 @@ def prefill_inputs(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaCf
 
 @torch.no_grad()
 def greedy_generate(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaCfg, max_new_tokens: int,
-                    eos_id=1, pad_id=0, scale_dtype=None):
+                    eos_id=1, pad_id=0, scale_dtype=None, mask_prompt_pads: bool = False):
     """`generate(inputs_embeds=..., do_sample=False)` (ref:Stage1/inference_stage1.py:176-187) restated
     WITHOUT a KV cache: every step re-runs the full forward over [inputs ; tokens so far].  Returns the
     new tokens i64 [B, n] (pad after eos, early stop when all rows finished) and the last-position
@@ -325,8 +343,12 @@ def greedy_generate(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaC
     B = X.shape[0]
     done = torch.zeros(B, dtype=torch.bool)
     toks, step_logits = [], []
+    attn = None
+    if mask_prompt_pads:       # ref:Stage2/trainer.py:594-596: ones for the image, (id != pad) for the question
+        attn = torch.cat([torch.ones(B, X.shape[1] - prompt_ids.shape[1], dtype=torch.int64),
+                          (prompt_ids != pad_id).long()], dim=1)
     for _ in range(max_new_tokens):
-        lg = last_position_logits(X, Wl, lcfg)
+        lg = last_position_logits(X, Wl, lcfg, attn)
         step_logits.append(lg)
         nxt = lg.argmax(dim=-1)
         nxt = torch.where(done, torch.full_like(nxt, pad_id), nxt)
@@ -335,6 +357,8 @@ def greedy_generate(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaC
         if bool(done.all()):
             break
         X = torch.cat([X, embed_tokens(nxt[:, None], Wl["embed"], lcfg.hidden, scale_dtype).to(X.dtype)], dim=1)
+        if attn is not None:
+            attn = torch.cat([attn, torch.ones(B, 1, dtype=torch.int64)], dim=1)
     return torch.stack(toks, dim=1), torch.stack(step_logits, dim=1)
 
 

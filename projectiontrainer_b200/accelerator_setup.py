@@ -72,6 +72,25 @@ class Stage1Accelerator:
         if self.num_processes > 1:
             dist.barrier()
 
+    def gather_object(self, obj: list) -> list:
+        """`accelerate.utils.gather_object` (ref:Stage2/trainer.py:13, 629): the per-process lists
+        concatenated in rank order."""
+        if self.num_processes == 1:
+            return list(obj)
+        out = [None] * self.num_processes
+        dist.all_gather_object(out, list(obj))
+        return [x for part in out for x in part]
+
+    @property
+    def backward_divisor(self) -> int:
+        """`accelerate.Accelerator.backward(loss)` divides the loss by `gradient_accumulation_steps`
+        before calling `.backward()` (every backend but DeepSpeed).  Both reference trainers have
+        already divided it (Stage1/projector_trainer.py:236, Stage2/trainer.py:419), so the gradients
+        the reference's optimizer sees are those of loss / GA**2; the trainers here ask for the same.
+        (Behaviour of the pinned accelerate==1.6.0 stated from its source as known; the package is
+        not in the build container — DESIGN.md lists it under "verify".)"""
+        return self.gradient_accumulation_steps
+
     # ---- autograd-facing members (used when MLPProjector is driven through torch autograd)
     def backward(self, loss):
         loss.backward()

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import math
 import os
+from collections import OrderedDict
 
 import torch
 
@@ -153,12 +154,21 @@ class Stage1Engine:
     """One data-parallel rank of the Stage-1 step on one B200."""
 
     def __init__(self, vis: PackedSiglip, llm: PackedGemma, proj: ProjectorState, device,
-                 grad_accum: int = 1):
+                 grad_accum: int = 1, loss_divisor: float | None = None):
         self.vis, self.llm, self.proj = vis, llm, proj
         self.vcfg, self.lcfg = vis.cfg, llm.cfg
         self.device = device
-        self.grad_accum = grad_accum
+        # gradients are those of loss / loss_divisor (the reference divides by gradient_accumulation_steps
+        # before backward: Stage1/projector_trainer.py:236, Stage2/trainer.py:419)
+        self.loss_divisor = float(grad_accum if loss_divisor is None else loss_divisor)
         self._ws: dict = {}
+        # one workspace + graph set per batch geometry (Stage 2 pads per batch: ref:Stage2/trainer.py:18-61);
+        # least-recently-used geometries are dropped beyond max_geometries
+        self._arenas: OrderedDict = OrderedDict()
+        self._geometry = ("default",)
+        self.max_geometries = int(os.environ.get("PT_STAGE1_MAX_GEOMETRIES", "6"))
+        self._acc_grad = None           # gradient accumulated over micro-batches that did not step
+        self._acc_pending = False
         self._rope: dict = {}
         self.n_img = self.vcfg.tokens - 1      # ref:projector_trainer.py:173 drops token 0
         self.saved = None
@@ -180,6 +190,24 @@ class Stage1Engine:
             t = (torch.zeros if zero else torch.empty)(shape, dtype=dtype, device=self.device)
             self._ws[key] = t
         return t
+
+    def select_geometry(self, key):
+        """Switch the workspace (and the CUDA graphs captured over it) to the arena of batch geometry
+        `key`.  Buffers are keyed by shape, so without this every new padded length would add a full
+        activation set; here at most `max_geometries` sets stay alive, oldest first out."""
+        if key == self._geometry:
+            return
+        self._arenas[self._geometry] = (self._ws, self._graphs)
+        if key in self._arenas:
+            self._ws, self._graphs = self._arenas.pop(key)
+        else:
+            self._ws, self._graphs = {}, {}
+            while len(self._arenas) >= max(1, self.max_geometries):
+                _, (ws, graphs) = self._arenas.popitem(last=False)
+                graphs.clear()
+                ws.clear()
+        self._geometry = key
+        self.saved = None
 
     def rope(self, S, full: bool):
         key = (S, full)
@@ -276,11 +304,13 @@ class Stage1Engine:
                      band_window=window, **epilogue)
 
     # ------------------------------------------------------------------ LLM forward + loss
-    def _llm_stack(self, x0: torch.Tensor, keyvalid, B: int, S: int, save: bool, cache=None):
+    def _llm_stack(self, x0: torch.Tensor, keyvalid, B: int, S: int, save: bool, cache=None, pos_ids=None):
         """Decoder stack over x0 f32 [B*S, h] (HF:models/gemma3/modeling_gemma3.py:404-434 per layer).
         Returns the final residual stream (before the final norm) and, with save=True, the per-layer
         activations the input-gradient backward needs.  With `cache` (prefill) the rotated keys and
-        the values of every layer are also stored into the KV cache at positions 0..S-1."""
+        the values of every layer are also stored into the KV cache at positions 0..S-1.  Positions
+        are arange(S) (F3) unless `pos_ids` i64 [B, S] gives them per sample (generate under a padded
+        prompt mask): the RoPE rows are then gathered once per table and looked up per (sample, position)."""
         c, Lm = self.lcfg, self.llm
         h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
         M = B * S
@@ -296,10 +326,15 @@ class Stage1Engine:
         act = self.buf("l_act", (M, ff), BF16)
         x = x0
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
+        rope_rows, tabs = S, {f: self.rope(S, f) for f in (True, False)}
+        if pos_ids is not None:
+            flat = pos_ids.reshape(-1)
+            tabs = {f: (t[0].index_select(0, flat), t[1].index_select(0, flat)) for f, t in tabs.items()}
+            rope_rows = M
         for li, L in enumerate(Lm.layers):
             tag = f"l{li}_" if save else "l_"
             full = c.is_full(li)
-            cos_t, sin_t = self.rope(S, full)
+            cos_t, sin_t = tabs[full]
             qkv = self.buf(tag + "qkv", (M, QKV), BF16)
             q_post = self.buf(tag + "q", (M, hq * hd), BF16)
             k_post = self.buf(tag + "k", (M, hkv * hd), BF16)
@@ -312,7 +347,7 @@ class Stage1Engine:
             y_mlp = self.buf(tag + "ym", (M, h), BF16)
             x2 = self.buf(tag + ("x2" if save else f"x2_{li & 1}"), (M, h), F32)
             ops.linear(a, L["qkv_w"], out=qkv)
-            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, S, hq,
+            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, rope_rows, hq,
                                 hkv, hd, c.eps)
             if cache is not None:      # KV-cache fill: device-to-device copies (plumbing, no arithmetic)
                 cache["k"][li][:, :S].copy_(k_post.view(B, S, hkv * hd))
@@ -348,26 +383,29 @@ class Stage1Engine:
         return x, sv
 
     def llm_forward_loss(self, x0: torch.Tensor, keyvalid: torch.Tensor, targets: torch.Tensor,
-                         B: int, S: int, T: int, save: bool = True) -> torch.Tensor:
+                         B: int, S: int, T: int, save: bool = True, lab0: int | None = None) -> torch.Tensor:
         """x0 f32 [B*S, h] spliced embeddings -> device scalar loss; leaves dlogits in place and the
-        activations the input-gradient backward needs in self.saved."""
+        activations the input-gradient backward needs in self.saved.  Only the T positions
+        lab0 .. lab0+T-1 of every sample go through the final norm and the LM head: the ones whose
+        shifted target can be a label (Stage 1: the caption, lab0 = S-T-1; Stage 2: the answer)."""
+        lab0 = S - T - 1 if lab0 is None else lab0
         c, Lm = self.lcfg, self.llm
         h = c.hidden
         x, sv = self._llm_stack(x0, keyvalid, B, S, save)
-        # final norm only on rows that can carry a label: positions n_img-1 .. S-2 of every sample
+        # final norm only on rows that can carry a label: positions lab0 .. lab0+T-1 of every sample
         R = B * T
         yf = self.buf("l_yf", (R, h), BF16)
-        ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(T, S, S - T - 1))
+        ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(T, S, lab0))
         logits = self.buf("l_logits", (R, _pad8(c.vocab)), BF16)[:, :c.vocab]    # row stride padded to 16 B
         ops.linear(yf, Lm.embed, out=logits)
         tgt = self.buf("l_tgt", (R,), torch.int32)
-        # targets[b, n_img-1+t] for t in 0..T-1 -> compact [B*T] (int copy: plumbing, not arithmetic)
-        tgt.view(B, T).copy_(targets.view(B, S)[:, S - T - 1:S - 1])
+        # targets[b, lab0+t] for t in 0..T-1 -> compact [B*T] (int copy: plumbing, not arithmetic)
+        tgt.view(B, T).copy_(targets.view(B, S)[:, lab0:lab0 + T])
         lse = self.buf("l_lse", (R,), F32)
         acc2 = self.buf("l_acc2", (2,), F32)
         loss = self.buf("l_loss", (1,), F32)
-        ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.grad_accum)
-        self.saved = dict(layers=sv, x_final=x, logits=logits, B=B, S=S, T=T) if save else None
+        ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.loss_divisor)
+        self.saved = dict(layers=sv, x_final=x, logits=logits, B=B, S=S, T=T, lab0=lab0) if save else None
         return loss
 
     # ------------------------------------------------------------------ LLM backward (input grads only)
@@ -383,7 +421,7 @@ class Stage1Engine:
         ops.linear_dgrad(s["logits"], Lm.embed, out=d_yf)          # dlogits @ E
         dx = self.buf("b_dx", (M, h), F32)
         dx.zero_()
-        grp = (T, S, S - T - 1)
+        grp = (T, S, s["lab0"])
         ops.rmsnorm_bwd(d_yf, s["x_final"], Lm.final_norm, dx, c.eps, rows=R, u_group=grp, dst_group=grp)
         d_y = self.buf("b_dy", (M, h), BF16)
         d_act = self.buf("b_dact", (M, ff), BF16)
@@ -500,18 +538,29 @@ class Stage1Engine:
                          x0, attn_mask, lm_labels, keyvalid, targets)
         return attn_mask, lm_labels, keyvalid, targets
 
+    def _span(self, T: int, label_span):
+        """(first position whose shifted target can be a label, number of such positions) in sequence
+        coordinates, from `label_span` = (offset of the first labelled text token, count) in text
+        coordinates; None = the whole text (Stage 1)."""
+        off, cnt = (0, T) if label_span is None else (int(label_span[0]), int(label_span[1]))
+        if off < 0 or cnt <= 0 or off + cnt > T:
+            raise ValueError(f"label_span {label_span} does not fit a text of {T} tokens")
+        return self.n_img + off - 1, cnt
+
     def forward_backward(self, pixels: torch.Tensor, token_ids: torch.Tensor, labels: torch.Tensor,
-                         pad_id=0) -> torch.Tensor:
-        """Steps 1-8 of the reference loop (ref:Stage1/projector_trainer.py:157-237): returns the
-        device-resident scalar loss; projector gradients (of loss / grad_accum) land in proj.grad."""
+                         pad_id=0, label_span=None) -> torch.Tensor:
+        """Steps 1-8 of the reference loop (ref:Stage1/projector_trainer.py:157-237; with `label_span`
+        the Stage-2 frozen-LLM step ref:Stage2/trainer.py:311-420): returns the device-resident scalar
+        loss; projector gradients (of loss / loss_divisor) land in proj.grad."""
         B, T = token_ids.shape
         S = self.n_img + T
+        lab0, Tl = self._span(T, label_span)
         h = self.lcfg.hidden
         patch = self.vision_forward(pixels)
         x0 = self.buf("x0", (B * S, h), F32)
         Z, Hm = self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * h)
         _, _, keyvalid, targets = self.splice(token_ids, labels, x0, pad_id)
-        loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, T)
+        loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, Tl, lab0=lab0)
         dx = self.llm_backward()
         self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
@@ -540,7 +589,8 @@ class Stage1Engine:
             slot["ids"].copy_(ti, non_blocking=True)
             slot["lab"].copy_(lb, non_blocking=True)
             slot["event"].record()
-        return {"pixel_values": pv, "token_ids": ti, "labels": lb, "_staged": slot}
+        return {"pixel_values": pv, "token_ids": ti, "labels": lb, "_staged": slot,
+                "label_span": batch.get("label_span")}
 
     def _graphed_forward_backward(self, batch: dict, pad_id) -> torch.Tensor:
         """forward_backward through a CUDA graph keyed on the batch geometry: inputs are copied into
@@ -548,7 +598,9 @@ class Stage1Engine:
         second captures, later calls replay.  The all-reduce and the optimizer stay outside the graph
         (lr and the step count change every step)."""
         pv, ti, lb = batch["pixel_values"], batch["token_ids"], batch["labels"]
-        key = (tuple(pv.shape), tuple(ti.shape), pad_id)
+        span = batch.get("label_span")
+        span = None if span is None else (int(span[0]), int(span[1]))
+        key = (tuple(pv.shape), tuple(ti.shape), pad_id, span, self.loss_divisor)
         g = self._graphs.get(key)
         if g is None:
             g = dict(px=torch.empty(pv.shape, dtype=F32, device=self.device),
@@ -569,13 +621,13 @@ class Stage1Engine:
         g["calls"] += 1
         if g["calls"] == 1:
             n0 = _lib.launch_count
-            loss = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id)
+            loss = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id, span)
             g["launches"] = _lib.launch_count - n0
             return loss
         if g["graph"] is None:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                g["loss"] = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id)
+                g["loss"] = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id, span)
             g["graph"] = graph
         g["graph"].replay()
         _lib.launch_count += g["launches"]          # kernels inside the replayed graph
@@ -590,25 +642,26 @@ class Stage1Engine:
         lab = batch["labels"].to(dev, non_blocking=True)
         B, T = ids.shape
         S = self.n_img + T
+        self.select_geometry((B, T))
+        lab0, Tl = self._span(T, batch.get("label_span"))
         patch = self.vision_forward(px)
         x0 = self.buf("x0", (B * S, self.lcfg.hidden), F32)
         self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * self.lcfg.hidden)
         _, _, keyvalid, targets = self.splice(ids, lab, x0, pad_id)
-        ga, self.grad_accum = self.grad_accum, 1
-        try:
-            loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, T)
-        finally:
-            self.grad_accum = ga
+        loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, Tl, save=False, lab0=lab0)
         return loss.clone()
 
     # ------------------------------------------------------------------ inference: prefill + decode
     @torch.no_grad()
     def prefill(self, pixels: torch.Tensor, prompt_ids: torch.Tensor | None = None,
-                max_new_tokens: int = 0) -> torch.Tensor:
+                max_new_tokens: int = 0, prompt_pad_id: int | None = None) -> torch.Tensor:
         """ref:Stage1/inference_stage1.py:150-175 (and projector_trainer.py:374-392): vision forward,
         `[:, 1:, :]`, projector, optional prompt embeddings appended, all-ones attention mask, frozen
         Gemma3 forward; the LM head runs on the LAST position only.  Returns f32 logits [B, V] and
-        leaves a KV cache sized for `max_new_tokens` more positions in self.cache."""
+        leaves a KV cache sized for `max_new_tokens` more positions in self.cache.  With
+        `prompt_pad_id` (Stage-2 evaluation, ref:Stage2/trainer.py:594-611: `[image][left-padded
+        question]`) prompt pads are masked as keys for the prefill and every decode step, and
+        positions follow HF generate (cumsum of the mask - 1)."""
         c = self.lcfg
         dev = self.device
         px = pixels.to(dev, dtype=F32, non_blocking=True)
@@ -619,9 +672,15 @@ class Stage1Engine:
         patch = self.vision_forward(px)
         x0 = self.buf("x0", (B * S, h), F32)
         self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * h, save=False)
+        keyvalid = pos_ids = None
         if T:
             ids = prompt_ids.to(dev, non_blocking=True)
-            self.splice(ids, ids, x0, None)          # pad_id None: every key valid (all-ones mask)
+            # pad_id None: every key valid (all-ones mask, ref:Stage1/inference_stage1.py:170)
+            _, _, kv, _ = self.splice(ids, ids, x0, prompt_pad_id)
+            if prompt_pad_id is not None:
+                keyvalid = kv
+                vm = kv.view(B, S).long()
+                pos_ids = (vm.cumsum(1) - 1).masked_fill_(vm == 0, 1)   # index plumbing (HF generate positions)
         Smax = _pad8(S + max_new_tokens)
         kvd = c.hkv * c.hd
         key = (B, Smax)
@@ -629,8 +688,12 @@ class Stage1Engine:
             self.cache = dict(k=[torch.zeros(B, Smax, kvd, dtype=BF16, device=dev) for _ in range(c.layers)],
                               v=[torch.zeros(B, Smax, kvd, dtype=BF16, device=dev) for _ in range(c.layers)])
             self._cache_key = key
-        self.cache.update(pos=S, B=B, Smax=Smax)
-        x, _ = self._llm_stack(x0, None, B, S, save=False, cache=self.cache)
+        self.cache.update(pos=S, B=B, Smax=Smax, valid=None, next_pos=None)
+        if keyvalid is not None:
+            valid = torch.ones(B, Smax, dtype=torch.uint8, device=dev)
+            valid[:, :S].copy_(keyvalid.view(B, S))
+            self.cache.update(valid=valid, next_pos=keyvalid.view(B, S).long().sum(1))
+        x, _ = self._llm_stack(x0, keyvalid, B, S, save=False, cache=self.cache, pos_ids=pos_ids)
         return self._last_logits(x, B, S)
 
     def _last_logits(self, x: torch.Tensor, B: int, S: int) -> torch.Tensor:
@@ -672,12 +735,20 @@ class Stage1Engine:
         gu = self.buf("d_gu", (B, 2 * ff), BF16)
         act = self.buf("d_act", (B, ff), BF16)
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
+        valid, next_pos = kc.get("valid"), kc.get("next_pos")
+        rope_rows, tabs = 1, {}
+        for f in (True, False):
+            cos_t, sin_t = self.rope(Smax, f)
+            if next_pos is None:
+                tabs[f] = (cos_t[pos:pos + 1], sin_t[pos:pos + 1])
+            else:       # per-sample positions (padded prompt): one table row per sample
+                tabs[f] = (cos_t.index_select(0, next_pos), sin_t.index_select(0, next_pos))
+                rope_rows = B
         for li, L in enumerate(Lm.layers):
             full = c.is_full(li)
-            cos_t, sin_t = self.rope(Smax, full)
             ops.linear(a, L["qkv_w"], out=qkv)
-            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t[pos:pos + 1], sin_t[pos:pos + 1],
-                                q_post, k_post, 1, hq, hkv, hd, c.eps)
+            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], tabs[full][0], tabs[full][1],
+                                q_post, k_post, rope_rows, hq, hkv, hd, c.eps)
             K, V = kc["k"][li], kc["v"][li]
             K[:, pos].copy_(k_post)
             V[:, pos].copy_(qkv[:, (hq + hkv) * hd:])
@@ -688,7 +759,8 @@ class Stage1Engine:
             ops.gemm_raw(M=G, N=n, K=hd, A=q_post, lda=hd, B=K, b_off=lo * kvd, ldb=kvd, Cout=sc, ldc=ld,
                          nz=(hkv, B, 1), a_zs=(G * hd, hq * hd, 0), b_zs=(hd, Smax * kvd, 0),
                          c_zs=(G * ld, hq * ld, 0), alpha=scale)
-            ops.softmax_fwd(sc, P, None, B * hq, 1, n, ld, hq, 0, 0)
+            kvm = None if valid is None else valid[:, lo:pos + 1].contiguous()
+            ops.softmax_fwd(sc, P, kvm, B * hq, 1, n, ld, hq, 0, 0)
             ops.gemm_raw(M=G, N=hd, K=n, A=P, lda=ld, B=V, b_off=lo * kvd, ldb=kvd, b_mn=True,
                          Cout=attn_o, ldc=hd, nz=(hkv, B, 1), a_zs=(G * ld, hq * ld, 0),
                          b_zs=(hd, Smax * kvd, 0), c_zs=(G * hd, hq * hd, 0))
@@ -705,6 +777,8 @@ class Stage1Engine:
                                      None if last else Lm.layers[li + 1]["in_norm"],
                                      None if last else a, c.eps)
         kc["pos"] = pos + 1
+        if next_pos is not None:
+            kc["next_pos"] = next_pos + 1
         return self._last_logits(x, B, 1)
 
     @torch.no_grad()
@@ -712,14 +786,14 @@ class Stage1Engine:
                  max_new_tokens: int = 64, do_sample: bool = False, temperature: float = 1.0,
                  top_p: float = 1.0, top_k: int = 50, repetition_penalty: float = 1.0,
                  pad_token_id: int | None = 0, eos_token_id: int | None = 1,
-                 generator: torch.Generator | None = None) -> torch.Tensor:
+                 generator: torch.Generator | None = None, prompt_pad_id: int | None = None) -> torch.Tensor:
         """`language_model.generate(inputs_embeds=projected, attention_mask=ones, ...)` of
         ref:Stage1/inference_stage1.py:176-187 / projector_trainer.py:386-393: returns the NEW tokens
         only, i64 [B, n<=max_new_tokens]; finished rows are filled with pad_token_id; stops early when
         every row has produced eos.  Token selection (HF logits processors: repetition penalty ->
         temperature -> top-k -> top-p -> multinomial, or argmax) is control logic on a [B, V] tensor
         and uses torch ops; all model arithmetic runs in the sm_100a kernels."""
-        logits = self.prefill(pixels, prompt_ids, max_new_tokens=max_new_tokens)
+        logits = self.prefill(pixels, prompt_ids, max_new_tokens=max_new_tokens, prompt_pad_id=prompt_pad_id)
         B = logits.shape[0]
         dev = self.device
         out = torch.full((B, max_new_tokens), pad_token_id if pad_token_id is not None else 0,
@@ -760,29 +834,50 @@ class Stage1Engine:
         return out[:, :n]
 
     def train_step(self, batch: dict, lr: float, *, pad_id=0, weight_decay: float = 0.01,
-                   allreduce=None, world_size: int = 1) -> torch.Tensor:
-        """One optimizer step from a (host or device) batch dict with the reference's keys
-        `pixel_values`, `token_ids`, `labels` (ref:Stage1/train_projection_stage1.py:114-118).
-        Host tensors are copied in (non_blocking from pinned memory).  `allreduce(flat_grad)` sums
-        the flat gradient over ranks (NCCL); the 1/world mean is folded into the optimizer kernel.
-        Returns the device scalar loss (no host sync here)."""
+                   allreduce=None, world_size: int = 1, max_norm: float = 5.0,
+                   sync_gradients: bool = True) -> torch.Tensor:
+        """One micro-batch (and, when `sync_gradients`, one optimizer step) from a host or device batch
+        dict with the reference's keys `pixel_values`, `token_ids`, `labels`
+        (ref:Stage1/train_projection_stage1.py:114-118) and optionally `label_span` (Stage 2, see
+        forward_backward).  Host tensors are copied in (non_blocking from pinned memory).
+        `sync_gradients=False` is a micro-batch inside `accelerator.accumulate()`
+        (ref:Stage2/trainer.py:306, 422): its gradient is added to the accumulator and neither the
+        all-reduce nor the optimizer run.  `allreduce(flat_grad)` sums the flat gradient over ranks
+        (NCCL); the 1/world mean is folded into the optimizer kernel.  Returns the device scalar loss
+        (no host sync here)."""
         dev = self.device
+        self.select_geometry((tuple(batch["pixel_values"].shape), tuple(batch["token_ids"].shape)))
         if self.use_graph:
             loss = self._graphed_forward_backward(batch, pad_id)
         else:
             st = batch.get("_staged")
+            span = batch.get("label_span")
             if st is not None:
                 torch.cuda.current_stream().wait_event(st["event"])
                 batch = {"pixel_values": st["px"], "token_ids": st["ids"], "labels": st["lab"]}
             px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
             ids = batch["token_ids"].to(dev, non_blocking=True)
             lab = batch["labels"].to(dev, non_blocking=True)
-            loss = self.forward_backward(px, ids, lab, pad_id)
+            loss = self.forward_backward(px, ids, lab, pad_id, span)
             if st is not None:
                 st["done"].record()
+        Pj = self.proj
+        if not sync_gradients:
+            # flat f32 axpy over the 22M-entry projector gradient: bookkeeping between micro-batches
+            if self._acc_grad is None:
+                self._acc_grad = torch.zeros_like(Pj.grad)
+            if self._acc_pending:
+                self._acc_grad.add_(Pj.grad)
+            else:
+                self._acc_grad.copy_(Pj.grad)
+            self._acc_pending = True
+            return loss
+        if self._acc_pending:
+            Pj.grad.add_(self._acc_grad)
+            self._acc_pending = False
         if allreduce is not None and world_size > 1:
-            allreduce(self.proj.grad)
-        self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size)
+            allreduce(Pj.grad)
+        self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size, max_norm=max_norm)
         return loss
 
 

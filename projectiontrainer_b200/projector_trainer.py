@@ -113,7 +113,9 @@ class ProjectionTrainerStage1:
             proj = ProjectorState.from_module(projection_layer, self.device)
         else:
             proj = projection_layer
-        self.engine = Stage1Engine(vis, llm, proj, self.device, grad_accum=accelerator.gradient_accumulation_steps)
+        ga = accelerator.gradient_accumulation_steps
+        self.engine = Stage1Engine(vis, llm, proj, self.device,
+                                   loss_divisor=ga * getattr(accelerator, "backward_divisor", ga))
         pad = getattr(tokenizer, "pad_token_id", None)
         self.pad_id = pad
         logger.info("Froze vision encoder and language model parameters (packed, no gradients are formed).")

@@ -1,0 +1,276 @@
+"""Drop-in for ref:Stage2/trainer.py, FROZEN-LLM VARIANT (first half): same
+`vqa_collate_fn`, same `VQATrainerStage2` constructor signature, `.train()`, `.evaluate()`, `.save_model()`,
+artefact names and logged metric names.  Vision encoder and LLM stay frozen, the projector trains
+(`--unfreeze_projection_layer`; no `--enable_qlora`, no `--unfreeze_llm`, no `--train_ve_first_epoch`): the
+micro-batch body (ref lines 311-420: vision forward, `[:, 1:, :]`, projector, question/answer embedding,
+`[image][question][answer]` concatenation, mask, answer-only labels, fp32 shifted CE, backward) runs in
+`engine.Stage1Engine` on the sm_100a kernels with the answer rows as its label span; this file is the host
+loop: dynamic per-batch padding, `accelerator.accumulate()` bookkeeping, clip 1.0, AdamW, cosine schedule.
+
+Not built (raises NotImplementedError, never falls back): trainable LLM weights — LoRA/QLoRA adapters or
+the full LLM need weight-gradient GEMMs through the decoder and a 4-bit base-weight GEMM — and the
+first-epoch vision-encoder training.  Validation generation samples (top-k 50, top-p 0.9) without the
+reference's 3-beam search (`num_beams=3`), which the engine's decode loop does not implement."""
+from __future__ import annotations
+
+import json
+import logging
+import math
+import os
+from functools import partial
+
+import torch
+import torch.nn as nn
+from torch.utils.data import DataLoader
+
+from . import weights as Wt
+from .engine import PackedGemma, PackedSiglip, ProjectorState, Stage1Engine
+from .projector_trainer import _ShardedLoader, cosine_with_warmup
+
+logger = logging.getLogger(__name__)
+
+
+def vqa_collate_fn(batch, tokenizer):
+    """ref:Stage2/trainer.py:18-61 — stack `pixel_values`; pad `question_input_ids` to the longest question
+    of the batch and `answer_input_ids` to the longest answer, pads on `tokenizer.padding_side`."""
+    pad_id, left = tokenizer.pad_token_id, tokenizer.padding_side == "left"
+
+    def pad_to_longest(seqs):
+        longest = max(int(s.shape[0]) for s in seqs)
+        out = torch.full((len(seqs), longest), pad_id, dtype=seqs[0].dtype)
+        for i, s in enumerate(seqs):
+            n = int(s.shape[0])
+            if left:
+                out[i, longest - n:] = s
+            else:
+                out[i, :n] = s
+        return out
+
+    return {"pixel_values": torch.stack([it["pixel_values"] for it in batch]),
+            "question_input_ids": pad_to_longest([it["question_input_ids"] for it in batch]),
+            "answer_input_ids": pad_to_longest([it["answer_input_ids"] for it in batch])}
+
+
+def vqa_step_inputs(batch: dict, pad_id: int, bucket: int = 1) -> dict:
+    """Collated VQA batch -> the engine's batch dict.  Integer work, bit-exact with
+    ref:Stage2/trainer.py:366-395: text = [question ; answer], labels = -100 over the question and the
+    answer ids with pads -> -100, `label_span` = the answer columns.  `bucket` > 1 appends pad columns
+    AFTER the answer so the text length is a multiple of it: masked keys without labels, at positions
+    behind every real token, so the loss and gradients are those of the unpadded batch while the number of
+    distinct sequence lengths (each owns a workspace and a CUDA graph in the engine) stays small."""
+    q, a = batch["question_input_ids"], batch["answer_input_ids"]
+    B, Lq = q.shape
+    La = a.shape[1]
+    T = Lq + La
+    Tb = -(-T // bucket) * bucket
+    ids = torch.full((B, Tb), pad_id, dtype=torch.int64)
+    ids[:, :Lq] = q
+    ids[:, Lq:T] = a
+    labels = torch.full((B, Tb), -100, dtype=torch.int64)
+    labels[:, Lq:T] = torch.where(a == pad_id, torch.full_like(a, -100), a)
+    if batch["pixel_values"].is_pinned():       # DataLoader(pin_memory=True): keep the step's copies asynchronous
+        ids, labels = ids.pin_memory(), labels.pin_memory()
+    return {"pixel_values": batch["pixel_values"], "token_ids": ids, "labels": labels, "label_span": (Lq, La)}
+
+
+def accumulate_sync_flag(micro_step: int, grad_accum: int, end_of_dataloader: bool):
+    """`accelerate.Accelerator.accumulate()` bookkeeping (ref:Stage2/trainer.py:306): returns
+    (sync_gradients, new micro_step).  Gradients synchronise on every `grad_accum`-th micro-batch and on
+    the loader's last batch, where the counter restarts."""
+    if end_of_dataloader:
+        return True, 0
+    micro_step += 1
+    return micro_step % grad_accum == 0, micro_step
+
+
+class VQATrainerStage2:
+    def __init__(self, accelerator, vision_encoder, language_model, projection_layer, tokenizer, train_dataset,
+                 val_dataset, output_dir: str, batch_size: int, learning_rate: float, weight_decay: float,
+                 num_epochs: int, gradient_accumulation_steps: int, warmup_ratio: float,
+                 freeze_vision_encoder: bool, freeze_projection_layer: bool, freeze_llm: bool,
+                 enable_qlora: bool, train_ve_first_epoch: bool, wandb_project: str):
+        if enable_qlora or not freeze_llm:
+            raise NotImplementedError(
+                "Stage 2 with trainable LLM weights (QLoRA adapters or --unfreeze_llm) is not built: it needs "
+                "decoder weight-gradient GEMMs and an NF4 base-weight GEMM (SURVEY.md §8f rank 2b/4); there is "
+                "no fallback path")
+        if train_ve_first_epoch or not freeze_vision_encoder:
+            raise NotImplementedError("first-epoch vision-encoder training (--train_ve_first_epoch) is not built: "
+                                      "the SigLIP tower is forward-only here")
+        if freeze_projection_layer:
+            # ref:Stage2/trainer.py:262-263
+            raise ValueError("No trainable parameters found. Check freezing configuration and QLoRA setup.")
+        self.accelerator, self.tokenizer = accelerator, tokenizer
+        self.vision_encoder, self.language_model, self.projection_layer = vision_encoder, language_model, projection_layer
+        self.device = accelerator.device
+        self.output_dir, self.num_epochs, self.batch_size = output_dir, num_epochs, batch_size
+        self.wandb_project, self.train_ve_first_epoch, self.enable_qlora = wandb_project, False, False
+        self.learning_rate, self.weight_decay = learning_rate, weight_decay
+        self.grad_accum = int(gradient_accumulation_steps)
+        if self.device.type != "cuda":
+            raise RuntimeError("VQATrainerStage2 (B200 build) needs a CUDA device: the step runs on sm_100a "
+                               "kernels only, there is no CPU path")
+        self.validation_dir = os.path.join(output_dir, "validation_examples")
+        if accelerator.is_main_process:
+            os.makedirs(self.validation_dir, exist_ok=True)
+            os.makedirs(output_dir, exist_ok=True)
+        self.bucket = int(os.environ.get("PT_STAGE2_BUCKET", "32"))
+
+        collate = partial(vqa_collate_fn, tokenizer=tokenizer)
+        gen = torch.Generator().manual_seed(0)      # same shuffle on every process (accelerate syncs RNG)
+        base_loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=True, num_workers=4,
+                                 pin_memory=True, collate_fn=collate, generator=gen)
+        val_base = DataLoader(val_dataset, batch_size=batch_size, shuffle=False, num_workers=4,
+                              pin_memory=True, collate_fn=collate)
+        # schedule length from the UNSHARDED loader, as the reference computes it before prepare() (:152-157)
+        self.max_train_steps = num_epochs * math.ceil(len(base_loader) / self.grad_accum)
+        self.num_warmup_steps = math.ceil(warmup_ratio * self.max_train_steps)
+        self._sched_step = 0
+        self.train_loader = _ShardedLoader(base_loader, accelerator.process_index, accelerator.num_processes)
+        self.val_loader = _ShardedLoader(val_base, accelerator.process_index, accelerator.num_processes)
+        self.val_loader.dataset = val_dataset
+
+        vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
+            PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), self.device)
+        llm = language_model if isinstance(language_model, PackedGemma) else \
+            PackedGemma(*Wt.gemma_from_hf(language_model), self.device)
+        if isinstance(projection_layer, nn.Module):
+            projection_layer.to(self.device).float()      # fp32 master weights (the reference casts the
+            projection_layer.requires_grad_(True)         # projector to bf16 under mixed precision: :288)
+            proj = ProjectorState.from_module(projection_layer, self.device)
+        else:
+            proj = projection_layer
+        ga = self.grad_accum
+        self.engine = Stage1Engine(vis, llm, proj, self.device,
+                                   loss_divisor=ga * getattr(accelerator, "backward_divisor", ga))
+        self.pad_id = tokenizer.pad_token_id
+        if self.pad_id is None:
+            raise ValueError("tokenizer.pad_token_id is None: the dataset sets it to eos (ref:Stage2/dataset.py:33-35)")
+        logger.info("Freezing LLM parameters (QLoRA disabled).")
+        logger.info("projection_layer parameters are trainable.")
+
+    # accelerate's prepared scheduler ticks num_processes times per optimizer step
+    def current_lr(self) -> float:
+        return self.learning_rate * cosine_with_warmup(self._sched_step, self.num_warmup_steps, self.max_train_steps)
+
+    def _step_inputs(self, batch):
+        return vqa_step_inputs(batch, self.pad_id, self.bucket)
+
+    def _prefetched(self, loader):
+        """One-batch look-ahead, yields (engine batch, is_last): the host->device copy of micro-batch i+1
+        runs on a side stream while micro-batch i computes."""
+        it = iter(loader)
+        cur = next(it, None)
+        cur = None if cur is None else self.engine.stage_batch(self._step_inputs(cur))
+        while cur is not None:
+            nxt = next(it, None)
+            nxt = None if nxt is None else self.engine.stage_batch(self._step_inputs(nxt))
+            yield cur, nxt is None
+            cur = nxt
+
+    def train(self):
+        acc = self.accelerator
+        logger.info(f"Process {acc.process_index}: Starting Stage 2 training for {self.num_epochs} epochs on device {self.device}")
+        global_step, micro = 0, 0
+        for epoch in range(self.num_epochs):
+            epoch_train_loss = 0.0
+            for batch, last in self._prefetched(self.train_loader):
+                sync, micro = accumulate_sync_flag(micro, self.grad_accum, last)
+                loss = self.engine.train_step(batch, self.current_lr(), pad_id=self.pad_id,
+                                              weight_decay=self.weight_decay, allreduce=acc.all_reduce_sum_,
+                                              world_size=acc.num_processes, max_norm=1.0, sync_gradients=sync)
+                micro_loss = acc.gather(loss).mean().item()             # the one host sync of the micro-batch
+                if sync:
+                    self._sched_step += acc.num_processes
+                    global_step += 1
+                    epoch_train_loss += micro_loss
+                if acc.is_main_process:
+                    d = {"train/batch_loss": micro_loss}
+                    if sync:
+                        d.update({"train/learning_rate": self.current_lr(), "step": global_step,
+                                  "train/step_loss": micro_loss})
+                    acc.log(d, step=global_step)
+            avg_epoch_loss = epoch_train_loss / max(1, len(self.train_loader))      # ref :467 (sync steps only)
+            if acc.is_main_process:
+                logger.info(f"Epoch {epoch + 1} Training Loss: {avg_epoch_loss:.4f}")
+                acc.log({"train/loss": avg_epoch_loss, "train/learning_rate": self.current_lr(),
+                         "epoch": epoch + 1}, step=global_step)
+            self.evaluate(epoch, global_step)
+            if acc.is_main_process:
+                self.save_model(os.path.join(self.output_dir, f"checkpoint-epoch_{epoch + 1}"))
+        logger.info(f"Process {acc.process_index}: Stage 2 training complete!")
+
+    @torch.no_grad()
+    def evaluate(self, epoch, global_step, max_new_tokens: int = 512):
+        """ref:Stage2/trainer.py:490-677: validation loss over the whole set (left-padded collation), sampled
+        predictions from `[image][question]`, up to 20 examples written to validation_examples/."""
+        acc, tok = self.accelerator, self.tokenizer
+        logger.info(f"Starting evaluation for Epoch {epoch + 1}...")
+        original_side = tok.padding_side
+        tok.padding_side = "left"
+        total_val_loss, n_batches, examples = 0.0, 0, []
+        max_examples = min(20, len(self.val_loader.dataset))
+        can_decode = hasattr(tok, "batch_decode")
+        try:
+            for vb in self.val_loader:
+                loss = self.engine.eval_loss(self._step_inputs(vb), pad_id=self.pad_id)
+                total_val_loss += acc.gather(loss).mean().item()
+                n_batches += 1
+                if not can_decode:
+                    continue
+                try:
+                    gen = self.engine.generate(vb["pixel_values"], vb["question_input_ids"],
+                                               max_new_tokens=max_new_tokens, do_sample=True, top_p=0.9, top_k=50,
+                                               pad_token_id=self.pad_id, eos_token_id=tok.eos_token_id,
+                                               prompt_pad_id=self.pad_id)
+                    preds = tok.batch_decode(gen.cpu(), skip_special_tokens=True)
+                    questions = tok.batch_decode(vb["question_input_ids"], skip_special_tokens=True)
+                    refs = tok.batch_decode(vb["answer_input_ids"], skip_special_tokens=True)
+                    examples.extend({"epoch": epoch + 1, "question": q, "ground_truth": r, "prediction": p}
+                                    for q, r, p in zip(questions, refs, preds))
+                except Exception as e:
+                    logger.error(f"Error during validation generation/logging: {e}", exc_info=True)
+        finally:
+            tok.padding_side = original_side
+        acc.wait_for_everyone()
+        gathered = acc.gather_object(examples) if hasattr(acc, "gather_object") else examples
+        gathered = gathered[:max_examples] if acc.is_main_process else []
+        avg_val_loss = total_val_loss / max(1, n_batches)
+        if acc.is_main_process:
+            logger.info(f"Epoch {epoch + 1} Validation Loss: {avg_val_loss:.4f}")
+            acc.log({"val/loss": avg_val_loss, "epoch": epoch + 1}, step=global_step)
+            if gathered:
+                block = [f"Validation Examples for Epoch {epoch + 1}\n", "=" * 80 + "\n\n"]
+                for i, ex in enumerate(gathered):
+                    block += [f"Example {i + 1}:\n", f"Question: {ex['question']}\n",
+                              f"Ground Truth: {ex['ground_truth']}\n", f"Prediction: {ex['prediction']}\n",
+                              "=" * 80 + "\n\n"]
+                with open(os.path.join(self.validation_dir, f"epoch_{epoch + 1}_examples.txt"), "w",
+                          encoding="utf-8") as f:
+                    f.writelines(block)
+                with open(os.path.join(self.validation_dir, "all_validation_examples.txt"),
+                          "a" if epoch > 0 else "w", encoding="utf-8") as f:
+                    f.writelines(["\n"] + block)
+        logger.info("Evaluation finished.")
+        return avg_val_loss
+
+    def save_model(self, path):
+        """ref:Stage2/trainer.py:679-768, frozen-LLM case: `projection_layer/model.safetensors` (what
+        `accelerator.save_model` writes and Stage2/train_vqa_stage2.py:25-80 loads back) +
+        `projector_config.json`; the optimizer moments stand in for `accelerator.save_state`.  The frozen
+        language model is not saved (ref :707-708)."""
+        if not self.accelerator.is_main_process:
+            return
+        from safetensors.torch import save_file
+        torch.cuda.synchronize(self.device)
+        proj = self.engine.proj
+        proj_dir = os.path.join(path, "projection_layer")
+        os.makedirs(proj_dir, exist_ok=True)
+        save_file({k: v.detach().cpu().clone().contiguous() for k, v in proj.params().items()},
+                  os.path.join(proj_dir, "model.safetensors"))
+        with open(os.path.join(proj_dir, "projector_config.json"), "w") as f:
+            json.dump({"vision_dim": int(proj.shapes[0][1]), "llm_dim": int(proj.shapes[2][0])}, f, indent=4)
+        torch.save({"exp_avg": proj.m.cpu(), "exp_avg_sq": proj.v.cpu(), "step": proj.step,
+                    "scheduler_step": self._sched_step}, os.path.join(path, "optimizer.bin"))
+        logger.info("Language model was frozen and not saved.")
+        logger.info(f"Projection layer saved to {proj_dir}")

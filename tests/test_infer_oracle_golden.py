@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from oracle import stage1_oracle as O
-from oracle.make_golden_infer import CASES
+from oracle.make_golden_infer import CASES, LEFT_PADS
 
 GOLDEN = Path(__file__).resolve().parent / "golden"
 
@@ -19,6 +19,8 @@ def load(name):
     vc, lc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
     Wv, Wl, P = O.init_siglip(vc), O.init_gemma(lc), O.init_projector(vc.hidden, lc.hidden)
     px, ids, _ = O.synthetic_batch(B, max(Tp, 1), vc, lc, left_pad=False)
+    for b, k in enumerate(LEFT_PADS.get(name, [])):
+        ids[b, :k] = lc.pad_id
     prompt = ids[:, :Tp] if Tp else None
     if Tp:
         assert np.array_equal(prompt.numpy(), g["prompt_ids"])
@@ -30,10 +32,18 @@ def test_prefill_logits_and_greedy_tokens_match_hf_generate(name):
     g, vc, lc, Wv, Wl, P, px, prompt, new = load(name)
     X0 = O.prefill_inputs(px, prompt, Wv, P, Wl, vc, lc)
     np.testing.assert_allclose(X0[:, :g["projected"].shape[1]].numpy(), g["projected"], rtol=0, atol=2e-5)
-    lg = O.last_position_logits(X0, Wl, lc)
+    padded = name in LEFT_PADS
+    if padded:      # a plain forward keeps arange positions under a padded mask (F3); only generate moves them
+        attn = torch.cat([torch.ones(X0.shape[0], X0.shape[1] - prompt.shape[1], dtype=torch.int64),
+                          (prompt != lc.pad_id).long()], dim=1)
+        hid = O.gemma3_hidden(X0, attn, Wl, lc)
+        lg = (O.rms_norm(hid[:, -1, :], Wl["final_norm"], lc.eps) @ Wl["embed"].T).float()
+    else:
+        lg = O.last_position_logits(X0, Wl, lc)
     ref = g["prefill_logits"]
     assert np.abs(lg.numpy() - ref).max() / np.abs(ref).max() < 1e-4
-    toks, _ = O.greedy_generate(px, prompt, Wv, P, Wl, vc, lc, new, eos_id=1, pad_id=lc.pad_id)
+    toks, _ = O.greedy_generate(px, prompt, Wv, P, Wl, vc, lc, new, eos_id=1, pad_id=lc.pad_id,
+                                mask_prompt_pads=padded)
     assert toks.dtype == torch.int64
     assert np.array_equal(toks.numpy(), g["generated"])              # integer work: exact
 
@@ -42,5 +52,5 @@ def test_prefill_logits_and_greedy_tokens_match_hf_generate(name):
 def test_eos_stops_and_pads_like_hf(name):
     g, vc, lc, Wv, Wl, P, px, prompt, new = load(name)
     toks, _ = O.greedy_generate(px, prompt, Wv, P, Wl, vc, lc, new, eos_id=int(g["eos_variant_id"]),
-                                pad_id=lc.pad_id)
+                                pad_id=lc.pad_id, mask_prompt_pads=name in LEFT_PADS)
     assert np.array_equal(toks.numpy(), g["generated_eos"])

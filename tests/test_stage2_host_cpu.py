@@ -1,0 +1,80 @@
+"""Host side of the Stage-2 drop-in on CPU: collate and step-input construction bit-exact against the oracle
+(which is pinned to the reference's recorded masks), accumulation bookkeeping, argument handling."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import stage1_oracle as O
+from oracle import stage2_oracle as O2
+from projectiontrainer_b200.vqa_trainer import (VQATrainerStage2, accumulate_sync_flag, vqa_collate_fn,
+                                                vqa_step_inputs)
+
+
+class Tok:
+    def __init__(self, pad, side):
+        self.pad_token_id, self.eos_token_id, self.padding_side = pad, 1, side
+
+
+@pytest.mark.parametrize("side", ["left", "right"])
+@pytest.mark.parametrize("bucket", [1, 8, 32])
+def test_collate_and_step_inputs_bit_exact_vs_oracle(side, bucket):
+    vc = O.SiglipCfg(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lc = O.GemmaCfg(vocab=512, hidden=64, ff=128, layers=6, hq=2, hkv=1, hd=16, window=8, q_scalar=16.0)
+    px, qs, as_ = O2.synthetic_vqa_samples(5, vc, lc, seed=3, q_len=(1, 9), a_len=(1, 17))
+    items = [{"pixel_values": px[i], "question_input_ids": qs[i], "answer_input_ids": as_[i]} for i in range(5)]
+    cb = vqa_collate_fn(items, Tok(lc.pad_id, side))
+    q_ref, a_ref = O2.vqa_collate([q.numpy() for q in qs], [a.numpy() for a in as_], lc.pad_id, side)
+    assert cb["question_input_ids"].dtype == torch.int64
+    assert np.array_equal(cb["question_input_ids"].numpy(), q_ref)
+    assert np.array_equal(cb["answer_input_ids"].numpy(), a_ref)
+    assert torch.equal(cb["pixel_values"], px)
+    st = vqa_step_inputs(cb, lc.pad_id, bucket)
+    n_img = 7
+    attn_ref, lab_ref = O2.vqa_masks_labels(q_ref, a_ref, n_img, lc.pad_id)
+    T = q_ref.shape[1] + a_ref.shape[1]
+    ids, lab = st["token_ids"].numpy(), st["labels"].numpy()
+    assert ids.shape[1] % bucket == 0 and ids.shape[1] - T < bucket
+    assert np.array_equal(ids[:, :T], np.concatenate([q_ref, a_ref], axis=1)) and (ids[:, T:] == lc.pad_id).all()
+    assert np.array_equal(lab[:, :T], lab_ref[:, n_img:]) and (lab[:, T:] == -100).all()
+    assert np.array_equal((ids[:, :T] != lc.pad_id).astype(np.int64), attn_ref[:, n_img:])
+    assert st["label_span"] == (q_ref.shape[1], a_ref.shape[1])
+
+
+def test_accumulate_bookkeeping_matches_oracle_schedule():
+    for n, ga in [(3, 2), (4, 1), (5, 4), (7, 3), (1, 8)]:
+        micro, flags = 0, []
+        for epoch in range(2):
+            for i in range(n):
+                f, micro = accumulate_sync_flag(micro, ga, i == n - 1)
+                flags.append(f)
+        assert flags == O2.sync_flags(n, ga) * 2, (n, ga)
+
+
+def test_unsupported_stage2_modes_fail_loudly():
+    class Acc:
+        device = torch.device("cpu")
+        is_main_process, process_index, num_processes, gradient_accumulation_steps = True, 0, 1, 1
+    base = dict(accelerator=Acc(), vision_encoder=None, language_model=None, projection_layer=None,
+                tokenizer=Tok(0, "right"), train_dataset=[], val_dataset=[], output_dir="/tmp/_unused_vqa",
+                batch_size=1, learning_rate=1e-4, weight_decay=0.01, num_epochs=1, gradient_accumulation_steps=1,
+                warmup_ratio=0.0, freeze_vision_encoder=True, freeze_projection_layer=False, freeze_llm=True,
+                enable_qlora=False, train_ve_first_epoch=False, wandb_project="x")
+    with pytest.raises(NotImplementedError):
+        VQATrainerStage2(**{**base, "enable_qlora": True})
+    with pytest.raises(NotImplementedError):
+        VQATrainerStage2(**{**base, "freeze_llm": False})
+    with pytest.raises(NotImplementedError):
+        VQATrainerStage2(**{**base, "train_ve_first_epoch": True})
+    with pytest.raises(ValueError, match="No trainable parameters"):
+        VQATrainerStage2(**{**base, "freeze_projection_layer": True})
+    with pytest.raises(RuntimeError, match="CUDA"):          # no CPU path
+        VQATrainerStage2(**base)
+
+
+def test_stage2_cli_rejects_lora_flags():
+    from projectiontrainer_b200.train_vqa_stage2 import build_parser, main
+    a = build_parser().parse_args([])
+    assert a.gradient_accumulation_steps == 8 and a.batch_size == 1 and a.warmup_ratio == 0.05
+    assert a.max_q_len == 128 and a.max_a_len == 512 and a.llm_name == "Qwen/Qwen3-8B"
+    with pytest.raises(SystemExit):
+        main(["--enable_qlora", "--synthetic", "4"])
