@@ -102,6 +102,19 @@ def _rank_main(rank, world, port, out):
     acc.all_reduce_sum_(g)                                   # the path's one exchange: SUM, mean folded later
     mean = g / world
     losses = acc.gather(torch.tensor(10.0 + rank))
+    # Stage 2 (ref:Stage2/trainer.py:306): gradients accumulate locally inside accumulate() windows and are
+    # exchanged ONCE per window, at the sync micro-batch; 3 micro-batches with GA=2 -> windows {0,1} and {2}
+    from projectiontrainer_b200.vqa_trainer import accumulate_sync_flag
+    window, micro, exchanged = torch.zeros(4), 0, []
+    for i in range(3):
+        sync, micro = accumulate_sync_flag(micro, acc.gradient_accumulation_steps, i == 2)
+        window += float(rank + 1) * (i + 1)
+        if sync:
+            acc.all_reduce_sum_(window)
+            exchanged.append(float(window[0]) / world)
+            window.zero_()
+    assert exchanged == [4.5, 4.5] and acc.backward_divisor == 2
+    assert acc.gather_object([f"r{rank}a", f"r{rank}b"]) == ["r0a", "r0b", "r1a", "r1b"]
     out.put((rank, float(mean[0]), losses.tolist()))
     acc.wait_for_everyone()
     acc.end_training()
