@@ -268,6 +268,21 @@ int pt_cast_f32_bf16(const float* x, void* y_bf16, long long n, void* stream);
 int pt_gather_cast_rows(const float* x, void* out_bf16, int rows_out, int D, int group_rows_out,
                         int group_rows_in, int group_row0, void* stream);
 
+/* ---- image preprocessing in front of the vision tower -------------------------------
+ * ref:Stage1/train_projection_stage1.py:99-104 and ref:Stage2/dataset.py:90-95:
+ *     image = image.resize((S, S)); pixel_values = processor(images=image, return_tensors="pt").pixel_values
+ * i.e. Pillow's antialiased BICUBIC resize (src/libImaging/Resample.c: 8-bit fixed point, horizontal then
+ * vertical pass, each rounded to uint8) followed by HF SiglipImageProcessor rescale (x * rescale in float64 ->
+ * float32) and normalize ((x - mean) / std in float32).  src_rgb: device uint8 [H, W, 3] with row stride
+ * src_row_stride bytes; dst_chw: device f32 [3, out_h, out_w]; dst_u8_hwc (nullable): the resized uint8 image
+ * [out_h, out_w, 3] (bit-exact with Pillow).  workspace: device scratch of at least
+ * pt_image_preprocess_workspace(H, W, out_h, out_w) bytes, 16-byte aligned. */
+long long pt_image_preprocess_workspace(int H, int W, int out_h, int out_w);
+int pt_image_preprocess(const uint8_t* src_rgb, int H, int W, long long src_row_stride, float* dst_chw,
+                        uint8_t* dst_u8_hwc, int out_h, int out_w, float mean0, float mean1, float mean2,
+                        float std0, float std1, float std2, double rescale, void* workspace,
+                        long long workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,7 @@ def lib() -> C.CDLL:
             "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for this path.")
     L = C.CDLL(str(LIB_PATH))
     L.pt_last_error.restype = C.c_char_p
+    L.pt_image_preprocess_workspace.restype = C.c_longlong
     _lib = L
     return L
 
@@ -62,7 +63,7 @@ def check(rc: int, what: str) -> None:
 
 
 # kernels launched per C-ABI call (for the bench's gpu_launches claim)
-KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3}
+KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_image_preprocess": 4}
 launch_count = 0
 
 

@@ -565,6 +565,32 @@ class Stage1Engine:
         self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
 
+    def preprocess_images(self, images, out: torch.Tensor | None = None, *, mean=(0.5, 0.5, 0.5),
+                          std=(0.5, 0.5, 0.5), rescale: float = 1 / 255) -> torch.Tensor:
+        """Decoded RGB images (uint8 [H, W, 3] tensors of any size, host or device) -> `pixel_values`
+        f32 [B, 3, S, S] on the device: what the reference's datasets do per item on the CPU with
+        `image.resize((S, S))` + `processor(images=image)` (ref:Stage1/train_projection_stage1.py:99-104,
+        ref:Stage2/dataset.py:90-95), here Pillow-exact on the GPU (`pt_image_preprocess`).  Runs on the
+        current stream; host images are copied in first (non_blocking when pinned)."""
+        S, dev = self.vcfg.image, self.device
+        B = len(images)
+        if out is None:
+            out = torch.empty(B, 3, S, S, dtype=F32, device=dev)
+        for i, im in enumerate(images):
+            if im.dim() != 3 or im.shape[2] != 3 or im.dtype != torch.uint8:
+                raise ValueError(f"image {i}: expected uint8 [H, W, 3], got {tuple(im.shape)} {im.dtype}")
+            src = im if im.is_cuda else im.to(dev, non_blocking=True)
+            H, W, _ = src.shape
+            need = ops.image_preprocess_workspace(H, W, S, S)
+            if not hasattr(self, "_img_ws"):
+                self._img_ws = {}
+            sid = torch.cuda.current_stream().cuda_stream      # one scratch buffer per stream that calls this
+            ws = self._img_ws.get(sid)
+            if ws is None or ws.numel() < need:
+                ws = self._img_ws[sid] = torch.empty(need, dtype=torch.uint8, device=dev)
+            ops.image_preprocess(src.contiguous(), out[i], ws, mean=mean, std=std, rescale=rescale)
+        return out
+
     def stage_batch(self, batch: dict) -> dict:
         """Start the host->device copy of a (pinned) host batch on a side stream so that it overlaps the step
         that is running; returns a batch dict to hand to train_step later.  Two staging slots alternate (the
@@ -574,7 +600,12 @@ class Stage1Engine:
         sg = self._stage
         i = sg["n"] & 1
         sg["n"] += 1
-        pv, ti, lb = batch["pixel_values"], batch["token_ids"], batch["labels"]
+        raw = batch.get("images_u8")            # undecoded-size uint8 images instead of processor output
+        ti, lb = batch["token_ids"], batch["labels"]
+        if raw is not None:
+            pv = torch.empty(len(raw), 3, self.vcfg.image, self.vcfg.image, dtype=F32, device="meta")
+        else:
+            pv = batch["pixel_values"]
         slot = sg["slots"][i]
         if slot is None or slot["px"].shape != pv.shape or slot["ids"].shape != ti.shape:
             slot = dict(px=torch.empty(pv.shape, dtype=F32, device=self.device),
@@ -585,12 +616,15 @@ class Stage1Engine:
             sg["slots"][i] = slot
         with torch.cuda.stream(sg["stream"]):
             sg["stream"].wait_event(slot["done"])       # the step that consumed this slot has read it
-            slot["px"].copy_(pv, non_blocking=True)
+            if raw is not None:
+                self.preprocess_images(raw, slot["px"])  # upload + resize + normalize on the copy stream
+            else:
+                slot["px"].copy_(pv, non_blocking=True)
             slot["ids"].copy_(ti, non_blocking=True)
             slot["lab"].copy_(lb, non_blocking=True)
             slot["event"].record()
-        return {"pixel_values": pv, "token_ids": ti, "labels": lb, "_staged": slot,
-                "label_span": batch.get("label_span")}
+        return {"pixel_values": slot["px"] if raw is not None else pv, "token_ids": ti, "labels": lb,
+                "_staged": slot, "label_span": batch.get("label_span")}
 
     def _graphed_forward_backward(self, batch: dict, pad_id) -> torch.Tensor:
         """forward_backward through a CUDA graph keyed on the batch geometry: inputs are copied into
@@ -637,7 +671,10 @@ class Stage1Engine:
     def eval_loss(self, batch: dict, pad_id=0) -> torch.Tensor:
         """Validation forward (ref:Stage1/projector_trainer.py:304-370): the same loss, no backward."""
         dev = self.device
-        px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
+        if "pixel_values" in batch:
+            px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
+        else:
+            px = self.preprocess_images(batch["images_u8"])
         ids = batch["token_ids"].to(dev, non_blocking=True)
         lab = batch["labels"].to(dev, non_blocking=True)
         B, T = ids.shape
@@ -846,6 +883,8 @@ class Stage1Engine:
         (NCCL); the 1/world mean is folded into the optimizer kernel.  Returns the device scalar loss
         (no host sync here)."""
         dev = self.device
+        if "pixel_values" not in batch:         # decoded images that were not staged: preprocess them now
+            batch = {**batch, "pixel_values": self.preprocess_images(batch["images_u8"])}
         self.select_geometry((tuple(batch["pixel_values"].shape), tuple(batch["token_ids"].shape)))
         if self.use_graph:
             loss = self._graphed_forward_backward(batch, pad_id)

@@ -320,3 +320,26 @@ def gather_cast_rows(x, out, *, group=(0, 0, 0)):
     _req_cuda(x, out)
     _lib.call("pt_gather_cast_rows", _ptr(x), _ptr(out), out.shape[0], out.shape[1],
               *map(int, group), _stream())
+
+
+def image_preprocess_workspace(H: int, W: int, out_h: int, out_w: int) -> int:
+    n = int(_lib.lib().pt_image_preprocess_workspace(int(H), int(W), int(out_h), int(out_w)))
+    if n < 0:
+        raise RuntimeError(f"pt_image_preprocess_workspace: bad sizes {(H, W, out_h, out_w)}")
+    return n
+
+
+def image_preprocess(src_u8_hwc, dst_chw, workspace, *, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5),
+                     rescale: float = 1 / 255, dst_u8=None):
+    """Decoded RGB uint8 [H, W, 3] (CUDA) -> pixel_values f32 [3, S, S]: Pillow's antialiased bicubic
+    `Image.resize((S, S))` + SiglipImageProcessor rescale / normalize (ref:Stage1/train_projection_stage1.py:99-104,
+    ref:Stage2/dataset.py:90-95).  `dst_u8` (optional, uint8 [S, S, 3]) receives the resized image itself."""
+    _req_cuda(src_u8_hwc, dst_chw, workspace, dst_u8)
+    H, W, ch = src_u8_hwc.shape
+    if ch != 3 or src_u8_hwc.dtype != torch.uint8 or src_u8_hwc.stride(2) != 1 or src_u8_hwc.stride(1) != 3:
+        raise RuntimeError("image_preprocess: source must be uint8 [H, W, 3] with packed pixels")
+    _, oh, ow = dst_chw.shape
+    _lib.call("pt_image_preprocess", _ptr(src_u8_hwc), int(H), int(W), C.c_longlong(int(src_u8_hwc.stride(0))),
+              _ptr(dst_chw), _ptr(dst_u8), int(oh), int(ow), _f(mean[0]), _f(mean[1]), _f(mean[2]),
+              _f(std[0]), _f(std[1]), _f(std[2]), C.c_double(float(rescale)), _ptr(workspace),
+              C.c_longlong(int(workspace.numel() * workspace.element_size())), _stream())

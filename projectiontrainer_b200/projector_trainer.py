@@ -67,6 +67,17 @@ class _ShardedLoader:
             yield first[self.rank % len(first)]
 
 
+def stage1_collate(items):
+    """torch's default collate, except that decoded images of different sizes (`images_u8`, datasets built
+    with gpu_preprocess=True) stay a list."""
+    from torch.utils.data import default_collate
+    if "images_u8" not in items[0]:
+        return default_collate(items)
+    out = default_collate([{k: v for k, v in it.items() if k != "images_u8"} for it in items])
+    out["images_u8"] = [it["images_u8"] for it in items]
+    return out
+
+
 class ProjectionTrainerStage1:
     def __init__(self, accelerator, vision_encoder, language_model, projection_layer, processor, tokenizer,
                  train_dataset, val_dataset=None, output_dir="./trained_projection_stage1", batch_size=8,
@@ -89,11 +100,11 @@ class ProjectionTrainerStage1:
 
         gen = torch.Generator().manual_seed(0)      # same shuffle on every process (accelerate syncs RNG)
         base_loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=True, num_workers=2,
-                                 generator=gen, pin_memory=True)
+                                 generator=gen, pin_memory=True, collate_fn=stage1_collate)
         self.val_loader = None
         if val_dataset is not None:
             self.val_loader = _ShardedLoader(DataLoader(val_dataset, batch_size=batch_size, shuffle=False,
-                                                        num_workers=2, pin_memory=True),
+                                                        num_workers=2, pin_memory=True, collate_fn=stage1_collate),
                                              accelerator.process_index, accelerator.num_processes)
         # schedule lengths are computed from the UNSHARDED loader, as the reference does (:82-87)
         steps_per_epoch = math.ceil(len(base_loader) / gradient_accumulation_steps)
@@ -127,13 +138,15 @@ class ProjectionTrainerStage1:
     def _prefetched(self, loader):
         """One-batch look-ahead: the host->device copy of batch i+1 runs on a side stream while step i
         computes (the reference gets the same overlap from DataLoader workers + pinned memory)."""
+        def on_host(b):
+            return "images_u8" in b or not b["pixel_values"].is_cuda
         it = iter(loader)
         cur = next(it, None)
-        if cur is not None and not cur["pixel_values"].is_cuda:
+        if cur is not None and on_host(cur):
             cur = self.engine.stage_batch(cur)
         while cur is not None:
             nxt = next(it, None)
-            if nxt is not None and not nxt["pixel_values"].is_cuda:
+            if nxt is not None and on_host(nxt):
                 nxt = self.engine.stage_batch(nxt)
             yield cur
             cur = nxt
@@ -169,6 +182,8 @@ class ProjectionTrainerStage1:
                 val_loss, val_steps, total_samples, correct_last_word = 0.0, 0, 0, 0
                 can_decode = hasattr(self.tokenizer, "batch_decode")
                 for vb in self.val_loader:
+                    if "images_u8" in vb:
+                        vb["pixel_values"] = self.engine.preprocess_images(vb["images_u8"])
                     val_loss += self.engine.eval_loss(vb, pad_id=self.pad_id).item()
                     val_steps += 1
                     if not can_decode:

@@ -29,7 +29,11 @@ class XrayTextPairDataset(Dataset):
     (ref:train_projection_stage1.py:25-126).  Items: pixel_values f32 [3,S,S] (processor output),
     token_ids i64 [max_length] (tokenizer padded to max_length), labels = token_ids with pad -> -100."""
 
-    def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_length=512, image_root_2=None):
+    def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_length=512, image_root_2=None,
+                 gpu_preprocess=False):
+        # gpu_preprocess (an addition): items carry the decoded image as `images_u8` uint8 [H, W, 3]; resize +
+        # rescale + normalize run on the GPU in the trainer's look-ahead stage (Pillow-exact kernels)
+        self.gpu_preprocess = gpu_preprocess
         self.image_root, self.image_root_2, self.img_size = image_root, image_root_2, img_size
         self.processor, self.tokenizer, self.max_length = processor, tokenizer, max_length
         self.samples = []
@@ -57,14 +61,18 @@ class XrayTextPairDataset(Dataset):
     def __getitem__(self, idx):
         from PIL import Image
         sample = self.samples[idx]
-        image = Image.open(self._resolve(sample["image"])).convert("RGB").resize((self.img_size, self.img_size))
-        image_inputs = self.processor(images=image, return_tensors="pt")
+        image = Image.open(self._resolve(sample["image"])).convert("RGB")
         text = self.tokenizer(sample["normal_caption"], max_length=self.max_length, padding="max_length",
                               truncation=True, return_tensors="pt")
         token_ids = text.input_ids.squeeze(0)
         labels = token_ids.clone()
         if self.tokenizer.pad_token_id is not None:
             labels[labels == self.tokenizer.pad_token_id] = -100
+        if self.gpu_preprocess:
+            import numpy as np
+            return {"images_u8": torch.from_numpy(np.array(image, dtype=np.uint8)), "token_ids": token_ids,
+                    "labels": labels}
+        image_inputs = self.processor(images=image.resize((self.img_size, self.img_size)), return_tensors="pt")
         return {"pixel_values": image_inputs.pixel_values.squeeze(0), "token_ids": token_ids, "labels": labels}
 
 
@@ -116,6 +124,8 @@ def build_parser():
     p.add_argument("--img_size", type=int, default=384)
     p.add_argument("--save_every_n_epochs", type=int, default=2)
     p.add_argument("--enable_qlora", action="store_true")
+    p.add_argument("--gpu_preprocess", action="store_true",
+                   help="resize / rescale / normalize the decoded images on the GPU (Pillow-exact) instead of in the workers")
     p.add_argument("--synthetic", type=int, default=0, help="train on N synthetic samples with random-init models")
     p.add_argument("--synthetic_llm", choices=["1b", "4b"], default="1b")
     p.add_argument("--max_length", type=int, default=512, help="caption tokens (the reference's dataset default)")
@@ -153,18 +163,18 @@ def main(argv=None):
         vision_dim = vision_encoder.config.vision_config.hidden_size
         llm_dim = language_model.config.hidden_size
         full = XrayTextPairDataset(args.image_root, args.train_json, processor, tokenizer, args.img_size,
-                                   max_length=args.max_length, image_root_2=args.image_root_2)
+                                   max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
         train_dataset, val_dataset = full, None
         if args.val_json:
             val_dataset = XrayTextPairDataset(args.image_root, args.val_json, processor, tokenizer, args.img_size,
-                                              max_length=args.max_length, image_root_2=args.image_root_2)
+                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
         elif args.train_val_split > 0:
             from sklearn.model_selection import train_test_split
             tr, va = train_test_split(full.samples, test_size=args.train_val_split, random_state=42)
             train_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
-                                                max_length=args.max_length, image_root_2=args.image_root_2)
+                                                max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
             val_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
-                                              max_length=args.max_length, image_root_2=args.image_root_2)
+                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
             train_dataset.samples, val_dataset.samples = tr, va
         if len(train_dataset) == 0:
             logger.error("Training dataset is empty.")

@@ -17,7 +17,11 @@ logger = logging.getLogger(__name__)
 
 class XrayVQADataset(Dataset):
     def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_q_len=128, max_a_len=512,
-                 image_root_2=None):
+                 image_root_2=None, gpu_preprocess=False):
+        """`gpu_preprocess=True` (an addition): items carry the decoded image as `images_u8` uint8 [H, W, 3]
+        instead of `pixel_values`; resize + rescale + normalize then run on the GPU inside the trainer's
+        look-ahead stage (`Stage1Engine.preprocess_images`, Pillow-exact)."""
+        self.gpu_preprocess = gpu_preprocess
         self.image_root, self.image_root_2, self.img_size = image_root, image_root_2, img_size
         self.processor, self.tokenizer = processor, tokenizer
         self.max_q_len, self.max_a_len = max_q_len, max_a_len
@@ -50,12 +54,18 @@ class XrayVQADataset(Dataset):
         name, question, answer = s.get("image"), s.get("problem"), s.get("normal_caption")
         if not all([name, question, answer]):
             raise KeyError(f"sample {idx} is missing image, problem or normal_caption")
-        image = Image.open(self._image_path(name)).convert("RGB").resize((self.img_size, self.img_size))
-        pixel_values = self.processor(images=image, return_tensors="pt").pixel_values.squeeze(0)
+        image = Image.open(self._image_path(name)).convert("RGB")
         q = self.tokenizer(question, max_length=self.max_q_len, truncation=True, add_special_tokens=False).input_ids
         a = self.tokenizer(answer, max_length=self.max_a_len, truncation=True).input_ids
-        return {"pixel_values": pixel_values, "question_input_ids": torch.tensor(q, dtype=torch.long),
+        item = {"question_input_ids": torch.tensor(q, dtype=torch.long),
                 "answer_input_ids": torch.tensor(a, dtype=torch.long)}
+        if self.gpu_preprocess:
+            import numpy as np
+            item["images_u8"] = torch.from_numpy(np.array(image, dtype=np.uint8))
+        else:
+            image = image.resize((self.img_size, self.img_size))
+            item["pixel_values"] = self.processor(images=image, return_tensors="pt").pixel_values.squeeze(0)
+        return item
 
     def __getitem__(self, idx):
         """A sample that cannot be read is skipped in favour of the next readable one, as the reference

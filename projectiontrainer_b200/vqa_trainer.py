@@ -46,9 +46,13 @@ def vqa_collate_fn(batch, tokenizer):
                 out[i, :n] = s
         return out
 
-    return {"pixel_values": torch.stack([it["pixel_values"] for it in batch]),
-            "question_input_ids": pad_to_longest([it["question_input_ids"] for it in batch]),
-            "answer_input_ids": pad_to_longest([it["answer_input_ids"] for it in batch])}
+    out = {"question_input_ids": pad_to_longest([it["question_input_ids"] for it in batch]),
+           "answer_input_ids": pad_to_longest([it["answer_input_ids"] for it in batch])}
+    if "images_u8" in batch[0]:      # GPU preprocessing (vqa_dataset gpu_preprocess=True): decoded images, any size
+        out["images_u8"] = [it["images_u8"] for it in batch]
+    else:
+        out["pixel_values"] = torch.stack([it["pixel_values"] for it in batch])
+    return out
 
 
 def vqa_step_inputs(batch: dict, pad_id: int, bucket: int = 1) -> dict:
@@ -68,9 +72,11 @@ def vqa_step_inputs(batch: dict, pad_id: int, bucket: int = 1) -> dict:
     ids[:, Lq:T] = a
     labels = torch.full((B, Tb), -100, dtype=torch.int64)
     labels[:, Lq:T] = torch.where(a == pad_id, torch.full_like(a, -100), a)
-    if batch["pixel_values"].is_pinned():       # DataLoader(pin_memory=True): keep the step's copies asynchronous
+    if q.is_pinned():       # DataLoader(pin_memory=True): keep the step's copies asynchronous
         ids, labels = ids.pin_memory(), labels.pin_memory()
-    return {"pixel_values": batch["pixel_values"], "token_ids": ids, "labels": labels, "label_span": (Lq, La)}
+    out = {"token_ids": ids, "labels": labels, "label_span": (Lq, La)}
+    out.update({k: batch[k] for k in ("pixel_values", "images_u8") if k in batch})
+    return out
 
 
 def accumulate_sync_flag(micro_step: int, grad_accum: int, end_of_dataloader: bool):
@@ -219,7 +225,8 @@ class VQATrainerStage2:
                 if not can_decode:
                     continue
                 try:
-                    gen = self.engine.generate(vb["pixel_values"], vb["question_input_ids"],
+                    px = vb["pixel_values"] if "pixel_values" in vb else self.engine.preprocess_images(vb["images_u8"])
+                    gen = self.engine.generate(px, vb["question_input_ids"],
                                                max_new_tokens=max_new_tokens, do_sample=True, top_p=0.9, top_k=50,
                                                pad_token_id=self.pad_id, eos_token_id=tok.eos_token_id,
                                                prompt_pad_id=self.pad_id)

@@ -78,3 +78,23 @@ def test_stage2_cli_rejects_lora_flags():
     assert a.max_q_len == 128 and a.max_a_len == 512 and a.llm_name == "Qwen/Qwen3-8B"
     with pytest.raises(SystemExit):
         main(["--enable_qlora", "--synthetic", "4"])
+
+
+def test_collates_keep_decoded_images_as_lists():
+    """gpu_preprocess datasets hand out `images_u8` of different sizes: both collates keep them a list and
+    collate everything else as before."""
+    from projectiontrainer_b200.projector_trainer import stage1_collate
+    a = {"images_u8": torch.zeros(5, 7, 3, dtype=torch.uint8), "token_ids": torch.arange(4), "labels": torch.arange(4)}
+    b = {"images_u8": torch.zeros(9, 2, 3, dtype=torch.uint8), "token_ids": torch.arange(4), "labels": torch.arange(4)}
+    out = stage1_collate([a, b])
+    assert isinstance(out["images_u8"], list) and out["images_u8"][1].shape == (9, 2, 3)
+    assert out["token_ids"].shape == (2, 4) and "pixel_values" not in out
+    plain = stage1_collate([{"pixel_values": torch.zeros(3, 4, 4), "token_ids": torch.arange(4), "labels": torch.arange(4)}] * 2)
+    assert plain["pixel_values"].shape == (2, 3, 4, 4)
+    items = [{"images_u8": a["images_u8"], "question_input_ids": torch.tensor([5, 6]), "answer_input_ids": torch.tensor([2, 7, 8])},
+             {"images_u8": b["images_u8"], "question_input_ids": torch.tensor([9]), "answer_input_ids": torch.tensor([2])}]
+    cb = vqa_collate_fn(items, Tok(0, "left"))
+    assert "pixel_values" not in cb and len(cb["images_u8"]) == 2
+    st = vqa_step_inputs(cb, 0, 4)
+    assert st["images_u8"] is cb["images_u8"] and st["token_ids"].tolist() == [[5, 6, 2, 7, 8, 0, 0, 0], [0, 9, 0, 0, 2, 0, 0, 0]]
+    assert st["labels"].tolist() == [[-100, -100, 2, 7, 8, -100, -100, -100], [-100] * 4 + [2, -100, -100, -100]]
