@@ -63,7 +63,7 @@ def check(rc: int, what: str) -> None:
 
 
 # kernels launched per C-ABI call (for the bench's gpu_launches claim)
-KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_image_preprocess": 4}
+KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_image_preprocess": 3}
 launch_count = 0
 
 

@@ -20,6 +20,7 @@ namespace pt {
 
 constexpr int kPrecisionBits = 32 - 8 - 2;
 constexpr int kChunk = 128;                  // output pixels per block in the horizontal pass
+constexpr int kMaxTaps = 1024;               // filter taps per output index (down-scale factors up to ~250)
 
 struct ResampleAxis {
     int in_size, out_size, ksize;
@@ -47,10 +48,21 @@ __device__ inline double bicubic_weight(double x) {
     return 0.0;
 }
 
-// One thread per output index of one axis: bounds[xx] = (first source index, tap count), and the fixed-point
-// weights, stored TRANSPOSED (coeffT[tap * out_size + xx]) so the passes read them coalesced.
-__global__ void resample_coeffs_kernel(ResampleAxis ax, int2* __restrict__ bounds, int* __restrict__ coeffT) {
-    const int xx = blockIdx.x * blockDim.x + threadIdx.x;
+// One warp per output index, both axes in one launch (blockIdx.y): bounds[xx] = (first source index, tap
+// count) and the fixed-point weights, stored TRANSPOSED (coeffT[tap * out_size + xx], `kpad` taps, zero beyond
+// the count) so the passes read them coalesced.  The lanes evaluate the filter in parallel; the normalising sum
+// is taken by lane 0 in tap order, as Pillow's loop does, so that its rounding is the same.
+__global__ void __launch_bounds__(128)
+resample_coeffs_kernel(ResampleAxis ax0, int2* __restrict__ bounds0, int* __restrict__ coeffT0, int kpad0,
+                       ResampleAxis ax1, int2* __restrict__ bounds1, int* __restrict__ coeffT1, int kpad1) {
+    __shared__ double wsh[4][kMaxTaps];
+    const bool second = blockIdx.y != 0;
+    const ResampleAxis ax = second ? ax1 : ax0;
+    int2* bounds = second ? bounds1 : bounds0;
+    int* coeffT = second ? coeffT1 : coeffT0;
+    const int kpad = second ? kpad1 : kpad0;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int xx = blockIdx.x * 4 + warp;
     if (xx >= ax.out_size) return;
     const double center = __dadd_rn(0.0, __dmul_rn(xx + 0.5, ax.scale));
     const double ss = __ddiv_rn(1.0, ax.filterscale);
@@ -59,23 +71,27 @@ __global__ void resample_coeffs_kernel(ResampleAxis ax, int2* __restrict__ bound
     int xmax = static_cast<int>(__dadd_rn(__dadd_rn(center, ax.support), 0.5));
     if (xmax > ax.in_size) xmax = ax.in_size;
     xmax -= xmin;
-    double ww = 0.0;
-    for (int x = 0; x < xmax; ++x) {
+    double* w = wsh[warp];
+    for (int x = lane; x < xmax; x += 32) {
         const double arg = __dmul_rn(__dadd_rn(__dadd_rn(static_cast<double>(x + xmin), -center), 0.5), ss);
-        ww = __dadd_rn(ww, bicubic_weight(arg));
+        w[x] = bicubic_weight(arg);
     }
-    for (int x = 0; x < ax.ksize; ++x) {
+    __syncwarp();
+    double ww = 0.0;
+    if (lane == 0)
+        for (int x = 0; x < xmax; ++x) ww = __dadd_rn(ww, w[x]);
+    ww = __shfl_sync(0xffffffffu, ww, 0);
+    for (int x = lane; x < kpad; x += 32) {
         int fixed = 0;
         if (x < xmax) {
-            const double arg = __dmul_rn(__dadd_rn(__dadd_rn(static_cast<double>(x + xmin), -center), 0.5), ss);
-            double w = bicubic_weight(arg);
-            if (ww != 0.0) w = __ddiv_rn(w, ww);
-            const double scaled = __dmul_rn(w, static_cast<double>(1 << kPrecisionBits));
-            fixed = static_cast<int>(w < 0 ? __dadd_rn(-0.5, scaled) : __dadd_rn(0.5, scaled));
+            double v = w[x];
+            if (ww != 0.0) v = __ddiv_rn(v, ww);
+            const double scaled = __dmul_rn(v, static_cast<double>(1 << kPrecisionBits));
+            fixed = static_cast<int>(v < 0 ? __dadd_rn(-0.5, scaled) : __dadd_rn(0.5, scaled));
         }
         coeffT[static_cast<long long>(x) * ax.out_size + xx] = fixed;
     }
-    bounds[xx] = make_int2(xmin, xmax);
+    if (lane == 0) bounds[xx] = make_int2(xmin, xmax);
 }
 
 __device__ inline int clip8(int acc) {
@@ -84,10 +100,14 @@ __device__ inline int clip8(int acc) {
 }
 
 // Horizontal pass: block = (chunk of kChunk output columns, one source row).  The source bytes the chunk needs
-// are staged in shared memory with aligned 4-byte loads; each thread then produces one RGB output pixel.
+// are staged in shared memory with aligned 4-byte loads; each thread then produces one RGB output pixel.  The
+// taps of a pixel are contiguous bytes, so they are consumed four at a time: 12 bytes = three 32-bit
+// shared-memory words (plus the word carried over), realigned with funnel shifts -- a quarter of the
+// shared-memory wavefronts of byte loads, which is what bounded the first version.  Weights beyond a pixel's
+// tap count are zero (kpad is a multiple of 4), so the ragged tail needs no branch.
 __global__ void __launch_bounds__(kChunk)
 resample_horizontal_kernel(const uint8_t* __restrict__ src, long long src_stride, int row0,
-                           const int2* __restrict__ bounds, const int* __restrict__ coeffT, int out_w, int ksize,
+                           const int2* __restrict__ bounds, const int* __restrict__ coeffT, int out_w, int kpad,
                            uint8_t* __restrict__ tmp) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int xx0 = blockIdx.x * kChunk;
@@ -110,14 +130,27 @@ resample_horizontal_kernel(const uint8_t* __restrict__ src, long long src_stride
     const int xx = xx0 + threadIdx.x;
     if (xx >= out_w) return;
     const int2 b = bounds[xx];
-    const uint8_t* p = s + (b.x - x_lo) * 3;
+    const int off = mis + (b.x - x_lo) * 3;                // byte offset of the pixel's first tap inside smem
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(smem) + (off >> 2);
+    const int sh = (off & 3) * 8;
     int r = 1 << (kPrecisionBits - 1), gg = r, bb = r;
-    for (int x = 0; x < b.y; ++x) {
-        const int k = coeffT[static_cast<long long>(x) * out_w + xx];
-        r += p[0] * k;
-        gg += p[1] * k;
-        bb += p[2] * k;
-        p += 3;
+    uint32_t w0 = wp[0];
+    const int* kp = coeffT + xx;
+    for (int x = 0; x < b.y; x += 4) {
+        const uint32_t w1 = wp[1], w2 = wp[2], w3 = wp[3];
+        const uint32_t x0 = __funnelshift_r(w0, w1, sh), x1 = __funnelshift_r(w1, w2, sh),
+                       x2 = __funnelshift_r(w2, w3, sh);          // 12 tap bytes, aligned
+        const int k0 = kp[0], k1 = kp[out_w], k2 = kp[2 * static_cast<long long>(out_w)],
+                  k3 = kp[3 * static_cast<long long>(out_w)];
+        r += static_cast<int>(x0 & 0xff) * k0 + static_cast<int>(x0 >> 24) * k1 +
+             static_cast<int>((x1 >> 16) & 0xff) * k2 + static_cast<int>((x2 >> 8) & 0xff) * k3;
+        gg += static_cast<int>((x0 >> 8) & 0xff) * k0 + static_cast<int>(x1 & 0xff) * k1 +
+              static_cast<int>(x1 >> 24) * k2 + static_cast<int>((x2 >> 16) & 0xff) * k3;
+        bb += static_cast<int>((x0 >> 16) & 0xff) * k0 + static_cast<int>((x1 >> 8) & 0xff) * k1 +
+              static_cast<int>(x2 & 0xff) * k2 + static_cast<int>(x2 >> 24) * k3;
+        w0 = w3;
+        wp += 3;
+        kp += 4 * static_cast<long long>(out_w);
     }
     uint8_t* o = tmp + (static_cast<long long>(row) * out_w + xx) * 3;
     o[0] = static_cast<uint8_t>(clip8(r));
@@ -161,6 +194,7 @@ resample_vertical_normalize_kernel(const uint8_t* __restrict__ tmp, int row_shif
 
 struct ImagePlan {
     ResampleAxis h, v;            // horizontal (over W), vertical (over H)
+    int kpad_h, kpad_v;           // taps stored per output index (multiple of 4, zero beyond the count)
     long long off_bounds_h, off_bounds_v, off_coeff_h, off_coeff_v, off_tmp, total;
     int smem_bytes;
 };
@@ -170,16 +204,18 @@ static ImagePlan plan_image(int H, int W, int out_h, int out_w) {
     p.h = make_axis(W, out_w);
     p.v = make_axis(H, out_h);
     auto up = [](long long x) { return (x + 255) / 256 * 256; };
+    p.kpad_h = (p.h.ksize + 3) / 4 * 4;
+    p.kpad_v = (p.v.ksize + 3) / 4 * 4;
     long long o = 0;
     p.off_bounds_h = o; o = up(o + static_cast<long long>(out_w) * sizeof(int2));
     p.off_bounds_v = o; o = up(o + static_cast<long long>(out_h) * sizeof(int2));
-    p.off_coeff_h = o;  o = up(o + static_cast<long long>(out_w) * p.h.ksize * sizeof(int));
-    p.off_coeff_v = o;  o = up(o + static_cast<long long>(out_h) * p.v.ksize * sizeof(int));
+    p.off_coeff_h = o;  o = up(o + static_cast<long long>(out_w) * p.kpad_h * sizeof(int));
+    p.off_coeff_v = o;  o = up(o + static_cast<long long>(out_h) * p.kpad_v * sizeof(int));
     p.off_tmp = o;      o = up(o + static_cast<long long>(H) * out_w * 3);
     p.total = o;
     // widest source span of one chunk: kChunk centres apart by `scale`, plus the filter support on both sides
     const long long span = static_cast<long long>(ceil(kChunk * p.h.scale + 2 * p.h.support)) + 4;
-    p.smem_bytes = static_cast<int>(std::min<long long>(span, W) * 3 + 8);
+    p.smem_bytes = static_cast<int>(std::min<long long>(span, W) * 3 + 8 + 32);      // + over-read of the last 4-tap group
     return p;
 }
 
@@ -213,8 +249,9 @@ extern "C" int pt_image_preprocess(const uint8_t* src_rgb, int H, int W, long lo
     int* coeff_h = reinterpret_cast<int*>(ws + p.off_coeff_h);
     int* coeff_v = reinterpret_cast<int*>(ws + p.off_coeff_v);
     uint8_t* tmp = ws + p.off_tmp;
-    resample_coeffs_kernel<<<(out_w + 127) / 128, 128, 0, st>>>(p.h, bounds_h, coeff_h);
-    resample_coeffs_kernel<<<(out_h + 127) / 128, 128, 0, st>>>(p.v, bounds_v, coeff_v);
+    PT_REQUIRE(p.h.ksize <= kMaxTaps && p.v.ksize <= kMaxTaps, "pt_image_preprocess: down-scale factor too large");
+    dim3 gc((std::max(out_w, out_h) + 3) / 4, 2);
+    resample_coeffs_kernel<<<gc, 128, 0, st>>>(p.h, bounds_h, coeff_h, p.kpad_h, p.v, bounds_v, coeff_v, p.kpad_v);
     // The horizontal pass covers every source row: which rows the vertical pass reads is only known on the
     // device (its bounds), and the rows outside that range are at most the filter support at either end.
     if (p.smem_bytes > 48 * 1024) {
@@ -224,7 +261,7 @@ extern "C" int pt_image_preprocess(const uint8_t* src_rgb, int H, int W, long lo
     }
     dim3 gh((out_w + kChunk - 1) / kChunk, H);
     resample_horizontal_kernel<<<gh, kChunk, p.smem_bytes, st>>>(src_rgb, src_row_stride, 0, bounds_h, coeff_h, out_w,
-                                                                p.h.ksize, tmp);
+                                                                p.kpad_h, tmp);
     dim3 gv((out_w + 127) / 128, out_h);
     resample_vertical_normalize_kernel<<<gv, 128, 0, st>>>(tmp, 0, bounds_v, coeff_v, out_h, out_w, rescale, mean0,
                                                            mean1, mean2, std0, std1, std2, dst_chw, dst_u8_hwc);
