@@ -48,7 +48,11 @@ typedef enum {
      * c_zs multiples of ldc); bias = delta, f32, one value per C row (row index = element offset / ldc) with
      * delta[r] = sum_k P[r,k] dP[r,k] = rowsum(dO * O) (pt_attn_delta); C (bf16) receives
      * alpha * P * (dP - delta), exactly 0 where P == 0. */
-    PT_ACT_SOFTMAX_BWD = 5
+    PT_ACT_SOFTMAX_BWD = 5,
+    /* PT_ACT_GEGLU / PT_ACT_GEGLU_BWD with SiLU in place of tanh-GELU: the SwiGLU MLP of the Qwen3 decoder
+     * (HF:models/qwen3/modeling_qwen3.py Qwen3MLP: down(silu(gate) * up)); same operands and layout. */
+    PT_ACT_SWIGLU = 6,
+    PT_ACT_SWIGLU_BWD = 7
 } pt_act;
 
 typedef enum {
@@ -235,6 +239,9 @@ int pt_attn_siglip_fwd_v1(const void* qkv_bf16, void* out_bf16, int B, int N, in
 /* GeGLU: act = gelu_tanh(g) * u with gu = [g | u] per row — HF:models/gemma3/modeling_gemma3.py:127-129. */
 int pt_geglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream);
 int pt_geglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, int ff, void* stream);
+/* SwiGLU (Qwen3MLP): the same two entries with silu(g) = g * sigmoid(g) in place of gelu_tanh(g). */
+int pt_swiglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream);
+int pt_swiglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, int ff, void* stream);
 
 /* dZ = dH * d/dz[0.5 z (1 + erf(z/sqrt2))] — backward of nn.GELU() in ref:Stage1/projectors.py:18. */
 int pt_gelu_erf_bwd(const void* dH, const void* Z, void* dZ, long long n, void* stream);

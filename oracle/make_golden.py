@@ -48,6 +48,13 @@ CASES = {
                        dict(vocab=304, hidden=48, ff=96, layers=7, hq=4, hkv=1, hd=32, window=5,
                             q_scalar=32.0), 2, 9, False, 1, 3, 0.34),
     "config1_full": ({}, {}, 2, 64, True, 2, 1, 0.0),
+    # Qwen3 decoder recipe (the reference's launch script trains against Qwen/Qwen3-8B:
+    # run_projection_train_stage1.sh:12): pre-norm only, SwiGLU, q/k norms, unscaled embeddings, untied LM head,
+    # full attention everywhere, GQA; the trainer takes its non-Gemma embedding branch (projector_trainer.py:190-195)
+    "tiny_qwen3_gqa": (dict(hidden=64, ff=128, layers=2, heads=2, image=64, patch=16),
+                       dict(vocab=512, hidden=64, ff=128, layers=3, hq=4, hkv=2, hd=32, window=0, q_scalar=32.0,
+                            pattern=1, sandwich_norm=False, silu=True, scale_embed=False, tie_lm_head=False),
+                       3, 12, True, 1, 3, 0.34),
 }
 
 
@@ -113,6 +120,37 @@ def build_hf_gemma(cfg: O.GemmaCfg, W: dict):
     assert not unexpected and not missing, (missing, unexpected)
     assert m.lm_head.weight.data_ptr() == m.model.embed_tokens.weight.data_ptr() or \
         torch.equal(m.lm_head.weight, m.model.embed_tokens.weight)
+    return m.eval()
+
+
+def build_hf_qwen3(cfg: O.GemmaCfg, W: dict):
+    """HF Qwen3ForCausalLM holding the oracle's weights; norm gains are stored as (gain - 1) in W."""
+    from transformers import Qwen3Config, Qwen3ForCausalLM
+    hc = Qwen3Config(vocab_size=cfg.vocab, hidden_size=cfg.hidden, intermediate_size=cfg.ff,
+                     num_hidden_layers=cfg.layers, num_attention_heads=cfg.hq, num_key_value_heads=cfg.hkv,
+                     head_dim=cfg.hd, rms_norm_eps=cfg.eps, max_position_embeddings=32768,
+                     tie_word_embeddings=cfg.tie_lm_head, use_sliding_window=False, attention_bias=False,
+                     pad_token_id=cfg.pad_id,
+                     rope_parameters={"rope_type": "default", "rope_theta": cfg.theta_global})
+    m = Qwen3ForCausalLM(hc)
+    assert m.config.hidden_act == "silu" and all(t == "full_attention" for t in m.config.layer_types)
+    qd, kd = cfg.hq * cfg.hd, cfg.hkv * cfg.hd
+    sd = {"model.embed_tokens.weight": W["embed"], "lm_head.weight": W.get("lm_head", W["embed"]),
+          "model.norm.weight": 1 + W["final_norm"]}
+    for l in range(cfg.layers):
+        s, p = f"model.layers.{l}.", f"l{l}."
+        sd[s + "input_layernorm.weight"] = 1 + W[p + "in_norm"]
+        sd[s + "post_attention_layernorm.weight"] = 1 + W[p + "pre_ffn_norm"]
+        sd[s + "self_attn.q_norm.weight"], sd[s + "self_attn.k_norm.weight"] = 1 + W[p + "q_norm"], 1 + W[p + "k_norm"]
+        sd[s + "self_attn.q_proj.weight"] = W[p + "qkv_w"][:qd]
+        sd[s + "self_attn.k_proj.weight"] = W[p + "qkv_w"][qd:qd + kd]
+        sd[s + "self_attn.v_proj.weight"] = W[p + "qkv_w"][qd + kd:]
+        sd[s + "self_attn.o_proj.weight"] = W[p + "o_w"]
+        sd[s + "mlp.gate_proj.weight"] = W[p + "gu_w"][:cfg.ff]
+        sd[s + "mlp.up_proj.weight"] = W[p + "gu_w"][cfg.ff:]
+        sd[s + "mlp.down_proj.weight"] = W[p + "down_w"]
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and not missing, (missing, unexpected)
     return m.eval()
 
 
@@ -196,7 +234,8 @@ def run_case(name: str, out_dir: Path):
     vc, lc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
     t0 = time.time()
     Wv, Wl, P = O.init_siglip(vc), O.init_gemma(lc), O.init_projector(vc.hidden, lc.hidden)
-    vision, llm = build_hf_siglip(vc, Wv), build_hf_gemma(lc, Wl)
+    vision = build_hf_siglip(vc, Wv)
+    llm = build_hf_gemma(lc, Wl) if lc.sandwich_norm else build_hf_qwen3(lc, Wl)
     proj = MLPProjector(vc.hidden, lc.hidden)
     proj.load_state_dict(P)
     pixels, ids, labels = O.synthetic_batch(B, T, vc, lc, left_pad=left_pad)

@@ -66,9 +66,24 @@ class GemmaCfg:
     q_scalar: float = 256.0           # query_pre_attn_scalar
     pattern: int = 6                  # layer i is full-attention iff (i+1) % pattern == 0
     pad_id: int = 0
+    # decoder recipe.  Defaults = Gemma3.  Qwen3 (HF:models/qwen3/modeling_qwen3.py): no norms on the branch
+    # outputs, SwiGLU, unscaled embeddings, every layer full attention (pattern=1), optionally an untied LM
+    # head (W["lm_head"]).  Norm gains are stored as (gain - 1) in both families so rms_norm is shared.
+    sandwich_norm: bool = True
+    silu: bool = False
+    scale_embed: bool = True
+    tie_lm_head: bool = True
 
     def is_full(self, i: int) -> bool:
         return (i + 1) % self.pattern == 0
+
+
+def qwen3_cfg(**kw) -> "GemmaCfg":
+    """A Qwen3-recipe decoder config (full attention everywhere, q_scalar = head_dim)."""
+    kw.setdefault("pattern", 1)
+    kw.setdefault("q_scalar", float(kw.get("hd", 128)))
+    kw.setdefault("theta_global", 1000000.0)
+    return GemmaCfg(sandwich_norm=False, silu=True, scale_embed=False, **kw)
 
 
 SIGLIP_L = SiglipCfg()
@@ -174,10 +189,12 @@ def shifted_targets(lm_labels: np.ndarray) -> np.ndarray:
     return out
 
 
-def embed_tokens(token_ids: torch.Tensor, E: torch.Tensor, hidden: int, scale_dtype=None):
+def embed_tokens(token_ids: torch.Tensor, E: torch.Tensor, hidden: int, scale_dtype=None, scale: bool = True):
     """HF:models/gemma3/modeling_gemma3.py:102-113 — embedding * sqrt(hidden), the scale being
     rounded to the embedding dtype first (scale_dtype=torch.bfloat16 emulates a bf16 checkpoint
     whose values are held in a wider tensor: sqrt(1152) = 33.94 -> 34.0)."""
+    if not scale:               # Qwen3: plain nn.Embedding
+        return E[token_ids]
     scale = torch.tensor(hidden ** 0.5, dtype=scale_dtype or E.dtype).to(E.dtype)
     return E[token_ids] * scale
 
@@ -254,11 +271,13 @@ def gemma3_hidden(X0, keyvalid, W: dict, cfg: GemmaCfg, pos_ids=None):
         pr = torch.softmax(s.float(), dim=-1).to(dt)
         pr = torch.nan_to_num(pr, nan=0.0)                        # fully masked (pad) rows: unused
         o = (pr @ v).transpose(1, 2).reshape(B, S, cfg.hq * cfg.hd)
-        x = x + rms_norm(o @ W[p + "o_w"].T, W[p + "post_attn_norm"], cfg.eps)
-        f = rms_norm(x, W[p + "pre_ffn_norm"], cfg.eps)
+        o = o @ W[p + "o_w"].T
+        x = x + (rms_norm(o, W[p + "post_attn_norm"], cfg.eps) if cfg.sandwich_norm else o)
+        f = rms_norm(x, W[p + "pre_ffn_norm"], cfg.eps)            # Qwen3: post_attention_layernorm
         gu = f @ W[p + "gu_w"].T                                  # fused [2*ff, h] = (gate; up)
         g, u = gu.split(cfg.ff, dim=-1)
-        x = x + rms_norm((gelu_tanh(g) * u) @ W[p + "down_w"].T, W[p + "post_ffn_norm"], cfg.eps)
+        mlp = ((F.silu(g) if cfg.silu else gelu_tanh(g)) * u) @ W[p + "down_w"].T
+        x = x + (rms_norm(mlp, W[p + "post_ffn_norm"], cfg.eps) if cfg.sandwich_norm else mlp)
     return x
 
 
@@ -269,7 +288,7 @@ def causal_lm_loss(hidden, W: dict, cfg: GemmaCfg, lm_labels: np.ndarray):
     tgt = torch.from_numpy(shifted_targets(lm_labels))
     sel = tgt != -100
     y = rms_norm(hidden, W["final_norm"], cfg.eps)[sel]          # [n, h]
-    logits = (y @ W["embed"].T).float()
+    logits = (y @ W.get("lm_head", W["embed"]).T).float()
     return F.cross_entropy(logits, tgt[sel], reduction="mean"), int(sel.sum())
 
 
@@ -282,7 +301,7 @@ def stage1_step(pixels, token_ids, labels, Wv, P, Wl, vcfg: SiglipCfg, lcfg: Gem
     with torch.no_grad():
         feats = siglip_forward(pixels, Wv, vcfg)
         patch = feats[:, 1:, :]                      # ref:projector_trainer.py:173 ("discard CLS")
-        txt = embed_tokens(token_ids, Wl["embed"], lcfg.hidden, scale_dtype)
+        txt = embed_tokens(token_ids, Wl["embed"], lcfg.hidden, scale_dtype, lcfg.scale_embed)
     proj = projector_forward(patch, P)
     X0 = torch.cat([proj, txt.to(proj.dtype)], dim=1)
     n_img = proj.shape[1]
@@ -318,7 +337,7 @@ def last_position_logits(X0, Wl: dict, lcfg: GemmaCfg, attn=None):
     else:
         hidden = gemma3_hidden(X0, attn, Wl, lcfg, pos_ids=generate_positions(attn))
     y = rms_norm(hidden[:, -1, :], Wl["final_norm"], lcfg.eps)
-    return (y @ Wl["embed"].T).float()
+    return (y @ Wl.get("lm_head", Wl["embed"]).T).float()
 
 
 @torch.no_grad()
@@ -328,7 +347,8 @@ def prefill_inputs(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaCf
     patch = siglip_forward(pixels, Wv, vcfg)[:, 1:, :]
     X0 = projector_forward(patch, P)
     if prompt_ids is not None and prompt_ids.shape[1] > 0:
-        X0 = torch.cat([X0, embed_tokens(prompt_ids, Wl["embed"], lcfg.hidden, scale_dtype).to(X0.dtype)], dim=1)
+        X0 = torch.cat([X0, embed_tokens(prompt_ids, Wl["embed"], lcfg.hidden, scale_dtype,
+                                         lcfg.scale_embed).to(X0.dtype)], dim=1)
     return X0
 
 
@@ -356,7 +376,8 @@ def greedy_generate(pixels, prompt_ids, Wv, P, Wl, vcfg: SiglipCfg, lcfg: GemmaC
         done |= nxt == eos_id
         if bool(done.all()):
             break
-        X = torch.cat([X, embed_tokens(nxt[:, None], Wl["embed"], lcfg.hidden, scale_dtype).to(X.dtype)], dim=1)
+        X = torch.cat([X, embed_tokens(nxt[:, None], Wl["embed"], lcfg.hidden, scale_dtype,
+                                       lcfg.scale_embed).to(X.dtype)], dim=1)
         if attn is not None:
             attn = torch.cat([attn, torch.ones(B, 1, dtype=torch.int64)], dim=1)
     return torch.stack(toks, dim=1), torch.stack(step_logits, dim=1)
@@ -412,9 +433,12 @@ def init_gemma(cfg: GemmaCfg, seed: int = 0, dtype=torch.float32) -> dict:
     h = cfg.hidden
     r = lambda *s, std=0.02: (torch.randn(*s, generator=g) * std).to(dtype)
     W = {"embed": r(cfg.vocab, h, std=0.02), "final_norm": r(h, std=0.3)}
+    if not cfg.tie_lm_head:
+        W["lm_head"] = r(cfg.vocab, h, std=0.02)
     for l in range(cfg.layers):
         p = f"l{l}."
-        for n in ("in_norm", "post_attn_norm", "pre_ffn_norm", "post_ffn_norm"):
+        for n in (("in_norm", "post_attn_norm", "pre_ffn_norm", "post_ffn_norm") if cfg.sandwich_norm
+                  else ("in_norm", "pre_ffn_norm")):
             W[p + n] = r(h, std=0.3)
         W[p + "q_norm"], W[p + "k_norm"] = r(cfg.hd, std=0.3), r(cfg.hd, std=0.3)
         W[p + "qkv_w"] = r((cfg.hq + 2 * cfg.hkv) * cfg.hd, h, std=0.02)

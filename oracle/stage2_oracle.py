@@ -75,8 +75,8 @@ def vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg: O.SiglipCfg, lcfg: O.Gemm
     dict of what the reference hands to the language model)."""
     with torch.no_grad():
         patch = O.siglip_forward(pixels, Wv, vcfg)[:, 1:, :]
-        q_emb = O.embed_tokens(q_ids, Wl["embed"], lcfg.hidden, scale_dtype)
-        a_emb = O.embed_tokens(a_ids, Wl["embed"], lcfg.hidden, scale_dtype)
+        q_emb = O.embed_tokens(q_ids, Wl["embed"], lcfg.hidden, scale_dtype, lcfg.scale_embed)
+        a_emb = O.embed_tokens(a_ids, Wl["embed"], lcfg.hidden, scale_dtype, lcfg.scale_embed)
     proj = O.projector_forward(patch, P)
     X0 = torch.cat([proj, q_emb.to(proj.dtype), a_emb.to(proj.dtype)], dim=1)
     attn, labels = vqa_masks_labels(q_ids.numpy(), a_ids.numpy(), proj.shape[1], lcfg.pad_id)

@@ -14,6 +14,7 @@ LIB_PATH = PKG / "libpt_stage1.so"
 PT_BF16, PT_F32, PT_I64, PT_I32 = 0, 1, 2, 3
 BAND_NONE, BAND_SCORES, BAND_K_BY_QUERY, BAND_K_BY_KEY = 0, 1, 2, 3
 ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD = 0, 1, 2, 3, 4, 5
+ACT_SWIGLU, ACT_SWIGLU_BWD = 6, 7
 
 
 class GemmArgs(C.Structure):

@@ -46,6 +46,13 @@ class GemmaCfg:
     q_scalar: float = 256.0
     pattern: int = 6
     pad_id: int = 0
+    # decoder recipe; the defaults are Gemma3.  Qwen3 (HF:models/qwen3/modeling_qwen3.py): no norm on the
+    # branch outputs (pre-norm only), SwiGLU, plain embeddings, full attention in every layer (pattern=1),
+    # possibly an untied LM head.  Norm gains are packed as (gain - 1) for both families (weights.py).
+    sandwich_norm: bool = True
+    silu: bool = False
+    scale_embed: bool = True
+    tie_lm_head: bool = True
 
     def is_full(self, i: int) -> bool:
         return (i + 1) % self.pattern == 0
@@ -57,6 +64,11 @@ GEMMA3_4B = GemmaCfg(vocab=262208, hidden=2560, ff=10240, layers=34, hq=8, hkv=4
                      window=1024, rope_factor_global=8.0)
 
 
+QWEN3_8B = GemmaCfg(vocab=151936, hidden=4096, ff=12288, layers=36, hq=32, hkv=8, hd=128, window=0,
+                    theta_global=1000000.0, q_scalar=128.0, pattern=1, pad_id=151643, sandwich_norm=False,
+                    silu=True, scale_embed=False, tie_lm_head=False)
+
+
 def siglip_cfg_from_hf(c) -> SiglipCfg:
     """c: transformers SiglipVisionConfig (or SiglipConfig.vision_config)."""
     if getattr(c, "hidden_act", "gelu_pytorch_tanh") != "gelu_pytorch_tanh":
@@ -66,11 +78,38 @@ def siglip_cfg_from_hf(c) -> SiglipCfg:
                      eps=c.layer_norm_eps)
 
 
+def qwen3_cfg_from_hf(c) -> GemmaCfg:
+    """c: transformers Qwen3Config (dense).  Rejects features the kernels do not implement."""
+    if getattr(c, "hidden_act", "silu") != "silu":
+        raise RuntimeError(f"unsupported Qwen3 activation {c.hidden_act!r} (only silu)")
+    if getattr(c, "attention_bias", False):
+        raise RuntimeError("Qwen3 with attention_bias is not implemented")
+    types = list(getattr(c, "layer_types", []) or [])
+    if getattr(c, "use_sliding_window", False) or any(t != "full_attention" for t in types):
+        raise RuntimeError("Qwen3 with sliding-window layers is not implemented")
+    theta = 1000000.0
+    rp = getattr(c, "rope_parameters", None)
+    if isinstance(rp, dict) and rp:
+        if rp.get("rope_type", "default") != "default":
+            raise RuntimeError(f"unsupported rope_type {rp.get('rope_type')!r}")
+        theta = float(rp.get("rope_theta", theta))
+    else:
+        if getattr(c, "rope_scaling", None):
+            raise RuntimeError("unsupported rope scaling")
+        theta = float(getattr(c, "rope_theta", theta))
+    hd = getattr(c, "head_dim", None) or c.hidden_size // c.num_attention_heads
+    return GemmaCfg(vocab=c.vocab_size, hidden=c.hidden_size, ff=c.intermediate_size, layers=c.num_hidden_layers,
+                    hq=c.num_attention_heads, hkv=c.num_key_value_heads, hd=hd, window=0, theta_global=theta,
+                    eps=c.rms_norm_eps, q_scalar=float(hd), pattern=1,
+                    pad_id=c.pad_token_id if c.pad_token_id is not None else 0, sandwich_norm=False, silu=True,
+                    scale_embed=False, tie_lm_head=bool(getattr(c, "tie_word_embeddings", False)))
+
+
 def gemma_cfg_from_hf(c) -> GemmaCfg:
     """c: transformers Gemma3TextConfig.  Rejects features the kernels do not implement."""
     if getattr(c, "model_type", "") not in ("gemma3_text",):
         raise RuntimeError(f"unsupported language model type {getattr(c, 'model_type', None)!r}: "
-                           "this build implements the Gemma3 text decoder only (no fallback)")
+                           "this build implements the Gemma3 text and Qwen3 dense decoders only (no fallback)")
     if getattr(c, "attn_logit_softcapping", None) or getattr(c, "final_logit_softcapping", None):
         raise RuntimeError("logit soft-capping is not implemented")
     if getattr(c, "hidden_activation", "gelu_pytorch_tanh") != "gelu_pytorch_tanh":

@@ -134,6 +134,7 @@ struct EpiGbwd {
     const uint8_t* GU;    // gu, same position
     long long c_row, g_row, ff_bytes;
     int rows_valid, row_lo, cols_q;
+    GluConsts glu;
 };
 
 __device__ __forceinline__ void epi_chunk_gbwd(const uint32_t (&v)[32], uint32_t stg, int lane, const EpiGbwd& o) {
@@ -167,7 +168,7 @@ __device__ __forceinline__ void epi_chunk_gbwd(const uint32_t (&v)[32], uint32_t
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             float val, grad;
-            gelu_tanh_fast_both(g[j], val, grad);
+            glu_act_fast_both(g[j], o.glu, val, grad);
             dg[j] = d[j] * u[j] * grad;
             du[j] = d[j] * val;
         }
@@ -495,7 +496,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const float g = round_bf16(__uint_as_float(vg[j])), u = round_bf16(__uint_as_float(vu[j]));
-                        vg[j] = __float_as_uint(gelu_tanh_fast_f(g) * u);
+                        vg[j] = __float_as_uint(glu_act_fast(g, p.glu) * u);
                     }
                     o.C = crow + static_cast<long long>(p.ff + colg) * 2;
                     epi_chunk<PT_ACT_NONE>(vu, stg, lane, o);
@@ -542,6 +543,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     o.GU = static_cast<const uint8_t*>(p.aux) + (static_cast<long long>(row0) * p.ld_aux + col0) * 2;
                     o.rows_valid = rows_valid; o.row_lo = row_lo;
                     o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
+                    o.glu = p.glu;
                     epi_chunk_gbwd(v, stg, lane, o);
                     continue;
                 }

@@ -34,6 +34,7 @@ struct GemmDev {
     void* aux;
     long long ld_aux;
     int ff;
+    GluConsts glu;    // activation of the fused gated-unit epilogues (tanh-GELU or SiLU)
     // causal / sliding-window band of self-attention products (pt_gemm_args.band): work that only meets
     // masked (query, key) pairs is not issued.  band_w = window (0: unbounded below).
     int band, band_w;

@@ -478,8 +478,10 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     }
     PT_REQUIRE((a->N % 4) == 0 || ((!a->bias || a->act == PT_ACT_SOFTMAX_BWD) && !a->residual && !a->C_pre),
                "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
-    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_SOFTMAX_BWD, "pt_gemm_bf16: bad act %d", a->act);
-    const bool geglu = a->act == PT_ACT_GEGLU, geglu_bwd = a->act == PT_ACT_GEGLU_BWD;
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_SWIGLU_BWD, "pt_gemm_bf16: bad act %d", a->act);
+    const bool silu = a->act == PT_ACT_SWIGLU || a->act == PT_ACT_SWIGLU_BWD;
+    const bool geglu = a->act == PT_ACT_GEGLU || a->act == PT_ACT_SWIGLU;
+    const bool geglu_bwd = a->act == PT_ACT_GEGLU_BWD || a->act == PT_ACT_SWIGLU_BWD;
     if (geglu || geglu_bwd) {
         PT_REQUIRE(a->aux != nullptr && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0 && a->ld_aux % 8 == 0,
                    "pt_gemm_bf16: fused GeGLU needs a 16B-aligned aux matrix with ld_aux %% 8 == 0");
@@ -518,7 +520,9 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     p.C = a->C; p.C_pre = a->C_pre; p.bias = a->bias; p.R = a->residual;
     p.ldc = a->ldc; p.ldr = a->ldr;
     p.c_f32 = a->c_dtype == PT_F32; p.r_f32 = a->r_dtype == PT_F32;
-    p.act = a->act; p.alpha = a->alpha;
+    p.act = geglu ? PT_ACT_GEGLU : (geglu_bwd ? PT_ACT_GEGLU_BWD : a->act);     // SwiGLU = same epilogues, other constants
+    p.alpha = a->alpha;
+    p.glu = glu_consts(silu);
     if (a->act == PT_ACT_SOFTMAX_BWD) {
         PT_REQUIRE(a->aux && a->bias && a->c_dtype == PT_BF16 && !a->residual && !a->C_pre && kg == 1,
                    "pt_gemm_bf16: fused softmax backward needs aux = P, bias = delta, bf16 C, no residual / C_pre");

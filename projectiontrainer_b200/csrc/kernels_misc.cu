@@ -29,8 +29,10 @@ __global__ void patchify_kernel(const float* __restrict__ px, __nv_bfloat16* __r
 }
 
 // ---- GeGLU: act = gelu_tanh(g) * u with gu = [g | u] per row -----------------------------------
+template <bool SILU>
 __global__ void geglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act,
                                  long long rows, int ff) {
+    auto f = [](float z) { return SILU ? silu_f(z) : gelu_tanh_f(z); };
     const int f8 = ff / 8;
     const long long n = rows * f8;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -43,15 +45,17 @@ __global__ void geglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bflo
         uint32_t o[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            o[j] = pack_bf16(gelu_tanh_f(bf16_lo(gw[j])) * bf16_lo(uw[j]),
-                             gelu_tanh_f(bf16_hi(gw[j])) * bf16_hi(uw[j]));
+            o[j] = pack_bf16(f(bf16_lo(gw[j])) * bf16_lo(uw[j]), f(bf16_hi(gw[j])) * bf16_hi(uw[j]));
         *reinterpret_cast<uint4*>(act + r * ff + c) = make_uint4(o[0], o[1], o[2], o[3]);
     }
 }
 
 // d_gu = [ d_act * u * gelu'(g) | d_act * gelu(g) ]
+template <bool SILU>
 __global__ void geglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* __restrict__ gu,
                                  __nv_bfloat16* __restrict__ dgu, long long rows, int ff) {
+    auto f = [](float z) { return SILU ? silu_f(z) : gelu_tanh_f(z); };
+    auto df = [](float z) { return SILU ? silu_grad_f(z) : gelu_tanh_grad_f(z); };
     const int f8 = ff / 8;
     const long long n = rows * f8;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -68,8 +72,8 @@ __global__ void geglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const _
             const float g0 = bf16_lo(gw[j]), g1 = bf16_hi(gw[j]);
             const float u0 = bf16_lo(uw[j]), u1 = bf16_hi(uw[j]);
             const float d0 = bf16_lo(dw[j]), d1 = bf16_hi(dw[j]);
-            og[j] = pack_bf16(d0 * u0 * gelu_tanh_grad_f(g0), d1 * u1 * gelu_tanh_grad_f(g1));
-            ou[j] = pack_bf16(d0 * gelu_tanh_f(g0), d1 * gelu_tanh_f(g1));
+            og[j] = pack_bf16(d0 * u0 * df(g0), d1 * u1 * df(g1));
+            ou[j] = pack_bf16(d0 * f(g0), d1 * f(g1));
         }
         *reinterpret_cast<uint4*>(dgu + r * 2 * ff + c) = make_uint4(og[0], og[1], og[2], og[3]);
         *reinterpret_cast<uint4*>(dgu + r * 2 * ff + ff + c) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
@@ -295,15 +299,29 @@ extern "C" int pt_patchify(const float* pixels, void* cols_bf16, int B, int H, i
 extern "C" int pt_geglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream) {
     PT_REQUIRE(gu && act && rows > 0 && ff > 0 && ff % 8 == 0, "pt_geglu_fwd: bad arguments");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
-    geglu_fwd_kernel<<<grid_for(rows * (ff / 8), 256), 256, 0, ST(stream)>>>(CBF(gu), BF(act), rows, ff);
+    geglu_fwd_kernel<false><<<grid_for(rows * (ff / 8), 256), 256, 0, ST(stream)>>>(CBF(gu), BF(act), rows, ff);
     return check_launch("geglu_fwd");
+}
+
+extern "C" int pt_swiglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream) {
+    PT_REQUIRE(gu && act && rows > 0 && ff > 0 && ff % 8 == 0, "pt_swiglu_fwd: bad arguments");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    geglu_fwd_kernel<true><<<grid_for(rows * (ff / 8), 256), 256, 0, ST(stream)>>>(CBF(gu), BF(act), rows, ff);
+    return check_launch("swiglu_fwd");
 }
 
 extern "C" int pt_geglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, int ff, void* stream) {
     PT_REQUIRE(dact && gu && dgu && rows > 0 && ff > 0 && ff % 8 == 0, "pt_geglu_bwd: bad arguments");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
-    geglu_bwd_kernel<<<grid_for(rows * (ff / 8), 256), 256, 0, ST(stream)>>>(CBF(dact), CBF(gu), BF(dgu), rows, ff);
+    geglu_bwd_kernel<false><<<grid_for(rows * (ff / 8), 256), 256, 0, ST(stream)>>>(CBF(dact), CBF(gu), BF(dgu), rows, ff);
     return check_launch("geglu_bwd");
+}
+
+extern "C" int pt_swiglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, int ff, void* stream) {
+    PT_REQUIRE(dact && gu && dgu && rows > 0 && ff > 0 && ff % 8 == 0, "pt_swiglu_bwd: bad arguments");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    geglu_bwd_kernel<true><<<grid_for(rows * (ff / 8), 256), 256, 0, ST(stream)>>>(CBF(dact), CBF(gu), BF(dgu), rows, ff);
+    return check_launch("swiglu_bwd");
 }
 
 extern "C" int pt_gelu_erf_bwd(const void* dH, const void* Z, void* dZ, long long n, void* stream) {

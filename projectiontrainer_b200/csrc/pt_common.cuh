@@ -106,6 +106,33 @@ __device__ __forceinline__ void gelu_tanh_fast_both(float z, float& val, float& 
     const float r = z * fmaf(6.f * k0 * k1, z2, 2.f * k0);
     grad = a * fmaf(r, 1.f - a, 1.f);
 }
+// Gated-unit activation with the constants as data, so one GEMM epilogue serves GeGLU and SwiGLU:
+//   a = (1 + tanh u) / 2,  u = z (c0 + c1 z^2):  act = z a,  act' = a (1 + z (1 - a) (c2 + c3 z^2))
+// tanh-GELU: c = (k0, k0 k1, 2 k0, 6 k0 k1);  SiLU (sigmoid(z) = (1 + tanh(z / 2)) / 2): c = (0.5, 0, 1, 0).
+struct GluConsts { float c0, c1, c2, c3; };
+__host__ __device__ inline GluConsts glu_consts(bool silu) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    return silu ? GluConsts{0.5f, 0.f, 1.f, 0.f} : GluConsts{k0, k0 * k1, 2.f * k0, 6.f * k0 * k1};
+}
+__device__ __forceinline__ float glu_act_fast(float z, const GluConsts& c) {
+    const float u = z * fmaf(c.c1, z * z, c.c0);
+    const float h = 0.5f * z;
+    return fmaf(h, tanh_fast(u), h);
+}
+__device__ __forceinline__ void glu_act_fast_both(float z, const GluConsts& c, float& val, float& grad) {
+    const float z2 = z * z;
+    const float t = tanh_fast(z * fmaf(c.c1, z2, c.c0));
+    const float a = fmaf(0.5f, t, 0.5f);
+    val = z * a;
+    const float r = z * fmaf(c.c3, z2, c.c2);
+    grad = a * fmaf(r, 1.f - a, 1.f);
+}
+// exact SiLU for the unfused kernels
+__device__ __forceinline__ float silu_f(float z) { return z / (1.f + __expf(-z)); }
+__device__ __forceinline__ float silu_grad_f(float z) {
+    const float s = 1.f / (1.f + __expf(-z));
+    return s * (1.f + z * (1.f - s));
+}
 __device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 // exact erf-GELU (projector): 0.5 z (1 + erf(z / sqrt 2))
 __device__ __forceinline__ float gelu_erf_f(float z) {

@@ -66,15 +66,18 @@ class PackedGemma:
         bf = lambda t: t.detach().to(device=device, dtype=BF16).contiguous()
         f32 = lambda t: t.detach().to(device=device, dtype=F32).contiguous()
         self.embed = bf(W["embed"])
+        self.lm_head = bf(W["lm_head"]) if "lm_head" in W else self.embed     # tied unless the container says otherwise
         self.final_norm = f32(W["final_norm"])
-        # HF casts sqrt(hidden) to the embedding dtype before multiplying (modeling_gemma3.py:102-113)
-        self.embed_scale = float(torch.tensor(cfg.hidden ** 0.5, dtype=BF16).float())
+        # HF casts sqrt(hidden) to the embedding dtype before multiplying (modeling_gemma3.py:102-113);
+        # Qwen3 embeddings are not scaled
+        self.embed_scale = float(torch.tensor(cfg.hidden ** 0.5, dtype=BF16).float()) if cfg.scale_embed else 1.0
         self.layers = []
+        post = (lambda k: f32(W[k])) if cfg.sandwich_norm else (lambda k: None)
         for l in range(cfg.layers):
             p = f"l{l}."
             self.layers.append(dict(
-                in_norm=f32(W[p + "in_norm"]), post_attn_norm=f32(W[p + "post_attn_norm"]),
-                pre_ffn_norm=f32(W[p + "pre_ffn_norm"]), post_ffn_norm=f32(W[p + "post_ffn_norm"]),
+                in_norm=f32(W[p + "in_norm"]), post_attn_norm=post(p + "post_attn_norm"),
+                pre_ffn_norm=f32(W[p + "pre_ffn_norm"]), post_ffn_norm=post(p + "post_ffn_norm"),
                 q_norm=f32(W[p + "q_norm"]), k_norm=f32(W[p + "k_norm"]),
                 qkv_w=bf(W[p + "qkv_w"]), o_w=bf(W[p + "o_w"]),
                 gu_w=bf(W[p + "gu_w"]), down_w=bf(W[p + "down_w"])))
@@ -341,10 +344,10 @@ class Stage1Engine:
             # fused attention writes P only inside the causal / window band: its buffers start zero-filled
             P = self.buf(tag + ("Pz" if self.fuse_attn_fwd else "P"), (B * hq, S, ld), BF16, zero=self.fuse_attn_fwd)
             attn_o = self.buf(tag + "ao", (M, hq * hd), BF16)      # kept: delta = rowsum(dO * O) in the backward
-            y_attn = self.buf(tag + "ya", (M, h), BF16)
+            y_attn = self.buf(tag + "ya", (M, h), BF16) if c.sandwich_norm else None
             x1 = self.buf(tag + "x1", (M, h), F32)
             gu = self.buf(tag + "gu", (M, 2 * ff), BF16)
-            y_mlp = self.buf(tag + "ym", (M, h), BF16)
+            y_mlp = self.buf(tag + "ym", (M, h), BF16) if c.sandwich_norm else None
             x2 = self.buf(tag + ("x2" if save else f"x2_{li & 1}"), (M, h), F32)
             ops.linear(a, L["qkv_w"], out=qkv)
             ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, rope_rows, hq,
@@ -364,18 +367,27 @@ class Stage1Engine:
                              Cout=attn_o, ldc=hq * hd, nz=(G, hkv, B),
                              a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * QKV),
                              c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY, band_window=win)
-            ops.linear(attn_o, L["o_w"], out=y_attn)
-            ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            last = li == len(Lm.layers) - 1
+            if c.sandwich_norm:
+                ops.linear(attn_o, L["o_w"], out=y_attn)
+                ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            else:       # pre-norm decoder (Qwen3): the residual add rides the o-projection epilogue, in f32
+                ops.linear(attn_o, L["o_w"], out=x1, residual=x)
+                ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a, c.eps)
             if self.fuse_geglu:
-                ops.linear_geglu(a, L["gu_w"], gu, act)
+                ops.linear_geglu(a, L["gu_w"], gu, act, silu=c.silu)
             else:
                 ops.linear(a, L["gu_w"], out=gu)
-                ops.geglu_fwd(gu, act)
-            ops.linear(act, L["down_w"], out=y_mlp)
-            last = li == len(Lm.layers) - 1
-            ops.rmsnorm_residual_fwd(y_mlp, L["post_ffn_norm"], x1, x2,
-                                     None if last else Lm.layers[li + 1]["in_norm"],
-                                     None if last else a, c.eps)
+                ops.geglu_fwd(gu, act, silu=c.silu)
+            if c.sandwich_norm:
+                ops.linear(act, L["down_w"], out=y_mlp)
+                ops.rmsnorm_residual_fwd(y_mlp, L["post_ffn_norm"], x1, x2,
+                                         None if last else Lm.layers[li + 1]["in_norm"],
+                                         None if last else a, c.eps)
+            else:
+                ops.linear(act, L["down_w"], out=x2, residual=x1)
+                if not last:
+                    ops.rmsnorm_fwd(x2, Lm.layers[li + 1]["in_norm"], a, c.eps)
             if save:
                 sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ao=attn_o, ya=y_attn, x1=x1, gu=gu,
                                ym=y_mlp, full=full))
@@ -397,7 +409,7 @@ class Stage1Engine:
         yf = self.buf("l_yf", (R, h), BF16)
         ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(T, S, lab0))
         logits = self.buf("l_logits", (R, _pad8(c.vocab)), BF16)[:, :c.vocab]    # row stride padded to 16 B
-        ops.linear(yf, Lm.embed, out=logits)
+        ops.linear(yf, Lm.lm_head, out=logits)
         tgt = self.buf("l_tgt", (R,), torch.int32)
         # targets[b, lab0+t] for t in 0..T-1 -> compact [B*T] (int copy: plumbing, not arithmetic)
         tgt.view(B, T).copy_(targets.view(B, S)[:, lab0:lab0 + T])
@@ -418,7 +430,7 @@ class Stage1Engine:
         G, ld, QKV = self._attn_geometry(B, S)
         scale = c.q_scalar ** -0.5
         d_yf = self.buf("b_dyf", (R, h), BF16)
-        ops.linear_dgrad(s["logits"], Lm.embed, out=d_yf)          # dlogits @ E
+        ops.linear_dgrad(s["logits"], Lm.lm_head, out=d_yf)        # dlogits @ E
         dx = self.buf("b_dx", (M, h), F32)
         dx.zero_()
         grp = (T, S, s["lab0"])
@@ -433,25 +445,31 @@ class Stage1Engine:
         dq = self.buf("b_dq", (M, hq * hd), BF16)
         dk = self.buf("b_dk", (M, hkv * hd), BF16)
         d_qkv = self.buf("b_dqkv", (M, QKV), BF16)
-        pair = h <= 2560
+        sandwich = c.sandwich_norm
+        pair = sandwich and h <= 2560
         for li in range(len(Lm.layers) - 1, -1, -1):
             L, a = Lm.layers[li], s["layers"][li]
             cos_t, sin_t = self.rope(S, a["full"])
             # ---- MLP branch
-            if li == len(Lm.layers) - 1 or not pair:
+            if not sandwich:        # pre-norm decoder: the branch output's gradient is the stream's, as bf16
+                ops.cast_f32_bf16(dx, d_y)
+            elif li == len(Lm.layers) - 1 or not pair:
                 ops.rmsnorm_bwd(dx, a["ym"], L["post_ffn_norm"], d_y, c.eps)
             if self.fuse_geglu:
-                ops.linear_dgrad_geglu_bwd(d_y, L["down_w"], a["gu"], d_gu)
+                ops.linear_dgrad_geglu_bwd(d_y, L["down_w"], a["gu"], d_gu, silu=c.silu)
             else:
                 ops.linear_dgrad(d_y, L["down_w"], out=d_act)
-                ops.geglu_bwd(d_act, a["gu"], d_gu)
+                ops.geglu_bwd(d_act, a["gu"], d_gu, silu=c.silu)
             ops.linear_dgrad(d_gu, L["gu_w"], out=d_y)
             # ---- attention branch (pre-ffn norm backward + post-attention norm backward in one pass)
             if pair:
                 ops.rmsnorm_bwd_pair(d_y, a["x1"], L["pre_ffn_norm"], dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
             else:
                 ops.rmsnorm_bwd(d_y, a["x1"], L["pre_ffn_norm"], dx, c.eps, add=dx)
-                ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
+                if sandwich:
+                    ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
+                else:
+                    ops.cast_f32_bf16(dx, d_y)
             ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
             win = 0 if a["full"] else c.window
@@ -738,7 +756,7 @@ class Stage1Engine:
         yf = self.buf("i_yf", (B, c.hidden), BF16)
         ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(1, S, S - 1))
         logits = self.buf("i_logits", (B, _pad8(c.vocab)), F32)[:, :c.vocab]
-        ops.linear(yf, Lm.embed, out=logits)
+        ops.linear(yf, Lm.lm_head, out=logits)
         return logits
 
     @torch.no_grad()
@@ -801,18 +819,27 @@ class Stage1Engine:
             ops.gemm_raw(M=G, N=hd, K=n, A=P, lda=ld, B=V, b_off=lo * kvd, ldb=kvd, b_mn=True,
                          Cout=attn_o, ldc=hd, nz=(hkv, B, 1), a_zs=(G * ld, hq * ld, 0),
                          b_zs=(hd, Smax * kvd, 0), c_zs=(G * hd, hq * hd, 0))
-            ops.linear(attn_o, L["o_w"], out=y)
-            ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            last = li == len(Lm.layers) - 1
+            if c.sandwich_norm:
+                ops.linear(attn_o, L["o_w"], out=y)
+                ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            else:
+                ops.linear(attn_o, L["o_w"], out=x1, residual=x)
+                ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a, c.eps)
             if self.fuse_geglu:
-                ops.linear_geglu(a, L["gu_w"], gu, act)
+                ops.linear_geglu(a, L["gu_w"], gu, act, silu=c.silu)
             else:
                 ops.linear(a, L["gu_w"], out=gu)
-                ops.geglu_fwd(gu, act)
-            ops.linear(act, L["down_w"], out=y)
-            last = li == len(Lm.layers) - 1
-            ops.rmsnorm_residual_fwd(y, L["post_ffn_norm"], x1, x,
-                                     None if last else Lm.layers[li + 1]["in_norm"],
-                                     None if last else a, c.eps)
+                ops.geglu_fwd(gu, act, silu=c.silu)
+            if c.sandwich_norm:
+                ops.linear(act, L["down_w"], out=y)
+                ops.rmsnorm_residual_fwd(y, L["post_ffn_norm"], x1, x,
+                                         None if last else Lm.layers[li + 1]["in_norm"],
+                                         None if last else a, c.eps)
+            else:
+                ops.linear(act, L["down_w"], out=x, residual=x1)
+                if not last:
+                    ops.rmsnorm_fwd(x, Lm.layers[li + 1]["in_norm"], a, c.eps)
         kc["pos"] = pos + 1
         if next_pos is not None:
             kc["next_pos"] = next_pos + 1

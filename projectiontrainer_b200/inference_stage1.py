@@ -70,7 +70,7 @@ def load_projector_state(projection_path: str) -> tuple[dict, dict]:
 
 def build_engine_from_hf(vision_encoder, llm_model, projection_layer: MLPProjector, device) -> Stage1Engine:
     vis = PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), device)
-    llm = PackedGemma(*Wt.gemma_from_hf(llm_model), device)
+    llm = PackedGemma(*Wt.llm_from_hf(llm_model), device)
     proj = ProjectorState({k: v.detach().float() for k, v in projection_layer.state_dict().items()}, device)
     return Stage1Engine(vis, llm, proj, device)
 

@@ -12,7 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import BAND_K_BY_KEY, BAND_K_BY_QUERY, BAND_NONE, BAND_SCORES  # noqa: F401
-from ._lib import ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
+from ._lib import ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
@@ -129,22 +129,23 @@ def geglu_fusable(ff: int) -> bool:
     return ff % 128 == 0
 
 
-def linear_geglu(x: torch.Tensor, w_gu: torch.Tensor, gu: torch.Tensor, act: torch.Tensor):
+def linear_geglu(x: torch.Tensor, w_gu: torch.Tensor, gu: torch.Tensor, act: torch.Tensor, silu: bool = False):
     """gu[M,2ff] = x @ w_gu^T (gate | up pre-activations, kept for the backward) and, in the same
     epilogue, act[M,ff] = gelu_tanh(gate) * up   (HF:models/gemma3/modeling_gemma3.py:127-129)."""
     M, K = x.shape
     N = w_gu.shape[0]
     gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w_gu, ldb=w_gu.stride(0), Cout=gu, ldc=gu.stride(0),
-             act=ACT_GEGLU, aux=act, ld_aux=act.stride(0))
+             act=ACT_SWIGLU if silu else ACT_GEGLU, aux=act, ld_aux=act.stride(0))
 
 
-def linear_dgrad_geglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, d_gu: torch.Tensor):
+def linear_dgrad_geglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, d_gu: torch.Tensor,
+                           silu: bool = False):
     """d_act = dy[M,h] @ w_down[h,ff] formed in TMEM only; the epilogue turns it into
     d_gu[M,2ff] = [d_act * up * gelu_tanh'(gate) | d_act * gelu_tanh(gate)] reading the saved gu."""
     M, N = dy.shape
     ff = w_down.shape[1]
     gemm_raw(M=M, N=ff, K=N, A=dy, lda=dy.stride(0), B=w_down, ldb=w_down.stride(0), b_mn=True, Cout=d_gu,
-             ldc=d_gu.stride(0), act=ACT_GEGLU_BWD, aux=gu, ld_aux=gu.stride(0))
+             ldc=d_gu.stride(0), act=ACT_SWIGLU_BWD if silu else ACT_GEGLU_BWD, aux=gu, ld_aux=gu.stride(0))
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None) -> torch.Tensor:
@@ -260,14 +261,14 @@ def attn_delta(dO, O, delta, S, hq, hd):
     _lib.call("pt_attn_delta", _ptr(dO), _ptr(O), _ptr(delta), dO.shape[0], int(S), int(hq), int(hd), _stream())
 
 
-def geglu_fwd(gu, act):
+def geglu_fwd(gu, act, silu=False):
     _req_cuda(gu, act)
-    _lib.call("pt_geglu_fwd", _ptr(gu), _ptr(act), C.c_longlong(gu.shape[0]), act.shape[1], _stream())
+    _lib.call("pt_swiglu_fwd" if silu else "pt_geglu_fwd", _ptr(gu), _ptr(act), C.c_longlong(gu.shape[0]), act.shape[1], _stream())
 
 
-def geglu_bwd(dact, gu, dgu):
+def geglu_bwd(dact, gu, dgu, silu=False):
     _req_cuda(dact, gu, dgu)
-    _lib.call("pt_geglu_bwd", _ptr(dact), _ptr(gu), _ptr(dgu), C.c_longlong(gu.shape[0]),
+    _lib.call("pt_swiglu_bwd" if silu else "pt_geglu_bwd", _ptr(dact), _ptr(gu), _ptr(dgu), C.c_longlong(gu.shape[0]),
               dact.shape[1], _stream())
 
 

@@ -117,7 +117,7 @@ class ProjectionTrainerStage1:
         vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
             PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), self.device)
         llm = language_model if isinstance(language_model, PackedGemma) else \
-            PackedGemma(*Wt.gemma_from_hf(language_model), self.device)
+            PackedGemma(*Wt.llm_from_hf(language_model), self.device)
         if isinstance(projection_layer, nn.Module):
             projection_layer.to(self.device).float()
             projection_layer.requires_grad_(True)

@@ -17,7 +17,7 @@ import torch
 from torch.utils.data import Dataset
 
 from .accelerator_setup import setup_accelerator_and_logging
-from .config import GEMMA3_1B, GEMMA3_4B, SIGLIP_L
+from .config import GEMMA3_1B, GEMMA3_4B, QWEN3_8B, SIGLIP_L
 from .projector_trainer import ProjectionTrainerStage1
 from .projectors import MLPProjector
 
@@ -127,7 +127,7 @@ def build_parser():
     p.add_argument("--gpu_preprocess", action="store_true",
                    help="resize / rescale / normalize the decoded images on the GPU (Pillow-exact) instead of in the workers")
     p.add_argument("--synthetic", type=int, default=0, help="train on N synthetic samples with random-init models")
-    p.add_argument("--synthetic_llm", choices=["1b", "4b"], default="1b")
+    p.add_argument("--synthetic_llm", choices=["1b", "4b", "qwen3_8b"], default="1b")
     p.add_argument("--max_length", type=int, default=512, help="caption tokens (the reference's dataset default)")
     return p
 
@@ -141,7 +141,7 @@ def main(argv=None):
     if args.synthetic > 0:
         from .engine import PackedGemma, PackedSiglip
         from . import weights as Wt
-        lc = GEMMA3_1B if args.synthetic_llm == "1b" else GEMMA3_4B
+        lc = {"1b": GEMMA3_1B, "4b": GEMMA3_4B, "qwen3_8b": QWEN3_8B}[args.synthetic_llm]
         vc, dev = SIGLIP_L, accelerator.device
         vision_encoder = PackedSiglip(Wt.random_siglip(vc, dev, 0), vc, dev)
         language_model = PackedGemma(Wt.random_gemma(lc, dev, 0), lc, dev)

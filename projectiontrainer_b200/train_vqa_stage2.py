@@ -19,7 +19,7 @@ import os
 import torch
 
 from .accelerator_setup import setup_accelerator_and_logging
-from .config import GEMMA3_1B, GEMMA3_4B, SIGLIP_L
+from .config import GEMMA3_1B, GEMMA3_4B, QWEN3_8B, SIGLIP_L
 from .projectors import MLPProjector
 from .vqa_dataset import SyntheticVQADataset, XrayVQADataset
 from .vqa_trainer import VQATrainerStage2
@@ -89,7 +89,7 @@ def build_parser():
     p.add_argument("--gpu_preprocess", action="store_true",
                    help="resize / rescale / normalize the decoded images on the GPU (Pillow-exact) instead of in the workers")
     p.add_argument("--synthetic", type=int, default=0, help="train on N synthetic triplets with random-init models")
-    p.add_argument("--synthetic_llm", choices=["1b", "4b"], default="1b")
+    p.add_argument("--synthetic_llm", choices=["1b", "4b", "qwen3_8b"], default="1b")
     return p
 
 
@@ -103,7 +103,7 @@ def main(argv=None):
     if args.synthetic > 0:
         from . import weights as Wt
         from .engine import PackedGemma, PackedSiglip
-        lc = GEMMA3_1B if args.synthetic_llm == "1b" else GEMMA3_4B
+        lc = {"1b": GEMMA3_1B, "4b": GEMMA3_4B, "qwen3_8b": QWEN3_8B}[args.synthetic_llm]
         vc, dev = SIGLIP_L, accelerator.device
         vision_encoder = PackedSiglip(Wt.random_siglip(vc, dev, 0), vc, dev)
         language_model = PackedGemma(Wt.random_gemma(lc, dev, 0), lc, dev)
@@ -116,8 +116,6 @@ def main(argv=None):
         if not (args.image_root and args.train_json and args.val_json and args.stage1_projector_path):
             raise SystemExit("--image_root, --train_json, --val_json and --stage1_projector_path are required "
                              "(or use --synthetic N)")
-        if "gemma-3" not in args.llm_name.lower() and "gemma3" not in args.llm_name.lower():
-            raise SystemExit(f"--llm_name {args.llm_name}: only the Gemma3 decoder recipe is built (SURVEY.md §8f rank 4)")
         from transformers import AutoModel, AutoModelForCausalLM, AutoProcessor, AutoTokenizer
         processor = AutoProcessor.from_pretrained(args.vision_model_name)
         vision_encoder = AutoModel.from_pretrained(args.vision_model_name, torch_dtype=torch.bfloat16)

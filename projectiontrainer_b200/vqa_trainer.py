@@ -139,7 +139,7 @@ class VQATrainerStage2:
         vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
             PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), self.device)
         llm = language_model if isinstance(language_model, PackedGemma) else \
-            PackedGemma(*Wt.gemma_from_hf(language_model), self.device)
+            PackedGemma(*Wt.llm_from_hf(language_model), self.device)
         if isinstance(projection_layer, nn.Module):
             projection_layer.to(self.device).float()      # fp32 master weights (the reference casts the
             projection_layer.requires_grad_(True)         # projector to bf16 under mixed precision: :288)

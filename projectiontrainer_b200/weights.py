@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import torch
 
-from .config import GemmaCfg, SiglipCfg, gemma_cfg_from_hf, siglip_cfg_from_hf
+from .config import GemmaCfg, SiglipCfg, gemma_cfg_from_hf, qwen3_cfg_from_hf, siglip_cfg_from_hf
 
 
 def siglip_from_hf(vision_model) -> tuple[dict, SiglipCfg]:
@@ -56,6 +56,41 @@ def gemma_from_hf(causal_lm) -> tuple[dict, GemmaCfg]:
     return W, cfg
 
 
+def qwen3_from_hf(causal_lm) -> tuple[dict, GemmaCfg]:
+    """causal_lm: HF Qwen3ForCausalLM (what AutoModelForCausalLM returns for Qwen/Qwen3-*, the LLM of
+    ref:Stage1/run_projection_train_stage1.sh:12).  Qwen3RMSNorm multiplies by `weight`, the norm kernels by
+    (1 + gain): gains are packed as weight - 1.  `input_layernorm` -> in_norm, `post_attention_layernorm` ->
+    pre_ffn_norm (it is the MLP's pre-norm); there are no norms on the branch outputs."""
+    cfg = qwen3_cfg_from_hf(causal_lm.config)
+    sd = {k: v.detach() for k, v in causal_lm.state_dict().items()}
+    m1 = lambda t: t.float() - 1.0
+    W = {"embed": sd["model.embed_tokens.weight"], "final_norm": m1(sd["model.norm.weight"])}
+    head = sd.get("lm_head.weight")
+    if head is not None and head.data_ptr() != W["embed"].data_ptr() and not torch.equal(head, W["embed"]):
+        W["lm_head"] = head
+        cfg.tie_lm_head = False
+    else:
+        cfg.tie_lm_head = True
+    for l in range(cfg.layers):
+        s, p = f"model.layers.{l}.", f"l{l}."
+        W[p + "in_norm"] = m1(sd[s + "input_layernorm.weight"])
+        W[p + "pre_ffn_norm"] = m1(sd[s + "post_attention_layernorm.weight"])
+        W[p + "q_norm"], W[p + "k_norm"] = m1(sd[s + "self_attn.q_norm.weight"]), m1(sd[s + "self_attn.k_norm.weight"])
+        W[p + "qkv_w"] = torch.cat([sd[s + f"self_attn.{n}_proj.weight"] for n in "qkv"], 0)
+        W[p + "o_w"] = sd[s + "self_attn.o_proj.weight"]
+        W[p + "gu_w"] = torch.cat([sd[s + "mlp.gate_proj.weight"], sd[s + "mlp.up_proj.weight"]], 0)
+        W[p + "down_w"] = sd[s + "mlp.down_proj.weight"]
+    return W, cfg
+
+
+def llm_from_hf(causal_lm) -> tuple[dict, GemmaCfg]:
+    """Dispatch on the HF model type: Gemma3 text and Qwen3 dense decoders; anything else raises."""
+    mt = getattr(causal_lm.config, "model_type", None)
+    if mt == "qwen3":
+        return qwen3_from_hf(causal_lm)
+    return gemma_from_hf(causal_lm)
+
+
 # ----------------------------------------------------------------------------- synthetic weights
 def _r(gen, device, *shape, std=0.02):
     return torch.randn(*shape, generator=gen, device=device, dtype=torch.float32) * std
@@ -83,9 +118,12 @@ def random_gemma(cfg: GemmaCfg, device, seed: int = 0) -> dict:
     g = torch.Generator(device=device).manual_seed(seed + 1)
     h = cfg.hidden
     W = {"embed": _r(g, device, cfg.vocab, h).to(torch.bfloat16), "final_norm": _r(g, device, h, std=0.3)}
+    if not cfg.tie_lm_head:
+        W["lm_head"] = _r(g, device, cfg.vocab, h).to(torch.bfloat16)
     for l in range(cfg.layers):
         p = f"l{l}."
-        for n in ("in_norm", "post_attn_norm", "pre_ffn_norm", "post_ffn_norm"):
+        for n in (("in_norm", "post_attn_norm", "pre_ffn_norm", "post_ffn_norm") if cfg.sandwich_norm
+                  else ("in_norm", "pre_ffn_norm")):
             W[p + n] = _r(g, device, h, std=0.3)
         W[p + "q_norm"], W[p + "k_norm"] = _r(g, device, cfg.hd, std=0.3), _r(g, device, cfg.hd, std=0.3)
         W[p + "qkv_w"] = _r(g, device, (cfg.hq + 2 * cfg.hkv) * cfg.hd, h).to(torch.bfloat16)

@@ -134,3 +134,26 @@ def test_two_process_allreduce_and_gather_gloo():
     for rank, mean, losses in res:
         assert mean == 1.5                      # mean over ranks of per-rank gradients (DDP semantics)
         assert losses == [10.0, 11.0]
+
+
+def test_qwen3_container_is_repacked_like_the_oracle_names_it():
+    """weights.llm_from_hf on an HF Qwen3ForCausalLM: gains packed as weight - 1, post_attention_layernorm is the
+    MLP's pre-norm, untied head kept, config recipe flags set; and unsupported variants raise."""
+    import torch
+    from oracle import stage1_oracle as O
+    from oracle.make_golden import CASES, build_hf_qwen3
+    from projectiontrainer_b200 import weights as Wt
+    lkw = CASES["tiny_qwen3_gqa"][1]
+    olc = O.GemmaCfg(**lkw)
+    Wl = O.init_gemma(olc)
+    hf = build_hf_qwen3(olc, Wl)
+    W, cfg = Wt.llm_from_hf(hf)
+    assert (cfg.sandwich_norm, cfg.silu, cfg.scale_embed, cfg.tie_lm_head, cfg.pattern) == (False, True, False, False, 1)
+    assert (cfg.hq, cfg.hkv, cfg.hd, cfg.ff, cfg.q_scalar) == (olc.hq, olc.hkv, olc.hd, olc.ff, float(olc.hd))
+    assert all(cfg.is_full(i) for i in range(cfg.layers))
+    assert set(W) == set(Wl)
+    for k in Wl:
+        assert torch.allclose(W[k].float(), Wl[k], atol=1e-7), k
+    hf.config.use_sliding_window = True
+    with pytest.raises(RuntimeError, match="sliding"):
+        Wt.llm_from_hf(hf)

@@ -1,7 +1,7 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_image_gpu.py -q > gpurun_out/t24_tests.log 2>&1
-echo "exit $?" >> gpurun_out/t24_tests.log
-timeout 300 python tools/bench_image.py > gpurun_out/t24_image_bench.json 2> gpurun_out/t24_image_bench.err
-timeout 120 python tools/image_one.py && timeout 300 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -k regex:resample --csv --log-file gpurun_out/t24_image_ncu.csv python tools/image_one.py > gpurun_out/t24_ncu.log 2>&1
+timeout 1500 python -m pytest tests -q -m gpu > gpurun_out/t25_all_tests.log 2>&1
+echo "exit $?" >> gpurun_out/t25_all_tests.log
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t25_bench.json 2> gpurun_out/t25_bench.err
+timeout 600 python tools/bench_qwen3.py > gpurun_out/t25_qwen3.json 2> gpurun_out/t25_qwen3.err
