@@ -21,6 +21,9 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
+# stdout carries the one JSON line: NCCL's own banner ("NCCL version ...", printed at communicator creation when
+# NCCL_DEBUG is VERSION or higher) goes to stderr instead
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 METRIC = "stage1_projector_train_images_per_sec"
 UNIT = "images/s"

@@ -1,7 +1,6 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -q -m gpu > gpurun_out/t25_all_tests.log 2>&1
-echo "exit $?" >> gpurun_out/t25_all_tests.log
-timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t25_bench.json 2> gpurun_out/t25_bench.err
-timeout 600 python tools/bench_qwen3.py > gpurun_out/t25_qwen3.json 2> gpurun_out/t25_qwen3.err
+timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29577 bench.py --gpus 8 --steps 6 --warmup 3 --no-cpu-baseline > gpurun_out/t26_bench_8gpu.json 2> gpurun_out/t26_bench_8gpu.err
+echo "exit $?" >> gpurun_out/t26_bench_8gpu.err
+tail -5 gpurun_out/t26_bench_8gpu.err
