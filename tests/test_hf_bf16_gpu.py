@@ -1,0 +1,73 @@
+"""Second parity witness on the GPU box: the same HF modules the reference drives, holding the same
+weights, run ON THE B200 in bf16 under torch.autocast with an fp32 spliced sequence (what `accelerate launch
+--mixed_precision bf16` gives the reference) — cuBLASLt / SDPA library kernels, torch autograd.  The
+engine must agree with it on the loss to 1e-2 rel; on the projector gradients both sides carry bf16 noise of their own
+(the north_star bound of 0.999 is against the fp32 reference, tests/test_step_gpu.py), so the cosine bound here is 0.997
+for the weight matrices and 0.99 for the small bias vectors.  GPU only."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float(torch.dot(a, b) / (a.norm() * b.norm()))
+
+
+def _hf_step(vision, llm, proj, px, ids, labels, pad_id, scale_embed):
+    """ref:Stage1/projector_trainer.py:157-237 under bf16 autocast."""
+    dev = px.device
+    B = px.shape[0]
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        with torch.no_grad():
+            patch = vision.vision_model(pixel_values=px.to(torch.bfloat16)).last_hidden_state[:, 1:, :]
+        projected = proj(patch).float()
+        with torch.no_grad():
+            text = llm.get_input_embeddings()(ids)
+        inputs = torch.cat([projected, text.to(projected.dtype)], dim=1)
+        n_img = projected.shape[1]
+        mask = torch.cat([torch.ones(B, n_img, dtype=torch.long, device=dev), (ids != pad_id).long()], dim=1)
+        lm_labels = torch.cat([torch.full((B, n_img), -100, dtype=torch.long, device=dev), labels], dim=1)
+        loss = llm(inputs_embeds=inputs, attention_mask=mask, labels=lm_labels, return_dict=True).loss
+    loss.backward()
+    return float(loss), {k: p.grad.detach().float().cpu() for k, p in proj.named_parameters()}
+
+
+@pytest.mark.parametrize("family", ["gemma3_hd256", "qwen3_hd128"])
+def test_engine_matches_hf_bf16_autocast_on_the_same_gpu(cuda_dev, family):
+    from oracle import stage1_oracle as O
+    from oracle.make_golden import build_hf_gemma, build_hf_qwen3, build_hf_siglip
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.projectors import MLPProjector
+    vkw = dict(hidden=128, ff=256, layers=2, heads=2, image=160, patch=16)
+    if family == "gemma3_hd256":
+        lkw = dict(vocab=1024, hidden=256, ff=256, layers=7, hq=4, hkv=2, hd=256, window=40, q_scalar=256.0,
+                   rope_factor_global=8.0)
+    else:
+        lkw = dict(vocab=1024, hidden=256, ff=384, layers=4, hq=8, hkv=2, hd=128, window=0, q_scalar=128.0, pattern=1,
+                   sandwich_norm=False, silu=True, scale_embed=False, tie_lm_head=False)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    px, ids, lab = O.synthetic_batch(3, 48, ovc, olc, left_pad=True)
+    vision = build_hf_siglip(ovc, Wv).to(cuda_dev, torch.bfloat16)
+    llm = (build_hf_gemma(olc, Wl) if olc.sandwich_norm else build_hf_qwen3(olc, Wl)).to(cuda_dev, torch.bfloat16)
+    for m in (vision, llm):
+        m.requires_grad_(False)
+    proj = MLPProjector(ovc.hidden, olc.hidden)
+    proj.load_state_dict(P)
+    hf_proj = torch.nn.Sequential(torch.nn.Linear(ovc.hidden, 10 * ovc.hidden), torch.nn.GELU(),
+                                  torch.nn.Linear(10 * ovc.hidden, olc.hidden)).to(cuda_dev)
+    hf_proj.load_state_dict({k.replace("model.", ""): v for k, v in P.items()})
+    ref_loss, ref_g = _hf_step(vision, llm, hf_proj, px.to(cuda_dev), ids.to(cuda_dev), lab.to(cuda_dev), olc.pad_id,
+                               olc.scale_embed)
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev)
+    loss = eng.forward_backward(px.to(cuda_dev), ids.to(cuda_dev), lab.to(cuda_dev), olc.pad_id)
+    torch.cuda.synchronize()
+    assert abs(loss.item() - ref_loss) / ref_loss < 1e-2, (loss.item(), ref_loss)
+    names = {"model.0.weight": "0.weight", "model.0.bias": "0.bias", "model.2.weight": "2.weight", "model.2.bias": "2.bias"}
+    for k, gr in eng.proj.grads().items():
+        c = _cos(gr.cpu(), ref_g[names[k]])
+        assert c > (0.997 if gr.numel() > 4096 else 0.99), (k, c)
