@@ -216,3 +216,68 @@ def test_generate_with_left_padded_prompt_matches_hf_golden(cuda_dev):
     out = eng.generate(px, ids[:, :Tp], max_new_tokens=new, do_sample=False, pad_token_id=olc.pad_id, eos_token_id=1,
                        prompt_pad_id=olc.pad_id)
     assert out.shape[0] == B and out.shape[1] <= new
+
+
+def test_vqa_trainer_dropin_end_to_end_tiny(cuda_dev, tmp_path):
+    """`VQATrainerStage2` + `vqa_collate_fn` through the real DataLoader (workers, pinned memory, look-ahead staging):
+    optimizer steps happen exactly on accelerate's sync micro-batches, the logged learning rates follow the cosine
+    schedule, every logged loss equals the oracle's for the micro-batch the loader actually drew (same parameters on
+    the first window), evaluation writes its loss and examples, and the checkpoint loads back through the Stage-2
+    script's own loader."""
+    import json
+    from oracle import stage1_oracle as O
+    from oracle import stage2_oracle as O2
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.accelerator_setup import Stage1Accelerator
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.projectors import MLPProjector
+    from projectiontrainer_b200.train_vqa_stage2 import load_pretrained_projector
+    from projectiontrainer_b200.vqa_trainer import VQATrainerStage2
+    g, vkw, lkw, ovc, olc, Wv, Wl, P, train, val = _load("vqa_tiny_right_gqa")
+    px, qs, as_ = train
+    seen = []
+
+    class DS(torch.utils.data.Dataset):
+        def __init__(self, s): self.s = s
+        def __len__(self): return len(self.s[1])
+        def __getitem__(self, i):
+            return {"pixel_values": self.s[0][i], "question_input_ids": self.s[1][i], "answer_input_ids": self.s[2][i]}
+
+    proj = MLPProjector(ovc.hidden, olc.hidden)
+    proj.load_state_dict(P)
+    GA, B, epochs = 2, 2, 2
+    acc = Stage1Accelerator(gradient_accumulation_steps=GA, device=cuda_dev)
+    tok = _Tok(olc.pad_id, "right")
+    tr = VQATrainerStage2(acc, E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                          proj, tok, DS(train), DS(val), str(tmp_path), B, 1e-3, 0.01, epochs, GA, 0.25,
+                          freeze_vision_encoder=True, freeze_projection_layer=False, freeze_llm=True, enable_qlora=False,
+                          train_ve_first_epoch=False, wandb_project="none")
+    assert tr.engine.loss_divisor == GA * GA and tr.max_train_steps == epochs * 2 and tr.num_warmup_steps == 1
+    orig = tr._step_inputs
+    tr._step_inputs = lambda b: (seen.append(b), orig(b))[1]
+    real_eval = tr.evaluate
+    tr.evaluate = lambda ep, gs: real_eval(ep, gs, max_new_tokens=4)
+    tr.train()
+    micro = [v for s, v in acc.logged if "train/batch_loss" in v]
+    steps = [v for v in micro if "train/step_loss" in v]
+    assert len(micro) == 6 and len(steps) == 4                      # 3 micro-batches per epoch, sync on the 2nd and 3rd
+    assert ["train/step_loss" in v for v in micro] == O2.sync_flags(3, GA) * epochs
+    for i, v in enumerate(steps):
+        assert abs(v["train/learning_rate"] - O.cosine_lr(i + 1, 1e-3, 1, 4)) < 1e-12 and v["step"] == i + 1
+    # first accumulation window = the initial parameters: the logged losses are the oracle's for the drawn batches
+    train_batches = [b for b in seen if b["question_input_ids"].shape[0] and "answer_input_ids" in b][:2]
+    for v, b in zip(micro[:2], train_batches):
+        ref = O2.vqa_micro_step(b["pixel_values"], b["question_input_ids"], b["answer_input_ids"], Wv, P, Wl, ovc, olc)
+        assert abs(v["train/batch_loss"] - ref["loss"]) / ref["loss"] < 1e-2
+    vals = [v["val/loss"] for s, v in acc.logged if "val/loss" in v]
+    assert len(vals) == epochs and all(5.0 < x < 7.5 for x in vals)
+    assert tok.padding_side == "right"                               # evaluation restores it (ref :675)
+    ex = (tmp_path / "validation_examples" / "epoch_2_examples.txt").read_text()
+    assert "Question:" in ex and "Prediction:" in ex
+    assert "Validation Examples for Epoch 1" in (tmp_path / "validation_examples" / "all_validation_examples.txt").read_text()
+    ck = tmp_path / "checkpoint-epoch_2" / "projection_layer"
+    assert json.loads((ck / "projector_config.json").read_text()) == {"vision_dim": ovc.hidden, "llm_dim": olc.hidden}
+    back = load_pretrained_projector(str(ck))
+    for k, p in proj.state_dict().items():
+        assert torch.equal(back.state_dict()[k], p.cpu())
+        assert not torch.equal(p.cpu(), P[k])                        # and it did train
