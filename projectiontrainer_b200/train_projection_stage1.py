@@ -30,7 +30,7 @@ class XrayTextPairDataset(Dataset):
     token_ids i64 [max_length] (tokenizer padded to max_length), labels = token_ids with pad -> -100."""
 
     def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_length=512, image_root_2=None,
-                 gpu_preprocess=False):
+                 gpu_preprocess=False, cache_tokens=False):
         # gpu_preprocess (an addition): items carry the decoded image as `images_u8` uint8 [H, W, 3]; resize +
         # rescale + normalize run on the GPU in the trainer's look-ahead stage (Pillow-exact kernels)
         self.gpu_preprocess = gpu_preprocess
@@ -40,8 +40,29 @@ class XrayTextPairDataset(Dataset):
         if json_file:
             with open(json_file, "r", encoding="utf-8") as f:
                 self.samples = json.load(f)
+        # cache_tokens (an addition): captions are tokenised once, on first use after the
+        # sample list is final, into one int64 matrix that forked DataLoader workers share, instead of once per
+        # epoch per sample inside the workers
+        self.cache_tokens, self._token_matrix = cache_tokens, None
+
+    def _tokens(self, idx):
+        if not self.cache_tokens:
+            return self.tokenizer(self.samples[idx]["normal_caption"], max_length=self.max_length,
+                                  padding="max_length", truncation=True, return_tensors="pt").input_ids.squeeze(0)
+        self._ensure_tokens()
+        return self._token_matrix[idx].clone()
+
+    def _ensure_tokens(self):
+        if self.cache_tokens and self.samples and (self._token_matrix is None or
+                                                   self._token_matrix.shape[0] != len(self.samples)):
+            enc = self.tokenizer([s["normal_caption"] for s in self.samples], max_length=self.max_length,
+                                 padding="max_length", truncation=True, return_tensors="pt")
+            self._token_matrix = enc.input_ids.contiguous().share_memory_()
 
     def __len__(self):
+        # the trainer sizes its schedule from len(loader) in the parent process, before any worker is forked:
+        # building the cache here makes every worker inherit it instead of rebuilding it
+        self._ensure_tokens()
         return len(self.samples)
 
     def _resolve(self, name):
@@ -62,9 +83,7 @@ class XrayTextPairDataset(Dataset):
         from PIL import Image
         sample = self.samples[idx]
         image = Image.open(self._resolve(sample["image"])).convert("RGB")
-        text = self.tokenizer(sample["normal_caption"], max_length=self.max_length, padding="max_length",
-                              truncation=True, return_tensors="pt")
-        token_ids = text.input_ids.squeeze(0)
+        token_ids = self._tokens(idx)
         labels = token_ids.clone()
         if self.tokenizer.pad_token_id is not None:
             labels[labels == self.tokenizer.pad_token_id] = -100
@@ -126,6 +145,7 @@ def build_parser():
     p.add_argument("--enable_qlora", action="store_true")
     p.add_argument("--gpu_preprocess", action="store_true",
                    help="resize / rescale / normalize the decoded images on the GPU (Pillow-exact) instead of in the workers")
+    p.add_argument("--cache_tokens", action="store_true", help="tokenise every caption once instead of once per epoch")
     p.add_argument("--synthetic", type=int, default=0, help="train on N synthetic samples with random-init models")
     p.add_argument("--synthetic_llm", choices=["1b", "4b", "qwen3_8b"], default="1b")
     p.add_argument("--max_length", type=int, default=512, help="caption tokens (the reference's dataset default)")
@@ -163,18 +183,22 @@ def main(argv=None):
         vision_dim = vision_encoder.config.vision_config.hidden_size
         llm_dim = language_model.config.hidden_size
         full = XrayTextPairDataset(args.image_root, args.train_json, processor, tokenizer, args.img_size,
-                                   max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
+                                   max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                   cache_tokens=args.cache_tokens)
         train_dataset, val_dataset = full, None
         if args.val_json:
             val_dataset = XrayTextPairDataset(args.image_root, args.val_json, processor, tokenizer, args.img_size,
-                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
+                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                   cache_tokens=args.cache_tokens)
         elif args.train_val_split > 0:
             from sklearn.model_selection import train_test_split
             tr, va = train_test_split(full.samples, test_size=args.train_val_split, random_state=42)
             train_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
-                                                max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
+                                                max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                   cache_tokens=args.cache_tokens)
             val_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
-                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
+                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                   cache_tokens=args.cache_tokens)
             train_dataset.samples, val_dataset.samples = tr, va
         if len(train_dataset) == 0:
             logger.error("Training dataset is empty.")

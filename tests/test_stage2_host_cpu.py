@@ -98,3 +98,31 @@ def test_collates_keep_decoded_images_as_lists():
     st = vqa_step_inputs(cb, 0, 4)
     assert st["images_u8"] is cb["images_u8"] and st["token_ids"].tolist() == [[5, 6, 2, 7, 8, 0, 0, 0], [0, 9, 0, 0, 2, 0, 0, 0]]
     assert st["labels"].tolist() == [[-100, -100, 2, 7, 8, -100, -100, -100], [-100] * 4 + [2, -100, -100, -100]]
+
+
+def test_stage1_dataset_token_cache_matches_lazy_tokenisation(tmp_path):
+    """cache_tokens=True: one batched tokenizer call, same ids as the per-item path, shared with workers."""
+    import json as _json
+    from projectiontrainer_b200.train_projection_stage1 import XrayTextPairDataset
+
+    class WordTok:
+        pad_token_id, calls = 0, 0
+
+        def __call__(self, text, max_length, padding, truncation, return_tensors):
+            WordTok.calls += 1
+            texts = [text] if isinstance(text, str) else text
+            rows = []
+            for t in texts:
+                ids = [2] + [3 + (hash(w) % 97) for w in t.split()][: max_length - 1]
+                rows.append([0] * (max_length - len(ids)) + ids)
+            return type("Enc", (), {"input_ids": torch.tensor(rows)})()
+
+    js = tmp_path / "d.json"
+    js.write_text(_json.dumps([{"image": f"{i}.png", "normal_caption": "lungs are clear " * (i + 1)} for i in range(5)]))
+    lazy = XrayTextPairDataset(str(tmp_path), str(js), None, WordTok(), 8, max_length=12)
+    cached = XrayTextPairDataset(str(tmp_path), str(js), None, WordTok(), 8, max_length=12, cache_tokens=True)
+    WordTok.calls = 0
+    assert len(cached) == 5 and WordTok.calls == 1 and cached._token_matrix.is_shared()
+    for i in range(5):
+        assert torch.equal(cached._tokens(i), lazy._tokens(i))
+    assert WordTok.calls == 1 + 5
