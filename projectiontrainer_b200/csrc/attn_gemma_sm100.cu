@@ -1,4 +1,5 @@
-// Fused causal / sliding-window GQA attention forward for the Gemma3 decoder (head_dim 256):
+// Fused causal / sliding-window GQA attention forward for the Gemma3 decoder (head_dim 256; also instantiated
+// for head_dim 128, the Qwen3 geometry):
 //     P = softmax(mask(Q K^T * scale)),  O = P V       HF:models/gemma3/modeling_gemma3.py:278-300,370-384
 // Replaces (band GEMM -> f32 scores in HBM -> softmax kernel -> bf16 P -> band GEMM): the scores never leave
 // TMEM.  The normalised probabilities P ARE written (bf16), because the input-gradient backward reads them
@@ -22,12 +23,10 @@ namespace pt {
 
 constexpr int kGqRows = 128;
 constexpr int kGkTile = 64;
-constexpr int kGhd = 256;
 constexpr int kGthreads = 192;
-constexpr int kGqBytes = kGqRows * kGhd * 2;        // 64 KB: 4 slabs (64 columns) of 128 rows x 128 B
-constexpr int kGkvBytes = kGkTile * kGhd * 2;       // 32 KB: 4 slabs of 64 rows x 128 B
 constexpr int kGpBytes = kGqRows * kGkTile * 2;     // 16 KB
-constexpr int kGsmem = kGqBytes + 4 * kGkvBytes + kGpBytes + 256 + 1024;
+// head_dim 256: Q 64 KB + ring of 4 x 32 KB + P 16 KB;  head_dim 128 (Qwen3): 32 KB + 4 x 16 KB + 16 KB
+constexpr int gemma_smem(int hd) { return kGqRows * hd * 2 + 4 * kGkTile * hd * 2 + kGpBytes + 256 + 1024; }
 
 struct AttnGemmaDev {
     int B, S, hq, hkv, G, window;     // window 0 = causal only
@@ -37,7 +36,7 @@ struct AttnGemmaDev {
     const unsigned long long* kvbits; // [B][ceil(S/64)] key-valid bit masks (bit i = key 64 w + i), or null
     int kvwords;
     __nv_bfloat16* P;                 // [B*hq, S, ldp]
-    __nv_bfloat16* O;                 // [B*S, hq*256]
+    __nv_bfloat16* O;                 // [B*S, hq*hd]
 };
 
 // keyvalid bytes [B][S] -> bit masks [B][ceil(S/64)]
@@ -66,15 +65,19 @@ __device__ __forceinline__ void gemma_item(const AttnGemmaDev& p, int item, int&
     nt = s1 / kGkTile - jlo + 1;
 }
 
+template <int HD>
 __global__ void __launch_bounds__(kGthreads, 1)
 attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                       const __grid_constant__ CUtensorMap tmV, const AttnGemmaDev p) {
+    constexpr int kQB = kGqRows * HD * 2;          // Q block: HD/64 slabs (64 columns) of 128 rows x 128 B
+    constexpr int kKVB = kGkTile * HD * 2;         // K or V tile: HD/64 slabs of 64 rows x 128 B
+    constexpr int kSlabs = HD / 64;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* sQ = smem;
-    uint8_t* sKV = sQ + kGqBytes;                // ring of 4 K-or-V tiles (pass 0: 4 K tiles in flight)
-    uint8_t* sP = sKV + 4 * kGkvBytes;
+    uint8_t* sKV = sQ + kQB;                // ring of 4 K-or-V tiles (pass 0: 4 K tiles in flight)
+    uint8_t* sP = sKV + 4 * kKVB;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kGpBytes);
     uint64_t* q_full = bars;            // TMA -> MMA
     uint64_t* q_empty = bars + 1;       // MMA (commit after the item's last S) -> TMA
@@ -116,17 +119,17 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 int b, kvh, qb, jlo, nt;
                 gemma_item(p, item, b, kvh, qb, jlo, nt);
                 ptx::mbar_wait(q_empty, (n_item & 1) ^ 1);           // previous item's S MMAs retired
-                ptx::mbar_arrive_expect_tx(q_full, kGqBytes);
+                ptx::mbar_arrive_expect_tx(q_full, kQB);
 #pragma unroll
-                for (int c = 0; c < 4; ++c)
+                for (int c = 0; c < kSlabs; ++c)
                     ptx::tma_load_5d(&tmQ, q_full, sQ + c * (kGqRows * 128), c * 64, 0, qb * p.pos_per_blk, kvh, b);
                 auto load_tile = [&](const CUtensorMap* tm, int j) {
                     const int st = lc & 3;
                     ptx::mbar_wait(&ld_empty[st], ((lc >> 2) & 1) ^ 1);
-                    ptx::mbar_arrive_expect_tx(&ld_full[st], kGkvBytes);
+                    ptx::mbar_arrive_expect_tx(&ld_full[st], kKVB);
 #pragma unroll
-                    for (int c = 0; c < 4; ++c)
-                        ptx::tma_load_5d(tm, &ld_full[st], sKV + st * kGkvBytes + c * (kGkTile * 128), c * 64,
+                    for (int c = 0; c < kSlabs; ++c)
+                        ptx::tma_load_5d(tm, &ld_full[st], sKV + st * kKVB + c * (kGkTile * 128), c * 64,
                                          (jlo + j) * kGkTile, kvh, b, 0);
                     ++lc;
                 };
@@ -138,16 +141,16 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t idescS = ptx::make_idesc_bf16(kGqRows, kGkTile, 0, 0);
-            const uint32_t idescO = ptx::make_idesc_bf16(kGqRows, kGhd, 0, 1);      // B = V, MN-major
+            const uint32_t idescO = ptx::make_idesc_bf16(kGqRows, HD, 0, 1);      // B = V, MN-major
             uint32_t n_item = 0, base = 0 /* ring index of the item's first tile */, sc = 0, pc = 0;
             auto issue_S = [&](uint32_t li) {              // li = ring index of the K tile
                 const int st = li & 3, sb = sc & 1;
                 ptx::mbar_wait(&ld_full[st], (li >> 2) & 1);
                 ptx::mbar_wait(&s_free[sb], ((sc >> 1) & 1) ^ 1);
                 ptx::tc_fence_after();
-                const uint32_t qa = ptx::smem_u32(sQ), ka = ptx::smem_u32(sKV + st * kGkvBytes);
+                const uint32_t qa = ptx::smem_u32(sQ), ka = ptx::smem_u32(sKV + st * kKVB);
 #pragma unroll
-                for (int k = 0; k < kGhd / 16; ++k) {
+                for (int k = 0; k < HD / 16; ++k) {
                     const uint64_t qdesc = ptx::make_smem_desc_sw128(qa + (k >> 2) * (kGqRows * 128) + (k & 3) * 32, 0, 1024);
                     const uint64_t kdesc = ptx::make_smem_desc_sw128(ka + (k >> 2) * (kGkTile * 128) + (k & 3) * 32, 0, 1024);
                     ptx::mma_bf16_ss(tS[sb], qdesc, kdesc, idescS, k != 0);
@@ -174,7 +177,7 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                     ptx::mbar_wait(p_full, pc & 1);
                     ptx::mbar_wait(&ld_full[sv], (lv >> 2) & 1);
                     ptx::tc_fence_after();
-                    const uint32_t pa = ptx::smem_u32(sP), va = ptx::smem_u32(sKV + sv * kGkvBytes);
+                    const uint32_t pa = ptx::smem_u32(sP), va = ptx::smem_u32(sKV + sv * kKVB);
 #pragma unroll
                     for (int k = 0; k < kGkTile / 16; ++k) {
                         const uint64_t pdesc = ptx::make_smem_desc_sw128(pa + k * 32, 0, 1024);
@@ -298,9 +301,9 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             // ---- epilogue: O -> bf16 -> global
             ptx::mbar_wait(pv_done, pc & 1); ++pc;
             ptx::tc_fence_after();
-            __nv_bfloat16* op = p.O + (static_cast<long long>(b) * p.S + (live ? s : 0)) * (p.hq * kGhd) + head * kGhd;
+            __nv_bfloat16* op = p.O + (static_cast<long long>(b) * p.S + (live ? s : 0)) * (p.hq * HD) + head * HD;
 #pragma unroll 1
-            for (int c = 0; c < kGhd / 32; ++c) {
+            for (int c = 0; c < HD / 32; ++c) {
                 uint32_t o[32];
                 ptx::tmem_ld_32x32(tO + lane_off + c * 32, o);
                 ptx::tmem_ld_wait();
@@ -344,7 +347,7 @@ extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const voi
                                  void* P_bf16, void* O_bf16, int B, int S, int hq, int hkv, int hd,
                                  int window, float scale, int ldp, void* stream) {
     PT_REQUIRE(q_rot && k_rot && qkv && P_bf16 && O_bf16, "pt_attn_gemma_fwd: null pointer");
-    PT_REQUIRE(hd == kGhd, "pt_attn_gemma_fwd: head_dim must be 256 (got %d)", hd);
+    PT_REQUIRE(hd == 256 || hd == 128, "pt_attn_gemma_fwd: head_dim must be 256 or 128 (got %d)", hd);
     PT_REQUIRE(B > 0 && S > 0 && hq > 0 && hkv > 0 && hq % hkv == 0 && window >= 0, "pt_attn_gemma_fwd: bad shape");
     const int G = hq / hkv;
     PT_REQUIRE(G <= 128 && (G & (G - 1)) == 0, "pt_attn_gemma_fwd: hq / hkv must be a power of two <= 128 (got %d)", G);
@@ -384,7 +387,11 @@ extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const voi
     }
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(attn_gemma_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGsmem);
+        cudaError_t e = cudaFuncSetAttribute(attn_gemma_fwd_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             gemma_smem(256));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(attn_gemma_fwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     gemma_smem(128));
         if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(attn_gemma): %s", cudaGetErrorString(e)); return PT_ERR_CUDA; }
         attr_done = true;
     }
@@ -401,6 +408,9 @@ extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const voi
     const long long items = static_cast<long long>(B) * hkv * p.nqb;
     PT_REQUIRE(items < (1ll << 31), "pt_attn_gemma_fwd: too many work items");
     const int grid = items < num_sms() ? static_cast<int>(items) : num_sms();
-    attn_gemma_fwd_kernel<<<grid, kGthreads, kGsmem, st>>>(tq, tk, tv, p);
+    if (hd == 256)
+        attn_gemma_fwd_kernel<256><<<grid, kGthreads, gemma_smem(256), st>>>(tq, tk, tv, p);
+    else
+        attn_gemma_fwd_kernel<128><<<grid, kGthreads, gemma_smem(128), st>>>(tq, tk, tv, p);
     return check_launch("attn_gemma_fwd_kernel");
 }

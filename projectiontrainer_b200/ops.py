@@ -239,7 +239,7 @@ def softmax_bwd(P, dP, dS, rows, Sk, ld, scale, Sq=0, causal=0, window=0):
 
 def attn_gemma_fusable(hq: int, hkv: int, hd: int) -> bool:
     G = hq // max(1, hkv)
-    return hd == 256 and hq % hkv == 0 and G <= 128 and (G & (G - 1)) == 0
+    return hd in (128, 256) and hq % hkv == 0 and G <= 128 and (G & (G - 1)) == 0
 
 
 def pack_keyvalid(keyvalid, kvbits):

@@ -32,12 +32,13 @@ def test_attn_siglip_fwd(cuda_dev, B, N, H, amp, v1):
 @pytest.mark.parametrize("B,S,hq,hkv,W,pad", [(2, 200, 4, 1, 0, False), (2, 200, 4, 1, 64, True), (1, 703, 4, 1, 512, True),
                                               (2, 300, 8, 4, 0, True), (3, 831, 8, 4, 100, False), (1, 40, 2, 2, 0, True),
                                               (2, 1247, 4, 1, 512, True), (1, 1247, 8, 4, 1024, True)])
-def test_attn_gemma_fwd(cuda_dev, B, S, hq, hkv, W, pad):
+@pytest.mark.parametrize("hd", [256, 128])
+def test_attn_gemma_fwd(cuda_dev, B, S, hq, hkv, W, pad, hd):
     """Fused causal / sliding-window GQA attention (hd 256) vs fp32 torch on the same bf16-rounded q/k/v: the
     normalised P it writes inside the band (everything else must stay at the caller's zero fill) and O."""
     from projectiontrainer_b200 import ops
     torch.manual_seed(S + hq + W)
-    hd, G = 256, hq // hkv
+    G = hq // hkv
     QKV = (hq + 2 * hkv) * hd
     ld = (S + 7) // 8 * 8
     q = (torch.randn(B * S, hq * hd, device=cuda_dev) * 1.0).to(torch.bfloat16)

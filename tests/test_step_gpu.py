@@ -224,7 +224,7 @@ def test_train_step_graph_replay_and_staged_host_batches_match_eager(cuda_dev):
     assert _cos(p0.cpu(), p1.cpu()) > 1 - 1e-6
 
 
-@pytest.mark.parametrize("fused", [True, False], ids=["fused_swiglu", "unfused_kernels"])
+@pytest.mark.parametrize("fused", [True, False], ids=["fused_kernels", "unfused_kernels"])
 def test_step_qwen3_recipe_hd128_vs_oracle(cuda_dev, fused, monkeypatch):
     """The Qwen3 decoder recipe (pre-norm only: residual adds in the o / down projection epilogues, SwiGLU fused
     into the gate||up and down-dgrad GEMMs, per-head q/k norms, unscaled embeddings, untied LM head, full
@@ -235,7 +235,7 @@ def test_step_qwen3_recipe_hd128_vs_oracle(cuda_dev, fused, monkeypatch):
     from projectiontrainer_b200 import engine as E
     from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
     if not fused:
-        for k in ("PT_STAGE1_FUSE_SOFTMAX_BWD", "PT_STAGE1_FUSE_GEGLU"):
+        for k in ("PT_STAGE1_FUSE_ATTN_FWD", "PT_STAGE1_FUSE_SOFTMAX_BWD", "PT_STAGE1_FUSE_GEGLU"):
             monkeypatch.setenv(k, "0")
     vkw = dict(hidden=128, ff=256, layers=2, heads=2, image=160, patch=16)
     lkw = dict(vocab=1024, hidden=256, ff=384, layers=4, hq=8, hkv=2, hd=128, window=0, q_scalar=128.0, pattern=1,
@@ -250,7 +250,7 @@ def test_step_qwen3_recipe_hd128_vs_oracle(cuda_dev, fused, monkeypatch):
     ref = O.stage1_step(px, ids, lab, Wv_q, P, Wl_q, ovc, olc, scale_dtype=torch.bfloat16)
     eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
                          E.ProjectorState(P, cuda_dev), cuda_dev)
-    assert eng.fuse_geglu == fused and not eng.fuse_attn_fwd
+    assert eng.fuse_geglu == fused and eng.fuse_attn_fwd == fused          # head_dim 128 instantiation of the fused attention
     for it in range(3):                                       # eager, graph capture, graph replay
         loss = eng._graphed_forward_backward({"pixel_values": px.to(cuda_dev), "token_ids": ids.to(cuda_dev),
                                               "labels": lab.to(cuda_dev)}, olc.pad_id)
