@@ -1,7 +1,7 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_attn_gpu.py tests/test_step_gpu.py tests/test_hf_bf16_gpu.py -q > gpurun_out/t29_tests.log 2>&1
-echo "exit $?" >> gpurun_out/t29_tests.log
-timeout 600 python tools/bench_qwen3.py > gpurun_out/t29_qwen3.json 2> gpurun_out/t29_qwen3.err
-timeout 300 python bench.py --steps 8 --warmup 3 --no-cpu-baseline > gpurun_out/t29_bench.json 2> gpurun_out/t29_bench.err
+timeout 120 python tools/image_one.py && timeout 400 ncu --set full --clock-control none --import-source on -k regex:resample_horizontal -s 2 -c 1 -o gpurun_out/t30_image_h python tools/image_one.py > gpurun_out/t30_ncu.log 2>&1
+ncu -i gpurun_out/t30_image_h.ncu-rep --page raw --csv > gpurun_out/t30_image_h_raw.csv 2>/dev/null
+ls -la gpurun_out/t30* >> gpurun_out/t30_ncu.log
+rm -f gpurun_out/t30_image_h.ncu-rep
