@@ -748,25 +748,152 @@ class Stage1Engine:
             valid = torch.ones(B, Smax, dtype=torch.uint8, device=dev)
             valid[:, :S].copy_(keyvalid.view(B, S))
             self.cache.update(valid=valid, next_pos=keyvalid.view(B, S).long().sum(1))
+        # device-side position state of the graphed decode step (one slot index for the whole batch, one RoPE
+        # position per sample, key validity per cache slot); allocated once per cache, refilled per prefill
+        kc = self.cache
+        if kc.get("g_valid") is None or kc["g_valid"].shape != (B, Smax):
+            kc.update(g_valid=torch.ones(B, Smax, dtype=torch.uint8, device=dev),
+                      g_slot=torch.zeros(1, dtype=torch.int64, device=dev),
+                      g_pos=torch.zeros(B, dtype=torch.int64, device=dev),
+                      g_ar=torch.arange(Smax, dtype=torch.int64, device=dev), g_graph=None, g_calls=0)
+        kc["g_valid"].fill_(1)
+        if keyvalid is not None:
+            kc["g_valid"][:, :S].copy_(keyvalid.view(B, S))
+            kc["g_pos"].copy_(kc["next_pos"])
+        else:
+            kc["g_pos"].fill_(S)
+        kc["g_slot"].fill_(S)
         x, _ = self._llm_stack(x0, keyvalid, B, S, save=False, cache=self.cache, pos_ids=pos_ids)
         return self._last_logits(x, B, S)
 
-    def _last_logits(self, x: torch.Tensor, B: int, S: int) -> torch.Tensor:
+    def _last_logits(self, x: torch.Tensor, B: int, S: int, buf=None) -> torch.Tensor:
         c, Lm = self.lcfg, self.llm
-        yf = self.buf("i_yf", (B, c.hidden), BF16)
+        buf = buf or self.buf
+        yf = buf("i_yf", (B, c.hidden), BF16)
         ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(1, S, S - 1))
-        logits = self.buf("i_logits", (B, _pad8(c.vocab)), F32)[:, :c.vocab]
+        logits = buf("i_logits", (B, _pad8(c.vocab)), F32)[:, :c.vocab]
         ops.linear(yf, Lm.lm_head, out=logits)
         return logits
 
     @torch.no_grad()
     def decode_step(self, tokens: torch.Tensor) -> torch.Tensor:
         """One cached decode step: tokens i64 [B] at position cache['pos'] -> f32 logits [B, V]
-        (HF generate's per-token forward; sliding layers attend to the last `window` keys only)."""
+        (HF generate's per-token forward; sliding layers attend to the last `window` keys only).
+        By default the step runs as ONE CUDA graph whose position lives on the device (fixed shapes: scores over
+        the whole cache, masked), so every token of every sequence replays the same graph; PT_STAGE1_DECODE_GRAPH=0
+        selects the eager step with exact-length contractions."""
+        kc = self.cache
+        if kc["pos"] >= kc["Smax"]:
+            raise RuntimeError("KV cache full: prefill(max_new_tokens=...) was sized too small")
+        if os.environ.get("PT_STAGE1_DECODE_GRAPH", "1") == "0":
+            return self._decode_step_eager(tokens)
+        B = kc["B"]
+        if kc.get("g_tokens") is None or kc["g_tokens"].shape[0] != B:
+            kc["g_tokens"] = torch.zeros(B, 1, dtype=torch.int64, device=self.device)
+        kc["g_tokens"].copy_(tokens.to(self.device).view(B, 1), non_blocking=True)
+        kc["g_calls"] += 1
+        if kc["g_calls"] == 1:                       # sizes the workspaces
+            logits = self._decode_step_fixed()
+        else:
+            if kc["g_graph"] is None:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    kc["g_logits"] = self._decode_step_fixed()
+                kc["g_graph"] = graph
+            kc["g_graph"].replay()
+            logits = kc["g_logits"]
+        kc["pos"] += 1
+        if kc.get("next_pos") is not None:
+            kc["next_pos"] = kc["next_pos"] + 1
+        return logits
+
+    def _decode_step_fixed(self) -> torch.Tensor:
+        """The decode step with position-independent shapes: the new key / value go to cache slot g_slot (device
+        scalar), scores and P V run over all Smax slots with the slots beyond g_slot (and, in sliding layers, before
+        g_slot - window + 1, and prompt pads) masked in the softmax; RoPE rows are gathered by the per-sample
+        positions g_pos.  Ends by advancing g_slot / g_pos, so a captured graph serves every step."""
+        c, Lm, kc = self.lcfg, self.llm, self.cache
+        B, Smax = kc["B"], kc["Smax"]
+        h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
+        G, QKV, kvd = hq // hkv, (hq + 2 * hkv) * hd, hkv * hd
+        scale = c.q_scalar ** -0.5
+        slot, posv, ar = kc["g_slot"], kc["g_pos"], kc["g_ar"]
+        ids = kc["g_tokens"]
+        ws = kc.setdefault("g_ws", {})      # owned by the cache, not by a batch-geometry arena: the graph keeps pointers
+
+        def dbuf(name, shape, dtype):
+            t = ws.get(name)
+            if t is None:
+                t = ws[name] = torch.empty(shape, dtype=dtype, device=self.device)
+            return t
+        x = dbuf("d_x", (B, h), F32)
+        ops.embed_splice(ids, ids, Lm.embed, Lm.embed_scale, None, 0, x,
+                         dbuf("d_mask", (B, 1), torch.int64), dbuf("d_lab", (B, 1), torch.int64),
+                         dbuf("d_kv", (B, 1), torch.uint8), dbuf("d_tgt", (B, 1), torch.int32))
+        a = dbuf("d_a", (B, h), BF16)
+        qkv = dbuf("d_qkv", (B, QKV), BF16)
+        q_post = dbuf("d_q", (B, hq * hd), BF16)
+        k_post = dbuf("d_k", (B, kvd), BF16)
+        ld = _pad8(Smax)
+        sc = dbuf("d_sc", (B * hq, ld), F32)
+        P = dbuf("d_P", (B * hq, ld), BF16)
+        attn_o = dbuf("d_o", (B, hq * hd), BF16)
+        y = dbuf("d_y", (B, h), BF16)
+        x1 = dbuf("d_x1", (B, h), F32)
+        gu = dbuf("d_gu", (B, 2 * ff), BF16)
+        act = dbuf("d_act", (B, ff), BF16)
+        # key masks of this step (index plumbing on [B, Smax] bytes): causal, prompt pads, sliding window
+        m_full = ((ar <= slot) & kc["g_valid"].bool()).to(torch.uint8)
+        m_slide = (m_full.bool() & (ar > slot - c.window)).to(torch.uint8) if c.window > 0 else m_full
+        tabs = {}
+        for f in (True, False):
+            cos_t, sin_t = self.rope(Smax, f)
+            tabs[f] = (cos_t.index_select(0, posv), sin_t.index_select(0, posv))
+        ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
+        for li, L in enumerate(Lm.layers):
+            full = c.is_full(li)
+            ops.linear(a, L["qkv_w"], out=qkv)
+            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], tabs[full][0], tabs[full][1], q_post, k_post, B, hq,
+                                hkv, hd, c.eps)
+            K, V = kc["k"][li], kc["v"][li]
+            K.index_copy_(1, slot, k_post.view(B, 1, kvd))
+            V.index_copy_(1, slot, qkv[:, (hq + hkv) * hd:].reshape(B, 1, kvd))
+            ops.gemm_raw(M=G, N=Smax, K=hd, A=q_post, lda=hd, B=K, ldb=kvd, Cout=sc, ldc=ld,
+                         nz=(hkv, B, 1), a_zs=(G * hd, hq * hd, 0), b_zs=(hd, Smax * kvd, 0),
+                         c_zs=(G * ld, hq * ld, 0), alpha=scale)
+            ops.softmax_fwd(sc, P, m_full if full else m_slide, B * hq, 1, Smax, ld, hq, 0, 0)
+            ops.gemm_raw(M=G, N=hd, K=Smax, A=P, lda=ld, B=V, ldb=kvd, b_mn=True, Cout=attn_o, ldc=hd,
+                         nz=(hkv, B, 1), a_zs=(G * ld, hq * ld, 0), b_zs=(hd, Smax * kvd, 0),
+                         c_zs=(G * hd, hq * hd, 0))
+            last = li == len(Lm.layers) - 1
+            if c.sandwich_norm:
+                ops.linear(attn_o, L["o_w"], out=y)
+                ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            else:
+                ops.linear(attn_o, L["o_w"], out=x1, residual=x)
+                ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a, c.eps)
+            if self.fuse_geglu:
+                ops.linear_geglu(a, L["gu_w"], gu, act, silu=c.silu)
+            else:
+                ops.linear(a, L["gu_w"], out=gu)
+                ops.geglu_fwd(gu, act, silu=c.silu)
+            if c.sandwich_norm:
+                ops.linear(act, L["down_w"], out=y)
+                ops.rmsnorm_residual_fwd(y, L["post_ffn_norm"], x1, x,
+                                         None if last else Lm.layers[li + 1]["in_norm"],
+                                         None if last else a, c.eps)
+            else:
+                ops.linear(act, L["down_w"], out=x, residual=x1)
+                if not last:
+                    ops.rmsnorm_fwd(x, Lm.layers[li + 1]["in_norm"], a, c.eps)
+        logits = self._last_logits(x, B, 1, buf=dbuf)
+        slot.add_(1)
+        posv.add_(1)
+        return logits
+
+    def _decode_step_eager(self, tokens: torch.Tensor) -> torch.Tensor:
         c, Lm, kc = self.lcfg, self.llm, self.cache
         B, pos, Smax = kc["B"], kc["pos"], kc["Smax"]
-        if pos >= Smax:
-            raise RuntimeError("KV cache full: prefill(max_new_tokens=...) was sized too small")
         h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
         G = hq // hkv
         QKV = (hq + 2 * hkv) * hd

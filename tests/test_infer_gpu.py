@@ -107,3 +107,41 @@ def test_prefill_config5_shape_full_size_llm_head_last_position_only(cuda_dev):
     lg_ref = eng.prefill(px, torch.cat([ids, nxt[:, None]], 1), max_new_tokens=0).clone()
     torch.cuda.synchronize()
     _close(lg2.cpu(), lg_ref.cpu(), "cached decode vs cache-free prefill")
+
+
+@pytest.mark.parametrize("padded", [False, True], ids=["plain_prompt", "left_padded_prompt"])
+def test_graphed_decode_step_equals_eager_decode_step(cuda_dev, padded, monkeypatch):
+    """The decode step as one CUDA graph with the position on the device (fixed shapes: scores over the whole
+    cache, masked; eager warm-up, capture, replay, and a second sequence re-using the captured graph) against the
+    eager step with exact-length contractions, on a sliding-window GQA decoder with head_dim 256."""
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    vkw = dict(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=7, hq=4, hkv=2, hd=256, window=12, q_scalar=256.0,
+               rope_factor_global=8.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev)
+    new = 7
+
+    def run(seed, graph):
+        monkeypatch.setenv("PT_STAGE1_DECODE_GRAPH", "1" if graph else "0")
+        px, ids, _ = O.synthetic_batch(3, 9, ovc, olc, seed=seed, left_pad=False)
+        if padded:
+            for b, k in enumerate((0, 3, 5)):
+                ids[b, :k] = olc.pad_id
+        gen = torch.Generator().manual_seed(seed)
+        toks = torch.randint(3, olc.vocab, (new, 3), generator=gen)
+        out = [eng.prefill(px, ids, max_new_tokens=new, prompt_pad_id=olc.pad_id if padded else None).clone()]
+        for t in range(new - 1):
+            out.append(eng.decode_step(toks[t].to(cuda_dev)).clone())
+        torch.cuda.synchronize()
+        return torch.stack(out).float().cpu()
+
+    for seed in (21, 22):                      # the second sequence replays the graph captured during the first
+        a, b = run(seed, True), run(seed, False)
+        assert bool(torch.isfinite(a).all())
+        assert float((a - b).abs().max()) / float(b.abs().max()) < 2e-3, seed
+    assert eng.cache["g_graph"] is not None
