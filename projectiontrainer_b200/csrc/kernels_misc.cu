@@ -150,20 +150,24 @@ ce_stats_kernel(const __nv_bfloat16* __restrict__ logits, long long ld, const in
     const int tgt = targets[r];
     if (tgt < 0) { if (threadIdx.x == 0) lse_out[r] = 0.f; return; }
     const __nv_bfloat16* row = logits + r * ld;
-    float m = -INFINITY;
+    // one pass over the row (it is 512 KB at V = 262144: a second pass re-reads it through L2): per thread a
+    // running maximum and a sum rescaled whenever the maximum moves, one rescale per 8 logits
+    float m = -INFINITY, s = 0.f;
+#pragma unroll 4
     for (int i = threadIdx.x * 8; i < V; i += blockDim.x * 8) {
         const uint4 u = *reinterpret_cast<const uint4*>(row + i);
-        m = fmaxf(m, fmaxf(fmaxf(fmaxf(bf16_lo(u.x), bf16_hi(u.x)), fmaxf(bf16_lo(u.y), bf16_hi(u.y))),
-                           fmaxf(fmaxf(bf16_lo(u.z), bf16_hi(u.z)), fmaxf(bf16_lo(u.w), bf16_hi(u.w)))));
+        const float v[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
+                            bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+        const float mx = fmaxf(fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3])), fmaxf(fmaxf(v[4], v[5]), fmaxf(v[6], v[7])));
+        const float mn = fmaxf(m, mx);
+        s *= __expf(m - mn);
+        m = mn;
+        s += (__expf(v[0] - mn) + __expf(v[1] - mn)) + (__expf(v[2] - mn) + __expf(v[3] - mn)) +
+             (__expf(v[4] - mn) + __expf(v[5] - mn)) + (__expf(v[6] - mn) + __expf(v[7] - mn));
     }
+    const float mt = m;
     m = block_max(m, sh);
-    float s = 0.f;
-    for (int i = threadIdx.x * 8; i < V; i += blockDim.x * 8) {
-        const uint4 u = *reinterpret_cast<const uint4*>(row + i);
-        s += __expf(bf16_lo(u.x) - m) + __expf(bf16_hi(u.x) - m) + __expf(bf16_lo(u.y) - m) +
-             __expf(bf16_hi(u.y) - m) + __expf(bf16_lo(u.z) - m) + __expf(bf16_hi(u.z) - m) +
-             __expf(bf16_lo(u.w) - m) + __expf(bf16_hi(u.w) - m);
-    }
+    s *= __expf(mt - m);              // a thread that saw no element has mt = -inf, s = 0: contributes 0
     s = block_sum(s, sh);
     if (threadIdx.x == 0) {
         const float lse = m + logf(s);

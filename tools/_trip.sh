@@ -1,13 +1,7 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -q -m gpu > gpurun_out/t32_all_tests.log 2>&1
-echo "exit $?" >> gpurun_out/t32_all_tests.log
-timeout 200 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/t32_smoke.log 2>&1
-echo "exit $?" >> gpurun_out/t32_smoke.log
-timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29581 bench.py --gpus 4 --steps 8 --warmup 3 --no-cpu-baseline > gpurun_out/t32_bench_4gpu.json 2> gpurun_out/t32_bench_4gpu.err
-echo "exit $?" >> gpurun_out/t32_bench_4gpu.err
-timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/t32_bench_full.json 2> gpurun_out/t32_bench_full.err
-echo "exit $?" >> gpurun_out/t32_bench_full.err
-timeout 400 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/t32_bench_ref.json 2> gpurun_out/t32_bench_ref.err
-echo "exit $?" >> gpurun_out/t32_bench_ref.err
+timeout 900 python -m pytest tests/test_step_gpu.py tests/test_gemm_gpu.py tests/test_stage2_gpu.py -q > gpurun_out/t33_tests.log 2>&1
+echo "exit $?" >> gpurun_out/t33_tests.log
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/t33_bench.json 2> gpurun_out/t33_bench.err
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:ce_ -c 6 --csv --log-file gpurun_out/t33_ce_ncu.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --graph 0 > gpurun_out/t33_ncu.log 2>&1
