@@ -230,6 +230,33 @@ __device__ __forceinline__ void epi_chunk_sbwd(const uint32_t (&v)[32], uint32_t
     __syncwarp();
 }
 
+// Same with P and delta already in registers: the caller loads the NEXT chunk's probabilities before it waits
+// for the current chunk's accumulator, so their L2 latency is off the critical path (with K = head_dim the
+// tile's MMAs are short and this epilogue is what the kernel waits for).
+__device__ __forceinline__ void epi_chunk_sbwd_pre(const uint32_t (&v)[32], uint32_t stg, int lane, const EpiSbwd& o,
+                                                   const uint2 (&pq)[8], const float (&dl)[8]) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        ptx::sts128(stg + lane * 128 + ((j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncwarp();
+    const int ch = lane & 7, c = ch * 4, rsub = lane >> 3;
+    const bool col_ok = c < o.cols_q;
+    const uint32_t sp = stg + rsub * 128;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + rsub;
+        const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
+        if (col_ok && r >= o.row_lo && r < o.rows_valid) {
+            const float p0 = bf16_lo(pq[it].x), p1 = bf16_hi(pq[it].x), p2 = bf16_lo(pq[it].y), p3 = bf16_hi(pq[it].y);
+            uint2 w;
+            w.x = pack_bf16(p0 != 0.f ? o.alpha * p0 * (a.x - dl[it]) : 0.f, p1 != 0.f ? o.alpha * p1 * (a.y - dl[it]) : 0.f);
+            w.y = pack_bf16(p2 != 0.f ? o.alpha * p2 * (a.z - dl[it]) : 0.f, p3 != 0.f ? o.alpha * p3 * (a.w - dl[it]) : 0.f);
+            *reinterpret_cast<uint2*>(o.C + r * o.c_row + c * 2) = w;
+        }
+    }
+    __syncwarp();
+}
+
 // ---- kernel ----------------------------------------------------------------------------------------
 template <int BN, int ACT>
 __global__ void __launch_bounds__(kGemm2Threads, 1)
@@ -460,10 +487,41 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         if (tile_n + hf * BNH + b / 2 < p.N) ptx::prefetch_l2(g + b);
                 }
             }
+            constexpr int NCH = BNH / 32;
+            // softmax backward: this lane's delta values and the first chunk's probabilities, fetched while the
+            // tile's MMAs are still running
+            [[maybe_unused]] uint2 sb_pq[8];
+            [[maybe_unused]] float sb_dl[8];
+            [[maybe_unused]] const uint8_t* sb_P = nullptr;
+            [[maybe_unused]] auto sb_load = [&](int c, uint2 (&dst)[8]) {
+                const int col0 = tile_n + hf * BNH + c * 32;
+                const int cols_q = min(32, ((p.N + 3) & ~3) - col0);
+                const int cq = (lane & 7) * 4, rsub = lane >> 3;
+                const bool col_live = col0 < p.N && col0 >= n_blk * BN && cq < cols_q;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int r = it * 4 + rsub;
+                    dst[it] = make_uint2(0u, 0u);
+                    if (col_live && r >= row_lo && r < rows_valid)
+                        dst[it] = *reinterpret_cast<const uint2*>(sb_P + static_cast<long long>(r) * p.ld_aux * 2 +
+                                                                  (c * 32 + cq) * 2);
+                }
+            };
+            if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
+                sb_P = static_cast<const uint8_t*>(p.aux) +
+                       (coff / p.ldc * p.ld_aux + static_cast<long long>(row0) * p.ld_aux + tile_n + hf * BNH) * 2;
+                const float* dbase = p.bias + coff / p.ldc + row0;
+                const int rsub = lane >> 3;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int r = it * 4 + rsub;
+                    sb_dl[it] = (r >= row_lo && r < rows_valid) ? __ldg(dbase + r) : 0.f;
+                }
+                sb_load(0, sb_pq);
+            }
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);
-            constexpr int NCH = BNH / 32;
             if constexpr (ACT == PT_ACT_GEGLU) {
                 // accumulator columns [0,128) = gate, [128,256) = up of ff columns n_blk*128 .. +127; this warp
                 // produces two 32-column chunks: gate and up pre-activations -> C, gelu_tanh(gate)*up -> aux
@@ -511,17 +569,25 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int col0 = tile_n + col_local;
                 const bool live = rows_valid > row_lo && col0 < p.N && col0 >= n_blk * BN;   // warp-uniform
                 uint32_t v[32];
-                if (live) {
-                    ptx::tmem_ld_32x32(taddr + col_local, v);
-                    ptx::tmem_ld_wait();
+                if (live) ptx::tmem_ld_32x32(taddr + col_local, v);
+                [[maybe_unused]] uint2 sb_pn[8];
+                if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
+                    if (c + 1 < NCH) sb_load(c + 1, sb_pn);          // next chunk's P: in flight during this chunk
                 }
+                if (live) ptx::tmem_ld_wait();
                 if (c == NCH - 1) {
                     // accumulator stage fully read by this warp: hand it back to the leader's MMA warp
                     ptx::tc_fence_before();
                     __syncwarp();
                     if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
                 }
-                if (!live) continue;
+                if (!live) {
+                    if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
+#pragma unroll
+                        for (int it = 0; it < 8; ++it) sb_pq[it] = sb_pn[it];
+                    }
+                    continue;
+                }
                 if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
                     EpiSbwd o;
                     const long long co = coff + static_cast<long long>(row0) * p.ldc + col0;
@@ -533,7 +599,9 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     o.alpha = p.alpha;
                     o.rows_valid = rows_valid; o.row_lo = row_lo;
                     o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
-                    epi_chunk_sbwd(v, stg, lane, o);
+                    epi_chunk_sbwd_pre(v, stg, lane, o, sb_pq, sb_dl);
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) sb_pq[it] = sb_pn[it];
                     continue;
                 }
                 if constexpr (ACT == PT_ACT_GEGLU_BWD) {
