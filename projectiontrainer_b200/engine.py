@@ -678,7 +678,8 @@ class Stage1Engine:
             return loss
         if g["graph"] is None:
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            # thread_local: the DataLoader's pin-memory thread may call cudaHostAlloc while this thread captures
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                 g["loss"] = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id, span)
             g["graph"] = graph
         g["graph"].replay()
@@ -797,7 +798,7 @@ class Stage1Engine:
         else:
             if kc["g_graph"] is None:
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                     kc["g_logits"] = self._decode_step_fixed()
                 kc["g_graph"] = graph
             kc["g_graph"].replay()

@@ -8,6 +8,7 @@ validation pass reports the loss and, when the tokenizer can decode, the sampled
 accuracy (prefill + KV-cached decode in the engine)."""
 from __future__ import annotations
 
+import gc
 import json
 import logging
 import math
@@ -41,6 +42,19 @@ def cosine_with_warmup(step: int, warmup: int, total: int) -> float:
     return max(0.0, 0.5 * (1.0 + math.cos(math.pi * progress)))
 
 
+def _fork_safe_iter(loader):
+    """DataLoader workers are forked when the iterator is built.  A child that inherits unreachable but not yet
+    collected CUDA objects (a dropped geometry's graphs, events, pinned blocks) and garbage-collects them calls
+    into a CUDA context it does not own and aborts: collect them in this process first, and keep the survivors
+    frozen (out of the child's collector) across the fork."""
+    gc.collect()
+    gc.freeze()
+    try:
+        return iter(loader)
+    finally:
+        gc.unfreeze()
+
+
 class _ShardedLoader:
     """What `accelerator.prepare(dataloader)` gives each process: batch i of the (identically shuffled)
     loader goes to process i % N; short processes wrap around so that every process takes the same
@@ -54,10 +68,10 @@ class _ShardedLoader:
 
     def __iter__(self):
         if self.world == 1:
-            yield from self.loader
+            yield from _fork_safe_iter(self.loader)
             return
         first, mine = [], 0
-        for i, b in enumerate(self.loader):
+        for i, b in enumerate(_fork_safe_iter(self.loader)):
             if i < self.world:
                 first.append(b)
             if i % self.world == self.rank:

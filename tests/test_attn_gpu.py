@@ -75,3 +75,42 @@ def test_attn_gemma_fwd(cuda_dev, B, S, hq, hkv, W, pad, hd):
     assert bool(torch.isfinite(got[live]).all())
     err = (got[live] - Oref[live]).abs().max().item()
     assert err < 2e-2 * Oref.abs().max().item() + 1e-3, err
+
+
+@pytest.mark.parametrize("rows,S,hq,hkv,hd", [(6000, 750, 4, 1, 256), (5000, 500, 8, 4, 128), (300, 100, 4, 1, 256),
+                                              (257, 257, 2, 2, 64), (96, 32, 2, 1, 512), (4800, 160, 3, 2, 72)])
+def test_qknorm_rope_fwd_bwd(cuda_dev, rows, S, hq, hkv, hd):
+    """q/k RMS-norm ((1 + w) gain) + rotate-half RoPE over the fused qkv activation, forward and backward, vs fp32
+    torch autograd on the same bf16-rounded inputs.  Covers the warp-per-row kernel (rows >= 4736, head_dim <=
+    256), the warp-per-(row, head) register kernel and the generic head_dim > 256 loop."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(rows + hd)
+    nh, half, eps = hq + hkv, hd // 2, 1e-6
+    qkv = torch.randn(rows, (hq + 2 * hkv) * hd, device=cuda_dev).to(torch.bfloat16)
+    wq, wk = torch.randn(hd, device=cuda_dev) * 0.3, torch.randn(hd, device=cuda_dev) * 0.3
+    ang = torch.rand(S, half, device=cuda_dev) * 6.28
+    cs, sn = ang.cos().contiguous(), ang.sin().contiguous()
+    q_out = torch.full((rows, hq * hd), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    k_out = torch.full((rows, hkv * hd), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    ops.qknorm_rope_fwd(qkv, wq, wk, cs, sn, q_out, k_out, S, hq, hkv, hd, eps)
+
+    x = qkv.float()[:, :nh * hd].reshape(rows, nh, hd).requires_grad_(True)
+    w = torch.cat([wq.expand(hq, hd), wk.expand(hkv, hd)], dim=0)
+    n = x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + eps) * (1 + w)
+    pos = torch.arange(rows, device=cuda_dev) % S
+    c, s = cs[pos][:, None, :], sn[pos][:, None, :]
+    y = torch.cat([n[..., :half] * c - n[..., half:] * s, n[..., half:] * c + n[..., :half] * s], dim=-1)
+    got = torch.cat([q_out.float().reshape(rows, hq, hd), k_out.float().reshape(rows, hkv, hd)], dim=1)
+    assert torch.isfinite(got).all()
+    assert (got - y).abs().max().item() < 2e-2 * y.abs().max().item()
+
+    dy = torch.randn(rows, nh, hd, device=cuda_dev).to(torch.bfloat16)
+    y.backward(dy.float())
+    dq, dk = dy[:, :hq].reshape(rows, hq * hd).contiguous(), dy[:, hq:].reshape(rows, hkv * hd).contiguous()
+    d_qkv = torch.full_like(qkv, 7.0)
+    ops.qknorm_rope_bwd(dq, dk, qkv, wq, wk, cs, sn, d_qkv, S, hq, hkv, hd, eps)
+    torch.cuda.synchronize()
+    gd = d_qkv.float()[:, :nh * hd].reshape(rows, nh, hd)
+    assert (gd - x.grad).abs().max().item() < 2e-2 * x.grad.abs().max().item()
+    assert torch.nn.functional.cosine_similarity(gd.flatten(), x.grad.flatten(), dim=0).item() > 0.9999
+    assert (d_qkv[:, nh * hd:] == 7.0).all()           # the v columns belong to the caller

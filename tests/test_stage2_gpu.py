@@ -179,6 +179,43 @@ def test_geometry_arenas_are_bounded_and_reusable(cuda_dev):
             assert abs(loss - first.setdefault(T, loss)) < 1e-4, (rnd, T)
 
 
+def test_graph_capture_survives_a_concurrent_pinning_thread(cuda_dev):
+    """DataLoader(pin_memory=True) pins every new batch shape on its own thread (cudaHostAlloc); with per-batch
+    padding that happens all through training, also while the step thread captures a geometry's CUDA graph.
+    The capture must not be invalidated by it (regression: a 640-triplet Stage-2 run died at its first capture)."""
+    import threading
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    vkw = dict(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=6, hq=2, hkv=1, hd=256, window=8, q_scalar=256.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev)
+    stop, pinned = threading.Event(), [0]
+
+    def pinner():
+        n = 1 << 16
+        while not stop.is_set():
+            torch.empty(n, dtype=torch.uint8).pin_memory()      # a fresh size every time: never served from the cache
+            n += 4096
+            pinned[0] += 1
+
+    th = threading.Thread(target=pinner, daemon=True)
+    th.start()
+    try:
+        for T in (8, 16, 24, 32, 40, 48):
+            px, ids, lab = O.synthetic_batch(2, T, ovc, olc, seed=200 + T, left_pad=True)
+            b = {"pixel_values": px.to(cuda_dev), "token_ids": ids.to(cuda_dev), "labels": lab.to(cuda_dev)}
+            losses = [eng.train_step(b, 0.0, pad_id=olc.pad_id, weight_decay=0.0).item() for _ in range(3)]
+            assert max(losses) - min(losses) < 1e-4, (T, losses)      # eager, capture + replay, replay
+    finally:
+        stop.set()
+        th.join()
+    assert pinned[0] > 0
+
+
 def test_generate_with_left_padded_prompt_matches_hf_golden(cuda_dev):
     """Stage-2 evaluation prompt `[image][left-padded question]` (ref:Stage2/trainer.py:594-611): prompt pads
     masked as keys through prefill and decode, positions from the mask as HF generate derives them; greedy

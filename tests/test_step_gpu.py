@@ -287,3 +287,44 @@ def test_qwen3_recipe_prefill_and_cached_decode_vs_oracle(cuda_dev):
         assert (lg - r).abs().max() / r.abs().max() < 3e-2, t
         if t + 1 < new:
             logits = eng.decode_step(toks[:, t].to(cuda_dev))
+
+
+class _CollectingDataset(torch.utils.data.Dataset):
+    """Every item forces a full garbage collection in the worker that produces it."""
+
+    def __len__(self):
+        return 6
+
+    def __getitem__(self, i):
+        import gc
+        gc.collect()
+        return torch.full((2,), float(i))
+
+
+def test_forked_loader_workers_do_not_collect_inherited_cuda_garbage(cuda_dev):
+    """The trainers fork DataLoader workers at the start of every epoch.  Unreachable CUDA objects waiting for the
+    cycle collector at that moment (a dropped geometry's graph) would be destroyed by the CHILD's collector,
+    which aborts the worker; `_ShardedLoader` collects and freezes before the fork (regression: a worker died with
+    'Fatal Python error: Aborted ... Garbage-collecting' when the trainer test ran late in the suite)."""
+    import gc
+    from torch.utils.data import DataLoader
+    from projectiontrainer_b200.projector_trainer import _ShardedLoader
+
+    class Cycle:
+        pass
+
+    x = torch.ones(8, device=cuda_dev)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        y = x * 2
+    graph.replay()
+    torch.cuda.synchronize()
+    c = Cycle()
+    c.me, c.graph, c.event, c.pinned = c, graph, torch.cuda.Event(), torch.empty(1 << 20).pin_memory()
+    c.event.record()
+    gc.collect()
+    gc.collect()                                  # age the cycle into the oldest generation, then orphan it
+    del c, graph, y
+    loader = _ShardedLoader(DataLoader(_CollectingDataset(), batch_size=2, num_workers=2), 0, 1)
+    got = torch.cat([b for b in loader])
+    assert got.shape == (6, 2) and got[:, 0].tolist() == [0.0, 1.0, 2.0, 3.0, 4.0, 5.0]
