@@ -290,6 +290,23 @@ int pt_image_preprocess(const uint8_t* src_rgb, int H, int W, long long src_row_
                         float std0, float std1, float std2, double rescale, void* workspace,
                         long long workspace_bytes, void* stream);
 
+/* ---- NF4 frozen LLM weights -----------------------------------------------------------
+ * ref:Stage1/train_projection_stage1.py:192-210: `--enable_qlora` loads the frozen LLM through bitsandbytes with
+ * BitsAndBytesConfig(load_in_4bit, "nf4", compute dtype bf16, double quant).  These entry points restate
+ * bitsandbytes 0.45 quantize_4bit / dequantize_4bit for that configuration (blocksize 64, nested 8-bit absmax
+ * with blocksize 256 and a mean offset); the codes are expanded to bf16 once at load time.
+ * via_fp16 != 0 reproduces transformers' float16 override of bitsandbytes loads (bf16 -> fp16 before quantising,
+ * fp16 -> bf16 after de-quantising).  n: elements of the weight, a multiple of 64.
+ *   pt_nf4_quantize:        w bf16 [n] -> packed uint8 [n/2] (first of a pair in the high nibble), absmax f32 [n/64]
+ *   pt_nf4_absmax_quantize: absmax f32 [nb] - offset -> qabsmax uint8 [nb], absmax2 f32 [ceil(nb/256)];
+ *                           code256: device f32 [256], the sorted dynamic map (create_dynamic_map)
+ *   pt_nf4_dequantize:      -> out bf16 [n] = bf16(fp16(NF4[c] * (code256[q] * absmax2 + offset))) */
+int pt_nf4_quantize(const void* w_bf16, long long n, int via_fp16, uint8_t* packed, float* absmax, void* stream);
+int pt_nf4_absmax_quantize(const float* absmax, long long nb, float offset, const float* code256,
+                           uint8_t* qabsmax, float* absmax2, void* stream);
+int pt_nf4_dequantize(const uint8_t* packed, const uint8_t* qabsmax, const float* absmax2, float offset,
+                      const float* code256, long long n, int via_fp16, void* out_bf16, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

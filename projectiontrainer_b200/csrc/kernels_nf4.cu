@@ -1,0 +1,152 @@
+// NF4 (4-bit NormalFloat, double-quantised) frozen LLM weights (second half).
+//
+//   ref:Stage1/train_projection_stage1.py:192-210 — `--enable_qlora` loads the frozen LLM through bitsandbytes:
+//     BitsAndBytesConfig(load_in_4bit=True, bnb_4bit_quant_type="nf4", bnb_4bit_compute_dtype=bf16,
+//                        bnb_4bit_use_double_quant=True)
+//   bitsandbytes 0.45 (not in /root/reference, not in this image; restated from its published source):
+//     functional.py quantize_4bit / dequantize_4bit / quantize_blockwise / create_dynamic_map,
+//     csrc/kernels.cu kQuantizeBlockwise (blocksize 64, reciprocal-multiply), dQuantizeNF4 (midpoint tree),
+//     dQuantize<0> (bisection over the 8-bit dynamic map), kDequantizeBlockwise.
+//
+// B200-first use of the format: 180 GB of HBM holds the bf16 copy of every LLM the reference's scripts name, so
+// the 4-bit codes are expanded ONCE at load time (these kernels) and the step runs the ordinary bf16 tcgen05 GEMMs
+// on exactly the values bitsandbytes' Linear4bit would feed its GEMM:
+//     w_bf16 -> fp16 -> codes (64-blocks) + 8-bit absmax (256-blocks) + offset -> fp16 -> bf16.
+// All three kernels are byte work bounded by one pass over the weight in HBM.
+#include <cuda_fp16.h>
+
+#include "pt_common.cuh"
+
+#define ST(s) static_cast<cudaStream_t>(s)
+
+namespace pt {
+
+__constant__ float kNf4[16] = {-1.0f, -0.6961928009986877f, -0.5250730514526367f, -0.39491748809814453f,
+                               -0.28444138169288635f, -0.18477343022823334f, -0.09105003625154495f, 0.0f,
+                               0.07958029955625534f, 0.16093020141124725f, 0.24611230194568634f,
+                               0.33791524171829224f, 0.44070982933044434f, 0.5626170039176941f,
+                               0.7229568362236023f, 1.0f};
+
+// dQuantizeNF4: the code index is the number of midpoints strictly below x (every comparison is `>`); a NaN
+// (all-zero block: 0 * inf) fails them all and lands on code 0.
+__device__ __forceinline__ unsigned nf4_code(float x) {
+    constexpr float m[15] = {-0.8480964004993439f, -0.6106329262256622f, -0.4599952697753906f, -0.33967943489551544f,
+                             -0.23460740596055984f, -0.13791173323988914f, -0.045525018125772476f,
+                             0.03979014977812767f, 0.1202552504837513f, 0.2035212516784668f, 0.2920137718319893f,
+                             0.3893125355243683f, 0.5016634166240692f, 0.6427869200706482f, 0.8614784181118011f};
+    unsigned c = 0;
+#pragma unroll
+    for (int k = 0; k < 15; ++k) c += x > m[k] ? 1u : 0u;
+    return c;
+}
+
+// One warp per 64-value block, 8 blocks per CTA: lane l holds values 2l and 2l+1 and writes one packed byte.
+__global__ void __launch_bounds__(256)
+nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int via_fp16,
+                    uint8_t* __restrict__ packed, float* __restrict__ absmax) {
+    const long long blk = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+    if (blk >= nblocks) return;
+    const int lane = threadIdx.x & 31;
+    const __nv_bfloat162 v2 = reinterpret_cast<const __nv_bfloat162*>(w)[blk * 32 + lane];
+    float a = __bfloat162float(v2.x), b = __bfloat162float(v2.y);
+    if (via_fp16) { a = __half2float(__float2half_rn(a)); b = __half2float(__float2half_rn(b)); }
+    float m = fmaxf(fabsf(a), fabsf(b));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    const float inv = __fdiv_rn(1.0f, m);
+    const unsigned hi = nf4_code(__fmul_rn(a, inv)), lo = nf4_code(__fmul_rn(b, inv));
+    packed[blk * 32 + lane] = static_cast<uint8_t>((hi << 4) | lo);
+    if (lane == 0) absmax[blk] = m;
+}
+
+// dQuantize<0>: seven-step bisection over the sorted 256-entry map, then the nearer of the landing code and its
+// bracketing neighbour.
+__device__ __forceinline__ unsigned dquantize8(const float* code, float x) {
+    int pivot = 127, upper_pivot = 255, lower_pivot = 0;
+    float lower = -1.0f, upper = 1.0f, val = code[pivot];
+#pragma unroll
+    for (int i = 64; i > 0; i >>= 1) {
+        if (x > val) { lower_pivot = pivot; lower = val; pivot += i; }
+        else { upper_pivot = pivot; upper = val; pivot -= i; }
+        val = code[pivot];
+    }
+    if (upper_pivot == 255) upper = code[upper_pivot];
+    if (lower_pivot == 0) lower = code[lower_pivot];
+    if (x > val) return x > __fmul_rn(__fadd_rn(upper, val), 0.5f) ? upper_pivot : pivot;
+    return x < __fmul_rn(__fadd_rn(lower, val), 0.5f) ? lower_pivot : pivot;
+}
+
+// One CTA of 256 threads per 256 first-level absmax values: (absmax - offset) -> 8-bit dynamic codes + absmax2.
+__global__ void __launch_bounds__(256)
+nf4_absmax_quantize_kernel(const float* __restrict__ absmax, long long nb, float offset,
+                           const float* __restrict__ code256, uint8_t* __restrict__ qabsmax,
+                           float* __restrict__ absmax2) {
+    __shared__ float code[256];
+    __shared__ float red[8];
+    code[threadIdx.x] = code256[threadIdx.x];
+    const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+    const bool on = i < nb;
+    const float v = on ? __fadd_rn(absmax[i], -offset) : 0.0f;
+    float m = fabsf(v);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = red[0];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) m = fmaxf(m, red[k]);
+    if (on) qabsmax[i] = static_cast<uint8_t>(dquantize8(code, __fmul_rn(v, __fdiv_rn(1.0f, m))));
+    if (threadIdx.x == 0) absmax2[blockIdx.x] = m;
+}
+
+// One thread per packed byte (two values).  absmax = code[q] * absmax2 (fp32 product), + offset (fp32 sum), value =
+// NF4[c] * absmax rounded to fp16 (the dtype bitsandbytes quantised from) and then to bf16 (the GEMM's dtype).
+__global__ void __launch_bounds__(256)
+nf4_dequantize_kernel(const uint8_t* __restrict__ packed, const uint8_t* __restrict__ qabsmax,
+                      const float* __restrict__ absmax2, float offset, const float* __restrict__ code256,
+                      long long nbytes, int via_fp16, __nv_bfloat16* __restrict__ out) {
+    const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= nbytes) return;
+    const long long blk = i >> 5;
+    const float a = __fadd_rn(__fmul_rn(__ldg(code256 + qabsmax[blk]), absmax2[blk >> 8]), offset);
+    const unsigned byte = packed[i];
+    float hi = __fmul_rn(kNf4[byte >> 4], a), lo = __fmul_rn(kNf4[byte & 15u], a);
+    if (via_fp16) { hi = __half2float(__float2half_rn(hi)); lo = __half2float(__float2half_rn(lo)); }
+    reinterpret_cast<__nv_bfloat162*>(out)[i] = __nv_bfloat162(__float2bfloat16_rn(hi), __float2bfloat16_rn(lo));
+}
+
+}  // namespace pt
+
+using namespace pt;
+
+extern "C" int pt_nf4_quantize(const void* w_bf16, long long n, int via_fp16, uint8_t* packed, float* absmax,
+                               void* stream) {
+    PT_REQUIRE(w_bf16 && packed && absmax, "pt_nf4_quantize: null pointer");
+    PT_REQUIRE(n > 0 && n % 64 == 0, "pt_nf4_quantize: the element count must be a positive multiple of 64");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    const long long nblocks = n / 64;
+    nf4_quantize_kernel<<<static_cast<unsigned>((nblocks + 7) / 8), 256, 0, ST(stream)>>>(
+        static_cast<const __nv_bfloat16*>(w_bf16), nblocks, via_fp16, packed, absmax);
+    return check_launch("nf4_quantize");
+}
+
+extern "C" int pt_nf4_absmax_quantize(const float* absmax, long long nb, float offset, const float* code256,
+                                      uint8_t* qabsmax, float* absmax2, void* stream) {
+    PT_REQUIRE(absmax && code256 && qabsmax && absmax2, "pt_nf4_absmax_quantize: null pointer");
+    PT_REQUIRE(nb > 0, "pt_nf4_absmax_quantize: no blocks");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    nf4_absmax_quantize_kernel<<<static_cast<unsigned>((nb + 255) / 256), 256, 0, ST(stream)>>>(
+        absmax, nb, offset, code256, qabsmax, absmax2);
+    return check_launch("nf4_absmax_quantize");
+}
+
+extern "C" int pt_nf4_dequantize(const uint8_t* packed, const uint8_t* qabsmax, const float* absmax2, float offset,
+                                 const float* code256, long long n, int via_fp16, void* out_bf16, void* stream) {
+    PT_REQUIRE(packed && qabsmax && absmax2 && code256 && out_bf16, "pt_nf4_dequantize: null pointer");
+    PT_REQUIRE(n > 0 && n % 64 == 0, "pt_nf4_dequantize: the element count must be a positive multiple of 64");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    const long long nbytes = n / 2;
+    nf4_dequantize_kernel<<<static_cast<unsigned>((nbytes + 255) / 256), 256, 0, ST(stream)>>>(
+        packed, qabsmax, absmax2, offset, code256, nbytes, via_fp16, static_cast<__nv_bfloat16*>(out_bf16));
+    return check_launch("nf4_dequantize");
+}

@@ -344,3 +344,63 @@ def image_preprocess(src_u8_hwc, dst_chw, workspace, *, mean=(0.5, 0.5, 0.5), st
               _ptr(dst_chw), _ptr(dst_u8), int(oh), int(ow), _f(mean[0]), _f(mean[1]), _f(mean[2]),
               _f(std[0]), _f(std[1]), _f(std[2]), C.c_double(float(rescale)), _ptr(workspace),
               C.c_longlong(int(workspace.numel() * workspace.element_size())), _stream())
+
+
+# ----------------------------------------------------------------------------- NF4 frozen weights
+_NF4_DYNAMIC_MAP: dict = {}
+
+
+def nf4_dynamic_map(device) -> torch.Tensor:
+    """bitsandbytes `create_dynamic_map(signed=True, max_exponent_bits=7, total_bits=8)`: the sorted 256-entry code
+    book of the nested (second-level) absmax quantiser — 2^i bucket means of linspace(0.1, 1, 2^i + 1) for each of
+    the decades 10^-6 .. 10^0, both signs, plus 0 and 1.0."""
+    key = str(device)
+    if key not in _NF4_DYNAMIC_MAP:
+        data: list = []
+        for i in range(7):
+            bounds = torch.linspace(0.1, 1, 2 ** i + 1)
+            means = (bounds[:-1] + bounds[1:]) / 2.0
+            data += ((10 ** (-6 + i)) * means).tolist()
+            data += (-(10 ** (-6 + i)) * means).tolist()
+        data += [0, 1.0]
+        data.sort()
+        _NF4_DYNAMIC_MAP[key] = torch.tensor(data, dtype=torch.float32, device=device)
+    return _NF4_DYNAMIC_MAP[key]
+
+
+def nf4_quantize(w: torch.Tensor, via_fp16: bool = True) -> dict:
+    """bf16 weight (any shape, numel % 64 == 0) -> bitsandbytes-style nested NF4 state: `packed` uint8 [n/2],
+    `qabsmax` uint8 [n/64], `absmax2` f32 [ceil(n/64/256)], `offset` (python float, the fp32 mean of the first-level
+    absmax), `code256`, `shape`, `via_fp16` (ref:Stage1/train_projection_stage1.py:195-200)."""
+    _req_cuda(w)
+    if w.dtype != torch.bfloat16 or not w.is_contiguous():
+        raise RuntimeError("nf4_quantize: contiguous bf16 weight expected")
+    n = w.numel()
+    if n == 0 or n % 64:
+        raise RuntimeError(f"nf4_quantize: numel {n} is not a positive multiple of 64")
+    nb = n // 64
+    packed = torch.empty(n // 2, dtype=torch.uint8, device=w.device)
+    absmax = torch.empty(nb, dtype=torch.float32, device=w.device)
+    _lib.call("pt_nf4_quantize", _ptr(w), C.c_longlong(n), int(bool(via_fp16)), _ptr(packed), _ptr(absmax), _stream())
+    offset = float(absmax.mean().item())
+    code = nf4_dynamic_map(w.device)
+    qabsmax = torch.empty(nb, dtype=torch.uint8, device=w.device)
+    absmax2 = torch.empty((nb + 255) // 256, dtype=torch.float32, device=w.device)
+    _lib.call("pt_nf4_absmax_quantize", _ptr(absmax), C.c_longlong(nb), _f(offset), _ptr(code), _ptr(qabsmax),
+              _ptr(absmax2), _stream())
+    return {"packed": packed, "qabsmax": qabsmax, "absmax2": absmax2, "offset": offset, "code256": code,
+            "shape": tuple(w.shape), "via_fp16": bool(via_fp16), "absmax": absmax}
+
+
+def nf4_dequantize(state: dict, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Nested NF4 state -> the bf16 weight bitsandbytes' Linear4bit feeds its GEMM."""
+    packed = state["packed"]
+    _req_cuda(packed, state["qabsmax"], state["absmax2"], state["code256"], out)
+    n = packed.numel() * 2
+    if out is None:
+        out = torch.empty(state["shape"], dtype=torch.bfloat16, device=packed.device)
+    if out.numel() != n or out.dtype != torch.bfloat16 or not out.is_contiguous():
+        raise RuntimeError("nf4_dequantize: output must be contiguous bf16 of the quantised weight's size")
+    _lib.call("pt_nf4_dequantize", _ptr(packed), _ptr(state["qabsmax"]), _ptr(state["absmax2"]), _f(state["offset"]),
+              _ptr(state["code256"]), C.c_longlong(n), int(bool(state["via_fp16"])), _ptr(out), _stream())
+    return out

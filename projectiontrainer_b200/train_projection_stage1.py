@@ -5,7 +5,9 @@ schema, same model-loading order; the training step itself runs on the B200 kern
     python -m projectiontrainer_b200.train_projection_stage1 --synthetic 64 --disable_wandb     # no files, no weights
 
 `--synthetic N` (an addition) trains on N random CXR-shaped samples with random-init SigLIP-L/16-384 and
-Gemma3 weights — there are no checkpoints or datasets on the build / GPU boxes."""
+Gemma3 weights — there are no checkpoints or datasets on the build / GPU boxes.  `--enable_qlora` (ref:192-210: the
+frozen LLM loaded as double-quantised NF4) stores the decoder's Linear weights as NF4 and expands them once at load time
+(`weights.nf4_frozen_llm_`); bitsandbytes is not needed."""
 from __future__ import annotations
 
 import argparse
@@ -152,11 +154,19 @@ def build_parser():
     return p
 
 
+def _nf4(Wt, Wl, lc, dev):
+    """ref:195-210 loads the frozen LLM as double-quantised NF4 (bitsandbytes); here the bf16 weights go through the
+    same quantise -> de-quantise once at load time and the step runs on the resulting bf16 matrices."""
+    import time
+    t0 = time.perf_counter()
+    errs = list(Wt.nf4_frozen_llm_(Wl, lc, dev).values())
+    torch.cuda.synchronize()
+    logger.info(f"Frozen LLM weights stored as NF4 (blocksize 64, double quant): {len(errs)} matrices in "
+                f"{time.perf_counter() - t0:.2f} s, relative error mean {sum(errs) / len(errs):.4f} max {max(errs):.4f}")
+
+
 def main(argv=None):
     args = build_parser().parse_args(argv)
-    if args.enable_qlora:
-        raise SystemExit("--enable_qlora is not supported: this build has no 4-bit (NF4) frozen-weight GEMM "
-                         "path (SURVEY.md §8f rank 4) and will not fall back to another backend")
     accelerator = setup_accelerator_and_logging(args)
     if args.synthetic > 0:
         from .engine import PackedGemma, PackedSiglip
@@ -164,7 +174,10 @@ def main(argv=None):
         lc = {"1b": GEMMA3_1B, "4b": GEMMA3_4B, "qwen3_8b": QWEN3_8B}[args.synthetic_llm]
         vc, dev = SIGLIP_L, accelerator.device
         vision_encoder = PackedSiglip(Wt.random_siglip(vc, dev, 0), vc, dev)
-        language_model = PackedGemma(Wt.random_gemma(lc, dev, 0), lc, dev)
+        Wl = Wt.random_gemma(lc, dev, 0)
+        if args.enable_qlora:
+            _nf4(Wt, Wl, lc, dev)
+        language_model = PackedGemma(Wl, lc, dev)
         vision_dim, llm_dim = vc.hidden, lc.hidden
         processor, tokenizer = None, _Tok(lc.pad_id)
         T = min(args.max_length, 128)
@@ -182,6 +195,12 @@ def main(argv=None):
         language_model = AutoModelForCausalLM.from_pretrained(args.llm_name, torch_dtype=torch.bfloat16)
         vision_dim = vision_encoder.config.vision_config.hidden_size
         llm_dim = language_model.config.hidden_size
+        if args.enable_qlora:
+            from .engine import PackedGemma
+            from . import weights as Wt
+            Wl, lc = Wt.llm_from_hf(language_model)
+            _nf4(Wt, Wl, lc, accelerator.device)
+            language_model = PackedGemma(Wl, lc, accelerator.device)
         full = XrayTextPairDataset(args.image_root, args.train_json, processor, tokenizer, args.img_size,
                                    max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
                                    cache_tokens=args.cache_tokens)

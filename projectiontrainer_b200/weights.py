@@ -142,3 +142,31 @@ def random_projector(vision_dim: int, llm_dim: int, device, expansion: int = 10,
             "model.0.bias": u(mid, bound=vision_dim ** -0.5),
             "model.2.weight": u(llm_dim, mid, bound=mid ** -0.5),
             "model.2.bias": u(llm_dim, bound=mid ** -0.5)}
+
+
+# ----------------------------------------------------------------------------- NF4 frozen LLM (--enable_qlora)
+def nf4_frozen_llm_(W: dict, cfg: GemmaCfg, device, via_fp16: bool = True) -> dict:
+    """What `--enable_qlora` does to the frozen LLM in Stage 1 (ref:Stage1/train_projection_stage1.py:192-210):
+    every decoder `nn.Linear` weight (q/k/v/o/gate/up/down — bitsandbytes leaves embeddings, norms and the LM head
+    alone) is stored as double-quantised NF4 and expanded again for the GEMM.  Here each such weight is replaced, in
+    place in the packed dict, by its quantise -> de-quantise image in bf16 on `device` (one pass at load time; 180 GB
+    of HBM keeps the bf16 copy resident, so the step itself is unchanged).  bitsandbytes quantises each Linear on its
+    own (its own 64-blocks, 256-blocks and mean offset): the fused qkv / gate||up matrices are split back into the
+    HF modules' row ranges first.  Returns {weight name: relative Frobenius error} for logging."""
+    from . import ops
+    q_rows, kv_rows = cfg.hq * cfg.hd, cfg.hkv * cfg.hd
+    report = {}
+    for l in range(cfg.layers):
+        p = f"l{l}."
+        for name, splits in ((p + "qkv_w", (q_rows, kv_rows, kv_rows)), (p + "o_w", None),
+                             (p + "gu_w", (cfg.ff, cfg.ff)), (p + "down_w", None)):
+            w = W[name].to(device=device, dtype=torch.bfloat16).contiguous()
+            out = torch.empty_like(w)
+            r0 = 0
+            for rows in (splits or (w.shape[0],)):
+                ops.nf4_dequantize(ops.nf4_quantize(w[r0:r0 + rows], via_fp16), out[r0:r0 + rows])
+                r0 += rows
+            assert r0 == w.shape[0], (name, r0, tuple(w.shape))
+            report[name] = float((out.float() - w.float()).norm() / w.float().norm().clamp_min(1e-30))
+            W[name] = out
+    return report
