@@ -40,23 +40,43 @@ __device__ __forceinline__ unsigned nf4_code(float x) {
     return c;
 }
 
-// One warp per 64-value block, 8 blocks per CTA: lane l holds values 2l and 2l+1 and writes one packed byte.
+// Eight lanes per 64-value block (a warp covers four blocks, a CTA 32): each lane loads 8 consecutive bf16 as one
+// 16-byte word and stores its 4 packed bytes as one 32-bit word, so that enough bytes are in flight per SM to
+// stream at HBM speed.
 __global__ void __launch_bounds__(256)
 nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int via_fp16,
                     uint8_t* __restrict__ packed, float* __restrict__ absmax) {
-    const long long blk = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
-    if (blk >= nblocks) return;
-    const int lane = threadIdx.x & 31;
-    const __nv_bfloat162 v2 = reinterpret_cast<const __nv_bfloat162*>(w)[blk * 32 + lane];
-    float a = __bfloat162float(v2.x), b = __bfloat162float(v2.y);
-    if (via_fp16) { a = __half2float(__float2half_rn(a)); b = __half2float(__float2half_rn(b)); }
-    float m = fmaxf(fabsf(a), fabsf(b));
+    const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;      // one thread per 8 values
+    const long long blk = t >> 3;
+    const bool on = blk < nblocks;
+    uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+    if (on) raw = reinterpret_cast<const uint4*>(w)[t];
+    const unsigned words[4] = {raw.x, raw.y, raw.z, raw.w};
+    float v[8];
+    float m = 0.0f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    for (int j = 0; j < 4; ++j) {
+        v[2 * j] = __uint_as_float(words[j] << 16);                // bf16 -> f32 is a shift
+        v[2 * j + 1] = __uint_as_float(words[j] & 0xffff0000u);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (via_fp16) v[j] = __half2float(__float2half_rn(v[j]));
+        m = fmaxf(m, fabsf(v[j]));
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     const float inv = __fdiv_rn(1.0f, m);
-    const unsigned hi = nf4_code(__fmul_rn(a, inv)), lo = nf4_code(__fmul_rn(b, inv));
-    packed[blk * 32 + lane] = static_cast<uint8_t>((hi << 4) | lo);
-    if (lane == 0) absmax[blk] = m;
+    unsigned out = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const unsigned hi = nf4_code(__fmul_rn(v[2 * j], inv)), lo = nf4_code(__fmul_rn(v[2 * j + 1], inv));
+        out |= ((hi << 4) | lo) << (8 * j);                        // byte j of the little-endian word
+    }
+    if (on) {
+        reinterpret_cast<unsigned*>(packed)[t] = out;
+        if ((threadIdx.x & 7) == 0) absmax[blk] = m;
+    }
 }
 
 // dQuantize<0>: seven-step bisection over the sorted 256-entry map, then the nearer of the landing code and its
@@ -99,20 +119,31 @@ nf4_absmax_quantize_kernel(const float* __restrict__ absmax, long long nb, float
     if (threadIdx.x == 0) absmax2[blockIdx.x] = m;
 }
 
-// One thread per packed byte (two values).  absmax = code[q] * absmax2 (fp32 product), + offset (fp32 sum), value =
-// NF4[c] * absmax rounded to fp16 (the dtype bitsandbytes quantised from) and then to bf16 (the GEMM's dtype).
+// One thread per 4 packed bytes (8 values, one 16-byte store).  absmax = code[q] * absmax2 (fp32 product), + offset
+// (fp32 sum), value = NF4[c] * absmax rounded to fp16 (the dtype bitsandbytes quantised from) and then to bf16 (the
+// GEMM's dtype).
 __global__ void __launch_bounds__(256)
 nf4_dequantize_kernel(const uint8_t* __restrict__ packed, const uint8_t* __restrict__ qabsmax,
                       const float* __restrict__ absmax2, float offset, const float* __restrict__ code256,
-                      long long nbytes, int via_fp16, __nv_bfloat16* __restrict__ out) {
-    const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
-    if (i >= nbytes) return;
-    const long long blk = i >> 5;
+                      long long nwords, int via_fp16, __nv_bfloat16* __restrict__ out) {
+    __shared__ float nf4[16];
+    if (threadIdx.x < 16) nf4[threadIdx.x] = kNf4[threadIdx.x];
+    __syncthreads();
+    const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+    if (t >= nwords) return;
+    const long long blk = t >> 3;
     const float a = __fadd_rn(__fmul_rn(__ldg(code256 + qabsmax[blk]), absmax2[blk >> 8]), offset);
-    const unsigned byte = packed[i];
-    float hi = __fmul_rn(kNf4[byte >> 4], a), lo = __fmul_rn(kNf4[byte & 15u], a);
-    if (via_fp16) { hi = __half2float(__float2half_rn(hi)); lo = __half2float(__float2half_rn(lo)); }
-    reinterpret_cast<__nv_bfloat162*>(out)[i] = __nv_bfloat162(__float2bfloat16_rn(hi), __float2bfloat16_rn(lo));
+    const unsigned word = reinterpret_cast<const unsigned*>(packed)[t];
+    unsigned res[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const unsigned byte = (word >> (8 * j)) & 0xffu;
+        float hi = __fmul_rn(nf4[byte >> 4], a), lo = __fmul_rn(nf4[byte & 15u], a);
+        if (via_fp16) { hi = __half2float(__float2half_rn(hi)); lo = __half2float(__float2half_rn(lo)); }
+        const __nv_bfloat162 pr = __nv_bfloat162(__float2bfloat16_rn(hi), __float2bfloat16_rn(lo));
+        res[j] = *reinterpret_cast<const unsigned*>(&pr);
+    }
+    reinterpret_cast<uint4*>(out)[t] = make_uint4(res[0], res[1], res[2], res[3]);
 }
 
 }  // namespace pt
@@ -123,9 +154,11 @@ extern "C" int pt_nf4_quantize(const void* w_bf16, long long n, int via_fp16, ui
                                void* stream) {
     PT_REQUIRE(w_bf16 && packed && absmax, "pt_nf4_quantize: null pointer");
     PT_REQUIRE(n > 0 && n % 64 == 0, "pt_nf4_quantize: the element count must be a positive multiple of 64");
+    PT_REQUIRE(reinterpret_cast<uintptr_t>(w_bf16) % 16 == 0 && reinterpret_cast<uintptr_t>(packed) % 4 == 0,
+               "pt_nf4_quantize: the weight must be 16-byte aligned and the code buffer 4-byte aligned");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const long long nblocks = n / 64;
-    nf4_quantize_kernel<<<static_cast<unsigned>((nblocks + 7) / 8), 256, 0, ST(stream)>>>(
+    nf4_quantize_kernel<<<static_cast<unsigned>((nblocks + 31) / 32), 256, 0, ST(stream)>>>(
         static_cast<const __nv_bfloat16*>(w_bf16), nblocks, via_fp16, packed, absmax);
     return check_launch("nf4_quantize");
 }
@@ -144,9 +177,11 @@ extern "C" int pt_nf4_dequantize(const uint8_t* packed, const uint8_t* qabsmax, 
                                  const float* code256, long long n, int via_fp16, void* out_bf16, void* stream) {
     PT_REQUIRE(packed && qabsmax && absmax2 && code256 && out_bf16, "pt_nf4_dequantize: null pointer");
     PT_REQUIRE(n > 0 && n % 64 == 0, "pt_nf4_dequantize: the element count must be a positive multiple of 64");
+    PT_REQUIRE(reinterpret_cast<uintptr_t>(out_bf16) % 16 == 0 && reinterpret_cast<uintptr_t>(packed) % 4 == 0,
+               "pt_nf4_dequantize: the output must be 16-byte aligned and the code buffer 4-byte aligned");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
-    const long long nbytes = n / 2;
-    nf4_dequantize_kernel<<<static_cast<unsigned>((nbytes + 255) / 256), 256, 0, ST(stream)>>>(
-        packed, qabsmax, absmax2, offset, code256, nbytes, via_fp16, static_cast<__nv_bfloat16*>(out_bf16));
+    const long long nwords = n / 8;
+    nf4_dequantize_kernel<<<static_cast<unsigned>((nwords + 255) / 256), 256, 0, ST(stream)>>>(
+        packed, qabsmax, absmax2, offset, code256, nwords, via_fp16, static_cast<__nv_bfloat16*>(out_bf16));
     return check_launch("nf4_dequantize");
 }

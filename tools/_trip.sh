@@ -1,10 +1,6 @@
 #!/bin/bash
-# trip 42: NF4 frozen weights
-timeout 600 python -m pytest tests/test_nf4_gpu.py -m gpu -x -q > gpurun_out/t42_nf4_tests.log 2>&1
-timeout 600 python -m projectiontrainer_b200.train_projection_stage1 --synthetic 128 --batch_size 16 --num_epochs 1 \
-  --enable_qlora --disable_wandb --output_dir /tmp/s1_nf4 > gpurun_out/t42_cli_nf4.log 2>&1
-echo "exit $?" >> gpurun_out/t42_cli_nf4.log
-timeout 600 python -m projectiontrainer_b200.train_projection_stage1 --synthetic 32 --batch_size 8 --num_epochs 1 \
-  --synthetic_llm qwen3_8b --enable_qlora --disable_wandb --output_dir /tmp/s1_nf4q > gpurun_out/t42_cli_nf4_qwen.log 2>&1
-echo "exit $?" >> gpurun_out/t42_cli_nf4_qwen.log
-tail -n 5 gpurun_out/t42_nf4_tests.log
+# trip 44: after dropping the backward row kernel — attention / step tests, bench, launch list
+timeout 900 python -m pytest tests/test_attn_gpu.py tests/test_step_gpu.py -m gpu -x -q > gpurun_out/t44_tests.log 2>&1
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/t44_bench.json 2> gpurun_out/t44_bench.err
+timeout 400 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/t44_launches.csv python bench.py --profile --steps 1 > gpurun_out/t44_ncu.log 2>&1
+tail -n 3 gpurun_out/t44_tests.log
