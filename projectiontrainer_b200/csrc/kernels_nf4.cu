@@ -28,15 +28,19 @@ __constant__ float kNf4[16] = {-1.0f, -0.6961928009986877f, -0.5250730514526367f
                                0.7229568362236023f, 1.0f};
 
 // dQuantizeNF4: the code index is the number of midpoints strictly below x (every comparison is `>`); a NaN
-// (all-zero block: 0 * inf) fails them all and lands on code 0.
-__device__ __forceinline__ unsigned nf4_code(float x) {
-    constexpr float m[15] = {-0.8480964004993439f, -0.6106329262256622f, -0.4599952697753906f, -0.33967943489551544f,
-                             -0.23460740596055984f, -0.13791173323988914f, -0.045525018125772476f,
-                             0.03979014977812767f, 0.1202552504837513f, 0.2035212516784668f, 0.2920137718319893f,
-                             0.3893125355243683f, 0.5016634166240692f, 0.6427869200706482f, 0.8614784181118011f};
-    unsigned c = 0;
-#pragma unroll
-    for (int k = 0; k < 15; ++k) c += x > m[k] ? 1u : 0u;
+// (all-zero block: 0 * inf) fails them all and lands on code 0.  The midpoints are sorted, so four comparisons of
+// a bisection give that count; `mid` is the 16-entry shared-memory copy (entry 15 unused).
+__constant__ float kNf4Mid[16] = {-0.8480964004993439f, -0.6106329262256622f, -0.4599952697753906f,
+                                  -0.33967943489551544f, -0.23460740596055984f, -0.13791173323988914f,
+                                  -0.045525018125772476f, 0.03979014977812767f, 0.1202552504837513f,
+                                  0.2035212516784668f, 0.2920137718319893f, 0.3893125355243683f, 0.5016634166240692f,
+                                  0.6427869200706482f, 0.8614784181118011f, 2.0f};
+
+__device__ __forceinline__ unsigned nf4_code(const float* mid, float x) {
+    unsigned c = x > mid[7] ? 8u : 0u;
+    c += x > mid[c + 3] ? 4u : 0u;
+    c += x > mid[c + 1] ? 2u : 0u;
+    c += x > mid[c] ? 1u : 0u;
     return c;
 }
 
@@ -46,6 +50,9 @@ __device__ __forceinline__ unsigned nf4_code(float x) {
 __global__ void __launch_bounds__(256)
 nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int via_fp16,
                     uint8_t* __restrict__ packed, float* __restrict__ absmax) {
+    __shared__ float mid[16];
+    if (threadIdx.x < 16) mid[threadIdx.x] = kNf4Mid[threadIdx.x];
+    __syncthreads();
     const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;      // one thread per 8 values
     const long long blk = t >> 3;
     const bool on = blk < nblocks;
@@ -60,9 +67,12 @@ nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int 
         v[2 * j + 1] = __uint_as_float(words[j] & 0xffff0000u);
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        if (via_fp16) v[j] = __half2float(__float2half_rn(v[j]));
-        m = fmaxf(m, fabsf(v[j]));
+    for (int j = 0; j < 4; ++j) {
+        if (via_fp16) {                                            // packed conversions: full-rate instructions
+            const float2 r = __half22float2(__floats2half2_rn(v[2 * j], v[2 * j + 1]));
+            v[2 * j] = r.x; v[2 * j + 1] = r.y;
+        }
+        m = fmaxf(m, fmaxf(fabsf(v[2 * j]), fabsf(v[2 * j + 1])));
     }
 #pragma unroll
     for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
@@ -70,7 +80,7 @@ nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int 
     unsigned out = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const unsigned hi = nf4_code(__fmul_rn(v[2 * j], inv)), lo = nf4_code(__fmul_rn(v[2 * j + 1], inv));
+        const unsigned hi = nf4_code(mid, __fmul_rn(v[2 * j], inv)), lo = nf4_code(mid, __fmul_rn(v[2 * j + 1], inv));
         out |= ((hi << 4) | lo) << (8 * j);                        // byte j of the little-endian word
     }
     if (on) {
@@ -119,9 +129,10 @@ nf4_absmax_quantize_kernel(const float* __restrict__ absmax, long long nb, float
     if (threadIdx.x == 0) absmax2[blockIdx.x] = m;
 }
 
-// One thread per 4 packed bytes (8 values, one 16-byte store).  absmax = code[q] * absmax2 (fp32 product), + offset
-// (fp32 sum), value = NF4[c] * absmax rounded to fp16 (the dtype bitsandbytes quantised from) and then to bf16 (the
-// GEMM's dtype).
+// A CTA expands 1024 packed words (8192 values); a thread takes words tid, tid + 256, ... so that loads and the
+// 16-byte stores stay coalesced, and issues its four loads (and their statistics) before the arithmetic so that
+// enough bytes are in flight.  absmax = code[q] * absmax2 (fp32 product), + offset (fp32 sum), value = NF4[c] *
+// absmax rounded to fp16 (the dtype bitsandbytes quantised from) and then to bf16 (the GEMM's dtype).
 __global__ void __launch_bounds__(256)
 nf4_dequantize_kernel(const uint8_t* __restrict__ packed, const uint8_t* __restrict__ qabsmax,
                       const float* __restrict__ absmax2, float offset, const float* __restrict__ code256,
@@ -129,21 +140,36 @@ nf4_dequantize_kernel(const uint8_t* __restrict__ packed, const uint8_t* __restr
     __shared__ float nf4[16];
     if (threadIdx.x < 16) nf4[threadIdx.x] = kNf4[threadIdx.x];
     __syncthreads();
-    const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
-    if (t >= nwords) return;
-    const long long blk = t >> 3;
-    const float a = __fadd_rn(__fmul_rn(__ldg(code256 + qabsmax[blk]), absmax2[blk >> 8]), offset);
-    const unsigned word = reinterpret_cast<const unsigned*>(packed)[t];
-    unsigned res[4];
+    const long long base = static_cast<long long>(blockIdx.x) * 1024 + threadIdx.x;
+    unsigned word[4];
+    float a[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const unsigned byte = (word >> (8 * j)) & 0xffu;
-        float hi = __fmul_rn(nf4[byte >> 4], a), lo = __fmul_rn(nf4[byte & 15u], a);
-        if (via_fp16) { hi = __half2float(__float2half_rn(hi)); lo = __half2float(__float2half_rn(lo)); }
-        const __nv_bfloat162 pr = __nv_bfloat162(__float2bfloat16_rn(hi), __float2bfloat16_rn(lo));
-        res[j] = *reinterpret_cast<const unsigned*>(&pr);
+    for (int u = 0; u < 4; ++u) {
+        const long long t = base + u * 256;
+        word[u] = 0u; a[u] = 0.0f;
+        if (t < nwords) {
+            const long long blk = t >> 3;
+            word[u] = reinterpret_cast<const unsigned*>(packed)[t];
+            a[u] = __fadd_rn(__fmul_rn(__ldg(code256 + qabsmax[blk]), absmax2[blk >> 8]), offset);
+        }
     }
-    reinterpret_cast<uint4*>(out)[t] = make_uint4(res[0], res[1], res[2], res[3]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const long long t = base + u * 256;
+        unsigned res[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const unsigned byte = (word[u] >> (8 * j)) & 0xffu;
+            float hi = __fmul_rn(nf4[byte >> 4], a[u]), lo = __fmul_rn(nf4[byte & 15u], a[u]);
+            if (via_fp16) {
+                const float2 r = __half22float2(__floats2half2_rn(hi, lo));
+                hi = r.x; lo = r.y;
+            }
+            const __nv_bfloat162 pr = __floats2bfloat162_rn(hi, lo);
+            res[j] = *reinterpret_cast<const unsigned*>(&pr);
+        }
+        if (t < nwords) reinterpret_cast<uint4*>(out)[t] = make_uint4(res[0], res[1], res[2], res[3]);
+    }
 }
 
 }  // namespace pt
@@ -181,7 +207,7 @@ extern "C" int pt_nf4_dequantize(const uint8_t* packed, const uint8_t* qabsmax, 
                "pt_nf4_dequantize: the output must be 16-byte aligned and the code buffer 4-byte aligned");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     const long long nwords = n / 8;
-    nf4_dequantize_kernel<<<static_cast<unsigned>((nwords + 255) / 256), 256, 0, ST(stream)>>>(
+    nf4_dequantize_kernel<<<static_cast<unsigned>((nwords + 1023) / 1024), 256, 0, ST(stream)>>>(
         packed, qabsmax, absmax2, offset, code256, nwords, via_fp16, static_cast<__nv_bfloat16*>(out_bf16));
     return check_launch("nf4_dequantize");
 }

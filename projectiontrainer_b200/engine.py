@@ -170,6 +170,8 @@ class Stage1Engine:
         self._arenas: OrderedDict = OrderedDict()
         self._geometry = ("default",)
         self.max_geometries = int(os.environ.get("PT_STAGE1_MAX_GEOMETRIES", "6"))
+        total = torch.cuda.get_device_properties(device).total_memory if torch.cuda.is_available() else 0
+        self.arena_budget_bytes = int(float(os.environ.get("PT_STAGE1_ARENA_GB", "0")) * 2 ** 30) or int(0.6 * total)
         self._acc_grad = None           # gradient accumulated over micro-batches that did not step
         self._acc_pending = False
         self._rope: dict = {}
@@ -204,9 +206,16 @@ class Stage1Engine:
         if key in self._arenas:
             self._ws, self._graphs = self._arenas.pop(key)
         else:
+            # a new arena will be about as large as the one being left: keep the total under the byte budget too
+            # (long Stage-2 sequences at large batch sizes: six arenas of 40 GB do not fit)
+            nbytes = lambda ws: sum(t.numel() * t.element_size() for t in ws.values())
+            sizes = [nbytes(ws) for ws, _ in self._arenas.values()]
+            estimate = sizes[-1] if sizes else 0
             self._ws, self._graphs = {}, {}
-            while len(self._arenas) >= max(1, self.max_geometries):
+            while self._arenas and (len(self._arenas) >= max(1, self.max_geometries) or
+                                    sum(sizes) + estimate > self.arena_budget_bytes):
                 _, (ws, graphs) = self._arenas.popitem(last=False)
+                sizes.pop(0)
                 graphs.clear()
                 ws.clear()
         self._geometry = key

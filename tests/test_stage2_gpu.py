@@ -179,6 +179,37 @@ def test_geometry_arenas_are_bounded_and_reusable(cuda_dev):
             assert abs(loss - first.setdefault(T, loss)) < 1e-4, (rnd, T)
 
 
+def test_geometry_arenas_respect_the_byte_budget(cuda_dev):
+    """Besides the count limit, the arenas' total size stays under `arena_budget_bytes` (default 60 % of the device):
+    with a budget smaller than two activation sets only the current one and at most one more survive, and the numbers
+    of a re-entered (re-built) geometry are unchanged."""
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    vkw = dict(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=6, hq=2, hkv=1, hd=256, window=8, q_scalar=256.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev)
+    assert eng.arena_budget_bytes > 2 ** 30            # default: a fraction of a real device
+
+    def step(T):
+        px, ids, lab = O.synthetic_batch(2, T, ovc, olc, seed=300 + T, left_pad=True)
+        b = {"pixel_values": px.to(cuda_dev), "token_ids": ids.to(cuda_dev), "labels": lab.to(cuda_dev)}
+        return eng.train_step(b, 0.0, pad_id=olc.pad_id, weight_decay=0.0).item()
+
+    first = {T: step(T) for T in (8, 16)}
+    one = sum(t.numel() * t.element_size() for t in eng._ws.values())
+    eng.arena_budget_bytes = int(2.5 * one)            # room for the current arena + one parked + the estimate
+    for T in (24, 32, 8, 16, 40, 8):
+        loss = step(T)
+        parked = sum(sum(t.numel() * t.element_size() for t in ws.values()) for ws, _ in eng._arenas.values())
+        assert len(eng._arenas) <= 2 and parked <= eng.arena_budget_bytes, (T, len(eng._arenas), parked)
+        if T in first:
+            assert abs(loss - first[T]) < 1e-4, T
+
+
 def test_graph_capture_survives_a_concurrent_pinning_thread(cuda_dev):
     """DataLoader(pin_memory=True) pins every new batch shape on its own thread (cudaHostAlloc); with per-batch
     padding that happens all through training, also while the step thread captures a geometry's CUDA graph.
