@@ -58,7 +58,7 @@ def quantize_nf4(w: np.ndarray):
     in the high nibble), absmax float32 [n/64].  The kernel multiplies by the reciprocal of absmax."""
     w = np.asarray(w, dtype=np.float32).reshape(-1, BLOCK)
     absmax = np.abs(w).max(axis=1)
-    with np.errstate(divide="ignore", invalid="ignore"):
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
         inv = (np.float32(1.0) / absmax).astype(np.float32)
         x = (w * inv[:, None]).astype(np.float32)
     code = np.searchsorted(NF4_MIDPOINTS, x, side="left").astype(np.uint8)     # number of midpoints below x
@@ -108,7 +108,7 @@ def double_quant(absmax: np.ndarray, offset=None):
     for b in range(absmax2.shape[0]):
         blk = a[b * BLOCK2:(b + 1) * BLOCK2]
         absmax2[b] = np.abs(blk).max()
-        with np.errstate(divide="ignore", invalid="ignore"):
+        with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
             x = (blk * (np.float32(1.0) / absmax2[b])).astype(np.float32)
         q[b * BLOCK2:(b + 1) * BLOCK2] = _dquantize8(code, x)
     return q, absmax2, offset

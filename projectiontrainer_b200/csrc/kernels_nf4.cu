@@ -28,20 +28,41 @@ __constant__ float kNf4[16] = {-1.0f, -0.6961928009986877f, -0.5250730514526367f
                                0.7229568362236023f, 1.0f};
 
 // dQuantizeNF4: the code index is the number of midpoints strictly below x (every comparison is `>`); a NaN
-// (all-zero block: 0 * inf) fails them all and lands on code 0.  The midpoints are sorted, so four comparisons of
-// a bisection give that count; `mid` is the 16-entry shared-memory copy (entry 15 unused).
-__constant__ float kNf4Mid[16] = {-0.8480964004993439f, -0.6106329262256622f, -0.4599952697753906f,
-                                  -0.33967943489551544f, -0.23460740596055984f, -0.13791173323988914f,
-                                  -0.045525018125772476f, 0.03979014977812767f, 0.1202552504837513f,
-                                  0.2035212516784668f, 0.2920137718319893f, 0.3893125355243683f, 0.5016634166240692f,
-                                  0.6427869200706482f, 0.8614784181118011f, 2.0f};
+// (all-zero block: 0 * inf) fails them all and lands on code 0.  Evaluated with one table look-up and ONE exact
+// comparison: k = round(128 x + 128) (taken from the mantissa of an FMA against 2^23: a single, exact rounding)
+// names a cell of width 1/128, narrower than any gap between midpoints, so a cell holds at most one of them;
+// kNf4Lut[k] = number of midpoints below the cell's lower edge, and `x > mid[that count]` settles the one midpoint
+// the cell may contain.  An x that sits exactly on a cell edge may go to either cell: both give the same count,
+// because no midpoint lies on an edge (nearest: 4.4e-4 away).  x is clamped to [-1, 1] first (+-inf from a
+// subnormal absmax; NaN -> -1 -> code 0), which does not change the count.
+constexpr float kNf4MidHost[15] = {-0.8480964004993439f, -0.6106329262256622f, -0.4599952697753906f,
+                                   -0.33967943489551544f, -0.23460740596055984f, -0.13791173323988914f,
+                                   -0.045525018125772476f, 0.03979014977812767f, 0.1202552504837513f,
+                                   0.2035212516784668f, 0.2920137718319893f, 0.3893125355243683f,
+                                   0.5016634166240692f, 0.6427869200706482f, 0.8614784181118011f};
+struct Nf4Tables {
+    float mid[16];
+    unsigned char lut[512];
+};
+constexpr Nf4Tables make_nf4_tables() {
+    Nf4Tables t{};
+    for (int i = 0; i < 15; ++i) t.mid[i] = kNf4MidHost[i];
+    t.mid[15] = 2.0f;
+    for (int k = 0; k <= 256; ++k) {
+        const double edge = (k - 128.5) / 128.0;
+        unsigned char c = 0;
+        for (int i = 0; i < 15; ++i) c += static_cast<double>(kNf4MidHost[i]) < edge ? 1 : 0;
+        t.lut[k] = c;
+    }
+    return t;
+}
+__constant__ Nf4Tables kNf4Tables = make_nf4_tables();
 
-__device__ __forceinline__ unsigned nf4_code(const float* mid, float x) {
-    unsigned c = x > mid[7] ? 8u : 0u;
-    c += x > mid[c + 3] ? 4u : 0u;
-    c += x > mid[c + 1] ? 2u : 0u;
-    c += x > mid[c] ? 1u : 0u;
-    return c;
+__device__ __forceinline__ unsigned nf4_code(const Nf4Tables& t, float x) {
+    const float xc = fminf(fmaxf(x, -1.0f), 1.0f);
+    const unsigned k = __float_as_uint(__fmaf_rn(xc, 128.0f, 8388608.0f + 128.0f)) & 0x1ffu;
+    const unsigned c = t.lut[k];
+    return c + (xc > t.mid[c] ? 1u : 0u);
 }
 
 // Eight lanes per 64-value block (a warp covers four blocks, a CTA 32): each lane loads 8 consecutive bf16 as one
@@ -50,8 +71,9 @@ __device__ __forceinline__ unsigned nf4_code(const float* mid, float x) {
 __global__ void __launch_bounds__(256)
 nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int via_fp16,
                     uint8_t* __restrict__ packed, float* __restrict__ absmax) {
-    __shared__ float mid[16];
-    if (threadIdx.x < 16) mid[threadIdx.x] = kNf4Mid[threadIdx.x];
+    __shared__ Nf4Tables tab;
+    if (threadIdx.x < sizeof(Nf4Tables) / 4)
+        reinterpret_cast<unsigned*>(&tab)[threadIdx.x] = reinterpret_cast<const unsigned*>(&kNf4Tables)[threadIdx.x];
     __syncthreads();
     const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;      // one thread per 8 values
     const long long blk = t >> 3;
@@ -80,7 +102,7 @@ nf4_quantize_kernel(const __nv_bfloat16* __restrict__ w, long long nblocks, int 
     unsigned out = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const unsigned hi = nf4_code(mid, __fmul_rn(v[2 * j], inv)), lo = nf4_code(mid, __fmul_rn(v[2 * j + 1], inv));
+        const unsigned hi = nf4_code(tab, __fmul_rn(v[2 * j], inv)), lo = nf4_code(tab, __fmul_rn(v[2 * j + 1], inv));
         out |= ((hi << 4) | lo) << (8 * j);                        // byte j of the little-endian word
     }
     if (on) {

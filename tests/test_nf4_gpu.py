@@ -14,6 +14,8 @@ def _weights(kind, shape, seed):
         w[::7, ::13] *= 40.0
     elif kind == "tiny":                     # below fp16's normal range: the fp16 detour loses bits / flushes
         w = w * 1e-6
+    elif kind == "subnormal":                # absmax below fp32's normal range: 1 / absmax overflows to +inf
+        w = w * 1e-38
     elif kind == "zero_blocks":
         w.view(-1, 64)[::3] = 0.0
     elif kind == "constant":                 # every block has the same absmax: the second level sees all zeros
@@ -23,7 +25,7 @@ def _weights(kind, shape, seed):
 
 @pytest.mark.parametrize("via_fp16", [True, False], ids=["via_fp16", "direct"])
 @pytest.mark.parametrize("kind,shape", [("gauss", (1152, 256)), ("gauss", (6912, 1152)), ("outliers", (1024, 1152)),
-                                        ("tiny", (256, 128)), ("zero_blocks", (512, 192)), ("constant", (64, 64)),
+                                        ("tiny", (256, 128)), ("subnormal", (128, 128)), ("zero_blocks", (512, 192)), ("constant", (64, 64)),
                                         ("gauss", (1, 64)), ("gauss", (257, 64 * 3))])
 def test_nf4_quantize_dequantize_bit_exact_vs_oracle(cuda_dev, kind, shape, via_fp16):
     from oracle import nf4_oracle as N
