@@ -48,6 +48,13 @@ def dynamic_map() -> np.ndarray:
     return torch.tensor(data, dtype=torch.float32).numpy()
 
 
+def _ftz(x):
+    """bitsandbytes' CUDA sources are built with --use_fast_math, i.e. -ftz=true: single-precision operations flush
+    subnormal inputs and results to zero (sign kept).  Applied after every fp32 operation restated below."""
+    x = np.asarray(x, dtype=np.float32)
+    return np.where(np.abs(x) < np.float32(2.0 ** -126), np.copysign(np.float32(0), x), x).astype(np.float32)
+
+
 def _round_dtype(x: np.ndarray, dtype: str) -> np.ndarray:
     t = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
     return t.to({"fp16": torch.float16, "bf16": torch.bfloat16}[dtype]).float().numpy()
@@ -56,11 +63,11 @@ def _round_dtype(x: np.ndarray, dtype: str) -> np.ndarray:
 def quantize_nf4(w: np.ndarray):
     """kQuantizeBlockwise<NF4>, blocksize 64: w float32 [n] (n % 64 == 0) -> packed uint8 [n/2] (first value of a pair
     in the high nibble), absmax float32 [n/64].  The kernel multiplies by the reciprocal of absmax."""
-    w = np.asarray(w, dtype=np.float32).reshape(-1, BLOCK)
+    w = _ftz(w).reshape(-1, BLOCK)
     absmax = np.abs(w).max(axis=1)
     with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
-        inv = (np.float32(1.0) / absmax).astype(np.float32)
-        x = (w * inv[:, None]).astype(np.float32)
+        inv = _ftz(np.float32(1.0) / absmax)
+        x = _ftz(w * inv[:, None])
     code = np.searchsorted(NF4_MIDPOINTS, x, side="left").astype(np.uint8)     # number of midpoints below x
     code[np.isnan(x)] = 0                                                       # all-zero block: every `>` is false
     code = code.reshape(-1, 2)
@@ -101,7 +108,7 @@ def double_quant(absmax: np.ndarray, offset=None):
     if offset is None:          # tests pass the device's fp32 mean: its summation order is not the CPU's
         offset = torch.from_numpy(absmax).mean().item()
     offset = np.float32(offset)
-    a = (absmax - offset).astype(np.float32)
+    a = _ftz(absmax - offset)
     nb = a.shape[0]
     q = np.empty(nb, dtype=np.uint8)
     absmax2 = np.empty((nb + BLOCK2 - 1) // BLOCK2, dtype=np.float32)
@@ -109,7 +116,7 @@ def double_quant(absmax: np.ndarray, offset=None):
         blk = a[b * BLOCK2:(b + 1) * BLOCK2]
         absmax2[b] = np.abs(blk).max()
         with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
-            x = (blk * (np.float32(1.0) / absmax2[b])).astype(np.float32)
+            x = _ftz(blk * _ftz(np.float32(1.0) / absmax2[b]))
         q[b * BLOCK2:(b + 1) * BLOCK2] = _dquantize8(code, x)
     return q, absmax2, offset
 
@@ -119,10 +126,10 @@ def dequantize_nf4(packed, qabsmax, absmax2, offset, out_dtype: str = "fp16") ->
     NF4[c] * absmax rounded to the dtype the weight was quantised from.  Returns those values as float32 [n]."""
     code = dynamic_map()
     nb = qabsmax.shape[0]
-    a = (code[qabsmax] * np.repeat(absmax2, BLOCK2)[:nb]).astype(np.float32)
-    a = (a + np.float32(offset)).astype(np.float32)
+    a = _ftz(code[qabsmax] * np.repeat(absmax2, BLOCK2)[:nb])
+    a = _ftz(a + np.float32(offset))
     c = np.stack([packed >> 4, packed & 0x0F], axis=1).reshape(-1, BLOCK)
-    v = (NF4_TABLE[c] * a[:, None]).astype(np.float32).reshape(-1)
+    v = _ftz(NF4_TABLE[c] * a[:, None]).reshape(-1)
     return _round_dtype(v, out_dtype)
 
 
