@@ -293,7 +293,8 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         del eng
         torch.cuda.empty_cache()
-        cb, *_ = cpu_step_sample(30.0, 1, 0, args.tokens)
+        # ~10-20 s of CPU work: one untimed warm-up image (thread pool, page faults), then up to 8 timed ones
+        cb, *_ = cpu_step_sample(20.0, 8, 1, args.tokens)
         line["cpu_baseline"] = cb
     print(json.dumps(line), flush=True)
     if world > 1:
