@@ -6,10 +6,12 @@ fails, a RuntimeError is raised.  Nothing here routes to PyTorch math.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libpt_stage1.so"
+# PT_STAGE1_LIB: A/B probes load another build of the same library (tools/); never set in the product path
+LIB_PATH = Path(os.environ.get("PT_STAGE1_LIB") or PKG / "libpt_stage1.so")
 
 PT_BF16, PT_F32, PT_I64, PT_I32 = 0, 1, 2, 3
 BAND_NONE, BAND_SCORES, BAND_K_BY_QUERY, BAND_K_BY_KEY = 0, 1, 2, 3

@@ -156,28 +156,32 @@ __device__ __forceinline__ void epi_chunk_gbwd(const uint32_t (&v)[32], uint32_t
         }
     }
     const uint32_t sp = stg + rsub * 128;
+    const GluConsts2 k2 = glu_consts2(o.glu);
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
         const int r = it * 4 + rsub;
         const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
         const bool ok = col_ok && r >= o.row_lo && r < o.rows_valid;
-        const float d[4] = {a.x, a.y, a.z, a.w};
-        const float g[4] = {bf16_lo(gq[it].x), bf16_hi(gq[it].x), bf16_lo(gq[it].y), bf16_hi(gq[it].y)};
-        const float u[4] = {bf16_lo(uq[it].x), bf16_hi(uq[it].x), bf16_lo(uq[it].y), bf16_hi(uq[it].y)};
-        float dg[4], du[4];
+        // two column pairs per lane and row, each as one packed-f32 register pair (FFMA2 / FMUL2)
+        const uint32_t gw[2] = {gq[it].x, gq[it].y}, uw[2] = {uq[it].x, uq[it].y};
+        const uint64_t d2[2] = {f2_pack(a.x, a.y), f2_pack(a.z, a.w)};
+        uint32_t wg[2], wu[2];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float val, grad;
-            glu_act_fast_both(g[j], o.glu, val, grad);
-            dg[j] = d[j] * u[j] * grad;
-            du[j] = d[j] * val;
+        for (int j = 0; j < 2; ++j) {
+            const uint64_t g2 = f2_pack(bf16_lo(gw[j]), bf16_hi(gw[j]));
+            const uint64_t u2 = f2_pack(bf16_lo(uw[j]), bf16_hi(uw[j]));
+            uint64_t val, grad;
+            glu_act_fast_both2(g2, k2, val, grad);
+            float x0, x1;
+            f2_unpack(f2_mul(f2_mul(d2[j], u2), grad), x0, x1);
+            wg[j] = pack_bf16(x0, x1);
+            f2_unpack(f2_mul(d2[j], val), x0, x1);
+            wu[j] = pack_bf16(x0, x1);
         }
         if (ok) {
             uint8_t* cp = o.C + r * o.c_row + c * 2;
-            uint2 w; w.x = pack_bf16(dg[0], dg[1]); w.y = pack_bf16(dg[2], dg[3]);
-            *reinterpret_cast<uint2*>(cp) = w;
-            w.x = pack_bf16(du[0], du[1]); w.y = pack_bf16(du[2], du[3]);
-            *reinterpret_cast<uint2*>(cp + o.ff_bytes) = w;
+            *reinterpret_cast<uint2*>(cp) = make_uint2(wg[0], wg[1]);
+            *reinterpret_cast<uint2*>(cp + o.ff_bytes) = make_uint2(wu[0], wu[1]);
         }
     }
     __syncwarp();

@@ -127,6 +127,43 @@ __device__ __forceinline__ void glu_act_fast_both(float z, const GluConsts& c, f
     const float r = z * fmaf(c.c3, z2, c.c2);
     grad = a * fmaf(r, 1.f - a, 1.f);
 }
+// The same on two values per instruction: Blackwell's packed-f32 FMA pipe (FFMA2 / FMUL2 via fma/mul .f32x2 on a
+// 64-bit register pair) halves the issue slots of the epilogue, which is what bounds the GeGLU-backward GEMM.
+// A bf16x2 word unpacks straight into such a pair {w << 16, w & 0xffff0000}.  Per-element operations and their
+// rounding are those of glu_act_fast_both.
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+struct GluConsts2 { uint64_t c0, c1, c2, c3, half, one, neg_one; };
+__device__ __forceinline__ GluConsts2 glu_consts2(const GluConsts& c) {
+    return GluConsts2{f2_pack(c.c0, c.c0), f2_pack(c.c1, c.c1), f2_pack(c.c2, c.c2), f2_pack(c.c3, c.c3),
+                      f2_pack(0.5f, 0.5f), f2_pack(1.f, 1.f), f2_pack(-1.f, -1.f)};
+}
+__device__ __forceinline__ void glu_act_fast_both2(uint64_t z, const GluConsts2& c, uint64_t& val, uint64_t& grad) {
+    const uint64_t z2 = f2_mul(z, z);
+    float w0, w1;
+    f2_unpack(f2_mul(z, f2_fma(c.c1, z2, c.c0)), w0, w1);
+    const uint64_t t = f2_pack(tanh_fast(w0), tanh_fast(w1));
+    const uint64_t a = f2_fma(c.half, t, c.half);
+    val = f2_mul(z, a);
+    const uint64_t r = f2_mul(z, f2_fma(c.c3, z2, c.c2));
+    grad = f2_mul(a, f2_fma(r, f2_fma(a, c.neg_one, c.one), c.one));
+}
 // exact SiLU for the unfused kernels
 __device__ __forceinline__ float silu_f(float z) { return z / (1.f + __expf(-z)); }
 __device__ __forceinline__ float silu_grad_f(float z) {
