@@ -185,6 +185,12 @@ class Stage1Engine:
             os.environ.get("PT_STAGE1_FUSE_ATTN_FWD", "1") != "0"
         self.bn_hint_dkv = int(os.environ.get("PT_STAGE1_BN_DKV", "0"))     # tile-width hint of the dV / dK GEMMs
         self.fuse_softmax_bwd = os.environ.get("PT_STAGE1_FUSE_SOFTMAX_BWD", "1") != "0"
+        # dV / dK / dQ of the attention backward on three streams (fork / join inside the captured graph).  Off by
+        # default: measured neutral on B200 (101.3 / 101.9 ms per step without, 100.9 / 102.3 ms with) — the step
+        # runs under sw_power_cap, and filling the last-wave bubbles lowered the SM clock (1459 -> 1421 MHz) by as
+        # much as it saved.
+        self.attn_bwd_streams = os.environ.get("PT_STAGE1_ATTN_BWD_STREAMS", "0") != "0"
+        self._side = None
         self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
@@ -430,6 +436,16 @@ class Stage1Engine:
         return loss
 
     # ------------------------------------------------------------------ LLM backward (input grads only)
+    def _attn_dv(self, a, d_o, d_qkv, B, S, G, ld, QKV, win):
+        """dV[b,k,kvh,:] = sum_g P[b,kvh*G+g]^T dO[b,:,kvh*G+g,:]  -> v columns of d_qkv"""
+        c = self.lcfg
+        hd, hq, hkv = c.hd, c.hq, c.hkv
+        ops.gemm_raw(M=S, N=hd, K=S, A=a["P"], lda=ld, a_mn=True, B=d_o, ldb=hq * hd, b_mn=True,
+                     Cout=d_qkv, c_off=(hq + hkv) * hd, ldc=QKV, nz=(hkv, B, 1),
+                     a_zs=(G * S * ld, hq * S * ld, 0), b_zs=(G * hd, S * hq * hd, 0),
+                     c_zs=(hd, S * QKV, 0), kg=G, a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY,
+                     band_window=win, bn_hint=self.bn_hint_dkv)
+
     def llm_backward(self) -> torch.Tensor:
         """Consumes self.saved; returns dL/dx0 as f32 [B*S, h] (weights are frozen: no wgrad GEMMs)."""
         c, Lm, s = self.lcfg, self.llm, self.saved
@@ -456,6 +472,13 @@ class Stage1Engine:
         d_qkv = self.buf("b_dqkv", (M, QKV), BF16)
         sandwich = c.sandwich_norm
         pair = sandwich and h <= 2560
+        side = self.attn_bwd_streams and ops.GEMM_PROFILE is None     # per-launch timing pass: one stream
+        if side:
+            if self._side is None:
+                self._side = (torch.cuda.Stream(self.device), torch.cuda.Stream(self.device),
+                              *(torch.cuda.Event() for _ in range(4)))
+            sv, sk, ev_do, ev_dv, ev_ds, ev_dk = self._side
+            main = torch.cuda.current_stream()
         for li in range(len(Lm.layers) - 1, -1, -1):
             L, a = Lm.layers[li], s["layers"][li]
             cos_t, sin_t = self.rope(S, a["full"])
@@ -482,6 +505,12 @@ class Stage1Engine:
             ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
             win = 0 if a["full"] else c.window
+            if side:        # dV needs only P and dO: it runs beside delta + the dS GEMM
+                ev_do.record(main)
+                sv.wait_event(ev_do)
+                with torch.cuda.stream(sv):
+                    self._attn_dv(a, d_o, d_qkv, B, S, G, ld, QKV, win)
+                    ev_dv.record(sv)
             if self.fuse_softmax_bwd:
                 # dS = scale * P * (dO V^T - delta) in the GEMM epilogue, delta = rowsum(dO * O)
                 ops.attn_delta(d_o, a["ao"], delta, S, hq, hd)
@@ -492,23 +521,34 @@ class Stage1Engine:
                 self._scores_like(d_o, 0, hq * hd, (hd, G * hd, S * hq * hd), a["qkv"], (hq + hkv) * hd,
                                   QKV, (0, hd, S * QKV), dP, B, S, 1.0, window=win)
                 ops.softmax_bwd(a["P"], dP, dS, B * hq * S, S, ld, scale, Sq=S, causal=1, window=win)
-            # dV[b,k,kvh,:] = sum_g P[b,kvh*G+g]^T dO[b,:,kvh*G+g,:]  -> v columns of d_qkv
-            ops.gemm_raw(M=S, N=hd, K=S, A=a["P"], lda=ld, a_mn=True, B=d_o, ldb=hq * hd, b_mn=True,
-                         Cout=d_qkv, c_off=(hq + hkv) * hd, ldc=QKV, nz=(hkv, B, 1),
-                         a_zs=(G * S * ld, hq * S * ld, 0), b_zs=(G * hd, S * hq * hd, 0),
-                         c_zs=(hd, S * QKV, 0), kg=G, a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY,
-                         band_window=win, bn_hint=self.bn_hint_dkv)
+            # The three remaining contractions are independent persistent launches whose last wave leaves most
+            # SMs idle (dV / dK: 96 tiles over 74 clusters); on separate streams the next launch's clusters take
+            # those SMs as they free up.
+            def dk_gemm():
+                # dK[b,k,kvh,:] = sum_g dS[b,kvh*G+g]^T Q[b,:,kvh*G+g,:]
+                ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, a_mn=True, B=a["q"], ldb=hq * hd, b_mn=True,
+                             Cout=dk, ldc=hkv * hd, nz=(hkv, B, 1), a_zs=(G * S * ld, hq * S * ld, 0),
+                             b_zs=(G * hd, S * hq * hd, 0), c_zs=(hd, S * hkv * hd, 0), kg=G,
+                             a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY, band_window=win,
+                             bn_hint=self.bn_hint_dkv)
+            if side:
+                ev_ds.record(main)
+                sk.wait_event(ev_ds)
+                with torch.cuda.stream(sk):
+                    dk_gemm()
+                    ev_dk.record(sk)
+            else:
+                self._attn_dv(a, d_o, d_qkv, B, S, G, ld, QKV, win)
             # dQ[b,q,head,:] = dS[b,head] K[b,:,kvh,:]
             ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
                          ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
                          b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY,
                          band_window=win)
-            # dK[b,k,kvh,:] = sum_g dS[b,kvh*G+g]^T Q[b,:,kvh*G+g,:]
-            ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, a_mn=True, B=a["q"], ldb=hq * hd, b_mn=True,
-                         Cout=dk, ldc=hkv * hd, nz=(hkv, B, 1), a_zs=(G * S * ld, hq * S * ld, 0),
-                         b_zs=(G * hd, S * hq * hd, 0), c_zs=(hd, S * hkv * hd, 0), kg=G,
-                         a_kgs=S * ld, b_kgs=hd, band=ops.BAND_K_BY_KEY, band_window=win,
-                         bn_hint=self.bn_hint_dkv)
+            if side:
+                main.wait_event(ev_dv)
+                main.wait_event(ev_dk)
+            else:
+                dk_gemm()
             ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                 hkv, hd, c.eps)
             ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)

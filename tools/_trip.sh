@@ -1,7 +1,9 @@
 #!/bin/bash
-# trip 58: A/B of the GeGLU-backward epilogue with packed-f32 math (old = HEAD)
-for i in 1 2; do
-  PT_STAGE1_LIB=$PWD/projectiontrainer_b200/libpt_stage1_old.so timeout 120 python tools/geglu_bwd_one.py 2>&1 | head -n 1 | sed "s/^/old: /"
-  timeout 120 python tools/geglu_bwd_one.py 2>&1 | head -n 2 | sed "s/^/new: /"
-done
-timeout 300 python -m pytest tests/test_gemm_gpu.py -m gpu -x -q 2>&1 | tail -n 2
+# trip 59: attention-backward GEMMs on three streams: step tests + bench A/B
+timeout 600 python -m pytest tests/test_step_gpu.py tests/test_stage2_gpu.py -m gpu -x -q 2>&1 | tail -n 3
+PT_STAGE1_ATTN_BWD_STREAMS=0 timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_nostreams.json 2> gpurun_out/s29_bench_nostreams.err
+timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_streams.json 2> gpurun_out/s29_bench_streams.err
+PT_STAGE1_ATTN_BWD_STREAMS=0 timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_nostreams2.json 2>> gpurun_out/s29_bench_nostreams.err
+timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_streams2.json 2>> gpurun_out/s29_bench_streams.err
+for f in nostreams streams nostreams2 streams2; do echo $f; cut -c1-200 gpurun_out/s29_bench_$f.json; grep -o '"clocks": {[^}]*}' gpurun_out/s29_bench_$f.json; done
+tail -n 3 gpurun_out/s29_bench_streams.err
