@@ -530,6 +530,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 // accumulator columns [0,128) = gate, [128,256) = up of ff columns n_blk*128 .. +127; this warp
                 // produces two 32-column chunks: gate and up pre-activations -> C, gelu_tanh(gate)*up -> aux
                 const bool live = rows_valid > row_lo;                                   // warp-uniform
+                const GluConsts2 k2 = glu_consts2(p.glu);
 #pragma unroll 1
                 for (int c2 = 0; c2 < 2; ++c2) {
                     const int cg = (hf * 2 + c2) * 32;
@@ -555,10 +556,14 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     uint8_t* crow = static_cast<uint8_t*>(p.C) + (coff + static_cast<long long>(row0) * p.ldc) * 2;
                     o.C = crow + static_cast<long long>(colg) * 2;
                     epi_chunk<PT_ACT_NONE>(vg, stg, lane, o);
+                    // on the packed-f32 pipe (FFMA2 / FMUL2): two columns per instruction
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float g = round_bf16(__uint_as_float(vg[j])), u = round_bf16(__uint_as_float(vu[j]));
-                        vg[j] = __float_as_uint(glu_act_fast(g, p.glu) * u);
+                    for (int j = 0; j < 32; j += 2) {
+                        const uint64_t g2 = round_bf16_pair(__uint_as_float(vg[j]), __uint_as_float(vg[j + 1]));
+                        const uint64_t u2 = round_bf16_pair(__uint_as_float(vu[j]), __uint_as_float(vu[j + 1]));
+                        float a0, a1;
+                        f2_unpack(f2_mul(glu_act_fast2(g2, k2), u2), a0, a1);
+                        vg[j] = __float_as_uint(a0); vg[j + 1] = __float_as_uint(a1);
                     }
                     o.C = crow + static_cast<long long>(p.ff + colg) * 2;
                     epi_chunk<PT_ACT_NONE>(vu, stg, lane, o);

@@ -164,6 +164,18 @@ __device__ __forceinline__ void glu_act_fast_both2(uint64_t z, const GluConsts2&
     const uint64_t r = f2_mul(z, f2_fma(c.c3, z2, c.c2));
     grad = f2_mul(a, f2_fma(r, f2_fma(a, c.neg_one, c.one), c.one));
 }
+// value only (GeGLU-forward epilogue): act = z a on a packed pair, 5 packed FP instructions + 2 MUFU per pair
+__device__ __forceinline__ uint64_t glu_act_fast2(uint64_t z, const GluConsts2& c) {
+    float w0, w1;
+    f2_unpack(f2_mul(z, f2_fma(c.c1, f2_mul(z, z), c.c0)), w0, w1);
+    const uint64_t h = f2_mul(c.half, z);
+    return f2_fma(h, f2_pack(tanh_fast(w0), tanh_fast(w1)), h);
+}
+// {round_bf16(a), round_bf16(b)} as a packed pair: one cvt.rn.bf16x2 and the two-instruction unpack
+__device__ __forceinline__ uint64_t round_bf16_pair(float a, float b) {
+    const uint32_t w = pack_bf16(a, b);
+    return f2_pack(bf16_lo(w), bf16_hi(w));
+}
 // exact SiLU for the unfused kernels
 __device__ __forceinline__ float silu_f(float z) { return z / (1.f + __expf(-z)); }
 __device__ __forceinline__ float silu_grad_f(float z) {
