@@ -271,6 +271,10 @@ int pt_clip_adamw(float* p, const float* g, float* m, float* v, void* shadow_bf1
                   const float* sumsq, float grad_scale, float max_norm, float lr, float beta1, float beta2,
                   float eps, float weight_decay, int step, void* stream);
 int pt_cast_f32_bf16(const float* x, void* y_bf16, long long n, void* stream);
+/* out[i] = bf16(sum_s x[s * slice_elems + i]), i < slice_elems (% 4 == 0): reduces the f32 partials of a split-K
+ * pt_gemm_bf16 launch (K slices as a batch dim) — the LM-head input gradient dlogits @ E of
+ * ref:Stage1/projector_trainer.py:236 (accelerator.backward through HF:models/gemma3/modeling_gemma3.py lm_head). */
+int pt_sum_slices(const float* x, long long slice_elems, int n_slices, void* out_bf16, void* stream);
 /* out[r] = bf16(x[remap(r)]) — e.g. the image-token rows of dL/dX0 handed to the projector backward. */
 int pt_gather_cast_rows(const float* x, void* out_bf16, int rows_out, int D, int group_rows_out,
                         int group_rows_in, int group_row0, void* stream);

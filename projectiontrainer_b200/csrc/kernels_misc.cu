@@ -277,6 +277,21 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16*
         y[i] = __float2bfloat16(x[i]);
 }
 
+// out[i] = bf16(sum_s x[s * slice + i]): the f32 partials of a split-K GEMM (slice % 4 == 0), 16-byte loads,
+// the S loads of one output quad independent of each other.
+__global__ void sum_slices_kernel(const float4* __restrict__ x, long long n4, int S, uint2* __restrict__ out) {
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float4 a = x[i];
+#pragma unroll 4
+        for (int s = 1; s < S; ++s) {
+            const float4 b = x[s * n4 + i];
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        out[i] = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+    }
+}
+
 static inline int grid_for(long long n, int threads) {
     long long b = (n + threads - 1) / threads;
     const long long cap = static_cast<long long>(num_sms()) * 16;
@@ -402,4 +417,14 @@ extern "C" int pt_cast_f32_bf16(const float* x, void* y_bf16, long long n, void*
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     cast_f32_bf16_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, BF(y_bf16), n);
     return check_launch("cast_f32_bf16");
+}
+
+extern "C" int pt_sum_slices(const float* x, long long slice_elems, int n_slices, void* out_bf16, void* stream) {
+    PT_REQUIRE(x && out_bf16 && slice_elems > 0 && n_slices >= 1, "pt_sum_slices: bad arguments");
+    PT_REQUIRE(slice_elems % 4 == 0, "pt_sum_slices: slice_elems must be a multiple of 4 (%lld)", slice_elems);
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    const long long n4 = slice_elems / 4;
+    sum_slices_kernel<<<grid_for(n4, 256), 256, 0, ST(stream)>>>(reinterpret_cast<const float4*>(x), n4, n_slices,
+                                                                 reinterpret_cast<uint2*>(out_bf16));
+    return check_launch("sum_slices");
 }

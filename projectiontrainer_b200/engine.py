@@ -191,6 +191,8 @@ class Stage1Engine:
         # much as it saved.
         self.attn_bwd_streams = os.environ.get("PT_STAGE1_ATTN_BWD_STREAMS", "0") != "0"
         self._side = None
+        # LM-head input gradient as a split-K launch (K = vocab) + partial sum; 1 = the single 128-wide-tile launch
+        self.lm_head_splitk = int(os.environ.get("PT_STAGE1_LM_HEAD_SPLITK", "8"))
         self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
@@ -455,7 +457,11 @@ class Stage1Engine:
         G, ld, QKV = self._attn_geometry(B, S)
         scale = c.q_scalar ** -0.5
         d_yf = self.buf("b_dyf", (R, h), BF16)
-        ops.linear_dgrad(s["logits"], Lm.lm_head, out=d_yf)        # dlogits @ E
+        if self.lm_head_splitk > 1 and c.vocab % (self.lm_head_splitk * 64) == 0 and (R * h) % 4 == 0:
+            part = self.buf("b_dyf_part", (self.lm_head_splitk, R, h), F32)
+            ops.linear_dgrad_splitk(s["logits"], Lm.lm_head, out=d_yf, partials=part, splits=self.lm_head_splitk)
+        else:
+            ops.linear_dgrad(s["logits"], Lm.lm_head, out=d_yf)        # dlogits @ E
         dx = self.buf("b_dx", (M, h), F32)
         dx.zero_()
         grp = (T, S, s["lab0"])

@@ -124,6 +124,23 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out=None, out_dtype=torch
     return out
 
 
+def linear_dgrad_splitk(dy: torch.Tensor, w: torch.Tensor, *, out: torch.Tensor, partials: torch.Tensor,
+                        splits: int) -> torch.Tensor:
+    """linear_dgrad for a very long contraction and a small output (LM head: dy [R,V] @ w [V,h]): the K range is cut
+    into `splits` slices run as a batch dim of ONE launch on 256-wide tiles (f32 partials [splits, M, K_out]), then
+    summed into the bf16 result.  80 tiles x 8 slices fill 74 clusters to 96 %, where the single launch has to take
+    128-wide tiles (144 tiles) and is bound by operand ingest per flop: 2395 -> 1875 us at R=4096, V=262144, h=1152."""
+    M, N = dy.shape
+    N2, K = w.shape
+    assert N == N2 and dy.stride(1) == 1 and w.stride(1) == 1 and N % (splits * 64) == 0 and (M * K) % 4 == 0
+    assert partials.dtype == torch.float32 and partials.numel() >= splits * M * K and out.is_contiguous()
+    ks = N // splits
+    gemm_raw(M=M, N=K, K=ks, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True, Cout=partials, ldc=K,
+             nz=(splits, 1, 1), a_zs=(ks, 0, 0), b_zs=(ks * w.stride(0), 0, 0), c_zs=(M * K, 0, 0), bn_hint=256)
+    _lib.call("pt_sum_slices", _ptr(partials), C.c_longlong(M * K), int(splits), _ptr(out), _stream())
+    return out
+
+
 def geglu_fusable(ff: int) -> bool:
     """The fused GeGLU GEMM epilogues tile ff in 128-column blocks (CTA-pair kernel only)."""
     return ff % 128 == 0

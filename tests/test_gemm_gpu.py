@@ -75,6 +75,30 @@ def test_gemm_dgrad_mn_major_b(cuda_dev, M, N, K):
     _check(out, ref, tol=1e-3, name="dgrad")
 
 
+@pytest.mark.parametrize("M,V,h,S", [(64, 512, 64, 8), (300, 4096, 328, 4), (1000, 16384, 1152, 8),
+                                     (24, 2048, 256, 2)])
+def test_gemm_dgrad_split_k(cuda_dev, gemm_impl, M, V, h, S):
+    """LM-head input gradient as a split-K launch (K slices as a batch dim, f32 partials) + pt_sum_slices:
+    same result as the single launch, and both match the f32 matmul."""
+    if gemm_impl != 2:
+        pytest.skip("bn_hint addresses the CTA-pair kernel")
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(V + h)
+    Vp = V + 8                                  # padded row stride, as the engine's logits buffer has
+    dy = _rand((M, Vp), cuda_dev, 0.1)[:, :V]
+    w = _rand((V, h), cuda_dev, 0.05)
+    ref = dy.float() @ w.float()
+    one = ops.linear_dgrad(dy, w)
+    part = torch.full((S, M, h), float("nan"), device=cuda_dev, dtype=torch.float32)
+    out = torch.empty(M, h, device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_dgrad_splitk(dy, w, out=out, partials=part, splits=S)
+    assert torch.isfinite(part).all()
+    _check(part.sum(0), ref, tol=1e-3, name="split-K partials")
+    _check(out, ref, name="split-K bf16")
+    # one bf16 rounding of (nearly) the same f32 sum on both sides
+    assert (out.float() - one.float()).abs().max().item() <= 2 ** -7 * ref.abs().max().item()
+
+
 @pytest.mark.parametrize("T,N,K", [(256, 128, 256), (1000, 1152, 1024), (18400, 1152, 256),
                                    (703, 703, 256)])
 def test_gemm_wgrad_mn_major_ab(cuda_dev, T, N, K):

@@ -1,7 +1,9 @@
 #!/bin/bash
-# trip 61: A/B of the GeGLU-forward epilogue with packed-f32 math (old = HEAD)
-for i in 1 2; do
-  PT_STAGE1_LIB=$PWD/projectiontrainer_b200/libpt_stage1_old.so timeout 120 python tools/geglu_one.py 2>&1 | head -n 1 | sed "s/^/old: /"
-  timeout 120 python tools/geglu_one.py 2>&1 | head -n 2 | sed "s/^/new: /"
-done
-timeout 300 python -m pytest tests/test_gemm_gpu.py tests/test_step_gpu.py -m gpu -x -q 2>&1 | tail -n 2
+# trip 63: split-K LM-head input gradient: tests + bench A/B
+timeout 600 python -m pytest tests/test_gemm_gpu.py tests/test_step_gpu.py tests/test_stage2_gpu.py -m gpu -x -q 2>&1 | tail -n 3
+PT_STAGE1_LM_HEAD_SPLITK=1 timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_sk1.json 2> gpurun_out/s29_bench_sk1.err
+timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_sk8.json 2> gpurun_out/s29_bench_sk8.err
+PT_STAGE1_LM_HEAD_SPLITK=1 timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_sk1b.json 2>> gpurun_out/s29_bench_sk1.err
+timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_sk8b.json 2>> gpurun_out/s29_bench_sk8.err
+for f in sk1 sk8 sk1b sk8b; do echo $f; grep -o '"ms_per_step": [0-9.]*' gpurun_out/s29_bench_$f.json | head -n 1; grep -o '"clocks": {[^}]*}' gpurun_out/s29_bench_$f.json; grep -o '"last_loss": [0-9.]*' gpurun_out/s29_bench_$f.json; done
+tail -n 3 gpurun_out/s29_bench_sk8.err
