@@ -360,9 +360,13 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int tile_iters = (kb_hi - kb_lo) * p.kg;
                 const int m0 = tile_m + static_cast<int>(rank) * BM;
                 // fused GeGLU: the pair's tile is [128 gate rows | the 128 up rows of the same ff range]
+                // half-width last n tile (GemmDev::n_half): a full in-bounds box whose second half holds this CTA's
+                // BNH / 2 rows of B
+                const bool half = p.n_half && n_blk == nt - 1;
                 const int n0 = ACT == PT_ACT_GEGLU
                                    ? n_blk * BNH + static_cast<int>(rank) * p.ff
-                                   : tile_n + static_cast<int>(rank) * BNH;
+                                   : half ? tile_n - BNH / 2 + static_cast<int>(rank) * (BNH / 2)
+                                          : tile_n + static_cast<int>(rank) * BNH;
                 int g = 0, kb = kb_lo;
                 for (int it = 0; it < tile_iters; ++it) {
                     if (kga) ea0 = g;
@@ -407,8 +411,19 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             uint32_t acc_phase = 0;
             int last_acc = -1;
             uint32_t last_phase = 0;
+            const uint32_t idesc_half = ptx::make_idesc_bf16(TM, BN / 2, p.a_mn, p.b_mn);
             for (int t = cid; t < total_tiles; t += ncl) {
                 int tile_iters = k_iters;
+                bool half = false;
+                if (p.n_half) {
+                    int m_blk, n_blk, z[3];
+                    decode(t, m_blk, n_blk, z);
+                    half = n_blk == nt - 1;
+                }
+                // the B rows of a half tile are the second half of the staged box: 64 rows x 128 B (K-major) or the
+                // second 64-column chunk, BK x 128 B (MN-major) — 8 KB further on either way
+                const uint32_t b_skip = half ? (BNH / 2) * 128 : 0;
+                const uint32_t idesc_t = half ? idesc_half : idesc;
                 if (p.band) {
                     int m_blk, n_blk, z[3];
                     decode(t, m_blk, n_blk, z);
@@ -426,10 +441,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     const uint64_t adesc = ptx::make_smem_desc_sw128(
                         ptx::smem_u32(smem_a + stage * Cfg::A_BYTES), a_lbo, 1024);
                     const uint64_t bdesc = ptx::make_smem_desc_sw128(
-                        ptx::smem_u32(smem_b + stage * Cfg::B_BYTES), b_lbo, 1024);
+                        ptx::smem_u32(smem_b + stage * Cfg::B_BYTES) + b_skip, b_lbo, 1024);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
-                        ptx::mma_bf16_ss_2sm(d_tmem, adesc + k * a_kstep, bdesc + k * b_kstep, idesc,
+                        ptx::mma_bf16_ss_2sm(d_tmem, adesc + k * a_kstep, bdesc + k * b_kstep, idesc_t,
                                              (it | k) != 0);
                     }
                     ptx::mma_commit_2sm_mc(&empty_bar[stage], 3);

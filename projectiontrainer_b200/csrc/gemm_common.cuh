@@ -30,6 +30,11 @@ struct GemmDev {
     // that are partly or wholly out of bounds were measured to stall the pipeline) and its epilogue skips
     // the rows / columns the previous tile already produced.
     int m_last, n_last;
+    // CTA-pair kernel, 256-wide tiles, N % 256 == 128 (the decoder's h = 1152): the last n tile runs as a
+    // 128-wide MMA on the 128 columns that are left instead of a shifted full tile that recomputes 128 columns
+    // of its neighbour (10 % of the MMA work of an N = 1152 GEMM).  Each CTA still loads a full, in-bounds
+    // 128-row B box placed so that its 64 rows are the box's second half.
+    int n_half;
     // fused GeGLU epilogues (PT_ACT_GEGLU / PT_ACT_GEGLU_BWD): second matrix, its row stride, and ff
     void* aux;
     long long ld_aux;

@@ -25,7 +25,7 @@ def _check(out, ref, tol=2e-2, name=""):
     assert err / den < tol, f"{name}: max err {err} vs scale {den}"
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 256, 256), (575, 1152, 1024),
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 256, 256), (575, 1152, 1024), (600, 384, 320), (4000, 1152, 6912),
                                    (1000, 1536, 1152), (130, 64, 768), (384, 192, 2048),
                                    (4096, 1024, 4096), (18400, 1152, 1280), (22496, 1536, 1152),
                                    (100, 40, 72), (257, 328, 8)])
@@ -60,7 +60,7 @@ def test_gemm_epilogues(cuda_dev):
 
 
 @pytest.mark.parametrize("M,N,K", [(256, 256, 256), (575, 1024, 1152), (1000, 10240, 1152),
-                                   (703, 256, 703)])
+                                   (703, 256, 703), (1000, 1152, 1536), (300, 384, 200), (22496, 1152, 1024)])
 def test_gemm_dgrad_mn_major_b(cuda_dev, M, N, K):
     """dx[M,N] = dy[M,K] @ W[K,N] with W row-major (B operand MN-major)."""
     from projectiontrainer_b200 import ops

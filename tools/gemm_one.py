@@ -10,7 +10,7 @@ ap.add_argument("M", type=int); ap.add_argument("N", type=int); ap.add_argument(
 ap.add_argument("--bmn", action="store_true"); ap.add_argument("--f32", action="store_true")
 ap.add_argument("--res", action="store_true"); ap.add_argument("--bias", action="store_true")
 ap.add_argument("--act", type=int, default=0); ap.add_argument("--impl", type=int, default=0)
-ap.add_argument("--iters", type=int, default=10); ap.add_argument("--cublas", type=int, default=1)
+ap.add_argument("--bn", type=int, default=0); ap.add_argument("--iters", type=int, default=10); ap.add_argument("--cublas", type=int, default=1)
 a = ap.parse_args()
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
@@ -23,7 +23,7 @@ res = out if a.res else None
 ops.set_gemm_impl(a.impl)
 def run():
     ops.gemm_raw(M=M, N=N, K=K, A=x, lda=K, B=w, ldb=w.stride(0), b_mn=a.bmn, Cout=out, ldc=N, bias=bias,
-                 residual=res, ldr=N, act=a.act)
+                 residual=res, ldr=N, act=a.act, bn_hint=a.bn)
 for _ in range(3): run()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -31,7 +31,7 @@ e0.record()
 for _ in range(a.iters): run()
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / a.iters
-print(f"ours impl={a.impl} {M}x{N}x{K} bmn={a.bmn}: {ms*1e3:.1f} us  {2.0*M*N*K/ms/1e9:.1f} TF/s", flush=True)
+print(f"ours impl={a.impl} bn_hint={a.bn} {M}x{N}x{K} bmn={a.bmn}: {ms*1e3:.1f} us  {2.0*M*N*K/ms/1e9:.1f} TF/s", flush=True)
 if a.cublas:
     wt = w if a.bmn else w.t()
     o2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
