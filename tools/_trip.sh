@@ -1,8 +1,9 @@
 #!/bin/bash
-# trip 66: half-width last n tile: full GPU suite + step A/B
-(timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -n 2)
-for r in a b; do
-PT_GEMM_HALF_TILE=0 timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_ht0$r.json 2> gpurun_out/s29_bench_ht0.err
-timeout 240 python bench.py --no-cpu-baseline > gpurun_out/s29_bench_ht1$r.json 2> gpurun_out/s29_bench_ht1.err
-done
-for f in ht0a ht1a ht0b ht1b; do echo $f; grep -o '"ms_per_step": [0-9.]*' gpurun_out/s29_bench_$f.json | head -n 1; grep -o '"clocks": {[^}]*}' gpurun_out/s29_bench_$f.json; grep -o '"last_loss": [0-9.]*' gpurun_out/s29_bench_$f.json; done
+# trip 67: final tree: smoke, bench line (with CPU baseline), launch list of one step
+timeout 120 python -c "import __graft_entry__ as g; g.smoke(); print('SMOKE OK')" > gpurun_out/s29g_smoke.log 2>&1
+timeout 300 python bench.py > gpurun_out/s29g_bench.json 2> gpurun_out/s29g_bench.err
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/s29g_bench20.json 2> gpurun_out/s29g_bench20.err
+timeout 200 python bench.py --profile --steps 1 > gpurun_out/s29g_profile_plain.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/s29g_launches.csv \
+   python bench.py --profile --steps 1 > gpurun_out/s29g_profile_ncu.log 2>&1
+tail -n 2 gpurun_out/s29g_smoke.log; cut -c1-230 gpurun_out/s29g_bench.json; cut -c1-230 gpurun_out/s29g_bench20.json; tail -n 1 gpurun_out/s29g_profile_plain.log
