@@ -25,6 +25,28 @@ sys.path.insert(0, str(ROOT))
 # NCCL_DEBUG is VERSION or higher) goes to stderr instead
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
+
+# ... and because NCCL 2.28 still printed the banner on stdout under torchrun on the GPU box, file descriptor 1 is
+# pointed at stderr for the whole run (C-level writes included) and the JSON line is written to the saved descriptor.
+_JSON_FD = None
+
+
+def _claim_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    sys.stdout.flush()
+    data = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.buffer.write(data); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
 METRIC = "stage1_projector_train_images_per_sec"
 UNIT = "images/s"
 B_PER_GPU, T_TOK = 32, 128
@@ -99,7 +121,7 @@ def run_reference(args):
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------- clocks
@@ -192,7 +214,7 @@ def run_ours(args):
         for _ in range(args.steps):
             step(dev_batch)
         sync()
-        print(json.dumps({"profile_run": True, "launches_per_step": (_lib.launch_count - n0) // args.steps}))
+        emit({"profile_run": True, "launches_per_step": (_lib.launch_count - n0) // args.steps})
         return
     for _ in range(max(args.warmup, 3)):
         step(dev_batch)
@@ -296,13 +318,14 @@ def run_ours(args):
         # ~10-20 s of CPU work: one untimed warm-up image (thread pool, page faults), then up to 8 timed ones
         cb, *_ = cpu_step_sample(20.0, 8, 1, args.tokens)
         line["cpu_baseline"] = cb
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = parse()
+    _claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
