@@ -246,15 +246,21 @@ __device__ __forceinline__ void epi_chunk_sbwd_pre(const uint32_t (&v)[32], uint
     const int ch = lane & 7, c = ch * 4, rsub = lane >> 3;
     const bool col_ok = c < o.cols_q;
     const uint32_t sp = stg + rsub * 128;
+    const uint64_t al2 = f2_pack(o.alpha, o.alpha), one2 = f2_pack(1.f, 1.f);
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
         const int r = it * 4 + rsub;
         const float4 a = ptx::lds128(sp + it * 512 + ((ch ^ (r & 7)) << 4));
         if (col_ok && r >= o.row_lo && r < o.rows_valid) {
+            // (alpha p) (dP - delta) on the packed-f32 pipe, two columns per instruction; p == 0 still selects 0
             const float p0 = bf16_lo(pq[it].x), p1 = bf16_hi(pq[it].x), p2 = bf16_lo(pq[it].y), p3 = bf16_hi(pq[it].y);
+            const uint64_t nd = f2_pack(-dl[it], -dl[it]);
+            float r0, r1, r2, r3;
+            f2_unpack(f2_mul(f2_mul(al2, f2_pack(p0, p1)), f2_fma(f2_pack(a.x, a.y), one2, nd)), r0, r1);
+            f2_unpack(f2_mul(f2_mul(al2, f2_pack(p2, p3)), f2_fma(f2_pack(a.z, a.w), one2, nd)), r2, r3);
             uint2 w;
-            w.x = pack_bf16(p0 != 0.f ? o.alpha * p0 * (a.x - dl[it]) : 0.f, p1 != 0.f ? o.alpha * p1 * (a.y - dl[it]) : 0.f);
-            w.y = pack_bf16(p2 != 0.f ? o.alpha * p2 * (a.z - dl[it]) : 0.f, p3 != 0.f ? o.alpha * p3 * (a.w - dl[it]) : 0.f);
+            w.x = pack_bf16(p0 != 0.f ? r0 : 0.f, p1 != 0.f ? r1 : 0.f);
+            w.y = pack_bf16(p2 != 0.f ? r2 : 0.f, p3 != 0.f ? r3 : 0.f);
             *reinterpret_cast<uint2*>(o.C + r * o.c_row + c * 2) = w;
         }
     }
