@@ -204,18 +204,30 @@ int pt_softmax_fwd(const float* scores, void* P_bf16, const uint8_t* keyvalid, i
 int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long rows, int Sk, int ld,
                    float scale, int Sq, int causal, int window, void* stream);
 
-/* Fused causal / sliding-window GQA attention forward of the Gemma3 decoder, head_dim 256
+/* Fused causal / sliding-window GQA attention forward of the Gemma3 decoder, head_dim 256 or 128, flash style
  * (HF:models/gemma3/modeling_gemma3.py:278-300,370-384; mask HF:masking_utils.py:74-99,148-159):
- *   P[b, head, q, k] = softmax_k(mask(q_rot . k_rot * scale))   (bf16, [B*hq, S, ldp], written only inside the
- *                      causal / window band — the caller zero-fills P once; masked keys inside the band get 0)
- *   O[b*S + q, head*256 ..] = sum_k P V                          (bf16, [B*S, hq*256])
- * q_rot [B*S, hq*256], k_rot [B*S, hkv*256] are the outputs of pt_qknorm_rope_fwd; V is read in place from the
- * fused activation qkv [B*S, (hq+2hkv)*256].  kvbits: optional key-padding bit masks from pt_pack_keyvalid
+ *   O[b*S + q, head*hd ..] = sum_k softmax_k(mask(q_rot . k_rot * scale)) V     (bf16, [B*S, hq*hd])
+ *   lse[(b*hq + head)*S + q] = log2(sum_k 2^(score * scale * log2 e))           (f32; +inf for a row without a
+ *                              visible key; NULL = not wanted: inference)
+ * q_rot [B*S, hq*hd], k_rot [B*S, hkv*hd] are the outputs of pt_qknorm_rope_fwd; V is read in place from the
+ * fused activation qkv [B*S, (hq+2hkv)*hd].  kvbits: optional key-padding bit masks from pt_pack_keyvalid
  * (NULL = every key valid).  window 0 = causal only.  hq/hkv a power of two.
- * Scores and un-normalised probabilities never reach HBM (two passes over the key tiles in TMEM). */
-int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const void* kvbits, void* P_bf16,
-                      void* O_bf16, int B, int S, int hq, int hkv, int hd, int window, float scale, int ldp,
-                      void* stream);
+ * One pass over the key tiles with an online softmax; scores and probabilities never reach HBM. */
+int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const void* kvbits, float* lse,
+                      void* O_bf16, int B, int S, int hq, int hkv, int hd, int window, float scale, void* stream);
+/* Fused backward of the same attention (autograd through HF:models/gemma3/modeling_gemma3.py:370-384, invoked at
+ * ref:Stage1/projector_trainer.py:236-237), key/value stationary, P recomputed from q_rot, k_rot and lse:
+ *   dV[b*S + k, kvh*hd ..] = sum_{heads of kvh} P^T dO          (bf16, row stride ld_dv elements)
+ *   dK[b*S + k, kvh*hd ..] = sum_{heads of kvh} dS^T q_rot      (bf16, row stride ld_dk; gradient w.r.t. k_rot)
+ *   dS[(b*hq + head), q, k] = scale * P * (dO V^T - delta)      (bf16, [B*hq, S, lds]; written only inside the
+ *                             (query block, key tile) pairs of the causal / window band — the caller zero-fills
+ *                             the buffer once per window value; masked positions inside get exact zeros)
+ * delta [B*hq, S] = rowsum(dO * O) (pt_attn_delta).  dQ = dS k_rot is left to a band-limited pt_gemm_bf16
+ * (PT_BAND_K_BY_QUERY): the one contraction that is stationary in the other operand. */
+int pt_attn_gemma_bwd(const void* q_rot, const void* k_rot, const void* qkv, const void* dO_bf16, const void* kvbits,
+                      const float* lse, const float* delta, void* dS_bf16, void* dK_bf16, long long ld_dk,
+                      void* dV_bf16, long long ld_dv, int B, int S, int hq, int hkv, int hd, int window, float scale,
+                      int lds, void* stream);
 /* keyvalid u8 [B,S] (0 = padded key, ref:Stage1/projector_trainer.py:205-208) -> u64 [B, ceil(S/64)] bit masks
  * (bit i of word w = key 64 w + i; keys >= S are 0). */
 int pt_pack_keyvalid(const uint8_t* keyvalid, void* kvbits, int B, int S, void* stream);

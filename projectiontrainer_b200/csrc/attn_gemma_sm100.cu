@@ -1,28 +1,26 @@
 // Fused causal / sliding-window GQA attention forward for the Gemma3 decoder (head_dim 256; also instantiated
-// for head_dim 128, the Qwen3 geometry):
-//     P = softmax(mask(Q K^T * scale)),  O = P V       HF:models/gemma3/modeling_gemma3.py:278-300,370-384
-// Replaces (band GEMM -> f32 scores in HBM -> softmax kernel -> bf16 P -> band GEMM): the scores never leave
-// TMEM.  The normalised probabilities P ARE written (bf16), because the input-gradient backward reads them
-// (dV = P^T dO, dS = P (dP - delta)); to have them normalised at the time they are produced the kernel makes
-// two passes over the key tiles of a query block:
-//     pass 0:  S_j = Q K_j^T (tcgen05.mma, TMEM)  ->  running row max m and row sum l (online, registers)
-//     pass 1:  S_j again  ->  p = exp2((s - m) c) / l  -> bf16 -> global P  and  swizzled smem -> O += P_j V_j
-// which costs one extra Q K^T (cheap: K = 256) and needs no O rescaling at all.
+// for head_dim 128, the Qwen3 geometry), flash style:
+//     O = softmax(mask(Q K^T * scale)) V,   LSE = log2-domain log-sum-exp of every score row
+//     HF:models/gemma3/modeling_gemma3.py:278-300,370-384
+// One pass over the key tiles of a query block with an online softmax: S_j = Q K_j^T lands in TMEM, the softmax
+// warps turn it into un-normalised probabilities p = exp2((s - m) c) against the running row max m (the O
+// accumulator in TMEM is rescaled only when some row's max grew by more than 2^8: a warp-uniform, rare event),
+// O += P_j V_j, and the epilogue divides by the row sum.  Neither scores nor probabilities reach HBM: the
+// backward (attn_gemma_bwd_sm100.cu) recomputes P from Q, K and the saved LSE.
 //
 // Work item = (batch, kv head, block of 128 stacked query rows): the G = hq/hkv query heads that share a kv
 // head are stacked with their positions, row r <-> (position s0 + r / G, head kvh*G + r % G), by a 5-D TMA box
 // over the rotated queries [B*S, hq*hd], so one K/V tile serves all G heads.  Only key tiles inside the causal
 // (and sliding-window) band of the block are visited.  Roles: warps 0-3 softmax (thread = row), warp 4 MMA
 // issuer, warp 5 TMA producer; every hand-off is an mbarrier (TMA tx, tcgen05.commit or 128 thread arrivals).
-// TMEM: S0 [0,64) S1 [64,128) O [128,384).
+// TMEM: S0 [0,64) S1 [64,128) O [128,128+hd).
 #include "pt_common.cuh"
 #include "sm100_ptx.cuh"
 #include "gemm_common.cuh"
+#include "attn_gemma_maps.cuh"
 
 namespace pt {
 
-constexpr int kGqRows = 128;
-constexpr int kGkTile = 64;
 constexpr int kGthreads = 192;
 constexpr int kGpBytes = kGqRows * kGkTile * 2;     // 16 KB
 // head_dim 256: Q 64 KB + ring of 4 x 32 KB + P 16 KB;  head_dim 128 (Qwen3): 32 KB + 4 x 16 KB + 16 KB
@@ -31,11 +29,10 @@ constexpr int gemma_smem(int hd) { return kGqRows * hd * 2 + 4 * kGkTile * hd * 
 struct AttnGemmaDev {
     int B, S, hq, hkv, G, window;     // window 0 = causal only
     int pos_per_blk, nqb;             // 128 / G query positions per block; blocks per (batch, kv head)
-    int ldp;                          // row stride of P (elements)
     float scale_log2e;
     const unsigned long long* kvbits; // [B][ceil(S/64)] key-valid bit masks (bit i = key 64 w + i), or null
     int kvwords;
-    __nv_bfloat16* P;                 // [B*hq, S, ldp]
+    float* lse;                       // [B*hq, S] log2-domain log-sum-exp (m c + log2 l; +inf: no visible key), or null
     __nv_bfloat16* O;                 // [B*S, hq*hd]
 };
 
@@ -76,7 +73,7 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint8_t* sQ = smem;
-    uint8_t* sKV = sQ + kQB;                // ring of 4 K-or-V tiles (pass 0: 4 K tiles in flight)
+    uint8_t* sKV = sQ + kQB;                // ring of 4 tiles: K_j, V_j, K_j+1, V_j+1
     uint8_t* sP = sKV + 4 * kKVB;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kGpBytes);
     uint64_t* q_full = bars;            // TMA -> MMA
@@ -133,8 +130,7 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                                          (jlo + j) * kGkTile, kvh, b, 0);
                     ++lc;
                 };
-                for (int j = 0; j < nt; ++j) load_tile(&tmK, j);                       // pass 0
-                for (int j = 0; j < nt; ++j) { load_tile(&tmK, j); load_tile(&tmV, j); }   // pass 1
+                for (int j = 0; j < nt; ++j) { load_tile(&tmK, j); load_tile(&tmV, j); }
             }
         }
     } else if (warp == 4) {
@@ -163,16 +159,14 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 int b, kvh, qb, jlo, nt;
                 gemma_item(p, item, b, kvh, qb, jlo, nt);
                 ptx::mbar_wait(q_full, n_item & 1);
-                for (int j = 0; j < nt; ++j) issue_S(base + j);           // pass 0: statistics
-                const uint32_t b1 = base + nt;                            // pass 1: K_j at b1 + 2j, V_j at b1 + 2j + 1
-                issue_S(b1);
+                issue_S(base);                                            // K_j at base + 2j, V_j at base + 2j + 1
                 if (nt == 1) ptx::mma_commit(q_empty);
                 for (int j = 0; j < nt; ++j) {
                     if (j + 1 < nt) {
-                        issue_S(b1 + 2 * (j + 1));
+                        issue_S(base + 2 * (j + 1));
                         if (j + 2 == nt) ptx::mma_commit(q_empty);        // last S of the item issued: Q is free
                     }
-                    const uint32_t lv = b1 + 2 * j + 1;
+                    const uint32_t lv = base + 2 * j + 1;
                     const int sv = lv & 3;
                     ptx::mbar_wait(p_full, pc & 1);
                     ptx::mbar_wait(&ld_full[sv], (lv >> 2) & 1);
@@ -188,7 +182,7 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                     ptx::mma_commit(&ld_empty[sv]);
                     ++pc;
                 }
-                base += 3 * nt;
+                base += 2 * nt;
             }
         }
     } else {
@@ -196,6 +190,7 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const int row = threadIdx.x;                               // TMEM lane
         const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
         const uint32_t p_row = ptx::smem_u32(sP) + row * 128;
+        const float c2 = p.scale_log2e;
         uint32_t sc = 0, pc = 0;
         for (int item = blockIdx.x; item < items; item += gridDim.x) {
             int b, kvh, qb, jlo, nt;
@@ -207,100 +202,97 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             const int k_lo = p.window > 0 ? max(0, s - p.window + 1) : 0;
             const unsigned long long* kvw = p.kvbits ? p.kvbits + static_cast<long long>(b) * p.kvwords : nullptr;
 
-            // visibility mask of the 64 keys of tile j for this row
-            // (the key-padding word is fetched by the caller BEFORE it waits for the S tile: an L2-latency load
-            //  right in front of its first use was the top stall of this kernel)
-            auto tile_mask = [&](int j, unsigned long long m) -> unsigned long long {
-                const int k0 = (jlo + j) * kGkTile;
-                const int hi = k_hi - k0, lo = k_lo - k0;            // visible local indices: lo <= i <= hi
-                if (hi < 0 || lo > 63) return 0ull;
-                if (hi < 63) m &= (2ull << hi) - 1ull;
-                if (lo > 0) m &= ~0ull << lo;
-                return m;
-            };
-            auto load_S = [&](uint32_t (&v)[2][32]) {
-                const int sb = sc & 1;
-                ptx::mbar_wait(&s_full[sb], (sc >> 1) & 1);
-                ptx::tc_fence_after();
-                ptx::tmem_ld_32x32(tS[sb] + lane_off, v[0]);
-                ptx::tmem_ld_32x32(tS[sb] + lane_off + 32, v[1]);
-                ptx::tmem_ld_wait();
-                ptx::tc_fence_before();
-                ptx::mbar_arrive(&s_free[sb]);
-                ++sc;
-            };
-
-            // ---- pass 0: row max and row sum over the band
             float m_run = -INFINITY, l_run = 0.f;
             for (int j = 0; j < nt; ++j) {
-                const unsigned long long kw = kvw ? __ldg(kvw + jlo + j) : ~0ull;
+                // the key-padding word is fetched BEFORE the wait for the S tile (an L2-latency load right in
+                // front of its first use was the top stall of the first version of this kernel)
+                const unsigned long long mask =
+                    gemma_tile_mask(kvw ? __ldg(kvw + jlo + j) : ~0ull, (jlo + j) * kGkTile, k_lo, k_hi);
                 uint32_t v[2][32];
-                load_S(v);
-                const unsigned long long mask = tile_mask(j, kw);
-                if (mask == 0ull) continue;
-                float mxs[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+                {
+                    const int sb = sc & 1;
+                    ptx::mbar_wait(&s_full[sb], (sc >> 1) & 1);
+                    ptx::tc_fence_after();
+                    ptx::tmem_ld_32x32(tS[sb] + lane_off, v[0]);
+                    ptx::tmem_ld_32x32(tS[sb] + lane_off + 32, v[1]);
+                    ptx::tmem_ld_wait();
+                    ptx::tc_fence_before();
+                    ptx::mbar_arrive(&s_free[sb]);
+                    ++sc;
+                }
+                // tiles strictly inside the band are fully visible for every row of the warp: no per-element select
+                if (!__all_sync(0xffffffffu, mask == ~0ull)) {
+#pragma unroll
+                    for (int c = 0; c < 2; ++c)
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (!((mask >> (c * 32 + i)) & 1ull)) v[c][i] = __float_as_uint(-INFINITY);
+                }
+                float mxs[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) mxs[i] = -INFINITY;
 #pragma unroll
                 for (int c = 0; c < 2; ++c)
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        if (!((mask >> (c * 32 + i)) & 1ull)) v[c][i] = __float_as_uint(-INFINITY);
-                        mxs[i & 3] = fmaxf(mxs[i & 3], __uint_as_float(v[c][i]));
+                    for (int i = 0; i < 32; ++i) mxs[i & 7] = fmaxf(mxs[i & 7], __uint_as_float(v[c][i]));
+                const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                                       fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
+                bool pv_waited = false;
+                if (j == 0) {
+                    m_run = mx;                                       // PV_0 overwrites O: nothing to rescale
+                } else {
+                    const float m_new = fmaxf(m_run, mx);
+                    // lazy rescale: only when some row's max grew by more than 2^8 (m_run = -inf: first visible key)
+                    const bool grow = m_new > m_run && (m_new - m_run) * c2 > 8.f;
+                    if (__any_sync(0xffffffffu, grow)) {
+                        const float alpha = m_new == -INFINITY ? 1.f : ptx::exp2_fast((m_run - m_new) * c2);
+                        ptx::mbar_wait(pv_done, pc & 1); ++pc;        // O += P_{j-1} V_{j-1} has retired
+                        pv_waited = true;
+                        ptx::tc_fence_after();
+#pragma unroll 1
+                        for (int c = 0; c < HD / 32; ++c) {
+                            uint32_t o[32];
+                            ptx::tmem_ld_32x32(tO + lane_off + c * 32, o);
+                            ptx::tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                            ptx::tmem_st_32x32(tO + lane_off + c * 32, o);
+                        }
+                        ptx::tmem_st_wait();
+                        l_run *= alpha;
+                        m_run = m_new;
                     }
-                const float m_new = fmaxf(m_run, fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])));
-                const float mb = m_new * p.scale_log2e;
+                }
+                // p = exp2(s c - m c): at most 2^8 under the lazy max; masked scores are -inf -> exactly 0
+                const float mb = m_run == -INFINITY ? 0.f : m_run * c2;
                 float ls[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int c = 0; c < 2; ++c)
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        ls[i & 3] += ptx::exp2_fast(fmaf(__uint_as_float(v[c][i]), p.scale_log2e, -mb));
-                const float alpha = (m_run == -INFINITY) ? 0.f : ptx::exp2_fast((m_run - m_new) * p.scale_log2e);
-                l_run = l_run * alpha + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
-                m_run = m_new;
-            }
-            const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-            const float mb = (m_run == -INFINITY ? 0.f : m_run) * p.scale_log2e;
-
-            // ---- pass 1: normalised probabilities -> global P and smem, O += P V
-            __nv_bfloat16* prow_g = p.P + ((static_cast<long long>(b) * p.hq + head) * p.S + (live ? s : 0)) * p.ldp;
-            for (int j = 0; j < nt; ++j) {
-                const unsigned long long kw = kvw ? __ldg(kvw + jlo + j) : ~0ull;
-                uint32_t v[2][32];
-                load_S(v);
-                const unsigned long long mask = tile_mask(j, kw);
                 uint32_t pk[32];
 #pragma unroll
                 for (int c = 0; c < 2; ++c)
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const int i0 = c * 32 + 2 * i;
-                        float e0 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i]), p.scale_log2e, -mb)) * inv;
-                        float e1 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i + 1]), p.scale_log2e, -mb)) * inv;
-                        if (!((mask >> i0) & 1ull)) e0 = 0.f;
-                        if (!((mask >> (i0 + 1)) & 1ull)) e1 = 0.f;
+                        const float e0 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i]), c2, -mb));
+                        const float e1 = ptx::exp2_fast(fmaf(__uint_as_float(v[c][2 * i + 1]), c2, -mb));
+                        ls[i & 3] += e0 + e1;
                         pk[c * 16 + i] = pack_bf16(e0, e1);
                     }
+                l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
                 // the single P buffer is free once the previous tile's PV has retired
-                if (j > 0) { ptx::mbar_wait(pv_done, pc & 1); ++pc; }
+                if (j > 0 && !pv_waited) { ptx::mbar_wait(pv_done, pc & 1); ++pc; }
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
                     ptx::sts128(p_row + ((q ^ (row & 7)) << 4), pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(p_full);
-                // the copy of P for the backward goes out after the hand-off (off the MMA's critical path)
-                if (live) {
-                    const int k0 = (jlo + j) * kGkTile;
-#pragma unroll
-                    for (int q = 0; q < 8; ++q)
-                        if (k0 + q * 8 < p.ldp)
-                            *reinterpret_cast<uint4*>(prow_g + k0 + q * 8) =
-                                make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-                }
             }
-            // ---- epilogue: O -> bf16 -> global
+            // ---- epilogue: O / l -> bf16 -> global, LSE
             ptx::mbar_wait(pv_done, pc & 1); ++pc;
             ptx::tc_fence_after();
+            const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+            if (live && p.lse)
+                p.lse[(static_cast<long long>(b) * p.hq + head) * p.S + s] =
+                    l_run > 0.f ? fmaf(m_run, c2, log2f(l_run)) : INFINITY;
             __nv_bfloat16* op = p.O + (static_cast<long long>(b) * p.S + (live ? s : 0)) * (p.hq * HD) + head * HD;
 #pragma unroll 1
             for (int c = 0; c < HD / 32; ++c) {
@@ -311,10 +303,10 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         uint4 u;
-                        u.x = pack_bf16(__uint_as_float(o[8 * q]), __uint_as_float(o[8 * q + 1]));
-                        u.y = pack_bf16(__uint_as_float(o[8 * q + 2]), __uint_as_float(o[8 * q + 3]));
-                        u.z = pack_bf16(__uint_as_float(o[8 * q + 4]), __uint_as_float(o[8 * q + 5]));
-                        u.w = pack_bf16(__uint_as_float(o[8 * q + 6]), __uint_as_float(o[8 * q + 7]));
+                        u.x = pack_bf16(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
+                        u.y = pack_bf16(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
+                        u.z = pack_bf16(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
+                        u.w = pack_bf16(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
                         *reinterpret_cast<uint4*>(op + c * 32 + q * 8) = u;
                     }
                 }
@@ -344,47 +336,26 @@ extern "C" int pt_pack_keyvalid(const uint8_t* keyvalid, void* kvbits, int B, in
 }
 
 extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const void* kvbits,
-                                 void* P_bf16, void* O_bf16, int B, int S, int hq, int hkv, int hd,
-                                 int window, float scale, int ldp, void* stream) {
-    PT_REQUIRE(q_rot && k_rot && qkv && P_bf16 && O_bf16, "pt_attn_gemma_fwd: null pointer");
+                                 float* lse, void* O_bf16, int B, int S, int hq, int hkv, int hd,
+                                 int window, float scale, void* stream) {
+    PT_REQUIRE(q_rot && k_rot && qkv && O_bf16, "pt_attn_gemma_fwd: null pointer");
     PT_REQUIRE(hd == 256 || hd == 128, "pt_attn_gemma_fwd: head_dim must be 256 or 128 (got %d)", hd);
     PT_REQUIRE(B > 0 && S > 0 && hq > 0 && hkv > 0 && hq % hkv == 0 && window >= 0, "pt_attn_gemma_fwd: bad shape");
     const int G = hq / hkv;
     PT_REQUIRE(G <= 128 && (G & (G - 1)) == 0, "pt_attn_gemma_fwd: hq / hkv must be a power of two <= 128 (got %d)", G);
-    PT_REQUIRE(ldp >= S && ldp % 8 == 0, "pt_attn_gemma_fwd: ldp must be >= S and a multiple of 8");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int QKV = (hq + 2 * hkv) * hd;
     const int pos = kGqRows / G;
     CUtensorMap tq, tk, tv;
-    {   // rotated queries [B*S, hq*hd] viewed as (hd, G, S, hkv, B); box = 64 columns x G heads x 128/G positions
-        const unsigned long long dims[5] = {(unsigned long long)hd, (unsigned long long)G, (unsigned long long)S,
-                                            (unsigned long long)hkv, (unsigned long long)B};
-        const unsigned long long str[4] = {(unsigned long long)hd * 2, (unsigned long long)hq * hd * 2,
-                                           (unsigned long long)G * hd * 2, (unsigned long long)S * hq * hd * 2};
-        const unsigned int box[5] = {64, (unsigned)G, (unsigned)pos, 1, 1};
-        int rc = encode_tiled_bf16_5d(&tq, q_rot, dims, str, box, "attn_gemma Q");
-        if (rc != PT_OK) return rc;
-    }
-    {   // rotated keys [B*S, hkv*hd] viewed as (hd, S, hkv, B, 1)
-        const unsigned long long dims[5] = {(unsigned long long)hd, (unsigned long long)S, (unsigned long long)hkv,
-                                            (unsigned long long)B, 1};
-        const unsigned long long str[4] = {(unsigned long long)hkv * hd * 2, (unsigned long long)hd * 2,
-                                           (unsigned long long)S * hkv * hd * 2, (unsigned long long)S * hkv * hd * 2 * B};
-        const unsigned int box[5] = {64, kGkTile, 1, 1, 1};
-        int rc = encode_tiled_bf16_5d(&tk, k_rot, dims, str, box, "attn_gemma K");
-        if (rc != PT_OK) return rc;
-    }
-    {   // values in place inside the fused qkv activation [B*S, QKV] at column (hq + hkv) * hd
-        const unsigned long long dims[5] = {(unsigned long long)hd, (unsigned long long)S, (unsigned long long)hkv,
-                                            (unsigned long long)B, 1};
-        const unsigned long long str[4] = {(unsigned long long)QKV * 2, (unsigned long long)hd * 2,
-                                           (unsigned long long)S * QKV * 2, (unsigned long long)S * QKV * 2 * B};
-        const unsigned int box[5] = {64, kGkTile, 1, 1, 1};
-        const __nv_bfloat16* vbase = static_cast<const __nv_bfloat16*>(qkv) + static_cast<long long>(hq + hkv) * hd;
-        int rc = encode_tiled_bf16_5d(&tv, vbase, dims, str, box, "attn_gemma V");
-        if (rc != PT_OK) return rc;
-    }
+    int rc = gemma_stacked_map(&tq, q_rot, B, S, hq, hkv, hd, "attn_gemma Q");
+    if (rc != PT_OK) return rc;
+    rc = gemma_kv_map(&tk, k_rot, static_cast<long long>(hkv) * hd, B, S, hkv, hd, "attn_gemma K");
+    if (rc != PT_OK) return rc;
+    // values in place inside the fused qkv activation [B*S, QKV] at column (hq + hkv) * hd
+    rc = gemma_kv_map(&tv, static_cast<const __nv_bfloat16*>(qkv) + static_cast<long long>(hq + hkv) * hd, QKV, B, S,
+                      hkv, hd, "attn_gemma V");
+    if (rc != PT_OK) return rc;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(attn_gemma_fwd_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -399,11 +370,10 @@ extern "C" int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const voi
     p.B = B; p.S = S; p.hq = hq; p.hkv = hkv; p.G = G; p.window = window;
     p.pos_per_blk = pos;
     p.nqb = (S + pos - 1) / pos;
-    p.ldp = ldp;
     p.scale_log2e = scale * 1.4426950408889634f;
     p.kvwords = (S + 63) / 64;
     p.kvbits = static_cast<const unsigned long long*>(kvbits);
-    p.P = static_cast<__nv_bfloat16*>(P_bf16);
+    p.lse = lse;
     p.O = static_cast<__nv_bfloat16*>(O_bf16);
     const long long items = static_cast<long long>(B) * hkv * p.nqb;
     PT_REQUIRE(items < (1ll << 31), "pt_attn_gemma_fwd: too many work items");

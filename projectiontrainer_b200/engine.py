@@ -358,8 +358,10 @@ class Stage1Engine:
             qkv = self.buf(tag + "qkv", (M, QKV), BF16)
             q_post = self.buf(tag + "q", (M, hq * hd), BF16)
             k_post = self.buf(tag + "k", (M, hkv * hd), BF16)
-            # fused attention writes P only inside the causal / window band: its buffers start zero-filled
-            P = self.buf(tag + ("Pz" if self.fuse_attn_fwd else "P"), (B * hq, S, ld), BF16, zero=self.fuse_attn_fwd)
+            # fused attention keeps only the log-sum-exp of every score row (the backward recomputes P);
+            # the GEMM + softmax + GEMM fall-back materialises the probabilities
+            P = None if self.fuse_attn_fwd else self.buf(tag + "P", (B * hq, S, ld), BF16)
+            lse = self.buf(tag + "lse", (B * hq, S), F32) if self.fuse_attn_fwd and save else None
             attn_o = self.buf(tag + "ao", (M, hq * hd), BF16)      # kept: delta = rowsum(dO * O) in the backward
             y_attn = self.buf(tag + "ya", (M, h), BF16) if c.sandwich_norm else None
             x1 = self.buf(tag + "x1", (M, h), F32)
@@ -374,7 +376,7 @@ class Stage1Engine:
                 cache["v"][li][:, :S].copy_(qkv.view(B, S, QKV)[:, :, (hq + hkv) * hd:])
             win = 0 if full else c.window
             if self.fuse_attn_fwd:
-                ops.attn_gemma_fwd(q_post, k_post, qkv, kvbits, P, attn_o, B, S, hq, hkv, hd, win, scale, ld)
+                ops.attn_gemma_fwd(q_post, k_post, qkv, kvbits, lse, attn_o, B, S, hq, hkv, hd, win, scale)
             else:
                 self._scores_like(q_post, 0, hq * hd, (hd, G * hd, S * hq * hd), k_post, 0, hkv * hd,
                                   (0, hd, S * hkv * hd), sc, B, S, scale, window=win)
@@ -406,8 +408,8 @@ class Stage1Engine:
                 if not last:
                     ops.rmsnorm_fwd(x2, Lm.layers[li + 1]["in_norm"], a, c.eps)
             if save:
-                sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, ao=attn_o, ya=y_attn, x1=x1, gu=gu,
-                               ym=y_mlp, full=full))
+                sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, lse=lse, kvbits=kvbits, ao=attn_o, ya=y_attn,
+                               x1=x1, gu=gu, ym=y_mlp, full=full))
             x = x2
         return x, sv
 
@@ -470,8 +472,15 @@ class Stage1Engine:
         d_act = self.buf("b_dact", (M, ff), BF16)
         d_gu = self.buf("b_dgu", (M, 2 * ff), BF16)
         d_o = self.buf("b_do", (M, hq * hd), BF16)
-        dP = None if self.fuse_softmax_bwd else self.buf("l_scores", (B * hq, S, ld), F32)
-        dS = self.buf("b_dS", (B * hq, S, ld), BF16)
+        fused_attn = self.fuse_attn_fwd           # flash-style backward: P recomputed from the saved log-sum-exp
+        dP = None if self.fuse_softmax_bwd or fused_attn else self.buf("l_scores", (B * hq, S, ld), F32)
+        if fused_attn:
+            # the fused backward writes dS only inside the (query block, key tile) pairs of a layer's band and the
+            # dQ GEMM reads whole K blocks: one zero-filled buffer per band shape (full-causal / sliding layers)
+            dS_by_band = {f: self.buf("b_dS_full" if f else "b_dS_slide", (B * hq, S, ld), BF16, zero=True)
+                          for f in {a["full"] for a in s["layers"]}}
+        else:
+            dS = self.buf("b_dS", (B * hq, S, ld), BF16)
         delta = self.buf("b_delta", (B * hq * S,), F32)
         dq = self.buf("b_dq", (M, hq * hd), BF16)
         dk = self.buf("b_dk", (M, hkv * hd), BF16)
@@ -509,8 +518,28 @@ class Stage1Engine:
                 else:
                     ops.cast_f32_bf16(dx, d_y)
             ops.linear_dgrad(d_y, L["o_w"], out=d_o)
-            # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
             win = 0 if a["full"] else c.window
+            if fused_attn:
+                # delta = rowsum(dO * O); dK, dV and dS in one key/value-stationary kernel; dQ = dS K as a band GEMM
+                dS = dS_by_band[a["full"]]
+                ops.attn_delta(d_o, a["ao"], delta, S, hq, hd)
+                ops.attn_gemma_bwd(a["q"], a["k"], a["qkv"], d_o, a["kvbits"], a["lse"], delta, dS, dk,
+                                   d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, win, scale, ld)
+                ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
+                             ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
+                             b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY,
+                             band_window=win)
+                ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
+                                    hkv, hd, c.eps)
+                ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)
+                if pair and li > 0:     # input-norm backward + the previous layer's post-ffn norm backward
+                    prev = s["layers"][li - 1]
+                    ops.rmsnorm_bwd_pair(d_y, a["x_in"], L["in_norm"], dx, prev["ym"],
+                                         Lm.layers[li - 1]["post_ffn_norm"], d_y, c.eps)
+                else:
+                    ops.rmsnorm_bwd(d_y, a["x_in"], L["in_norm"], dx, c.eps, add=dx)
+                continue
+            # dP[b, head] = dO[b,:,head,:] V[b,:,kvh,:]^T
             if side:        # dV needs only P and dO: it runs beside delta + the dS GEMM
                 ev_do.record(main)
                 sv.wait_event(ev_do)

@@ -265,12 +265,23 @@ def pack_keyvalid(keyvalid, kvbits):
     _lib.call("pt_pack_keyvalid", _ptr(keyvalid), _ptr(kvbits), keyvalid.shape[0], keyvalid.shape[1], _stream())
 
 
-def attn_gemma_fwd(q_rot, k_rot, qkv, kvbits, P, O, B, S, hq, hkv, hd, window, scale, ldp):
-    """Fused causal / sliding-window GQA attention forward (hd 256): writes normalised P (band only) and O.
+def attn_gemma_fwd(q_rot, k_rot, qkv, kvbits, lse, O, B, S, hq, hkv, hd, window, scale):
+    """Fused causal / sliding-window GQA attention forward (hd 256 / 128), one pass with an online softmax:
+    writes O and (unless None) the log2-domain log-sum-exp of every score row, f32 [B*hq, S].
     kvbits: packed key-padding masks (pack_keyvalid) or None."""
-    _req_cuda(q_rot, k_rot, qkv, kvbits, P, O)
-    _lib.call("pt_attn_gemma_fwd", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(kvbits), _ptr(P),
-              _ptr(O), int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), int(ldp), _stream())
+    _req_cuda(q_rot, k_rot, qkv, kvbits, lse, O)
+    _lib.call("pt_attn_gemma_fwd", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(kvbits), _ptr(lse),
+              _ptr(O), int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), _stream())
+
+
+def attn_gemma_bwd(q_rot, k_rot, qkv, dO, kvbits, lse, delta, dS, dK, dV, B, S, hq, hkv, hd, window, scale, lds):
+    """Fused backward of attn_gemma_fwd: dK (gradient w.r.t. k_rot), dV and dS (bf16 [B*hq, S, lds], band only:
+    zero-fill once).  dK / dV may be column slices of wider row-major buffers (their row stride is passed on)."""
+    _req_cuda(q_rot, k_rot, qkv, dO, kvbits, lse, delta, dS, dK, dV)
+    assert dK.stride(1) == 1 and dV.stride(1) == 1
+    _lib.call("pt_attn_gemma_bwd", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(dO), _ptr(kvbits), _ptr(lse),
+              _ptr(delta), _ptr(dS), _ptr(dK), C.c_longlong(dK.stride(0)), _ptr(dV), C.c_longlong(dV.stride(0)),
+              int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), int(lds), _stream())
 
 
 def attn_delta(dO, O, delta, S, hq, hd):
