@@ -50,7 +50,15 @@ struct AttnGemmaBwdDev {
     __nv_bfloat16* dK;                // element (b*S + k, kvh*hd + d) at dK[(b*S + k) * ld_dk + kvh*hd + d]
     __nv_bfloat16* dV;
     long long ld_dk, ld_dv;
+    long long* trace;                 // tools/attn_bwd_trace.py: SM-clock timestamps of CTA 0's hand-offs, or null
+    int trace_iters;
 };
+
+// timeline probe (debug hook, null in the product path): event e of block `it` of CTA 0
+__device__ __forceinline__ void bwd_trace(const AttnGemmaBwdDev& p, uint32_t it, int e) {
+    if (p.trace != nullptr && blockIdx.x == 0 && it < static_cast<uint32_t>(p.trace_iters))
+        p.trace[it * 16 + e] = clock64();
+}
 
 // item -> (batch, kv head, key tile, first query block, number of query blocks).  Items are ordered by key tile:
 // early keys are seen by the most queries, so the heaviest items start first.
@@ -135,6 +143,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                     const int s0 = (qb0 + i) * p.pos_per_blk;
                     // dO first: its buffer is released one MMA group earlier (after dV^T) than Q's (after dK^T)
                     ptx::mbar_wait(do_empty, (it & 1) ^ 1);
+                    bwd_trace(p, it, 0);
                     if (i == 0) {
                         // every MMA of the previous item has retired (q_empty below was its last commit, and the
                         // wait on it precedes this point for it > 0 ... see the q_empty wait of the last block)
@@ -151,6 +160,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                     for (int c = 0; c < kSlabs; ++c)
                         ptx::tma_load_5d(&tmdO, do_full, sdO + c * kSlabQ, c * 64, 0, s0, kvh, b);
                     if (i != 0) ptx::mbar_wait(q_empty, (it & 1) ^ 1);
+                    bwd_trace(p, it, 1);
                     ptx::mbar_arrive_expect_tx(q_full, kQB);
 #pragma unroll
                     for (int c = 0; c < kSlabs; ++c)
@@ -195,10 +205,12 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 for (int i = 0; i < nqb; ++i, ++it) {
                     const uint32_t ph = it & 1;
                     ptx::mbar_wait(do_full, ph);
+                    bwd_trace(p, it, 2);
                     ptx::tc_fence_after();
                     issue_scores(tdP, doa, va);
                     ptx::mma_commit(dp_full);
                     ptx::mbar_wait(q_full, ph);
+                    bwd_trace(p, it, 3);
                     ptx::tc_fence_after();
                     issue_scores(tS, qa, ka);
                     ptx::mma_commit(s_full);
@@ -207,10 +219,12 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                         ptx::tc_fence_after();
                     }
                     ptx::mbar_wait(p_full, ph);
+                    bwd_trace(p, it, 4);
                     ptx::tc_fence_after();
                     issue_grad(tdV, doa, pa, i == 0);
                     ptx::mma_commit(do_empty);
                     ptx::mbar_wait(ds_full, ph);
+                    bwd_trace(p, it, 5);
                     ptx::tc_fence_after();
                     issue_grad(tdK, qa, dsa, i == 0);
                     ptx::mma_commit(q_empty);
@@ -249,6 +263,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 {
                     uint32_t v[2][32];
                     ptx::mbar_wait(s_full, ph);
+                    if (row == 0) bwd_trace(p, it, 6);
                     ptx::tc_fence_after();
                     ptx::tmem_ld_32x32(tS + lane_off, v[0]);
                     ptx::tmem_ld_32x32(tS + lane_off + 32, v[1]);
@@ -272,10 +287,12 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(p_full);
+                if (row == 0) bwd_trace(p, it, 7);
 
                 // ---- dS = scale P (dP - delta) -> bf16 -> smem (B operand of dK^T += Q^T dS) and global
                 uint32_t dk[32];
                 ptx::mbar_wait(dp_full, ph);
+                if (row == 0) bwd_trace(p, it, 8);
                 ptx::tc_fence_after();
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
@@ -295,6 +312,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(ds_full);
+                if (row == 0) bwd_trace(p, it, 9);
                 if (live) {
                     __nv_bfloat16* g = p.dS + ridx * p.lds + k0;
 #pragma unroll
@@ -303,6 +321,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                             *reinterpret_cast<uint4*>(g + q * 8) = make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
                 }
             }
+            if (row == 0) bwd_trace(p, it - 1, 10);
             // ---- epilogue: thread = head-dim row (h * 128 + row) of the transposed accumulators; 64 keys each
             ptx::mbar_wait(acc_full, n_item & 1);
             ptx::tc_fence_after();
@@ -328,6 +347,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             }
             ptx::tc_fence_before();
             ptx::mbar_arrive(acc_free);
+            if (row == 0) bwd_trace(p, it - 1, 11);
         }
     }
     ptx::tc_fence_before();
@@ -341,6 +361,15 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 }  // namespace pt
 
 using namespace pt;
+
+static long long* g_bwd_trace = nullptr;
+static int g_bwd_trace_iters = 0;
+// debug hook for tools/attn_bwd_trace.py (not part of the product path): device buffer of 16 * iters int64
+extern "C" int pt_attn_gemma_bwd_set_trace(void* buf, int iters) {
+    g_bwd_trace = static_cast<long long*>(buf);
+    g_bwd_trace_iters = buf ? iters : 0;
+    return PT_OK;
+}
 
 extern "C" int pt_attn_gemma_bwd(const void* q_rot, const void* k_rot, const void* qkv, const void* dO_bf16,
                                  const void* kvbits, const float* lse, const float* delta, void* dS_bf16,
@@ -393,6 +422,7 @@ extern "C" int pt_attn_gemma_bwd(const void* q_rot, const void* k_rot, const voi
     p.dK = static_cast<__nv_bfloat16*>(dK_bf16);
     p.dV = static_cast<__nv_bfloat16*>(dV_bf16);
     p.ld_dk = ld_dk; p.ld_dv = ld_dv;
+    p.trace = g_bwd_trace; p.trace_iters = g_bwd_trace_iters;
     const long long items = static_cast<long long>(B) * hkv * p.nkt;
     PT_REQUIRE(items < (1ll << 31), "pt_attn_gemma_bwd: too many work items");
     const int grid = items < num_sms() ? static_cast<int>(items) : num_sms();
