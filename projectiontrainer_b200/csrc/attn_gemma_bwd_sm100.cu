@@ -22,8 +22,9 @@
 // the SM's shared memory, so there is one block in flight; within it the loads, the two early and the two late
 // MMA groups and the two softmax phases overlap pairwise (dO lands first -> dP; Q -> S; P -> dV^T runs while dS
 // is computed; dO of the next block loads while dK^T runs).
-// Roles: warps 0-3 softmax (thread = TMEM lane = stacked query row; at item end = head_dim row of the
-// transposed accumulators), warp 4 MMA issuer, warp 5 TMA producer.
+// Roles: warps 0-7 softmax (two threads per TMEM lane = stacked query row, 32 key columns each; at item end
+// lane = head_dim row of the transposed accumulators, which go back to [key][head_dim] rows through smem),
+// warp 8 MMA issuer, warp 9 TMA producer.
 // TMEM columns: S [0,64) dP [64,128) dV^T [128,128+64 MB) dK^T [..+64 MB), MB = hd / 128.
 #include "pt_common.cuh"
 #include "sm100_ptx.cuh"
@@ -32,7 +33,7 @@
 
 namespace pt {
 
-constexpr int kBwThreads = 192;
+constexpr int kBwThreads = 320;         // 8 softmax warps + MMA issuer + TMA producer
 constexpr int kBwPBytes = kGqRows * kGkTile * 2;            // 16 KB: P or dS block, one 128-byte row per query row
 // K + V tiles, Q + dO blocks, P + dS, barriers, alignment slack
 constexpr int gemma_bwd_smem(int hd) { return 2 * kGkTile * hd * 2 + 2 * kGqRows * hd * 2 + 2 * kBwPBytes + 256 + 1024; }
@@ -103,24 +104,24 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     uint64_t* do_empty = bars + 4;      // commit after dV^T (last reader of dO)
     uint64_t* s_full = bars + 5;        // commit after S -> softmax
     uint64_t* dp_full = bars + 6;       // commit after dP -> softmax
-    uint64_t* p_full = bars + 7;        // softmax (128 arrivals) -> MMA: P in smem, S read
-    uint64_t* ds_full = bars + 8;       // softmax (128 arrivals) -> MMA: dS in smem, dP read
+    uint64_t* p_full = bars + 7;        // softmax (256 arrivals) -> MMA: P in smem, S read
+    uint64_t* ds_full = bars + 8;       // softmax (256 arrivals) -> MMA: dS in smem, dP read
     uint64_t* acc_full = bars + 9;      // commit after the item's last dK^T -> epilogue
-    uint64_t* acc_free = bars + 10;     // epilogue (128 arrivals) -> MMA: accumulators read
+    uint64_t* acc_free = bars + 10;     // epilogue (256 arrivals) -> MMA: accumulators read
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 128) {
+    if (threadIdx.x == 256) {
         ptx::prefetch_tmap(&tmQ); ptx::prefetch_tmap(&tmdO); ptx::prefetch_tmap(&tmK); ptx::prefetch_tmap(&tmV);
         ptx::mbar_init(kv_full, 1); ptx::mbar_init(q_full, 1); ptx::mbar_init(do_full, 1);
         ptx::mbar_init(q_empty, 1); ptx::mbar_init(do_empty, 1);
         ptx::mbar_init(s_full, 1); ptx::mbar_init(dp_full, 1);
-        ptx::mbar_init(p_full, 128); ptx::mbar_init(ds_full, 128);
-        ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_free, 128);
+        ptx::mbar_init(p_full, 256); ptx::mbar_init(ds_full, 256);
+        ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_free, 256);
         ptx::fence_mbar_init();
     }
     constexpr uint32_t kTmemCols = HD == 256 ? 512 : 256;
-    if (warp == 4) {
+    if (warp == 8) {
         ptx::tmem_alloc(tmem_slot, kTmemCols);
         ptx::tmem_relinquish();
     }
@@ -132,7 +133,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const uint32_t tdV = tmem_base + 2 * kGkTile, tdK = tdV + MB * kGkTile;
     const int items = p.B * p.hkv * p.nkt;
 
-    if (warp == 5) {
+    if (warp == 9) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t n_item = 0, it = 0;                    // it = blocks loaded so far (all items)
@@ -168,7 +169,7 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 }
             }
         }
-    } else if (warp == 4) {
+    } else if (warp == 8) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t idescS = ptx::make_idesc_bf16(kGqRows, kGkTile, 0, 0);     // A = Q / dO, B = K / V: K-major
@@ -233,12 +234,17 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             }
         }
     } else {
-        // ===================== softmax warps: thread = stacked query row =====================
-        const int row = threadIdx.x;                               // TMEM lane
-        const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+        // ===================== softmax warps: two threads per stacked query row =====================
+        // warps 0-3 own key columns [0,32) of rows 32 (warp & 3) .. +31, warps 4-7 columns [32,64) (a warp may touch
+        // TMEM lanes 32 (warp % 4) .. +31 only).  The backward needs no cross-thread row reduction: LSE and delta
+        // are per-row inputs.
+        const int row = (warp & 3) * 32 + lane;                    // TMEM lane
+        const int half = warp >> 2;
+        const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
         const uint32_t p_row = ptx::smem_u32(sP) + row * 128;
         const uint32_t ds_row = ptx::smem_u32(sdS) + row * 128;
         const float c2 = p.scale_log2e;
+        const bool tr0 = threadIdx.x == 0;
         uint32_t n_item = 0, it = 0;
         for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
             int b, kvh, kt, qb0, nqb;
@@ -254,105 +260,112 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 // row statistics: in flight while the block's MMAs run
                 const float lse = live ? __ldg(p.lse + ridx) : INFINITY;
                 const float dl = live ? __ldg(p.delta + ridx) : 0.f;
-                const unsigned long long mask =
-                    gemma_tile_mask(kw, k0, p.window > 0 ? max(0, s - p.window + 1) : 0, live ? s : -1);
-                const bool all_vis = __all_sync(0xffffffffu, mask == ~0ull);
+                const uint32_t mask = static_cast<uint32_t>(
+                    gemma_tile_mask(kw, k0, p.window > 0 ? max(0, s - p.window + 1) : 0, live ? s : -1) >> (half * 32));
+                const bool all_vis = __all_sync(0xffffffffu, mask == 0xffffffffu);
 
                 // ---- P = exp2(S c - LSE) -> bf16 -> smem (B operand of dV^T += dO^T P)
-                float pf[64];
+                float pf[32];
                 {
-                    uint32_t v[2][32];
+                    uint32_t v[32];
                     ptx::mbar_wait(s_full, ph);
-                    if (row == 0) bwd_trace(p, it, 6);
+                    if (tr0) bwd_trace(p, it, 6);
                     ptx::tc_fence_after();
-                    ptx::tmem_ld_32x32(tS + lane_off, v[0]);
-                    ptx::tmem_ld_32x32(tS + lane_off + 32, v[1]);
+                    ptx::tmem_ld_32x32(tS + lane_off + half * 32, v);
                     ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int c = 0; c < 2; ++c)
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            pf[c * 32 + j] = ptx::exp2_fast(fmaf(__uint_as_float(v[c][j]), c2, -lse));
+                    for (int j = 0; j < 32; ++j) pf[j] = ptx::exp2_fast(fmaf(__uint_as_float(v[j]), c2, -lse));
                 }
                 if (!all_vis) {
 #pragma unroll
-                    for (int j = 0; j < 64; ++j)
-                        if (!((mask >> j) & 1ull)) pf[j] = 0.f;
+                    for (int j = 0; j < 32; ++j)
+                        if (!((mask >> j) & 1u)) pf[j] = 0.f;
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q)
-                    ptx::sts128(p_row + ((q ^ (row & 7)) << 4), pack_bf16(pf[8 * q], pf[8 * q + 1]),
+                for (int q = 0; q < 4; ++q)
+                    ptx::sts128(p_row + (((half * 4 + q) ^ (row & 7)) << 4), pack_bf16(pf[8 * q], pf[8 * q + 1]),
                                 pack_bf16(pf[8 * q + 2], pf[8 * q + 3]), pack_bf16(pf[8 * q + 4], pf[8 * q + 5]),
                                 pack_bf16(pf[8 * q + 6], pf[8 * q + 7]));
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(p_full);
-                if (row == 0) bwd_trace(p, it, 7);
+                if (tr0) bwd_trace(p, it, 7);
 
                 // ---- dS = scale P (dP - delta) -> bf16 -> smem (B operand of dK^T += Q^T dS) and global
-                uint32_t dk[32];
+                uint32_t dk[16];
                 ptx::mbar_wait(dp_full, ph);
-                if (row == 0) bwd_trace(p, it, 8);
+                if (tr0) bwd_trace(p, it, 8);
                 ptx::tc_fence_after();
-#pragma unroll
-                for (int c = 0; c < 2; ++c) {
+                {
                     uint32_t v[32];
-                    ptx::tmem_ld_32x32(tdP + lane_off + c * 32, v);
+                    ptx::tmem_ld_32x32(tdP + lane_off + half * 32, v);
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
-                        const float d0 = p.scale * pf[c * 32 + 2 * j] * (__uint_as_float(v[2 * j]) - dl);
-                        const float d1 = p.scale * pf[c * 32 + 2 * j + 1] * (__uint_as_float(v[2 * j + 1]) - dl);
-                        dk[c * 16 + j] = pack_bf16(d0, d1);
+                        const float d0 = p.scale * pf[2 * j] * (__uint_as_float(v[2 * j]) - dl);
+                        const float d1 = p.scale * pf[2 * j + 1] * (__uint_as_float(v[2 * j + 1]) - dl);
+                        dk[j] = pack_bf16(d0, d1);
                     }
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q)
-                    ptx::sts128(ds_row + ((q ^ (row & 7)) << 4), dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+                for (int q = 0; q < 4; ++q)
+                    ptx::sts128(ds_row + (((half * 4 + q) ^ (row & 7)) << 4), dk[4 * q], dk[4 * q + 1], dk[4 * q + 2],
+                                dk[4 * q + 3]);
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(ds_full);
-                if (row == 0) bwd_trace(p, it, 9);
+                if (tr0) bwd_trace(p, it, 9);
                 if (live) {
-                    __nv_bfloat16* g = p.dS + ridx * p.lds + k0;
+                    __nv_bfloat16* g = p.dS + ridx * p.lds + k0 + half * 32;
 #pragma unroll
-                    for (int q = 0; q < 8; ++q)
-                        if (k0 + q * 8 < p.lds)
+                    for (int q = 0; q < 4; ++q)
+                        if (k0 + half * 32 + q * 8 < p.lds)
                             *reinterpret_cast<uint4*>(g + q * 8) = make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
                 }
             }
-            if (row == 0) bwd_trace(p, it - 1, 10);
-            // ---- epilogue: thread = head-dim row (h * 128 + row) of the transposed accumulators; 64 keys each
+            if (tr0) bwd_trace(p, it - 1, 10);
+            // ---- epilogue.  The accumulators are transposed: TMEM lane = head-dim row (h * 128 + row), column =
+            // key; this thread owns keys half * 32 .. +31.  They are turned back into [key][head_dim] rows through
+            // shared memory (the P and dS blocks: 32 KB, idle until this warp group writes the next item's first P)
+            // and leave as 16-byte coalesced stores.
             ptx::mbar_wait(acc_full, n_item & 1);
             ptx::tc_fence_after();
             const int nk = min(kGkTile, p.S - k0);
+            uint8_t* stage = sP;                                    // [64 keys][HD] bf16
 #pragma unroll 1
             for (int t = 0; t < 2; ++t) {
                 const uint32_t tacc = t == 0 ? tdV : tdK;
-                __nv_bfloat16* outp = t == 0 ? p.dV : p.dK;
-                const long long ldo = t == 0 ? p.ld_dv : p.ld_dk;
 #pragma unroll 1
                 for (int h = 0; h < MB; ++h) {
-                    __nv_bfloat16* o = outp + (static_cast<long long>(b) * p.S + k0) * ldo + kvh * HD + h * 128 + row;
-#pragma unroll 1
-                    for (int c = 0; c < 2; ++c) {
-                        uint32_t v[32];
-                        ptx::tmem_ld_32x32(tacc + h * kGkTile + lane_off + c * 32, v);
-                        ptx::tmem_ld_wait();
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(tacc + h * kGkTile + lane_off + half * 32, v);
+                    ptx::tmem_ld_wait();
+                    __nv_bfloat16* st = reinterpret_cast<__nv_bfloat16*>(stage) + (half * 32) * HD + h * 128 + row;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (c * 32 + j < nk) o[(c * 32 + j) * ldo] = __float2bfloat16(__uint_as_float(v[j]));
-                    }
+                    for (int j = 0; j < 32; ++j) st[j * HD] = __float2bfloat16(__uint_as_float(v[j]));
                 }
+                if (t == 1) {                                       // both accumulators are in registers / smem now
+                    ptx::tc_fence_before();
+                    ptx::mbar_arrive(acc_free);
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                __nv_bfloat16* outp = t == 0 ? p.dV : p.dK;
+                const long long ldo = t == 0 ? p.ld_dv : p.ld_dk;
+                __nv_bfloat16* o = outp + (static_cast<long long>(b) * p.S + k0) * ldo + kvh * HD;
+                constexpr int kChunks = HD / 8;                     // 16-byte chunks per key row
+                for (int idx = threadIdx.x; idx < nk * kChunks; idx += 256) {
+                    const int key = idx / kChunks, c = idx - key * kChunks;
+                    *reinterpret_cast<uint4*>(o + key * ldo + c * 8) =
+                        *reinterpret_cast<const uint4*>(stage + (key * HD + c * 8) * 2);
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
             }
-            ptx::tc_fence_before();
-            ptx::mbar_arrive(acc_free);
-            if (row == 0) bwd_trace(p, it - 1, 11);
+            if (tr0) bwd_trace(p, it - 1, 11);
         }
     }
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 8) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc(tmem_base, kTmemCols);
     }
