@@ -258,19 +258,26 @@ int pt_swiglu_bwd(const void* dact, const void* gu, void* dgu, long long rows, i
 /* dZ = dH * d/dz[0.5 z (1 + erf(z/sqrt2))] — backward of nn.GELU() in ref:Stage1/projectors.py:18. */
 int pt_gelu_erf_bwd(const void* dH, const void* Z, void* dZ, long long n, void* stream);
 
+/* Device-side input validation.  nn.Embedding and CrossEntropyLoss raise on an out-of-range index; a kernel
+ * cannot, so it ORs a bit into the caller's int32 flag word (nullable) and keeps its reads in bounds; the host
+ * checks the word where it already synchronises on the loss (Stage1Engine.check_errors). */
+#define PT_ERRFLAG_TOKEN_ID 1   /* pt_embed_splice: a token id outside [0, vocab): row 0 was read instead */
+#define PT_ERRFLAG_TARGET   2   /* pt_ce_fwd_bwd: a target >= V: the row was left out of the loss */
+
 /* Text half of the splice (ref:Stage1/projector_trainer.py:186-220): x0[b, n_img+t, :] =
- * bf16(embed[token_ids[b,t]] * scale); attention mask / lm labels (int64, bit-exact),
+ * bf16(embed[token_ids[b,t]] * scale), embed bf16 [vocab, h]; attention mask / lm labels (int64, bit-exact),
  * key-valid bytes and shifted int32 targets (HF:loss/loss_utils.py:57-60) for all S = n_img+T positions. */
 int pt_embed_splice(const int64_t* token_ids, const int64_t* labels, const void* embed_bf16, float scale,
                     int64_t pad_id, int has_pad, int B, int T, int n_img, int h, float* x0,
                     int64_t* attn_mask, int64_t* lm_labels, uint8_t* keyvalid, int32_t* targets,
-                    void* stream);
+                    int64_t vocab, int32_t* err_flags, void* stream);
 
 /* Masked causal-LM cross-entropy over bf16 logits [rows, V] (HF:loss/loss_utils.py:28-67): writes
- * lse[rows], acc2 = {sum of row losses, #valid rows}, loss = mean; then overwrites the logits with
- * dlogits = (softmax - onehot) * gscale / n_valid (zero rows where target < 0). */
+ * lse[rows], acc2 = {sum of row losses, #valid rows}, loss = mean (NaN when no row has a label, as HF's mean
+ * over an empty set); then overwrites the logits with dlogits = (softmax - onehot) * gscale / n_valid (zero rows
+ * where target < 0). */
 int pt_ce_fwd_bwd(void* logits_bf16, long long ld, const int32_t* targets, int rows, int V, float* lse,
-                  float* acc2, float* loss, float gscale, void* stream);
+                  float* acc2, float* loss, float gscale, int32_t* err_flags, void* stream);
 
 /* out[n] = sum_m x[m][n] (bias gradients). */
 int pt_colsum(const void* x_bf16, long long ld, float* out, int M, int N, void* stream);

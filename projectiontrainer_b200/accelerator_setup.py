@@ -5,6 +5,7 @@ per GPU, launched by torchrun / `python -m torch.distributed.run`."""
 from __future__ import annotations
 
 import logging
+from collections import deque
 import os
 
 import torch
@@ -23,7 +24,9 @@ class Stage1Accelerator:
         self.sync_gradients = True        # ref never enters accumulate(): every micro-batch steps (F7)
         self.log_with = log_with
         self.trackers: list = []
-        self.logged: list = []
+        # the last records handed to log(): bounded (both trainers log every micro-batch; an unbounded list grows by
+        # millions of dicts over a long run and is inherited by every forked DataLoader worker)
+        self.logged = deque(maxlen=int(os.environ.get("PT_STAGE1_LOG_KEEP", "4096")))
         world = int(os.environ.get("WORLD_SIZE", "1"))
         self.process_index = int(os.environ.get("RANK", "0"))
         self.local_process_index = int(os.environ.get("LOCAL_RANK", "0"))

@@ -103,11 +103,16 @@ __global__ void embed_splice_kernel(const long long* __restrict__ token_ids, con
                                     const __nv_bfloat16* __restrict__ embed, float scale, long long pad_id,
                                     int has_pad, int B, int T, int n_img, int h, float* __restrict__ x0,
                                     long long* __restrict__ attn_mask, long long* __restrict__ lm_labels,
-                                    uint8_t* __restrict__ keyvalid, int* __restrict__ targets) {
+                                    uint8_t* __restrict__ keyvalid, int* __restrict__ targets, long long vocab,
+                                    int* __restrict__ err) {
     const int S = n_img + T;
     if (blockIdx.x < B * T) {
         const int b = blockIdx.x / T, t = blockIdx.x - b * T;
-        const long long id = token_ids[blockIdx.x];
+        long long id = token_ids[blockIdx.x];
+        if (id < 0 || id >= vocab) {        // nn.Embedding raises here; flag it (PT_ERRFLAG_TOKEN_ID) and read row 0
+            if (threadIdx.x == 0 && err) atomicOr(err, PT_ERRFLAG_TOKEN_ID);
+            id = 0;
+        }
         const __nv_bfloat16* e = embed + id * h;
         float* dst = x0 + (static_cast<long long>(b) * S + n_img + t) * h;
         for (int i = threadIdx.x * 8; i < h; i += blockDim.x * 8) {
@@ -144,11 +149,13 @@ __global__ void embed_splice_kernel(const long long* __restrict__ token_ids, con
 // stats: one block per row; lse, per-row loss, and (loss_sum, n_valid) accumulated with atomics.
 __global__ void __launch_bounds__(1024)
 ce_stats_kernel(const __nv_bfloat16* __restrict__ logits, long long ld, const int* __restrict__ targets,
-                int V, float* __restrict__ lse_out, float* __restrict__ acc /* [loss_sum, n_valid] */) {
+                int V, float* __restrict__ lse_out, float* __restrict__ acc /* [loss_sum, n_valid] */,
+                int* __restrict__ err) {
     __shared__ float sh[32];
     const int r = blockIdx.x;
     const int tgt = targets[r];
-    if (tgt < 0) { if (threadIdx.x == 0) lse_out[r] = 0.f; return; }
+    if (tgt >= V && threadIdx.x == 0 && err) atomicOr(err, PT_ERRFLAG_TARGET);   // CrossEntropyLoss raises here
+    if (tgt < 0 || tgt >= V) { if (threadIdx.x == 0) lse_out[r] = 0.f; return; }
     const __nv_bfloat16* row = logits + r * ld;
     // one pass over the row (it is 512 KB at V = 262144: a second pass re-reads it through L2): per thread a
     // running maximum and a sum rescaled whenever the maximum moves, one rescale per 8 logits
@@ -186,7 +193,7 @@ ce_grad_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const int* __re
     __nv_bfloat16* row = logits + r * ld;
     const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
     if (i >= V) return;
-    if (tgt < 0) { *reinterpret_cast<uint4*>(row + i) = make_uint4(0, 0, 0, 0); return; }
+    if (tgt < 0 || tgt >= V) { *reinterpret_cast<uint4*>(row + i) = make_uint4(0, 0, 0, 0); return; }
     const float k = gscale / fmaxf(acc[1], 1.f);
     const float l = lse[r];
     const uint4 u = *reinterpret_cast<const uint4*>(row + i);
@@ -201,7 +208,8 @@ ce_grad_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const int* __re
 }
 
 __global__ void ce_finalize_kernel(const float* __restrict__ acc, float* __restrict__ loss) {
-    loss[0] = acc[1] > 0.f ? acc[0] / acc[1] : 0.f;
+    // no valid label at all: HF's mean over an empty set is NaN (HF:loss/loss_utils.py:28-45) — keep it visible
+    loss[0] = acc[1] > 0.f ? acc[0] / acc[1] : __int_as_float(0x7fc00000);
 }
 
 // ---- column sums of a bf16 [M,N] matrix into f32 [N] (bias gradients) ---------------------------
@@ -353,26 +361,27 @@ extern "C" int pt_gelu_erf_bwd(const void* dH, const void* Z, void* dZ, long lon
 extern "C" int pt_embed_splice(const int64_t* token_ids, const int64_t* labels, const void* embed_bf16,
                                float scale, int64_t pad_id, int has_pad, int B, int T, int n_img, int h,
                                float* x0, int64_t* attn_mask, int64_t* lm_labels, uint8_t* keyvalid,
-                               int32_t* targets, void* stream) {
+                               int32_t* targets, int64_t vocab, int32_t* err_flags, void* stream) {
     PT_REQUIRE(token_ids && labels && embed_bf16 && x0 && attn_mask && lm_labels && keyvalid && targets,
                "pt_embed_splice: null pointer");
-    PT_REQUIRE(B > 0 && T > 0 && n_img >= 0 && h > 0 && h % 8 == 0, "pt_embed_splice: bad shape");
+    PT_REQUIRE(B > 0 && T > 0 && n_img >= 0 && h > 0 && h % 8 == 0 && vocab > 0, "pt_embed_splice: bad shape");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     embed_splice_kernel<<<B * T + B, 128, 0, ST(stream)>>>(
         reinterpret_cast<const long long*>(token_ids), reinterpret_cast<const long long*>(labels),
         CBF(embed_bf16), scale, pad_id, has_pad, B, T, n_img, h, x0,
-        reinterpret_cast<long long*>(attn_mask), reinterpret_cast<long long*>(lm_labels), keyvalid, targets);
+        reinterpret_cast<long long*>(attn_mask), reinterpret_cast<long long*>(lm_labels), keyvalid, targets,
+        static_cast<long long>(vocab), err_flags);
     return check_launch("embed_splice");
 }
 
 extern "C" int pt_ce_fwd_bwd(void* logits_bf16, long long ld, const int32_t* targets, int rows, int V,
-                             float* lse, float* acc2, float* loss, float gscale, void* stream) {
+                             float* lse, float* acc2, float* loss, float gscale, int32_t* err_flags, void* stream) {
     PT_REQUIRE(logits_bf16 && targets && lse && acc2 && loss, "pt_ce_fwd_bwd: null pointer");
     PT_REQUIRE(rows > 0 && V > 0 && V % 8 == 0 && ld % 8 == 0, "pt_ce_fwd_bwd: V and ld must be multiples of 8");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     cudaStream_t st = ST(stream);
     if (cudaMemsetAsync(acc2, 0, 2 * sizeof(float), st) != cudaSuccess) return check_launch("ce memset");
-    ce_stats_kernel<<<rows, 1024, 0, st>>>(CBF(logits_bf16), ld, targets, V, lse, acc2);
+    ce_stats_kernel<<<rows, 1024, 0, st>>>(CBF(logits_bf16), ld, targets, V, lse, acc2, err_flags);
     ce_finalize_kernel<<<1, 1, 0, st>>>(acc2, loss);
     dim3 grid((V / 8 + 255) / 256, rows);
     ce_grad_kernel<<<grid, 256, 0, st>>>(BF(logits_bf16), ld, targets, V, lse, acc2, gscale);

@@ -172,6 +172,9 @@ class Stage1Engine:
         self.max_geometries = int(os.environ.get("PT_STAGE1_MAX_GEOMETRIES", "6"))
         total = torch.cuda.get_device_properties(device).total_memory if torch.cuda.is_available() else 0
         self.arena_budget_bytes = int(float(os.environ.get("PT_STAGE1_ARENA_GB", "0")) * 2 ** 30) or int(0.6 * total)
+        # device-side input validation (token ids / targets out of range): kernels OR bits into this word, the host
+        # reads it where it already synchronises on the loss (check_errors)
+        self._err = torch.zeros(1, dtype=torch.int32, device=device) if torch.cuda.is_available() else None
         self._acc_grad = None           # gradient accumulated over micro-batches that did not step
         self._acc_pending = False
         self._rope: dict = {}
@@ -179,7 +182,10 @@ class Stage1Engine:
         self.saved = None
         # CUDA-graph replay of forward+backward (launch-bound inner loop: ~900 launches per step)
         self.use_graph = os.environ.get("PT_STAGE1_GRAPH", "1") != "0"
-        self._graphs: dict = {}
+        # graphs of the current geometry, least recently used first; at most max_graphs stay captured per geometry
+        # (a graph pins ~900 kernel nodes; Stage 2 keys it on the bucketed label span as well)
+        self._graphs: OrderedDict = OrderedDict()
+        self.max_graphs = int(os.environ.get("PT_STAGE1_MAX_GRAPHS", "8"))
         # GeGLU forward / backward fused into the gate||up and down-dgrad GEMM epilogues (needs ff % 128 == 0)
         self.fuse_attn_fwd = ops.attn_gemma_fusable(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_FUSE_ATTN_FWD", "1") != "0"
@@ -219,7 +225,7 @@ class Stage1Engine:
             nbytes = lambda ws: sum(t.numel() * t.element_size() for t in ws.values())
             sizes = [nbytes(ws) for ws, _ in self._arenas.values()]
             estimate = sizes[-1] if sizes else 0
-            self._ws, self._graphs = {}, {}
+            self._ws, self._graphs = {}, OrderedDict()
             while self._arenas and (len(self._arenas) >= max(1, self.max_geometries) or
                                     sum(sizes) + estimate > self.arena_budget_bytes):
                 _, (ws, graphs) = self._arenas.popitem(last=False)
@@ -228,6 +234,19 @@ class Stage1Engine:
                 ws.clear()
         self._geometry = key
         self.saved = None
+
+    def arena_bytes(self) -> int:
+        """Bytes held by the workspaces of every live geometry (current one included)."""
+        nbytes = lambda ws: sum(t.numel() * t.element_size() for t in ws.values())
+        return nbytes(self._ws) + sum(nbytes(ws) for ws, _ in self._arenas.values())
+
+    def _enforce_budget(self) -> None:
+        """After the current geometry grew (first call at a new label span sizes new CE-side buffers): drop the
+        least recently used OTHER geometries until the total is back under the byte budget."""
+        while self._arenas and self.arena_bytes() > self.arena_budget_bytes:
+            _, (ws, graphs) = self._arenas.popitem(last=False)
+            graphs.clear()
+            ws.clear()
 
     def rope(self, S, full: bool):
         key = (S, full)
@@ -435,7 +454,7 @@ class Stage1Engine:
         lse = self.buf("l_lse", (R,), F32)
         acc2 = self.buf("l_acc2", (2,), F32)
         loss = self.buf("l_loss", (1,), F32)
-        ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.loss_divisor)
+        ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.loss_divisor, err=self._err)
         self.saved = dict(layers=sv, x_final=x, logits=logits, B=B, S=S, T=T, lab0=lab0) if save else None
         return loss
 
@@ -637,8 +656,23 @@ class Stage1Engine:
         keyvalid = self.buf("s_kv", (B, S), torch.uint8)
         targets = self.buf("s_tgt", (B, S), torch.int32)
         ops.embed_splice(token_ids, labels, self.llm.embed, self.llm.embed_scale, pad_id, self.n_img,
-                         x0, attn_mask, lm_labels, keyvalid, targets)
+                         x0, attn_mask, lm_labels, keyvalid, targets, err=self._err)
         return attn_mask, lm_labels, keyvalid, targets
+
+    def check_errors(self) -> None:
+        """Raise if a kernel flagged an out-of-range token id or CE target since the last call (what
+        `nn.Embedding` / `CrossEntropyLoss` raise on in the reference).  Costs a 4-byte device read: call it where
+        the loss is read back anyway (the trainers do, once per optimizer step)."""
+        flags = int(self._err.item())
+        if flags:
+            self._err.zero_()
+            what = []
+            if flags & ops.ERRFLAG_TOKEN_ID:
+                what.append(f"a token id outside the embedding table [0, {self.llm.embed.shape[0]})")
+            if flags & ops.ERRFLAG_TARGET:
+                what.append(f"a label >= the vocabulary size {self.lcfg.vocab}")
+            raise IndexError("Stage-1 step: " + " and ".join(what) + " (the tokenizer has ids the language model "
+                             "does not: resize the embedding table or fix the pad / eos id)")
 
     def _span(self, T: int, label_span):
         """(first position whose shifted target can be a label, number of such positions) in sequence
@@ -739,11 +773,15 @@ class Stage1Engine:
         key = (tuple(pv.shape), tuple(ti.shape), pad_id, span, self.loss_divisor)
         g = self._graphs.get(key)
         if g is None:
+            while len(self._graphs) >= max(1, self.max_graphs):      # least recently used graph of this geometry
+                self._graphs.popitem(last=False)
             g = dict(px=torch.empty(pv.shape, dtype=F32, device=self.device),
                      ids=torch.empty(ti.shape, dtype=torch.int64, device=self.device),
                      lab=torch.empty(lb.shape, dtype=torch.int64, device=self.device),
                      graph=None, calls=0, loss=None)
             self._graphs[key] = g
+        else:
+            self._graphs.move_to_end(key)
         st = batch.get("_staged")
         if st is not None:
             # inputs were prefetched by stage_batch() on the copy stream: order after that copy, then D2D
@@ -759,6 +797,7 @@ class Stage1Engine:
             n0 = _lib.launch_count
             loss = self.forward_backward(g["px"], g["ids"], g["lab"], pad_id, span)
             g["launches"] = _lib.launch_count - n0
+            self._enforce_budget()
             return loss
         if g["graph"] is None:
             graph = torch.cuda.CUDAGraph()

@@ -305,21 +305,27 @@ def gelu_erf_bwd(dH, Z, dZ):
     _lib.call("pt_gelu_erf_bwd", _ptr(dH), _ptr(Z), _ptr(dZ), C.c_longlong(dH.numel()), _stream())
 
 
+ERRFLAG_TOKEN_ID, ERRFLAG_TARGET = 1, 2
+
+
 def embed_splice(token_ids, labels, embed, scale, pad_id, n_img, x0, attn_mask, lm_labels,
-                 keyvalid, targets):
-    _req_cuda(token_ids, labels, embed, x0, attn_mask, lm_labels, keyvalid, targets)
+                 keyvalid, targets, err=None):
+    """`err` (int32 [1], optional): ERRFLAG_TOKEN_ID is OR-ed in when a token id lies outside the table."""
+    _req_cuda(token_ids, labels, embed, x0, attn_mask, lm_labels, keyvalid, targets, err)
     B, T = token_ids.shape
     has_pad = pad_id is not None
     _lib.call("pt_embed_splice", _ptr(token_ids), _ptr(labels), _ptr(embed), _f(scale),
               _i64(pad_id if has_pad else 0), int(has_pad), B, T, int(n_img), embed.shape[1],
-              _ptr(x0), _ptr(attn_mask), _ptr(lm_labels), _ptr(keyvalid), _ptr(targets), _stream())
+              _ptr(x0), _ptr(attn_mask), _ptr(lm_labels), _ptr(keyvalid), _ptr(targets),
+              _i64(embed.shape[0]), _ptr(err), _stream())
 
 
-def ce_fwd_bwd(logits, targets, lse, acc2, loss, gscale):
-    _req_cuda(logits, targets, lse, acc2, loss)
+def ce_fwd_bwd(logits, targets, lse, acc2, loss, gscale, err=None):
+    """`err` (int32 [1], optional): ERRFLAG_TARGET is OR-ed in when a target is >= V."""
+    _req_cuda(logits, targets, lse, acc2, loss, err)
     rows, V = logits.shape
     _lib.call("pt_ce_fwd_bwd", _ptr(logits), C.c_longlong(logits.stride(0)), _ptr(targets), rows, V,
-              _ptr(lse), _ptr(acc2), _ptr(loss), _f(gscale), _stream())
+              _ptr(lse), _ptr(acc2), _ptr(loss), _f(gscale), _ptr(err), _stream())
 
 
 def colsum(x, out):

@@ -55,19 +55,75 @@ def _fork_safe_iter(loader):
         gc.unfreeze()
 
 
+class _ShardedBatchSampler(torch.utils.data.Sampler):
+    """Batch sampler of ONE process: what accelerate's `BatchSamplerShard` (split_batches=False, even_batches=True)
+    hands it.  Every process draws the same index stream (same seeded sampler), cuts it into batches and keeps
+    batch i iff i % world == rank, so a process only ever LOADS its own samples (decode / resize / tokenize run for
+    1/world of the data set per process); processes that come up short take one of the first `world` batches again so
+    that all of them run the same number of optimizer steps."""
+
+    def __init__(self, sampler, batch_size: int, rank: int, world: int):
+        self.sampler, self.batch_size, self.rank, self.world = sampler, int(batch_size), int(rank), int(world)
+
+    @property
+    def unsharded_len(self) -> int:
+        return math.ceil(len(self.sampler) / self.batch_size)
+
+    def __len__(self):
+        return math.ceil(self.unsharded_len / self.world)
+
+    def __iter__(self):
+        first, mine, batch, i = [], 0, [], 0
+        def done(b):
+            nonlocal mine, i
+            if i < self.world:
+                first.append(b)
+            take = i % self.world == self.rank
+            i += 1
+            if take:
+                mine += 1
+            return take
+        for idx in self.sampler:
+            batch.append(idx)
+            if len(batch) == self.batch_size:
+                if done(batch):
+                    yield batch
+                batch = []
+        if batch and done(batch):
+            yield batch
+        if mine < len(self) and first:
+            yield first[self.rank % len(first)]
+
+
+def sharded_loader(dataset, *, batch_size, shuffle, rank, world, generator=None, **loader_kw):
+    """DataLoader over this process's share of the batches (see _ShardedBatchSampler), wrapped for fork-safe
+    iteration.  `.unsharded_len` = number of batches of the whole data set (the reference sizes its schedule from
+    the loader BEFORE `accelerator.prepare` shards it: ref:Stage1/projector_trainer.py:82-87)."""
+    from torch.utils.data import RandomSampler, SequentialSampler
+    sampler = RandomSampler(dataset, generator=generator) if shuffle else SequentialSampler(dataset)
+    bs = _ShardedBatchSampler(sampler, batch_size, rank, world)
+    # the DataLoader draws its workers' base seed from the same generator, as DataLoader(shuffle=True, generator=g) does
+    out = _ShardedLoader(DataLoader(dataset, batch_sampler=bs, generator=generator, **loader_kw), rank, world,
+                         presharded=True)
+    out.unsharded_len = bs.unsharded_len
+    return out
+
+
 class _ShardedLoader:
     """What `accelerator.prepare(dataloader)` gives each process: batch i of the (identically shuffled)
     loader goes to process i % N; short processes wrap around so that every process takes the same
-    number of optimizer steps (accelerate's even_batches)."""
+    number of optimizer steps (accelerate's even_batches).  With `presharded` the wrapped DataLoader already
+    yields this process's batches only (sharded_loader: nothing is loaded and thrown away); otherwise any iterable of
+    batches is filtered here."""
 
-    def __init__(self, loader, rank, world):
-        self.loader, self.rank, self.world = loader, rank, world
+    def __init__(self, loader, rank, world, presharded: bool = False):
+        self.loader, self.rank, self.world, self.presharded = loader, rank, world, presharded
 
     def __len__(self):
-        return math.ceil(len(self.loader) / self.world)
+        return len(self.loader) if self.presharded else math.ceil(len(self.loader) / self.world)
 
     def __iter__(self):
-        if self.world == 1:
+        if self.world == 1 or self.presharded:
             yield from _fork_safe_iter(self.loader)
             return
         first, mine = [], 0
@@ -113,19 +169,18 @@ class ProjectionTrainerStage1:
             os.makedirs(output_dir, exist_ok=True)
 
         gen = torch.Generator().manual_seed(0)      # same shuffle on every process (accelerate syncs RNG)
-        base_loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=True, num_workers=2,
-                                 generator=gen, pin_memory=True, collate_fn=stage1_collate)
+        rank, world = accelerator.process_index, accelerator.num_processes
+        self.train_loader = sharded_loader(train_dataset, batch_size=batch_size, shuffle=True, rank=rank, world=world,
+                                           generator=gen, num_workers=2, pin_memory=True, collate_fn=stage1_collate)
         self.val_loader = None
         if val_dataset is not None:
-            self.val_loader = _ShardedLoader(DataLoader(val_dataset, batch_size=batch_size, shuffle=False,
-                                                        num_workers=2, pin_memory=True, collate_fn=stage1_collate),
-                                             accelerator.process_index, accelerator.num_processes)
+            self.val_loader = sharded_loader(val_dataset, batch_size=batch_size, shuffle=False, rank=rank,
+                                             world=world, num_workers=2, pin_memory=True, collate_fn=stage1_collate)
         # schedule lengths are computed from the UNSHARDED loader, as the reference does (:82-87)
-        steps_per_epoch = math.ceil(len(base_loader) / gradient_accumulation_steps)
+        steps_per_epoch = math.ceil(self.train_loader.unsharded_len / gradient_accumulation_steps)
         self.max_train_steps = num_epochs * steps_per_epoch
         self.num_warmup_steps = math.ceil(warmup_ratio * self.max_train_steps)
         self._sched_step = 0
-        self.train_loader = _ShardedLoader(base_loader, accelerator.process_index, accelerator.num_processes)
 
         # frozen towers -> packed bf16 weights (read once; none of the HF forward code runs afterwards)
         vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
@@ -181,6 +236,7 @@ class ProjectionTrainerStage1:
                 global_step += 1
                 n_steps += 1
                 avg_loss_step = acc.gather(loss).mean().item()          # the one host sync of the step
+                self.engine.check_errors()      # out-of-range token ids / labels flagged by the kernels
                 epoch_train_loss += avg_loss_step
                 if acc.is_main_process:
                     acc.log({"train/batch_loss": avg_loss_step, "train/learning_rate": self.current_lr(),

@@ -25,7 +25,7 @@ from torch.utils.data import DataLoader
 
 from . import weights as Wt
 from .engine import PackedGemma, PackedSiglip, ProjectorState, Stage1Engine
-from .projector_trainer import _ShardedLoader, cosine_with_warmup
+from .projector_trainer import cosine_with_warmup, sharded_loader
 
 logger = logging.getLogger(__name__)
 
@@ -58,7 +58,8 @@ def vqa_collate_fn(batch, tokenizer):
 def vqa_step_inputs(batch: dict, pad_id: int, bucket: int = 1) -> dict:
     """Collated VQA batch -> the engine's batch dict.  Integer work, bit-exact with
     ref:Stage2/trainer.py:366-395: text = [question ; answer], labels = -100 over the question and the
-    answer ids with pads -> -100, `label_span` = the answer columns.  `bucket` > 1 appends pad columns
+    answer ids with pads -> -100, `label_span` = the columns that can carry a label (the answer; widened to
+    bucket boundaries, see below).  `bucket` > 1 appends pad columns
     AFTER the answer so the text length is a multiple of it: masked keys without labels, at positions
     behind every real token, so the loss and gradients are those of the unpadded batch while the number of
     distinct sequence lengths (each owns a workspace and a CUDA graph in the engine) stays small."""
@@ -74,7 +75,12 @@ def vqa_step_inputs(batch: dict, pad_id: int, bucket: int = 1) -> dict:
     labels[:, Lq:T] = torch.where(a == pad_id, torch.full_like(a, -100), a)
     if q.is_pinned():       # DataLoader(pin_memory=True): keep the step's copies asynchronous
         ids, labels = ids.pin_memory(), labels.pin_memory()
-    out = {"token_ids": ids, "labels": labels, "label_span": (Lq, La)}
+    # the span of positions that go through the final norm / LM head / CE is bucketed as well (start rounded down,
+    # end = the bucketed text length): the extra rows carry target -100, which the CE kernels skip, so loss and
+    # gradients are unchanged, while the engine keys its CUDA graph and its [rows, vocab] logits buffer on the span —
+    # exact (Lq, La) pairs would re-capture a graph and add a logits buffer for almost every micro-batch
+    off = (Lq // bucket) * bucket
+    out = {"token_ids": ids, "labels": labels, "label_span": (off, Tb - off)}
     out.update({k: batch[k] for k in ("pixel_values", "images_u8") if k in batch})
     return out
 
@@ -124,16 +130,15 @@ class VQATrainerStage2:
 
         collate = partial(vqa_collate_fn, tokenizer=tokenizer)
         gen = torch.Generator().manual_seed(0)      # same shuffle on every process (accelerate syncs RNG)
-        base_loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=True, num_workers=4,
-                                 pin_memory=True, collate_fn=collate, generator=gen)
-        val_base = DataLoader(val_dataset, batch_size=batch_size, shuffle=False, num_workers=4,
-                              pin_memory=True, collate_fn=collate)
+        rank, world = accelerator.process_index, accelerator.num_processes
+        self.train_loader = sharded_loader(train_dataset, batch_size=batch_size, shuffle=True, rank=rank, world=world,
+                                           generator=gen, num_workers=4, pin_memory=True, collate_fn=collate)
+        self.val_loader = sharded_loader(val_dataset, batch_size=batch_size, shuffle=False, rank=rank, world=world,
+                                         num_workers=4, pin_memory=True, collate_fn=collate)
         # schedule length from the UNSHARDED loader, as the reference computes it before prepare() (:152-157)
-        self.max_train_steps = num_epochs * math.ceil(len(base_loader) / self.grad_accum)
+        self.max_train_steps = num_epochs * math.ceil(self.train_loader.unsharded_len / self.grad_accum)
         self.num_warmup_steps = math.ceil(warmup_ratio * self.max_train_steps)
         self._sched_step = 0
-        self.train_loader = _ShardedLoader(base_loader, accelerator.process_index, accelerator.num_processes)
-        self.val_loader = _ShardedLoader(val_base, accelerator.process_index, accelerator.num_processes)
         self.val_loader.dataset = val_dataset
 
         vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
@@ -186,6 +191,7 @@ class VQATrainerStage2:
                                               weight_decay=self.weight_decay, allreduce=acc.all_reduce_sum_,
                                               world_size=acc.num_processes, max_norm=1.0, sync_gradients=sync)
                 micro_loss = acc.gather(loss).mean().item()             # the one host sync of the micro-batch
+                self.engine.check_errors()      # out-of-range token ids / labels flagged by the kernels
                 if sync:
                     self._sched_step += acc.num_processes
                     global_step += 1

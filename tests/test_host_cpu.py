@@ -69,6 +69,46 @@ def test_sharded_loader_even_batches():
         assert set(sum(seen, [])) == set(batches)                       # every batch is consumed
 
 
+def test_sharded_loader_loads_only_its_own_samples():
+    """shard at the batch sampler (accelerate's BatchSamplerShard) — a rank must not decode the batches
+    of the other ranks.  Every rank sees the same seeded permutation, takes batch i iff i % world == rank, and
+    short ranks wrap around to one of the first batches so that all ranks step equally often."""
+    import torch
+    from projectiontrainer_b200.projector_trainer import sharded_loader
+
+    class Counting(torch.utils.data.Dataset):
+        def __init__(self, n):
+            self.n, self.calls = n, []
+        def __len__(self):
+            return self.n
+        def __getitem__(self, i):
+            self.calls.append(i)
+            return {"x": torch.tensor(i)}
+
+    n, bs = 23, 4                                   # 6 batches, the last one short
+    for world in (1, 2, 4):
+        per_rank, lens = [], []
+        for r in range(world):
+            ds = Counting(n)
+            ld = sharded_loader(ds, batch_size=bs, shuffle=True, rank=r, world=world,
+                                generator=torch.Generator().manual_seed(0), num_workers=0)
+            assert ld.unsharded_len == 6 and len(ld) == math.ceil(6 / world)
+            batches = [b["x"].tolist() for b in ld]
+            assert len(batches) == len(ld)
+            assert sorted(ds.calls) == sorted(sum(batches, []))          # nothing loaded and thrown away
+            assert len(ds.calls) <= math.ceil(6 / world) * bs
+            per_rank.append(batches)
+            lens.append(len(batches))
+        assert len(set(lens)) == 1
+        assert set(sum(sum(per_rank, []), [])) == set(range(n))          # together: the whole data set
+    # two epochs draw two different permutations, identically on every rank
+    lds = [sharded_loader(Counting(n), batch_size=bs, shuffle=True, rank=r, world=2,
+                          generator=torch.Generator().manual_seed(0), num_workers=0) for r in range(2)]
+    e1 = [[b["x"].tolist() for b in ld] for ld in lds]
+    e2 = [[b["x"].tolist() for b in ld] for ld in lds]
+    assert e1 != e2 and set(sum(e2[0] + e2[1], [])) == set(range(n))
+
+
 def test_config_rejects_unsupported_models():
     from projectiontrainer_b200.config import gemma_cfg_from_hf
 

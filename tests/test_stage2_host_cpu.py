@@ -37,7 +37,29 @@ def test_collate_and_step_inputs_bit_exact_vs_oracle(side, bucket):
     assert np.array_equal(ids[:, :T], np.concatenate([q_ref, a_ref], axis=1)) and (ids[:, T:] == lc.pad_id).all()
     assert np.array_equal(lab[:, :T], lab_ref[:, n_img:]) and (lab[:, T:] == -100).all()
     assert np.array_equal((ids[:, :T] != lc.pad_id).astype(np.int64), attn_ref[:, n_img:])
-    assert st["label_span"] == (q_ref.shape[1], a_ref.shape[1])
+    # the label span covers the answer columns, widened to bucket boundaries (extra rows carry label -100)
+    Lq, La = q_ref.shape[1], a_ref.shape[1]
+    off, cnt = st["label_span"]
+    assert off % bucket == 0 and off <= Lq and Lq - off < bucket and off + cnt == ids.shape[1]
+    assert (lab[:, off:Lq] == -100).all() and (lab[:, Lq + La:] == -100).all()
+    if bucket == 1:
+        assert st["label_span"] == (Lq, La)
+
+
+def test_ragged_spans_bucket_to_few_graph_keys():
+    """at batch_size 1 every (Lq, La) pair is distinct; the graph key (text length, label span) must not be."""
+    lc = O.GemmaCfg(vocab=512, hidden=64, ff=128, layers=6, hq=2, hkv=1, hd=16, window=8, q_scalar=16.0)
+    rng = np.random.default_rng(0)
+    keys, exact = set(), set()
+    for _ in range(400):
+        Lq, La = int(rng.integers(4, 129)), int(rng.integers(4, 513))
+        cb = {"question_input_ids": torch.full((1, Lq), 5, dtype=torch.int64),
+              "answer_input_ids": torch.full((1, La), 7, dtype=torch.int64),
+              "pixel_values": torch.zeros(1, 3, 8, 8)}
+        st = vqa_step_inputs(cb, lc.pad_id, 32)
+        keys.add((st["token_ids"].shape[1], st["label_span"]))
+        exact.add((Lq, La))
+    assert len(exact) > 390 and len(keys) <= 5 * 21, (len(exact), len(keys))
 
 
 def test_accumulate_bookkeeping_matches_oracle_schedule():
