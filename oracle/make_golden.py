@@ -48,6 +48,8 @@ CASES = {
                        dict(vocab=304, hidden=48, ff=96, layers=7, hq=4, hkv=1, hd=32, window=5,
                             q_scalar=32.0), 2, 9, False, 1, 3, 0.34),
     "config1_full": ({}, {}, 2, 64, True, 2, 1, 0.0),
+    # the BENCHMARKED geometry (BASELINE.json configs[2]: T = 128, S = 703 > window 512) at full model size, B = 2
+    "config3_b2_full": ({}, {}, 2, 128, True, 1, 1, 0.0),
     # Qwen3 decoder recipe (the reference's launch script trains against Qwen/Qwen3-8B:
     # run_projection_train_stage1.sh:12): pre-norm only, SwiGLU, q/k norms, unscaled embeddings, untied LM head,
     # full attention everywhere, GQA; the trainer takes its non-Gemma embedding branch (projector_trainer.py:190-195)

@@ -179,6 +179,46 @@ def test_geometry_arenas_are_bounded_and_reusable(cuda_dev):
             assert abs(loss - first.setdefault(T, loss)) < 1e-4, (rnd, T)
 
 
+def test_ragged_label_spans_keep_graphs_and_arena_bounded(cuda_dev):
+    """at batch_size 1 every micro-batch has its own (question, answer) lengths.  With the text length
+    AND the label span bucketed (vqa_step_inputs) the engine captures a bounded number of CUDA graphs and its arenas
+    stop growing, and the bucketing leaves the loss of a batch where the exact span would give it."""
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.vqa_trainer import vqa_step_inputs
+    vkw = dict(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=6, hq=2, hkv=1, hd=256, window=8, q_scalar=256.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev)
+    eng.max_graphs = 3
+    g = torch.Generator().manual_seed(5)
+    px = (torch.rand(1, 3, ovc.image, ovc.image, generator=g) * 2 - 1).to(cuda_dev)
+    sizes, keys = [], set()
+    for it in range(60):
+        Lq, La = int(torch.randint(1, 40, (1,), generator=g)), int(torch.randint(1, 70, (1,), generator=g))
+        cb = {"question_input_ids": torch.randint(3, olc.vocab, (1, Lq), generator=g),
+              "answer_input_ids": torch.randint(3, olc.vocab, (1, La), generator=g), "pixel_values": px}
+        st = vqa_step_inputs(cb, olc.pad_id, 32)
+        keys.add((st["token_ids"].shape[1], st["label_span"]))
+        b = {k: (v.to(cuda_dev) if torch.is_tensor(v) else v) for k, v in st.items()}
+        loss = eng.train_step(b, 0.0, pad_id=olc.pad_id, weight_decay=0.0).item()          # lr 0: weights fixed
+        assert len(eng._graphs) <= eng.max_graphs and len(eng._arenas) < eng.max_geometries
+        sizes.append(eng.arena_bytes())
+        if it % 20 == 0:        # the same batch with its exact span, eager: same loss
+            ex = vqa_step_inputs(cb, olc.pad_id, 1)
+            eng.use_graph = False
+            ref = eng.train_step({k: (v.to(cuda_dev) if torch.is_tensor(v) else v) for k, v in ex.items()}, 0.0,
+                                 pad_id=olc.pad_id, weight_decay=0.0).item()
+            eng.use_graph = True
+            assert abs(loss - ref) < 2e-4 * abs(ref), (it, loss, ref)
+            sizes[-1] = eng.arena_bytes()
+    assert len(keys) <= 8                                   # 60 distinct (Lq, La) pairs, a handful of graph keys
+    assert max(sizes[40:]) <= max(sizes[:40])               # no growth once every bucket has been seen
+
+
 def test_geometry_arenas_respect_the_byte_budget(cuda_dev):
     """Besides the count limit, the arenas' total size stays under `arena_budget_bytes` (default 60 % of the device):
     with a budget smaller than two activation sets only the current one and at most one more survive, and the numbers
