@@ -136,10 +136,13 @@ def test_trainer_accepts_hf_modules_front_door(cuda_dev, tmp_path):
     assert a.llm.embed_scale == b.llm.embed_scale and a.llm.lm_head.data_ptr() == a.llm.embed.data_ptr()
     for la, lb in zip(a.llm.layers, b.llm.layers):
         assert all((la[k] is None and lb[k] is None) or torch.equal(la[k], lb[k]) for k in la)
-    # (2) same trajectory: the kernels are deterministic given identical buffers
-    assert len(traj_hf) == 3 and traj_hf == traj_pk
+    # (2) same trajectory up to the summation order of the atomics in the loss / bias-gradient reductions
+    assert len(traj_hf) == 3
+    for (l1, lr1), (l2, lr2) in zip(traj_hf, traj_pk):
+        assert lr1 == lr2 and abs(l1 - l2) < 1e-5 * abs(l2), (traj_hf, traj_pk)
     for k, v in proj_hf.state_dict().items():
-        assert torch.equal(v, proj_pk.state_dict()[k]), k
+        d1, d2 = v.cpu().double() - P[k].double(), proj_pk.state_dict()[k].cpu().double() - P[k].double()
+        assert float((d1 - d2).norm() / d2.norm()) < 2e-2, k        # an entry with a ~0 gradient may flip its Adam sign
     # and it is the reference's trajectory (recorded from its own trainer on the same HF modules)
     g = np.load(GOLDEN / f"{case}.npz")
     # (the golden run of this case used grad_accum 2 / 2 epochs / lr 1e-3 / no warm-up: only step 0's loss is comparable)
