@@ -282,13 +282,23 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = t.tolist()
 
+    dp = None
+    if world > 1:
+        # all-reduced gradient == mean of the per-rank gradients; parameters identical on every rank (tools/dp_check.py)
+        from tools.dp_check import dp_check
+        try:
+            dp = dp_check(eng, dev_batch, lc.pad_id, world)
+        except Exception as e:
+            dp = {"ok": False, "error": f"{type(e).__name__}: {e}"}
+
     # ---- roofline pass for the dominant kernel (gemm_bf16_kernel): CUDA events around every launch
     roof = None
     if rank == 0:
         ops.GEMM_PROFILE = []
         eng.use_graph = False
-        # rank-local pass (no collective: the other ranks do not take part in it)
-        eng.train_step(dev_batch, lr, pad_id=lc.pad_id, allreduce=None, world_size=1)
+        # rank-local pass (no collective: the other ranks do not take part in it) over the forward + backward only:
+        # every GEMM of the step is in it, and no optimizer step runs that the other ranks would not see
+        eng.forward_backward(px, ids, lab, lc.pad_id)
         torch.cuda.synchronize()
         prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
         fl = sum(p[0] for p in prof)
@@ -361,6 +371,8 @@ def run_ours(args):
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof,
             "step_tflops_per_gpu": ips / world * fpi / 1e12, "flops_per_image": fpi, "last_loss": lv}
+    if dp is not None:
+        line["dp_check"] = dp
     if parity is not None:
         line["parity"] = parity
     if configs is not None:
