@@ -27,13 +27,20 @@ constexpr int kGemm2Threads = 384;     // 4 control warps + 8 epilogue warps
 constexpr int kEpiWarps = 8;
 constexpr int kEpiStageBytes = 4096;   // per epilogue warp: 32 rows x 128 B
 constexpr int kSmemTotal = 232448;
+// internal activation code: the GeGLU-backward epilogue on the load/store unit (first version, kept as the A/B
+// reference: PT_GEMM_GBWD_TMA=0); PT_ACT_GEGLU_BWD itself moves its tiles with TMA
+constexpr int kActGbwdLsu = 100;
+// PT_ACT_GEGLU_BWD: per epilogue warp two TMA buffers of (gate 32 x 32 | up 32 x 32) bf16, 64-byte rows
+constexpr int kGbwdBufBytes = 4096;
+constexpr int kGbwdStageBytes = 2 * kGbwdBufBytes;
 
-template <int BN>
+template <int BN, int ACT = PT_ACT_NONE>
 struct Gemm2Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int EPI_BYTES = kEpiWarps * kEpiStageBytes;
+    static constexpr int EPI_WARP_BYTES = ACT == PT_ACT_GEGLU_BWD ? kGbwdStageBytes : kEpiStageBytes;
+    static constexpr int EPI_BYTES = kEpiWarps * EPI_WARP_BYTES;
     static constexpr int BAR_BYTES = 512;
     static constexpr int STAGES_RAW = (kSmemTotal - 1024 - EPI_BYTES - BAR_BYTES) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
@@ -271,8 +278,8 @@ __device__ __forceinline__ void epi_chunk_sbwd_pre(const uint32_t (&v)[32], uint
 template <int BN, int ACT>
 __global__ void __launch_bounds__(kGemm2Threads, 1)
 gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const GemmDev p) {
-    using Cfg = Gemm2Cfg<BN>;
+                  const __grid_constant__ CUtensorMap tmAux, const __grid_constant__ CUtensorMap tmC, const GemmDev p) {
+    using Cfg = Gemm2Cfg<BN, ACT>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int BNH = BN / 2;                 // B rows staged by each CTA
     constexpr int TM = 2 * BM;                  // tile rows per cluster
@@ -289,6 +296,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     uint64_t* tfull_bar = bars + 2 * STAGES;         // per CTA (multicast commit)
     uint64_t* tempty_bar = bars + 2 * STAGES + 2;    // leader's are the live ones
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    [[maybe_unused]] uint64_t* gbwd_bar = bars + 2 * STAGES + 5;     // [kEpiWarps][2]: TMA gate / up tiles landed
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -307,6 +315,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmB);
+        if constexpr (ACT == PT_ACT_GEGLU_BWD) { ptx::prefetch_tmap(&tmAux); ptx::prefetch_tmap(&tmC); }
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -317,6 +326,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             ptx::mbar_init(&tfull_bar[s], 1);
             ptx::mbar_init(&tempty_bar[s], 2 * kEpiWarps);
         }
+        if constexpr (ACT == PT_ACT_GEGLU_BWD)
+            for (int s = 0; s < 2 * kEpiWarps; ++s) ptx::mbar_init(&gbwd_bar[s], 1);
         ptx::fence_mbar_init();
     }
     ptx::cluster_sync_all();                      // peer barriers initialised before any remote signal
@@ -468,9 +479,11 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int ew = warp - 4;
         const int q = warp & 3;                 // TMEM lane quarter this warp may read
         const int hf = ew >> 2;                 // which half of the BN columns
-        const uint32_t stg = ptx::smem_u32(smem_epi + ew * kEpiStageBytes);
+        const uint32_t stg = ptx::smem_u32(smem_epi + ew * Cfg::EPI_WARP_BYTES);
         int acc = 0;
         uint32_t acc_phase = 0;
+        [[maybe_unused]] uint32_t gb_phase = 0;      // bit b: parity of this warp's TMA buffer b
+        [[maybe_unused]] bool gb_pref = false;       // chunk 0 of the tile at hand has been requested already
         for (int t = cid; t < total_tiles; t += ncl) {
             int m_blk, n_blk, z[3];
             decode(t, m_blk, n_blk, z);
@@ -486,7 +499,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int rows_valid = min(32, p.M - row0);                            // may be <= 0
             const int row_lo = max(0, m_blk * TM - row0);                          // rows below: previous tile's
 
-            if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+            if constexpr (ACT == kActGbwdLsu) {
                 // pull this warp's slab of the saved gate / up pre-activations into L2 while the tile's MMAs run
                 const int pr = row0 + lane;
                 if (pr < p.M && pr >= m_blk * TM) {
@@ -543,6 +556,104 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     sb_dl[it] = (r >= row_lo && r < rows_valid) ? __ldg(dbase + r) : 0.f;
                 }
                 sb_load(0, sb_pq);
+            }
+            if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+                // ---- GeGLU backward with TMA-moved tiles.  The accumulator chunk (d_act: lane = row, 32 columns)
+                // is used in the layout tcgen05.ld delivers; the saved gate / up tiles of the same 32 x 32 block
+                // arrive by TMA in a 64-byte-swizzled buffer (conflict-free 16-byte row reads), d_gate / d_up are
+                // written over them and leave by TMA store.  No transpose through smem, no global LD/ST
+                // instructions, no per-row address arithmetic: ~half the instructions of the LSU version, and the
+                // epilogue was what bounded this launch (22 k cycles per tile against 9.2 k of MMAs).
+                constexpr int NCHg = BNH / 32;
+                const bool live = row0 < p.M;                               // warp-uniform
+                uint8_t* wst = smem_epi + ew * Cfg::EPI_WARP_BYTES;
+                uint64_t* gb = gbwd_bar + 2 * ew;
+                auto request = [&](int buf, int r0, int c0) {               // lane 0: gate and up tile -> buffer buf
+                    ptx::mbar_arrive_expect_tx(&gb[buf], kGbwdBufBytes);
+                    ptx::tma_load_2d(&tmAux, &gb[buf], wst + buf * kGbwdBufBytes, c0, r0);
+                    ptx::tma_load_2d(&tmAux, &gb[buf], wst + buf * kGbwdBufBytes + kGbwdBufBytes / 2, c0 + p.ff, r0);
+                };
+                const int colb = tile_n + hf * BNH;
+                if (live && !gb_pref && lane == 0) {
+                    ptx::bulk_wait_read<0>();
+                    request(0, row0, colb);
+                }
+                ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+                ptx::tc_fence_after();
+                const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);
+                const GluConsts2 k2 = glu_consts2(p.glu);
+                const uint32_t sw = (lane >> 1) & 3;                        // SWIZZLE_64B: chunk ^= (row >> 1) & 3
+#pragma unroll 1
+                for (int c = 0; c < NCHg; ++c) {
+                    const int buf = c & 1;
+                    uint32_t v[32];
+                    if (live) {
+                        ptx::tmem_ld_32x32(taddr + hf * BNH + c * 32, v);
+                        if (lane == 0 && c + 1 < NCHg) {
+                            ptx::bulk_wait_read<0>();                       // chunk c-1's store has read buffer buf^1
+                            request(buf ^ 1, row0, colb + (c + 1) * 32);
+                        }
+                        ptx::mbar_wait(&gb[buf], (gb_phase >> buf) & 1u);
+                        gb_phase ^= 1u << buf;
+                        ptx::tmem_ld_wait();
+                    }
+                    if (c == NCHg - 1) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
+                    }
+                    if (!live) continue;
+                    const uint32_t ga = ptx::smem_u32(wst + buf * kGbwdBufBytes) + lane * 64, ua = ga + kGbwdBufBytes / 2;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {                           // 16-byte chunk j = columns 8 j .. 8 j + 7
+                        const uint32_t off = (static_cast<uint32_t>(j) ^ sw) << 4;
+                        const float4 gq = ptx::lds128(ga + off), uq = ptx::lds128(ua + off);
+                        const uint32_t gw[4] = {__float_as_uint(gq.x), __float_as_uint(gq.y), __float_as_uint(gq.z), __float_as_uint(gq.w)};
+                        const uint32_t uw[4] = {__float_as_uint(uq.x), __float_as_uint(uq.y), __float_as_uint(uq.z), __float_as_uint(uq.w)};
+                        uint32_t og[4], ou[4];
+#pragma unroll
+                        for (int w = 0; w < 4; ++w) {
+                            const uint64_t g2 = f2_pack(bf16_lo(gw[w]), bf16_hi(gw[w]));
+                            const uint64_t u2 = f2_pack(bf16_lo(uw[w]), bf16_hi(uw[w]));
+                            const uint64_t d2 = f2_pack(__uint_as_float(v[8 * j + 2 * w]), __uint_as_float(v[8 * j + 2 * w + 1]));
+                            uint64_t val, grad;
+                            glu_act_fast_both2(g2, k2, val, grad);
+                            float x0, x1;
+                            f2_unpack(f2_mul(f2_mul(d2, u2), grad), x0, x1);
+                            og[w] = pack_bf16(x0, x1);
+                            f2_unpack(f2_mul(d2, val), x0, x1);
+                            ou[w] = pack_bf16(x0, x1);
+                        }
+                        ptx::sts128(ga + off, og[0], og[1], og[2], og[3]);
+                        ptx::sts128(ua + off, ou[0], ou[1], ou[2], ou[3]);
+                    }
+                    ptx::fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::tma_store_2d(&tmC, wst + buf * kGbwdBufBytes, colb + c * 32, row0);
+                        ptx::tma_store_2d(&tmC, wst + buf * kGbwdBufBytes + kGbwdBufBytes / 2, colb + c * 32 + p.ff, row0);
+                        ptx::bulk_commit();
+                    }
+                }
+                // request the next tile's first chunk now: its L2 latency then overlaps that tile's hand-over
+                gb_pref = false;
+                if (t + ncl < total_tiles) {
+                    int m2, n2, z2[3];
+                    decode(t + ncl, m2, n2, z2);
+                    const int r2 = (m2 == mt - 1 ? p.m_last : m2 * TM) + static_cast<int>(rank) * BM + q * 32;
+                    const int c2 = (n2 == nt - 1 ? p.n_last : n2 * BN) + hf * BNH;
+                    if (r2 < p.M) {
+                        gb_pref = true;
+                        if (lane == 0) {
+                            // buffer 0 was last read by the store of the last even chunk: the most recent group
+                            // (odd last chunk -> buffer 1) may still be pending, nothing older
+                            if (((NCHg - 1) & 1) && live) ptx::bulk_wait_read<1>(); else ptx::bulk_wait_read<0>();
+                            request(0, r2, c2);
+                        }
+                    }
+                }
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+                continue;
             }
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             ptx::tc_fence_after();
@@ -634,7 +745,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     for (int it = 0; it < 8; ++it) sb_pq[it] = sb_pn[it];
                     continue;
                 }
-                if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+                if constexpr (ACT == kActGbwdLsu) {
                     EpiGbwd o;
                     o.c_row = p.ldc * 2; o.g_row = p.ld_aux * 2; o.ff_bytes = static_cast<long long>(p.ff) * 2;
                     o.C = static_cast<uint8_t*>(p.C) + (static_cast<long long>(row0) * p.ldc + col0) * 2;
@@ -666,6 +777,9 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
     }
 
+    if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+        if (warp >= 4 && lane == 0) ptx::bulk_wait_all<0>();     // this warp's TMA stores have been performed
+    }
     ptx::tc_fence_before();
     ptx::cluster_sync_all();
     if (warp == 2) {
@@ -676,9 +790,9 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
 // ---- host ----------------------------------------------------------------------------------------
 template <int BN, int ACT>
-static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, int tiles,
-                          cudaStream_t st) {
-    using Cfg = Gemm2Cfg<BN>;
+static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& t_aux,
+                          const CUtensorMap& t_c, const GemmDev& p, int tiles, cudaStream_t st) {
+    using Cfg = Gemm2Cfg<BN, ACT>;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(gemm2_bf16_kernel<BN, ACT>,
@@ -704,7 +818,7 @@ static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const Ge
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_bf16_kernel<BN, ACT>, ta, tb, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_bf16_kernel<BN, ACT>, ta, tb, t_aux, t_c, p);
     if (e != cudaSuccess) {
         set_error("gemm2_bf16_kernel<%d>: launch failed: %s", BN, cudaGetErrorString(e));
         return PT_ERR_CUDA;
@@ -718,19 +832,28 @@ int gemm2_tiles(const GemmDev& p, int bn) {
     return t < (1ll << 31) ? static_cast<int>(t) : -1;
 }
 
-int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st) {
+// PT_GEMM_GBWD_TMA=0: the first-generation (load/store unit) GeGLU-backward epilogue, for A/B probes
+static int gbwd_tma_enabled() {
+    static const int v = [] { const char* e = getenv("PT_GEMM_GBWD_TMA"); return !(e && e[0] == '0'); }();
+    return v;
+}
+
+int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& t_aux, const CUtensorMap& t_c,
+                 const GemmDev& p, cudaStream_t st) {
     const int tiles = gemm2_tiles(p, bn);
     if (tiles <= 0) { set_error("gemm2: bad tile count"); return PT_ERR_INVALID; }
 #define PT_G2(BN_)                                                                      \
     case BN_:                                                                           \
-        if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, p, tiles, st); \
-        if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, p, tiles, st);   \
-        if (p.act == PT_ACT_GEGLU_BWD) return launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, p, tiles, st); \
-        if (p.act == PT_ACT_SOFTMAX_BWD) return launch_gemm2_t<BN_, PT_ACT_SOFTMAX_BWD>(ta, tb, p, tiles, st); \
-        return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, p, tiles, st);
+        if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, t_aux, t_c, p, tiles, st); \
+        if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, t_aux, t_c, p, tiles, st);   \
+        if (p.act == PT_ACT_GEGLU_BWD)                                                                      \
+            return gbwd_tma_enabled() ? launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, t_aux, t_c, p, tiles, st) \
+                                      : launch_gemm2_t<BN_, kActGbwdLsu>(ta, tb, t_aux, t_c, p, tiles, st);  \
+        if (p.act == PT_ACT_SOFTMAX_BWD) return launch_gemm2_t<BN_, PT_ACT_SOFTMAX_BWD>(ta, tb, t_aux, t_c, p, tiles, st); \
+        return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, t_aux, t_c, p, tiles, st);
     if (p.act == PT_ACT_GEGLU) {
         if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }
-        return launch_gemm2_t<256, PT_ACT_GEGLU>(ta, tb, p, tiles, st);
+        return launch_gemm2_t<256, PT_ACT_GEGLU>(ta, tb, t_aux, t_c, p, tiles, st);
     }
     switch (bn) {
         PT_G2(256) PT_G2(192) PT_G2(128) PT_G2(64)

@@ -79,8 +79,15 @@ int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, i
                    const int ext[3], const long long est[3], int rows_box, const char* name);
 int encode_tiled_bf16_5d(CUtensorMap* out, const void* base, const unsigned long long dims[5],
                          const unsigned long long strides_bytes[4], const unsigned int box[5], const char* name);
-// CTA-pair kernel (gemm2_sm100.cu): bn in {64,128,192,256}; tensor map of B must use box rows bn/2
-int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st);
+// row-major bf16 matrix [rows, cols] with row stride ld (elements) as a 2-D map; box = box_cols x box_rows;
+// swizzle_bytes in {0, 64, 128} (box_cols * 2 must equal it when non-zero)
+int encode_tiled_bf16_2d(CUtensorMap* out, const void* base, long long cols, long long rows, long long ld,
+                         int box_cols, int box_rows, int swizzle_bytes, const char* name);
+// CTA-pair kernel (gemm2_sm100.cu): bn in {64,128,192,256}; tensor map of B must use box rows bn/2.
+// t_aux / t_c: 2-D maps (32 x 32 boxes, 64-byte swizzle) of the aux matrix and of C for the epilogues that move their
+// tiles with TMA (PT_ACT_GEGLU_BWD); any valid map otherwise (unused).
+int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& t_aux, const CUtensorMap& t_c,
+                 const GemmDev& p, cudaStream_t st);
 int gemm2_tiles(const GemmDev& p, int bn);
 
 }  // namespace pt

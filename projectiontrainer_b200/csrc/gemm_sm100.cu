@@ -374,6 +374,26 @@ int encode_operand(CUtensorMap* out, const void* base, int mn_major, int rows, i
 }
 
 // Generic 5-D bf16 tiled map with 128-byte swizzle (attention kernels build their own geometries).
+int encode_tiled_bf16_2d(CUtensorMap* out, const void* base, long long cols, long long rows, long long ld,
+                         int box_cols, int box_rows, int swizzle_bytes, const char* name) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return PT_ERR_CUDA; }
+    cuuint64_t d[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t st[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t bx[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)}, es[2] = {1, 1};
+    const CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                  : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE;
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), d, st, bx, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(%s) failed: CUresult %d (dims %lld %lld, ld %lld, box %d %d, swizzle %d)", name,
+                  static_cast<int>(r), cols, rows, ld, box_cols, box_rows, swizzle_bytes);
+        return PT_ERR_CUDA;
+    }
+    return PT_OK;
+}
+
 int encode_tiled_bf16_5d(CUtensorMap* out, const void* base, const unsigned long long dims[5],
                          const unsigned long long strides_bytes[4], const unsigned int box[5], const char* name) {
     EncodeTiledFn enc = get_encode_fn();
@@ -570,7 +590,15 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         if (rc != PT_OK) return rc;
         rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn / 2, "B");
         if (rc != PT_OK) return rc;
-        return launch_gemm2(bn, ta, tb, p, st);
+        CUtensorMap t_aux = ta, t_c = ta;
+        if (geglu_bwd) {
+            // the GeGLU-backward epilogue moves its gate / up tiles in and its d_gate / d_up tiles out with TMA
+            rc = encode_tiled_bf16_2d(&t_aux, a->aux, 2ll * p.ff, a->M, a->ld_aux, 32, 32, 64, "gu (epilogue)");
+            if (rc != PT_OK) return rc;
+            rc = encode_tiled_bf16_2d(&t_c, a->C, 2ll * p.ff, a->M, a->ldc, 32, 32, 64, "d_gu (epilogue)");
+            if (rc != PT_OK) return rc;
+        }
+        return launch_gemm2(bn, ta, tb, t_aux, t_c, p, st);
     }
     const int bn = pick_bn(a->M, a->N, nbatch);
     const long long tiles_ll = static_cast<long long>((a->M + BM - 1) / BM) * ((a->N + bn - 1) / bn) * nbatch;
