@@ -139,10 +139,6 @@ typedef struct {
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);
-/* Kernel selection for pt_gemm_bf16: 0 = default (CTA-pair tcgen05.mma.cta_group::2 kernel),
- * 1 = single-CTA kernel, 2 = CTA-pair kernel.  Test / profiling aid; results are identical in value
- * up to fp32 summation order (same K order: bit-identical accumulators). */
-int pt_set_gemm_impl(int impl);
 
 
 /* ------------------------------------------------------------------------- *
@@ -243,10 +239,6 @@ int pt_attn_delta(const void* dO_bf16, const void* O_bf16, float* delta, int row
  * tcgen05 flash-style kernel (96-key K/V tiles streamed by TMA, online softmax with lazy rescale, two CTAs
  * per SM); requires hd == 64, any N. */
 int pt_attn_siglip_fwd(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale, void* stream);
-/* First-generation kernel (K/V of a whole (image, head) resident in shared memory, one CTA per SM; N <= 576):
- * kept as a cross-check for the tests. */
-int pt_attn_siglip_fwd_v1(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale,
-                          void* stream);
 
 /* GeGLU: act = gelu_tanh(g) * u with gu = [g | u] per row — HF:models/gemma3/modeling_gemma3.py:127-129. */
 int pt_geglu_fwd(const void* gu, void* act, long long rows, int ff, void* stream);

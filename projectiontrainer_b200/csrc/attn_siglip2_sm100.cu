@@ -1,9 +1,8 @@
 // Fused non-causal attention forward for the SigLIP tower, second generation (head_dim 64):
 //     O[b, q, h, :] = softmax(Q K^T * scale) V        HF:models/siglip/modeling_siglip.py:293-306
 //
-// The first kernel (attn_siglip_sm100.cu) keeps K/V of a whole (image, head) resident in smem, which costs
-// 224 KB and therefore one CTA (one softmax warpgroup) per SM: tensor pipe and softmax warps take turns and
-// the kernel sits at ~190 TFLOP/s.  Here K/V tiles of 96 keys stream through a TMA ring (3 K stages, 2 V stages) (they are
+// (A first version kept K/V of a whole (image, head) resident in smem: 224 KB, hence one CTA — one softmax
+// warpgroup — per SM; tensor pipe and softmax warps took turns at ~190 TFLOP/s.)  Here K/V tiles of 96 keys stream through a TMA ring (3 K stages, 2 V stages) (they are
 // L2 hits: 144 KB per (image, head), re-read once per 128-row query block), smem drops to ~109 KB and TMEM to
 // 256 columns, so TWO CTAs are co-resident per SM and one CTA's softmax overlaps the other's MMAs.
 //
@@ -285,9 +284,6 @@ attn_siglip2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
 }  // namespace pt
 
 using namespace pt;
-
-extern "C" int pt_attn_siglip_fwd_v1(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale,
-                                     void* stream);
 
 extern "C" int pt_attn_siglip_fwd(const void* qkv_bf16, void* out_bf16, int B, int N, int H, int hd, float scale,
                                   void* stream) {

@@ -4,7 +4,8 @@
     -> input-gradient-only backward -> projector wgrads -> clip + AdamW
 
 mirroring ref:Stage1/projector_trainer.py:152-245.  torch supplies device memory and
-streams only; no torch math runs on the hot path and there is no CPU fallback.
+streams; all arithmetic of the step runs in the sm_100a kernels (what torch does on the step path is plumbing: one
+buffer zero-fill, an int32 target copy, KV-cache slot copies) and there is no CPU fallback.
 
 Numerics (bf16 mode = what `accelerate launch --mixed_precision bf16` gives the reference):
 bf16 GEMM operands with fp32 accumulation, fp32 residual streams, fp32 norm / softmax /
@@ -23,6 +24,26 @@ from .config import GemmaCfg, SiglipCfg
 from .ops import ACT_GELU_ERF, ACT_GELU_TANH
 
 BF16, F32 = torch.bfloat16, torch.float32
+
+# NVTX ranges per phase of the step (off by default: PT_STAGE1_NVTX=1 turns them on for nsys / ncu --nvtx timelines)
+_NVTX = os.environ.get("PT_STAGE1_NVTX", "0") != "0"
+
+
+class _phase:
+    """`with _phase("llm_backward"):` — an NVTX range when PT_STAGE1_NVTX=1, nothing otherwise."""
+    __slots__ = ("name",)
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if _NVTX:
+            torch.cuda.nvtx.range_push("stage1/" + self.name)
+
+    def __exit__(self, *exc):
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
+        return False
 
 
 def _pad8(n: int) -> int:
@@ -692,13 +713,19 @@ class Stage1Engine:
         S = self.n_img + T
         lab0, Tl = self._span(T, label_span)
         h = self.lcfg.hidden
-        patch = self.vision_forward(pixels)
+        with _phase("vision_forward"):
+            patch = self.vision_forward(pixels)
         x0 = self.buf("x0", (B * S, h), F32)
-        Z, Hm = self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * h)
-        _, _, keyvalid, targets = self.splice(token_ids, labels, x0, pad_id)
-        loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, Tl, lab0=lab0)
-        dx = self.llm_backward()
-        self.projector_backward(dx, patch, Z, Hm, B, S)
+        with _phase("projector_forward"):
+            Z, Hm = self.projector_forward(patch, x0, rows_per_img=self.n_img, out_batch_stride=S * h)
+        with _phase("splice"):
+            _, _, keyvalid, targets = self.splice(token_ids, labels, x0, pad_id)
+        with _phase("llm_forward_loss"):
+            loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, Tl, lab0=lab0)
+        with _phase("llm_backward"):
+            dx = self.llm_backward()
+        with _phase("projector_backward"):
+            self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
 
     def preprocess_images(self, images, out: torch.Tensor | None = None, *, mean=(0.5, 0.5, 0.5),
@@ -1193,8 +1220,10 @@ class Stage1Engine:
             Pj.grad.add_(self._acc_grad)
             self._acc_pending = False
         if allreduce is not None and world_size > 1:
-            allreduce(Pj.grad)
-        self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size, max_norm=max_norm)
+            with _phase("grad_allreduce"):
+                allreduce(Pj.grad)
+        with _phase("clip_adamw"):
+            self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size, max_norm=max_norm)
         return loss
 
 

@@ -91,11 +91,6 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     _lib.call("pt_gemm_bf16", C.byref(g), _stream())
 
 
-def set_gemm_impl(impl: int) -> None:
-    """0 = default (CTA-pair kernel), 1 = single-CTA kernel, 2 = CTA-pair kernel (tests / profiling)."""
-    _lib.check(_lib.lib().pt_set_gemm_impl(int(impl)), "pt_set_gemm_impl")
-
-
 def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residual=None,
            out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0) -> torch.Tensor:
     """y[M,N] = act(x[M,K] @ w[N,K]^T + bias) (+ residual).  x, w bf16 row-major 2-D."""
@@ -236,10 +231,10 @@ def qknorm_rope_bwd(dq, dk, qkv, wq, wk, cos_t, sin_t, d_qkv, S, hq, hkv, hd, ep
               _ptr(sin_t), _ptr(d_qkv), qkv.shape[0], int(S), hq, hkv, hd, _f(eps), _stream())
 
 
-def attn_siglip_fwd(qkv, out, B, N, H, hd, scale, v1=False):
+def attn_siglip_fwd(qkv, out, B, N, H, hd, scale):
     """Fused non-causal attention over the fused qkv activation [B*N, 3*H*hd] -> out [B*N, H*hd]."""
     _req_cuda(qkv, out)
-    _lib.call("pt_attn_siglip_fwd_v1" if v1 else "pt_attn_siglip_fwd", _ptr(qkv), _ptr(out), int(B), int(N), int(H), int(hd), _f(scale), _stream())
+    _lib.call("pt_attn_siglip_fwd", _ptr(qkv), _ptr(out), int(B), int(N), int(H), int(hd), _f(scale), _stream())
 
 
 def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, window):

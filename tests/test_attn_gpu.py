@@ -5,19 +5,16 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("v1", [False, True], ids=["streamed_kv", "resident_kv"])
 @pytest.mark.parametrize("B,N,H,amp", [(2, 576, 16, 1.5), (3, 100, 2, 1.5), (1, 193, 3, 1.5), (2, 384, 4, 1.5),
                                        (1, 9, 1, 1.5), (40, 576, 16, 1.5), (2, 576, 4, 6.0), (2, 1000, 2, 3.0)])
-def test_attn_siglip_fwd(cuda_dev, B, N, H, amp, v1):
+def test_attn_siglip_fwd(cuda_dev, B, N, H, amp):
     """amp = 6 drives score ranges far past the lazy-rescale threshold (row max grows by > 2^8 between tiles)."""
     from projectiontrainer_b200 import ops
-    if v1 and N > 576:
-        pytest.skip("first-generation kernel holds at most 576 keys")
     torch.manual_seed(N + H)
     hd, d = 64, H * 64
     qkv = (torch.randn(B * N, 3 * d, device=cuda_dev) * amp).to(torch.bfloat16)
     out = torch.full((B * N, d), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
-    ops.attn_siglip_fwd(qkv, out, B, N, H, hd, hd ** -0.5, v1=v1)
+    ops.attn_siglip_fwd(qkv, out, B, N, H, hd, hd ** -0.5)
     torch.cuda.synchronize()
     q, k, v = (t.reshape(B, N, H, hd).transpose(1, 2) for t in qkv.float().split(d, dim=1))
     ref = torch.softmax(q @ k.transpose(-1, -2) * hd ** -0.5, dim=-1) @ v

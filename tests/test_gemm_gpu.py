@@ -5,15 +5,6 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=[2, 1], ids=["cta_pair", "single_cta"])
-def gemm_impl(request):
-    """Every case runs on both tensor-core kernels behind pt_gemm_bf16 (2 = the default CTA-pair kernel)."""
-    from projectiontrainer_b200 import ops
-    ops.set_gemm_impl(request.param)
-    yield request.param
-    ops.set_gemm_impl(0)
-
-
 def _rand(shape, dev, scale=1.0):
     return (torch.randn(shape, device=dev, dtype=torch.float32) * scale).to(torch.bfloat16)
 
@@ -77,11 +68,9 @@ def test_gemm_dgrad_mn_major_b(cuda_dev, M, N, K):
 
 @pytest.mark.parametrize("M,V,h,S", [(64, 512, 64, 8), (300, 4096, 328, 4), (1000, 16384, 1152, 8),
                                      (24, 2048, 256, 2)])
-def test_gemm_dgrad_split_k(cuda_dev, gemm_impl, M, V, h, S):
+def test_gemm_dgrad_split_k(cuda_dev, M, V, h, S):
     """LM-head input gradient as a split-K launch (K slices as a batch dim, f32 partials) + pt_sum_slices:
     same result as the single launch, and both match the f32 matmul."""
-    if gemm_impl != 2:
-        pytest.skip("bn_hint addresses the CTA-pair kernel")
     from projectiontrainer_b200 import ops
     torch.manual_seed(V + h)
     Vp = V + 8                                  # padded row stride, as the engine's logits buffer has
@@ -157,12 +146,10 @@ def test_gemm_grouped_contraction(cuda_dev):
 
 
 @pytest.mark.parametrize("M,ff,h", [(700, 384, 192), (22496, 6912, 1152), (64, 128, 64), (3, 256, 128)])
-def test_gemm_fused_geglu_fwd_bwd(cuda_dev, gemm_impl, M, ff, h):
+def test_gemm_fused_geglu_fwd_bwd(cuda_dev, M, ff, h):
     """GeGLU fused into the gate||up epilogue and its backward fused into the down-dgrad epilogue, against
     the unfused kernels (same bf16 rounding points) and a torch fp32 reference."""
     from projectiontrainer_b200 import ops
-    if gemm_impl == 1:
-        pytest.skip("fused GeGLU epilogues exist in the CTA-pair kernel only")
     torch.manual_seed(M + ff)
     x, w_gu = _rand((M, h), cuda_dev), _rand((2 * ff, h), cuda_dev, 0.08)
     gu = torch.empty(M, 2 * ff, device=cuda_dev, dtype=torch.bfloat16)
@@ -226,12 +213,10 @@ def test_gemm_attention_bands_skip_only_masked_work(cuda_dev, S, W):
 
 
 @pytest.mark.parametrize("S,W", [(703, 0), (703, 512), (90, 16)])
-def test_gemm_fused_softmax_backward_epilogue(cuda_dev, gemm_impl, S, W):
+def test_gemm_fused_softmax_backward_epilogue(cuda_dev, S, W):
     """dS = scale * P * (dO V^T - delta) in the GEMM epilogue (delta = rowsum(dO * O)) vs torch autograd
     through softmax(QK^T * scale) V on the same bf16-rounded tensors."""
     from projectiontrainer_b200 import ops
-    if gemm_impl == 1:
-        pytest.skip("fused softmax-backward epilogue exists in the CTA-pair kernel only")
     torch.manual_seed(S + W)
     Bn, hq, hd, scale = 2, 2, 64, 0.125
     ld = (S + 7) // 8 * 8

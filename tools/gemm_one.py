@@ -20,7 +20,6 @@ w = (torch.randn(K, N, device=dev) * 0.05).to(torch.bfloat16) if a.bmn else (tor
 out = torch.empty(M, N, device=dev, dtype=torch.float32 if a.f32 else torch.bfloat16)
 bias = torch.randn(N, device=dev) if a.bias else None
 res = out if a.res else None
-ops.set_gemm_impl(a.impl)
 def run():
     ops.gemm_raw(M=M, N=N, K=K, A=x, lda=K, B=w, ldb=w.stride(0), b_mn=a.bmn, Cout=out, ldc=N, bias=bias,
                  residual=res, ldr=N, act=a.act, bn_hint=a.bn)
