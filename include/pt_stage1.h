@@ -52,7 +52,17 @@ typedef enum {
     /* PT_ACT_GEGLU / PT_ACT_GEGLU_BWD with SiLU in place of tanh-GELU: the SwiGLU MLP of the Qwen3 decoder
      * (HF:models/qwen3/modeling_qwen3.py Qwen3MLP: down(silu(gate) * up)); same operands and layout. */
     PT_ACT_SWIGLU = 6,
-    PT_ACT_SWIGLU_BWD = 7
+    PT_ACT_SWIGLU_BWD = 7,
+    /* Backward of nn.GELU() (ref:Stage1/projectors.py:18) fused into the projector's second-layer input gradient:
+     * the accumulator is dH [M, N]; aux = the saved pre-activations Z [M, N] bf16 (row stride ld_aux, read only);
+     * C [M, N] bf16 receives dH * gelu_erf'(Z) (exact erf).  Not batched; N % 32 == 0. */
+    PT_ACT_GELU_ERF_BWD = 8,
+    /* delta = rowsum(dO * O) of the attention backward fused into the o-projection input gradient: the accumulator
+     * is dO [M = B*S, N = hq*hd]; aux = the attention output O, bf16, same shape (row stride ld_aux); C (bf16)
+     * receives dO and aux2 (f32 [B*hq, S], zero-filled by pt_gemm_bf16 itself) receives
+     * delta[(b*hq + head)*S + s] = sum_d bf16(dO[b*S+s, head*hd + d]) * O[...], with S = aux_i0, hd = aux_i1
+     * (hd % 128 == 0, N % 256 == 0).  Replaces pt_attn_delta + one read of dO and O. */
+    PT_ACT_ATTN_DELTA = 9
 } pt_act;
 
 typedef enum {
@@ -136,6 +146,9 @@ typedef struct {
     /* Output-tile width override for the CTA-pair kernel: 0 = cost model, else 64 / 128 / 192 / 256 (a tuning
      * hint for few-tile problems whose last wave would leave most clusters idle; results do not depend on it). */
     int32_t bn_hint;
+    /* PT_ACT_ATTN_DELTA only (see pt_act): f32 output [B*hq, S], sequence length, head dim; NULL / 0 otherwise. */
+    void* aux2;
+    int32_t aux_i0, aux_i1;
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);

@@ -30,16 +30,20 @@ constexpr int kSmemTotal = 232448;
 // internal activation code: the GeGLU-backward epilogue on the load/store unit (first version, kept as the A/B
 // reference: PT_GEMM_GBWD_TMA=0); PT_ACT_GEGLU_BWD itself moves its tiles with TMA
 constexpr int kActGbwdLsu = 100;
-// PT_ACT_GEGLU_BWD: per epilogue warp two TMA buffers of (gate 32 x 32 | up 32 x 32) bf16, 64-byte rows
+// Epilogues that move their tiles with TMA (tma_epilogue(ACT)): per epilogue warp two buffers of up to two 32 x 32
+// bf16 tiles (PT_ACT_GEGLU_BWD: gate | up), 64-byte rows, SWIZZLE_64B
 constexpr int kGbwdBufBytes = 4096;
 constexpr int kGbwdStageBytes = 2 * kGbwdBufBytes;
+__host__ __device__ constexpr bool tma_epilogue(int act) {
+    return act == PT_ACT_GEGLU_BWD || act == PT_ACT_GELU_ERF_BWD || act == PT_ACT_ATTN_DELTA;
+}
 
 template <int BN, int ACT = PT_ACT_NONE>
 struct Gemm2Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int EPI_WARP_BYTES = ACT == PT_ACT_GEGLU_BWD ? kGbwdStageBytes : kEpiStageBytes;
+    static constexpr int EPI_WARP_BYTES = tma_epilogue(ACT) ? kGbwdStageBytes : kEpiStageBytes;
     static constexpr int EPI_BYTES = kEpiWarps * EPI_WARP_BYTES;
     static constexpr int BAR_BYTES = 512;
     static constexpr int STAGES_RAW = (kSmemTotal - 1024 - EPI_BYTES - BAR_BYTES) / STAGE_BYTES;
@@ -315,7 +319,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmB);
-        if constexpr (ACT == PT_ACT_GEGLU_BWD) { ptx::prefetch_tmap(&tmAux); ptx::prefetch_tmap(&tmC); }
+        if constexpr (tma_epilogue(ACT)) { ptx::prefetch_tmap(&tmAux); ptx::prefetch_tmap(&tmC); }
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -326,7 +330,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             ptx::mbar_init(&tfull_bar[s], 1);
             ptx::mbar_init(&tempty_bar[s], 2 * kEpiWarps);
         }
-        if constexpr (ACT == PT_ACT_GEGLU_BWD)
+        if constexpr (tma_epilogue(ACT))
             for (int s = 0; s < 2 * kEpiWarps; ++s) ptx::mbar_init(&gbwd_bar[s], 1);
         ptx::fence_mbar_init();
     }
@@ -557,21 +561,23 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 }
                 sb_load(0, sb_pq);
             }
-            if constexpr (ACT == PT_ACT_GEGLU_BWD) {
-                // ---- GeGLU backward with TMA-moved tiles.  The accumulator chunk (d_act: lane = row, 32 columns)
-                // is used in the layout tcgen05.ld delivers; the saved gate / up tiles of the same 32 x 32 block
-                // arrive by TMA in a 64-byte-swizzled buffer (conflict-free 16-byte row reads), d_gate / d_up are
-                // written over them and leave by TMA store.  No transpose through smem, no global LD/ST
-                // instructions, no per-row address arithmetic: ~half the instructions of the LSU version, and the
-                // epilogue was what bounded this launch (22 k cycles per tile against 9.2 k of MMAs).
+            if constexpr (tma_epilogue(ACT)) {
+                // ---- Epilogues with TMA-moved tiles (GeGLU backward; erf-GELU backward; attention delta).  The
+                // accumulator chunk (lane = row, 32 columns) is used in the layout tcgen05.ld delivers; the saved
+                // tile(s) of the same 32 x 32 block (gate and up / Z / O) arrive by TMA in a 64-byte-swizzled buffer
+                // (conflict-free 16-byte row reads), the results are written over them and leave by TMA store.  No
+                // transpose through smem, no global LD/ST instructions, no per-row address arithmetic: about half
+                // the instructions of the load/store-unit version of the GeGLU backward (165 -> 114 registers).
                 constexpr int NCHg = BNH / 32;
+                constexpr int NT = ACT == PT_ACT_GEGLU_BWD ? 2 : 1;         // tiles per chunk (in and out)
                 const bool live = row0 < p.M;                               // warp-uniform
                 uint8_t* wst = smem_epi + ew * Cfg::EPI_WARP_BYTES;
                 uint64_t* gb = gbwd_bar + 2 * ew;
-                auto request = [&](int buf, int r0, int c0) {               // lane 0: gate and up tile -> buffer buf
-                    ptx::mbar_arrive_expect_tx(&gb[buf], kGbwdBufBytes);
+                auto request = [&](int buf, int r0, int c0) {               // lane 0: saved tile(s) -> buffer buf
+                    ptx::mbar_arrive_expect_tx(&gb[buf], NT * (kGbwdBufBytes / 2));
                     ptx::tma_load_2d(&tmAux, &gb[buf], wst + buf * kGbwdBufBytes, c0, r0);
-                    ptx::tma_load_2d(&tmAux, &gb[buf], wst + buf * kGbwdBufBytes + kGbwdBufBytes / 2, c0 + p.ff, r0);
+                    if constexpr (NT == 2)
+                        ptx::tma_load_2d(&tmAux, &gb[buf], wst + buf * kGbwdBufBytes + kGbwdBufBytes / 2, c0 + p.ff, r0);
                 };
                 const int colb = tile_n + hf * BNH;
                 if (live && !gb_pref && lane == 0) {
@@ -581,7 +587,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 ptx::mbar_wait(&tfull_bar[acc], acc_phase);
                 ptx::tc_fence_after();
                 const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + (static_cast<uint32_t>(q * 32) << 16);
-                const GluConsts2 k2 = glu_consts2(p.glu);
+                [[maybe_unused]] const GluConsts2 k2 = glu_consts2(p.glu);
+                [[maybe_unused]] float dsum = 0.f;
                 const uint32_t sw = (lane >> 1) & 3;                        // SWIZZLE_64B: chunk ^= (row >> 1) & 3
 #pragma unroll 1
                 for (int c = 0; c < NCHg; ++c) {
@@ -607,32 +614,60 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {                           // 16-byte chunk j = columns 8 j .. 8 j + 7
                         const uint32_t off = (static_cast<uint32_t>(j) ^ sw) << 4;
-                        const float4 gq = ptx::lds128(ga + off), uq = ptx::lds128(ua + off);
+                        const float4 gq = ptx::lds128(ga + off);
                         const uint32_t gw[4] = {__float_as_uint(gq.x), __float_as_uint(gq.y), __float_as_uint(gq.z), __float_as_uint(gq.w)};
-                        const uint32_t uw[4] = {__float_as_uint(uq.x), __float_as_uint(uq.y), __float_as_uint(uq.z), __float_as_uint(uq.w)};
-                        uint32_t og[4], ou[4];
+                        uint32_t og[4];
+                        if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+                            const float4 uq = ptx::lds128(ua + off);
+                            const uint32_t uw[4] = {__float_as_uint(uq.x), __float_as_uint(uq.y), __float_as_uint(uq.z), __float_as_uint(uq.w)};
+                            uint32_t ou[4];
 #pragma unroll
-                        for (int w = 0; w < 4; ++w) {
-                            const uint64_t g2 = f2_pack(bf16_lo(gw[w]), bf16_hi(gw[w]));
-                            const uint64_t u2 = f2_pack(bf16_lo(uw[w]), bf16_hi(uw[w]));
-                            const uint64_t d2 = f2_pack(__uint_as_float(v[8 * j + 2 * w]), __uint_as_float(v[8 * j + 2 * w + 1]));
-                            uint64_t val, grad;
-                            glu_act_fast_both2(g2, k2, val, grad);
-                            float x0, x1;
-                            f2_unpack(f2_mul(f2_mul(d2, u2), grad), x0, x1);
-                            og[w] = pack_bf16(x0, x1);
-                            f2_unpack(f2_mul(d2, val), x0, x1);
-                            ou[w] = pack_bf16(x0, x1);
+                            for (int w = 0; w < 4; ++w) {
+                                const uint64_t g2 = f2_pack(bf16_lo(gw[w]), bf16_hi(gw[w]));
+                                const uint64_t u2 = f2_pack(bf16_lo(uw[w]), bf16_hi(uw[w]));
+                                const uint64_t d2 = f2_pack(__uint_as_float(v[8 * j + 2 * w]), __uint_as_float(v[8 * j + 2 * w + 1]));
+                                uint64_t val, grad;
+                                glu_act_fast_both2(g2, k2, val, grad);
+                                float x0, x1;
+                                f2_unpack(f2_mul(f2_mul(d2, u2), grad), x0, x1);
+                                og[w] = pack_bf16(x0, x1);
+                                f2_unpack(f2_mul(d2, val), x0, x1);
+                                ou[w] = pack_bf16(x0, x1);
+                            }
+                            ptx::sts128(ua + off, ou[0], ou[1], ou[2], ou[3]);
+                        } else if constexpr (ACT == PT_ACT_GELU_ERF_BWD) {
+                            // dZ = dH * gelu_erf'(Z): backward of nn.GELU() (ref:Stage1/projectors.py:18), exact erf
+#pragma unroll
+                            for (int w = 0; w < 4; ++w)
+                                og[w] = pack_bf16(__uint_as_float(v[8 * j + 2 * w]) * gelu_erf_grad_f(bf16_lo(gw[w])),
+                                                  __uint_as_float(v[8 * j + 2 * w + 1]) * gelu_erf_grad_f(bf16_hi(gw[w])));
+                        } else {
+                            // dO tile as bf16 + this row's share of delta = sum_d dO[d] * O[d] (on the rounded dO, as
+                            // pt_attn_delta computes it)
+#pragma unroll
+                            for (int w = 0; w < 4; ++w) {
+                                og[w] = pack_bf16(__uint_as_float(v[8 * j + 2 * w]), __uint_as_float(v[8 * j + 2 * w + 1]));
+                                dsum = fmaf(bf16_lo(og[w]), bf16_lo(gw[w]), dsum);
+                                dsum = fmaf(bf16_hi(og[w]), bf16_hi(gw[w]), dsum);
+                            }
                         }
                         ptx::sts128(ga + off, og[0], og[1], og[2], og[3]);
-                        ptx::sts128(ua + off, ou[0], ou[1], ou[2], ou[3]);
                     }
                     ptx::fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
                         ptx::tma_store_2d(&tmC, wst + buf * kGbwdBufBytes, colb + c * 32, row0);
-                        ptx::tma_store_2d(&tmC, wst + buf * kGbwdBufBytes + kGbwdBufBytes / 2, colb + c * 32 + p.ff, row0);
+                        if constexpr (NT == 2)
+                            ptx::tma_store_2d(&tmC, wst + buf * kGbwdBufBytes + kGbwdBufBytes / 2, colb + c * 32 + p.ff, row0);
                         ptx::bulk_commit();
+                    }
+                }
+                if constexpr (ACT == PT_ACT_ATTN_DELTA) {
+                    // this warp covered BNH columns of one head (hd % BNH == 0): add the row's partial to delta[b, head, s]
+                    const int r = row0 + lane;
+                    if (live && r < p.M && r >= m_blk * TM) {               // (rows a shifted last tile repeats: counted once)
+                        const int bb = r / p.dl_S, ss = r - bb * p.dl_S, head = colb / p.dl_hd;
+                        atomicAdd(p.delta + (static_cast<long long>(bb) * p.dl_hq + head) * p.dl_S + ss, dsum);
                     }
                 }
                 // request the next tile's first chunk now: its L2 latency then overlaps that tile's hand-over
@@ -777,7 +812,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
     }
 
-    if constexpr (ACT == PT_ACT_GEGLU_BWD) {
+    if constexpr (tma_epilogue(ACT)) {
         if (warp >= 4 && lane == 0) ptx::bulk_wait_all<0>();     // this warp's TMA stores have been performed
     }
     ptx::tc_fence_before();
@@ -850,6 +885,8 @@ int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUt
             return gbwd_tma_enabled() ? launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, t_aux, t_c, p, tiles, st) \
                                       : launch_gemm2_t<BN_, kActGbwdLsu>(ta, tb, t_aux, t_c, p, tiles, st);  \
         if (p.act == PT_ACT_SOFTMAX_BWD) return launch_gemm2_t<BN_, PT_ACT_SOFTMAX_BWD>(ta, tb, t_aux, t_c, p, tiles, st); \
+        if (p.act == PT_ACT_GELU_ERF_BWD) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF_BWD>(ta, tb, t_aux, t_c, p, tiles, st); \
+        if (p.act == PT_ACT_ATTN_DELTA) return launch_gemm2_t<BN_, PT_ACT_ATTN_DELTA>(ta, tb, t_aux, t_c, p, tiles, st); \
         return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, t_aux, t_c, p, tiles, st);
     if (p.act == PT_ACT_GEGLU) {
         if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }

@@ -40,6 +40,9 @@ struct GemmDev {
     long long ld_aux;
     int ff;
     GluConsts glu;    // activation of the fused gated-unit epilogues (tanh-GELU or SiLU)
+    // PT_ACT_ATTN_DELTA: delta [B*hq, S] f32 (zeroed by the host wrapper), row r = b * dl_S + s, head = column / dl_hd
+    float* delta;
+    int dl_S, dl_hd, dl_hq;
     // causal / sliding-window band of self-attention products (pt_gemm_args.band): work that only meets
     // masked (query, key) pairs is not issued.  band_w = window (0: unbounded below).
     int band, band_w;

@@ -178,7 +178,21 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     }
     PT_REQUIRE((a->N % 4) == 0 || ((!a->bias || a->act == PT_ACT_SOFTMAX_BWD) && !a->residual && !a->C_pre),
                "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
-    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_SWIGLU_BWD, "pt_gemm_bf16: bad act %d", a->act);
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_ATTN_DELTA, "pt_gemm_bf16: bad act %d", a->act);
+    const bool tile_epi = a->act == PT_ACT_GELU_ERF_BWD || a->act == PT_ACT_ATTN_DELTA;
+    if (tile_epi) {
+        PT_REQUIRE(a->aux != nullptr && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0 && a->ld_aux % 8 == 0 &&
+                       a->ld_aux >= a->N, "pt_gemm_bf16: act %d needs a 16B-aligned aux matrix [M, N] with ld_aux %% 8 == 0", a->act);
+        PT_REQUIRE(a->c_dtype == PT_BF16 && !a->bias && !a->residual && !a->C_pre && a->alpha == 1.0f && a->N % 32 == 0,
+                   "pt_gemm_bf16: act %d takes bf16 C, N %% 32 == 0 and no bias / residual / C_pre / alpha", a->act);
+        PT_REQUIRE(a->nz[0] * a->nz[1] * a->nz[2] == 1 && kg == 1 && a->band == PT_BAND_NONE, "pt_gemm_bf16: act %d is not batched", a->act);
+    }
+    if (a->act == PT_ACT_ATTN_DELTA) {
+        PT_REQUIRE(a->aux2 != nullptr && a->aux_i0 > 0 && a->aux_i1 > 0 && a->aux_i1 % 128 == 0 && a->N % 256 == 0 &&
+                       a->N % a->aux_i1 == 0 && a->M % a->aux_i0 == 0,
+                   "pt_gemm_bf16: PT_ACT_ATTN_DELTA needs aux2 = delta, aux_i0 = S (M %% S == 0), aux_i1 = head_dim "
+                   "(%% 128 == 0) and N %% 256 == 0");
+    }
     const bool silu = a->act == PT_ACT_SWIGLU || a->act == PT_ACT_SWIGLU_BWD;
     const bool geglu = a->act == PT_ACT_GEGLU || a->act == PT_ACT_SWIGLU;
     const bool geglu_bwd = a->act == PT_ACT_GEGLU_BWD || a->act == PT_ACT_SWIGLU_BWD;
@@ -230,6 +244,10 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
             PT_REQUIRE(a->c_zs[i] % a->ldc == 0, "pt_gemm_bf16: fused softmax backward needs c_zs %% ldc == 0");
     }
     p.aux = a->aux; p.ld_aux = a->ld_aux; p.ff = geglu ? a->N / 2 : a->N;
+    if (a->act == PT_ACT_ATTN_DELTA) {
+        p.delta = static_cast<float*>(a->aux2);
+        p.dl_S = a->aux_i0; p.dl_hd = a->aux_i1; p.dl_hq = a->N / a->aux_i1;
+    }
     PT_REQUIRE(a->band >= PT_BAND_NONE && a->band <= PT_BAND_K_BY_KEY && a->band_window >= 0,
                "pt_gemm_bf16: bad band %d / window %d", a->band, a->band_window);
     p.band = a->band; p.band_w = a->band_window;
@@ -238,8 +256,8 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUtensorMap ta, tb;
     // CTA-pair kernel (gemm2_sm100.cu): 256 x bn tiles, one per cluster of two SMs
-    int bn = geglu ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
-    if (!geglu && a->bn_hint != 0) {
+    int bn = (geglu || a->act == PT_ACT_ATTN_DELTA) ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
+    if (!geglu && a->act != PT_ACT_ATTN_DELTA && a->bn_hint != 0) {
         PT_REQUIRE(a->bn_hint == 64 || a->bn_hint == 128 || a->bn_hint == 192 || a->bn_hint == 256,
                    "pt_gemm_bf16: bn_hint must be 0, 64, 128, 192 or 256");
         PT_REQUIRE(!p.b_mn || (a->bn_hint / 2) % 64 == 0, "pt_gemm_bf16: an MN-major B operand needs bn_hint 128 or 256");
@@ -268,6 +286,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         if (rc != PT_OK) return rc;
         rc = encode_tiled_bf16_2d(&t_c, a->C, 2ll * p.ff, a->M, a->ldc, 32, 32, 64, "d_gu (epilogue)");
         if (rc != PT_OK) return rc;
+    } else if (tile_epi) {
+        rc = encode_tiled_bf16_2d(&t_aux, a->aux, a->N, a->M, a->ld_aux, 32, 32, 64, "aux (epilogue)");
+        if (rc != PT_OK) return rc;
+        rc = encode_tiled_bf16_2d(&t_c, a->C, a->N, a->M, a->ldc, 32, 32, 64, "C (epilogue)");
+        if (rc != PT_OK) return rc;
+        if (a->act == PT_ACT_ATTN_DELTA &&
+            cudaMemsetAsync(p.delta, 0, static_cast<size_t>(a->M) * p.dl_hq * sizeof(float), st) != cudaSuccess)
+            return check_launch("attn delta memset");
     }
     return launch_gemm2(bn, ta, tb, t_aux, t_c, p, st);
 }

@@ -221,6 +221,10 @@ class Stage1Engine:
         # LM-head input gradient as a split-K launch (K = vocab) + partial sum; 1 = the single 128-wide-tile launch
         self.lm_head_splitk = int(os.environ.get("PT_STAGE1_LM_HEAD_SPLITK", "8"))
         self.fuse_geglu = ops.geglu_fusable(self.lcfg.ff) and os.environ.get("PT_STAGE1_FUSE_GEGLU", "1") != "0"
+        # delta = rowsum(dO * O) in the o-projection dgrad epilogue; erf-GELU backward in the projector dgrad epilogue
+        self.fuse_attn_delta = ops.attn_delta_fusable(self.lcfg.hq, self.lcfg.hd) and \
+            os.environ.get("PT_STAGE1_FUSE_DELTA", "1") != "0"
+        self.fuse_gelu_bwd = os.environ.get("PT_STAGE1_FUSE_GELU_BWD", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
     def buf(self, name, shape, dtype, zero=False):
@@ -557,12 +561,17 @@ class Stage1Engine:
                     ops.rmsnorm_bwd(dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
                 else:
                     ops.cast_f32_bf16(dx, d_y)
-            ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             win = 0 if a["full"] else c.window
+            if fused_attn and self.fuse_attn_delta:
+                # o-projection input gradient with delta = rowsum(dO * O) formed in its epilogue
+                ops.linear_dgrad_attn_delta(d_y, L["o_w"], a["ao"], d_o, delta, S, hd)
+            else:
+                ops.linear_dgrad(d_y, L["o_w"], out=d_o)
             if fused_attn:
-                # delta = rowsum(dO * O); dK, dV and dS in one key/value-stationary kernel; dQ = dS K as a band GEMM
+                # dK, dV and dS in one key/value-stationary kernel; dQ = dS K as a band GEMM
                 dS = dS_by_band[a["full"]]
-                ops.attn_delta(d_o, a["ao"], delta, S, hq, hd)
+                if not self.fuse_attn_delta:
+                    ops.attn_delta(d_o, a["ao"], delta, S, hq, hd)
                 ops.attn_gemma_bwd(a["q"], a["k"], a["qkv"], d_o, a["kvbits"], a["lse"], delta, dS, dk,
                                    d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, win, scale, ld)
                 ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
@@ -650,8 +659,11 @@ class Stage1Engine:
         ops.linear_wgrad(dP, Hm, out=Pj.view(g, 2))                 # dW2 = dP^T Hm
         ops.colsum(dP, Pj.view(g, 3))                               # db2
         dH = self.buf("p_dH", (R, mid), BF16)
-        ops.linear_dgrad(dP, Pj.w2, out=dH)                         # dH = dP W2
-        ops.gelu_erf_bwd(dH, Z, dH)                                 # dZ in place
+        if self.fuse_gelu_bwd and mid % 32 == 0:
+            ops.linear_dgrad_gelu_erf_bwd(dP, Pj.w2, Z, dH)         # dZ = (dP W2) * gelu'(Z) in the GEMM epilogue
+        else:
+            ops.linear_dgrad(dP, Pj.w2, out=dH)                     # dH = dP W2
+            ops.gelu_erf_bwd(dH, Z, dH)                             # dZ in place
         ops.linear_wgrad(dH, patch, out=Pj.view(g, 0))              # dW1 = dZ^T patch
         ops.colsum(dH, Pj.view(g, 1))                               # db1
 

@@ -12,7 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import BAND_K_BY_KEY, BAND_K_BY_QUERY, BAND_NONE, BAND_SCORES  # noqa: F401
-from ._lib import ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
+from ._lib import ACT_ATTN_DELTA, ACT_GELU_ERF_BWD, ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
@@ -38,7 +38,8 @@ def _req_cuda(*ts):
 def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0), b_zs=(0, 0, 0),
              c_zs=(0, 0, 0), a_mn=False, b_mn=False, bias=None, residual=None, ldr=0,
              r_zs=(0, 0, 0), act=ACT_NONE, alpha=1.0, c_pre=None, kg=1, a_kgs=0, b_kgs=0,
-             a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0, band=0, band_window=0, bn_hint=0):
+             a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0, band=0, band_window=0, bn_hint=0,
+             aux2=None, aux_i0=0, aux_i1=0):
     """Fully general launcher; A/B/Cout are tensors used only as base pointers
     (+ element offsets), all geometry comes from the explicit arguments."""
     _req_cuda(A, B, Cout, bias, residual, c_pre, aux)
@@ -80,6 +81,9 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     if aux is not None:
         g.aux = aux.data_ptr()
         g.ld_aux = int(ld_aux)
+    if aux2 is not None:
+        g.aux2 = aux2.data_ptr()
+    g.aux_i0, g.aux_i1 = int(aux_i0), int(aux_i1)
     if GEMM_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -158,6 +162,37 @@ def linear_dgrad_geglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Ten
     ff = w_down.shape[1]
     gemm_raw(M=M, N=ff, K=N, A=dy, lda=dy.stride(0), B=w_down, ldb=w_down.stride(0), b_mn=True, Cout=d_gu,
              ldc=d_gu.stride(0), act=ACT_SWIGLU_BWD if silu else ACT_GEGLU_BWD, aux=gu, ld_aux=gu.stride(0))
+
+
+def linear_dgrad_gelu_erf_bwd(dy: torch.Tensor, w: torch.Tensor, Z: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """out[M,K] = (dy[M,N] @ w[N,K]) * gelu_erf'(Z[M,K]): the projector's second-layer input gradient with the backward
+    of nn.GELU() (ref:Stage1/projectors.py:18) in the GEMM epilogue — dH never reaches HBM.  `out` must not alias Z (edge tiles overlap their neighbours)."""
+    M, N = dy.shape
+    N2, K = w.shape
+    assert N == N2 and Z.shape == (M, K) and out.shape == (M, K) and Z.stride(1) == 1 and out.stride(1) == 1
+    assert out.data_ptr() != Z.data_ptr()
+    gemm_raw(M=M, N=K, K=N, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True, Cout=out, ldc=out.stride(0),
+             act=ACT_GELU_ERF_BWD, aux=Z, ld_aux=Z.stride(0))
+    return out
+
+
+def linear_dgrad_attn_delta(dy: torch.Tensor, w: torch.Tensor, O: torch.Tensor, out: torch.Tensor,
+                            delta: torch.Tensor, S: int, hd: int) -> torch.Tensor:
+    """out[M, hq*hd] = dy[M,N] @ w[N, hq*hd] (the o-projection input gradient dO) and, in the same epilogue,
+    delta[(b*hq + head)*S + s] = sum_d dO * O over each head's hd columns (f32 [B*hq*S]; replaces attn_delta)."""
+    M, N = dy.shape
+    N2, K = w.shape
+    assert N == N2 and O.shape == (M, K) and out.shape == (M, K) and delta.dtype == torch.float32
+    assert delta.numel() >= M * (K // hd)
+    _req_cuda(delta)
+    gemm_raw(M=M, N=K, K=N, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True, Cout=out, ldc=out.stride(0),
+             act=ACT_ATTN_DELTA, aux=O, ld_aux=O.stride(0), aux2=delta, aux_i0=S, aux_i1=hd)
+    return out
+
+
+def attn_delta_fusable(hq: int, hd: int) -> bool:
+    """The delta epilogue works on 256-wide output tiles whose 128-column halves must lie inside one head."""
+    return hd % 128 == 0 and (hq * hd) % 256 == 0
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None) -> torch.Tensor:

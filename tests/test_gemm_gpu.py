@@ -177,6 +177,45 @@ def test_gemm_fused_geglu_fwd_bwd(cuda_dev, M, ff, h):
     _check(d_gu, torch.cat([gt.grad, ut.grad], 1), tol=1e-2, name="d_gu vs torch autograd")
 
 
+@pytest.mark.parametrize("M,N,K", [(18400, 10240, 1152), (575, 640, 256), (70, 32, 64), (300, 2560, 320)])
+def test_gemm_fused_gelu_erf_backward_epilogue(cuda_dev, M, N, K):
+    """dZ = (dP W2) * gelu_erf'(Z) in the GEMM epilogue (TMA-moved Z / dZ tiles) vs the unfused pair and torch autograd."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(M + N)
+    dy, w = _rand((M, K), cuda_dev), _rand((K, N), cuda_dev, 0.05)
+    Z = _rand((M, N), cuda_dev, 1.5)
+    out = torch.full((M, N), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_dgrad_gelu_erf_bwd(dy, w, Z, out)
+    dH = dy.float() @ w.float()
+    zr = Z.float().requires_grad_(True)
+    torch.nn.functional.gelu(zr).backward(dH)
+    _check(out, zr.grad, tol=1e-2, name="vs autograd")
+    un = ops.linear_dgrad(dy, w)
+    ops.gelu_erf_bwd(un, Z, un)
+    _check(out, un.float(), tol=1e-2, name="vs unfused kernels")
+
+
+@pytest.mark.parametrize("B,S,hq,hd,K", [(32, 703, 4, 256, 1152), (2, 100, 4, 256, 128), (3, 77, 8, 128, 256), (1, 300, 2, 128, 64)])
+def test_gemm_fused_attention_delta_epilogue(cuda_dev, B, S, hq, hd, K):
+    """dO = d_y W_o with delta[b, head, s] = sum_d dO * O in the epilogue vs linear_dgrad + pt_attn_delta."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(S + hq)
+    M, N = B * S, hq * hd
+    dy, w = _rand((M, K), cuda_dev), _rand((K, N), cuda_dev, 0.05)
+    O = _rand((M, N), cuda_dev)
+    dO = torch.full((M, N), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    delta = torch.full((B * hq * S,), float("nan"), device=cuda_dev)
+    ops.linear_dgrad_attn_delta(dy, w, O, dO, delta, S, hd)
+    ref = ops.linear_dgrad(dy, w)
+    assert torch.equal(dO, ref)
+    d_ref = torch.empty_like(delta)
+    ops.attn_delta(ref, O, d_ref, S, hq, hd)
+    d64 = (ref.double() * O.double()).view(B, S, hq, hd).sum(-1).permute(0, 2, 1).reshape(-1)
+    assert torch.isfinite(delta).all()
+    assert (delta.double() - d64).abs().max().item() < 1e-4 * d64.abs().max().item() + 1e-5
+    assert (delta - d_ref).abs().max().item() < 1e-4 * d_ref.abs().max().item() + 1e-5
+
+
 @pytest.mark.parametrize("S,W", [(703, 0), (703, 512), (300, 64), (1000, 100)])
 def test_gemm_attention_bands_skip_only_masked_work(cuda_dev, S, W):
     """pt_gemm_args.band: causal / sliding-window tile and K-block skipping must not change any value a masked
