@@ -237,6 +237,17 @@ int pt_attn_gemma_bwd(const void* q_rot, const void* k_rot, const void* qkv, con
                       const float* lse, const float* delta, void* dS_bf16, void* dK_bf16, long long ld_dk,
                       void* dV_bf16, long long ld_dv, int B, int S, int hq, int hkv, int hd, int window, float scale,
                       int lds, void* stream);
+/* The same backward on a CTA PAIR per tile of 128 keys (attn_gemma_bwd2_sm100.cu: one SM keeps the K tile and forms
+ * P^T and dV, its partner keeps the V tile and forms dS^T and dK; P^T crosses by a bulk DSMEM copy) — about twice as
+ * fast at head_dim 256.  Difference to pt_attn_gemma_bwd: dS leaves TRANSPOSED:
+ *   dST[(b*hq + head), k, q] = scale * P[q, k] * (dO V^T - delta)[q, k]     (bf16, [B*hq, S keys, ldt]; written only
+ *                              inside the (128-key tile, 64-position block) pairs of the band; zero-fill once per
+ *                              window value)
+ * so dQ = dS k_rot is a band-limited pt_gemm_bf16 with dST as an MN-major A operand (a_mn_major = 1). */
+int pt_attn_gemma_bwd_pair(const void* q_rot, const void* k_rot, const void* qkv, const void* dO_bf16,
+                           const void* kvbits, const float* lse, const float* delta, void* dST_bf16, void* dK_bf16,
+                           long long ld_dk, void* dV_bf16, long long ld_dv, int B, int S, int hq, int hkv, int hd,
+                           int window, float scale, int ldt, void* stream);
 /* keyvalid u8 [B,S] (0 = padded key, ref:Stage1/projector_trainer.py:205-208) -> u64 [B, ceil(S/64)] bit masks
  * (bit i of word w = key 64 w + i; keys >= S are 0). */
 int pt_pack_keyvalid(const uint8_t* keyvalid, void* kvbits, int B, int S, void* stream);

@@ -137,7 +137,9 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t n_item = 0, it = 0;                    // it = blocks loaded so far (all items)
-            for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+            for (int jj = 0; jj * static_cast<int>(gridDim.x) < items; ++jj, ++n_item) {
+                const int item = snake_item(jj, blockIdx.x, gridDim.x);
+                if (item >= items) break;          // (only in the last run)
                 int b, kvh, kt, qb0, nqb;
                 gemma_bwd_item(p, item, b, kvh, kt, qb0, nqb);
                 for (int i = 0; i < nqb; ++i, ++it) {
@@ -199,7 +201,9 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                         ptx::mma_bf16_ss(d + h * kGkTile, adesc, bdesc, idescT, !(first && k == 0));
                     }
             };
-            for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+            for (int jj = 0; jj * static_cast<int>(gridDim.x) < items; ++jj, ++n_item) {
+                const int item = snake_item(jj, blockIdx.x, gridDim.x);
+                if (item >= items) break;          // (only in the last run)
                 int b, kvh, kt, qb0, nqb;
                 gemma_bwd_item(p, item, b, kvh, kt, qb0, nqb);
                 ptx::mbar_wait(kv_full, n_item & 1);
@@ -246,7 +250,9 @@ attn_gemma_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const float c2 = p.scale_log2e;
         const bool tr0 = threadIdx.x == 0;
         uint32_t n_item = 0, it = 0;
-        for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+        for (int jj = 0; jj * static_cast<int>(gridDim.x) < items; ++jj, ++n_item) {
+                const int item = snake_item(jj, blockIdx.x, gridDim.x);
+                if (item >= items) break;          // (only in the last run)
             int b, kvh, kt, qb0, nqb;
             gemma_bwd_item(p, item, b, kvh, kt, qb0, nqb);
             const int k0 = kt * kGkTile;

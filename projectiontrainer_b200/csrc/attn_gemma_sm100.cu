@@ -112,7 +112,9 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t n_item = 0, lc = 0;                  // lc = tiles loaded so far -> ring stage / parity
-            for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+            for (int jj = 0; jj * static_cast<int>(gridDim.x) < items; ++jj, ++n_item) {
+                const int item = snake_item(jj, blockIdx.x, gridDim.x);
+                if (item >= items) break;          // (only in the last run)
                 int b, kvh, qb, jlo, nt;
                 gemma_item(p, item, b, kvh, qb, jlo, nt);
                 ptx::mbar_wait(q_empty, (n_item & 1) ^ 1);           // previous item's S MMAs retired
@@ -155,7 +157,9 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 ptx::mma_commit(&ld_empty[st]);
                 ++sc;
             };
-            for (int item = blockIdx.x; item < items; item += gridDim.x, ++n_item) {
+            for (int jj = 0; jj * static_cast<int>(gridDim.x) < items; ++jj, ++n_item) {
+                const int item = snake_item(jj, blockIdx.x, gridDim.x);
+                if (item >= items) break;          // (only in the last run)
                 int b, kvh, qb, jlo, nt;
                 gemma_item(p, item, b, kvh, qb, jlo, nt);
                 ptx::mbar_wait(q_full, n_item & 1);
@@ -192,7 +196,9 @@ attn_gemma_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const uint32_t p_row = ptx::smem_u32(sP) + row * 128;
         const float c2 = p.scale_log2e;
         uint32_t sc = 0, pc = 0;
-        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        for (int jj = 0; jj * static_cast<int>(gridDim.x) < items; ++jj) {
+            const int item = snake_item(jj, blockIdx.x, gridDim.x);
+            if (item >= items) break;              // (only in the last run)
             int b, kvh, qb, jlo, nt;
             gemma_item(p, item, b, kvh, qb, jlo, nt);
             const int s = qb * p.pos_per_blk + row / p.G;           // query position of this row

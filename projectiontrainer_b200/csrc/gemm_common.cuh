@@ -86,6 +86,9 @@ int encode_tiled_bf16_5d(CUtensorMap* out, const void* base, const unsigned long
 // swizzle_bytes in {0, 64, 128} (box_cols * 2 must equal it when non-zero)
 int encode_tiled_bf16_2d(CUtensorMap* out, const void* base, long long cols, long long rows, long long ld,
                          int box_cols, int box_rows, int swizzle_bytes, const char* name);
+// generic bf16 map of rank 3 (dims / box innermost first; strides_bytes for dims 1, 2), 128-byte swizzle
+int encode_tiled_bf16_3d(CUtensorMap* out, const void* base, const unsigned long long dims[3],
+                         const unsigned long long strides_bytes[2], const unsigned int box[3], const char* name);
 // CTA-pair kernel (gemm2_sm100.cu): bn in {64,128,192,256}; tensor map of B must use box rows bn/2.
 // t_aux / t_c: 2-D maps (32 x 32 boxes, 64-byte swizzle) of the aux matrix and of C for the epilogues that move their
 // tiles with TMA (PT_ACT_GEGLU_BWD); any valid map otherwise (unused).

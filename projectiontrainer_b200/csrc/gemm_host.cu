@@ -103,6 +103,24 @@ int encode_tiled_bf16_2d(CUtensorMap* out, const void* base, long long cols, lon
     return PT_OK;
 }
 
+int encode_tiled_bf16_3d(CUtensorMap* out, const void* base, const unsigned long long dims[3],
+                         const unsigned long long strides_bytes[2], const unsigned int box[3], const char* name) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return PT_ERR_CUDA; }
+    cuuint64_t d[3] = {dims[0], dims[1], dims[2]}, st[2] = {strides_bytes[0], strides_bytes[1]};
+    cuuint32_t bx[3] = {box[0], box[1], box[2]}, es[3] = {1, 1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), d, st, bx, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(%s) failed: CUresult %d (dims %llu %llu %llu, strides %llu %llu, box %u %u %u)",
+                  name, static_cast<int>(r), dims[0], dims[1], dims[2], strides_bytes[0], strides_bytes[1], box[0],
+                  box[1], box[2]);
+        return PT_ERR_CUDA;
+    }
+    return PT_OK;
+}
+
 int encode_tiled_bf16_5d(CUtensorMap* out, const void* base, const unsigned long long dims[5],
                          const unsigned long long strides_bytes[4], const unsigned int box[5], const char* name) {
     EncodeTiledFn enc = get_encode_fn();

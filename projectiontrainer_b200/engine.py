@@ -225,6 +225,9 @@ class Stage1Engine:
         self.fuse_attn_delta = ops.attn_delta_fusable(self.lcfg.hq, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_FUSE_DELTA", "1") != "0"
         self.fuse_gelu_bwd = os.environ.get("PT_STAGE1_FUSE_GELU_BWD", "1") != "0"
+        # attention backward on a CTA pair per 128 keys (0: the single-CTA kernel on 64-key tiles)
+        self.attn_bwd_pair = ops.attn_gemma_bwd_pair_ok(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
+            os.environ.get("PT_STAGE1_ATTN_BWD_PAIR", "1") != "0"
 
     # ------------------------------------------------------------------ workspace
     def buf(self, name, shape, dtype, zero=False):
@@ -521,7 +524,8 @@ class Stage1Engine:
         if fused_attn:
             # the fused backward writes dS only inside the (query block, key tile) pairs of a layer's band and the
             # dQ GEMM reads whole K blocks: one zero-filled buffer per band shape (full-causal / sliding layers)
-            dS_by_band = {f: self.buf("b_dS_full" if f else "b_dS_slide", (B * hq, S, ld), BF16, zero=True)
+            tag = "b_dST_" if self.attn_bwd_pair else "b_dS_"
+            dS_by_band = {f: self.buf(tag + ("full" if f else "slide"), (B * hq, S, ld), BF16, zero=True)
                           for f in {a["full"] for a in s["layers"]}}
         else:
             dS = self.buf("b_dS", (B * hq, S, ld), BF16)
@@ -572,12 +576,19 @@ class Stage1Engine:
                 dS = dS_by_band[a["full"]]
                 if not self.fuse_attn_delta:
                     ops.attn_delta(d_o, a["ao"], delta, S, hq, hd)
-                ops.attn_gemma_bwd(a["q"], a["k"], a["qkv"], d_o, a["kvbits"], a["lse"], delta, dS, dk,
-                                   d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, win, scale, ld)
-                ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
-                             ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
-                             b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY,
-                             band_window=win)
+                if self.attn_bwd_pair:
+                    # a CTA pair per 128 keys (K tile -> P^T, dV on one SM; V tile -> dS^T, dK on its partner);
+                    # dS leaves transposed and feeds the dQ GEMM as an MN-major operand
+                    ops.attn_gemma_bwd_pair(a["q"], a["k"], a["qkv"], d_o, a["kvbits"], a["lse"], delta, dS, dk,
+                                            d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, win, scale, ld)
+                    ops.attn_dq_from_dst(dS, a["k"], dq, B, S, hq, hkv, hd, win, ld)
+                else:
+                    ops.attn_gemma_bwd(a["q"], a["k"], a["qkv"], d_o, a["kvbits"], a["lse"], delta, dS, dk,
+                                       d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, win, scale, ld)
+                    ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=a["k"], ldb=hkv * hd, b_mn=True, Cout=dq,
+                                 ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
+                                 b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY,
+                                 band_window=win)
                 ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                     hkv, hd, c.eps)
                 ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)

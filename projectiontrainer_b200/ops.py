@@ -314,6 +314,28 @@ def attn_gemma_bwd(q_rot, k_rot, qkv, dO, kvbits, lse, delta, dS, dK, dV, B, S, 
               int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), int(lds), _stream())
 
 
+def attn_gemma_bwd_pair_ok(hq: int, hkv: int, hd: int) -> bool:
+    G = hq // max(1, hkv)
+    return hd in (128, 256) and hq % hkv == 0 and G >= 1
+
+
+def attn_gemma_bwd_pair(q_rot, k_rot, qkv, dO, kvbits, lse, delta, dST, dK, dV, B, S, hq, hkv, hd, window, scale, ldt):
+    """CTA-pair backward of attn_gemma_fwd: dK, dV and dS^T (bf16 [B*hq, S keys, ldt], band only: zero-fill once)."""
+    _req_cuda(q_rot, k_rot, qkv, dO, kvbits, lse, delta, dST, dK, dV)
+    assert dK.stride(1) == 1 and dV.stride(1) == 1
+    _lib.call("pt_attn_gemma_bwd_pair", _ptr(q_rot), _ptr(k_rot), _ptr(qkv), _ptr(dO), _ptr(kvbits), _ptr(lse),
+              _ptr(delta), _ptr(dST), _ptr(dK), C.c_longlong(dK.stride(0)), _ptr(dV), C.c_longlong(dV.stride(0)),
+              int(B), int(S), int(hq), int(hkv), int(hd), int(window), _f(scale), int(ldt), _stream())
+
+
+def attn_dq_from_dst(dST, k_rot, dQ, B, S, hq, hkv, hd, window, ldt):
+    """dQ[b, q, head, :] = sum_k dS^T[b, head, k, q] K[b, k, kvh, :]: band-limited GEMM, dS^T read MN-major."""
+    G = hq // hkv
+    gemm_raw(M=S, N=hd, K=S, A=dST, lda=ldt, a_mn=True, B=k_rot, ldb=hkv * hd, b_mn=True, Cout=dQ, ldc=hq * hd,
+             nz=(G, hkv, B), a_zs=(S * ldt, G * S * ldt, hq * S * ldt), b_zs=(0, hd, S * hkv * hd),
+             c_zs=(hd, G * hd, S * hq * hd), band=BAND_K_BY_QUERY, band_window=window)
+
+
 def attn_delta(dO, O, delta, S, hq, hd):
     _req_cuda(dO, O, delta)
     _lib.call("pt_attn_delta", _ptr(dO), _ptr(O), _ptr(delta), dO.shape[0], int(S), int(hq), int(hd), _stream())

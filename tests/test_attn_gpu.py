@@ -92,7 +92,8 @@ def test_attn_gemma_fwd(cuda_dev, B, S, hq, hkv, W, pad, hd, amp):
 
 @pytest.mark.parametrize("B,S,hq,hkv,W,pad", GEMMA_GEOMS)
 @pytest.mark.parametrize("hd", [256, 128])
-def test_attn_gemma_bwd(cuda_dev, B, S, hq, hkv, W, pad, hd):
+@pytest.mark.parametrize("pair", [True, False], ids=["cta_pair", "single_cta"])
+def test_attn_gemma_bwd(cuda_dev, B, S, hq, hkv, W, pad, hd, pair):
     """Fused key/value-stationary backward (P recomputed from the forward's log-sum-exp) + the band-limited dQ GEMM
     vs fp32 torch autograd through softmax attention on the same bf16-rounded q/k/v/dO: dQ, dK, dV (max error
     < 2e-2 of range, cosine > 0.9995), exact zeros on masked dS entries and on rows without a visible key."""
@@ -116,12 +117,17 @@ def test_attn_gemma_bwd(cuda_dev, B, S, hq, hkv, W, pad, hd):
     dS = torch.zeros(B * hq, S, ld, dtype=torch.bfloat16, device=cuda_dev)
     dK = torch.full((B * S, hkv * hd), float("nan"), dtype=torch.bfloat16, device=cuda_dev)
     d_qkv = torch.full((B * S, QKV), 7.0, dtype=torch.bfloat16, device=cuda_dev)
-    ops.attn_gemma_bwd(q, k, qkv, dO, kvbits, lse, delta, dS, dK, d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, W,
-                       scale, ld)
     dQ = torch.full((B * S, hq * hd), float("nan"), dtype=torch.bfloat16, device=cuda_dev)
-    ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=k, ldb=hkv * hd, b_mn=True, Cout=dQ, ldc=hq * hd, nz=(G, hkv, B),
-                 a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd),
-                 band=ops.BAND_K_BY_QUERY, band_window=W)
+    if pair:        # CTA pair per 128 keys; dS leaves transposed ([head, key, query]) for an MN-major dQ GEMM
+        ops.attn_gemma_bwd_pair(q, k, qkv, dO, kvbits, lse, delta, dS, dK, d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv,
+                                hd, W, scale, ld)
+        ops.attn_dq_from_dst(dS, k, dQ, B, S, hq, hkv, hd, W, ld)
+    else:
+        ops.attn_gemma_bwd(q, k, qkv, dO, kvbits, lse, delta, dS, dK, d_qkv[:, (hq + hkv) * hd:], B, S, hq, hkv, hd, W,
+                           scale, ld)
+        ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=k, ldb=hkv * hd, b_mn=True, Cout=dQ, ldc=hq * hd, nz=(G, hkv, B),
+                     a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd),
+                     band=ops.BAND_K_BY_QUERY, band_window=W)
     torch.cuda.synchronize()
     # fp32 autograd reference
     qr, kr, vr = qf.clone().requires_grad_(True), kf.clone().requires_grad_(True), vf.clone().requires_grad_(True)
@@ -141,6 +147,8 @@ def test_attn_gemma_bwd(cuda_dev, B, S, hq, hkv, W, pad, hd):
         cos = torch.nn.functional.cosine_similarity(got.flatten(), ref.flatten(), dim=0).item()
         assert cos > 0.9995, (name, cos)
     dSg = dS[:, :, :S].float().view(B, hq, S, S)
+    if pair:
+        dSg = dSg.transpose(-1, -2)
     assert float(dSg[~allowed.expand_as(dSg)].abs().max()) == 0.0    # masked / out of band: exactly 0
     assert float(dQ.float().view(B * S, hq, hd)[~live_rows].abs().max() if (~live_rows).any() else 0.0) == 0.0
 

@@ -44,10 +44,14 @@ for (B, S, hq, hkv, hd, windows) in ((32, 703, 4, 1, 256, (0, 512)), (16, 831, 8
         t_d = timed(lambda: ops.attn_delta(dO, O, delta, S, hq, hd))
         t_b = timed(lambda: ops.attn_gemma_bwd(q, k, qkv, dO, bits, lse, delta, dS, dK, dV, B, S, hq, hkv, hd, W,
                                                1 / 16, ld))
+        t_p = timed(lambda: ops.attn_gemma_bwd_pair(q, k, qkv, dO, bits, lse, delta, dS, dK, dV, B, S, hq, hkv, hd, W,
+                                                    1 / 16, ld))
+        t_q2 = timed(lambda: ops.attn_dq_from_dst(dS, k, dQ, B, S, hq, hkv, hd, W, ld))
         t_q = timed(lambda: ops.gemm_raw(M=S, N=hd, K=S, A=dS, lda=ld, B=k, ldb=hkv * hd, b_mn=True, Cout=dQ,
                                          ldc=hq * hd, nz=(G, hkv, B), a_zs=(S * ld, G * S * ld, hq * S * ld),
                                          b_zs=(0, hd, S * hkv * hd), c_zs=(hd, G * hd, S * hq * hd),
                                          band=ops.BAND_K_BY_QUERY, band_window=W))
-        print(f"B={B} S={S} {hq}:{hkv} hd={hd} window={W}: fwd {t_f:.1f} us ({gf / t_f * 1e-3:.0f} TF/s)  "
-              f"delta {t_d:.1f}  bwd(dK,dV,dS) {t_b:.1f} us ({2 * gf / t_b * 1e-3:.0f} TF/s of 4 products)  "
-              f"dQ gemm {t_q:.1f} us", flush=True)
+        print(f"B={B} S={S} {hq}:{hkv} hd={hd} window={W}: fwd {t_f:.1f} us ({gf / t_f * 1e3:.0f} TF/s)  "
+              f"delta {t_d:.1f}  bwd(dK,dV,dS) {t_b:.1f} us ({2 * gf / t_b * 1e3:.0f} TF/s of 4 products)  "
+              f"dQ gemm {t_q:.1f} us | pair bwd {t_p:.1f} us ({2 * gf / t_p * 1e3:.0f} TF/s)  dQ gemm (dS^T, MN-major A) {t_q2:.1f} us",
+              flush=True)
