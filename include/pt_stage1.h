@@ -328,6 +328,18 @@ int pt_image_preprocess(const uint8_t* src_rgb, int H, int W, long long src_row_
                         uint8_t* dst_u8_hwc, int out_h, int out_w, float mean0, float mean1, float mean2,
                         float std0, float std1, float std2, double rescale, void* workspace,
                         long long workspace_bytes, void* stream);
+/* pt_image_preprocess without a caller workspace and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The scratch (tap tables + the horizontally resampled intermediate) lives
+ * in a file-scope device array of pt_image_preprocess_static_max_bytes() = 8 MiB that every GPU loading the library
+ * holds until exit; a resize whose pt_image_preprocess_workspace() exceeds it is rejected with PT_ERR_INVALID.  Same
+ * kernels, same results as pt_image_preprocess.  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams without an ordering between them) race; calls on one stream are safe.  Nothing needs clearing
+ * between calls (every byte read was written earlier in the same call). */
+long long pt_image_preprocess_static_max_bytes(void);
+int pt_image_preprocess_static(const uint8_t* src_rgb, int H, int W, long long src_row_stride, float* dst_chw,
+                               uint8_t* dst_u8_hwc, int out_h, int out_w, float mean0, float mean1, float mean2,
+                               float std0, float std1, float std2, double rescale, void* stream);
 
 /* ---- NF4 frozen LLM weights -----------------------------------------------------------
  * ref:Stage1/train_projection_stage1.py:192-210: `--enable_qlora` loads the frozen LLM through bitsandbytes with

@@ -11,6 +11,7 @@
 // Byte work bounded by reading the source image once from HBM; the coefficient tables are computed on the
 // device in double precision with explicitly unfused operations so that every weight equals Pillow's.
 #include <algorithm>
+#include <mutex>
 
 #include "pt_common.cuh"
 
@@ -266,4 +267,63 @@ extern "C" int pt_image_preprocess(const uint8_t* src_rgb, int H, int W, long lo
     resample_vertical_normalize_kernel<<<gv, 128, 0, st>>>(tmp, 0, bounds_v, coeff_v, out_h, out_w, rescale, mean0,
                                                            mean1, mean2, std0, std1, std2, dst_chw, dst_u8_hwc);
     return check_launch("image_preprocess");
+}
+
+// ---- allocation-free variant ------------------------------------------------------------------------------------
+// pt_image_preprocess_static: the same three kernels with their scratch (tap tables + the horizontally resampled
+// intermediate) in a file-scope device array instead of a caller-allocated workspace, for callers that cannot
+// allocate: code under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc.  No counterpart in the
+// reference.  Every GPU that loads the library holds the array until
+// exit.  All calls on a device share it: calls that overlap on the GPU (different streams) race.  Nothing in it has
+// to start at zero — every byte a call reads (bounds, taps including their zero padding, intermediate rows) was
+// written earlier in the same call — so the previous call's contents need no clearing.
+namespace pt {
+constexpr long long kImageStaticScratchBytes = 8ll << 20;      // 8 MiB: e.g. a 6900-row source down to 384 x 384
+static __device__ __align__(256) uint8_t g_image_scratch[kImageStaticScratchBytes];
+
+// Device address of g_image_scratch on the CURRENT device (the host-side symbol is only a handle), looked up once
+// per device.
+static int image_static_scratch(void** out) {
+    constexpr int kMaxDev = 64;
+    static void* ptrs[kMaxDev] = {};
+    static std::mutex mu;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+        set_error("pt_image_preprocess_static: cudaGetDevice failed or device ordinal >= %d", kMaxDev);
+        return PT_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_image_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("pt_image_preprocess_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                      cudaGetErrorString(e));
+            return PT_ERR_CUDA;
+        }
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return PT_OK;
+}
+}  // namespace pt
+
+extern "C" long long pt_image_preprocess_static_max_bytes(void) { return pt::kImageStaticScratchBytes; }
+
+extern "C" int pt_image_preprocess_static(const uint8_t* src_rgb, int H, int W, long long src_row_stride,
+                                          float* dst_chw, uint8_t* dst_u8_hwc, int out_h, int out_w, float mean0,
+                                          float mean1, float mean2, float std0, float std1, float std2,
+                                          double rescale, void* stream) {
+    PT_REQUIRE(H > 0 && W > 0 && out_h > 0 && out_w > 0, "pt_image_preprocess_static: bad image size");
+    const long long need = plan_image(H, W, out_h, out_w).total;
+    PT_REQUIRE(need <= kImageStaticScratchBytes,
+               "pt_image_preprocess_static: a %d x %d -> %d x %d resize needs %lld bytes of scratch, the built-in "
+               "array holds %lld: use pt_image_preprocess with a caller-allocated workspace", H, W, out_h, out_w,
+               need, kImageStaticScratchBytes);
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    void* ws = nullptr;
+    const int rc = image_static_scratch(&ws);
+    if (rc != PT_OK) return rc;
+    return pt_image_preprocess(src_rgb, H, W, src_row_stride, dst_chw, dst_u8_hwc, out_h, out_w, mean0, mean1, mean2,
+                               std0, std1, std2, rescale, ws, kImageStaticScratchBytes, stream);
 }
