@@ -149,6 +149,17 @@ typedef struct {
     /* PT_ACT_ATTN_DELTA only (see pt_act): f32 output [B*hq, S], sequence length, head dim; NULL / 0 otherwise. */
     void* aux2;
     int32_t aux_i0, aux_i1;
+    /* Optional second contraction segment: the accumulator also takes sum_k A2[m][k] * B2[n][k] over K2 before the
+     * epilogue, i.e. C = epilogue(alpha * ([A | A2] . [B | B2]^T)).  A2 / B2 are bf16 with the SAME major-ness as
+     * A / B (a_mn_major / b_mn_major), row strides lda2 / ldb2, no batch dims (nz = 1, kg <= 1, band none); K2 = 0
+     * disables it.  This is how a LoRA adapter rides the base projection: A2 = t = x A_lora^T, B2 = B_lora
+     * (peft's `result + lora_B(lora_A(x)) * scaling`, ref:Stage2/train_vqa_stage2.py:225-250), and for the input
+     * gradient A2 = dt, B2 = A_lora read MN-major — one pass over the output, every fused epilogue still applies. */
+    const void* A2;
+    int64_t lda2;
+    const void* B2;
+    int64_t ldb2;
+    int32_t K2;
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);

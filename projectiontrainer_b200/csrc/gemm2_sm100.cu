@@ -282,7 +282,8 @@ __device__ __forceinline__ void epi_chunk_sbwd_pre(const uint32_t (&v)[32], uint
 template <int BN, int ACT>
 __global__ void __launch_bounds__(kGemm2Threads, 1)
 gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const __grid_constant__ CUtensorMap tmAux, const __grid_constant__ CUtensorMap tmC, const GemmDev p) {
+                  const __grid_constant__ CUtensorMap tmAux, const __grid_constant__ CUtensorMap tmC,
+                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2, const GemmDev p) {
     using Cfg = Gemm2Cfg<BN, ACT>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int BNH = BN / 2;                 // B rows staged by each CTA
@@ -312,13 +313,16 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int tiles_per_z = mt * nt;
     const int total_tiles = tiles_per_z * p.nz[0] * p.nz[1] * p.nz[2];
     const int nkb = (p.K + BK - 1) / BK;
-    const int k_iters = nkb * p.kg;
+    // second contraction segment (GemmDev::K2): nkb2 more K blocks per tile, read through tmA2 / tmB2
+    const int nkb2 = (p.K2 + BK - 1) / BK;
+    const int k_iters = nkb * p.kg + nkb2;
     const int cid = static_cast<int>(ptx::cluster_id_x());
     const int ncl = static_cast<int>(ptx::num_clusters_x());
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmB);
+        if (p.K2 > 0) { ptx::prefetch_tmap(&tmA2); ptx::prefetch_tmap(&tmB2); }
         if constexpr (tma_epilogue(ACT)) { ptx::prefetch_tmap(&tmAux); ptx::prefetch_tmap(&tmC); }
     }
     if (warp == 1 && lane == 0) {
@@ -378,7 +382,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int tile_n = n_blk == nt - 1 ? p.n_last : n_blk * BN;
                 int kb_lo = 0, kb_hi = nkb;
                 if (p.band && band_span(p, tile_m, tile_n, TM, BN, nkb, kb_lo, kb_hi)) continue;
-                const int tile_iters = (kb_hi - kb_lo) * p.kg;
+                const int main_iters = (kb_hi - kb_lo) * p.kg;
                 const int m0 = tile_m + static_cast<int>(rank) * BM;
                 // fused GeGLU: the pair's tile is [128 gate rows | the 128 up rows of the same ff range]
                 // half-width last n tile (GemmDev::n_half): a full in-bounds box whose second half holds this CTA's
@@ -388,35 +392,40 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                                    ? n_blk * BNH + static_cast<int>(rank) * p.ff
                                    : half ? tile_n - BNH / 2 + static_cast<int>(rank) * (BNH / 2)
                                           : tile_n + static_cast<int>(rank) * BNH;
-                int g = 0, kb = kb_lo;
-                for (int it = 0; it < tile_iters; ++it) {
-                    if (kga) ea0 = g;
-                    if (kgb) eb0 = g;
+                // one pipeline stage: wait for the slot, post the byte count, issue this CTA's A and B boxes
+                auto fill = [&](const CUtensorMap* mA, const CUtensorMap* mB, int kc, int a0, int a1, int a2, int b0,
+                                int b1, int b2) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
                     if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
                     uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
                     if (!p.a_mn) {
-                        ptx::tma_load_5d_2sm(&tmA, fb, sa, kb * BK, m0, ea0, ea1, ea2);
+                        ptx::tma_load_5d_2sm(mA, fb, sa, kc, m0, a0, a1, a2);
                     } else {
 #pragma unroll
                         for (int c = 0; c < BM / 64; ++c)
-                            ptx::tma_load_5d_2sm(&tmA, fb, sa + c * (BK * 128), m0 + c * 64, kb * BK, ea0,
-                                                 ea1, ea2);
+                            ptx::tma_load_5d_2sm(mA, fb, sa + c * (BK * 128), m0 + c * 64, kc, a0, a1, a2);
                     }
                     if (!p.b_mn) {
-                        ptx::tma_load_5d_2sm(&tmB, fb, sb, kb * BK, n0, eb0, eb1, eb2);
+                        ptx::tma_load_5d_2sm(mB, fb, sb, kc, n0, b0, b1, b2);
                     } else {
 #pragma unroll
                         for (int c = 0; c < BNH / 64; ++c)
-                            ptx::tma_load_5d_2sm(&tmB, fb, sb + c * (BK * 128), n0 + c * 64, kb * BK, eb0,
-                                                 eb1, eb2);
+                            ptx::tma_load_5d_2sm(mB, fb, sb + c * (BK * 128), n0 + c * 64, kc, b0, b1, b2);
                     }
                     if (!leader) ptx::mbar_arrive_cluster(fb);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                };
+                int g = 0, kb = kb_lo;
+                for (int it = 0; it < main_iters; ++it) {
+                    if (kga) ea0 = g;
+                    if (kgb) eb0 = g;
+                    fill(&tmA, &tmB, kb * BK, ea0, ea1, ea2, eb0, eb1, eb2);
                     if (++kb == kb_hi) { kb = kb_lo; ++g; }
                 }
+                // K blocks past the main contraction come from the second operand pair (no batch dims)
+                for (int it = 0; it < nkb2; ++it) fill(&tmA2, &tmB2, it * BK, 0, 0, 0, 0, 0, 0);
             }
         }
     } else if (warp == 1) {
@@ -451,7 +460,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     int kb_lo, kb_hi;
                     if (band_span(p, m_blk == mt - 1 ? p.m_last : m_blk * TM, n_blk == nt - 1 ? p.n_last : n_blk * BN,
                                   TM, BN, nkb, kb_lo, kb_hi)) continue;
-                    tile_iters = (kb_hi - kb_lo) * p.kg;
+                    tile_iters = (kb_hi - kb_lo) * p.kg + nkb2;
                 }
                 ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
                 ptx::tc_fence_after();
@@ -826,7 +835,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 // ---- host ----------------------------------------------------------------------------------------
 template <int BN, int ACT>
 static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& t_aux,
-                          const CUtensorMap& t_c, const GemmDev& p, int tiles, cudaStream_t st) {
+                          const CUtensorMap& t_c, const CUtensorMap& ta2, const CUtensorMap& tb2, const GemmDev& p,
+                          int tiles, cudaStream_t st) {
     using Cfg = Gemm2Cfg<BN, ACT>;
     static bool attr_done = false;
     if (!attr_done) {
@@ -853,7 +863,7 @@ static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const CU
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_bf16_kernel<BN, ACT>, ta, tb, t_aux, t_c, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_bf16_kernel<BN, ACT>, ta, tb, t_aux, t_c, ta2, tb2, p);
     if (e != cudaSuccess) {
         set_error("gemm2_bf16_kernel<%d>: launch failed: %s", BN, cudaGetErrorString(e));
         return PT_ERR_CUDA;
@@ -874,23 +884,23 @@ static int gbwd_tma_enabled() {
 }
 
 int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& t_aux, const CUtensorMap& t_c,
-                 const GemmDev& p, cudaStream_t st) {
+                 const CUtensorMap& ta2, const CUtensorMap& tb2, const GemmDev& p, cudaStream_t st) {
     const int tiles = gemm2_tiles(p, bn);
     if (tiles <= 0) { set_error("gemm2: bad tile count"); return PT_ERR_INVALID; }
 #define PT_G2(BN_)                                                                      \
     case BN_:                                                                           \
-        if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, t_aux, t_c, p, tiles, st); \
-        if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, t_aux, t_c, p, tiles, st);   \
+        if (p.act == PT_ACT_GELU_TANH) return launch_gemm2_t<BN_, PT_ACT_GELU_TANH>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st); \
+        if (p.act == PT_ACT_GELU_ERF) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);   \
         if (p.act == PT_ACT_GEGLU_BWD)                                                                      \
-            return gbwd_tma_enabled() ? launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, t_aux, t_c, p, tiles, st) \
-                                      : launch_gemm2_t<BN_, kActGbwdLsu>(ta, tb, t_aux, t_c, p, tiles, st);  \
-        if (p.act == PT_ACT_SOFTMAX_BWD) return launch_gemm2_t<BN_, PT_ACT_SOFTMAX_BWD>(ta, tb, t_aux, t_c, p, tiles, st); \
-        if (p.act == PT_ACT_GELU_ERF_BWD) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF_BWD>(ta, tb, t_aux, t_c, p, tiles, st); \
-        if (p.act == PT_ACT_ATTN_DELTA) return launch_gemm2_t<BN_, PT_ACT_ATTN_DELTA>(ta, tb, t_aux, t_c, p, tiles, st); \
-        return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, t_aux, t_c, p, tiles, st);
+            return gbwd_tma_enabled() ? launch_gemm2_t<BN_, PT_ACT_GEGLU_BWD>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st) \
+                                      : launch_gemm2_t<BN_, kActGbwdLsu>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);  \
+        if (p.act == PT_ACT_SOFTMAX_BWD) return launch_gemm2_t<BN_, PT_ACT_SOFTMAX_BWD>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st); \
+        if (p.act == PT_ACT_GELU_ERF_BWD) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF_BWD>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st); \
+        if (p.act == PT_ACT_ATTN_DELTA) return launch_gemm2_t<BN_, PT_ACT_ATTN_DELTA>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st); \
+        return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);
     if (p.act == PT_ACT_GEGLU) {
         if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }
-        return launch_gemm2_t<256, PT_ACT_GEGLU>(ta, tb, t_aux, t_c, p, tiles, st);
+        return launch_gemm2_t<256, PT_ACT_GEGLU>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);
     }
     switch (bn) {
         PT_G2(256) PT_G2(192) PT_G2(128) PT_G2(64)

@@ -46,6 +46,9 @@ struct GemmDev {
     // causal / sliding-window band of self-attention products (pt_gemm_args.band): work that only meets
     // masked (query, key) pairs is not issued.  band_w = window (0: unbounded below).
     int band, band_w;
+    // second contraction segment (pt_gemm_args.K2): the accumulator also takes sum_k A2[m][k] * B2[n][k] over K2,
+    // read through a second pair of tensor maps after the main K blocks (LoRA: [x | t] . [W | B]^T in one pass)
+    int K2;
 };
 
 // K-block range [lo, hi) a tile must contract over, or skip = true when the whole tile is masked.
@@ -93,6 +96,7 @@ int encode_tiled_bf16_3d(CUtensorMap* out, const void* base, const unsigned long
 // t_aux / t_c: 2-D maps (32 x 32 boxes, 64-byte swizzle) of the aux matrix and of C for the epilogues that move their
 // tiles with TMA (PT_ACT_GEGLU_BWD); any valid map otherwise (unused).
 int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& t_aux, const CUtensorMap& t_c,
+                 const CUtensorMap& ta2, const CUtensorMap& tb2,
                  const GemmDev& p, cudaStream_t st);
 int gemm2_tiles(const GemmDev& p, int bn);
 

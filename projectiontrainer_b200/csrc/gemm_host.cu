@@ -224,6 +224,12 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         PT_REQUIRE(ff % 128 == 0 && (!geglu || a->N == 2 * ff), "pt_gemm_bf16: fused GeGLU needs ff %% 128 == 0 (ff=%d)", ff);
         PT_REQUIRE(a->ldc >= 2 * ff && a->ld_aux >= (geglu ? ff : 2 * ff), "pt_gemm_bf16: fused GeGLU: ldc / ld_aux too small");
     }
+    PT_REQUIRE(a->K2 >= 0, "pt_gemm_bf16: K2 must be >= 0");
+    if (a->K2 > 0) {
+        PT_REQUIRE(a->A2 && a->B2, "pt_gemm_bf16: K2 > 0 needs A2 and B2");
+        PT_REQUIRE(a->nz[0] * a->nz[1] * a->nz[2] == 1 && kg == 1 && a->band == PT_BAND_NONE,
+                   "pt_gemm_bf16: the second contraction segment is not batched, grouped or banded");
+    }
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
 
     GemmDev p;
@@ -297,7 +303,16 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     if (rc != PT_OK) return rc;
     rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn / 2, "B");
     if (rc != PT_OK) return rc;
-    CUtensorMap t_aux = ta, t_c = ta;
+    CUtensorMap t_aux = ta, t_c = ta, ta2 = ta, tb2 = tb;
+    p.K2 = a->K2;
+    if (a->K2 > 0) {
+        const int one[3] = {1, 1, 1};
+        const long long none[3] = {0, 0, 0};
+        rc = encode_operand(&ta2, a->A2, p.a_mn, a->M, a->K2, a->lda2, one, none, BM, "A2");
+        if (rc != PT_OK) return rc;
+        rc = encode_operand(&tb2, a->B2, p.b_mn, a->N, a->K2, a->ldb2, one, none, bn / 2, "B2");
+        if (rc != PT_OK) return rc;
+    }
     if (geglu_bwd) {
         // the GeGLU-backward epilogue moves its gate / up tiles in and its d_gate / d_up tiles out with TMA
         rc = encode_tiled_bf16_2d(&t_aux, a->aux, 2ll * p.ff, a->M, a->ld_aux, 32, 32, 64, "gu (epilogue)");
@@ -313,5 +328,5 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
             cudaMemsetAsync(p.delta, 0, static_cast<size_t>(a->M) * p.dl_hq * sizeof(float), st) != cudaSuccess)
             return check_launch("attn delta memset");
     }
-    return launch_gemm2(bn, ta, tb, t_aux, t_c, p, st);
+    return launch_gemm2(bn, ta, tb, t_aux, t_c, ta2, tb2, p, st);
 }

@@ -39,7 +39,7 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
              c_zs=(0, 0, 0), a_mn=False, b_mn=False, bias=None, residual=None, ldr=0,
              r_zs=(0, 0, 0), act=ACT_NONE, alpha=1.0, c_pre=None, kg=1, a_kgs=0, b_kgs=0,
              a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0, band=0, band_window=0, bn_hint=0,
-             aux2=None, aux_i0=0, aux_i1=0):
+             aux2=None, aux_i0=0, aux_i1=0, A2=None, lda2=0, B2=None, ldb2=0, K2=0):
     """Fully general launcher; A/B/Cout are tensors used only as base pointers
     (+ element offsets), all geometry comes from the explicit arguments."""
     _req_cuda(A, B, Cout, bias, residual, c_pre, aux)
@@ -84,20 +84,37 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
     if aux2 is not None:
         g.aux2 = aux2.data_ptr()
     g.aux_i0, g.aux_i1 = int(aux_i0), int(aux_i1)
+    if K2:
+        _req_cuda(A2, B2)
+        if A2.dtype != torch.bfloat16 or B2.dtype != torch.bfloat16:
+            raise RuntimeError("gemm operands must be bf16")
+        g.A2, g.lda2, g.B2, g.ldb2, g.K2 = A2.data_ptr(), int(lda2), B2.data_ptr(), int(ldb2), int(K2)
     if GEMM_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         _lib.call("pt_gemm_bf16", C.byref(g), _stream())
         e1.record()
         nb = int(nz[0]) * int(nz[1]) * int(nz[2])
-        GEMM_PROFILE.append((2.0 * M * N * K * nb * max(1, int(kg)), e0, e1, (M, N, K, nb, int(kg))))
+        GEMM_PROFILE.append((2.0 * M * N * (K * nb * max(1, int(kg)) + int(K2)), e0, e1, (M, N, K, nb, int(kg))))
         return
     _lib.call("pt_gemm_bf16", C.byref(g), _stream())
 
 
+def _seg2(M: int, N: int, a2, b2, b_mn: bool) -> dict:
+    """Second contraction segment (pt_gemm_args.K2) of a linear / dgrad launch: a2 [M, K2] K-major and b2 either
+    [N, K2] (forward: the LoRA B matrices) or [K2, N] read MN-major (input gradient: the LoRA A matrices)."""
+    if a2 is None:
+        return {}
+    K2 = a2.shape[1]
+    assert a2.shape[0] == M and a2.stride(1) == 1 and b2.stride(1) == 1
+    assert tuple(b2.shape) == ((K2, N) if b_mn else (N, K2)), (tuple(a2.shape), tuple(b2.shape), N)
+    return dict(A2=a2, lda2=a2.stride(0), B2=b2, ldb2=b2.stride(0), K2=K2)
+
+
 def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residual=None,
-           out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0) -> torch.Tensor:
-    """y[M,N] = act(x[M,K] @ w[N,K]^T + bias) (+ residual).  x, w bf16 row-major 2-D."""
+           out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0, x2=None, w2=None) -> torch.Tensor:
+    """y[M,N] = act(alpha * (x[M,K] @ w[N,K]^T (+ x2[M,K2] @ w2[N,K2]^T)) + bias) (+ residual).  bf16 row-major 2-D
+    operands."""
     M, K = x.shape
     N, K2 = w.shape
     assert K == K2 and x.stride(1) == 1 and w.stride(1) == 1
@@ -105,21 +122,23 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residua
         out = torch.empty((M, N), dtype=out_dtype, device=x.device)
     gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w, ldb=w.stride(0), Cout=out,
              ldc=out.stride(0), bias=bias, residual=residual,
-             ldr=0 if residual is None else residual.stride(0), act=act, alpha=alpha, c_pre=c_pre)
+             ldr=0 if residual is None else residual.stride(0), act=act, alpha=alpha, c_pre=c_pre,
+             **_seg2(M, N, x2, w2, False))
     return out
 
 
 def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out=None, out_dtype=torch.bfloat16,
-                 residual=None) -> torch.Tensor:
-    """dx[M,K] = dy[M,N] @ w[N,K] without transposing w (B operand MN-major)."""
+                 residual=None, alpha=1.0, dy2=None, w2=None) -> torch.Tensor:
+    """dx[M,K] = alpha * (dy[M,N] @ w[N,K] (+ dy2[M,N2] @ w2[N2,K])) (+ residual) without transposing w (B operands
+    MN-major)."""
     M, N = dy.shape
     N2, K = w.shape
     assert N == N2 and dy.stride(1) == 1 and w.stride(1) == 1
     if out is None:
         out = torch.empty((M, K), dtype=out_dtype, device=dy.device)
     gemm_raw(M=M, N=K, K=N, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True, Cout=out,
-             ldc=out.stride(0), residual=residual,
-             ldr=0 if residual is None else residual.stride(0))
+             ldc=out.stride(0), residual=residual, alpha=alpha,
+             ldr=0 if residual is None else residual.stride(0), **_seg2(M, K, dy2, w2, True))
     return out
 
 
@@ -145,23 +164,25 @@ def geglu_fusable(ff: int) -> bool:
     return ff % 128 == 0
 
 
-def linear_geglu(x: torch.Tensor, w_gu: torch.Tensor, gu: torch.Tensor, act: torch.Tensor, silu: bool = False):
+def linear_geglu(x: torch.Tensor, w_gu: torch.Tensor, gu: torch.Tensor, act: torch.Tensor, silu: bool = False,
+                 x2=None, w2=None):
     """gu[M,2ff] = x @ w_gu^T (gate | up pre-activations, kept for the backward) and, in the same
     epilogue, act[M,ff] = gelu_tanh(gate) * up   (HF:models/gemma3/modeling_gemma3.py:127-129)."""
     M, K = x.shape
     N = w_gu.shape[0]
     gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w_gu, ldb=w_gu.stride(0), Cout=gu, ldc=gu.stride(0),
-             act=ACT_SWIGLU if silu else ACT_GEGLU, aux=act, ld_aux=act.stride(0))
+             act=ACT_SWIGLU if silu else ACT_GEGLU, aux=act, ld_aux=act.stride(0), **_seg2(M, N, x2, w2, False))
 
 
 def linear_dgrad_geglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, d_gu: torch.Tensor,
-                           silu: bool = False):
+                           silu: bool = False, dy2=None, w2=None):
     """d_act = dy[M,h] @ w_down[h,ff] formed in TMEM only; the epilogue turns it into
     d_gu[M,2ff] = [d_act * up * gelu_tanh'(gate) | d_act * gelu_tanh(gate)] reading the saved gu."""
     M, N = dy.shape
     ff = w_down.shape[1]
     gemm_raw(M=M, N=ff, K=N, A=dy, lda=dy.stride(0), B=w_down, ldb=w_down.stride(0), b_mn=True, Cout=d_gu,
-             ldc=d_gu.stride(0), act=ACT_SWIGLU_BWD if silu else ACT_GEGLU_BWD, aux=gu, ld_aux=gu.stride(0))
+             ldc=d_gu.stride(0), act=ACT_SWIGLU_BWD if silu else ACT_GEGLU_BWD, aux=gu, ld_aux=gu.stride(0),
+             **_seg2(M, ff, dy2, w2, True))
 
 
 def linear_dgrad_gelu_erf_bwd(dy: torch.Tensor, w: torch.Tensor, Z: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
@@ -177,7 +198,7 @@ def linear_dgrad_gelu_erf_bwd(dy: torch.Tensor, w: torch.Tensor, Z: torch.Tensor
 
 
 def linear_dgrad_attn_delta(dy: torch.Tensor, w: torch.Tensor, O: torch.Tensor, out: torch.Tensor,
-                            delta: torch.Tensor, S: int, hd: int) -> torch.Tensor:
+                            delta: torch.Tensor, S: int, hd: int, dy2=None, w2=None) -> torch.Tensor:
     """out[M, hq*hd] = dy[M,N] @ w[N, hq*hd] (the o-projection input gradient dO) and, in the same epilogue,
     delta[(b*hq + head)*S + s] = sum_d dO * O over each head's hd columns (f32 [B*hq*S]; replaces attn_delta)."""
     M, N = dy.shape
@@ -186,7 +207,8 @@ def linear_dgrad_attn_delta(dy: torch.Tensor, w: torch.Tensor, O: torch.Tensor, 
     assert delta.numel() >= M * (K // hd)
     _req_cuda(delta)
     gemm_raw(M=M, N=K, K=N, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True, Cout=out, ldc=out.stride(0),
-             act=ACT_ATTN_DELTA, aux=O, ld_aux=O.stride(0), aux2=delta, aux_i0=S, aux_i1=hd)
+             act=ACT_ATTN_DELTA, aux=O, ld_aux=O.stride(0), aux2=delta, aux_i0=S, aux_i1=hd,
+             **_seg2(M, K, dy2, w2, True))
     return out
 
 
@@ -195,15 +217,17 @@ def attn_delta_fusable(hq: int, hd: int) -> bool:
     return hd % 128 == 0 and (hq * hd) % 256 == 0
 
 
-def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None) -> torch.Tensor:
-    """dw[N,K] = dy[M,N]^T @ x[M,K] (f32 out), both operands MN-major, no transposes."""
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None, alpha=1.0) -> torch.Tensor:
+    """dw[N,K] = alpha * dy[M,N]^T @ x[M,K] (f32 out), both operands MN-major, no transposes.  dy / x / out may be
+    column slices of wider matrices (LoRA: one adapter's columns of a packed projection)."""
     M, N = dy.shape
     M2, K = x.shape
     assert M == M2 and dy.stride(1) == 1 and x.stride(1) == 1
     if out is None:
         out = torch.empty((N, K), dtype=torch.float32, device=dy.device)
+    assert out.stride(1) == 1 and tuple(out.shape) == (N, K)
     gemm_raw(M=N, N=K, K=M, A=dy, lda=dy.stride(0), a_mn=True, B=x, ldb=x.stride(0), b_mn=True,
-             Cout=out, ldc=out.stride(0))
+             Cout=out, ldc=out.stride(0), alpha=alpha)
     return out
 
 

@@ -285,3 +285,86 @@ def test_gemm_fused_softmax_backward_epilogue(cuda_dev, S, W):
     inband = allowed[None, None].expand_as(got)
     assert bool(torch.isfinite(got[inband]).all())
     _check(got[inband], ref[inband], tol=2e-2, name="dS in band")
+
+
+@pytest.mark.parametrize("M,N,K,K2", [(703, 1536, 1152, 64), (22496, 1152, 1024, 64), (300, 256, 200, 128),
+                                      (1000, 13824, 1152, 64), (128, 64, 64, 64)])
+def test_gemm_second_contraction_segment(cuda_dev, M, N, K, K2):
+    """C = [A | A2] . [B | B2]^T (pt_gemm_args.K2): the LoRA ride-along, forward (all operands K-major) and input
+    gradient (B operands MN-major), against the two products summed in fp32."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(M + K2)
+    x, w = _rand((M, K), cuda_dev), _rand((N, K), cuda_dev, 0.05)
+    t, b = _rand((M, K2), cuda_dev), _rand((N, K2), cuda_dev, 0.05)
+    ref = x.float() @ w.float().t() + t.float() @ b.float().t()
+    _check(ops.linear(x, w, x2=t, w2=b), ref, name="fwd bf16")
+    _check(ops.linear(x, w, x2=t, w2=b, out_dtype=torch.float32), ref, tol=1e-3, name="fwd f32")
+    res = torch.randn(M, N, device=cuda_dev)
+    _check(ops.linear(x, w, x2=t, w2=b, residual=res, out_dtype=torch.float32), ref + res, tol=1e-3, name="fwd + residual")
+    # dx[M, K] = dy[M, N] @ w[N, K] + dt[M, K2] @ a[K2, K]
+    dy, dt, a = _rand((M, N), cuda_dev), _rand((M, K2), cuda_dev), _rand((K2, K), cuda_dev, 0.05)
+    ref = dy.float() @ w.float() + dt.float() @ a.float()
+    _check(ops.linear_dgrad(dy, w, dy2=dt, w2=a, out_dtype=torch.float32), ref, tol=1e-3, name="dgrad f32")
+    _check(ops.linear_dgrad(dy, w, dy2=dt, w2=a), ref, name="dgrad bf16")
+    # without a segment the launcher is what it was
+    _check(ops.linear_dgrad(dy, w, out_dtype=torch.float32), dy.float() @ w.float(), tol=1e-3, name="no segment")
+
+
+def test_gemm_second_segment_under_fused_epilogues(cuda_dev):
+    """The segment feeds the same accumulator the fused epilogues read: GeGLU forward / backward and the attention
+    delta epilogue with adapters riding along."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(3)
+    M, h, ff, R = 600, 256, 512, 64
+    x, w = _rand((M, h), cuda_dev), _rand((2 * ff, h), cuda_dev, 0.06)
+    t, b = _rand((M, R), cuda_dev), _rand((2 * ff, R), cuda_dev, 0.06)
+    gu, act = torch.empty(M, 2 * ff, device=cuda_dev, dtype=torch.bfloat16), torch.empty(M, ff, device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_geglu(x, w, gu, act, x2=t, w2=b)
+    gu_ref = x.float() @ w.float().t() + t.float() @ b.float().t()
+    _check(gu, gu_ref, name="gu")
+    g_, u_ = gu.float()[:, :ff], gu.float()[:, ff:]
+    _check(act, torch.nn.functional.gelu(g_, approximate="tanh") * u_, name="act")
+    # down-projection input gradient with the GeGLU backward in the epilogue
+    dy, wd = _rand((M, h), cuda_dev), _rand((h, ff), cuda_dev, 0.06)
+    dt, a = _rand((M, R), cuda_dev), _rand((R, ff), cuda_dev, 0.06)
+    d_gu = torch.empty(M, 2 * ff, device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_dgrad_geglu_bwd(dy, wd, gu, d_gu, dy2=dt, w2=a)
+    d_act = dy.float() @ wd.float() + dt.float() @ a.float()
+    gr = g_.clone().requires_grad_(True)
+    ur = u_.clone().requires_grad_(True)
+    (torch.nn.functional.gelu(gr, approximate="tanh") * ur).backward(d_act)
+    _check(d_gu[:, :ff], gr.grad, name="d_gate")
+    _check(d_gu[:, ff:], ur.grad, name="d_up")
+    # o-projection input gradient + delta
+    B, S, hq, hd = 2, 300, 2, 128
+    dy, wo = _rand((B * S, h), cuda_dev), _rand((h, hq * hd), cuda_dev, 0.06)
+    dt, a = _rand((B * S, R), cuda_dev), _rand((R, hq * hd), cuda_dev, 0.06)
+    O = _rand((B * S, hq * hd), cuda_dev)
+    d_o = torch.empty(B * S, hq * hd, device=cuda_dev, dtype=torch.bfloat16)
+    delta = torch.empty(B * hq * S, device=cuda_dev)
+    ops.linear_dgrad_attn_delta(dy, wo, O, d_o, delta, S, hd, dy2=dt, w2=a)
+    ref = dy.float() @ wo.float() + dt.float() @ a.float()
+    _check(d_o, ref, name="d_o")
+    dref = (ref * O.float()).view(B, S, hq, hd).sum(-1).permute(0, 2, 1).reshape(-1)
+    _check(delta, dref, tol=2e-2, name="delta")
+
+
+def test_gemm_wgrad_on_column_slices(cuda_dev):
+    """One adapter's weight gradient: dB_i = dy[:, rows_i]^T t[:, i*r:(i+1)*r] written into a diagonal block of a
+    wider f32 matrix — operand and output views with their parents' row strides, 16-column output."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(4)
+    T, out, R, r = 1406, 1536, 64, 16
+    dy, t = _rand((T, out), cuda_dev), _rand((T, R), cuda_dev)
+    gB = torch.full((out, R), 7.0, device=cuda_dev)
+    blocks = [(0, 1024), (1024, 256), (1280, 256)]
+    for i, (r0, n) in enumerate(blocks):
+        ops.linear_wgrad(dy[:, r0:r0 + n], t[:, i * r:(i + 1) * r], out=gB[r0:r0 + n, i * r:(i + 1) * r])
+        ref = dy[:, r0:r0 + n].float().t() @ t[:, i * r:(i + 1) * r].float()
+        _check(gB[r0:r0 + n, i * r:(i + 1) * r], ref, tol=2e-3, name=f"block {i}")
+    mask = torch.ones(out, R, dtype=torch.bool, device=cuda_dev)
+    for i, (r0, n) in enumerate(blocks):
+        mask[r0:r0 + n, i * r:(i + 1) * r] = False
+    assert (gB[mask] == 7.0).all()          # nothing outside the diagonal blocks was written
+    dt, x = _rand((T, R), cuda_dev), _rand((T, 1152), cuda_dev)
+    _check(ops.linear_wgrad(dt, x, alpha=2.0), 2.0 * dt.float().t() @ x.float(), tol=2e-3, name="dA")
