@@ -6,7 +6,9 @@ transformers; only the vectors it writes travel to the GPU box.
 
 What runs: the reference's own `VQATrainerStage2.train()` and `vqa_collate_fn`
 (/root/reference/Stage2/trainer.py:18, 63, 268) with `freeze_llm=True, freeze_projection_layer=False,
-freeze_vision_encoder=True, enable_qlora=False` — the frozen-LLM variant SURVEY.md §8(f) rank 2 names —
+freeze_vision_encoder=True, enable_qlora=False` — the frozen-LLM variant SURVEY.md §8(f) rank 2 names — and, for the
+vqa_lora_* cases, with `enable_qlora=True` on an LLM whose projection Linears are wrapped by a hand-rolled LoRA module
+(`LoRALinear` below = peft's forward with dropout 0; peft itself is not in this image) —
 on HF `SiglipVisionModel` / `Gemma3ForCausalLM` built from explicit configs on CPU in fp32, with the
 reference's `MLPProjector` (Stage1/projectors.py).  Stand-ins, because `accelerate` is not installed in
 this image:
@@ -90,7 +92,8 @@ class _PreparedLoader:
 
 
 class SingleProcessAccelerator:
-    def __init__(self, grad_accum: int, rec: Recorder, projector_ref):
+    def __init__(self, grad_accum: int, rec: Recorder, projector_ref, llm_ref=None):
+        self._llm = llm_ref
         self.device = torch.device("cpu")
         self.is_main_process = True
         self.num_processes, self.process_index = 1, 0
@@ -130,7 +133,12 @@ class SingleProcessAccelerator:
 
     def clip_grad_norm_(self, params, max_norm):
         assert max_norm == 1.0
-        self._cur = {"grads": {n: p.grad.detach().clone() for n, p in self._proj.named_parameters()}}
+        if self._cur is None:       # first module of this optimizer step: nothing has been clipped yet
+            self._cur = {"grads": {n: p.grad.detach().clone() for n, p in self._proj.named_parameters()
+                                   if p.grad is not None}}
+            if self._llm is not None:
+                self._cur["lora_grads"] = {n: p.grad.detach().clone() for n, p in self._llm.named_parameters()
+                                           if p.requires_grad}
         return torch.nn.utils.clip_grad_norm_(list(params), max_norm)
 
     def gather(self, t):
@@ -143,6 +151,9 @@ class SingleProcessAccelerator:
         if "train/step_loss" in d and self._cur is not None:
             self._cur["lr_after"] = float(d["train/learning_rate"])
             self._cur["params"] = {n: p.detach().clone() for n, p in self._proj.named_parameters()}
+            if self._llm is not None:
+                self._cur["lora_params"] = {n: p.detach().clone() for n, p in self._llm.named_parameters()
+                                            if p.requires_grad}
             self._rec.steps.append(self._cur)
             self._cur = None
         if "val/loss" in d:
@@ -177,9 +188,53 @@ class Tok:
     def batch_decode(self, ids, skip_special_tokens=True):
         return [" ".join(str(int(t)) for t in row) for row in ids]
 
+    def save_pretrained(self, path):
+        pass
+
+
+class LoRALinear(torch.nn.Module):
+    """peft.tuners.lora.layer.Linear, forward only, dropout p = 0 (peft is not in this image):
+    result = base_layer(x) + lora_B(lora_A(x)) * scaling."""
+
+    def __init__(self, base: torch.nn.Linear, r: int, alpha: float):
+        super().__init__()
+        self.base_layer = base
+        self.lora_A = torch.nn.Linear(base.in_features, r, bias=False)
+        self.lora_B = torch.nn.Linear(r, base.out_features, bias=False)
+        self.scaling = alpha / r
+
+    def forward(self, x):
+        return self.base_layer(x) + self.lora_B(self.lora_A(x)) * self.scaling
+
+
+def inject_lora(llm, lora: dict, r: int, alpha: float, targets):
+    """What `get_peft_model(llm, LoraConfig(...))` does to the module tree (ref:Stage2/train_vqa_stage2.py:225-246):
+    every target Linear of every decoder layer is wrapped, the base model is frozen, the adapters train."""
+    llm.requires_grad_(False)
+    for i, layer in enumerate(llm.model.layers):
+        for t in targets:
+            parent = layer.self_attn if t in ("q_proj", "k_proj", "v_proj", "o_proj") else layer.mlp
+            w = LoRALinear(getattr(parent, t), r, alpha)
+            with torch.no_grad():
+                w.lora_A.weight.copy_(lora[f"l{i}.{t}.A"])
+                w.lora_B.weight.copy_(lora[f"l{i}.{t}.B"])
+            setattr(parent, t, w)
+    return llm
+
+
+def _lora_key(name: str) -> str:
+    """HF parameter name `model.layers.3.self_attn.q_proj.lora_A.weight` -> oracle key `l3.q_proj.A`."""
+    parts = name.split(".")
+    return f"l{parts[2]}.{parts[4]}.{parts[5][-1]}"
+
 
 def run_case(name: str, out_dir: Path):
-    vkw, lkw, n_train, n_val, B, side, accum, epochs, warm = CASES[name]
+    lora_cfg = None
+    if name in O2.LORA_CASES:
+        *base, lora_cfg = O2.LORA_CASES[name]
+        vkw, lkw, n_train, n_val, B, side, accum, epochs, warm = base
+    else:
+        vkw, lkw, n_train, n_val, B, side, accum, epochs, warm = CASES[name]
     import transformers                                  # resolves its own optional-dependency checks first
     from transformers import get_cosine_schedule_with_warmup  # noqa: F401
     install_accelerate_stub()
@@ -195,8 +250,14 @@ def run_case(name: str, out_dir: Path):
     px_t, q_t, a_t = O2.synthetic_vqa_samples(n_train, vc, lc, seed=4321)
     px_v, q_v, a_v = O2.synthetic_vqa_samples(n_val, vc, lc, seed=9876)
 
+    train_proj = True
+    if lora_cfg is not None:
+        r, alpha, targets, b_std, train_proj = lora_cfg
+        L0 = O2.init_lora(lc, r, targets, b_std=b_std)
+        inject_lora(llm, L0, r, alpha, targets)
+
     rec = Recorder()
-    acc = SingleProcessAccelerator(accum, rec, proj)
+    acc = SingleProcessAccelerator(accum, rec, proj, llm if lora_cfg is not None else None)
 
     def vis_pre(mod, args, kwargs):
         if acc._in_train:
@@ -216,8 +277,8 @@ def run_case(name: str, out_dir: Path):
         tokenizer=Tok(lc.pad_id, side), train_dataset=VQAList(px_t, q_t, a_t),
         val_dataset=VQAList(px_v, q_v, a_v), output_dir=str(out_dir / "_tmp_vqa"), batch_size=B,
         learning_rate=1e-3, weight_decay=0.01, num_epochs=epochs, gradient_accumulation_steps=accum,
-        warmup_ratio=warm, freeze_vision_encoder=True, freeze_projection_layer=False, freeze_llm=True,
-        enable_qlora=False, train_ve_first_epoch=False, wandb_project="none")
+        warmup_ratio=warm, freeze_vision_encoder=True, freeze_projection_layer=not train_proj, freeze_llm=True,
+        enable_qlora=lora_cfg is not None, train_ve_first_epoch=False, wandb_project="none")
     t0 = time.time()
     tr.train()
     print(f"[{name}] reference train(): {len(rec.micro)} micro-batches, {len(rec.steps)} optimizer steps, "
@@ -240,9 +301,16 @@ def run_case(name: str, out_dir: Path):
         save[f"step{i}.lr_after"] = np.array(s["lr_after"])
         for n, g in s["grads"].items():
             save[f"step{i}.grad.{n}"] = g.float().numpy()
+        for n, g in s.get("lora_grads", {}).items():
+            save[f"step{i}.lora_grad.{_lora_key(n)}"] = g.float().numpy()
         if i == len(rec.steps) - 1:
             for n, p in s["params"].items():
                 save[f"step{i}.param.{n}"] = p.float().numpy()
+            for n, p in s.get("lora_params", {}).items():
+                save[f"step{i}.lora_param.{_lora_key(n)}"] = p.float().numpy()
+    if lora_cfg is not None:
+        save.update({"lora_r": r, "lora_alpha": alpha, "lora_targets": np.array(list(targets)), "lora_b_std": b_std,
+                     "train_projector": int(train_proj)})
     out_dir.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(out_dir / f"{name}.npz", **save)
     import shutil
@@ -253,5 +321,5 @@ def run_case(name: str, out_dir: Path):
 if __name__ == "__main__":
     torch.set_num_threads(8)
     only = sys.argv[1] if len(sys.argv) > 1 else None
-    for n in ([only] if only else CASES):
+    for n in ([only] if only else [*CASES, *O2.LORA_CASES]):
         run_case(n, GOLDEN)

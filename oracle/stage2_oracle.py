@@ -1,4 +1,4 @@
-"""CPU oracle for the Stage-2 VQA step, frozen-LLM variant.  TEST INFRASTRUCTURE ONLY.
+"""CPU oracle for the Stage-2 VQA step: frozen LLM, optionally with LoRA adapters.  TEST INFRASTRUCTURE ONLY.
 
 Only tests/ may import this module (see oracle/stage1_oracle.py for the rule); the product path
 (projectiontrainer_b200/) never does.
@@ -37,6 +37,72 @@ GOLDEN_CASES = {
 }
 
 
+# LoRA fixtures (oracle/make_golden_stage2.py, `enable_qlora=True` with a hand-rolled adapter wrapper — peft is not in
+# this image): the tuple above + (rank, lora_alpha, target modules, std of the initial B, projector trains?)
+ALL_TARGETS = ("q_proj", "k_proj", "v_proj", "o_proj", "gate_proj", "up_proj", "down_proj")
+LORA_CASES = {
+    "vqa_lora_all_right": (dict(hidden=64, ff=128, layers=2, heads=2, image=64, patch=16),
+                           dict(vocab=512, hidden=64, ff=128, layers=4, hq=4, hkv=2, hd=16, window=8,
+                                q_scalar=16.0, rope_factor_global=8.0), 5, 2, 2, "right", 2, 2, 0.25,
+                           (8, 16.0, ALL_TARGETS, 0.02, True)),
+    "vqa_lora_qvd_left_frozen_proj": (dict(hidden=64, ff=128, layers=1, heads=4, image=48, patch=16),
+                                      dict(vocab=304, hidden=48, ff=96, layers=3, hq=4, hkv=1, hd=32, window=5,
+                                           q_scalar=32.0), 4, 2, 2, "left", 1, 2, 0.0,
+                                      (16, 32.0, ("q_proj", "v_proj", "down_proj"), 0.05, False)),
+}
+
+
+# --------------------------------------------------------------------------- LoRA adapters
+def lora_target_rows(cfg: O.GemmaCfg):
+    """target module -> (packed weight of the Stage-1 oracle, first row, rows, input width)."""
+    qd, kd = cfg.hq * cfg.hd, cfg.hkv * cfg.hd
+    return {"q_proj": ("qkv_w", 0, qd, cfg.hidden), "k_proj": ("qkv_w", qd, kd, cfg.hidden),
+            "v_proj": ("qkv_w", qd + kd, kd, cfg.hidden), "o_proj": ("o_w", 0, cfg.hidden, qd),
+            "gate_proj": ("gu_w", 0, cfg.ff, cfg.hidden), "up_proj": ("gu_w", cfg.ff, cfg.ff, cfg.hidden),
+            "down_proj": ("down_w", 0, cfg.hidden, cfg.ff)}
+
+
+def init_lora(cfg: O.GemmaCfg, r: int, targets, seed: int = 7, b_std: float = 0.0) -> dict:
+    """{"l<i>.<target>.A": [r, in], "l<i>.<target>.B": [out, r]}: A as peft initialises it (kaiming_uniform_ with
+    a = sqrt(5), i.e. U(+-1/sqrt(in))), B zero as in peft or N(0, b_std) so that a fixture exercises every gradient
+    path from the first step (with B = 0 the first dA is identically zero)."""
+    g = torch.Generator().manual_seed(seed)
+    rows = lora_target_rows(cfg)
+    out = {}
+    for i in range(cfg.layers):
+        for t in targets:
+            _, _, n, in_dim = rows[t]
+            out[f"l{i}.{t}.A"] = (torch.rand(r, in_dim, generator=g) * 2 - 1) / in_dim ** 0.5
+            out[f"l{i}.{t}.B"] = torch.randn(n, r, generator=g) * b_std
+    return out
+
+
+def lora_merge(Wl: dict, lora: dict, cfg: O.GemmaCfg, scale: float) -> dict:
+    """peft `Linear.forward`: result = base(x) + lora_B(lora_A(dropout(x))) * scaling, dropout p = 0, written on the
+    weights: W + scale * B A for every adapted target (the same function of A and B, so autograd through this gives
+    the adapter gradients).  ref:Stage2/train_vqa_stage2.py:225-250 builds the adapters."""
+    rows = lora_target_rows(cfg)
+    W = dict(Wl)
+    for i in range(cfg.layers):
+        by_w: dict = {}
+        for t, (wname, r0, n, _) in rows.items():
+            if f"l{i}.{t}.A" in lora:
+                by_w.setdefault(wname, []).append((r0, n, lora[f"l{i}.{t}.B"] @ lora[f"l{i}.{t}.A"]))
+        for wname, parts in by_w.items():
+            base = Wl[f"l{i}.{wname}"]
+            zero = torch.zeros_like(base)
+            pieces, at = [], 0
+            for r0, n, d in sorted(parts, key=lambda q: q[0]):
+                if r0 > at:
+                    pieces.append(zero[at:r0])
+                pieces.append(scale * d)
+                at = r0 + n
+            if at < base.shape[0]:
+                pieces.append(zero[at:])
+            W[f"l{i}.{wname}"] = base + torch.cat(pieces, dim=0)
+    return W
+
+
 # --------------------------------------------------------------------------- collate (integer, bit-exact)
 def vqa_collate(questions: list, answers: list, pad_id: int, padding_side: str = "right"):
     """ref:Stage2/trainer.py:18-61 — pad every question to the batch's longest question and every
@@ -69,7 +135,8 @@ def vqa_masks_labels(q_ids: np.ndarray, a_ids: np.ndarray, n_img: int, pad_id: i
     return attn, labels
 
 
-def vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg: O.SiglipCfg, lcfg: O.GemmaCfg, scale_dtype=None):
+def vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg: O.SiglipCfg, lcfg: O.GemmaCfg, scale_dtype=None,
+                lora: dict | None = None, lora_scale: float = 1.0):
     """ref:Stage2/trainer.py:311-416 — frozen SigLIP, `[:, 1:, :]`, projector, Gemma3 embedding * scale
     for question and answer, concatenation, frozen Gemma3, fp32 shifted CE.  Returns (loss tensor,
     dict of what the reference hands to the language model)."""
@@ -80,6 +147,8 @@ def vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg: O.SiglipCfg, lcfg: O.Gemm
     proj = O.projector_forward(patch, P)
     X0 = torch.cat([proj, q_emb.to(proj.dtype), a_emb.to(proj.dtype)], dim=1)
     attn, labels = vqa_masks_labels(q_ids.numpy(), a_ids.numpy(), proj.shape[1], lcfg.pad_id)
+    if lora is not None:
+        Wl = lora_merge(Wl, lora, lcfg, lora_scale)
     hidden = O.gemma3_hidden(X0, torch.from_numpy(attn), Wl, lcfg)
     loss, n_valid = O.causal_lm_loss(hidden, Wl, lcfg, labels)
     return loss, dict(spliced=X0, attention_mask=attn, lm_labels=labels, n_valid=n_valid,
@@ -87,21 +156,26 @@ def vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg: O.SiglipCfg, lcfg: O.Gemm
 
 
 def vqa_micro_step(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, loss_divisor: float = 1.0,
-                   scale_dtype=None):
-    """One micro-batch forward+backward: the loss as logged (undivided) and the projector gradients
-    of loss / loss_divisor (ref:Stage2/trainer.py:418-420)."""
-    P = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
-    loss, aux = vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype)
+                   scale_dtype=None, lora: dict | None = None, lora_scale: float = 1.0, train_projector: bool = True):
+    """One micro-batch forward+backward: the loss as logged (undivided) and the projector (and adapter)
+    gradients of loss / loss_divisor (ref:Stage2/trainer.py:418-420)."""
+    P = {k: v.detach().clone().requires_grad_(train_projector) for k, v in P.items()}
+    if lora is not None:
+        lora = {k: v.detach().clone().requires_grad_(True) for k, v in lora.items()}
+    loss, aux = vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype, lora, lora_scale)
     (loss / loss_divisor).backward()
-    out = {"loss": float(loss.detach()), "grads": {k: v.grad.detach() for k, v in P.items()}}
+    out = {"loss": float(loss.detach()),
+           "grads": {k: v.grad.detach() for k, v in P.items()} if train_projector else {}}
+    if lora is not None:
+        out["lora_grads"] = {k: v.grad.detach() for k, v in lora.items()}
     out.update({k: (v.detach() if torch.is_tensor(v) else v) for k, v in aux.items()})
     return out
 
 
 @torch.no_grad()
-def vqa_eval_loss(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype=None) -> float:
+def vqa_eval_loss(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype=None, lora=None, lora_scale=1.0) -> float:
     """ref:Stage2/trainer.py:517-590 — the validation loss of one batch (same arithmetic, no backward)."""
-    loss, _ = vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype)
+    loss, _ = vqa_forward(pixels, q_ids, a_ids, Wv, P, Wl, vcfg, lcfg, scale_dtype, lora, lora_scale)
     return float(loss)
 
 
