@@ -13,6 +13,7 @@ cross-entropy internals, fp32 projector master weights, gradients and AdamW stat
 """
 from __future__ import annotations
 
+import contextlib
 import math
 import os
 from collections import OrderedDict
@@ -178,8 +179,15 @@ class Stage1Engine:
     """One data-parallel rank of the Stage-1 step on one B200."""
 
     def __init__(self, vis: PackedSiglip, llm: PackedGemma, proj: ProjectorState, device,
-                 grad_accum: int = 1, loss_divisor: float | None = None):
+                 grad_accum: int = 1, loss_divisor: float | None = None, lora=None, train_projector: bool = True):
         self.vis, self.llm, self.proj = vis, llm, proj
+        # Stage 2 with --enable_qlora: LoRA adapters on the decoder projections (lora.LoraState); the decoder then
+        # also runs weight-gradient GEMMs for the adapter matrices.  train_projector=False freezes the projector
+        # (ref:Stage2/trainer.py:214-217) — only valid together with adapters.
+        self.lora = lora
+        self.train_projector = bool(train_projector)
+        if not self.train_projector and lora is None:
+            raise ValueError("No trainable parameters found. Check freezing configuration and QLoRA setup.")
         self.vcfg, self.lcfg = vis.cfg, llm.cfg
         self.device = device
         # gradients are those of loss / loss_divisor (the reference divides by gradient_accumulation_steps
@@ -384,13 +392,15 @@ class Stage1Engine:
         G, ld, QKV = self._attn_geometry(B, S)
         scale = c.q_scalar ** -0.5
         sv = []
-        a = self.buf("l_a", (M, h), BF16)
+        lo = self.lora
+        keep = save and lo is not None          # adapter weight gradients need every projection's input
+        abuf = lambda li, which: self.buf(f"l{li}_a{which}" if keep else "l_a", (M, h), BF16)
+        a = abuf(0, "in")
         sc = None if self.fuse_attn_fwd else self.buf("l_scores", (B * hq, S, ld), F32)
         kvbits = None
         if self.fuse_attn_fwd and keyvalid is not None:
             kvbits = self.buf("l_kvbits", (B * ((S + 63) // 64),), torch.int64)
             ops.pack_keyvalid(keyvalid.view(B, S), kvbits)
-        act = self.buf("l_act", (M, ff), BF16)
         x = x0
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
         rope_rows, tabs = S, {f: self.rope(S, f) for f in (True, False)}
@@ -415,7 +425,20 @@ class Stage1Engine:
             gu = self.buf(tag + "gu", (M, 2 * ff), BF16)
             y_mlp = self.buf(tag + "ym", (M, h), BF16) if c.sandwich_norm else None
             x2 = self.buf(tag + ("x2" if save else f"x2_{li & 1}"), (M, h), F32)
-            ops.linear(a, L["qkv_w"], out=qkv)
+            act = self.buf(f"l{li}_act" if keep else "l_act", (M, ff), BF16)
+            a_in, ts = a, {}
+
+            def adapter(g, x_in, _li=li, _tag=tag, _ts=ts):
+                """t = (alpha / r) * x A_cat^T of packed projection g -> the (x2, w2) segment of its base GEMM."""
+                grp = None if lo is None else lo.layers[_li].get(g)
+                if grp is None:
+                    return {}
+                t = self.buf(_tag + "t_" + g, (M, grp.R), BF16)
+                ops.linear(x_in, grp.A(lo.shadow), out=t, alpha=lo.scale)
+                _ts[g] = t
+                return dict(x2=t, w2=grp.B(lo.shadow))
+
+            ops.linear(a_in, L["qkv_w"], out=qkv, **adapter("qkv", a_in))
             ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, rope_rows, hq,
                                 hkv, hd, c.eps)
             if cache is not None:      # KV-cache fill: device-to-device copies (plumbing, no arithmetic)
@@ -434,29 +457,31 @@ class Stage1Engine:
                              a_zs=(S * ld, G * S * ld, hq * S * ld), b_zs=(0, hd, S * QKV),
                              c_zs=(hd, G * hd, S * hq * hd), band=ops.BAND_K_BY_QUERY, band_window=win)
             last = li == len(Lm.layers) - 1
+            a_ffn = abuf(li, "ffn")
             if c.sandwich_norm:
-                ops.linear(attn_o, L["o_w"], out=y_attn)
-                ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+                ops.linear(attn_o, L["o_w"], out=y_attn, **adapter("o", attn_o))
+                ops.rmsnorm_residual_fwd(y_attn, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a_ffn, c.eps)
             else:       # pre-norm decoder (Qwen3): the residual add rides the o-projection epilogue, in f32
-                ops.linear(attn_o, L["o_w"], out=x1, residual=x)
-                ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a, c.eps)
+                ops.linear(attn_o, L["o_w"], out=x1, residual=x, **adapter("o", attn_o))
+                ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a_ffn, c.eps)
             if self.fuse_geglu:
-                ops.linear_geglu(a, L["gu_w"], gu, act, silu=c.silu)
+                ops.linear_geglu(a_ffn, L["gu_w"], gu, act, silu=c.silu, **adapter("gu", a_ffn))
             else:
-                ops.linear(a, L["gu_w"], out=gu)
+                ops.linear(a_ffn, L["gu_w"], out=gu, **adapter("gu", a_ffn))
                 ops.geglu_fwd(gu, act, silu=c.silu)
+            a = a_ffn if last else abuf(li + 1, "in")
             if c.sandwich_norm:
-                ops.linear(act, L["down_w"], out=y_mlp)
+                ops.linear(act, L["down_w"], out=y_mlp, **adapter("down", act))
                 ops.rmsnorm_residual_fwd(y_mlp, L["post_ffn_norm"], x1, x2,
                                          None if last else Lm.layers[li + 1]["in_norm"],
                                          None if last else a, c.eps)
             else:
-                ops.linear(act, L["down_w"], out=x2, residual=x1)
+                ops.linear(act, L["down_w"], out=x2, residual=x1, **adapter("down", act))
                 if not last:
                     ops.rmsnorm_fwd(x2, Lm.layers[li + 1]["in_norm"], a, c.eps)
             if save:
                 sv.append(dict(x_in=x, qkv=qkv, q=q_post, k=k_post, P=P, lse=lse, kvbits=kvbits, ao=attn_o, ya=y_attn,
-                               x1=x1, gu=gu, ym=y_mlp, full=full))
+                               x1=x1, gu=gu, ym=y_mlp, full=full, a_in=a_in, a_ffn=a_ffn, act=act, t=ts))
             x = x2
         return x, sv
 
@@ -542,6 +567,28 @@ class Stage1Engine:
                               *(torch.cuda.Event() for _ in range(4)))
             sv, sk, ev_do, ev_dv, ev_ds, ev_dk = self._side
             main = torch.cuda.current_stream()
+        lo = self.lora
+
+        def lora_pre(li, g, dy):
+            """dt = (alpha / r) * dy B_blk of packed projection g -> the (dy2, w2) segment of its input-gradient GEMM."""
+            grp = None if lo is None else lo.layers[li].get(g)
+            if grp is None:
+                return {}, None
+            dt = self.buf("b_dt_" + g, (M, grp.R), BF16)
+            ops.linear_dgrad(dy, grp.B(lo.shadow), out=dt, alpha=lo.scale)
+            return dict(dy2=dt, w2=grp.A(lo.shadow)), (grp, dt)
+
+        def lora_wgrad(st, dy, x_in, t):
+            """dA_cat = dt^T x (rows past the adapters' ranks come out zero: those dt columns are);
+            dB_i = dy_i^T t_i into the i-th diagonal block."""
+            if st is None:
+                return
+            grp, dt = st
+            ops.linear_wgrad(dt, x_in, out=grp.A(lo.grad))
+            gB, r = grp.B(lo.grad), lo.r
+            for _, r0, n, i in grp.parts:
+                ops.linear_wgrad(dy[:, r0:r0 + n], t[:, i * r:(i + 1) * r], out=gB[r0:r0 + n, i * r:(i + 1) * r])
+
         for li in range(len(Lm.layers) - 1, -1, -1):
             L, a = Lm.layers[li], s["layers"][li]
             cos_t, sin_t = self.rope(S, a["full"])
@@ -550,12 +597,16 @@ class Stage1Engine:
                 ops.cast_f32_bf16(dx, d_y)
             elif li == len(Lm.layers) - 1 or not pair:
                 ops.rmsnorm_bwd(dx, a["ym"], L["post_ffn_norm"], d_y, c.eps)
+            pre, st = lora_pre(li, "down", d_y)
             if self.fuse_geglu:
-                ops.linear_dgrad_geglu_bwd(d_y, L["down_w"], a["gu"], d_gu, silu=c.silu)
+                ops.linear_dgrad_geglu_bwd(d_y, L["down_w"], a["gu"], d_gu, silu=c.silu, **pre)
             else:
-                ops.linear_dgrad(d_y, L["down_w"], out=d_act)
+                ops.linear_dgrad(d_y, L["down_w"], out=d_act, **pre)
                 ops.geglu_bwd(d_act, a["gu"], d_gu, silu=c.silu)
-            ops.linear_dgrad(d_gu, L["gu_w"], out=d_y)
+            lora_wgrad(st, d_y, a["act"], a["t"].get("down"))
+            pre, st = lora_pre(li, "gu", d_gu)
+            lora_wgrad(st, d_gu, a["a_ffn"], a["t"].get("gu"))
+            ops.linear_dgrad(d_gu, L["gu_w"], out=d_y, **pre)
             # ---- attention branch (pre-ffn norm backward + post-attention norm backward in one pass)
             if pair:
                 ops.rmsnorm_bwd_pair(d_y, a["x1"], L["pre_ffn_norm"], dx, a["ya"], L["post_attn_norm"], d_y, c.eps)
@@ -566,11 +617,13 @@ class Stage1Engine:
                 else:
                     ops.cast_f32_bf16(dx, d_y)
             win = 0 if a["full"] else c.window
+            pre, st = lora_pre(li, "o", d_y)
             if fused_attn and self.fuse_attn_delta:
                 # o-projection input gradient with delta = rowsum(dO * O) formed in its epilogue
-                ops.linear_dgrad_attn_delta(d_y, L["o_w"], a["ao"], d_o, delta, S, hd)
+                ops.linear_dgrad_attn_delta(d_y, L["o_w"], a["ao"], d_o, delta, S, hd, **pre)
             else:
-                ops.linear_dgrad(d_y, L["o_w"], out=d_o)
+                ops.linear_dgrad(d_y, L["o_w"], out=d_o, **pre)
+            lora_wgrad(st, d_y, a["ao"], a["t"].get("o"))
             if fused_attn:
                 # dK, dV and dS in one key/value-stationary kernel; dQ = dS K as a band GEMM
                 dS = dS_by_band[a["full"]]
@@ -591,7 +644,9 @@ class Stage1Engine:
                                  band_window=win)
                 ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                     hkv, hd, c.eps)
-                ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)
+                pre, st = lora_pre(li, "qkv", d_qkv)
+                lora_wgrad(st, d_qkv, a["a_in"], a["t"].get("qkv"))
+                ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y, **pre)
                 if pair and li > 0:     # input-norm backward + the previous layer's post-ffn norm backward
                     prev = s["layers"][li - 1]
                     ops.rmsnorm_bwd_pair(d_y, a["x_in"], L["in_norm"], dx, prev["ym"],
@@ -646,7 +701,9 @@ class Stage1Engine:
                 dk_gemm()
             ops.qknorm_rope_bwd(dq, dk, a["qkv"], L["q_norm"], L["k_norm"], cos_t, sin_t, d_qkv, S, hq,
                                 hkv, hd, c.eps)
-            ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y)
+            pre, st = lora_pre(li, "qkv", d_qkv)
+            lora_wgrad(st, d_qkv, a["a_in"], a["t"].get("qkv"))
+            ops.linear_dgrad(d_qkv, L["qkv_w"], out=d_y, **pre)
             if pair and li > 0:     # input-norm backward + the previous layer's post-ffn norm backward
                 prev = s["layers"][li - 1]
                 ops.rmsnorm_bwd_pair(d_y, a["x_in"], L["in_norm"], dx, prev["ym"],
@@ -684,12 +741,55 @@ class Stage1Engine:
                        grad_scale: float = 1.0):
         """clip_grad_norm_(5.0) + AdamW on the flat projector buffer
         (ref:Stage1/projector_trainer.py:241-243); refreshes the bf16 shadow weights."""
-        Pj = self.proj
-        Pj.step += 1
-        ops.sumsq(Pj.grad, Pj.sumsq)
-        ops.clip_adamw(Pj.flat, Pj.grad, Pj.m, Pj.v, Pj.shadow, Pj.sumsq, grad_scale=grad_scale,
-                       max_norm=max_norm, lr=lr, beta1=beta1, beta2=beta2, eps=eps, wd=weight_decay,
-                       step=Pj.step)
+        # one flat buffer per trainable module, each clipped on its own norm (Stage 2 clips module by module:
+        # ref:Stage2/trainer.py:436-439) and updated with the same AdamW hyper-parameters (:145-150)
+        for st in self.trainables():
+            st.step += 1
+            ops.sumsq(st.grad, st.sumsq)
+            ops.clip_adamw(st.flat, st.grad, st.m, st.v, st.shadow, st.sumsq, grad_scale=grad_scale,
+                           max_norm=max_norm, lr=lr, beta1=beta1, beta2=beta2, eps=eps, wd=weight_decay,
+                           step=st.step)
+
+    def trainables(self):
+        """The flat-buffer states the optimizer steps: the projector (unless frozen) and the LoRA adapters."""
+        return ([self.proj] if self.train_projector else []) + ([self.lora] if self.lora is not None else [])
+
+    # ------------------------------------------------------------------ adapters folded into the weights
+    def merge_adapters(self):
+        """Decoder layers with W' = W + (alpha / r) * B A in bf16 (peft `merge_and_unload`), for the decode loop: one
+        GEMM per packed projection, the base weight entering as the epilogue's residual.  The merged matrices live in
+        buffers the engine keeps and refreshes in place on every call (a captured decode graph holds their addresses).
+        Returns a layer list for `merged()`; None without adapters."""
+        lo = self.lora
+        if lo is None:
+            return None
+        if getattr(self, "_merged_layers", None) is None:
+            self._merged_layers = []
+            for li, L in enumerate(self.llm.layers):
+                Lm = dict(L)
+                for g, key in (("qkv", "qkv_w"), ("o", "o_w"), ("gu", "gu_w"), ("down", "down_w")):
+                    if lo.layers[li].get(g) is not None:
+                        Lm[key] = torch.empty_like(L[key])
+                self._merged_layers.append(Lm)
+        for li, (L, Lm) in enumerate(zip(self.llm.layers, self._merged_layers)):
+            for g, key in (("qkv", "qkv_w"), ("o", "o_w"), ("gu", "gu_w"), ("down", "down_w")):
+                grp = lo.layers[li].get(g)
+                if grp is not None:
+                    ops.linear_dgrad(grp.B(lo.shadow), grp.A(lo.shadow), out=Lm[key], residual=L[key], alpha=lo.scale)
+        return self._merged_layers
+
+    @contextlib.contextmanager
+    def merged(self, layers):
+        """Run with the merged decoder layers of merge_adapters() and the adapter path off (generation)."""
+        if layers is None:
+            yield
+            return
+        keep = (self.llm.layers, self.lora)
+        self.llm.layers, self.lora = layers, None
+        try:
+            yield
+        finally:
+            self.llm.layers, self.lora = keep
 
     # ------------------------------------------------------------------ whole step
     def splice(self, token_ids: torch.Tensor, labels: torch.Tensor, x0: torch.Tensor, pad_id):
@@ -747,8 +847,9 @@ class Stage1Engine:
             loss = self.llm_forward_loss(x0, keyvalid, targets, B, S, Tl, lab0=lab0)
         with _phase("llm_backward"):
             dx = self.llm_backward()
-        with _phase("projector_backward"):
-            self.projector_backward(dx, patch, Z, Hm, B, S)
+        if self.train_projector:
+            with _phase("projector_backward"):
+                self.projector_backward(dx, patch, Z, Hm, B, S)
         return loss
 
     def preprocess_images(self, images, out: torch.Tensor | None = None, *, mean=(0.5, 0.5, 0.5),
@@ -956,6 +1057,9 @@ class Stage1Engine:
         By default the step runs as ONE CUDA graph whose position lives on the device (fixed shapes: scores over
         the whole cache, masked), so every token of every sequence replays the same graph; PT_STAGE1_DECODE_GRAPH=0
         selects the eager step with exact-length contractions."""
+        if self.lora is not None:
+            raise RuntimeError("decode_step with live LoRA adapters: run it inside `with engine.merged(engine."
+                               "merge_adapters())` (generate() does)")
         kc = self.cache
         if kc["pos"] >= kc["Smax"]:
             raise RuntimeError("KV cache full: prefill(max_new_tokens=...) was sized too small")
@@ -1158,6 +1262,13 @@ class Stage1Engine:
         every row has produced eos.  Token selection (HF logits processors: repetition penalty ->
         temperature -> top-k -> top-p -> multinomial, or argmax) is control logic on a [B, V] tensor
         and uses torch ops; all model arithmetic runs in the sm_100a kernels."""
+        if self.lora is not None:
+            # the decode loop reads the packed weights only: fold the adapters in for the length of this call
+            kw = dict(max_new_tokens=max_new_tokens, do_sample=do_sample, temperature=temperature, top_p=top_p,
+                      top_k=top_k, repetition_penalty=repetition_penalty, pad_token_id=pad_token_id,
+                      eos_token_id=eos_token_id, generator=generator, prompt_pad_id=prompt_pad_id)
+            with self.merged(self.merge_adapters()):
+                return self.generate(pixels, prompt_ids, **kw)
         logits = self.prefill(pixels, prompt_ids, max_new_tokens=max_new_tokens, prompt_pad_id=prompt_pad_id)
         B = logits.shape[0]
         dev = self.device
@@ -1228,23 +1339,27 @@ class Stage1Engine:
             loss = self.forward_backward(px, ids, lab, pad_id, span)
             if st is not None:
                 st["done"].record()
-        Pj = self.proj
+        states = self.trainables()
         if not sync_gradients:
-            # flat f32 axpy over the 22M-entry projector gradient: bookkeeping between micro-batches
+            # flat f32 axpy over the gradient buffers (22M projector entries, + the adapters): bookkeeping between
+            # micro-batches
             if self._acc_grad is None:
-                self._acc_grad = torch.zeros_like(Pj.grad)
-            if self._acc_pending:
-                self._acc_grad.add_(Pj.grad)
-            else:
-                self._acc_grad.copy_(Pj.grad)
+                self._acc_grad = [torch.zeros_like(st.grad) for st in states]
+            for acc, st in zip(self._acc_grad, states):
+                if self._acc_pending:
+                    acc.add_(st.grad)
+                else:
+                    acc.copy_(st.grad)
             self._acc_pending = True
             return loss
         if self._acc_pending:
-            Pj.grad.add_(self._acc_grad)
+            for acc, st in zip(self._acc_grad, states):
+                st.grad.add_(acc)
             self._acc_pending = False
         if allreduce is not None and world_size > 1:
             with _phase("grad_allreduce"):
-                allreduce(Pj.grad)
+                for st in states:
+                    allreduce(st.grad)
         with _phase("clip_adamw"):
             self.optimizer_step(lr, weight_decay=weight_decay, grad_scale=1.0 / world_size, max_norm=max_norm)
         return loss

@@ -1,0 +1,134 @@
+"""Stage-2 LoRA path on the CUDA kernels (second half), GPU only.  Checkers: the vectors
+recorded from the reference's `VQATrainerStage2.train()` with `enable_qlora=True` (tests/golden/vqa_lora_*.npz) and the
+CPU oracle on the same inputs.  bf16 tolerances: loss 1e-2 relative, gradient cosine per adapter group."""
+import math
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+GOLDEN = Path(__file__).resolve().parent / "golden"
+
+
+def _cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float(torch.dot(a, b) / (a.norm() * b.norm() + 1e-300))
+
+
+def _to_peft(L: dict) -> dict:
+    """oracle keys `l<i>.<target>.A` -> peft keys."""
+    from projectiontrainer_b200.lora import LoraState
+    out = {}
+    for k, v in L.items():
+        li, t, w = k.split(".")
+        out[LoraState.key(int(li[1:]), t, w)] = v
+    return out
+
+
+def _by_oracle_key(lo, buf) -> dict:
+    from projectiontrainer_b200.lora import LoraState
+    sd = lo.state_dict(buf)
+    out = {}
+    for li, groups in enumerate(lo.layers):
+        for g in groups.values():
+            for t, _, _, _ in g.parts:
+                for w in "AB":
+                    out[f"l{li}.{t}.{w}"] = sd[LoraState.key(li, t, w)]
+    return out
+
+
+def _group_cos(ours: dict, ref: dict, which: str) -> float:
+    """Cosine over all adapter matrices of one kind (A or B) taken as one vector."""
+    ks = sorted(k for k in ours if k.endswith("." + which))
+    a = torch.cat([ours[k].detach().cpu().float().flatten() for k in ks])
+    b = torch.cat([torch.as_tensor(ref[k]).float().flatten() for k in ks])
+    return _cos(a, b)
+
+
+class _Tok:
+    def __init__(self, pad, side):
+        self.pad_token_id, self.eos_token_id, self.padding_side = pad, 1, side
+
+
+def _collated(samples, idx, tok):
+    from projectiontrainer_b200.vqa_trainer import vqa_collate_fn
+    px, qs, as_ = samples
+    return vqa_collate_fn([{"pixel_values": px[i], "question_input_ids": qs[i], "answer_input_ids": as_[i]}
+                           for i in idx], tok)
+
+
+@pytest.mark.parametrize("case", ["vqa_lora_all_right", "vqa_lora_qvd_left_frozen_proj"])
+def test_lora_engine_trajectory_matches_reference_golden(cuda_dev, case):
+    """The reference's recorded `enable_qlora=True` run through `train_step`: micro-batch losses, accumulated adapter
+    (and projector) gradients at each clip, one clip per module + AdamW, adapter weights at the end, validation loss."""
+    from oracle import stage1_oracle as O
+    from oracle import stage2_oracle as O2
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.lora import LoraState
+    from projectiontrainer_b200.vqa_trainer import accumulate_sync_flag, vqa_step_inputs
+    vkw, lkw = O2.LORA_CASES[case][:2]
+    r, alpha, targets, b_std, train_proj = O2.LORA_CASES[case][-1]
+    g = dict(np.load(GOLDEN / f"{case}.npz", allow_pickle=False))
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    L0 = O2.init_lora(olc, r, targets, b_std=b_std)
+    train = O2.synthetic_vqa_samples(int(g["n_train"]), ovc, olc, seed=4321)
+    val = O2.synthetic_vqa_samples(int(g["n_val"]), ovc, olc, seed=9876)
+    GA, B, epochs = int(g["grad_accum"]), int(g["B"]), int(g["epochs"])
+    tok = _Tok(olc.pad_id, str(g["padding_side"]))
+    lcfg = GemmaCfg(**lkw)
+    lo = LoraState(lcfg, cuda_dev, r=r, alpha=alpha, targets=targets)
+    lo.load_state_dict(_to_peft(L0))
+    assert lo.num_parameters() == sum(v.numel() for v in L0.values())
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, lcfg, cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev, loss_divisor=GA * int(g["backward_divisor"]),
+                         lora=lo, train_projector=train_proj)
+    n_batches = math.ceil(int(g["n_train"]) / B)
+    total = epochs * math.ceil(n_batches / GA)
+    warm = math.ceil(float(g["warmup_ratio"]) * total)
+    mi, step, micro = 0, 0, 0
+    for ep in range(epochs):
+        for bi in range(n_batches):
+            sync, micro = accumulate_sync_flag(micro, GA, bi == n_batches - 1)
+            assert sync == bool(g[f"micro{mi}.sync"])
+            cb = _collated(train, g[f"micro{mi}.idx"].tolist(), tok)
+            batch = vqa_step_inputs(cb, olc.pad_id, 1)
+            lr = O.cosine_lr(step, float(g["base_lr"]), warm, total)
+            loss = eng.train_step(batch, lr, pad_id=olc.pad_id, weight_decay=float(g["weight_decay"]),
+                                  max_norm=1.0, sync_gradients=sync)
+            torch.cuda.synchronize()
+            ref_loss = float(g[f"micro{mi}.loss"])
+            assert abs(loss.item() - ref_loss) / ref_loss < 1e-2, (mi, loss.item(), ref_loss)
+            if sync:
+                ours = _by_oracle_key(lo, lo.grad)
+                ref = {k: g[f"step{step}.lora_grad.{k}"] for k in ours}
+                for w in "AB":
+                    c = _group_cos(ours, ref, w)
+                    assert c > (0.999 if step == 0 else 0.99), (step, w, c)
+                if train_proj:
+                    for k, gr in eng.proj.grads().items():
+                        c = _cos(gr.cpu(), torch.from_numpy(g[f"step{step}.grad.{k}"]))
+                        assert c > (0.999 if step == 0 else 0.99), (step, k, c)
+                step += 1
+            mi += 1
+    assert step == int(g["n_steps"])
+    final = _by_oracle_key(lo, lo.flat)
+    for w in "AB":
+        ks = sorted(k for k in final if k.endswith("." + w))
+        ours = torch.cat([(final[k].cpu() - L0[k]).flatten() for k in ks])
+        ref = torch.cat([(torch.from_numpy(g[f"step{step - 1}.lora_param.{k}"]) - L0[k]).flatten() for k in ks])
+        assert _cos(ours, ref) > 0.97, (w, _cos(ours, ref))
+    # block layout: nothing outside the adapters' own entries ever moved
+    assert int((lo.flat != 0).sum().item()) <= lo.num_parameters()
+    if not train_proj:
+        for k, p in eng.proj.params().items():
+            assert torch.equal(p.cpu(), P[k]), k
+    vt = _Tok(olc.pad_id, "left")
+    n_val, losses = int(g["n_val"]), []
+    for s in range(0, n_val, B):
+        vb = vqa_step_inputs(_collated(val, list(range(s, min(s + B, n_val))), vt), olc.pad_id, 1)
+        losses.append(eng.eval_loss(vb, pad_id=olc.pad_id).item())
+    assert abs(np.mean(losses) - float(g["val_loss"][-1])) / float(g["val_loss"][-1]) < 1e-2
