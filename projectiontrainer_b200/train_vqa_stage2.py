@@ -1,14 +1,16 @@
-"""Drop-in for ref:Stage2/train_vqa_stage2.py, frozen-LLM variant: same flags (ref lines 84-120), same
-projector loading (`--stage1_projector_path` directory with projector_config.json + .safetensors/.bin), same
-dataset schema; the step runs on the B200 kernels.
+"""Drop-in for ref:Stage2/train_vqa_stage2.py: same flags (ref lines 84-120), same projector loading
+(`--stage1_projector_path` directory with projector_config.json + .safetensors/.bin), same dataset schema, the
+same LoRA configuration under `--enable_qlora` (ref lines 225-250); the step runs on the B200 kernels.
 
     torchrun --nproc-per-node N -m projectiontrainer_b200.train_vqa_stage2 --image_root ... --train_json ... \
         --val_json ... --stage1_projector_path ... --unfreeze_projection_layer --llm_name google/gemma-3-1b-it
     python -m projectiontrainer_b200.train_vqa_stage2 --synthetic 64 --unfreeze_projection_layer --disable_wandb
 
-`--enable_qlora`, `--unfreeze_llm`, `--train_ve_first_epoch` and `--resume_qlora_adapter_path` are parsed and
-rejected: trainable LLM / vision weights are not built (see vqa_trainer.py).  `--synthetic N` (an addition)
-trains on N random triplets with random-init SigLIP-L/16-384 and Gemma3 weights."""
+`--enable_qlora` puts the decoder's projection weights through NF4 (weights.nf4_frozen_llm_) and trains LoRA adapters
+(r=16, alpha=32, all seven projections; lora.py), `--resume_qlora_adapter_path` loads a peft adapter directory.
+`--unfreeze_llm` and `--train_ve_first_epoch` are parsed and rejected: full LLM / vision fine-tuning is not built
+(see vqa_trainer.py).  `--synthetic N` (an addition) trains on N random triplets with random-init SigLIP-L/16-384 and
+Gemma3 weights."""
 from __future__ import annotations
 
 import argparse
@@ -54,6 +56,25 @@ def load_pretrained_projector(projector_path):
     return projector
 
 
+def load_qlora_adapter(path):
+    """ref:Stage2/train_vqa_stage2.py:206-223 (`PeftModel.from_pretrained(llm, path, is_trainable=True)`): the LoRA
+    fields of adapter_config.json + the tensors of adapter_model.safetensors / adapter_model.bin, by peft key."""
+    if not os.path.isdir(path):
+        raise SystemExit(f"Provided adapter path is not a directory: {path}")
+    with open(os.path.join(path, "adapter_config.json")) as f:
+        c = json.load(f)
+    cfg = {"r": c["r"], "lora_alpha": c["lora_alpha"], "target_modules": list(c["target_modules"]),
+           "lora_dropout": c.get("lora_dropout", 0.0)}
+    st = os.path.join(path, "adapter_model.safetensors")
+    if os.path.exists(st):
+        from safetensors.torch import load_file
+        sd = load_file(st, device="cpu")
+    else:
+        sd = torch.load(os.path.join(path, "adapter_model.bin"), map_location="cpu")
+    logger.info(f"Successfully loaded QLoRA adapter from {path}.")
+    return cfg, sd
+
+
 class _Tok:
     def __init__(self, pad, eos=1, side="right"):
         self.pad_token_id, self.eos_token_id, self.padding_side = pad, eos, side
@@ -95,10 +116,18 @@ def build_parser():
 
 def main(argv=None):
     args = build_parser().parse_args(argv)
-    if args.enable_qlora or args.resume_qlora_adapter_path or args.unfreeze_llm or args.train_ve_first_epoch:
-        raise SystemExit("--enable_qlora / --resume_qlora_adapter_path / --unfreeze_llm / --train_ve_first_epoch are "
-                         "not supported by this build (frozen-LLM Stage 2 only; no fallback to another backend)")
+    if args.unfreeze_llm or args.train_ve_first_epoch:
+        raise SystemExit("--unfreeze_llm / --train_ve_first_epoch are not supported by this build (the LLM trains "
+                         "through LoRA adapters only; no fallback to another backend)")
+    if args.resume_qlora_adapter_path and not args.enable_qlora:
+        raise SystemExit("--resume_qlora_adapter_path needs --enable_qlora")
     freeze_proj = not args.unfreeze_projection_layer
+    # ref:Stage2/train_vqa_stage2.py:229-236
+    lora_config = {"r": 16, "lora_alpha": 32, "lora_dropout": 0.05,
+                   "target_modules": ["q_proj", "k_proj", "v_proj", "o_proj", "gate_proj", "up_proj", "down_proj"]}
+    lora_sd = None
+    if args.resume_qlora_adapter_path:
+        lora_config, lora_sd = load_qlora_adapter(args.resume_qlora_adapter_path)
     accelerator = setup_accelerator_and_logging(args)
     if args.synthetic > 0:
         from . import weights as Wt
@@ -106,7 +135,10 @@ def main(argv=None):
         lc = {"1b": GEMMA3_1B, "4b": GEMMA3_4B, "qwen3_8b": QWEN3_8B}[args.synthetic_llm]
         vc, dev = SIGLIP_L, accelerator.device
         vision_encoder = PackedSiglip(Wt.random_siglip(vc, dev, 0), vc, dev)
-        language_model = PackedGemma(Wt.random_gemma(lc, dev, 0), lc, dev)
+        Wl = Wt.random_gemma(lc, dev, 0)
+        if args.enable_qlora:
+            Wt.nf4_frozen_llm_(Wl, lc, dev)
+        language_model = PackedGemma(Wl, lc, dev)
         tokenizer = _Tok(lc.pad_id)
         projection_layer = MLPProjector(vc.hidden, lc.hidden)
         n_val = max(1, args.synthetic // 8)
@@ -134,8 +166,9 @@ def main(argv=None):
         val_dataset=val_dataset, output_dir=args.output_dir, batch_size=args.batch_size,
         learning_rate=args.learning_rate, weight_decay=args.weight_decay, num_epochs=args.num_epochs,
         gradient_accumulation_steps=args.gradient_accumulation_steps, warmup_ratio=args.warmup_ratio,
-        freeze_vision_encoder=True, freeze_projection_layer=freeze_proj, freeze_llm=True, enable_qlora=False,
-        train_ve_first_epoch=False, wandb_project=args.wandb_project)
+        freeze_vision_encoder=True, freeze_projection_layer=freeze_proj, freeze_llm=True,
+        enable_qlora=args.enable_qlora, train_ve_first_epoch=False, wandb_project=args.wandb_project,
+        lora_config=lora_config if args.enable_qlora else None, lora_state_dict=lora_sd)
     try:
         trainer.train()
     finally:

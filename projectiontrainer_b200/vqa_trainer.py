@@ -1,16 +1,17 @@
-"""Drop-in for ref:Stage2/trainer.py, FROZEN-LLM VARIANT (first half): same
-`vqa_collate_fn`, same `VQATrainerStage2` constructor signature, `.train()`, `.evaluate()`, `.save_model()`,
-artefact names and logged metric names.  Vision encoder and LLM stay frozen, the projector trains
-(`--unfreeze_projection_layer`; no `--enable_qlora`, no `--unfreeze_llm`, no `--train_ve_first_epoch`): the
-micro-batch body (ref lines 311-420: vision forward, `[:, 1:, :]`, projector, question/answer embedding,
-`[image][question][answer]` concatenation, mask, answer-only labels, fp32 shifted CE, backward) runs in
-`engine.Stage1Engine` on the sm_100a kernels with the answer rows as its label span; this file is the host
-loop: dynamic per-batch padding, `accelerator.accumulate()` bookkeeping, clip 1.0, AdamW, cosine schedule.
+"""Drop-in for ref:Stage2/trainer.py: same `vqa_collate_fn`, same `VQATrainerStage2`
+constructor signature, `.train()`, `.evaluate()`, `.save_model()`, artefact names and logged metric names.  The
+vision encoder and the LLM's own weights stay frozen; what trains is the projector
+(`--unfreeze_projection_layer`) and / or LoRA adapters on the decoder projections (`--enable_qlora`,
+ref:Stage2/train_vqa_stage2.py:225-250; lora.py).  The micro-batch body (ref lines 311-420: vision forward,
+`[:, 1:, :]`, projector, question/answer embedding, `[image][question][answer]` concatenation, mask, answer-only
+labels, fp32 shifted CE, backward) runs in `engine.Stage1Engine` on the sm_100a kernels with the answer rows as its
+label span; this file is the host loop: dynamic per-batch padding, `accelerator.accumulate()` bookkeeping, one
+clip to 1.0 per trainable module, AdamW, cosine schedule.
 
-Not built (raises NotImplementedError, never falls back): trainable LLM weights — LoRA/QLoRA adapters or
-the full LLM need weight-gradient GEMMs through the decoder and a 4-bit base-weight GEMM — and the
-first-epoch vision-encoder training.  Validation generation samples (top-k 50, top-p 0.9) without the
-reference's 3-beam search (`num_beams=3`), which the engine's decode loop does not implement."""
+Not built (raises NotImplementedError, never falls back): full fine-tuning of the LLM (`--unfreeze_llm`) and the
+first-epoch vision-encoder training.  LoRA dropout is not applied (lora.py).  Validation generation samples
+(top-k 50, top-p 0.9) without the reference's 3-beam search (`num_beams=3`), which the engine's decode loop does
+not implement."""
 from __future__ import annotations
 
 import json
@@ -25,6 +26,7 @@ from torch.utils.data import DataLoader
 
 from . import weights as Wt
 from .engine import PackedGemma, PackedSiglip, ProjectorState, Stage1Engine
+from .lora import TARGETS as LORA_TARGETS, LoraState
 from .projector_trainer import cosine_with_warmup, sharded_loader
 
 logger = logging.getLogger(__name__)
@@ -95,28 +97,45 @@ def accumulate_sync_flag(micro_step: int, grad_accum: int, end_of_dataloader: bo
     return micro_step % grad_accum == 0, micro_step
 
 
+def _peft_adapters(language_model):
+    """(LoraConfig fields, adapter state dict by peft key) of a peft-wrapped model, (None, None) for anything else.
+    Only attributes are read — peft itself is never imported or run."""
+    pc = getattr(language_model, "peft_config", None)
+    if not pc:
+        return None, None
+    c = pc.get("default") or next(iter(pc.values()))
+    cfg = {"r": c.r, "lora_alpha": c.lora_alpha, "target_modules": sorted(c.target_modules),
+           "lora_dropout": getattr(c, "lora_dropout", 0.0)}
+    sd = {n.replace(".default.", "."): p.detach() for n, p in language_model.named_parameters() if ".lora_" in n}
+    return cfg, sd
+
+
 class VQATrainerStage2:
     def __init__(self, accelerator, vision_encoder, language_model, projection_layer, tokenizer, train_dataset,
                  val_dataset, output_dir: str, batch_size: int, learning_rate: float, weight_decay: float,
                  num_epochs: int, gradient_accumulation_steps: int, warmup_ratio: float,
                  freeze_vision_encoder: bool, freeze_projection_layer: bool, freeze_llm: bool,
-                 enable_qlora: bool, train_ve_first_epoch: bool, wandb_project: str):
-        if enable_qlora or not freeze_llm:
+                 enable_qlora: bool, train_ve_first_epoch: bool, wandb_project: str, lora_config: dict | None = None,
+                 lora_state_dict: dict | None = None):
+        """`lora_config` / `lora_state_dict` are additions (the reference wraps the LLM with peft before it builds the
+        trainer; peft module trees are not executed here): LoraConfig fields `r`, `lora_alpha`, `target_modules`,
+        `lora_dropout` (defaults = ref:Stage2/train_vqa_stage2.py:229-236) and adapter weights by peft key
+        (`--resume_qlora_adapter_path`).  A peft-wrapped `language_model` is read for both instead."""
+        if not freeze_llm and not enable_qlora:
             raise NotImplementedError(
-                "Stage 2 with trainable LLM weights (QLoRA adapters or --unfreeze_llm) is not built: it needs "
-                "decoder weight-gradient GEMMs and an NF4 base-weight GEMM (SURVEY.md §8f rank 2b/4); there is "
-                "no fallback path")
+                "Stage 2 with the LLM's own weights trainable (--unfreeze_llm) is not built: the decoder's "
+                "weight-gradient GEMMs exist for LoRA adapters only (SURVEY.md §8f); there is no fallback path")
         if train_ve_first_epoch or not freeze_vision_encoder:
             raise NotImplementedError("first-epoch vision-encoder training (--train_ve_first_epoch) is not built: "
                                       "the SigLIP tower is forward-only here")
-        if freeze_projection_layer:
-            # ref:Stage2/trainer.py:262-263
+        if freeze_projection_layer and not enable_qlora:
+            # ref:Stage2/trainer.py:242-243
             raise ValueError("No trainable parameters found. Check freezing configuration and QLoRA setup.")
         self.accelerator, self.tokenizer = accelerator, tokenizer
         self.vision_encoder, self.language_model, self.projection_layer = vision_encoder, language_model, projection_layer
         self.device = accelerator.device
         self.output_dir, self.num_epochs, self.batch_size = output_dir, num_epochs, batch_size
-        self.wandb_project, self.train_ve_first_epoch, self.enable_qlora = wandb_project, False, False
+        self.wandb_project, self.train_ve_first_epoch, self.enable_qlora = wandb_project, False, bool(enable_qlora)
         self.learning_rate, self.weight_decay = learning_rate, weight_decay
         self.grad_accum = int(gradient_accumulation_steps)
         if self.device.type != "cuda":
@@ -143,22 +162,47 @@ class VQATrainerStage2:
 
         vis = vision_encoder if isinstance(vision_encoder, PackedSiglip) else \
             PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), self.device)
-        llm = language_model if isinstance(language_model, PackedGemma) else \
-            PackedGemma(*Wt.llm_from_hf(language_model), self.device)
+        peft_cfg, peft_sd = _peft_adapters(language_model) if enable_qlora else (None, None)
+        if isinstance(language_model, PackedGemma):
+            llm = language_model        # already packed (and, for QLoRA, already through weights.nf4_frozen_llm_)
+        else:
+            Wl, lc = Wt.llm_from_hf(language_model)
+            if enable_qlora:
+                # ref:Stage2/train_vqa_stage2.py:168-186: the base weights the adapters ride on are the NF4 images
+                err = Wt.nf4_frozen_llm_(Wl, lc, self.device)
+                logger.info(f"LLM base weights through NF4: mean relative error {sum(err.values()) / len(err):.4f}")
+            llm = PackedGemma(Wl, lc, self.device)
         if isinstance(projection_layer, nn.Module):
             projection_layer.to(self.device).float()      # fp32 master weights (the reference casts the
-            projection_layer.requires_grad_(True)         # projector to bf16 under mixed precision: :288)
+            projection_layer.requires_grad_(not freeze_projection_layer)   # projector to bf16 under mixed precision)
             proj = ProjectorState.from_module(projection_layer, self.device)
         else:
             proj = projection_layer
+        lora = None
+        if enable_qlora:
+            cfg = {"r": 16, "lora_alpha": 32, "target_modules": list(LORA_TARGETS), "lora_dropout": 0.05}
+            cfg.update(peft_cfg or {})
+            cfg.update(lora_config or {})
+            lora = LoraState(llm.cfg, self.device, r=int(cfg["r"]), alpha=float(cfg["lora_alpha"]),
+                             targets=tuple(cfg["target_modules"]), dropout=float(cfg["lora_dropout"]))
+            sd = lora_state_dict or peft_sd
+            if sd:
+                lora.load_state_dict(sd)
+            if lora.dropout > 0:
+                logger.warning(f"lora_dropout={lora.dropout} is recorded in adapter_config.json but NOT applied "
+                               "during training (stated difference from the reference, see lora.py)")
+            logger.info(f"trainable params: {lora.num_parameters():,d} (LoRA r={lora.r}, alpha={lora.alpha:g}, "
+                        f"targets {list(lora.targets)})")
         ga = self.grad_accum
-        self.engine = Stage1Engine(vis, llm, proj, self.device,
+        self.engine = Stage1Engine(vis, llm, proj, self.device, lora=lora, train_projector=not freeze_projection_layer,
                                    loss_divisor=ga * getattr(accelerator, "backward_divisor", ga))
         self.pad_id = tokenizer.pad_token_id
         if self.pad_id is None:
             raise ValueError("tokenizer.pad_token_id is None: the dataset sets it to eos (ref:Stage2/dataset.py:33-35)")
-        logger.info("Freezing LLM parameters (QLoRA disabled).")
-        logger.info("projection_layer parameters are trainable.")
+        logger.info("QLoRA enabled. Trainable parameters determined by PEFT." if enable_qlora
+                    else "Freezing LLM parameters (QLoRA disabled).")
+        logger.info("Freezing projection_layer parameters." if freeze_projection_layer
+                    else "projection_layer parameters are trainable.")
 
     # accelerate's prepared scheduler ticks num_processes times per optimizer step
     def current_lr(self) -> float:
@@ -268,22 +312,41 @@ class VQATrainerStage2:
         return avg_val_loss
 
     def save_model(self, path):
-        """ref:Stage2/trainer.py:679-768, frozen-LLM case: `projection_layer/model.safetensors` (what
-        `accelerator.save_model` writes and Stage2/train_vqa_stage2.py:25-80 loads back) +
-        `projector_config.json`; the optimizer moments stand in for `accelerator.save_state`.  The frozen
-        language model is not saved (ref :707-708)."""
+        """ref:Stage2/trainer.py:679-768: `language_model/adapter_model.safetensors` + `adapter_config.json` (what
+        peft's `save_pretrained` writes, :724-729) when adapters train; `projection_layer/model.safetensors` (what
+        `accelerator.save_model` writes and Stage2/train_vqa_stage2.py:25-80 loads back) + `projector_config.json`
+        when the projector trains; the optimizer moments stand in for `accelerator.save_state`.  The frozen base
+        model is not saved (ref :735-736)."""
         if not self.accelerator.is_main_process:
             return
         from safetensors.torch import save_file
         torch.cuda.synchronize(self.device)
-        proj = self.engine.proj
-        proj_dir = os.path.join(path, "projection_layer")
-        os.makedirs(proj_dir, exist_ok=True)
-        save_file({k: v.detach().cpu().clone().contiguous() for k, v in proj.params().items()},
-                  os.path.join(proj_dir, "model.safetensors"))
-        with open(os.path.join(proj_dir, "projector_config.json"), "w") as f:
-            json.dump({"vision_dim": int(proj.shapes[0][1]), "llm_dim": int(proj.shapes[2][0])}, f, indent=4)
-        torch.save({"exp_avg": proj.m.cpu(), "exp_avg_sq": proj.v.cpu(), "step": proj.step,
-                    "scheduler_step": self._sched_step}, os.path.join(path, "optimizer.bin"))
-        logger.info("Language model was frozen and not saved.")
-        logger.info(f"Projection layer saved to {proj_dir}")
+        os.makedirs(path, exist_ok=True)
+        eng, opt = self.engine, {"scheduler_step": self._sched_step}
+        if eng.lora is not None:
+            lo, llm_dir = eng.lora, os.path.join(path, "language_model")
+            os.makedirs(llm_dir, exist_ok=True)
+            logger.info("Saving QLoRA adapters using PEFT save_pretrained...")
+            save_file({k: v.detach().cpu().clone().contiguous() for k, v in lo.state_dict().items()},
+                      os.path.join(llm_dir, "adapter_model.safetensors"))
+            base = getattr(getattr(self.language_model, "config", None), "_name_or_path", "") or ""
+            with open(os.path.join(llm_dir, "adapter_config.json"), "w") as f:
+                json.dump(lo.adapter_config(base), f, indent=2)
+            if hasattr(self.tokenizer, "save_pretrained"):
+                self.tokenizer.save_pretrained(llm_dir)
+            host = lambda buf: {n: t.cpu().clone() for n, t in lo.state_dict(buf).items()}
+            opt["lora"] = {"exp_avg": host(lo.m), "exp_avg_sq": host(lo.v), "step": lo.step}
+            logger.info(f"QLoRA adapters saved to {llm_dir}")
+        else:
+            logger.info("Language model was frozen and not saved.")
+        if eng.train_projector:
+            proj = eng.proj
+            proj_dir = os.path.join(path, "projection_layer")
+            os.makedirs(proj_dir, exist_ok=True)
+            save_file({k: v.detach().cpu().clone().contiguous() for k, v in proj.params().items()},
+                      os.path.join(proj_dir, "model.safetensors"))
+            with open(os.path.join(proj_dir, "projector_config.json"), "w") as f:
+                json.dump({"vision_dim": int(proj.shapes[0][1]), "llm_dim": int(proj.shapes[2][0])}, f, indent=4)
+            opt.update({"exp_avg": proj.m.cpu(), "exp_avg_sq": proj.v.cpu(), "step": proj.step})
+            logger.info(f"Projection layer saved to {proj_dir}")
+        torch.save(opt, os.path.join(path, "optimizer.bin"))

@@ -83,8 +83,30 @@ def qwen3_from_hf(causal_lm) -> tuple[dict, GemmaCfg]:
     return W, cfg
 
 
+class _BaseView:
+    """A peft-wrapped causal LM seen as its base model: `state_dict()` with peft's `base_model.model.` prefix and
+    `.base_layer` infixes stripped and the adapter tensors left out (those go to lora.LoraState)."""
+
+    def __init__(self, peft_model):
+        self._m, self.config = peft_model, peft_model.config
+
+    def state_dict(self):
+        out = {}
+        for k, v in self._m.state_dict().items():
+            if ".lora_" in k:
+                continue
+            k = k[len("base_model.model."):] if k.startswith("base_model.model.") else k
+            out[k.replace(".base_layer.", ".")] = v
+        return out
+
+
 def llm_from_hf(causal_lm) -> tuple[dict, GemmaCfg]:
     """Dispatch on the HF model type: Gemma3 text and Qwen3 dense decoders; anything else raises."""
+    if any(getattr(p, "quant_state", None) is not None or p.dtype == torch.uint8 for p in causal_lm.parameters()):
+        raise RuntimeError("the language model holds bitsandbytes 4-bit weights: pass the bf16 model — with "
+                           "enable_qlora the NF4 quantise / de-quantise pass runs here (weights.nf4_frozen_llm_)")
+    if getattr(causal_lm, "peft_config", None):
+        causal_lm = _BaseView(causal_lm)
     mt = getattr(causal_lm.config, "model_type", None)
     if mt == "qwen3":
         return qwen3_from_hf(causal_lm)

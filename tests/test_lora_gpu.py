@@ -199,3 +199,78 @@ def test_lora_step_hd256_fused_path_vs_oracle(cuda_dev, targets, train_proj):
     with eng.merged(eng.merge_adapters()):
         gen2 = eng.generate(px, cb["question_input_ids"], max_new_tokens=4, prompt_pad_id=olc.pad_id)
     assert torch.equal(gen, gen2) and eng.lora is lo
+
+
+def test_qlora_trainer_dropin_end_to_end_tiny(cuda_dev, tmp_path):
+    """`VQATrainerStage2(enable_qlora=True)` through the real DataLoader: adapters (peft init: B = 0) and the projector
+    train, the checkpoint holds peft's adapter files, and a second trainer resumed from them
+    (`--resume_qlora_adapter_path`) starts from the same adapter weights and the same validation loss."""
+    import json
+    from oracle import stage1_oracle as O
+    from oracle import stage2_oracle as O2
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.accelerator_setup import Stage1Accelerator
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.projectors import MLPProjector
+    from projectiontrainer_b200.train_vqa_stage2 import load_pretrained_projector, load_qlora_adapter
+    from projectiontrainer_b200.vqa_trainer import VQATrainerStage2
+    vkw, lkw = O2.LORA_CASES["vqa_lora_all_right"][:2]
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    train = O2.synthetic_vqa_samples(6, ovc, olc, seed=4321)
+    val = O2.synthetic_vqa_samples(2, ovc, olc, seed=9876)
+
+    class DS(torch.utils.data.Dataset):
+        def __init__(self, s): self.s = s
+        def __len__(self): return len(self.s[1])
+        def __getitem__(self, i):
+            return {"pixel_values": self.s[0][i], "question_input_ids": self.s[1][i], "answer_input_ids": self.s[2][i]}
+
+    class Tok(_Tok):
+        saved = None
+        def batch_decode(self, ids, skip_special_tokens=True):
+            return [" ".join(str(int(t)) for t in row) for row in ids]
+        def save_pretrained(self, path):
+            Tok.saved = path
+
+    def make(out_dir, proj_sd, lora_cfg, lora_sd, epochs):
+        proj = MLPProjector(ovc.hidden, olc.hidden)
+        proj.load_state_dict(proj_sd)
+        acc = Stage1Accelerator(gradient_accumulation_steps=2, device=cuda_dev)
+        tr = VQATrainerStage2(acc, E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev),
+                              E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev), proj, Tok(olc.pad_id, "right"), DS(train),
+                              DS(val), str(out_dir), 2, 1e-3, 0.01, epochs, 2, 0.25, freeze_vision_encoder=True,
+                              freeze_projection_layer=False, freeze_llm=True, enable_qlora=True,
+                              train_ve_first_epoch=False, wandb_project="none", lora_config=lora_cfg,
+                              lora_state_dict=lora_sd)
+        real_eval = tr.evaluate
+        tr.evaluate = lambda ep, gs: real_eval(ep, gs, max_new_tokens=3)
+        return tr, acc, proj
+
+    cfg = {"r": 8, "lora_alpha": 16, "target_modules": ["q_proj", "v_proj", "gate_proj", "down_proj"], "lora_dropout": 0.05}
+    tr, acc, proj = make(tmp_path / "a", P, cfg, None, 2)
+    lo = tr.engine.lora
+    assert lo.r == 8 and lo.targets == ("q_proj", "v_proj", "gate_proj", "down_proj") and lo.dropout == 0.05
+    sd0 = {k: v.cpu().clone() for k, v in lo.state_dict().items()}
+    assert all((v == 0).all() for k, v in sd0.items() if "lora_B" in k)          # peft init
+    tr.train()
+    losses = [v["train/batch_loss"] for s, v in acc.logged if "train/batch_loss" in v]
+    vals = [v["val/loss"] for s, v in acc.logged if "val/loss" in v]
+    assert len(losses) == 6 and all(math.isfinite(x) for x in losses) and len(vals) == 2
+    sd1 = {k: v.cpu().clone() for k, v in lo.state_dict().items()}
+    assert all(not torch.equal(sd1[k], sd0[k]) for k in sd0)                     # every adapter matrix moved
+    ck = tmp_path / "a" / "checkpoint-epoch_2"
+    ad = ck / "language_model"
+    assert Tok.saved == str(ad)                                                  # ref :740-741
+    meta = json.loads((ad / "adapter_config.json").read_text())
+    assert meta["peft_type"] == "LORA" and meta["r"] == 8 and meta["lora_alpha"] == 16 and meta["lora_dropout"] == 0.05
+    cfg2, sd2 = load_qlora_adapter(str(ad))
+    assert set(sd2) == set(sd1) and all(torch.equal(sd2[k], sd1[k]) for k in sd1)
+    opt = torch.load(ck / "optimizer.bin")
+    assert opt["lora"]["step"] == 4 and set(opt["lora"]["exp_avg"]) == set(sd1) and opt["step"] == 4
+    back = load_pretrained_projector(str(ck / "projection_layer"))
+    # resumed trainer: same adapters, same validation loss as the first trainer ended with
+    tr2, acc2, _ = make(tmp_path / "b", back.state_dict(), cfg2, sd2, 1)
+    assert all(torch.equal(v.cpu(), sd1[k]) for k, v in tr2.engine.lora.state_dict().items())
+    v2 = tr2.evaluate(0, 0)
+    assert abs(v2 - vals[-1]) / vals[-1] < 1e-3, (v2, vals)

@@ -81,8 +81,10 @@ def test_unsupported_stage2_modes_fail_loudly():
                 batch_size=1, learning_rate=1e-4, weight_decay=0.01, num_epochs=1, gradient_accumulation_steps=1,
                 warmup_ratio=0.0, freeze_vision_encoder=True, freeze_projection_layer=False, freeze_llm=True,
                 enable_qlora=False, train_ve_first_epoch=False, wandb_project="x")
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError, match="CUDA"):          # adapters train on the kernels too: no CPU path
         VQATrainerStage2(**{**base, "enable_qlora": True})
+    with pytest.raises(RuntimeError, match="CUDA"):          # adapters alone are a valid trainable set
+        VQATrainerStage2(**{**base, "enable_qlora": True, "freeze_projection_layer": True})
     with pytest.raises(NotImplementedError):
         VQATrainerStage2(**{**base, "freeze_llm": False})
     with pytest.raises(NotImplementedError):
@@ -93,13 +95,34 @@ def test_unsupported_stage2_modes_fail_loudly():
         VQATrainerStage2(**base)
 
 
-def test_stage2_cli_rejects_lora_flags():
+def test_stage2_cli_flags():
     from projectiontrainer_b200.train_vqa_stage2 import build_parser, main
     a = build_parser().parse_args([])
     assert a.gradient_accumulation_steps == 8 and a.batch_size == 1 and a.warmup_ratio == 0.05
     assert a.max_q_len == 128 and a.max_a_len == 512 and a.llm_name == "Qwen/Qwen3-8B"
     with pytest.raises(SystemExit):
-        main(["--enable_qlora", "--synthetic", "4"])
+        main(["--unfreeze_llm", "--synthetic", "4"])
+    with pytest.raises(SystemExit):
+        main(["--resume_qlora_adapter_path", "/nonexistent", "--synthetic", "4"])      # needs --enable_qlora
+
+
+def test_qlora_adapter_directory_round_trip(tmp_path):
+    """`--resume_qlora_adapter_path`: adapter_config.json + adapter_model.safetensors in peft's layout are read back
+    into the LoRA fields and the tensors by peft key."""
+    import json as _json
+    from safetensors.torch import save_file
+    from projectiontrainer_b200.lora import LoraState
+    from projectiontrainer_b200.train_vqa_stage2 import load_qlora_adapter
+    sd = {LoraState.key(0, "q_proj", "A"): torch.randn(8, 32), LoraState.key(0, "q_proj", "B"): torch.randn(64, 8),
+          LoraState.key(1, "down_proj", "A"): torch.randn(8, 96)}
+    assert LoraState.key(1, "down_proj", "A") == "base_model.model.model.layers.1.mlp.down_proj.lora_A.weight"
+    assert LoraState.key(0, "q_proj", "B") == "base_model.model.model.layers.0.self_attn.q_proj.lora_B.weight"
+    save_file(sd, str(tmp_path / "adapter_model.safetensors"))
+    (tmp_path / "adapter_config.json").write_text(_json.dumps(
+        {"peft_type": "LORA", "r": 8, "lora_alpha": 16, "target_modules": ["q_proj", "down_proj"], "lora_dropout": 0.1}))
+    cfg, got = load_qlora_adapter(str(tmp_path))
+    assert cfg == {"r": 8, "lora_alpha": 16, "target_modules": ["q_proj", "down_proj"], "lora_dropout": 0.1}
+    assert set(got) == set(sd) and all(torch.equal(got[k], sd[k]) for k in sd)
 
 
 def test_collates_keep_decoded_images_as_lists():
