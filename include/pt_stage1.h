@@ -160,6 +160,12 @@ typedef struct {
     const void* B2;
     int64_t ldb2;
     int32_t K2;
+    /* Split-K: 0 / 1 = off.  n > 1 cuts the contraction into (at most) n slices that run as separate tiles and ADD
+     * their partial products into C with f32 atomics: C += alpha * A . B^T, so the caller clears (or pre-loads) C.
+     * -1 = pick n so that the launch has about one tile per SM pair.  Needs f32 C and no bias / act / residual /
+     * C_pre / band / K groups / K2.  For products with a long contraction and a small output (the adapters' weight
+     * gradients); the summation order, hence the last bits of C, varies from run to run. */
+    int32_t ksplit;
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);

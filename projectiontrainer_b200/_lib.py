@@ -36,6 +36,7 @@ class GemmArgs(C.Structure):
         ("bn_hint", C.c_int32),
         ("aux2", C.c_void_p), ("aux_i0", C.c_int32), ("aux_i1", C.c_int32),
         ("A2", C.c_void_p), ("lda2", C.c_int64), ("B2", C.c_void_p), ("ldb2", C.c_int64), ("K2", C.c_int32),
+        ("ksplit", C.c_int32),
     ]
 
 

@@ -69,6 +69,7 @@ struct EpiArgs {
     long long c_step, p_step, r_step;   // bytes per 4 rows
     long long c_row, p_row, r_row;      // bytes per row
     int c_f32, r_f32;
+    int c_atomic;         // split-K launch: f32 C is accumulated into with vector atomics instead of stored
     float alpha;
     int rows_valid;       // rows of the slab that exist (1..32)
     int row_lo;           // rows of the slab below this one belong to the previous (overlapped) tile
@@ -126,7 +127,10 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], uint32_t stg,
         }
         if (o.R) { x0 += res[it].x; x1 += res[it].y; x2 += res[it].z; x3 += res[it].w; }
         if (o.c_f32) {
-            if (ok) *reinterpret_cast<float4*>(cp) = make_float4(x0, x1, x2, x3);
+            if (ok) {
+                if (o.c_atomic) atomicAdd(reinterpret_cast<float4*>(cp), make_float4(x0, x1, x2, x3));
+                else *reinterpret_cast<float4*>(cp) = make_float4(x0, x1, x2, x3);
+            }
         } else {
             uint2 u; u.x = pack_bf16(x0, x1); u.y = pack_bf16(x2, x3);
             if (ok) *reinterpret_cast<uint2*>(cp) = u;
@@ -311,7 +315,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int mt = (p.M + TM - 1) / TM;
     const int nt = (p.N + BN - 1) / BN;
     const int tiles_per_z = mt * nt;
-    const int total_tiles = tiles_per_z * p.nz[0] * p.nz[1] * p.nz[2];
+    // split-K (GemmDev::ksplit > 1): the tile list repeats once per K slice; slice s contracts over K blocks
+    // [s * kb_per, min(nkb, (s + 1) * kb_per)) and its epilogue adds into C
+    const int tiles_per_split = tiles_per_z * p.nz[0] * p.nz[1] * p.nz[2];
+    const int total_tiles = tiles_per_split * (p.ksplit > 1 ? p.ksplit : 1);
     const int nkb = (p.K + BK - 1) / BK;
     // second contraction segment (GemmDev::K2): nkb2 more K blocks per tile, read through tmA2 / tmB2
     const int nkb2 = (p.K2 + BK - 1) / BK;
@@ -349,6 +356,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const uint32_t tmem_base = *tmem_slot;
 
     auto decode = [&](int t, int& m_blk, int& n_blk, int (&z)[3]) {
+        if (p.ksplit > 1) t %= tiles_per_split;
         int zz = t / tiles_per_z;
         const int r = t - zz * tiles_per_z;
         if (p.raster_n) { m_blk = r / nt; n_blk = r - m_blk * nt; }
@@ -382,6 +390,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int tile_n = n_blk == nt - 1 ? p.n_last : n_blk * BN;
                 int kb_lo = 0, kb_hi = nkb;
                 if (p.band && band_span(p, tile_m, tile_n, TM, BN, nkb, kb_lo, kb_hi)) continue;
+                if (p.ksplit > 1) { kb_lo = (t / tiles_per_split) * p.kb_per; kb_hi = min(nkb, kb_lo + p.kb_per); }
                 const int main_iters = (kb_hi - kb_lo) * p.kg;
                 const int m0 = tile_m + static_cast<int>(rank) * BM;
                 // fused GeGLU: the pair's tile is [128 gate rows | the 128 up rows of the same ff range]
@@ -444,6 +453,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const uint32_t idesc_half = ptx::make_idesc_bf16(TM, BN / 2, p.a_mn, p.b_mn);
             for (int t = cid; t < total_tiles; t += ncl) {
                 int tile_iters = k_iters;
+                if (p.ksplit > 1) {
+                    const int lo = (t / tiles_per_split) * p.kb_per;
+                    tile_iters = min(nkb, lo + p.kb_per) - lo;
+                }
                 bool half = false;
                 if (p.n_half) {
                     int m_blk, n_blk, z[3];
@@ -726,7 +739,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     EpiArgs o;
                     o.Cpre = nullptr; o.R = nullptr; o.bias = nullptr;
                     o.p_row = 0; o.p_step = 0; o.r_row = 0; o.r_step = 0;
-                    o.c_f32 = 0; o.r_f32 = 0; o.alpha = 1.f;
+                    o.c_f32 = 0; o.r_f32 = 0; o.alpha = 1.f; o.c_atomic = 0;
                     o.rows_valid = rows_valid; o.row_lo = row_lo; o.cols_q = 32;
                     o.c_row = p.ldc * 2; o.c_step = 4 * o.c_row;
                     uint8_t* crow = static_cast<uint8_t*>(p.C) + (coff + static_cast<long long>(row0) * p.ldc) * 2;
@@ -812,6 +825,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 o.r_row = p.ldr * re; o.r_step = 4 * o.r_row;
                 o.bias = p.bias ? p.bias + col0 : nullptr;
                 o.c_f32 = p.c_f32; o.r_f32 = p.r_f32; o.alpha = p.alpha;
+                o.c_atomic = p.ksplit > 1;
                 o.rows_valid = rows_valid; o.row_lo = row_lo;
                 o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
                 epi_chunk<ACT>(v, stg, lane, o);
@@ -873,7 +887,7 @@ static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const CU
 
 int gemm2_tiles(const GemmDev& p, int bn) {
     const long long mt = (p.M + 2 * BM - 1) / (2 * BM), nt = (p.N + bn - 1) / bn;
-    const long long t = mt * nt * p.nz[0] * p.nz[1] * p.nz[2];
+    const long long t = mt * nt * p.nz[0] * p.nz[1] * p.nz[2] * (p.ksplit > 1 ? p.ksplit : 1);
     return t < (1ll << 31) ? static_cast<int>(t) : -1;
 }
 

@@ -49,6 +49,10 @@ struct GemmDev {
     // second contraction segment (pt_gemm_args.K2): the accumulator also takes sum_k A2[m][k] * B2[n][k] over K2,
     // read through a second pair of tensor maps after the main K blocks (LoRA: [x | t] . [W | B]^T in one pass)
     int K2;
+    // split-K: > 1 cuts the K blocks into ksplit slices of kb_per blocks, each slice a tile of its own whose epilogue
+    // adds (vector atomics) into the f32 C — thin weight-gradient products whose output has fewer tiles than the
+    // GPU has SM pairs (LoRA: dA [64, in], dB_i [out_i, r] contracted over all B*S rows)
+    int ksplit, kb_per;
 };
 
 // K-block range [lo, hi) a tile must contract over, or skip = true when the whole tile is masked.

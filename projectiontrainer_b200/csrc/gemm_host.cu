@@ -230,6 +230,13 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         PT_REQUIRE(a->nz[0] * a->nz[1] * a->nz[2] == 1 && kg == 1 && a->band == PT_BAND_NONE,
                    "pt_gemm_bf16: the second contraction segment is not batched, grouped or banded");
     }
+    if (a->ksplit > 1 || a->ksplit == -1) {
+        PT_REQUIRE(a->c_dtype == PT_F32 && !a->bias && !a->residual && !a->C_pre && a->act == PT_ACT_NONE &&
+                       a->band == PT_BAND_NONE && kg == 1 && a->K2 == 0,
+                   "pt_gemm_bf16: split-K needs f32 C and no bias / act / residual / C_pre / band / K groups / K2");
+    } else {
+        PT_REQUIRE(a->ksplit == 0 || a->ksplit == 1, "pt_gemm_bf16: bad ksplit %d", a->ksplit);
+    }
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
 
     GemmDev p;
@@ -303,6 +310,15 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     if (rc != PT_OK) return rc;
     rc = encode_operand(&tb, a->B, p.b_mn, a->N, a->K, a->ldb, ext, bst, bn / 2, "B");
     if (rc != PT_OK) return rc;
+    if (a->ksplit > 1 || a->ksplit == -1) {
+        const int nkb = (a->K + BK - 1) / BK;
+        const long long tiles = mt * nt * nbatch, slots = num_sms() / 2;
+        long long want = a->ksplit > 1 ? a->ksplit : (tiles >= slots ? 1 : (slots + tiles - 1) / tiles);
+        if (want > nkb) want = nkb;
+        p.kb_per = static_cast<int>((nkb + want - 1) / want);
+        p.ksplit = (nkb + p.kb_per - 1) / p.kb_per;          // every slice non-empty
+        PT_REQUIRE(tiles * p.ksplit < (1ll << 31), "pt_gemm_bf16: too many tiles");
+    }
     CUtensorMap t_aux = ta, t_c = ta, ta2 = ta, tb2 = tb;
     p.K2 = a->K2;
     if (a->K2 > 0) {

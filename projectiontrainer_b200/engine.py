@@ -568,6 +568,8 @@ class Stage1Engine:
             sv, sk, ev_do, ev_dv, ev_ds, ev_dk = self._side
             main = torch.cuda.current_stream()
         lo = self.lora
+        if lo is not None:
+            lo.grad.zero_()         # the adapter weight gradients are accumulated into by split-K launches
 
         def lora_pre(li, g, dy):
             """dt = (alpha / r) * dy B_blk of packed projection g -> the (dy2, w2) segment of its input-gradient GEMM."""
@@ -583,11 +585,13 @@ class Stage1Engine:
             dB_i = dy_i^T t_i into the i-th diagonal block."""
             if st is None:
                 return
+            # thin outputs contracted over all B*S rows: split-K launches that add into the (cleared) gradient buffer
             grp, dt = st
-            ops.linear_wgrad(dt, x_in, out=grp.A(lo.grad))
+            ops.linear_wgrad(dt, x_in, out=grp.A(lo.grad), accumulate=True)
             gB, r = grp.B(lo.grad), lo.r
             for _, r0, n, i in grp.parts:
-                ops.linear_wgrad(dy[:, r0:r0 + n], t[:, i * r:(i + 1) * r], out=gB[r0:r0 + n, i * r:(i + 1) * r])
+                ops.linear_wgrad(dy[:, r0:r0 + n], t[:, i * r:(i + 1) * r], out=gB[r0:r0 + n, i * r:(i + 1) * r],
+                                 accumulate=True)
 
         for li in range(len(Lm.layers) - 1, -1, -1):
             L, a = Lm.layers[li], s["layers"][li]

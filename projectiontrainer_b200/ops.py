@@ -39,7 +39,7 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
              c_zs=(0, 0, 0), a_mn=False, b_mn=False, bias=None, residual=None, ldr=0,
              r_zs=(0, 0, 0), act=ACT_NONE, alpha=1.0, c_pre=None, kg=1, a_kgs=0, b_kgs=0,
              a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0, band=0, band_window=0, bn_hint=0,
-             aux2=None, aux_i0=0, aux_i1=0, A2=None, lda2=0, B2=None, ldb2=0, K2=0):
+             aux2=None, aux_i0=0, aux_i1=0, A2=None, lda2=0, B2=None, ldb2=0, K2=0, ksplit=0):
     """Fully general launcher; A/B/Cout are tensors used only as base pointers
     (+ element offsets), all geometry comes from the explicit arguments."""
     _req_cuda(A, B, Cout, bias, residual, c_pre, aux)
@@ -89,6 +89,7 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
         if A2.dtype != torch.bfloat16 or B2.dtype != torch.bfloat16:
             raise RuntimeError("gemm operands must be bf16")
         g.A2, g.lda2, g.B2, g.ldb2, g.K2 = A2.data_ptr(), int(lda2), B2.data_ptr(), int(ldb2), int(K2)
+    g.ksplit = int(ksplit)
     if GEMM_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -217,9 +218,11 @@ def attn_delta_fusable(hq: int, hd: int) -> bool:
     return hd % 128 == 0 and (hq * hd) % 256 == 0
 
 
-def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None, alpha=1.0) -> torch.Tensor:
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None, alpha=1.0, accumulate: bool = False) -> torch.Tensor:
     """dw[N,K] = alpha * dy[M,N]^T @ x[M,K] (f32 out), both operands MN-major, no transposes.  dy / x / out may be
-    column slices of wider matrices (LoRA: one adapter's columns of a packed projection)."""
+    column slices of wider matrices (LoRA: one adapter's columns of a packed projection).  accumulate=True:
+    dw += ... as a split-K launch (pt_gemm_args.ksplit = -1) — for small outputs contracted over many rows, where one
+    tile per output block would leave most SMs idle; the caller clears `out` first."""
     M, N = dy.shape
     M2, K = x.shape
     assert M == M2 and dy.stride(1) == 1 and x.stride(1) == 1
@@ -227,7 +230,7 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out=None, alpha=1.0) -> t
         out = torch.empty((N, K), dtype=torch.float32, device=dy.device)
     assert out.stride(1) == 1 and tuple(out.shape) == (N, K)
     gemm_raw(M=N, N=K, K=M, A=dy, lda=dy.stride(0), a_mn=True, B=x, ldb=x.stride(0), b_mn=True,
-             Cout=out, ldc=out.stride(0), alpha=alpha)
+             Cout=out, ldc=out.stride(0), alpha=alpha, ksplit=-1 if accumulate else 0)
     return out
 
 

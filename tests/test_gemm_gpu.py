@@ -368,3 +368,28 @@ def test_gemm_wgrad_on_column_slices(cuda_dev):
     assert (gB[mask] == 7.0).all()          # nothing outside the diagonal blocks was written
     dt, x = _rand((T, R), cuda_dev), _rand((T, 1152), cuda_dev)
     _check(ops.linear_wgrad(dt, x, alpha=2.0), 2.0 * dt.float().t() @ x.float(), tol=2e-3, name="dA")
+
+
+@pytest.mark.parametrize("T,N,K", [(22496, 64, 1152), (1406, 1024, 16), (22496, 16, 64), (703, 256, 256), (100, 64, 72)])
+def test_gemm_split_k_accumulates_into_f32_output(cuda_dev, T, N, K):
+    """ksplit: the contraction is cut into slices that run as separate tiles and add into C with f32 atomics
+    (C += alpha * A^T B): thin weight gradients contracted over all rows of the batch."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(T + N)
+    dy, x = _rand((T, N), cuda_dev), _rand((T, K), cuda_dev)
+    ref = dy.float().t() @ x.float()
+    out = torch.zeros(N, K, device=cuda_dev)
+    ops.linear_wgrad(dy, x, out=out, accumulate=True)
+    _check(out, ref, tol=2e-3, name="auto split")
+    ops.linear_wgrad(dy, x, out=out, accumulate=True, alpha=0.5)             # adds to what is there
+    _check(out, 1.5 * ref, tol=2e-3, name="accumulate")
+    # explicit slice counts, K-major operands, a contraction that is not a multiple of the K block
+    Tp = (T + 7) // 8 * 8                       # row stride of a K-major operand: a multiple of 8 elements
+    a, b = _rand((N, Tp), cuda_dev)[:, :T], _rand((K, Tp), cuda_dev)[:, :T]
+    ref = a.float() @ b.float().t()
+    for ks in (2, 7, 1000):
+        out = torch.zeros(N, K, device=cuda_dev)
+        ops.gemm_raw(M=N, N=K, K=T, A=a, lda=Tp, B=b, ldb=Tp, Cout=out, ldc=K, ksplit=ks)
+        _check(out, ref, tol=2e-3, name=f"ksplit {ks}")
+    with pytest.raises(RuntimeError, match="split-K"):
+        ops.gemm_raw(M=N, N=K, K=T, A=a, lda=Tp, B=b, ldb=Tp, Cout=out.to(torch.bfloat16), ldc=K, ksplit=2)
