@@ -358,6 +358,31 @@ int pt_image_preprocess_static(const uint8_t* src_rgb, int H, int W, long long s
                                uint8_t* dst_u8_hwc, int out_h, int out_w, float mean0, float mean1, float mean2,
                                float std0, float std1, float std2, double rescale, void* stream);
 
+/* ---- baseline JPEG decode in front of pt_image_preprocess (the decode half) ---------------
+ * ref:Stage1/train_projection_stage1.py:99 and ref:Stage2/dataset.py:86-90: `Image.open(path).convert("RGB")`, i.e.
+ * Pillow's libjpeg-turbo decode of a baseline file: Huffman decode, de-quantise, islow integer IDCT, fancy chroma
+ * up-sampling (h2v1 / h2v2), JFIF YCbCr -> RGB; bit-exact with Pillow.  Host part (no GPU needed, meant for the
+ * data-loader workers):
+ *   pt_jpeg_plan   parses n files (pointers + sizes); fills widths[n], heights[n], rgb_offsets[n + 1] (byte offset of
+ *                  image i in the packed destination, [n] = its total size) and the sizes of the blob and the
+ *                  device workspace
+ *   pt_jpeg_pack   writes the blob (16-byte aligned host buffer, ideally pinned): per-image geometry, quantisation
+ *                  and Huffman look-up tables, and the entropy-coded data with the FF00 stuffing removed, cut at the
+ *                  restart markers
+ * Device part:
+ *   pt_jpeg_decode_batch   host_blob = the packed blob (its header is read on the host), dev_blob = the same bytes
+ *                  in device memory; dst_rgb = device uint8, image i at rgb_offsets[i] as [height][width][3];
+ *                  workspace = device scratch (256-byte aligned).  One Huffman launch for the whole batch (one warp
+ *                  per restart segment; a file without restart markers is one segment), then IDCT and colour
+ *                  launches per image.
+ * Rejected with PT_ERR_INVALID (nothing falls back): progressive / lossless / arithmetic / 12-bit files, CMYK,
+ * multi-scan files, chroma sub-sampling other than 4:4:4 / 4:2:2 / 4:2:0. */
+int pt_jpeg_plan(const uint8_t* const* files, const int64_t* sizes, int n, int32_t* widths, int32_t* heights,
+                 int64_t* rgb_offsets, int64_t* blob_bytes, int64_t* workspace_bytes);
+int pt_jpeg_pack(const uint8_t* const* files, const int64_t* sizes, int n, uint8_t* host_blob, int64_t blob_bytes);
+int pt_jpeg_decode_batch(const uint8_t* host_blob, const uint8_t* dev_blob, uint8_t* dst_rgb, void* workspace,
+                         int64_t workspace_bytes, void* stream);
+
 /* ---- NF4 frozen LLM weights -----------------------------------------------------------
  * ref:Stage1/train_projection_stage1.py:192-210: `--enable_qlora` loads the frozen LLM through bitsandbytes with
  * BitsAndBytesConfig(load_in_4bit, "nf4", compute dtype bf16, double quant).  These entry points restate

@@ -69,7 +69,7 @@ def check(rc: int, what: str) -> None:
 
 
 # kernels launched per C-ABI call (for the bench's gpu_launches claim)
-KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_image_preprocess": 3}
+KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_image_preprocess": 3, "pt_jpeg_decode_batch": 3}
 launch_count = 0
 
 

@@ -459,6 +459,51 @@ def image_preprocess(src_u8_hwc, dst_chw, workspace, *, mean=(0.5, 0.5, 0.5), st
               C.c_longlong(int(workspace.numel() * workspace.element_size())), _stream())
 
 
+# ----------------------------------------------------------------------------- JPEG decode
+def jpeg_pack(files, pin: bool = True) -> dict:
+    """Host half of the GPU JPEG decode (runs without a GPU; meant for DataLoader workers): `files` = encoded baseline
+    JPEG files as bytes / bytearray / uint8 tensors.  Returns {"blob": uint8 host tensor (pinned when possible),
+    "sizes": [(H, W)], "rgb_offsets": [n + 1], "workspace_bytes"} for jpeg_decode."""
+    n = len(files)
+    keep, addr, length = [], [], []
+    for f in files:
+        if isinstance(f, torch.Tensor):
+            if f.dtype != torch.uint8 or f.is_cuda or not f.is_contiguous():
+                raise RuntimeError("jpeg_pack: file tensors must be contiguous host uint8")
+            keep.append(f); addr.append(f.data_ptr()); length.append(f.numel())
+        else:
+            b = bytes(f) if not isinstance(f, bytes) else f
+            keep.append(b); addr.append(C.cast(C.c_char_p(b), C.c_void_p).value); length.append(len(b))
+    ptrs = (C.c_void_p * n)(*addr)
+    sizes = (C.c_int64 * n)(*length)
+    w, h = (C.c_int32 * n)(), (C.c_int32 * n)()
+    offs = (C.c_int64 * (n + 1))()
+    blob_b, ws_b = C.c_int64(0), C.c_int64(0)
+    L = _lib.lib()
+    _lib.check(L.pt_jpeg_plan(ptrs, sizes, n, w, h, offs, C.byref(blob_b), C.byref(ws_b)), "pt_jpeg_plan")
+    blob = torch.empty(blob_b.value, dtype=torch.uint8)
+    if pin and torch.cuda.is_available():
+        blob = blob.pin_memory()
+    _lib.check(L.pt_jpeg_pack(ptrs, sizes, n, C.c_void_p(blob.data_ptr()), C.c_int64(blob_b.value)), "pt_jpeg_pack")
+    return {"blob": blob, "sizes": [(int(h[i]), int(w[i])) for i in range(n)], "rgb_offsets": [int(o) for o in offs],
+            "workspace_bytes": int(ws_b.value)}
+
+
+def jpeg_decode(packed: dict, device, workspace: torch.Tensor | None = None) -> list:
+    """Device half: uploads the blob and decodes the batch; returns one uint8 [H, W, 3] CUDA tensor per file (views of
+    one buffer), bit-exact with `PIL.Image.open(f).convert("RGB")`."""
+    blob = packed["blob"]
+    dev_blob = blob.to(device, non_blocking=True)
+    need = packed["workspace_bytes"]
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty(need, dtype=torch.uint8, device=device)
+    offs = packed["rgb_offsets"]
+    dst = torch.empty(offs[-1], dtype=torch.uint8, device=device)
+    _lib.call("pt_jpeg_decode_batch", C.c_void_p(blob.data_ptr()), _ptr(dev_blob), _ptr(dst), _ptr(workspace),
+              C.c_int64(workspace.numel()), _stream())
+    return [dst[offs[i]:offs[i] + 3 * hh * ww].view(hh, ww, 3) for i, (hh, ww) in enumerate(packed["sizes"])]
+
+
 # ----------------------------------------------------------------------------- NF4 frozen weights
 _NF4_DYNAMIC_MAP: dict = {}
 

@@ -1,0 +1,113 @@
+"""GPU baseline-JPEG decode (decode half) through the C ABI against Pillow — the library the
+reference's datasets call (`Image.open(path).convert("RGB")`, ref:Stage1/train_projection_stage1.py:99): every stage is
+integer work with libjpeg's constants, so the bar is bit-exact.  Files are produced here with Pillow's encoder."""
+import io
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _encode(arr, **kw):
+    from PIL import Image
+    b = io.BytesIO()
+    Image.fromarray(arr).save(b, "JPEG", **kw)
+    return b.getvalue()
+
+
+def _pillow(data):
+    from PIL import Image
+    return np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+
+
+def _images(H, W, rng):
+    yy, xx = np.mgrid[0:H, 0:W]
+    smooth = np.stack([yy * 255 // max(H - 1, 1), xx * 255 // max(W - 1, 1), (yy * 3 + xx * 5) % 256], -1).astype(np.uint8)
+    noise = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    edges = np.zeros((H, W, 3), dtype=np.uint8)
+    edges[::7, :, 0] = 255
+    edges[:, ::5, 1] = 255
+    edges[H // 3:, W // 2:, 2] = 200
+    return smooth, noise, edges
+
+
+@pytest.mark.parametrize("H,W", [(64, 64), (40, 56), (33, 17), (1, 1), (2, 3), (8, 8), (17, 16), (250, 301), (16, 2)])
+@pytest.mark.parametrize("subsampling", [0, 1, 2, "gray"])
+def test_jpeg_decode_bit_exact_vs_pillow(cuda_dev, H, W, subsampling):
+    from projectiontrainer_b200 import ops
+    rng = np.random.default_rng(H * 131 + W)
+    files = []
+    for img in _images(H, W, rng):
+        for q in (35, 90, 100):
+            if subsampling == "gray":
+                files.append(_encode(img[..., 0], quality=q))
+            else:
+                files.append(_encode(img, quality=q, subsampling=subsampling))
+    out = ops.jpeg_decode(ops.jpeg_pack(files), cuda_dev)
+    torch.cuda.synchronize()
+    for i, (f, o) in enumerate(zip(files, out)):
+        ref = _pillow(f)
+        got = o.cpu().numpy()
+        assert got.shape == ref.shape, (i, got.shape, ref.shape)
+        bad = int((got != ref).sum())
+        assert bad == 0, (i, bad, int(np.abs(got.astype(int) - ref.astype(int)).max()))
+
+
+@pytest.mark.parametrize("kw", [dict(restart_marker_blocks=1), dict(restart_marker_blocks=7), dict(restart_marker_rows=1),
+                                dict(optimize=True), dict(optimize=True, restart_marker_blocks=3)])
+@pytest.mark.parametrize("subsampling", [0, 2, "gray"])
+def test_jpeg_restart_intervals_and_optimised_tables(cuda_dev, kw, subsampling):
+    from projectiontrainer_b200 import ops
+    rng = np.random.default_rng(7)
+    files = []
+    for H, W in [(100, 130), (37, 259)]:
+        for img in _images(H, W, rng):
+            files.append(_encode(img[..., 1], quality=80, **kw) if subsampling == "gray"
+                         else _encode(img, quality=80, subsampling=subsampling, **kw))
+    packed = ops.jpeg_pack(files)
+    out = ops.jpeg_decode(packed, cuda_dev)
+    torch.cuda.synchronize()
+    for f, o in zip(files, out):
+        assert np.array_equal(o.cpu().numpy(), _pillow(f))
+
+
+def test_jpeg_chest_xray_sized_batch_and_preprocess(cuda_dev):
+    """A batch of 2500 x 2048 grayscale files (the dataset's image size) decoded side by side, then through
+    pt_image_preprocess: `pixel_values` equal to what Pillow decode + Pillow resize + the processor give."""
+    from PIL import Image
+    from oracle import image_oracle as IO
+    from projectiontrainer_b200 import ops
+    rng = np.random.default_rng(3)
+    H, W, S = 2500, 2048, 384
+    yy, xx = np.mgrid[0:H, 0:W]
+    base = (128 + 100 * np.sin(yy / 97.0) * np.cos(xx / 61.0)).astype(np.float32)
+    files = [_encode(np.clip(base + rng.normal(0, 12 * (i + 1), (H, W)), 0, 255).astype(np.uint8), quality=92 - 10 * i)
+             for i in range(3)]
+    out = ops.jpeg_decode(ops.jpeg_pack(files), cuda_dev)
+    torch.cuda.synchronize()
+    for f, o in zip(files, out):
+        ref = _pillow(f)
+        assert np.array_equal(o.cpu().numpy(), ref)
+        ws = torch.empty(ops.image_preprocess_workspace(H, W, S, S), dtype=torch.uint8, device=cuda_dev)
+        px = torch.empty(3, S, S, device=cuda_dev)
+        ops.image_preprocess(o, px, ws)
+        ref_px = IO.rescale_normalize(np.asarray(Image.fromarray(ref).resize((S, S))))
+        assert np.array_equal(px.cpu().numpy(), ref_px)
+
+
+def test_jpeg_unsupported_files_are_rejected(cuda_dev):
+    from PIL import Image
+    from projectiontrainer_b200 import ops
+    img = np.random.default_rng(0).integers(0, 256, (32, 32, 3), dtype=np.uint8)
+    with pytest.raises(RuntimeError, match="progressive"):
+        ops.jpeg_pack([_encode(img, progressive=True)])
+    with pytest.raises(RuntimeError, match="not a JPEG"):
+        ops.jpeg_pack([b"\x89PNG\r\n\x1a\n" + bytes(64)])
+    b = io.BytesIO()
+    Image.fromarray(np.dstack([img, img[..., :1]])).convert("CMYK").save(b, "JPEG")
+    with pytest.raises(RuntimeError, match="components"):
+        ops.jpeg_pack([b.getvalue()])
+    with pytest.raises(RuntimeError, match="truncated|restart segments|bad segment"):
+        ops.jpeg_pack([_encode(img, restart_marker_blocks=1)[:400]])
