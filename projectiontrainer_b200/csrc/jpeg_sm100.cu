@@ -50,14 +50,32 @@ struct JpegImg {                   // per image, in the blob (host and device re
 };
 
 struct JpegSeg {                   // one restart segment
-    int32_t img, first_mcu, n_mcu, pad;
+    int32_t img, first_mcu, n_mcu;
+    int32_t mode;                  // 0: decoded by one warp front to back; 1: decoded in parallel sub-sequences
     int64_t byte_off, byte_len;    // blob offset (8-byte aligned) and length of the un-stuffed bit stream
+    int32_t sub0, nsub;            // mode 1: first entry in the SubInfo array, sub-sequences of kSubBits bits
+    int32_t total_blocks, pad;     // blocks the segment holds (n_mcu * blocks per MCU)
+};
+
+constexpr int kSubBits = 1024;     // sub-sequence length of the parallel Huffman decode
+constexpr int kSubThreads = 256;   // sub-sequences synchronised inside one CTA
+constexpr int64_t kParallelMinBytes = 8192;     // shorter segments take the one-warp path
+
+struct JpegCta { int32_t seg, first_sub; };     // work list of the per-sub-sequence kernels
+
+struct SubInfo {                   // device scratch, one per sub-sequence
+    int32_t p_start, p_end;        // bit positions in the segment: first symbol decoded here / first symbol of the next
+    int32_t st_start, st_end;      // parser state there: (block slot in the MCU << 8) | zig-zag index
+    int32_t nblk, blk0;            // blocks completed inside; blocks completed before (exclusive scan)
 };
 
 struct JpegBlobHeader {
     uint32_t magic; int32_t n, total_segs, pad;
     int64_t blob_bytes, workspace_bytes, coef_bytes, rgb_bytes;
     int64_t imgs_off, segs_off;
+    int64_t cta_off, pseg_off;     // JpegCta list, list of the mode-1 segment indices (capacities fixed by the plan)
+    int32_t n_cta, n_pseg, total_subs, pad1;
+    int64_t sub_off;               // workspace offset of the SubInfo array
 };
 
 static const uint8_t kZigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48,
@@ -264,12 +282,24 @@ static int layout_batch(const uint8_t* const* files, const int64_t* sizes, int n
     int64_t o = up(sizeof(JpegBlobHeader), 16);
     h.imgs_off = o; o = up(o + static_cast<int64_t>(n) * sizeof(JpegImg), 16);
     h.segs_off = o; o = up(o + total_segs * sizeof(JpegSeg), 16);
+    // the un-stuffed lengths are known only after packing: capacities from the stuffed lengths
+    int64_t cap_subs = 0, cap_cta = 0;
+    for (int i = 0; i < n; ++i) {
+        const int64_t len = L.P[i].scan_end - L.P[i].scan_begin;
+        const int64_t subs = len * 8 / kSubBits + 2 * L.P[i].im.nseg;
+        cap_subs += subs;
+        cap_cta += subs / kSubThreads + L.P[i].im.nseg;
+    }
+    PT_REQUIRE(cap_subs < (1ll << 31), "pt_jpeg: batch too large");
+    h.cta_off = o; o = up(o + cap_cta * sizeof(JpegCta), 16);
+    h.pseg_off = o; o = up(o + total_segs * 4, 16);
     int64_t ws = 0, rgb = 0;
     for (int i = 0; i < n; ++i) {
         JpegImg& im = L.P[i].im;
         im.tables_off = o; o = up(o + kTablesBytes, 16);
         // un-stuffed data is never longer than the stuffed data; every segment start is aligned to 8 bytes
-        o = up(o + (L.P[i].scan_end - L.P[i].scan_begin) + 8ll * im.nseg + 16, 16);
+        // (+ room behind the last byte: the parallel parse reads up to one sub-sequence past a segment's end)
+        o = up(o + (L.P[i].scan_end - L.P[i].scan_begin) + 8ll * im.nseg + kSubBits / 8 + 64, 16);
         for (int c = 0; c < im.ncomp; ++c) { im.coef_off[c] = ws; ws = up(ws + 128ll * im.bw[c] * im.bh[c], 256); }
         im.rgb_off = rgb; rgb += 3ll * im.width * im.height;
     }
@@ -278,6 +308,7 @@ static int layout_batch(const uint8_t* const* files, const int64_t* sizes, int n
         JpegImg& im = L.P[i].im;
         for (int c = 0; c < im.ncomp; ++c) { im.plane_off[c] = ws; ws = up(ws + 64ll * im.bw[c] * im.bh[c], 256); }
     }
+    h.sub_off = ws; ws = up(ws + cap_subs * static_cast<int64_t>(sizeof(SubInfo)), 256);
     h.blob_bytes = o; h.workspace_bytes = ws; h.rgb_bytes = rgb;
     return PT_OK;
 }
@@ -311,6 +342,9 @@ extern "C" int pt_jpeg_pack(const uint8_t* const* files, const int64_t* sizes, i
     memcpy(blob, &L.h, sizeof(L.h));
     JpegImg* imgs = reinterpret_cast<JpegImg*>(blob + L.h.imgs_off);
     JpegSeg* segs = reinterpret_cast<JpegSeg*>(blob + L.h.segs_off);
+    JpegBlobHeader* hdr = reinterpret_cast<JpegBlobHeader*>(blob);
+    JpegCta* ctas = reinterpret_cast<JpegCta*>(blob + L.h.cta_off);
+    int32_t* pseg = reinterpret_cast<int32_t*>(blob + L.h.pseg_off);
     for (int i = 0; i < n; ++i) {
         const Parsed& P = L.P[i];
         const JpegImg& im = P.im;
@@ -326,13 +360,26 @@ extern "C" int pt_jpeg_pack(const uint8_t* const* files, const int64_t* sizes, i
         int64_t o = up(im.tables_off + kTablesBytes, 16);
         int seg = 0;
         int64_t start = o, q = P.scan_begin;
-        auto close = [&](int64_t end_o) {
+        auto close = [&](int64_t end_o) -> int {
             JpegSeg& s = segs[im.seg0 + seg];
             s.img = i;
             s.first_mcu = seg * (im.restart_interval > 0 ? im.restart_interval : 0);
             s.n_mcu = static_cast<int32_t>(im.restart_interval > 0
                                                ? std::min<int64_t>(im.restart_interval, mcus - s.first_mcu) : mcus);
             s.byte_off = start; s.byte_len = end_o - start;
+            int bpm = 0;
+            for (int c = 0; c < im.ncomp; ++c) bpm += im.hs[c] * im.vs[c];
+            s.total_blocks = s.n_mcu * bpm;
+            PT_REQUIRE(s.byte_len < (1ll << 27), "jpeg[%d]: entropy-coded segment too long", i);
+            s.mode = s.byte_len >= kParallelMinBytes ? 1 : 0;
+            if (s.mode) {
+                s.nsub = static_cast<int32_t>((s.byte_len * 8 + kSubBits - 1) / kSubBits);
+                s.sub0 = hdr->total_subs;
+                hdr->total_subs += s.nsub;
+                pseg[hdr->n_pseg++] = im.seg0 + seg;
+                for (int fs = 0; fs < s.nsub; fs += kSubThreads) { ctas[hdr->n_cta].seg = im.seg0 + seg; ctas[hdr->n_cta++].first_sub = fs; }
+            }
+            return PT_OK;
         };
         while (q < P.scan_end) {
             const uint8_t b = f[q++];
@@ -343,12 +390,14 @@ extern "C" int pt_jpeg_pack(const uint8_t* const* files, const int64_t* sizes, i
             else if (m >= 0xD0 && m <= 0xD7) {
                 ++q;
                 PT_REQUIRE(seg + 1 < im.nseg, "jpeg[%d]: more restart markers than the restart interval allows", i);
-                close(o);
+                rc = close(o);
+                if (rc != PT_OK) return rc;
                 ++seg;
                 o = up(o, 8); start = o;
             }                                           // else: a fill byte (FF FF): drop this FF, look at the next
         }
-        close(o);
+        rc = close(o);
+        if (rc != PT_OK) return rc;
         PT_REQUIRE(seg + 1 == im.nseg, "jpeg[%d]: %d restart segments found, %d expected (truncated file?)", i, seg + 1, im.nseg);
     }
     return PT_OK;
@@ -395,6 +444,7 @@ jpeg_huffman_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t 
     __shared__ HuffDev sh[4];          // dc luma-side, dc chroma-side, ac luma-side, ac chroma-side as the scan names them
     __shared__ int sel_dc[3], sel_ac[3];
     const JpegSeg seg = reinterpret_cast<const JpegSeg*>(blob + segs_off)[blockIdx.x];
+    if (seg.mode != 0) return;         // long segments: the parallel kernels below
     const JpegImg& im = reinterpret_cast<const JpegImg*>(blob + imgs_off)[seg.img];
     const HuffDev* tab = reinterpret_cast<const HuffDev*>(blob + im.tables_off + 4 * 64 * 2);
     // at most two distinct DC and two distinct AC tables are in use (luma / chroma)
@@ -463,6 +513,286 @@ jpeg_huffman_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t 
                 }
         }
         if (++mx == im.mcux) { mx = 0; ++my; }
+    }
+}
+
+// ---- device [1b]: Huffman decode of long segments in parallel sub-sequences ------------------------------------
+// A file without restart markers is one bit stream that only parses front to back.  Huffman streams re-synchronise,
+// though: a decoder started at a wrong position falls into step with the true parse after a few symbols.  So
+// (Klein & Wiseman 2003; Weissenberger & Schmidt 2018 for JPEG): cut the stream into sub-sequences of kSubBits bits,
+//   A  every thread parses its sub-sequence from a guessed state; then, repeatedly, re-parses it from the state in
+//      which its left neighbour ENDED, until no end state in the CTA changes (state = bit position, block slot in the
+//      MCU, zig-zag index: everything the further parse depends on; DC prediction is handled separately);
+//   B  one thread per segment walks the CTA boundaries left to right and re-parses from the true state until the
+//      stored end state is met again;
+//   C  exclusive scan of the blocks completed per sub-sequence -> first block index of each;
+//   D  every thread parses its sub-sequence once more from its now-true start state and stores the coefficients (DC
+//      as differences);
+//   E  running sums turn the DC differences of each component into DC values.
+struct SegCtx {
+    const uint32_t* words;         // un-stuffed stream
+    int bpm;                       // blocks per MCU
+    int slot_comp[6], slot_h[6], slot_v[6];
+};
+
+__device__ __forceinline__ void seg_context(const JpegImg& im, const uint8_t* blob, const JpegSeg& seg, SegCtx& cx) {
+    cx.words = reinterpret_cast<const uint32_t*>(blob + seg.byte_off);
+    cx.bpm = 0;
+    for (int c = 0; c < im.ncomp; ++c)
+        for (int v = 0; v < im.vs[c]; ++v)
+            for (int h = 0; h < im.hs[c]; ++h) { cx.slot_comp[cx.bpm] = c; cx.slot_h[cx.bpm] = h; cx.slot_v[cx.bpm] = v; ++cx.bpm; }
+}
+
+struct PosReader {                 // BitReader that knows its bit position in the segment
+    const uint32_t* base; const uint32_t* p; uint64_t buf; int cnt;
+    __device__ __forceinline__ void seek(const uint32_t* b, int bit) {
+        base = b; p = b + (bit >> 5); buf = 0; cnt = 0;
+        refill(); skip(bit & 31); refill();
+    }
+    __device__ __forceinline__ void refill() {
+        if (cnt <= 32) {
+            const uint32_t w = __byte_perm(__ldg(p++), 0, 0x0123);
+            buf |= static_cast<uint64_t>(w) << (32 - cnt);
+            cnt += 32;
+        }
+    }
+    __device__ __forceinline__ uint32_t peek(int n) const { return static_cast<uint32_t>(buf >> (64 - n)); }
+    __device__ __forceinline__ void skip(int n) { buf <<= n; cnt -= n; }
+    __device__ __forceinline__ int pos() const { return static_cast<int>(p - base) * 32 - cnt; }
+};
+
+__device__ __forceinline__ int huff_symbol_p(PosReader& br, const HuffDev& H) {
+    const uint32_t lk = H.look[br.peek(kLookBits)];
+    if (lk) { br.skip(lk >> 8); return lk & 0xFF; }
+    int l = kLookBits + 1;
+    int code = br.peek(l);
+    while (l <= 16 && code > H.maxcode[l]) { ++l; code = br.peek(l); }
+    if (l > 16) { br.skip(16); return 0; }
+    br.skip(l);
+    return H.huffval[(code + H.valoff[l]) & 0xFF];
+}
+
+// Parse from (p, state) while symbols START before bit `limit`; returns the end position / state and the number of
+// blocks completed.  WRITE: also store the coefficients, the first block being number blk of the segment.
+template <bool WRITE>
+__device__ __forceinline__ void parse_sub(const SegCtx& cx, const HuffDev* sh, const int* sel_dc, const int* sel_ac,
+                                          int p, int st, int limit, int& p_end, int& st_end, int& nblk,
+                                          const JpegImg* im, const JpegSeg* seg, uint8_t* ws, int blk) {
+    PosReader br;
+    br.seek(cx.words, p);
+    int slot = st >> 8, k = st & 0xFF, done = 0;
+    int16_t* out = nullptr;
+    [[maybe_unused]] auto locate = [&]() {
+        const int mcu = seg->first_mcu + blk / cx.bpm;
+        const int c = cx.slot_comp[slot];
+        const int my = mcu / im->mcux, mx = mcu - my * im->mcux;
+        out = reinterpret_cast<int16_t*>(ws + im->coef_off[c]) +
+              (static_cast<int64_t>(my * im->vs[c] + cx.slot_v[slot]) * im->bw[c] + (mx * im->hs[c] + cx.slot_h[slot])) * 64;
+    };
+    if (WRITE) {
+        if (blk >= seg->total_blocks) { p_end = p; st_end = st; nblk = 0; return; }
+        locate();
+    }
+    while (br.pos() < limit) {
+        const int c = cx.slot_comp[slot];
+        br.refill();
+        if (k == 0) {
+            const int s = huff_symbol_p(br, sh[sel_dc[c]]);
+            if (s) {
+                br.refill();
+                const int d = huff_extend(br.peek(s), s);
+                br.skip(s);
+                if (WRITE && d) out[0] = static_cast<int16_t>(d);
+            }
+            k = 1;
+        } else {
+            const int rs = huff_symbol_p(br, sh[sel_ac[c]]);
+            const int r = rs >> 4, s = rs & 15;
+            if (s) {
+                k += r;
+                br.refill();
+                const int val = huff_extend(br.peek(s), s);
+                br.skip(s);
+                if (WRITE && k < 64) out[c_zigzag[k]] = static_cast<int16_t>(val);
+                ++k;
+            } else if (r == 15) {
+                k += 16;
+            } else {
+                k = 64;
+            }
+        }
+        if (k >= 64) {
+            k = 0; ++done;
+            if (++slot == cx.bpm) slot = 0;
+            if (WRITE) {
+                if (++blk >= seg->total_blocks) break;
+                locate();
+            }
+        }
+    }
+    p_end = br.pos(); st_end = (slot << 8) | k; nblk = done;
+}
+
+// shared by kernels A, B, D: the image's four Huffman tables into shared memory
+__device__ __forceinline__ void stage_tables(const uint8_t* blob, const JpegImg& im, HuffDev* sh, int* sel_dc, int* sel_ac) {
+    const HuffDev* tab = reinterpret_cast<const HuffDev*>(blob + im.tables_off + 4 * 64 * 2);
+    int dc_ids[2] = {im.dcsel[0], im.dcsel[0]}, ac_ids[2] = {im.acsel[0], im.acsel[0]};
+    for (int c = 1; c < im.ncomp; ++c) {
+        if (im.dcsel[c] != dc_ids[0]) dc_ids[1] = im.dcsel[c];
+        if (im.acsel[c] != ac_ids[0]) ac_ids[1] = im.acsel[c];
+    }
+    constexpr int W = sizeof(HuffDev) / 4;
+    for (int t = 0; t < 4; ++t) {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(tab + (t < 2 ? dc_ids[t] : 4 + ac_ids[t - 2]));
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&sh[t]);
+        for (int i = threadIdx.x; i < W; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    if (threadIdx.x < 3) {
+        const int c = threadIdx.x < im.ncomp ? threadIdx.x : 0;
+        sel_dc[threadIdx.x] = im.dcsel[c] == dc_ids[0] ? 0 : 1;
+        sel_ac[threadIdx.x] = im.acsel[c] == ac_ids[0] ? 2 : 3;
+    }
+    __syncthreads();
+}
+
+// A: synchronise the sub-sequences of one CTA with each other
+__global__ void __launch_bounds__(kSubThreads)
+jpeg_sync_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t segs_off, int64_t cta_off, SubInfo* __restrict__ subs) {
+    __shared__ HuffDev sh[4];
+    __shared__ int sel_dc[3], sel_ac[3];
+    __shared__ int e_p[kSubThreads], e_st[kSubThreads];
+    const JpegCta w = reinterpret_cast<const JpegCta*>(blob + cta_off)[blockIdx.x];
+    const JpegSeg& seg = reinterpret_cast<const JpegSeg*>(blob + segs_off)[w.seg];
+    const JpegImg& im = reinterpret_cast<const JpegImg*>(blob + imgs_off)[seg.img];
+    stage_tables(blob, im, sh, sel_dc, sel_ac);
+    SegCtx cx;
+    seg_context(im, blob, seg, cx);
+    const int t = threadIdx.x, sub = w.first_sub + t;
+    const bool valid = sub < seg.nsub;
+    const int limit = (sub + 1) * kSubBits;
+    int p0 = sub * kSubBits, st0 = 0, pe = p0, se = 0, nb = 0;
+    if (valid) parse_sub<false>(cx, sh, sel_dc, sel_ac, p0, st0, limit, pe, se, nb, nullptr, nullptr, nullptr, 0);
+    e_p[t] = pe; e_st[t] = se;
+    for (int it = 0; it < kSubThreads; ++it) {
+        __syncthreads();
+        const int pp = t > 0 ? e_p[t - 1] : p0, ps = t > 0 ? e_st[t - 1] : st0;
+        const bool redo = valid && t > 0 && (pp != p0 || ps != st0);
+        __syncthreads();
+        if (redo) {
+            p0 = pp; st0 = ps;
+            parse_sub<false>(cx, sh, sel_dc, sel_ac, p0, st0, limit, pe, se, nb, nullptr, nullptr, nullptr, 0);
+            e_p[t] = pe; e_st[t] = se;
+        }
+        if (!__syncthreads_or(redo)) break;
+    }
+    if (valid) {
+        SubInfo& o = subs[seg.sub0 + sub];
+        o.p_start = p0; o.st_start = st0; o.p_end = pe; o.st_end = se; o.nblk = nb; o.blk0 = 0;
+    }
+}
+
+// B: carry the true state across the CTA boundaries of a segment, then C: exclusive scan of the block counts
+__global__ void __launch_bounds__(32)
+jpeg_stitch_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t segs_off, int64_t pseg_off, SubInfo* __restrict__ subs) {
+    __shared__ HuffDev sh[4];
+    __shared__ int sel_dc[3], sel_ac[3];
+    const int si = reinterpret_cast<const int32_t*>(blob + pseg_off)[blockIdx.x];
+    const JpegSeg& seg = reinterpret_cast<const JpegSeg*>(blob + segs_off)[si];
+    const JpegImg& im = reinterpret_cast<const JpegImg*>(blob + imgs_off)[seg.img];
+    stage_tables(blob, im, sh, sel_dc, sel_ac);
+    SubInfo* S = subs + seg.sub0;
+    if (threadIdx.x == 0) {
+        SegCtx cx;
+        seg_context(im, blob, seg, cx);
+        for (int first = kSubThreads; first < seg.nsub; first += kSubThreads) {
+            int pp = S[first - 1].p_end, ps = S[first - 1].st_end;
+            for (int cur = first; cur < seg.nsub; ++cur) {
+                if (S[cur].p_start == pp && S[cur].st_start == ps) break;          // in step with the true parse
+                int pe, se, nb;
+                parse_sub<false>(cx, sh, sel_dc, sel_ac, pp, ps, (cur + 1) * kSubBits, pe, se, nb, nullptr, nullptr, nullptr, 0);
+                const bool same_end = pe == S[cur].p_end && se == S[cur].st_end;
+                S[cur].p_start = pp; S[cur].st_start = ps; S[cur].p_end = pe; S[cur].st_end = se; S[cur].nblk = nb;
+                if (same_end) break;
+                pp = pe; ps = se;
+            }
+        }
+    }
+    __syncwarp();
+    // exclusive scan of nblk over the segment's sub-sequences (warp scan, 32 at a time)
+    int carry = 0;
+    for (int base = 0; base < seg.nsub; base += 32) {
+        const int i = base + threadIdx.x;
+        const int v = i < seg.nsub ? S[i].nblk : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, inc, o); if (static_cast<int>(threadIdx.x) >= o) inc += u; }
+        if (i < seg.nsub) S[i].blk0 = carry + inc - v;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
+// D: the final parse, storing coefficients
+__global__ void __launch_bounds__(kSubThreads)
+jpeg_write_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t segs_off, int64_t cta_off,
+                  const SubInfo* __restrict__ subs, uint8_t* __restrict__ ws) {
+    __shared__ HuffDev sh[4];
+    __shared__ int sel_dc[3], sel_ac[3];
+    const JpegCta w = reinterpret_cast<const JpegCta*>(blob + cta_off)[blockIdx.x];
+    const JpegSeg& seg = reinterpret_cast<const JpegSeg*>(blob + segs_off)[w.seg];
+    const JpegImg& im = reinterpret_cast<const JpegImg*>(blob + imgs_off)[seg.img];
+    stage_tables(blob, im, sh, sel_dc, sel_ac);
+    const int sub = w.first_sub + threadIdx.x;
+    if (sub >= seg.nsub) return;
+    SegCtx cx;
+    seg_context(im, blob, seg, cx);
+    const SubInfo in = subs[seg.sub0 + sub];
+    int pe, se, nb;
+    parse_sub<true>(cx, sh, sel_dc, sel_ac, in.p_start, in.st_start, (sub + 1) * kSubBits, pe, se, nb, &im, &seg, ws, in.blk0);
+}
+
+// E: DC differences -> DC values, one CTA per (mode-1 segment, component), blocks in decode order
+__global__ void __launch_bounds__(1024)
+jpeg_dc_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t segs_off, int64_t pseg_off, uint8_t* __restrict__ ws) {
+    __shared__ int wsum[32];
+    __shared__ int carry_s;
+    const int si = reinterpret_cast<const int32_t*>(blob + pseg_off)[blockIdx.x];
+    const JpegSeg& seg = reinterpret_cast<const JpegSeg*>(blob + segs_off)[si];
+    const JpegImg& im = reinterpret_cast<const JpegImg*>(blob + imgs_off)[seg.img];
+    const int c = blockIdx.y;
+    if (c >= im.ncomp) return;
+    const int hs = im.hs[c], vs = im.vs[c], per = hs * vs, bw = im.bw[c];
+    const int n = seg.n_mcu * per;
+    int16_t* coef = reinterpret_cast<int16_t*>(ws + im.coef_off[c]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        int16_t* ptr = nullptr;
+        int v = 0;
+        if (i < n) {
+            const int mcu = seg.first_mcu + i / per, r = i % per;
+            const int my = mcu / im.mcux, mx = mcu - my * im.mcux;
+            ptr = coef + (static_cast<int64_t>(my * vs + r / hs) * bw + (mx * hs + r % hs)) * 64;
+            v = *ptr;
+        }
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = wsum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += u; }
+            wsum[lane] = w;
+        }
+        __syncthreads();
+        const int total = carry_s + (warp ? wsum[warp - 1] : 0) + inc;
+        if (ptr) *ptr = static_cast<int16_t>(total);
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = total;
+        __syncthreads();
     }
 }
 
@@ -612,7 +942,14 @@ extern "C" int pt_jpeg_decode_batch(const uint8_t* host_blob, const uint8_t* dev
     }
     uint8_t* ws = static_cast<uint8_t*>(workspace);
     if (cudaMemsetAsync(ws, 0, static_cast<size_t>(h.coef_bytes), st) != cudaSuccess) return check_launch("jpeg coefficient clear");
-    jpeg_huffman_kernel<<<h.total_segs, 32, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, ws);
+    if (h.n_pseg < h.total_segs) jpeg_huffman_kernel<<<h.total_segs, 32, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, ws);
+    if (h.n_pseg > 0) {
+        SubInfo* subs = reinterpret_cast<SubInfo*>(ws + h.sub_off);
+        jpeg_sync_kernel<<<h.n_cta, kSubThreads, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.cta_off, subs);
+        jpeg_stitch_kernel<<<h.n_pseg, 32, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.pseg_off, subs);
+        jpeg_write_kernel<<<h.n_cta, kSubThreads, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.cta_off, subs, ws);
+        jpeg_dc_kernel<<<dim3(h.n_pseg, 3), 1024, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.pseg_off, ws);
+    }
     const JpegImg* imgs = reinterpret_cast<const JpegImg*>(host_blob + h.imgs_off);
     for (int i = 0; i < h.n; ++i) {
         const JpegImg& im = imgs[i];

@@ -11,7 +11,8 @@ pytestmark = pytest.mark.gpu
 
 
 def _encode(arr, **kw):
-    from PIL import Image
+    from PIL import Image, ImageFile
+    ImageFile.MAXBLOCK = max(ImageFile.MAXBLOCK, 1 << 24)      # optimize=True needs the whole file in one buffer
     b = io.BytesIO()
     Image.fromarray(arr).save(b, "JPEG", **kw)
     return b.getvalue()
@@ -111,3 +112,30 @@ def test_jpeg_unsupported_files_are_rejected(cuda_dev):
         ops.jpeg_pack([b.getvalue()])
     with pytest.raises(RuntimeError, match="truncated|restart segments|bad segment"):
         ops.jpeg_pack([_encode(img, restart_marker_blocks=1)[:400]])
+
+
+@pytest.mark.parametrize("subsampling", [0, 1, 2, "gray"])
+@pytest.mark.parametrize("kw", [dict(), dict(restart_marker_rows=8), dict(optimize=True)])
+def test_jpeg_long_segments_decode_in_parallel_subsequences(cuda_dev, subsampling, kw):
+    """Entropy-coded segments of 8 KB and more take the self-synchronising parallel parse (sub-sequences of 1024 bits,
+    several CTAs per segment, boundary stitching, DC running sums): same bytes as Pillow, for detailed and for flat
+    images (long and short codes, few and many blocks per sub-sequence), mixed in one batch with short files."""
+    from projectiontrainer_b200 import ops
+    rng = np.random.default_rng(11)
+    files = []
+    for H, W in [(700, 900), (333, 1501)]:
+        smooth, noise, edges = _images(H, W, rng)
+        flat = np.full((H, W, 3), 77, dtype=np.uint8)
+        flat[H // 2, W // 2] = 255
+        for img, q in ((noise, 95), (smooth, 60), (edges, 85), (flat, 90), (noise // 4 + smooth // 2, 75)):
+            files.append(_encode(img[..., 0], quality=q, **kw) if subsampling == "gray"
+                         else _encode(img, quality=q, subsampling=subsampling, **kw))
+    files.append(_encode(_images(16, 24, rng)[1], quality=90))              # a short one beside them
+    packed = ops.jpeg_pack(files)
+    assert sum(len(f) >= 9000 for f in files) >= 6
+    out = ops.jpeg_decode(packed, cuda_dev)
+    torch.cuda.synchronize()
+    for i, (f, o) in enumerate(zip(files, out)):
+        ref = _pillow(f)
+        got = o.cpu().numpy()
+        assert np.array_equal(got, ref), (i, len(f), int((got != ref).sum()))
