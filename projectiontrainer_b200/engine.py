@@ -882,6 +882,25 @@ class Stage1Engine:
             ops.image_preprocess(src.contiguous(), out[i], ws, mean=mean, std=std, rescale=rescale)
         return out
 
+    def raw_images(self, batch: dict):
+        """The batch's undecoded-size uint8 images, or None: `images_u8` (list of [H, W, 3] tensors) with the slots
+        of files that travel encoded (`jpeg` = ops.jpeg_pack + `index`, image_io.collate_images) filled by the GPU
+        JPEG decode on the current stream."""
+        raw, pack = batch.get("images_u8"), batch.get("jpeg")
+        if pack is None:
+            return raw
+        if not hasattr(self, "_jpeg_ws"):
+            self._jpeg_ws = {}
+        sid = torch.cuda.current_stream().cuda_stream
+        ws = self._jpeg_ws.get(sid)
+        if ws is None or ws.numel() < pack["workspace_bytes"]:
+            ws = self._jpeg_ws[sid] = torch.empty(pack["workspace_bytes"], dtype=torch.uint8, device=self.device)
+        decoded = ops.jpeg_decode(pack, self.device, ws)
+        raw = list(raw) if raw is not None else [None] * len(decoded)
+        for i, im in zip(pack.get("index", range(len(decoded))), decoded):
+            raw[i] = im
+        return raw
+
     def stage_batch(self, batch: dict) -> dict:
         """Start the host->device copy of a (pinned) host batch on a side stream so that it overlaps the step
         that is running; returns a batch dict to hand to train_step later.  Two staging slots alternate (the
@@ -891,10 +910,11 @@ class Stage1Engine:
         sg = self._stage
         i = sg["n"] & 1
         sg["n"] += 1
-        raw = batch.get("images_u8")            # undecoded-size uint8 images instead of processor output
+        has_raw = "images_u8" in batch or "jpeg" in batch   # undecoded-size images instead of processor output
+        raw = None
         ti, lb = batch["token_ids"], batch["labels"]
-        if raw is not None:
-            pv = torch.empty(len(raw), 3, self.vcfg.image, self.vcfg.image, dtype=F32, device="meta")
+        if has_raw:
+            pv = torch.empty(ti.shape[0], 3, self.vcfg.image, self.vcfg.image, dtype=F32, device="meta")
         else:
             pv = batch["pixel_values"]
         slot = sg["slots"][i]
@@ -907,14 +927,15 @@ class Stage1Engine:
             sg["slots"][i] = slot
         with torch.cuda.stream(sg["stream"]):
             sg["stream"].wait_event(slot["done"])       # the step that consumed this slot has read it
-            if raw is not None:
+            if has_raw:
+                raw = self.raw_images(batch)             # JPEG decode of the encoded files, on the copy stream
                 self.preprocess_images(raw, slot["px"])  # upload + resize + normalize on the copy stream
             else:
                 slot["px"].copy_(pv, non_blocking=True)
             slot["ids"].copy_(ti, non_blocking=True)
             slot["lab"].copy_(lb, non_blocking=True)
             slot["event"].record()
-        return {"pixel_values": slot["px"] if raw is not None else pv, "token_ids": ti, "labels": lb,
+        return {"pixel_values": slot["px"] if has_raw else pv, "token_ids": ti, "labels": lb,
                 "_staged": slot, "label_span": batch.get("label_span")}
 
     def _graphed_forward_backward(self, batch: dict, pad_id) -> torch.Tensor:
@@ -971,7 +992,7 @@ class Stage1Engine:
         if "pixel_values" in batch:
             px = batch["pixel_values"].to(dev, dtype=F32, non_blocking=True)
         else:
-            px = self.preprocess_images(batch["images_u8"])
+            px = self.preprocess_images(self.raw_images(batch))
         ids = batch["token_ids"].to(dev, non_blocking=True)
         lab = batch["labels"].to(dev, non_blocking=True)
         B, T = ids.shape
@@ -1327,7 +1348,7 @@ class Stage1Engine:
         (no host sync here)."""
         dev = self.device
         if "pixel_values" not in batch:         # decoded images that were not staged: preprocess them now
-            batch = {**batch, "pixel_values": self.preprocess_images(batch["images_u8"])}
+            batch = {**batch, "pixel_values": self.preprocess_images(self.raw_images(batch))}
         self.select_geometry((tuple(batch["pixel_values"].shape), tuple(batch["token_ids"].shape)))
         if self.use_graph:
             loss = self._graphed_forward_backward(batch, pad_id)

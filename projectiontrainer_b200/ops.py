@@ -460,10 +460,7 @@ def image_preprocess(src_u8_hwc, dst_chw, workspace, *, mean=(0.5, 0.5, 0.5), st
 
 
 # ----------------------------------------------------------------------------- JPEG decode
-def jpeg_pack(files, pin: bool = True) -> dict:
-    """Host half of the GPU JPEG decode (runs without a GPU; meant for DataLoader workers): `files` = encoded baseline
-    JPEG files as bytes / bytearray / uint8 tensors.  Returns {"blob": uint8 host tensor (pinned when possible),
-    "sizes": [(H, W)], "rgb_offsets": [n + 1], "workspace_bytes"} for jpeg_decode."""
+def _jpeg_args(files):
     n = len(files)
     keep, addr, length = [], [], []
     for f in files:
@@ -474,8 +471,27 @@ def jpeg_pack(files, pin: bool = True) -> dict:
         else:
             b = bytes(f) if not isinstance(f, bytes) else f
             keep.append(b); addr.append(C.cast(C.c_char_p(b), C.c_void_p).value); length.append(len(b))
-    ptrs = (C.c_void_p * n)(*addr)
-    sizes = (C.c_int64 * n)(*length)
+    return keep, (C.c_void_p * n)(*addr), (C.c_int64 * n)(*length)
+
+
+def jpeg_plan(files) -> list:
+    """Host-side header parse only: [(H, W)] per file; raises RuntimeError naming the reason for a file the GPU
+    decoder does not take (not a JPEG, progressive, CMYK, unusual sub-sampling, ...)."""
+    n = len(files)
+    keep, ptrs, sizes = _jpeg_args(files)
+    w, h = (C.c_int32 * n)(), (C.c_int32 * n)()
+    offs = (C.c_int64 * (n + 1))()
+    blob_b, ws_b = C.c_int64(0), C.c_int64(0)
+    _lib.check(_lib.lib().pt_jpeg_plan(ptrs, sizes, n, w, h, offs, C.byref(blob_b), C.byref(ws_b)), "pt_jpeg_plan")
+    return [(int(h[i]), int(w[i])) for i in range(n)]
+
+
+def jpeg_pack(files, pin: bool = True) -> dict:
+    """Host half of the GPU JPEG decode (runs without a GPU; meant for DataLoader workers): `files` = encoded baseline
+    JPEG files as bytes / bytearray / uint8 tensors.  Returns {"blob": uint8 host tensor (pinned when possible),
+    "sizes": [(H, W)], "rgb_offsets": [n + 1], "workspace_bytes"} for jpeg_decode."""
+    n = len(files)
+    keep, ptrs, sizes = _jpeg_args(files)
     w, h = (C.c_int32 * n)(), (C.c_int32 * n)()
     offs = (C.c_int64 * (n + 1))()
     blob_b, ws_b = C.c_int64(0), C.c_int64(0)

@@ -139,12 +139,14 @@ class _ShardedLoader:
 
 def stage1_collate(items):
     """torch's default collate, except that decoded images of different sizes (`images_u8`, datasets built
-    with gpu_preprocess=True) stay a list."""
+    with gpu_preprocess=True) stay a list and encoded JPEG files (`jpeg_bytes`, gpu_decode=True) are packed for the
+    GPU decoder (image_io.collate_images)."""
     from torch.utils.data import default_collate
-    if "images_u8" not in items[0]:
+    from .image_io import collate_images, has_raw_images, strip_images
+    if not has_raw_images(items):
         return default_collate(items)
-    out = default_collate([{k: v for k, v in it.items() if k != "images_u8"} for it in items])
-    out["images_u8"] = [it["images_u8"] for it in items]
+    out = default_collate([strip_images(it) for it in items])
+    out.update(collate_images(items))
     return out
 
 
@@ -208,7 +210,7 @@ class ProjectionTrainerStage1:
         """One-batch look-ahead: the host->device copy of batch i+1 runs on a side stream while step i
         computes (the reference gets the same overlap from DataLoader workers + pinned memory)."""
         def on_host(b):
-            return "images_u8" in b or not b["pixel_values"].is_cuda
+            return "images_u8" in b or "jpeg" in b or not b["pixel_values"].is_cuda
         it = iter(loader)
         cur = next(it, None)
         if cur is not None and on_host(cur):
@@ -252,8 +254,8 @@ class ProjectionTrainerStage1:
                 val_loss, val_steps, total_samples, correct_last_word = 0.0, 0, 0, 0
                 can_decode = hasattr(self.tokenizer, "batch_decode")
                 for vb in self.val_loader:
-                    if "images_u8" in vb:
-                        vb["pixel_values"] = self.engine.preprocess_images(vb["images_u8"])
+                    if "images_u8" in vb or "jpeg" in vb:
+                        vb["pixel_values"] = self.engine.preprocess_images(self.engine.raw_images(vb))
                     val_loss += self.engine.eval_loss(vb, pad_id=self.pad_id).item()
                     val_steps += 1
                     if not can_decode:

@@ -32,10 +32,12 @@ class XrayTextPairDataset(Dataset):
     token_ids i64 [max_length] (tokenizer padded to max_length), labels = token_ids with pad -> -100."""
 
     def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_length=512, image_root_2=None,
-                 gpu_preprocess=False, cache_tokens=False):
+                 gpu_preprocess=False, cache_tokens=False, gpu_decode=False):
         # gpu_preprocess (an addition): items carry the decoded image as `images_u8` uint8 [H, W, 3]; resize +
         # rescale + normalize run on the GPU in the trainer's look-ahead stage (Pillow-exact kernels)
-        self.gpu_preprocess = gpu_preprocess
+        # gpu_decode (an addition, implies gpu_preprocess): workers only read the file; baseline JPEGs are decoded on
+        # the GPU too (image_io.py)
+        self.gpu_preprocess, self.gpu_decode = gpu_preprocess or gpu_decode, gpu_decode
         self.image_root, self.image_root_2, self.img_size = image_root, image_root_2, img_size
         self.processor, self.tokenizer, self.max_length = processor, tokenizer, max_length
         self.samples = []
@@ -84,11 +86,14 @@ class XrayTextPairDataset(Dataset):
     def __getitem__(self, idx):
         from PIL import Image
         sample = self.samples[idx]
-        image = Image.open(self._resolve(sample["image"])).convert("RGB")
+        image = None if self.gpu_decode else Image.open(self._resolve(sample["image"])).convert("RGB")
         token_ids = self._tokens(idx)
         labels = token_ids.clone()
         if self.tokenizer.pad_token_id is not None:
             labels[labels == self.tokenizer.pad_token_id] = -100
+        if self.gpu_decode:
+            from .image_io import load_image_item
+            return {**load_image_item(self._resolve(sample["image"]), True), "token_ids": token_ids, "labels": labels}
         if self.gpu_preprocess:
             import numpy as np
             return {"images_u8": torch.from_numpy(np.array(image, dtype=np.uint8)), "token_ids": token_ids,
@@ -145,6 +150,9 @@ def build_parser():
     p.add_argument("--img_size", type=int, default=384)
     p.add_argument("--save_every_n_epochs", type=int, default=2)
     p.add_argument("--enable_qlora", action="store_true")
+    p.add_argument("--gpu_decode", action="store_true",
+                   help="workers only read the image files; baseline JPEGs are decoded on the GPU (bit-exact with Pillow), "
+                        "then resized / normalized there (implies --gpu_preprocess)")
     p.add_argument("--gpu_preprocess", action="store_true",
                    help="resize / rescale / normalize the decoded images on the GPU (Pillow-exact) instead of in the workers")
     p.add_argument("--cache_tokens", action="store_true", help="tokenise every caption once instead of once per epoch")
@@ -202,21 +210,21 @@ def main(argv=None):
             _nf4(Wt, Wl, lc, accelerator.device)
             language_model = PackedGemma(Wl, lc, accelerator.device)
         full = XrayTextPairDataset(args.image_root, args.train_json, processor, tokenizer, args.img_size,
-                                   max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                   max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess, gpu_decode=args.gpu_decode,
                                    cache_tokens=args.cache_tokens)
         train_dataset, val_dataset = full, None
         if args.val_json:
             val_dataset = XrayTextPairDataset(args.image_root, args.val_json, processor, tokenizer, args.img_size,
-                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess, gpu_decode=args.gpu_decode,
                                    cache_tokens=args.cache_tokens)
         elif args.train_val_split > 0:
             from sklearn.model_selection import train_test_split
             tr, va = train_test_split(full.samples, test_size=args.train_val_split, random_state=42)
             train_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
-                                                max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                                max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess, gpu_decode=args.gpu_decode,
                                    cache_tokens=args.cache_tokens)
             val_dataset = XrayTextPairDataset(args.image_root, None, processor, tokenizer, args.img_size,
-                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                                              max_length=args.max_length, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess, gpu_decode=args.gpu_decode,
                                    cache_tokens=args.cache_tokens)
             train_dataset.samples, val_dataset.samples = tr, va
         if len(train_dataset) == 0:

@@ -107,6 +107,9 @@ def build_parser():
     p.add_argument("--wandb_project", type=str, default="xray_vqa_training_stage2")
     p.add_argument("--wandb_run_name", type=str, default=None)
     p.add_argument("--disable_wandb", action="store_true")
+    p.add_argument("--gpu_decode", action="store_true",
+                   help="workers only read the image files; baseline JPEGs are decoded on the GPU (bit-exact with Pillow), "
+                        "then resized / normalized there (implies --gpu_preprocess)")
     p.add_argument("--gpu_preprocess", action="store_true",
                    help="resize / rescale / normalize the decoded images on the GPU (Pillow-exact) instead of in the workers")
     p.add_argument("--synthetic", type=int, default=0, help="train on N synthetic triplets with random-init models")
@@ -157,7 +160,8 @@ def main(argv=None):
             tokenizer.pad_token = tokenizer.eos_token
         projection_layer = load_pretrained_projector(args.stage1_projector_path)
         kw = dict(processor=processor, tokenizer=tokenizer, img_size=args.img_size, max_q_len=args.max_q_len,
-                  max_a_len=args.max_a_len, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess)
+                  max_a_len=args.max_a_len, image_root_2=args.image_root_2, gpu_preprocess=args.gpu_preprocess,
+                  gpu_decode=args.gpu_decode)
         train_dataset = XrayVQADataset(args.image_root, args.train_json, **kw)
         val_dataset = XrayVQADataset(args.image_root, args.val_json, **kw)
     trainer = VQATrainerStage2(

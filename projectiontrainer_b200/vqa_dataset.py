@@ -17,11 +17,13 @@ logger = logging.getLogger(__name__)
 
 class XrayVQADataset(Dataset):
     def __init__(self, image_root, json_file, processor, tokenizer, img_size, max_q_len=128, max_a_len=512,
-                 image_root_2=None, gpu_preprocess=False):
+                 image_root_2=None, gpu_preprocess=False, gpu_decode=False):
         """`gpu_preprocess=True` (an addition): items carry the decoded image as `images_u8` uint8 [H, W, 3]
         instead of `pixel_values`; resize + rescale + normalize then run on the GPU inside the trainer's
         look-ahead stage (`Stage1Engine.preprocess_images`, Pillow-exact)."""
-        self.gpu_preprocess = gpu_preprocess
+        # gpu_decode (an addition, implies gpu_preprocess): workers only read the file; baseline JPEGs are decoded on
+        # the GPU too (image_io.py)
+        self.gpu_preprocess, self.gpu_decode = gpu_preprocess or gpu_decode, gpu_decode
         self.image_root, self.image_root_2, self.img_size = image_root, image_root_2, img_size
         self.processor, self.tokenizer = processor, tokenizer
         self.max_q_len, self.max_a_len = max_q_len, max_a_len
@@ -54,12 +56,15 @@ class XrayVQADataset(Dataset):
         name, question, answer = s.get("image"), s.get("problem"), s.get("normal_caption")
         if not all([name, question, answer]):
             raise KeyError(f"sample {idx} is missing image, problem or normal_caption")
-        image = Image.open(self._image_path(name)).convert("RGB")
+        image = None if self.gpu_decode else Image.open(self._image_path(name)).convert("RGB")
         q = self.tokenizer(question, max_length=self.max_q_len, truncation=True, add_special_tokens=False).input_ids
         a = self.tokenizer(answer, max_length=self.max_a_len, truncation=True).input_ids
         item = {"question_input_ids": torch.tensor(q, dtype=torch.long),
                 "answer_input_ids": torch.tensor(a, dtype=torch.long)}
-        if self.gpu_preprocess:
+        if self.gpu_decode:
+            from .image_io import load_image_item
+            item.update(load_image_item(self._image_path(name), True))
+        elif self.gpu_preprocess:
             import numpy as np
             item["images_u8"] = torch.from_numpy(np.array(image, dtype=np.uint8))
         else:

@@ -50,8 +50,10 @@ def vqa_collate_fn(batch, tokenizer):
 
     out = {"question_input_ids": pad_to_longest([it["question_input_ids"] for it in batch]),
            "answer_input_ids": pad_to_longest([it["answer_input_ids"] for it in batch])}
-    if "images_u8" in batch[0]:      # GPU preprocessing (vqa_dataset gpu_preprocess=True): decoded images, any size
-        out["images_u8"] = [it["images_u8"] for it in batch]
+    if "images_u8" in batch[0] or "jpeg_bytes" in batch[0]:
+        # GPU preprocessing (vqa_dataset gpu_preprocess / gpu_decode): decoded images of any size, encoded JPEG files
+        from .image_io import collate_images
+        out.update(collate_images(batch))
     else:
         out["pixel_values"] = torch.stack([it["pixel_values"] for it in batch])
     return out
@@ -83,7 +85,7 @@ def vqa_step_inputs(batch: dict, pad_id: int, bucket: int = 1) -> dict:
     # exact (Lq, La) pairs would re-capture a graph and add a logits buffer for almost every micro-batch
     off = (Lq // bucket) * bucket
     out = {"token_ids": ids, "labels": labels, "label_span": (off, Tb - off)}
-    out.update({k: batch[k] for k in ("pixel_values", "images_u8") if k in batch})
+    out.update({k: batch[k] for k in ("pixel_values", "images_u8", "jpeg") if k in batch})
     return out
 
 
@@ -275,7 +277,8 @@ class VQATrainerStage2:
                 if not can_decode:
                     continue
                 try:
-                    px = vb["pixel_values"] if "pixel_values" in vb else self.engine.preprocess_images(vb["images_u8"])
+                    px = vb["pixel_values"] if "pixel_values" in vb else \
+                        self.engine.preprocess_images(self.engine.raw_images(vb))
                     gen = self.engine.generate(px, vb["question_input_ids"],
                                                max_new_tokens=max_new_tokens, do_sample=True, top_p=0.9, top_k=50,
                                                pad_token_id=self.pad_id, eos_token_id=tok.eos_token_id,

@@ -139,3 +139,69 @@ def test_jpeg_long_segments_decode_in_parallel_subsequences(cuda_dev, subsamplin
         ref = _pillow(f)
         got = o.cpu().numpy()
         assert np.array_equal(got, ref), (i, len(f), int((got != ref).sum()))
+
+
+def test_gpu_decode_loader_feeds_the_step(cuda_dev, tmp_path):
+    """`gpu_decode=True` end to end: files on disk -> dataset (workers read bytes) -> collate (pack in the worker) ->
+    pinned DataLoader -> `stage_batch` (JPEG decode + resize + normalize on the copy stream) -> the step.  The
+    `pixel_values` the step sees equal the reference pipeline's (Pillow decode, Pillow resize, processor arithmetic)
+    bit for bit, a PNG and a progressive file in the same batch included, and the losses equal those of a batch that
+    carries those `pixel_values`."""
+    import json
+    from PIL import Image
+    from oracle import image_oracle as IO
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.projector_trainer import stage1_collate
+    from projectiontrainer_b200.train_projection_stage1 import XrayTextPairDataset
+    vkw = dict(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=6, hq=2, hkv=1, hd=256, window=8, q_scalar=256.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    rng = np.random.default_rng(5)
+    specs = [((300, 200), "JPEG", dict(quality=90, subsampling=2)), ((64, 64), "PNG", {}),
+             ((129, 500), "JPEG", dict(quality=75, subsampling=0, restart_marker_rows=2)),
+             ((700, 640), "JPEG", dict(quality=95)), ((90, 70), "JPEG", dict(progressive=True)),
+             ((211, 97), "JPEG", dict(quality=85, subsampling=1))]
+    names = []
+    for i, ((h, w), fmt, kw) in enumerate(specs):
+        arr = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        if i == 3:
+            arr = arr[..., 0]                                   # a grayscale file, long enough for the parallel parse
+        name = f"x{i}.{'png' if fmt == 'PNG' else 'jpg'}"
+        Image.fromarray(arr).save(tmp_path / name, fmt, **kw)
+        names.append(name)
+    (tmp_path / "d.json").write_text(json.dumps([{"image": n, "normal_caption": "c"} for n in names]))
+    ref = np.stack([IO.rescale_normalize(np.asarray(Image.open(tmp_path / n).convert("RGB").resize((64, 64)))) for n in names])
+    _, ids, lab = O.synthetic_batch(len(names), 10, ovc, olc, left_pad=True)
+
+    class Tok:
+        pad_token_id = olc.pad_id
+        def __call__(self, text, max_length, padding, truncation, return_tensors):
+            Tok.i = getattr(Tok, "i", -1) + 1
+            return type("Enc", (), {"input_ids": ids[Tok.i % len(names)][None]})()
+
+    ds = XrayTextPairDataset(str(tmp_path), str(tmp_path / "d.json"), None, Tok(), 64, max_length=10, gpu_decode=True)
+    loader = torch.utils.data.DataLoader(ds, batch_size=len(names), shuffle=False, num_workers=2, pin_memory=True,
+                                         collate_fn=stage1_collate)
+    batch = next(iter(loader))
+    assert batch["jpeg"]["index"] == [0, 2, 3, 5] and batch["jpeg"]["blob"].is_pinned()
+    batch["token_ids"], batch["labels"] = ids, lab              # (worker-side tokenizer call order is not the point)
+
+    def run(b):
+        eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
+                             E.ProjectorState(P, cuda_dev), cuda_dev)
+        staged = eng.stage_batch(b)
+        if "_staged" in staged:
+            torch.cuda.current_stream().wait_event(staged["_staged"]["event"])      # the copy stream's work
+        px = staged["pixel_values"].clone()
+        losses = [eng.train_step(staged, 1e-3, pad_id=olc.pad_id).item()]
+        losses += [eng.train_step(eng.stage_batch(b), 1e-3, pad_id=olc.pad_id).item() for _ in range(2)]
+        return px, losses
+
+    px, l_jpeg = run(batch)
+    torch.cuda.synchronize()
+    assert np.array_equal(px.cpu().numpy(), ref)
+    _, l_px = run({"pixel_values": torch.from_numpy(ref), "token_ids": ids, "labels": lab})
+    assert np.allclose(l_jpeg, l_px, rtol=1e-6)
