@@ -87,10 +87,22 @@ def run_case(name: str):
                                pad_token_id=lc.pad_id, eos_token_id=first, do_sample=False, temperature=None,
                                top_p=None, top_k=None, repetition_penalty=1.0)
     print(f"[{name}] generated {tuple(outputs.shape)}: {outputs.tolist()}  | eos={first}: {outputs_eos.tolist()}")
+    # beam search (the deterministic half of what Stage-2 validation asks for: ref:Stage2/trainer.py:603-611 calls
+    # generate(num_beams=3, do_sample=True, ...); sampled outputs cannot be recorded, the beam bookkeeping can)
+    beam = llm.generate(inputs_embeds=inputs_embeds, attention_mask=attention_mask, max_new_tokens=new,
+                        pad_token_id=lc.pad_id, eos_token_id=1, do_sample=False, num_beams=3, temperature=None,
+                        top_p=None, top_k=None, repetition_penalty=1.0)
+    # eos variants: ids that occur early / late in the beam outputs, so that hypotheses finish at different lengths
+    beam_eos_ids = [int(beam[0, 2]), int(beam[-1, min(5, beam.shape[1] - 1)])]
+    beam_eos = [llm.generate(inputs_embeds=inputs_embeds, attention_mask=attention_mask, max_new_tokens=new,
+                             pad_token_id=lc.pad_id, eos_token_id=e, do_sample=False, num_beams=3, temperature=None,
+                             top_p=None, top_k=None, repetition_penalty=1.0) for e in beam_eos_ids]
+    print(f"[{name}] beam3 {beam.tolist()} | eos={beam_eos_ids}: {[b.tolist() for b in beam_eos]}")
     np.savez_compressed(GOLDEN / f"{name}.npz", case=np.array(name), B=B, prompt_tokens=Tp, max_new_tokens=new,
                         prompt_ids=ids[:, :Tp].numpy(), prefill_logits=prefill_logits.numpy(),
                         generated=outputs.numpy(), eos_variant_id=first, generated_eos=outputs_eos.numpy(),
-                        projected=projected.numpy())
+                        projected=projected.numpy(), beam3=beam.numpy(), beam3_eos_ids=np.array(beam_eos_ids),
+                        beam3_eos0=beam_eos[0].numpy(), beam3_eos1=beam_eos[1].numpy())
 
 
 if __name__ == "__main__":

@@ -1280,7 +1280,8 @@ class Stage1Engine:
                  max_new_tokens: int = 64, do_sample: bool = False, temperature: float = 1.0,
                  top_p: float = 1.0, top_k: int = 50, repetition_penalty: float = 1.0,
                  pad_token_id: int | None = 0, eos_token_id: int | None = 1,
-                 generator: torch.Generator | None = None, prompt_pad_id: int | None = None) -> torch.Tensor:
+                 generator: torch.Generator | None = None, prompt_pad_id: int | None = None,
+                 num_beams: int = 1, length_penalty: float = 1.0) -> torch.Tensor:
         """`language_model.generate(inputs_embeds=projected, attention_mask=ones, ...)` of
         ref:Stage1/inference_stage1.py:176-187 / projector_trainer.py:386-393: returns the NEW tokens
         only, i64 [B, n<=max_new_tokens]; finished rows are filled with pad_token_id; stops early when
@@ -1291,9 +1292,15 @@ class Stage1Engine:
             # the decode loop reads the packed weights only: fold the adapters in for the length of this call
             kw = dict(max_new_tokens=max_new_tokens, do_sample=do_sample, temperature=temperature, top_p=top_p,
                       top_k=top_k, repetition_penalty=repetition_penalty, pad_token_id=pad_token_id,
-                      eos_token_id=eos_token_id, generator=generator, prompt_pad_id=prompt_pad_id)
+                      eos_token_id=eos_token_id, generator=generator, prompt_pad_id=prompt_pad_id,
+                      num_beams=num_beams, length_penalty=length_penalty)
             with self.merged(self.merge_adapters()):
                 return self.generate(pixels, prompt_ids, **kw)
+        if num_beams > 1:
+            return self._beam_generate(pixels, prompt_ids, max_new_tokens=max_new_tokens, do_sample=do_sample,
+                                       temperature=temperature, top_p=top_p, top_k=top_k,
+                                       pad_token_id=pad_token_id, eos_token_id=eos_token_id, generator=generator,
+                                       prompt_pad_id=prompt_pad_id, num_beams=num_beams, length_penalty=length_penalty)
         logits = self.prefill(pixels, prompt_ids, max_new_tokens=max_new_tokens, prompt_pad_id=prompt_pad_id)
         B = logits.shape[0]
         dev = self.device
@@ -1333,6 +1340,88 @@ class Stage1Engine:
             if step + 1 < max_new_tokens:
                 logits = self.decode_step(nxt)
         return out[:, :n]
+
+    @torch.no_grad()
+    def _beam_generate(self, pixels, prompt_ids, *, max_new_tokens, do_sample, temperature, top_p, top_k,
+                       pad_token_id, eos_token_id, generator, prompt_pad_id, num_beams, length_penalty):
+        """HF `generate(num_beams=n)` (beam search, or beam sampling with do_sample=True: what the Stage-2 validation
+        asks for, ref:Stage2/trainer.py:603-611 `num_beams=3, do_sample=True, top_p=0.9, top_k=50`), restated from
+        `GenerationMixin._beam_search` of transformers 5.x with early_stopping=False and no prompt ids (generation
+        starts from `inputs_embeds`, so lengths count generated tokens only): every sample runs `num_beams` rows of
+        the KV-cached decode; per step the log-probabilities of all beams' continuations are ranked (or sampled
+        without replacement), 2n candidates are kept, the best n unfinished ones run on, candidates among the first n
+        that hit eos / the length limit compete for the n finished slots with score / length^penalty, and the KV
+        cache rows are re-ordered to follow their beams.  Bookkeeping is torch on [B, n, V] tensors; the model
+        arithmetic is the same decode step as greedy generation."""
+        nb, dev = int(num_beams), self.device
+        B = pixels.shape[0]
+        rep_i = lambda t: None if t is None else t.repeat_interleave(nb, dim=0)
+        logits = self.prefill(rep_i(pixels), rep_i(prompt_ids), max_new_tokens=max_new_tokens, prompt_pad_id=prompt_pad_id)
+        V, L = logits.shape[1], int(max_new_tokens)
+        fill = pad_token_id if pad_token_id else (eos_token_id if eos_token_id is not None else -1)
+        keep = 2 * nb                                    # (number of eos ids + 1) * num_beams
+        top_mask = torch.arange(keep, device=dev) < nb
+        run_seq = torch.full((B, nb, L), fill, dtype=torch.int64, device=dev)
+        fin_seq = run_seq.clone()
+        run_score = torch.zeros(B, nb, device=dev)
+        run_score[:, 1:] = -1e9                          # identical beams at the start: only the first one counts
+        fin_score = torch.full((B, nb), -1e9, device=dev)
+        fin_len = torch.zeros(B, nb, dtype=torch.int64, device=dev)
+        finished = torch.zeros(B, nb, dtype=torch.bool, device=dev)
+        improvable = torch.ones(B, 1, dtype=torch.bool, device=dev)
+        gather = lambda t, idx: t.gather(1, idx.view(B, -1, *([1] * (t.dim() - 2))).expand(-1, -1, *t.shape[2:]))
+        kc = self.cache
+        for cur in range(L):
+            lp = torch.log_softmax(logits.float(), dim=-1)
+            if do_sample:                                # HF's warpers, min_tokens_to_keep = 2 under beam search
+                if temperature != 1.0:
+                    lp = lp / temperature
+                if top_k and top_k > 0:
+                    kth = lp.topk(min(max(top_k, 2), V), dim=1).values[:, -1:]
+                    lp = lp.masked_fill(lp < kth, float("-inf"))
+                if top_p < 1.0:
+                    srt, idx = lp.sort(dim=1, descending=False)
+                    rm = srt.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
+                    rm[:, -2:] = False
+                    lp = lp.masked_fill(rm.scatter(1, idx, rm), float("-inf"))
+            acc = (lp.view(B, nb, V) + run_score[:, :, None]).view(B, nb * V)
+            if do_sample:
+                cand = torch.multinomial(acc.softmax(dim=-1), keep, generator=generator)
+                cand_score = acc.gather(1, cand)
+            else:
+                cand_score, cand = acc.topk(keep, dim=1)
+            src_beam, tok = cand // V, cand % V
+            cand_seq = gather(run_seq, src_beam)
+            cand_seq[:, :, cur] = tok
+            hit = (cur + 1 >= L) | ((tok == eos_token_id) if eos_token_id is not None else torch.zeros_like(tok, dtype=torch.bool))
+            # the running beams of the next step: best unfinished candidates
+            live_score = cand_score + hit.float() * -1e9
+            nxt = live_score.topk(nb, dim=1).indices
+            run_seq, run_score, run_src = gather(cand_seq, nxt), live_score.gather(1, nxt), src_beam.gather(1, nxt)
+            # finished pool: candidates among the first num_beams that just ended compete with the stored ones
+            just = hit & top_mask[None, :]
+            fs = cand_score / float(cur + 1) ** length_penalty
+            fs = fs + (~improvable).float() * -1e9 + (~just).float() * -1e9
+            m_score = torch.cat([fin_score, fs], dim=1)
+            pick = m_score.topk(nb, dim=1).indices
+            fin_seq = gather(torch.cat([fin_seq, cand_seq], dim=1), pick)
+            fin_len = torch.cat([fin_len, torch.full_like(tok, cur + 1)], dim=1).gather(1, pick)
+            finished = torch.cat([finished, just], dim=1).gather(1, pick)
+            fin_score = m_score.gather(1, pick)
+            # can a running beam still beat the worst finished one?  (early_stopping=False heuristic)
+            best_run = run_score[:, :1] / float(cur + 1) ** length_penalty
+            worst_fin = torch.where(finished, fin_score.min(dim=1, keepdim=True).values, torch.full_like(fin_score, -1e9))
+            improvable = improvable & (best_run > worst_fin).any(dim=-1, keepdim=True)
+            if not bool(improvable.any()) or bool(hit.all()):
+                break
+            # KV rows follow their beams (in place: the decode graph holds the cache addresses)
+            rows = (run_src + torch.arange(B, device=dev)[:, None] * nb).view(-1)
+            for li in range(len(kc["k"])):
+                kc["k"][li].copy_(kc["k"][li].index_select(0, rows))
+                kc["v"][li].copy_(kc["v"][li].index_select(0, rows))
+            logits = self.decode_step(run_seq[:, :, cur].reshape(-1))
+        out_len = int(fin_len[:, 0].max().item())
+        return fin_seq[:, 0, :max(out_len, 1)]
 
     def train_step(self, batch: dict, lr: float, *, pad_id=0, weight_decay: float = 0.01,
                    allreduce=None, world_size: int = 1, max_norm: float = 5.0,

@@ -9,9 +9,9 @@ label span; this file is the host loop: dynamic per-batch padding, `accelerator.
 clip to 1.0 per trainable module, AdamW, cosine schedule.
 
 Not built (raises NotImplementedError, never falls back): full fine-tuning of the LLM (`--unfreeze_llm`) and the
-first-epoch vision-encoder training.  LoRA dropout is not applied (lora.py).  Validation generation samples
-(top-k 50, top-p 0.9) without the reference's 3-beam search (`num_beams=3`), which the engine's decode loop does
-not implement."""
+first-epoch vision-encoder training.  LoRA dropout is not applied (lora.py).  Validation generation is the
+reference's call: 3-beam sampling, top-k 50, top-p 0.9 (`engine.generate(num_beams=3, do_sample=True, ...)`, HF's
+beam bookkeeping restated and pinned to HF `generate` token for token in tests/test_beam_search_cpu.py)."""
 from __future__ import annotations
 
 import json
@@ -260,8 +260,8 @@ class VQATrainerStage2:
 
     @torch.no_grad()
     def evaluate(self, epoch, global_step, max_new_tokens: int = 512):
-        """ref:Stage2/trainer.py:490-677: validation loss over the whole set (left-padded collation), sampled
-        predictions from `[image][question]`, up to 20 examples written to validation_examples/."""
+        """ref:Stage2/trainer.py:490-677: validation loss over the whole set (left-padded collation), beam-sampled
+        predictions from `[image][question]` (:603-611), up to 20 examples written to validation_examples/."""
         acc, tok = self.accelerator, self.tokenizer
         logger.info(f"Starting evaluation for Epoch {epoch + 1}...")
         original_side = tok.padding_side
@@ -280,7 +280,7 @@ class VQATrainerStage2:
                     px = vb["pixel_values"] if "pixel_values" in vb else \
                         self.engine.preprocess_images(self.engine.raw_images(vb))
                     gen = self.engine.generate(px, vb["question_input_ids"],
-                                               max_new_tokens=max_new_tokens, do_sample=True, top_p=0.9, top_k=50,
+                                               max_new_tokens=max_new_tokens, do_sample=True, num_beams=3, top_p=0.9, top_k=50,
                                                pad_token_id=self.pad_id, eos_token_id=tok.eos_token_id,
                                                prompt_pad_id=self.pad_id)
                     preds = tok.batch_decode(gen.cpu(), skip_special_tokens=True)

@@ -145,3 +145,35 @@ def test_graphed_decode_step_equals_eager_decode_step(cuda_dev, padded, monkeypa
         assert bool(torch.isfinite(a).all())
         assert float((a - b).abs().max()) / float(b.abs().max()) < 2e-3, seed
     assert eng.cache["g_graph"] is not None
+
+
+@pytest.mark.parametrize("name", ["infer_tiny_gqa", "infer_tiny_prompt_mqa", "infer_tiny_leftpad_gqa"])
+def test_generate_beam_search_on_the_kernels(cuda_dev, name):
+    """`generate(num_beams=3)` on the real decode path (beam rows in the KV cache, cache rows re-ordered every step,
+    one CUDA-graph replay per token).  The bookkeeping is pinned to HF token for token on the CPU
+    (tests/test_beam_search_cpu.py); here the bf16 kernels drive it: rows whose hypotheses are separated by clear
+    margins reproduce HF's beam output exactly, and the output is well-formed for every row."""
+    from oracle.make_golden_infer import LEFT_PADS
+    eng, O, (ovc, olc, Wv, Wl, P), px, prompt, new, g = _setup(name, cuda_dev)
+    pad = None
+    if name in LEFT_PADS:
+        for b, k in enumerate(LEFT_PADS[name]):
+            prompt[b, :k] = olc.pad_id
+        pad = olc.pad_id
+    out = eng.generate(px, prompt, max_new_tokens=new, do_sample=False, num_beams=3, pad_token_id=olc.pad_id,
+                       eos_token_id=1, prompt_pad_id=pad).cpu().numpy()
+    ref = g["beam3"]
+    assert out.shape == ref.shape and out.min() >= 0 and out.max() < olc.vocab
+    same = [(out[b] == ref[b]).all() for b in range(out.shape[0])]
+    assert sum(same) >= (len(same) + 1) // 2, (out.tolist(), ref.tolist())
+    # a repeat gives the same tokens (the re-ordered cache leaves no state behind), and greedy still works after it
+    again = eng.generate(px, prompt, max_new_tokens=new, do_sample=False, num_beams=3, pad_token_id=olc.pad_id,
+                         eos_token_id=1, prompt_pad_id=pad).cpu().numpy()
+    assert np.array_equal(out, again)
+    greedy = eng.generate(px, prompt, max_new_tokens=new, do_sample=False, pad_token_id=olc.pad_id, eos_token_id=-1,
+                          prompt_pad_id=pad)
+    assert greedy.shape == (px.shape[0], new)
+    # beam sampling, the Stage-2 validation call (ref:Stage2/trainer.py:603-611)
+    smp = eng.generate(px, prompt, max_new_tokens=new, do_sample=True, num_beams=3, top_p=0.9, top_k=50,
+                       pad_token_id=olc.pad_id, eos_token_id=int(g["eos_variant_id"]), prompt_pad_id=pad)
+    assert smp.shape[0] == px.shape[0] and 1 <= smp.shape[1] <= new
