@@ -523,8 +523,9 @@ jpeg_huffman_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t 
 //   A  every thread parses its sub-sequence from a guessed state; then, repeatedly, re-parses it from the state in
 //      which its left neighbour ENDED, until no end state in the CTA changes (state = bit position, block slot in the
 //      MCU, zig-zag index: everything the further parse depends on; DC prediction is handled separately);
-//   B  one thread per segment walks the CTA boundaries left to right and re-parses from the true state until the
-//      stored end state is met again;
+//   B  the true state is carried across the CTA boundaries: all boundaries in parallel first (a CTA's last end state
+//      is almost always already true), then one thread per segment walks them left to right, re-parsing from the
+//      true state until the stored end state is met again wherever the chain does not hold yet;
 //   C  exclusive scan of the blocks completed per sub-sequence -> first block index of each;
 //   D  every thread parses its sub-sequence once more from its now-true start state and stores the coefficients (DC
 //      as differences);
@@ -691,7 +692,39 @@ jpeg_sync_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t seg
     }
 }
 
-// B: carry the true state across the CTA boundaries of a segment, then C: exclusive scan of the block counts
+// B1: all CTA boundaries at once.  The end state of a CTA's last sub-sequence is almost always already the true one
+// (the parse falls into step within a few sub-sequences of the CTA's guessed start), so every boundary can be
+// carried over independently: one warp per boundary, lane 0 re-parses from the left neighbour's end state until the
+// stored end state is met again (at most to the end of its own CTA).  Kernel B2 below then only has to confirm the
+// chain — and repairs the rare boundary whose left neighbour did change.
+__global__ void __launch_bounds__(32)
+jpeg_stitch_par_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t segs_off, int64_t cta_off, SubInfo* __restrict__ subs) {
+    __shared__ HuffDev sh[4];
+    __shared__ int sel_dc[3], sel_ac[3];
+    const JpegCta w = reinterpret_cast<const JpegCta*>(blob + cta_off)[blockIdx.x];
+    if (w.first_sub == 0) return;
+    const JpegSeg& seg = reinterpret_cast<const JpegSeg*>(blob + segs_off)[w.seg];
+    const JpegImg& im = reinterpret_cast<const JpegImg*>(blob + imgs_off)[seg.img];
+    stage_tables(blob, im, sh, sel_dc, sel_ac);
+    if (threadIdx.x != 0) return;
+    SubInfo* S = subs + seg.sub0;
+    SegCtx cx;
+    seg_context(im, blob, seg, cx);
+    int pp = S[w.first_sub - 1].p_end, ps = S[w.first_sub - 1].st_end;
+    const int stop = min(seg.nsub, w.first_sub + kSubThreads);
+    for (int cur = w.first_sub; cur < stop; ++cur) {
+        if (S[cur].p_start == pp && S[cur].st_start == ps) break;
+        int pe, se, nb;
+        parse_sub<false>(cx, sh, sel_dc, sel_ac, pp, ps, (cur + 1) * kSubBits, pe, se, nb, nullptr, nullptr, nullptr, 0);
+        const bool same_end = pe == S[cur].p_end && se == S[cur].st_end;
+        S[cur].p_start = pp; S[cur].st_start = ps; S[cur].p_end = pe; S[cur].st_end = se; S[cur].nblk = nb;
+        if (same_end) break;
+        pp = pe; ps = se;
+    }
+}
+
+// B2: confirm / carry the true state across the CTA boundaries of a segment left to right, then C: exclusive scan of
+// the block counts
 __global__ void __launch_bounds__(32)
 jpeg_stitch_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t segs_off, int64_t pseg_off, SubInfo* __restrict__ subs) {
     __shared__ HuffDev sh[4];
@@ -946,6 +979,8 @@ extern "C" int pt_jpeg_decode_batch(const uint8_t* host_blob, const uint8_t* dev
     if (h.n_pseg > 0) {
         SubInfo* subs = reinterpret_cast<SubInfo*>(ws + h.sub_off);
         jpeg_sync_kernel<<<h.n_cta, kSubThreads, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.cta_off, subs);
+        if (h.n_cta > h.n_pseg)
+            jpeg_stitch_par_kernel<<<h.n_cta, 32, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.cta_off, subs);
         jpeg_stitch_kernel<<<h.n_pseg, 32, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.pseg_off, subs);
         jpeg_write_kernel<<<h.n_cta, kSubThreads, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.cta_off, subs, ws);
         jpeg_dc_kernel<<<dim3(h.n_pseg, 3), 1024, 0, st>>>(dev_blob, h.imgs_off, h.segs_off, h.pseg_off, ws);
