@@ -347,6 +347,7 @@ def run_ours(args):
         c3 = config3_4b_step(dev, rank, world, allreduce, sync, peak_sus)       # every rank takes part
         if rank == 0:
             configs["configs[3]"] = c3
+            configs["next_rows"] = next_rows_block(vc, lc, dev)
             try:
                 sm = ClockSampler(local)
                 t0 = time.time()
@@ -445,6 +446,86 @@ def parity_block(eng, dev_batch, vc, lc, dev):
                 "ok": abs(loss - ref_loss) / abs(ref_loss) < 1e-2 and min(cos.values()) >= 0.999}
     except Exception as e:
         return {"unavailable": f"{type(e).__name__}: {e}"}
+
+
+def next_rows_block(vc, lc, dev):
+    """SURVEY.md §8(f) rows on the driver-run line (rank 0, after the main engine is gone): the Stage-2 micro-batch
+    with LoRA adapters (rank 2: r=16 on the seven decoder projections, ref:Stage2/train_vqa_stage2.py:229-236) next to
+    the same micro-batch with the LLM frozen, and the GPU JPEG decode + resize + normalize of one batch of
+    chest-X-ray-sized files (rank 3) next to Pillow on one host core.  Short runs: a few seconds each."""
+    import io
+    import numpy as np
+    import torch
+    from projectiontrainer_b200 import ops
+    from projectiontrainer_b200.engine import build_engine
+    from projectiontrainer_b200.lora import LoraState
+    out = {}
+    try:
+        B, T = 32, 128
+        g = torch.Generator(device=dev).manual_seed(7)
+        batch = {"pixel_values": torch.rand(B, 3, vc.image, vc.image, generator=g, device=dev) * 2 - 1,
+                 "token_ids": torch.randint(3, lc.vocab, (B, T), generator=g, device=dev)}
+        batch["labels"] = batch["token_ids"].clone()
+        batch["labels"][:, :T // 2] = -100
+        batch["label_span"] = (T // 2, T - T // 2)
+        res = {}
+        for name, lora in (("frozen_llm", False), ("lora_r16_all_targets", True)):
+            eng = build_engine(vc, lc, dev)
+            if lora:
+                eng.lora = LoraState(lc, dev, r=16, alpha=32.0)
+                mask = torch.zeros_like(eng.lora.flat)
+                for v in eng.lora.state_dict(mask).values():
+                    v.fill_(1.0)
+                eng.lora.flat.add_(torch.randn_like(mask) * 0.01 * mask * (eng.lora.flat == 0))    # B != 0: no zero shortcuts
+                eng.lora.refresh_shadow()
+            ms = _timed(lambda: eng.train_step(batch, 1e-4, max_norm=1.0), 6, warm=4)
+            res[name] = {"ms_per_step": ms, "images_per_s": B / ms * 1e3}
+            if lora:
+                res[name]["adapter_params"] = eng.lora.num_parameters()
+            del eng
+            torch.cuda.empty_cache()
+        out["stage2_vqa_microbatch"] = {"what": f"SigLIP-L + Gemma3-1B, B={B}, question {T // 2} + answer {T - T // 2} "
+                                                "tokens, forward + backward + clip 1.0 + AdamW through the CUDA graph",
+                                        **res}
+    except Exception as e:
+        out["stage2_vqa_microbatch"] = {"error": f"{type(e).__name__}: {e}"}
+    try:
+        from PIL import Image
+        H, W, N, S = 2500, 2048, 16, vc.image
+        rng = np.random.default_rng(0)
+        yy, xx = np.mgrid[0:H, 0:W]
+        base = (128 + 90 * np.sin(yy / 97.0) * np.cos(xx / 61.0)).astype(np.float32)
+        files = []
+        for i in range(2):
+            b = io.BytesIO()
+            Image.fromarray(np.clip(base + rng.normal(0, 6 + 2 * i, (H, W)), 0, 255).astype(np.uint8)).save(b, "JPEG", quality=90)
+            files.append(b.getvalue())
+        files = [files[i % 2] for i in range(N)]
+        t0 = time.perf_counter()
+        ref = np.asarray(Image.open(io.BytesIO(files[0])).convert("RGB").resize((S, S)))
+        t_pil = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        packed = ops.jpeg_pack(files)
+        t_pack = (time.perf_counter() - t0) / N
+        ws = torch.empty(packed["workspace_bytes"], dtype=torch.uint8, device=dev)
+        ws2 = torch.empty(ops.image_preprocess_workspace(H, W, S, S), dtype=torch.uint8, device=dev)
+        px = torch.empty(N, 3, S, S, device=dev)
+        u8 = torch.empty(S, S, 3, dtype=torch.uint8, device=dev)
+
+        def run():
+            imgs = ops.jpeg_decode(packed, dev, ws)
+            for i, im in enumerate(imgs):
+                ops.image_preprocess(im, px[i], ws2, dst_u8=u8 if i == 0 else None)
+        ms = _timed(run, 3, warm=2)
+        out["jpeg_decode_resize_normalize"] = {
+            "what": f"{N} baseline grayscale JPEG files of {H} x {W} (quality 90, no restart markers, "
+                    f"{len(files[0]) / 1e6:.2f} MB each): upload + Huffman/IDCT/colour + bicubic resize to {S} x {S} + "
+                    "normalize on the GPU, vs Pillow decode + resize on one host core",
+            "gpu_ms_per_batch": ms, "gpu_images_per_s": N / ms * 1e3, "host_pack_ms_per_image": t_pack * 1e3,
+            "pillow_ms_per_image": t_pil * 1e3, "resized_image_equals_pillow": bool(np.array_equal(u8.cpu().numpy(), ref))}
+    except Exception as e:
+        out["jpeg_decode_resize_normalize"] = {"error": f"{type(e).__name__}: {e}"}
+    return out
 
 
 def aux_configs_1b(eng, vc, lc, dev, peak):
