@@ -62,7 +62,14 @@ typedef enum {
      * receives dO and aux2 (f32 [B*hq, S], zero-filled by pt_gemm_bf16 itself) receives
      * delta[(b*hq + head)*S + s] = sum_d bf16(dO[b*S+s, head*hd + d]) * O[...], with S = aux_i0, hd = aux_i1
      * (hd % 128 == 0, N % 256 == 0).  Replaces pt_attn_delta + one read of dO and O. */
-    PT_ACT_ATTN_DELTA = 9
+    PT_ACT_ATTN_DELTA = 9,
+    /* Cross-entropy statistics of the LM head (HF:models/gemma3/modeling_gemma3.py:649-656 + HF:loss/loss_utils.py:45-67)
+     * in the epilogue of the logits GEMM: C [M, N] bf16 receives the logits as usual and aux2 (f32
+     * [2 * ceil(N / 256)][M][2]) receives, per row and per 128-column half tile, the running maximum and
+     * sum(exp(x - max)) of the bf16-ROUNDED logits (what a pass over the stored logits would see).
+     * pt_ce_from_partials turns them into the row log-sum-exps: one 2.1 GB read of the logits less per step.
+     * No bias / residual / C_pre / alpha, not batched; 256-wide tiles. */
+    PT_ACT_CE_STATS = 10
 } pt_act;
 
 typedef enum {
@@ -314,6 +321,12 @@ int pt_ce_fwd_bwd(void* logits_bf16, long long ld, const int32_t* targets, int r
 
 /* out[n] = sum_m x[m][n] (bias gradients). */
 int pt_colsum(const void* x_bf16, long long ld, float* out, int M, int N, void* stream);
+/* The rest of the shifted masked cross-entropy when the logits GEMM ran with PT_ACT_CE_STATS: combines the per-tile
+ * partials (stats: f32 [parts][rows][2], parts = 2 * ceil(V / 256)) into lse [rows], forms the loss
+ * (mean over targets >= 0 of lse - logit[target]; NaN when there is none) and overwrites the logits with
+ * dlogits = (softmax - onehot) * gscale / n_valid, exactly as pt_ce_fwd_bwd does after its own statistics pass. */
+int pt_ce_from_partials(void* logits_bf16, long long ld, const int32_t* targets, int rows, int V, const float* stats,
+                        int parts, float* lse, float* acc2, float* loss, float gscale, int32_t* err_flags, void* stream);
 /* out[0] = sum g^2 */
 int pt_sumsq(const float* g, long long n, float* out, void* stream);
 /* clip_grad_norm_(max_norm) + AdamW step on a flat f32 buffer, refreshing a bf16 shadow copy

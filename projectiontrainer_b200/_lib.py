@@ -16,7 +16,7 @@ LIB_PATH = Path(os.environ.get("PT_STAGE1_LIB") or PKG / "libpt_stage1.so")
 PT_BF16, PT_F32, PT_I64, PT_I32 = 0, 1, 2, 3
 BAND_NONE, BAND_SCORES, BAND_K_BY_QUERY, BAND_K_BY_KEY = 0, 1, 2, 3
 ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD = 0, 1, 2, 3, 4, 5
-ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GELU_ERF_BWD, ACT_ATTN_DELTA = 6, 7, 8, 9
+ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GELU_ERF_BWD, ACT_ATTN_DELTA, ACT_CE_STATS = 6, 7, 8, 9, 10
 
 
 class GemmArgs(C.Structure):
@@ -69,7 +69,7 @@ def check(rc: int, what: str) -> None:
 
 
 # kernels launched per C-ABI call (for the bench's gpu_launches claim)
-KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_image_preprocess": 3, "pt_jpeg_decode_batch": 3}
+KERNELS_PER_CALL = {"pt_ce_fwd_bwd": 3, "pt_ce_from_partials": 3, "pt_image_preprocess": 3, "pt_jpeg_decode_batch": 3}
 launch_count = 0
 
 

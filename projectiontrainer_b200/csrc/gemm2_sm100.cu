@@ -761,6 +761,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     epi_chunk<PT_ACT_NONE>(vg, stg, lane, o);
                 }
             } else {
+            [[maybe_unused]] float ce_m = -INFINITY, ce_s = 0.f;       // PT_ACT_CE_STATS: this lane's row, this half tile
 #pragma unroll 1
             for (int c = 0; c < NCH; ++c) {
                 const int col_local = hf * BNH + c * 32;
@@ -785,6 +786,27 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         for (int it = 0; it < 8; ++it) sb_pq[it] = sb_pn[it];
                     }
                     continue;
+                }
+                if constexpr (ACT == PT_ACT_CE_STATS) {
+                    // running maximum and sum of exponentials over the chunk's columns, from the logits as they
+                    // will be stored (rounded to bf16); lane = row, so no exchange between lanes is needed
+                    const int ncol = min(32, p.N - col0);
+                    float x[32], cm = -INFINITY;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        x[j] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j])));
+                        if (j < ncol) cm = fmaxf(cm, x[j]);
+                    }
+                    const float mn = fmaxf(ce_m, cm);
+                    const float k = 1.4426950408889634f, mk = -mn * k;
+                    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        if (j < ncol) s0 += exp2f(fmaf(x[j], k, mk));
+                        if (j + 1 < ncol) s1 += exp2f(fmaf(x[j + 1], k, mk));
+                    }
+                    ce_s = ce_s * exp2f((ce_m - mn) * k) + (s0 + s1);
+                    ce_m = mn;
                 }
                 if constexpr (ACT == PT_ACT_SOFTMAX_BWD) {
                     EpiSbwd o;
@@ -829,6 +851,13 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 o.rows_valid = rows_valid; o.row_lo = row_lo;
                 o.cols_q = min(32, ((p.N + 3) & ~3) - col0);
                 epi_chunk<ACT>(v, stg, lane, o);
+            }
+            if constexpr (ACT == PT_ACT_CE_STATS) {
+                // one (max, sum) pair per row and half tile, part-major so that a warp's 32 rows are contiguous
+                if (lane >= row_lo && lane < rows_valid) {
+                    const long long part = static_cast<long long>(n_blk) * 2 + hf;
+                    reinterpret_cast<float2*>(p.delta)[part * p.M + row0 + lane] = make_float2(ce_m, ce_s);
+                }
             }
             }   // !GEGLU
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -912,6 +941,10 @@ int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUt
         if (p.act == PT_ACT_GELU_ERF_BWD) return launch_gemm2_t<BN_, PT_ACT_GELU_ERF_BWD>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st); \
         if (p.act == PT_ACT_ATTN_DELTA) return launch_gemm2_t<BN_, PT_ACT_ATTN_DELTA>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st); \
         return launch_gemm2_t<BN_, PT_ACT_NONE>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);
+    if (p.act == PT_ACT_CE_STATS) {
+        if (bn != 256) { set_error("gemm2: the CE-statistics epilogue needs BN = 256"); return PT_ERR_INVALID; }
+        return launch_gemm2_t<256, PT_ACT_CE_STATS>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);
+    }
     if (p.act == PT_ACT_GEGLU) {
         if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }
         return launch_gemm2_t<256, PT_ACT_GEGLU>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);

@@ -40,6 +40,7 @@ struct GemmDev {
     long long ld_aux;
     int ff;
     GluConsts glu;    // activation of the fused gated-unit epilogues (tanh-GELU or SiLU)
+    // (PT_ACT_CE_STATS re-uses `delta` for its f32 partials [2 * nt][M][2])
     // PT_ACT_ATTN_DELTA: delta [B*hq, S] f32 (zeroed by the host wrapper), row r = b * dl_S + s, head = column / dl_hd
     float* delta;
     int dl_S, dl_hd, dl_hq;

@@ -196,7 +196,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     }
     PT_REQUIRE((a->N % 4) == 0 || ((!a->bias || a->act == PT_ACT_SOFTMAX_BWD) && !a->residual && !a->C_pre),
                "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
-    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_ATTN_DELTA, "pt_gemm_bf16: bad act %d", a->act);
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_CE_STATS, "pt_gemm_bf16: bad act %d", a->act);
+    if (a->act == PT_ACT_CE_STATS) {
+        PT_REQUIRE(a->aux2 != nullptr && (reinterpret_cast<uintptr_t>(a->aux2) & 7) == 0,
+                   "pt_gemm_bf16: PT_ACT_CE_STATS needs aux2 = the f32 partials buffer [2 * ceil(N / 256)][M][2]");
+        PT_REQUIRE(a->c_dtype == PT_BF16 && !a->bias && !a->residual && !a->C_pre && a->alpha == 1.0f && a->K2 == 0 &&
+                       a->nz[0] * a->nz[1] * a->nz[2] == 1 && kg == 1 && a->band == PT_BAND_NONE && a->N >= 256,
+                   "pt_gemm_bf16: PT_ACT_CE_STATS takes bf16 C, N >= 256, no bias / residual / C_pre / alpha / K2 and is not batched");
+    }
     const bool tile_epi = a->act == PT_ACT_GELU_ERF_BWD || a->act == PT_ACT_ATTN_DELTA;
     if (tile_epi) {
         PT_REQUIRE(a->aux != nullptr && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0 && a->ld_aux % 8 == 0 &&
@@ -279,6 +286,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         p.delta = static_cast<float*>(a->aux2);
         p.dl_S = a->aux_i0; p.dl_hd = a->aux_i1; p.dl_hq = a->N / a->aux_i1;
     }
+    if (a->act == PT_ACT_CE_STATS) p.delta = static_cast<float*>(a->aux2);
     PT_REQUIRE(a->band >= PT_BAND_NONE && a->band <= PT_BAND_K_BY_KEY && a->band_window >= 0,
                "pt_gemm_bf16: bad band %d / window %d", a->band, a->band_window);
     p.band = a->band; p.band_w = a->band_window;
@@ -287,8 +295,9 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUtensorMap ta, tb;
     // CTA-pair kernel (gemm2_sm100.cu): 256 x bn tiles, one per cluster of two SMs
-    int bn = (geglu || a->act == PT_ACT_ATTN_DELTA) ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
-    if (!geglu && a->act != PT_ACT_ATTN_DELTA && a->bn_hint != 0) {
+    const bool wide_only = geglu || a->act == PT_ACT_ATTN_DELTA || a->act == PT_ACT_CE_STATS;
+    int bn = wide_only ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
+    if (!wide_only && a->bn_hint != 0) {
         PT_REQUIRE(a->bn_hint == 64 || a->bn_hint == 128 || a->bn_hint == 192 || a->bn_hint == 256,
                    "pt_gemm_bf16: bn_hint must be 0, 64, 128, 192 or 256");
         PT_REQUIRE(!p.b_mn || (a->bn_hint / 2) % 64 == 0, "pt_gemm_bf16: an MN-major B operand needs bn_hint 128 or 256");

@@ -184,6 +184,45 @@ ce_stats_kernel(const __nv_bfloat16* __restrict__ logits, long long ld, const in
     }
 }
 
+// The same statistics from the per-tile partials the logits GEMM left behind (PT_ACT_CE_STATS): stats
+// [parts][rows][2] = (max, sum exp(x - max)) per row and 128-column half tile.  Block = 32 rows x 8 part lanes; every
+// warp-iteration reads 32 consecutive rows of one part (256 contiguous bytes).
+__global__ void __launch_bounds__(256)
+ce_combine_kernel(const float2* __restrict__ stats, int parts, int rows, const __nv_bfloat16* __restrict__ logits,
+                  long long ld, const int* __restrict__ targets, int V, float* __restrict__ lse_out,
+                  float* __restrict__ acc, int* __restrict__ err) {
+    __shared__ float sm[8][32], ss[8][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int r = blockIdx.x * 32 + lane;
+    float m = -INFINITY, s = 0.f;
+    if (r < rows) {
+#pragma unroll 4
+        for (int pidx = w; pidx < parts; pidx += 8) {
+            const float2 v = stats[static_cast<long long>(pidx) * rows + r];
+            const float mn = fmaxf(m, v.x);
+            if (mn > -INFINITY) {
+                s = s * __expf(m - mn) + v.y * __expf(v.x - mn);
+                m = mn;
+            }
+        }
+    }
+    sm[w][lane] = m; ss[w][lane] = s;
+    __syncthreads();
+    if (w != 0 || r >= rows) return;
+    for (int k = 1; k < 8; ++k) {
+        const float m2 = sm[k][lane], s2 = ss[k][lane];
+        const float mn = fmaxf(m, m2);
+        if (mn > -INFINITY) { s = s * __expf(m - mn) + s2 * __expf(m2 - mn); m = mn; }
+    }
+    const int tgt = targets[r];
+    if (tgt >= V && err) atomicOr(err, PT_ERRFLAG_TARGET);
+    if (tgt < 0 || tgt >= V) { lse_out[r] = 0.f; return; }
+    const float lse = m + logf(s);
+    lse_out[r] = lse;
+    atomicAdd(acc, lse - __bfloat162float(logits[r * ld + tgt]));
+    atomicAdd(acc + 1, 1.f);
+}
+
 // grad: dlogits = (softmax - onehot) * gscale / n_valid, in place over the bf16 logits.
 __global__ void __launch_bounds__(1024)
 ce_grad_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const int* __restrict__ targets, int V,
@@ -372,6 +411,23 @@ extern "C" int pt_embed_splice(const int64_t* token_ids, const int64_t* labels, 
         reinterpret_cast<long long*>(attn_mask), reinterpret_cast<long long*>(lm_labels), keyvalid, targets,
         static_cast<long long>(vocab), err_flags);
     return check_launch("embed_splice");
+}
+
+extern "C" int pt_ce_from_partials(void* logits_bf16, long long ld, const int32_t* targets, int rows, int V,
+                                   const float* stats, int parts, float* lse, float* acc2, float* loss, float gscale,
+                                   int32_t* err_flags, void* stream) {
+    PT_REQUIRE(logits_bf16 && targets && stats && lse && acc2 && loss, "pt_ce_from_partials: null pointer");
+    PT_REQUIRE(rows > 0 && V > 0 && V % 8 == 0 && ld % 8 == 0, "pt_ce_from_partials: V and ld must be multiples of 8");
+    PT_REQUIRE(parts == 2 * ((V + 255) / 256), "pt_ce_from_partials: parts must be 2 * ceil(V / 256) (got %d for V = %d)", parts, V);
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    cudaStream_t st = ST(stream);
+    if (cudaMemsetAsync(acc2, 0, 2 * sizeof(float), st) != cudaSuccess) return check_launch("ce acc memset");
+    ce_combine_kernel<<<(rows + 31) / 32, 256, 0, st>>>(reinterpret_cast<const float2*>(stats), parts, rows,
+                                                        CBF(logits_bf16), ld, targets, V, lse, acc2, err_flags);
+    ce_finalize_kernel<<<1, 1, 0, st>>>(acc2, loss);
+    dim3 grid((V / 8 + 255) / 256, rows);
+    ce_grad_kernel<<<grid, 256, 0, st>>>(BF(logits_bf16), ld, targets, V, lse, acc2, gscale);
+    return check_launch("ce_from_partials");
 }
 
 extern "C" int pt_ce_fwd_bwd(void* logits_bf16, long long ld, const int32_t* targets, int rows, int V,

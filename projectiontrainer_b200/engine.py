@@ -233,6 +233,9 @@ class Stage1Engine:
         self.fuse_attn_delta = ops.attn_delta_fusable(self.lcfg.hq, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_FUSE_DELTA", "1") != "0"
         self.fuse_gelu_bwd = os.environ.get("PT_STAGE1_FUSE_GELU_BWD", "1") != "0"
+        # cross-entropy statistics (row max / sum exp partials) in the LM-head GEMM epilogue: the separate statistics
+        # pass over the 2.1 GB of logits goes away
+        self.fuse_ce_stats = self.lcfg.vocab >= 256 and os.environ.get("PT_STAGE1_FUSE_CE_STATS", "1") != "0"
         # attention backward on a CTA pair per 128 keys (0: the single-CTA kernel on 64-key tiles)
         self.attn_bwd_pair = ops.attn_gemma_bwd_pair_ok(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_ATTN_BWD_PAIR", "1") != "0"
@@ -500,14 +503,22 @@ class Stage1Engine:
         yf = self.buf("l_yf", (R, h), BF16)
         ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(T, S, lab0))
         logits = self.buf("l_logits", (R, _pad8(c.vocab)), BF16)[:, :c.vocab]    # row stride padded to 16 B
-        ops.linear(yf, Lm.lm_head, out=logits)
+        stats = None
+        if self.fuse_ce_stats:
+            stats = self.buf("l_ce_parts", (ops.ce_stats_parts(c.vocab), R, 2), F32)
+            ops.linear_ce_stats(yf, Lm.lm_head, logits, stats)
+        else:
+            ops.linear(yf, Lm.lm_head, out=logits)
         tgt = self.buf("l_tgt", (R,), torch.int32)
         # targets[b, lab0+t] for t in 0..T-1 -> compact [B*T] (int copy: plumbing, not arithmetic)
         tgt.view(B, T).copy_(targets.view(B, S)[:, lab0:lab0 + T])
         lse = self.buf("l_lse", (R,), F32)
         acc2 = self.buf("l_acc2", (2,), F32)
         loss = self.buf("l_loss", (1,), F32)
-        ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.loss_divisor, err=self._err)
+        if stats is not None:
+            ops.ce_from_partials(logits, tgt, stats, lse, acc2, loss, 1.0 / self.loss_divisor, err=self._err)
+        else:
+            ops.ce_fwd_bwd(logits, tgt, lse, acc2, loss, 1.0 / self.loss_divisor, err=self._err)
         self.saved = dict(layers=sv, x_final=x, logits=logits, B=B, S=S, T=T, lab0=lab0) if save else None
         return loss
 

@@ -12,7 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import BAND_K_BY_KEY, BAND_K_BY_QUERY, BAND_NONE, BAND_SCORES  # noqa: F401
-from ._lib import ACT_ATTN_DELTA, ACT_GELU_ERF_BWD, ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
+from ._lib import ACT_CE_STATS, ACT_ATTN_DELTA, ACT_GELU_ERF_BWD, ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
@@ -405,6 +405,31 @@ def ce_fwd_bwd(logits, targets, lse, acc2, loss, gscale, err=None):
     rows, V = logits.shape
     _lib.call("pt_ce_fwd_bwd", _ptr(logits), C.c_longlong(logits.stride(0)), _ptr(targets), rows, V,
               _ptr(lse), _ptr(acc2), _ptr(loss), _f(gscale), _ptr(err), _stream())
+
+
+def ce_stats_parts(V: int) -> int:
+    """Partials per row that the CE-statistics epilogue writes: one per 128-column half of every 256-wide tile."""
+    return 2 * ((V + 255) // 256)
+
+
+def linear_ce_stats(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor, stats: torch.Tensor) -> torch.Tensor:
+    """logits[M, V] = x[M, K] @ w[V, K]^T (bf16, the LM head) with, in the same epilogue, the per-row (max, sum exp)
+    partials of the rounded logits into stats (f32 [ce_stats_parts(V), M, 2]) — ce_from_partials finishes the loss."""
+    M, K = x.shape
+    V = w.shape[0]
+    assert stats.dtype == torch.float32 and stats.numel() >= ce_stats_parts(V) * M * 2 and V >= 256
+    _req_cuda(stats)
+    gemm_raw(M=M, N=V, K=K, A=x, lda=x.stride(0), B=w, ldb=w.stride(0), Cout=out, ldc=out.stride(0),
+             act=ACT_CE_STATS, aux2=stats)
+    return out
+
+
+def ce_from_partials(logits, targets, stats, lse, acc2, loss, gscale, err=None):
+    """ce_fwd_bwd without its pass over the logits for the statistics (they come from linear_ce_stats)."""
+    _req_cuda(logits, targets, stats, lse, acc2, loss, err)
+    rows, V = logits.shape
+    _lib.call("pt_ce_from_partials", _ptr(logits), C.c_longlong(logits.stride(0)), _ptr(targets), int(rows), int(V),
+              _ptr(stats), int(ce_stats_parts(V)), _ptr(lse), _ptr(acc2), _ptr(loss), _f(gscale), _ptr(err), _stream())
 
 
 def colsum(x, out):

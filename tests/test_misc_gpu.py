@@ -226,3 +226,46 @@ def test_cast_and_patchify(cuda_dev):
     ops.patchify(px, p, cols)
     ref = torch.nn.functional.unfold(px, kernel_size=p, stride=p).transpose(1, 2).reshape(-1, 3 * p * p)
     assert torch.equal(cols, ref.to(torch.bfloat16))
+
+
+# ------------------------------------------------------------------------------------------------ CE statistics in the LM-head epilogue
+@pytest.mark.parametrize("rows,V,K", [(64, 1024, 128), (300, 304, 64), (257, 1312, 192), (128, 262208, 64),
+                                      (4096, 4096, 1152), (96, 151936, 64)])
+def test_lm_head_gemm_with_ce_statistics_epilogue(cuda_dev, rows, V, K):
+    """PT_ACT_CE_STATS + pt_ce_from_partials == the logits GEMM followed by pt_ce_fwd_bwd: same logits, same lse,
+    loss and dlogits; against torch's cross-entropy on the stored bf16 logits.  Vocabularies that are not multiples of
+    the 256-wide tile (shifted last tile: 1312, 262208 = Gemma3-4B, 151936 = Qwen3; columns past the end: 304) and
+    row counts that are not multiples of the 256-row tile."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(rows + V)
+    x = (torch.randn(rows, K, device=cuda_dev) * 1.5).to(torch.bfloat16)
+    w = (torch.randn(V, K, device=cuda_dev) * (3.0 / K ** 0.5)).to(torch.bfloat16)
+    tgt = torch.randint(0, V, (rows,), device=cuda_dev, dtype=torch.int32)
+    tgt[torch.rand(rows, device=cuda_dev) < 0.25] = -100
+    tgt[0] = V - 1
+    ld = (V + 7) // 8 * 8 + 8
+    mk = lambda: torch.zeros(rows, ld, device=cuda_dev, dtype=torch.bfloat16)[:, :V]
+    # reference path: plain GEMM, then the statistics pass over the stored logits
+    lg_a = ops.linear(x, w, out=mk())
+    stored = lg_a.clone()
+    lse_a, acc_a, loss_a = torch.empty(rows, device=cuda_dev), torch.empty(2, device=cuda_dev), torch.empty(1, device=cuda_dev)
+    ops.ce_fwd_bwd(lg_a, tgt, lse_a, acc_a, loss_a, 0.5)
+    # fused path
+    stats = torch.full((ops.ce_stats_parts(V), rows, 2), float("nan"), device=cuda_dev)
+    lg_b = ops.linear_ce_stats(x, w, mk(), stats)
+    assert torch.equal(lg_b, stored)                              # the epilogue stores the same logits
+    lse_b, acc_b, loss_b = torch.empty(rows, device=cuda_dev), torch.empty(2, device=cuda_dev), torch.empty(1, device=cuda_dev)
+    err = torch.zeros(1, dtype=torch.int32, device=cuda_dev)
+    ops.ce_from_partials(lg_b, tgt, stats, lse_b, acc_b, loss_b, 0.5, err=err)
+    valid = tgt >= 0
+    ref = stored.float()
+    lse_ref = torch.logsumexp(ref, dim=-1)
+    assert (lse_b[valid] - lse_ref[valid]).abs().max().item() < 1e-4
+    assert (lse_b[valid] - lse_a[valid]).abs().max().item() < 1e-4
+    ref_loss = torch.nn.functional.cross_entropy(ref, tgt.long(), ignore_index=-100)
+    assert abs(loss_b.item() - ref_loss.item()) < 2e-5 * abs(ref_loss.item())
+    assert int(acc_b[1].item()) == int(valid.sum()) and int(err.item()) == 0
+    d = (lg_b.float() - lg_a.float()).abs().max().item()
+    assert d <= 2.0 ** -8 * lg_a.float().abs().max().item() + 1e-12, d          # dlogits of both paths
+    assert (lg_b.float()[~valid] == 0).all()
+    assert not torch.isnan(stats).any()                           # every (part, row) pair was written
