@@ -274,3 +274,57 @@ def test_qlora_trainer_dropin_end_to_end_tiny(cuda_dev, tmp_path):
     assert all(torch.equal(v.cpu(), sd1[k]) for k, v in tr2.engine.lora.state_dict().items())
     v2 = tr2.evaluate(0, 0)
     assert abs(v2 - vals[-1]) / vals[-1] < 1e-3, (v2, vals)
+
+
+@pytest.mark.parametrize("fused", [True, False], ids=["fused_kernels", "unfused_kernels"])
+def test_lora_qwen3_recipe_projector_frozen_vs_oracle(cuda_dev, fused, monkeypatch):
+    """What the reference's Stage-2 launch script runs (ref:Stage2/run_vqa_train_stage2.sh: Qwen3 + `--enable_qlora`,
+    projector frozen): the Qwen3 decoder recipe (pre-norm, residual adds in the o / down epilogues, SwiGLU, untied LM
+    head, head_dim 128) with LoRA on all seven projections and no projector gradient, Stage-2 layout, against the CPU
+    oracle on the same bf16-rounded matrices; fused and unfused kernel paths."""
+    from oracle import stage1_oracle as O
+    from oracle import stage2_oracle as O2
+    from projectiontrainer_b200 import engine as E
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    from projectiontrainer_b200.lora import LoraState
+    from projectiontrainer_b200.vqa_trainer import vqa_step_inputs
+    if not fused:
+        for k in ("PT_STAGE1_FUSE_ATTN_FWD", "PT_STAGE1_FUSE_SOFTMAX_BWD", "PT_STAGE1_FUSE_GEGLU", "PT_STAGE1_FUSE_CE_STATS"):
+            monkeypatch.setenv(k, "0")
+    vkw = dict(hidden=128, ff=256, layers=2, heads=2, image=160, patch=16)
+    lkw = dict(vocab=1024, hidden=256, ff=384, layers=4, hq=8, hkv=2, hd=128, window=0, q_scalar=128.0, pattern=1,
+               sandwich_norm=False, silu=True, scale_embed=False, tie_lm_head=False)
+    r, alpha = 16, 32.0
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    Wv, Wl, P = O.init_siglip(ovc), O.init_gemma(olc), O.init_projector(ovc.hidden, olc.hidden)
+    qz = lambda t: t.to(torch.bfloat16).float()
+    L0 = {k: qz(v) for k, v in O2.init_lora(olc, r, O2.ALL_TARGETS, b_std=0.02).items()}
+    samples = O2.synthetic_vqa_samples(3, ovc, olc, seed=78, q_len=(3, 14), a_len=(5, 30))
+    cb = _collated(samples, [0, 1, 2], _Tok(olc.pad_id, "left"))
+    Wv_q = {k: (qz(v) if v.dim() == 2 and k != "pos" else v) for k, v in Wv.items()}
+    Wl_q = {k: (qz(v) if v.dim() == 2 else v) for k, v in Wl.items()}
+    ref = O2.vqa_micro_step(cb["pixel_values"], cb["question_input_ids"], cb["answer_input_ids"], Wv_q, P, Wl_q,
+                            ovc, olc, scale_dtype=torch.bfloat16, lora=L0, lora_scale=alpha / r, train_projector=False)
+    lcfg = GemmaCfg(**lkw)
+    lo = LoraState(lcfg, cuda_dev, r=r, alpha=alpha)
+    lo.load_state_dict(_to_peft(L0))
+    eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, lcfg, cuda_dev),
+                         E.ProjectorState(P, cuda_dev), cuda_dev, lora=lo, train_projector=False)
+    assert eng.fuse_geglu == fused and eng.fuse_attn_fwd == fused
+    batch = vqa_step_inputs(cb, olc.pad_id, bucket=32)
+    eng.proj.grad.fill_(123.0)
+    for it in range(3):
+        lo.grad.fill_(float("nan"))
+        loss = eng._graphed_forward_backward({k: (v.to(cuda_dev) if torch.is_tensor(v) else v)
+                                              for k, v in batch.items()}, olc.pad_id)
+        torch.cuda.synchronize()
+        assert abs(loss.item() - ref["loss"]) / ref["loss"] < 1e-2, (it, loss.item(), ref["loss"])
+        ours = _by_oracle_key(lo, lo.grad)
+        for w in "AB":
+            c = _group_cos(ours, ref["lora_grads"], w)
+            assert c > 0.999, (it, w, c)
+        assert min(_cos(ours[k].cpu(), ref["lora_grads"][k]) for k in ours) > 0.99
+    assert (eng.proj.grad == 123.0).all()                 # frozen projector: its backward never ran
+    p0 = {k: v.clone() for k, v in eng.proj.params().items()}
+    eng.optimizer_step(1e-3, max_norm=1.0)
+    assert all(torch.equal(v, p0[k]) for k, v in eng.proj.params().items()) and lo.step == 1

@@ -14,29 +14,31 @@ from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import torch
 from projectiontrainer_b200 import _lib, ops
-from projectiontrainer_b200.config import GEMMA3_1B, SIGLIP_L
+from projectiontrainer_b200.config import GEMMA3_1B, GEMMA3_4B, QWEN3_8B, SIGLIP_L
 from projectiontrainer_b200.engine import build_engine
 from projectiontrainer_b200.lora import LoraState
 
 dev = torch.device("cuda:0")
-B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
-T = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+B = int(sys.argv[1]) if len(sys.argv) > 1 and not sys.argv[1].startswith("-") else 32
+T = int(sys.argv[2]) if len(sys.argv) > 2 and not sys.argv[2].startswith("-") else 128
 STEPS, WARM = 10, 4
+LLM_NAME = sys.argv[sys.argv.index("--llm") + 1] if "--llm" in sys.argv else "gemma3_1b"
+LLM = {"gemma3_1b": GEMMA3_1B, "gemma3_4b": GEMMA3_4B, "qwen3_8b": QWEN3_8B}[LLM_NAME]
 
 
 def batch(seed):
     g = torch.Generator(device=dev).manual_seed(seed)
     px = torch.rand(B, 3, 384, 384, generator=g, device=dev) * 2 - 1
-    ids = torch.randint(3, GEMMA3_1B.vocab, (B, T), generator=g, device=dev)
+    ids = torch.randint(3, LLM.vocab, (B, T), generator=g, device=dev)
     lab = ids.clone()
     lab[:, :T // 2] = -100
     return {"pixel_values": px, "token_ids": ids, "labels": lab, "label_span": (T // 2, T - T // 2)}
 
 
 def run(name, lora, train_projector):
-    eng = build_engine(SIGLIP_L, GEMMA3_1B, dev)
+    eng = build_engine(SIGLIP_L, LLM, dev)
     if lora:
-        eng.lora = LoraState(GEMMA3_1B, dev, r=16, alpha=32.0)
+        eng.lora = LoraState(LLM, dev, r=16, alpha=32.0)
         # B = 0 at the start would make every dt (and dA) exactly zero: give the adapters a trained-like state
         eng.lora.flat.add_(torch.randn_like(eng.lora.flat) * 0.01 * (eng.lora.flat == 0) *
                            _adapter_mask(eng.lora))
@@ -89,7 +91,7 @@ def _adapter_mask(lo):
     return m
 
 
-res = {"workload": f"Stage-2 micro-batch, SigLIP-L/16-384 + Gemma3-1B, B={B}, question {T // 2} + answer {T - T // 2} tokens, "
+res = {"workload": f"Stage-2 micro-batch, SigLIP-L/16-384 + {LLM_NAME}, B={B}, question {T // 2} + answer {T - T // 2} tokens, "
                    f"S={575 + T}, LoRA r=16 alpha=32 on q,k,v,o,gate,up,down", "steps": STEPS, "warmup": WARM}
 for name, lora, tp in (("frozen", False, True), ("lora", True, True)) + ((("lora_only", True, False),) if "--all" in sys.argv else ()):
     res[name] = run(name, lora, tp)
