@@ -381,6 +381,20 @@ class Stage1Engine:
                      c_zs=(S * ld, G * S * ld, c.hq * S * ld), alpha=alpha, band=ops.BAND_SCORES,
                      band_window=window, **epilogue)
 
+    def _thin(self, fn, x, w, out, alpha):
+        """A rank-wide adapter product out[M, R] = alpha * x . w (fn = ops.linear or ops.linear_dgrad).  At small batch
+        sizes it has a handful of 256-row tiles for 74 SM pairs and a long contraction: then it runs split-K into an
+        f32 scratch matrix (cleared first) that is cast to bf16 afterwards."""
+        M, K = x.shape
+        tiles = -(-M // 256) * -(-out.shape[1] // 64)
+        if tiles * 2 > 74 or K < 1024:
+            fn(x, w, out=out, alpha=alpha)
+            return
+        tmp = self.buf("lora_thin_f32", tuple(out.shape), F32)
+        tmp.zero_()
+        fn(x, w, out=tmp, alpha=alpha, ksplit=-1)
+        ops.cast_f32_bf16(tmp, out)
+
     # ------------------------------------------------------------------ LLM forward + loss
     def _llm_stack(self, x0: torch.Tensor, keyvalid, B: int, S: int, save: bool, cache=None, pos_ids=None):
         """Decoder stack over x0 f32 [B*S, h] (HF:models/gemma3/modeling_gemma3.py:404-434 per layer).
@@ -437,7 +451,7 @@ class Stage1Engine:
                 if grp is None:
                     return {}
                 t = self.buf(_tag + "t_" + g, (M, grp.R), BF16)
-                ops.linear(x_in, grp.A(lo.shadow), out=t, alpha=lo.scale)
+                self._thin(ops.linear, x_in, grp.A(lo.shadow), t, lo.scale)
                 _ts[g] = t
                 return dict(x2=t, w2=grp.B(lo.shadow))
 
@@ -588,7 +602,7 @@ class Stage1Engine:
             if grp is None:
                 return {}, None
             dt = self.buf("b_dt_" + g, (M, grp.R), BF16)
-            ops.linear_dgrad(dy, grp.B(lo.shadow), out=dt, alpha=lo.scale)
+            self._thin(ops.linear_dgrad, dy, grp.B(lo.shadow), dt, lo.scale)
             return dict(dy2=dt, w2=grp.A(lo.shadow)), (grp, dt)
 
         def lora_wgrad(st, dy, x_in, t):

@@ -113,7 +113,7 @@ def _seg2(M: int, N: int, a2, b2, b_mn: bool) -> dict:
 
 
 def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residual=None,
-           out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0, x2=None, w2=None) -> torch.Tensor:
+           out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0, x2=None, w2=None, ksplit=0) -> torch.Tensor:
     """y[M,N] = act(alpha * (x[M,K] @ w[N,K]^T (+ x2[M,K2] @ w2[N,K2]^T)) + bias) (+ residual).  bf16 row-major 2-D
     operands."""
     M, K = x.shape
@@ -123,13 +123,13 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residua
         out = torch.empty((M, N), dtype=out_dtype, device=x.device)
     gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w, ldb=w.stride(0), Cout=out,
              ldc=out.stride(0), bias=bias, residual=residual,
-             ldr=0 if residual is None else residual.stride(0), act=act, alpha=alpha, c_pre=c_pre,
+             ldr=0 if residual is None else residual.stride(0), act=act, alpha=alpha, c_pre=c_pre, ksplit=ksplit,
              **_seg2(M, N, x2, w2, False))
     return out
 
 
 def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out=None, out_dtype=torch.bfloat16,
-                 residual=None, alpha=1.0, dy2=None, w2=None) -> torch.Tensor:
+                 residual=None, alpha=1.0, dy2=None, w2=None, ksplit=0) -> torch.Tensor:
     """dx[M,K] = alpha * (dy[M,N] @ w[N,K] (+ dy2[M,N2] @ w2[N2,K])) (+ residual) without transposing w (B operands
     MN-major)."""
     M, N = dy.shape
@@ -138,7 +138,7 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out=None, out_dtype=torch
     if out is None:
         out = torch.empty((M, K), dtype=out_dtype, device=dy.device)
     gemm_raw(M=M, N=K, K=N, A=dy, lda=dy.stride(0), B=w, ldb=w.stride(0), b_mn=True, Cout=out,
-             ldc=out.stride(0), residual=residual, alpha=alpha,
+             ldc=out.stride(0), residual=residual, alpha=alpha, ksplit=ksplit,
              ldr=0 if residual is None else residual.stride(0), **_seg2(M, K, dy2, w2, True))
     return out
 

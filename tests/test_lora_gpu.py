@@ -328,3 +328,35 @@ def test_lora_qwen3_recipe_projector_frozen_vs_oracle(cuda_dev, fused, monkeypat
     p0 = {k: v.clone() for k, v in eng.proj.params().items()}
     eng.optimizer_step(1e-3, max_norm=1.0)
     assert all(torch.equal(v, p0[k]) for k, v in eng.proj.params().items()) and lo.step == 1
+
+
+def test_thin_adapter_products_split_k_at_small_batch(cuda_dev):
+    """At small batch sizes (the reference's Stage-2 default is 4 per GPU) the rank-wide products t = x A^T and
+    dt = dy B have few row tiles and a long contraction: the engine runs them split-K through an f32 scratch matrix.
+    Same numbers as the direct launch, forward and input-gradient form, scale included."""
+    from projectiontrainer_b200 import engine as E, ops
+    eng = E.Stage1Engine.__new__(E.Stage1Engine)
+    eng._ws, eng.device = {}, cuda_dev
+    torch.manual_seed(0)
+    M, K, R = 3324, 4096, 64
+    x = torch.randn(M, K, device=cuda_dev).to(torch.bfloat16)
+    a = (torch.randn(R, K, device=cuda_dev) * 0.02).to(torch.bfloat16)
+    out = torch.empty(M, R, device=cuda_dev, dtype=torch.bfloat16)
+    eng._thin(ops.linear, x, a, out, 2.0)
+    assert ("lora_thin_f32", (M, R), torch.float32) in eng._ws                      # the split-K route was taken
+    ref = 2.0 * x.float() @ a.float().t()
+    assert (out.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item()
+    direct = ops.linear(x, a, alpha=2.0)
+    assert (out.float() - direct.float()).abs().max().item() <= 2.0 ** -7 * ref.abs().max().item()
+    dy = torch.randn(M, 12288, device=cuda_dev).to(torch.bfloat16)
+    b = (torch.randn(12288, R, device=cuda_dev) * 0.02).to(torch.bfloat16)
+    eng._thin(ops.linear_dgrad, dy, b, out, 0.5)
+    ref = 0.5 * dy.float() @ b.float()
+    assert (out.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item()
+    # many row tiles: the direct launch
+    eng._ws.clear()
+    xl = torch.randn(22496, 1152, device=cuda_dev).to(torch.bfloat16)
+    al = (torch.randn(R, 1152, device=cuda_dev) * 0.02).to(torch.bfloat16)
+    outl = torch.empty(22496, R, device=cuda_dev, dtype=torch.bfloat16)
+    eng._thin(ops.linear, xl, al, outl, 1.0)
+    assert not eng._ws
