@@ -322,7 +322,19 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     if (a->ksplit > 1 || a->ksplit == -1) {
         const int nkb = (a->K + BK - 1) / BK;
         const long long tiles = mt * nt * nbatch, slots = num_sms() / 2;
-        long long want = a->ksplit > 1 ? a->ksplit : (tiles >= slots ? 1 : (slots + tiles - 1) / tiles);
+        long long want = a->ksplit;
+        if (a->ksplit == -1) {
+            // the slice count that fills the waves best: a launch of tiles * n clusters' worth of work runs
+            // ceil(tiles * n / slots) waves; n between "one wave" and four times that, smaller n on ties
+            const long long lo = tiles >= slots ? 1 : (slots + tiles - 1) / tiles;
+            double best = -1.0;
+            want = lo;
+            for (long long n = lo; n <= 4 * lo && n <= nkb; ++n) {
+                const long long waves = (tiles * n + slots - 1) / slots;
+                const double eff = static_cast<double>(tiles * n) / static_cast<double>(waves * slots);
+                if (eff > best + 0.02) { best = eff; want = n; }
+            }
+        }
         if (want > nkb) want = nkb;
         p.kb_per = static_cast<int>((nkb + want - 1) / want);
         p.ksplit = (nkb + p.kb_per - 1) / p.kb_per;          // every slice non-empty

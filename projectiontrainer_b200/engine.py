@@ -387,7 +387,9 @@ class Stage1Engine:
         f32 scratch matrix (cleared first) that is cast to bf16 afterwards."""
         M, K = x.shape
         tiles = -(-M // 256) * -(-out.shape[1] // 64)
-        if tiles * 2 > 74 or K < 1024:
+        waves = -(-tiles // 74)
+        # few tiles, or a badly filled last wave in front of a long contraction (88 tiles = 1.2 waves at B*S = 22 496)
+        if not (K >= 1024 and (tiles * 2 <= 74 or (K >= 4096 and tiles < 0.7 * waves * 74))):
             fn(x, w, out=out, alpha=alpha)
             return
         tmp = self.buf("lora_thin_f32", tuple(out.shape), F32)
