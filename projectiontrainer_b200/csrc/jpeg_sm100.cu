@@ -410,11 +410,13 @@ __constant__ uint8_t c_zigzag[64];
 
 struct BitReader {
     const uint32_t* p;     // next aligned word of the un-stuffed stream
+    const uint32_t* end;   // first word past the segment (+ slack): a corrupt stream reads zeros from there on
     uint64_t buf;          // left-aligned bit buffer
     int cnt;               // valid bits in buf
     __device__ __forceinline__ void refill() {          // after this, cnt >= 33
         if (cnt <= 32) {
-            const uint32_t w = __byte_perm(__ldg(p++), 0, 0x0123);      // big-endian bit order
+            const uint32_t w = p < end ? __byte_perm(__ldg(p), 0, 0x0123) : 0u;      // big-endian bit order
+            ++p;
             buf |= static_cast<uint64_t>(w) << (32 - cnt);
             cnt += 32;
         }
@@ -470,6 +472,7 @@ jpeg_huffman_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t 
     if (threadIdx.x != 0) return;
     BitReader br;
     br.p = reinterpret_cast<const uint32_t*>(blob + seg.byte_off);
+    br.end = br.p + (seg.byte_len + 3) / 4 + 2;
     br.buf = 0; br.cnt = 0;
     int pred[3] = {0, 0, 0};
     const int ncomp = im.ncomp;
@@ -532,12 +535,14 @@ jpeg_huffman_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t 
 //   E  running sums turn the DC differences of each component into DC values.
 struct SegCtx {
     const uint32_t* words;         // un-stuffed stream
+    const uint32_t* end;           // first word past it (+ slack)
     int bpm;                       // blocks per MCU
     int slot_comp[6], slot_h[6], slot_v[6];
 };
 
 __device__ __forceinline__ void seg_context(const JpegImg& im, const uint8_t* blob, const JpegSeg& seg, SegCtx& cx) {
     cx.words = reinterpret_cast<const uint32_t*>(blob + seg.byte_off);
+    cx.end = cx.words + (seg.byte_len + 3) / 4 + 2;
     cx.bpm = 0;
     for (int c = 0; c < im.ncomp; ++c)
         for (int v = 0; v < im.vs[c]; ++v)
@@ -545,14 +550,15 @@ __device__ __forceinline__ void seg_context(const JpegImg& im, const uint8_t* bl
 }
 
 struct PosReader {                 // BitReader that knows its bit position in the segment
-    const uint32_t* base; const uint32_t* p; uint64_t buf; int cnt;
-    __device__ __forceinline__ void seek(const uint32_t* b, int bit) {
-        base = b; p = b + (bit >> 5); buf = 0; cnt = 0;
+    const uint32_t* base; const uint32_t* p; const uint32_t* end; uint64_t buf; int cnt;
+    __device__ __forceinline__ void seek(const uint32_t* b, const uint32_t* e, int bit) {
+        base = b; end = e; p = b + (bit >> 5); buf = 0; cnt = 0;
         refill(); skip(bit & 31); refill();
     }
     __device__ __forceinline__ void refill() {
         if (cnt <= 32) {
-            const uint32_t w = __byte_perm(__ldg(p++), 0, 0x0123);
+            const uint32_t w = p < end ? __byte_perm(__ldg(p), 0, 0x0123) : 0u;     // past the segment: zeros
+            ++p;
             buf |= static_cast<uint64_t>(w) << (32 - cnt);
             cnt += 32;
         }
@@ -580,7 +586,7 @@ __device__ __forceinline__ void parse_sub(const SegCtx& cx, const HuffDev* sh, c
                                           int p, int st, int limit, int& p_end, int& st_end, int& nblk,
                                           const JpegImg* im, const JpegSeg* seg, uint8_t* ws, int blk) {
     PosReader br;
-    br.seek(cx.words, p);
+    br.seek(cx.words, cx.end, p);
     int slot = st >> 8, k = st & 0xFF, done = 0;
     int16_t* out = nullptr;
     [[maybe_unused]] auto locate = [&]() {

@@ -205,3 +205,28 @@ def test_gpu_decode_loader_feeds_the_step(cuda_dev, tmp_path):
     assert np.array_equal(px.cpu().numpy(), ref)
     _, l_px = run({"pixel_values": torch.from_numpy(ref), "token_ids": ids, "labels": lab})
     assert np.allclose(l_jpeg, l_px, rtol=1e-6)
+
+
+def test_jpeg_corrupt_entropy_data_does_not_fault(cuda_dev):
+    """A file whose entropy-coded bytes are damaged (bit flips, zeroed runs, a truncated tail padded to the old length)
+    still parses on the host; the device decode must stay inside its buffers — garbage pixels, no fault — and a clean
+    file decoded right after it is still bit-exact."""
+    from projectiontrainer_b200 import ops
+    rng = np.random.default_rng(21)
+    img = _images(400, 600, rng)[1]
+    good = [_encode(img, quality=92, subsampling=2), _encode(img[..., 0], quality=92), _encode(img, quality=80, restart_marker_rows=1)]
+    bad = []
+    for f in good:
+        b = bytearray(f)
+        sos = b.index(b"\xff\xda")
+        lo, hi = sos + 16, len(b) - 2
+        for pos in rng.integers(lo, hi, 200):
+            if b[pos] != 0xFF and b[pos - 1] != 0xFF:
+                b[pos] ^= 1 << int(rng.integers(0, 8))
+        b[lo + (hi - lo) // 2: lo + (hi - lo) // 2 + 3000] = bytes(3000)
+        bad.append(bytes(b))
+    out = ops.jpeg_decode(ops.jpeg_pack(bad + good), cuda_dev)
+    torch.cuda.synchronize()
+    for f, o in zip(good, out[3:]):
+        assert np.array_equal(o.cpu().numpy(), _pillow(f))
+    assert all(o.shape == (400, 600, 3) for o in out[:3])
