@@ -487,7 +487,7 @@ jpeg_huffman_kernel(const uint8_t* __restrict__ blob, int64_t imgs_off, int64_t 
                 for (int h = 0; h < hs; ++h) {
                     int16_t* blk = coef + (static_cast<int64_t>(my * vs + v) * bw + (mx * hs + h)) * 64;
                     br.refill();
-                    int s = huff_symbol(br, Hd);
+                    int s = min(huff_symbol(br, Hd), 16);          // (a damaged table may name any byte)
                     if (s) {
                         br.refill();
                         const int d = huff_extend(br.peek(s), s);
@@ -604,7 +604,7 @@ __device__ __forceinline__ void parse_sub(const SegCtx& cx, const HuffDev* sh, c
         const int c = cx.slot_comp[slot];
         br.refill();
         if (k == 0) {
-            const int s = huff_symbol_p(br, sh[sel_dc[c]]);
+            const int s = min(huff_symbol_p(br, sh[sel_dc[c]]), 16);   // (a damaged table may name any byte)
             if (s) {
                 br.refill();
                 const int d = huff_extend(br.peek(s), s);

@@ -112,3 +112,37 @@ def test_gpu_decode_dataset_items_and_collates(tmp_path):
     cb = vqa_collate_fn(vq, Tok())
     st = vqa_step_inputs(cb, 0, 4)
     assert st["jpeg"]["index"] == [0, 3] and st["images_u8"][1] is cb["images_u8"][1] and "pixel_values" not in st
+
+
+def test_host_parser_survives_damaged_files():
+    """Truncated and bit-flipped files (headers included) either parse or raise RuntimeError with a message: the parser
+    never reads outside the file and packing never writes outside the blob (a crash here would take a loader worker
+    down)."""
+    from projectiontrainer_b200 import ops
+    rng = np.random.default_rng(4)
+    img = rng.integers(0, 256, (64, 80, 3), dtype=np.uint8)
+    seeds = [_encode(img, quality=85, subsampling=2, restart_marker_blocks=3), _encode(img[..., 0], quality=60),
+             _encode(img, quality=95, subsampling=0, optimize=True)]
+    ok = err = 0
+    for it in range(1500):
+        b = bytearray(seeds[it % 3])
+        mode = it % 4
+        if mode == 0:
+            b = b[:int(rng.integers(2, len(b)))]
+        elif mode == 1:
+            for pos in rng.integers(0, min(len(b), 700), 6):
+                b[pos] = int(rng.integers(0, 256))
+        elif mode == 2:
+            pos = int(rng.integers(2, len(b) - 4))
+            b[pos:pos + 2] = b"\xff" + bytes([int(rng.integers(0xC0, 0xFF))])
+        else:
+            pos = int(rng.integers(2, len(b)))
+            b[pos:pos] = bytes(rng.integers(0, 256, int(rng.integers(1, 40)), dtype=np.uint8))
+        try:
+            p = ops.jpeg_pack([bytes(b)], pin=False)
+            assert p["blob"].numel() > 0 and p["rgb_offsets"][0] == 0
+            ok += 1
+        except RuntimeError as e:
+            assert "jpeg" in str(e)
+            err += 1
+    assert ok > 50 and err > 200, (ok, err)
