@@ -203,6 +203,12 @@ int pt_rmsnorm_fwd(const void* x, int x_dtype, const float* w, void* out_bf16, i
 int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, const float* x_in, float* x_out,
                             const float* w_next, void* next_bf16, int rows, int D, float eps,
                             void* stream);
+/* The same step behind a split-K GEMM (the decode step's o-projection and down-projection: 64 rows, where one
+ * CTA pair per 64 output columns would stream the whole contraction alone): y_acc f32 [rows, D] holds the sum of
+ * the GEMM slices' atomic adds; it is rounded to bf16 (what the GEMM's bf16 output would have been), used as y
+ * above, and CLEARED in the same pass — the caller zeroes it once, every later GEMM finds it empty.  D <= 4096. */
+int pt_rmsnorm_residual_fwd_acc(float* y_acc, const float* w_post, const float* x_in, float* x_out,
+                                const float* w_next, void* next_bf16, int rows, int D, float eps, void* stream);
 
 /* RMSNorm input gradient.  g: grad of the norm output; u: saved norm input (u_group_* remap);
  * dst bf16: dst = du;  dst f32: dst[remap(r)] = (add ? add[remap(r)] : 0) + du. */
@@ -248,6 +254,21 @@ int pt_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long
  * One pass over the key tiles with an online softmax; scores and probabilities never reach HBM. */
 int pt_attn_gemma_fwd(const void* q_rot, const void* k_rot, const void* qkv, const void* kvbits, float* lse,
                       void* O_bf16, int B, int S, int hq, int hkv, int hd, int window, float scale, void* stream);
+/* One cached decode step of the same attention in one launch (the per-token forward of `generate`,
+ * ref:Stage1/inference_stage1.py:170 -> HF:models/gemma3/modeling_gemma3.py:278-300,362-384 with a DynamicCache):
+ * per (sample, kv head): q/k RMSNorm + RoPE of this token's heads from the fused row qkv [B, (hq+2hkv)*hd]
+ * (as pt_qknorm_rope_fwd; table row pos[b] of cos_t / sin_t [table_rows, hd/2]), the cache append
+ * K[b, slot] = k_rot, V[b, slot] = v (K, V bf16 [B, Smax, hkv*hd]; slot = *slot, a device scalar so a captured graph
+ * serves every token), and out[b, head*hd ..] = softmax_k(scale * q_rot . K[b, k]) V[b, k] over the keys
+ * k in [window > 0 ? max(0, slot - window + 1) : 0, slot] with valid[b*Smax + k] != 0 (NULL = all valid).
+ * The keys are split over a cluster of nsplit CTAs (1, 2, 4, 8; <= 0: chosen from B * hkv) that merge through
+ * distributed shared memory.  hd in {16, 32, 64, 128, 256}, hq / hkv in {1, 2, 4, 8}
+ * (pt_decode_attn_supported); other geometries are rejected — the caller keeps the GEMM + softmax launches. */
+int pt_decode_attn_supported(int hq, int hkv, int hd);
+int pt_decode_attn(const void* qkv, const float* wq, const float* wk, const float* cos_t, const float* sin_t,
+                   int table_rows, const long long* pos, const long long* slot, const uint8_t* valid, void* K,
+                   void* V, void* out_bf16, int B, int Smax, int hq, int hkv, int hd, int window, float eps,
+                   float scale, int nsplit, void* stream);
 /* Fused backward of the same attention (autograd through HF:models/gemma3/modeling_gemma3.py:370-384, invoked at
  * ref:Stage1/projector_trainer.py:236-237), key/value stationary, P recomputed from q_rot, k_rot and lse:
  *   dV[b*S + k, kvh*hd ..] = sum_{heads of kvh} P^T dO          (bf16, row stride ld_dv elements)

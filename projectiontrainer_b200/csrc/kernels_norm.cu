@@ -179,8 +179,11 @@ rmsnorm_residual_fwd_kernel(const __nv_bfloat16* __restrict__ y, const float* __
 }
 
 // Block-per-row variant of the sandwich step (D <= 4096): every operand is read once, the row stays in registers.
+// TY = float: y is a split-K accumulator (f32 partial sums added up by the GEMM slices): it is rounded to bf16 as the
+// GEMM's own bf16 output would have been, and CLEARED after the read, ready for the next GEMM's slices.
+template <typename TY>
 __global__ void __launch_bounds__(512)
-rmsnorm_residual_fwd_row_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ w_post,
+rmsnorm_residual_fwd_row_kernel(TY* __restrict__ y, const float* __restrict__ w_post,
                                 const float* x_in, float* x_out, const float* __restrict__ w_next,
                                 __nv_bfloat16* __restrict__ nxt, int D, float eps) {
     __shared__ float red[16];
@@ -192,6 +195,12 @@ rmsnorm_residual_fwd_row_kernel(const __nv_bfloat16* __restrict__ y, const float
     float q = 0.f;
     if (on) {
         load8(y + base + i, v); load8(x_in + base + i, xi); load8(w_post + i, g);
+        if constexpr (sizeof(TY) == 4) {
+            const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            store8(y + base + i, z);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = round_bf16(v[j]);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) q += v[j] * v[j];
     }
@@ -402,7 +411,8 @@ extern "C" int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, 
     PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0, "pt_rmsnorm_residual_fwd: D must be a positive multiple of 8");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     if (D <= 4096)
-        rmsnorm_residual_fwd_row_kernel<<<rows, ((D / 8 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        rmsnorm_residual_fwd_row_kernel<const __nv_bfloat16><<<rows, ((D / 8 + 31) / 32) * 32, 0,
+                                                               static_cast<cudaStream_t>(stream)>>>(
             static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
             static_cast<__nv_bfloat16*>(next_bf16), D, eps);
     else
@@ -410,6 +420,19 @@ extern "C" int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, 
             static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
             static_cast<__nv_bfloat16*>(next_bf16), rows, D, eps);
     return check_launch("rmsnorm_residual_fwd");
+}
+
+extern "C" int pt_rmsnorm_residual_fwd_acc(float* y_acc, const float* w_post, const float* x_in, float* x_out,
+                                           const float* w_next, void* next_bf16, int rows, int D, float eps,
+                                           void* stream) {
+    PT_REQUIRE(y_acc && w_post && x_in && x_out, "pt_rmsnorm_residual_fwd_acc: null pointer");
+    PT_REQUIRE((w_next == nullptr) == (next_bf16 == nullptr), "pt_rmsnorm_residual_fwd_acc: w_next/next mismatch");
+    PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0 && D <= 4096,
+               "pt_rmsnorm_residual_fwd_acc: D must be a positive multiple of 8, at most 4096");
+    if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
+    rmsnorm_residual_fwd_row_kernel<float><<<rows, ((D / 8 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        y_acc, w_post, x_in, x_out, w_next, static_cast<__nv_bfloat16*>(next_bf16), D, eps);
+    return check_launch("rmsnorm_residual_fwd_acc");
 }
 
 extern "C" int pt_rmsnorm_bwd(const void* g, int g_dtype, const void* u, int u_dtype, const float* w,

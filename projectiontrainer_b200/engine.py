@@ -236,6 +236,15 @@ class Stage1Engine:
         # cross-entropy statistics (row max / sum exp partials) in the LM-head GEMM epilogue: the separate statistics
         # pass over the 2.1 GB of logits goes away
         self.fuse_ce_stats = self.lcfg.vocab >= 256 and os.environ.get("PT_STAGE1_FUSE_CE_STATS", "1") != "0"
+        # graphed decode step: q/k norm + RoPE, cache append and attention over the cache in one launch per layer
+        # (0: pt_qknorm_rope_fwd, two cache row copies, score GEMM, softmax, P V GEMM)
+        self.fuse_decode_attn = ops.decode_attn_supported(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
+            os.environ.get("PT_STAGE1_FUSE_DECODE_ATTN", "1") != "0"
+        # graphed decode step, sandwich-norm decoders: o- and down-projection as split-K GEMMs into an f32 accumulator
+        # that the following norm kernel rounds, consumes and clears (0: one CTA pair per 64 output columns streams
+        # the whole contraction)
+        self.decode_splitk = self.lcfg.sandwich_norm and self.lcfg.hidden <= 4096 and \
+            os.environ.get("PT_STAGE1_DECODE_SPLITK", "1") != "0"
         # attention backward on a CTA pair per 128 keys (0: the single-CTA kernel on 64-key tiles)
         self.attn_bwd_pair = ops.attn_gemma_bwd_pair_ok(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_ATTN_BWD_PAIR", "1") != "0"
@@ -1090,6 +1099,8 @@ class Stage1Engine:
         else:
             kc["g_pos"].fill_(S)
         kc["g_slot"].fill_(S)
+        if "d_yacc" in kc.get("g_ws", {}):          # the split-K accumulator is empty between uses; make sure of it
+            kc["g_ws"]["d_yacc"].zero_()            # after a step that did not finish
         x, _ = self._llm_stack(x0, keyvalid, B, S, save=False, cache=self.cache, pos_ids=pos_ids)
         return self._last_logits(x, B, S)
 
@@ -1121,6 +1132,9 @@ class Stage1Engine:
         if kc.get("g_tokens") is None or kc["g_tokens"].shape[0] != B:
             kc["g_tokens"] = torch.zeros(B, 1, dtype=torch.int64, device=self.device)
         kc["g_tokens"].copy_(tokens.to(self.device).view(B, 1), non_blocking=True)
+        variant = (self.fuse_decode_attn, self.decode_splitk)
+        if kc.get("g_variant") != variant:          # the captured graph belongs to one variant of the step
+            kc.update(g_variant=variant, g_graph=None, g_calls=0)
         kc["g_calls"] += 1
         if kc["g_calls"] == 1:                       # sizes the workspaces
             logits = self._decode_step_fixed()
@@ -1139,9 +1153,11 @@ class Stage1Engine:
 
     def _decode_step_fixed(self) -> torch.Tensor:
         """The decode step with position-independent shapes: the new key / value go to cache slot g_slot (device
-        scalar), scores and P V run over all Smax slots with the slots beyond g_slot (and, in sliding layers, before
-        g_slot - window + 1, and prompt pads) masked in the softmax; RoPE rows are gathered by the per-sample
-        positions g_pos.  Ends by advancing g_slot / g_pos, so a captured graph serves every step."""
+        scalar) and attention sees the slots up to g_slot (in sliding layers from g_slot - window + 1) that are not
+        prompt pads; RoPE uses the per-sample positions g_pos.  Per layer the attention is ONE launch
+        (pt_decode_attn: norm + RoPE, cache append, flash-decoding over a CTA cluster), or, for geometries it does not
+        take, six (scores and P V over all Smax slots, masked in the softmax).  Ends by advancing g_slot / g_pos, so
+        a captured graph serves every step."""
         c, Lm, kc = self.lcfg, self.llm, self.cache
         B, Smax = kc["B"], kc["Smax"]
         h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
@@ -1162,41 +1178,48 @@ class Stage1Engine:
                          dbuf("d_kv", (B, 1), torch.uint8), dbuf("d_tgt", (B, 1), torch.int32))
         a = dbuf("d_a", (B, h), BF16)
         qkv = dbuf("d_qkv", (B, QKV), BF16)
-        q_post = dbuf("d_q", (B, hq * hd), BF16)
-        k_post = dbuf("d_k", (B, kvd), BF16)
-        ld = _pad8(Smax)
-        sc = dbuf("d_sc", (B * hq, ld), F32)
-        P = dbuf("d_P", (B * hq, ld), BF16)
         attn_o = dbuf("d_o", (B, hq * hd), BF16)
         y = dbuf("d_y", (B, h), BF16)
         x1 = dbuf("d_x1", (B, h), F32)
         gu = dbuf("d_gu", (B, 2 * ff), BF16)
         act = dbuf("d_act", (B, ff), BF16)
-        # key masks of this step (index plumbing on [B, Smax] bytes): causal, prompt pads, sliding window
-        m_full = ((ar <= slot) & kc["g_valid"].bool()).to(torch.uint8)
-        m_slide = (m_full.bool() & (ar > slot - c.window)).to(torch.uint8) if c.window > 0 else m_full
+        fused = self.fuse_decode_attn
+        splitk = self.decode_splitk
+        if splitk and "d_yacc" not in ws:
+            ws["d_yacc"] = torch.zeros((B, h), dtype=F32, device=self.device)   # empty between uses, see the kernel
+        yacc = ws.get("d_yacc")
         tabs = {}
-        for f in (True, False):
-            cos_t, sin_t = self.rope(Smax, f)
-            tabs[f] = (cos_t.index_select(0, posv), sin_t.index_select(0, posv))
+        if fused:       # the kernel reads the table row g_pos[b] and masks from g_slot / g_valid itself
+            for f in (True, False):
+                tabs[f] = self.rope(Smax, f)
+        else:
+            q_post = dbuf("d_q", (B, hq * hd), BF16)
+            k_post = dbuf("d_k", (B, kvd), BF16)
+            ld = _pad8(Smax)
+            sc = dbuf("d_sc", (B * hq, ld), F32)
+            P = dbuf("d_P", (B * hq, ld), BF16)
+            # key masks of this step (index plumbing on [B, Smax] bytes): causal, prompt pads, sliding window
+            m_full = ((ar <= slot) & kc["g_valid"].bool()).to(torch.uint8)
+            m_slide = (m_full.bool() & (ar > slot - c.window)).to(torch.uint8) if c.window > 0 else m_full
+            for f in (True, False):
+                cos_t, sin_t = self.rope(Smax, f)
+                tabs[f] = (cos_t.index_select(0, posv), sin_t.index_select(0, posv))
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
         for li, L in enumerate(Lm.layers):
             full = c.is_full(li)
             ops.linear(a, L["qkv_w"], out=qkv)
-            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], tabs[full][0], tabs[full][1], q_post, k_post, B, hq,
-                                hkv, hd, c.eps)
             K, V = kc["k"][li], kc["v"][li]
-            K.index_copy_(1, slot, k_post.view(B, 1, kvd))
-            V.index_copy_(1, slot, qkv[:, (hq + hkv) * hd:].reshape(B, 1, kvd))
-            ops.gemm_raw(M=G, N=Smax, K=hd, A=q_post, lda=hd, B=K, ldb=kvd, Cout=sc, ldc=ld,
-                         nz=(hkv, B, 1), a_zs=(G * hd, hq * hd, 0), b_zs=(hd, Smax * kvd, 0),
-                         c_zs=(G * ld, hq * ld, 0), alpha=scale)
-            ops.softmax_fwd(sc, P, m_full if full else m_slide, B * hq, 1, Smax, ld, hq, 0, 0)
-            ops.gemm_raw(M=G, N=hd, K=Smax, A=P, lda=ld, B=V, ldb=kvd, b_mn=True, Cout=attn_o, ldc=hd,
-                         nz=(hkv, B, 1), a_zs=(G * ld, hq * ld, 0), b_zs=(hd, Smax * kvd, 0),
-                         c_zs=(G * hd, hq * hd, 0))
+            if fused:
+                ops.decode_attn(qkv, L["q_norm"], L["k_norm"], tabs[full][0], tabs[full][1], posv, slot,
+                                kc["g_valid"], K, V, attn_o, hq, hkv, hd, 0 if full else c.window, c.eps, scale)
+            else:
+                self._decode_attn_unfused(qkv, L, tabs[full], q_post, k_post, K, V, slot, sc, P,
+                                          m_full if full else m_slide, attn_o, B, Smax, ld, scale)
             last = li == len(Lm.layers) - 1
-            if c.sandwich_norm:
+            if splitk:
+                ops.linear(attn_o, L["o_w"], out=yacc, ksplit=-1)
+                ops.rmsnorm_residual_fwd_acc(yacc, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
+            elif c.sandwich_norm:
                 ops.linear(attn_o, L["o_w"], out=y)
                 ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
             else:
@@ -1207,7 +1230,12 @@ class Stage1Engine:
             else:
                 ops.linear(a, L["gu_w"], out=gu)
                 ops.geglu_fwd(gu, act, silu=c.silu)
-            if c.sandwich_norm:
+            if splitk:
+                ops.linear(act, L["down_w"], out=yacc, ksplit=-1)
+                ops.rmsnorm_residual_fwd_acc(yacc, L["post_ffn_norm"], x1, x,
+                                             None if last else Lm.layers[li + 1]["in_norm"],
+                                             None if last else a, c.eps)
+            elif c.sandwich_norm:
                 ops.linear(act, L["down_w"], out=y)
                 ops.rmsnorm_residual_fwd(y, L["post_ffn_norm"], x1, x,
                                          None if last else Lm.layers[li + 1]["in_norm"],
@@ -1220,6 +1248,23 @@ class Stage1Engine:
         slot.add_(1)
         posv.add_(1)
         return logits
+
+    def _decode_attn_unfused(self, qkv, L, tab, q_post, k_post, K, V, slot, sc, P, mask, attn_o, B, Smax, ld, scale):
+        """The decode attention as six launches (geometries pt_decode_attn does not take, and the A/B of it):
+        scores and P V run over all Smax slots, `mask` zeroes what the step may not see."""
+        c = self.lcfg
+        hd, hq, hkv = c.hd, c.hq, c.hkv
+        G, kvd = hq // hkv, hkv * hd
+        ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], tab[0], tab[1], q_post, k_post, B, hq, hkv, hd, c.eps)
+        K.index_copy_(1, slot, k_post.view(B, 1, kvd))
+        V.index_copy_(1, slot, qkv[:, (hq + hkv) * hd:].reshape(B, 1, kvd))
+        ops.gemm_raw(M=G, N=Smax, K=hd, A=q_post, lda=hd, B=K, ldb=kvd, Cout=sc, ldc=ld,
+                     nz=(hkv, B, 1), a_zs=(G * hd, hq * hd, 0), b_zs=(hd, Smax * kvd, 0),
+                     c_zs=(G * ld, hq * ld, 0), alpha=scale)
+        ops.softmax_fwd(sc, P, mask, B * hq, 1, Smax, ld, hq, 0, 0)
+        ops.gemm_raw(M=G, N=hd, K=Smax, A=P, lda=ld, B=V, ldb=kvd, b_mn=True, Cout=attn_o, ldc=hd,
+                     nz=(hkv, B, 1), a_zs=(G * ld, hq * ld, 0), b_zs=(hd, Smax * kvd, 0),
+                     c_zs=(G * hd, hq * hd, 0))
 
     def _decode_step_eager(self, tokens: torch.Tensor) -> torch.Tensor:
         c, Lm, kc = self.lcfg, self.llm, self.cache

@@ -267,6 +267,16 @@ def rmsnorm_residual_fwd(y, w_post, x_in, x_out, w_next, nxt, eps):
               _ptr(w_next), _ptr(nxt), y.shape[0], y.shape[1], _f(eps), _stream())
 
 
+def rmsnorm_residual_fwd_acc(y_acc, w_post, x_in, x_out, w_next, nxt, eps):
+    """rmsnorm_residual_fwd behind a split-K GEMM: y_acc f32 [rows, D] (the slices' atomic sums) is rounded to bf16,
+    used, and cleared for the next GEMM in the same pass."""
+    _req_cuda(y_acc, x_in, x_out)
+    if y_acc.dtype != torch.float32 or not y_acc.is_contiguous():
+        raise RuntimeError("rmsnorm_residual_fwd_acc: y_acc must be contiguous float32")
+    _lib.call("pt_rmsnorm_residual_fwd_acc", _ptr(y_acc), _ptr(w_post), _ptr(x_in), _ptr(x_out),
+              _ptr(w_next), _ptr(nxt), y_acc.shape[0], y_acc.shape[1], _f(eps), _stream())
+
+
 def rmsnorm_bwd(g, u, w, dst, eps, *, add=None, rows=None, u_group=(0, 0, 0), dst_group=(0, 0, 0)):
     _req_cuda(g, u, dst)
     rows = g.shape[0] if rows is None else rows
@@ -303,6 +313,23 @@ def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, win
     _req_cuda(scores, P, keyvalid)
     _lib.call("pt_softmax_fwd", _ptr(scores), _ptr(P), _ptr(keyvalid), int(Z), int(Sq), int(Sk),
               int(ld), int(heads_per_batch), int(causal), int(window), _stream())
+
+
+def decode_attn_supported(hq: int, hkv: int, hd: int) -> bool:
+    return bool(_lib.lib().pt_decode_attn_supported(int(hq), int(hkv), int(hd)))
+
+
+def decode_attn(qkv, wq, wk, cos_t, sin_t, pos, slot, valid, K, V, out, hq, hkv, hd, window, eps, scale, nsplit=0):
+    """One cached decode step of attention in one launch: q/k norm + RoPE of this token (table row pos[b]), the
+    cache append at *slot, attention over the visible cache slots.  qkv bf16 [B, (hq+2hkv)*hd]; K, V bf16
+    [B, Smax, hkv*hd]; pos i64 [B]; slot i64 [1]; valid u8 [B, Smax] or None; out bf16 [B, hq*hd]."""
+    _req_cuda(qkv, K, V, out, pos, slot, valid, cos_t, sin_t)
+    B, Smax = K.shape[0], K.shape[1]
+    if pos.dtype != torch.int64 or slot.dtype != torch.int64 or (valid is not None and valid.dtype != torch.uint8):
+        raise RuntimeError("decode_attn: pos / slot must be int64, valid uint8")
+    _lib.call("pt_decode_attn", _ptr(qkv), _ptr(wq), _ptr(wk), _ptr(cos_t), _ptr(sin_t), int(cos_t.shape[0]),
+              _ptr(pos), _ptr(slot), _ptr(valid), _ptr(K), _ptr(V), _ptr(out), int(B), int(Smax), int(hq), int(hkv),
+              int(hd), int(window), _f(eps), _f(scale), int(nsplit), _stream())
 
 
 def softmax_bwd(P, dP, dS, rows, Sk, ld, scale, Sq=0, causal=0, window=0):

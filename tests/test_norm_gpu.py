@@ -96,6 +96,51 @@ def test_rmsnorm_residual_fwd(cuda_dev, rows, D, with_next):
         assert torch.isnan(nxt.float()).all()          # untouched
 
 
+@pytest.mark.parametrize("rows,D", [(64, 1152), (3, 128), (64, 2560), (8, 4096)])
+@pytest.mark.parametrize("with_next", [True, False])
+def test_rmsnorm_residual_fwd_acc_equals_the_bf16_input_kernel_and_clears(cuda_dev, rows, D, with_next):
+    """The split-K accumulator variant: y_acc (f32 sums of the GEMM slices) is rounded to bf16, used exactly as
+    pt_rmsnorm_residual_fwd uses a bf16 y (bit-equal outputs), and left zeroed; and through a split-K GEMM it
+    reproduces GEMM -> bf16 y -> norm up to the summation order of the slices."""
+    from projectiontrainer_b200 import ops
+    torch.manual_seed(rows + D)
+    y_acc = torch.randn(rows, D, device=cuda_dev)
+    x_in = torch.randn(rows, D, device=cuda_dev) * 4
+    wp, wn = torch.randn(D, device=cuda_dev) * 0.3, torch.randn(D, device=cuda_dev) * 0.3
+    outs = []
+    for acc in (False, True):
+        x_out = torch.full((rows, D), float("nan"), device=cuda_dev)
+        nxt = torch.full((rows, D), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+        if acc:
+            y = y_acc.clone()
+            ops.rmsnorm_residual_fwd_acc(y, wp, x_in, x_out, wn if with_next else None, nxt if with_next else None, 1e-6)
+            assert int(torch.count_nonzero(y)) == 0
+        else:
+            ops.rmsnorm_residual_fwd(y_acc.bfloat16(), wp, x_in, x_out, wn if with_next else None,
+                                     nxt if with_next else None, 1e-6)
+        outs.append((x_out, nxt))
+    assert torch.equal(outs[0][0], outs[1][0])
+    if with_next:
+        assert torch.equal(outs[0][1], outs[1][1])
+    # behind a split-K GEMM, twice in a row on the same accumulator (the second finds it cleared)
+    K = 1024
+    a = torch.randn(rows, K, device=cuda_dev).bfloat16()
+    w = (torch.randn(D, K, device=cuda_dev) * K ** -0.5).bfloat16()
+    y_ref = ops.linear(a, w)
+    x_ref = torch.empty(rows, D, device=cuda_dev)
+    ops.rmsnorm_residual_fwd(y_ref, wp, x_in, x_ref, None, None, 1e-6)
+    acc = torch.zeros(rows, D, device=cuda_dev)
+    for _ in range(2):
+        ops.linear(a, w, out=acc, ksplit=-1)
+        x_out = torch.empty(rows, D, device=cuda_dev)
+        ops.rmsnorm_residual_fwd_acc(acc, wp, x_in, x_out, None, None, 1e-6)
+        branch = (x_ref - x_in).abs().max().item()
+        assert (x_out - x_ref).abs().max().item() <= 2.0 ** -7 * branch
+    with pytest.raises(RuntimeError, match="4096"):
+        big = torch.zeros(2, 4104, device=cuda_dev)
+        ops.rmsnorm_residual_fwd_acc(big, torch.zeros(4104, device=cuda_dev), big.clone(), big.clone(), None, None, 1e-6)
+
+
 def _rms_bwd_ref(g, u, w, eps):
     u = u.float().clone().requires_grad_(True)
     _rms(u, w, eps).backward(g.float())
