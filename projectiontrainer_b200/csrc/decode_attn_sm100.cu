@@ -13,8 +13,10 @@
 // per-key reads below are bank-conflict free), then
 //   scores: warp w takes keys 8w..8w+7 of the tile: S[G x 8] = Q[G x HD] K^T on mma.sync m16n8k16 (the G <= 8 query
 //           heads of the group are rows 0..G-1 of the 16-row A operand, kept in registers for the whole launch);
-//   softmax: warp g updates head g's running (max, sum) over the tile and turns the scores into bf16 probabilities;
-//   P V:    warp w takes channel blocks of 8: O[G x 8] += P[G x 64] V[64 x 8], V fragments by ldmatrix.trans.
+//   softmax + P V: every warp turns the scores of its lanes' query head into the A fragments of the P V product in
+//           registers (a quad of lanes holds the 32 scores of a head: two shuffle steps give the tile maximum and
+//           sum; every warp keeps the same running (max, sum)), then takes channel blocks of 8:
+//           O[G x 8] += P[G x 32] V[32 x 8], V fragments by ldmatrix.trans.  Two block barriers per tile.
 // (tcgen05 does not fit here: its M is 64+ rows and a decode step has G = 1..8 per K/V row — the kernel is bound by
 // the K/V bytes, the tensor cores only have to keep the arithmetic out of the way, which mma.sync does.)
 // The CTAs of the cluster merge their (max, sum, o) through distributed shared memory into rank 0, which writes
@@ -33,7 +35,7 @@ namespace pt {
 constexpr int kDecThreads = 256;
 constexpr int kDecWarps = kDecThreads / 32;
 constexpr int kDecTile = 32;                            // keys per shared-memory tile
-constexpr int kDecStages = 3;                           // tiles in flight per CTA (cp.async ring)
+constexpr int kDecStages = 2;                           // tiles in flight per CTA (cp.async ring)
 
 template <int EPL>
 __device__ __forceinline__ void ld_row(const __nv_bfloat16* p, float (&v)[EPL]) {
@@ -68,27 +70,32 @@ struct DecodeAttnArgs {
     __nv_bfloat16 *K, *V;           // [B, Smax, hkv * HD]
     __nv_bfloat16* out;             // [B, hq * HD]
     int B, Smax, hq, hkv, window, table_rows;
+    int vm_bytes;                   // shared-memory bytes for the key-visibility table (0: read `valid` per tile)
     float eps, scale;
 };
 
 // shared-memory carve-up (bytes), the same on the host (size) and the device (offsets)
 template <int HD, int G>
 struct DecSmem {
-    static constexpr int KROW = HD + 8;                                     // bf16 per staged K / V row (16-byte pad:
-                                                                            // fragment loads hit 32 distinct banks)
-    static constexpr int PROW = kDecTile + 8;                               // bf16 per probability row
+    // bf16 per staged row.  HD >= 64: rows are unpadded and their 16-byte chunks XOR-swizzled — K: chunk ^ 4 (row & 1)
+    // (a quarter-warp reads 4 chunks of an even and an odd row: disjoint banks), V: chunk ^ (row & 7) (ldmatrix reads
+    // one chunk column of 8 rows).  Below 64 (tests only): 16-byte pad, 4-byte fragment reads.
+    static constexpr int KROW = HD >= 64 ? HD : HD + 8;
+    static constexpr int VROW = HD >= 64 ? HD : HD + 8;
+    static constexpr int SROW = kDecTile + 8;                               // f32 per score row (bank spread)
+    static constexpr int kstage = kDecTile * KROW * 2;
+    static constexpr int vstage = kDecTile * VROW * 2;
     static constexpr int oK = 0;
-    static constexpr int stage = kDecTile * KROW * 2;                       // one K (or V) tile
-    static constexpr int oV = oK + kDecStages * stage;
-    static constexpr int oQ = oV + kDecStages * stage;                      // bf16 [G][HD]
+    static constexpr int oV = oK + kDecStages * kstage;
+    static constexpr int oQ = oV + kDecStages * vstage;                     // bf16 [G][HD]
     static constexpr int oKnew = oQ + G * HD * 2;                           // bf16 [HD]
     static constexpr int oVnew = oKnew + HD * 2;                            // bf16 [HD]
-    static constexpr int oSc = oVnew + HD * 2;                              // f32 [G][tile]: scores
-    static constexpr int oP = oSc + G * kDecTile * 4;                       // bf16 [G][PROW]: probabilities
-    static constexpr int oCorr = oP + G * PROW * 2;                         // f32 [G]
-    static constexpr int oRml = oCorr + 16 * 4;                             // f32 [G][2]  merged (max, sum)
-    static constexpr int oRo = oRml + 16 * 4;                               // f32 [G][HD] merged o
-    static constexpr int bytes = oRo + G * HD * 4;
+    static constexpr int oSc = oVnew + HD * 2;                              // f32 [2][G][SROW]: score partials
+    static constexpr int oVm = oSc + 2 * G * SROW * 4;                      // u8 [vm_bytes]: key visibility, this CTA's tiles
+    // after the key-visibility bytes (vm_bytes, a multiple of 16, chosen by the host):
+    static constexpr int rml = 16 * 4;                                      // f32 [G][2]  merged (max, sum)
+    static constexpr int ro = G * HD * 4;                                   // f32 [G][HD] merged o
+    static constexpr int fixed = oVm + rml + ro;
 };
 
 // D += A B for one m16n8k16 bf16 tile (A row-major 16x16, B "col": 16x8 given as [n][k] rows), f32 accumulate
@@ -104,6 +111,11 @@ __device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& b0, uint32_t& b1, co
     const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(smem_row));
     asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(a));
 }
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 template <int HD, int G>
 __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAttnArgs p) {
@@ -111,11 +123,15 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
     constexpr int EPL = HD >= 64 ? HD / 32 : 2;         // norm + RoPE: channels per lane
     constexpr int LA = HD / EPL;                        // lanes that hold channels (32 from HD = 64 up)
     constexpr int HALF = HD / 2;
-    constexpr int T = kDecTile, KROW = L::KROW;
-    constexpr int PROW = L::PROW;
+    constexpr int T = kDecTile, KROW = L::KROW, VROW = L::VROW, SROW = L::SROW;
     constexpr int CH = HD / 8;                          // 16-byte chunks per row
+    constexpr bool kWide = HD >= 64;                    // scores: 16-byte fragments, k-steps split over warp pairs
+    constexpr int RSTEP = kDecThreads / CH;             // rows between a thread's chunks of a tile
+    constexpr int NJ = (T + RSTEP - 1) / RSTEP;         // chunks per thread per tile (per operand)
     constexpr int KS = HD / 16;                         // k-steps of the score MMAs
+    constexpr int NPW = kWide ? HD / 64 : 0;            // pairs of k-steps per warp (wide path)
     constexpr int NTW = HD >= 64 ? HD / 64 : 1;         // 8-channel blocks of O per warp (block = warp + 8 t)
+    static_assert(T == 32, "a quad of lanes holds the 32 scores of a head");
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw + L::oK);
     __nv_bfloat16* Vs = reinterpret_cast<__nv_bfloat16*>(smem_raw + L::oV);
@@ -123,10 +139,9 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
     __nv_bfloat16* knew = reinterpret_cast<__nv_bfloat16*>(smem_raw + L::oKnew);
     __nv_bfloat16* vnew = reinterpret_cast<__nv_bfloat16*>(smem_raw + L::oVnew);
     float* sc = reinterpret_cast<float*>(smem_raw + L::oSc);
-    __nv_bfloat16* Pb = reinterpret_cast<__nv_bfloat16*>(smem_raw + L::oP);
-    float* corr_s = reinterpret_cast<float*>(smem_raw + L::oCorr);
-    float* r_ml = reinterpret_cast<float*>(smem_raw + L::oRml);
-    float* r_o = reinterpret_cast<float*>(smem_raw + L::oRo);
+    uint8_t* vm = smem_raw + L::oVm;
+    float* r_ml = reinterpret_cast<float*>(smem_raw + L::oVm + p.vm_bytes);
+    float* r_o = r_ml + 16;
 
     cg::cluster_group cluster = cg::this_cluster();
     const int nsplit = static_cast<int>(cluster.num_blocks()), rank = static_cast<int>(cluster.block_rank());
@@ -139,6 +154,71 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
     trow = trow < 0 ? 0 : (trow >= p.table_rows ? p.table_rows - 1 : trow);
     const int kvd = p.hkv * HD;
     const __nv_bfloat16* row = p.qkv + static_cast<long long>(b) * (p.hq + 2 * p.hkv) * HD;
+
+    // keys lo .. slot: cache rows, except `slot` itself = this token (staged from knew / vnew, appended to the cache)
+    const int lo = p.window > 0 ? max(0, slot - p.window + 1) : 0;
+    const int nkeys = slot - lo + 1;
+    const int ntiles = (nkeys + T - 1) / T;
+    const uint8_t* vb = p.valid ? p.valid + static_cast<long long>(b) * p.Smax : nullptr;
+    const bool vm_on = p.vm_bytes > 0;
+
+    auto kchunk = [](int r, int ci) { return kWide ? ci ^ ((r & 1) << 2) : ci; };
+    auto vchunk = [](int r, int ci) { return kWide ? ci ^ (r & 7) : ci; };
+    static_assert(!kWide || RSTEP % 8 == 0, "a thread's rows of a tile share their swizzle");
+    // ---- staging.  A thread copies the 16-byte chunk `sci` of rows sr0, sr0 + RSTEP, ... of a tile.
+    const int sr0 = tid / CH, sci = tid - sr0 * CH;
+    const long long cbase = (static_cast<long long>(b) * p.Smax) * kvd + kvh * HD;
+    const long long gofs0 = cbase + static_cast<long long>(lo + sr0) * kvd + sci * 8;
+    // the cache rows of a tile (every row of every tile but the last one)
+    auto stage_rows = [&](int tile, int st) {
+        if (tile < ntiles) {
+            __nv_bfloat16* Kd = Ks + st * (T * KROW) + sr0 * KROW + kchunk(sr0, sci) * 8;   // rows sr0 + j RSTEP: the
+            __nv_bfloat16* Vd = Vs + st * (T * VROW) + sr0 * VROW + vchunk(sr0, sci) * 8;   // same swizzle (RSTEP % 8 == 0)
+            const long long g0 = gofs0 + static_cast<long long>(tile) * T * kvd;
+            const int nrow = min(T, slot - (lo + tile * T));            // rows before `slot`
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                if (sr0 + j * RSTEP < nrow) {
+                    cp_async16(Kd + j * RSTEP * KROW, p.K + g0 + static_cast<long long>(j) * RSTEP * kvd);
+                    cp_async16(Vd + j * RSTEP * VROW, p.V + g0 + static_cast<long long>(j) * RSTEP * kvd);
+                }
+            }
+        }
+        cp_async_commit();                               // one group per call, empty or not: the wait counts groups
+    };
+    // the last tile: row `slot` = this token (also appended to the cache), the rows past it zeroed (P is 0 there
+    // and V must not hold NaN bits)
+    auto patch_rows = [&](int tile, int st) {
+        if (tile == ntiles - 1) {
+            const int k0 = lo + tile * T;
+            for (int c = tid; c < T * CH; c += kDecThreads) {
+                const int r = c / CH, ci = c - r * CH;
+                const int key = k0 + r;
+                if (key < slot) continue;
+                uint4 kk = make_uint4(0u, 0u, 0u, 0u), vv = kk;
+                if (key == slot) {
+                    kk = reinterpret_cast<const uint4*>(knew)[ci];
+                    vv = reinterpret_cast<const uint4*>(vnew)[ci];
+                    const long long off = cbase + static_cast<long long>(key) * kvd + ci * 8;
+                    *reinterpret_cast<uint4*>(p.K + off) = kk;
+                    *reinterpret_cast<uint4*>(p.V + off) = vv;
+                }
+                *reinterpret_cast<uint4*>(Ks + st * (T * KROW) + r * KROW + kchunk(r, ci) * 8) = kk;
+                *reinterpret_cast<uint4*>(Vs + st * (T * VROW) + r * VROW + vchunk(r, ci) * 8) = vv;
+            }
+        }
+    };
+    // the first tiles are on their way while this token's heads are normalised
+#pragma unroll
+    for (int s = 0; s < kDecStages - 1; ++s) stage_rows(rank + s * nsplit, s);
+
+    if (vm_on) {    // visibility of this CTA's keys, local tile by local tile
+        const int nloc = ntiles > rank ? (ntiles - rank + nsplit - 1) / nsplit : 0;
+        for (int i = tid; i < nloc * T && i < p.vm_bytes; i += kDecThreads) {
+            const int key = lo + (rank + (i / T) * nsplit) * T + (i % T);
+            vm[i] = key <= slot && (vb == nullptr || vb[key] != 0);
+        }
+    }
 
     // ---- this token: q heads of the group (bf16 like pt_qknorm_rope_fwd's q_out), k, v
     {
@@ -172,9 +252,7 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
                 const float n = on ? a[j] * rstd * (1.f + w[lane * EPL + j]) : 0.f;
                 const float o = __shfl_xor_sync(0xffffffffu, n, LA / 2);
                 const float y = n * cc[j] + o * ss[j];
-                if (on) {
-                    (isq ? qs + h * HD : knew)[lane * EPL + j] = __float2bfloat16_rn(y);
-                }
+                if (on) (isq ? qs + h * HD : knew)[lane * EPL + j] = __float2bfloat16_rn(y);
             }
         }
         if (tid < CH)
@@ -182,113 +260,136 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
                 __ldg(reinterpret_cast<const uint4*>(row + (p.hq + p.hkv + kvh) * HD) + tid);
     }
     __syncthreads();
-
-    // keys lo .. slot: cache rows, except `slot` itself = this token (staged from knew / vnew, appended to the cache)
-    const int lo = p.window > 0 ? max(0, slot - p.window + 1) : 0;
-    const int nkeys = slot - lo + 1;
-    const int ntiles = (nkeys + T - 1) / T;
-    const long long cbase = (static_cast<long long>(b) * p.Smax) * kvd + kvh * HD;
-    const uint8_t* vb = p.valid ? p.valid + static_cast<long long>(b) * p.Smax : nullptr;
-    const int fr = lane >> 2, fk = (lane & 3) * 2;      // fragment row (query head / key) and column pair
-    uint32_t qa[KS][2];                                  // A fragments of Q: rows >= G (and 8..15) are zero
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-        qa[ks][0] = fr < G ? *reinterpret_cast<const uint32_t*>(qs + fr * HD + ks * 16 + fk) : 0u;
-        qa[ks][1] = fr < G ? *reinterpret_cast<const uint32_t*>(qs + fr * HD + ks * 16 + 8 + fk) : 0u;
+    for (int s = 0; s < kDecStages - 1; ++s) patch_rows(rank + s * nsplit, s);
+
+    const int fr = lane >> 2, fk = (lane & 3) * 2;      // fragment row (query head / key) and column pair
+    // A fragments of Q (rows >= G and 8..15 are zero).  Wide path: warp w scores keys 8 (w & 3) .. + 7 over the
+    // k-step pairs NPW (w >> 2) .. + NPW - 1; the contraction index is permuted inside each pair so that a lane's two
+    // fragments of two k-steps are 16 contiguous bytes (the same permutation on Q and K leaves the sum unchanged).
+    const int nt_qk = warp & 3, kh = warp >> 2;
+    uint4 qw[kWide ? NPW : 1];
+    uint32_t qa[kWide ? 1 : KS][2];
+    if constexpr (kWide) {
+#pragma unroll
+        for (int g = 0; g < NPW; ++g)
+            qw[g] = fr < G ? *reinterpret_cast<const uint4*>(qs + fr * HD + (kh * NPW + g) * 32 + (lane & 3) * 8)
+                           : make_uint4(0u, 0u, 0u, 0u);
+    } else {
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+            qa[ks][0] = fr < G ? *reinterpret_cast<const uint32_t*>(qs + fr * HD + ks * 16 + fk) : 0u;
+            qa[ks][1] = fr < G ? *reinterpret_cast<const uint32_t*>(qs + fr * HD + ks * 16 + 8 + fk) : 0u;
+        }
     }
     float acc[NTW][4];
 #pragma unroll
     for (int t = 0; t < NTW; ++t) { acc[t][0] = 0.f; acc[t][1] = 0.f; acc[t][2] = 0.f; acc[t][3] = 0.f; }
-    float m_run = -INFINITY, l_run = 0.f;               // head `warp`'s running state (warps < G)
-
-    // stage one tile (cache rows by cp.async; `slot` = this token, also appended to the cache; rows past it zeroed:
-    // P is 0 there and V must not hold NaN bits)
-    auto stage_tile = [&](int tile, int st) {
-        if (tile < ntiles) {
-            __nv_bfloat16* Kd = Ks + st * (T * KROW);
-            __nv_bfloat16* Vd = Vs + st * (T * KROW);
-            const int k0 = lo + tile * T;
-            for (int c = tid; c < T * CH; c += kDecThreads) {
-                const int r = c / CH, ci = c - r * CH;
-                const int key = k0 + r;
-                const long long off = cbase + static_cast<long long>(key) * kvd + ci * 8;
-                if (key < slot) {
-                    cp_async16(Kd + r * KROW + ci * 8, p.K + off);
-                    cp_async16(Vd + r * KROW + ci * 8, p.V + off);
-                } else if (key == slot) {
-                    const uint4 kk = reinterpret_cast<const uint4*>(knew)[ci], vv = reinterpret_cast<const uint4*>(vnew)[ci];
-                    *reinterpret_cast<uint4*>(Kd + r * KROW + ci * 8) = kk;
-                    *reinterpret_cast<uint4*>(Vd + r * KROW + ci * 8) = vv;
-                    *reinterpret_cast<uint4*>(p.K + off) = kk;
-                    *reinterpret_cast<uint4*>(p.V + off) = vv;
-                } else {
-                    *reinterpret_cast<uint4*>(Kd + r * KROW + ci * 8) = make_uint4(0u, 0u, 0u, 0u);
-                    *reinterpret_cast<uint4*>(Vd + r * KROW + ci * 8) = make_uint4(0u, 0u, 0u, 0u);
-                }
-            }
-        }
-        cp_async_commit();                               // one group per call, empty or not: the wait counts groups
-    };
-#pragma unroll
-    for (int s = 0; s < kDecStages - 1; ++s) stage_tile(rank + s * nsplit, s);
+    float m_run = -INFINITY, l_run = 0.f;               // running state of head `fr`, log2 domain (every warp the same)
+    const float sl2 = p.scale * 1.4426950408889634f;
 
     int it = 0;
     for (int tile = rank; tile < ntiles; tile += nsplit, ++it) {
-        const int k0 = lo + tile * T;
-        const int tn = min(T, nkeys - tile * T);
-        const __nv_bfloat16* Kt = Ks + (it % kDecStages) * (T * KROW);
-        const __nv_bfloat16* Vt = Vs + (it % kDecStages) * (T * KROW);
+        const int st = it % kDecStages;
+        const __nv_bfloat16* Kt = Ks + st * (T * KROW);
+        const __nv_bfloat16* Vt = Vs + st * (T * VROW);
         cp_async_wait<kDecStages - 2>();                 // this tile has landed (the younger groups may be in flight)
         __syncthreads();                                 // ... for every thread; and the previous tile is consumed
-        stage_tile(tile + (kDecStages - 1) * nsplit, (it + kDecStages - 1) % kDecStages);
-        if (warp < T / 8) {   // scores of keys 8 warp .. 8 warp + 7
-            const int r0 = warp * 8 + fk;
-            bool ok0 = false, ok1 = false;
-            if (fr < G) {
-                ok0 = r0 < tn && (vb == nullptr || vb[k0 + r0] != 0);
-                ok1 = r0 + 1 < tn && (vb == nullptr || vb[k0 + r0 + 1] != 0);
-            }
-            const __nv_bfloat16* kr = Kt + (warp * 8 + fr) * KROW + fk;
-            float c[4] = {0.f, 0.f, 0.f, 0.f};
+        {
+            const int nxt = tile + (kDecStages - 1) * nsplit, nst = (it + kDecStages - 1) % kDecStages;
+            stage_rows(nxt, nst);
+            patch_rows(nxt, nst);
+        }
+        if (kWide || warp < T / 8) {   // score partials of keys 8 nt_qk .. + 7
+            const int r0 = nt_qk * 8 + fk;
+            float c0, c1;
+            if constexpr (kWide) {
+                const __nv_bfloat16* kr = Kt + (nt_qk * 8 + fr) * KROW;
+                float ca[4] = {0.f, 0.f, 0.f, 0.f}, cb[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int ks = 0; ks < KS; ++ks) {
-                const uint32_t b0 = *reinterpret_cast<const uint32_t*>(kr + ks * 16);
-                const uint32_t b1 = *reinterpret_cast<const uint32_t*>(kr + ks * 16 + 8);
-                mma16816(c, qa[ks][0], 0u, qa[ks][1], 0u, b0, b1);
+                for (int g = 0; g < NPW; ++g) {
+                    const uint4 kk =
+                        *reinterpret_cast<const uint4*>(kr + kchunk(fr, (kh * NPW + g) * 4 + (lane & 3)) * 8);
+                    mma16816(ca, qw[g].x, 0u, qw[g].y, 0u, kk.x, kk.y);
+                    mma16816(cb, qw[g].z, 0u, qw[g].w, 0u, kk.z, kk.w);
+                }
+                c0 = ca[0] + cb[0]; c1 = ca[1] + cb[1];
+            } else {
+                const __nv_bfloat16* kr = Kt + (nt_qk * 8 + fr) * KROW + fk;
+                float ca[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int ks = 0; ks < KS; ++ks)
+                    mma16816(ca, qa[ks][0], 0u, qa[ks][1], 0u, *reinterpret_cast<const uint32_t*>(kr + ks * 16),
+                             *reinterpret_cast<const uint32_t*>(kr + ks * 16 + 8));
+                c0 = ca[0]; c1 = ca[1];
             }
             if (fr < G) {
-                sc[fr * T + r0] = ok0 ? c[0] * p.scale : -INFINITY;
-                sc[fr * T + r0 + 1] = ok1 ? c[1] * p.scale : -INFINITY;
+                float2 o2 = make_float2(c0 * sl2, c1 * sl2);
+                if (!kWide || kh == 0) {                 // the mask rides on the first partial
+                    bool ok0, ok1;
+                    if (vm_on) {
+                        const uchar2 v2 = *reinterpret_cast<const uchar2*>(vm + it * T + r0);
+                        ok0 = v2.x != 0; ok1 = v2.y != 0;
+                    } else {
+                        const int k0 = lo + tile * T;
+                        ok0 = k0 + r0 <= slot && (vb == nullptr || vb[k0 + r0] != 0);
+                        ok1 = k0 + r0 + 1 <= slot && (vb == nullptr || vb[k0 + r0 + 1] != 0);
+                    }
+                    if (!ok0) o2.x = -INFINITY;
+                    if (!ok1) o2.y = -INFINITY;
+                }
+                *reinterpret_cast<float2*>(sc + ((kWide ? kh : 0) * G + fr) * SROW + r0) = o2;
             }
         }
         __syncthreads();
-        if (warp < G) {                                  // head `warp`: running max / sum, scores -> probabilities
-            static_assert(T == 32, "one score per lane");
-            const float s0 = sc[warp * T + lane];
-            const float mn = fmaxf(m_run, warp_max(s0));
-            const float corr = m_run == -INFINITY ? 0.f : __expf(m_run - mn);
-            const float p0 = s0 == -INFINITY ? 0.f : __expf(s0 - mn);
-            Pb[warp * PROW + lane] = __float2bfloat16_rn(p0);
-            l_run = l_run * corr + warp_sum(p0);
+        {   // head fr: the tile's scores -> running (max, sum) and the A fragments of P; O = corr * O + P V
+            float sv[T / 4];
+#pragma unroll
+            for (int kk = 0; kk < T / 16; ++kk) {
+                float2 lo2 = make_float2(-INFINITY, -INFINITY), hi2 = lo2;
+                if (fr < G) {
+                    lo2 = *reinterpret_cast<const float2*>(sc + fr * SROW + kk * 16 + fk);
+                    hi2 = *reinterpret_cast<const float2*>(sc + fr * SROW + kk * 16 + 8 + fk);
+                    if constexpr (kWide) {
+                        const float2 l1 = *reinterpret_cast<const float2*>(sc + (G + fr) * SROW + kk * 16 + fk);
+                        const float2 h1 = *reinterpret_cast<const float2*>(sc + (G + fr) * SROW + kk * 16 + 8 + fk);
+                        lo2.x += l1.x; lo2.y += l1.y; hi2.x += h1.x; hi2.y += h1.y;
+                    }
+                }
+                sv[4 * kk] = lo2.x; sv[4 * kk + 1] = lo2.y; sv[4 * kk + 2] = hi2.x; sv[4 * kk + 3] = hi2.y;
+            }
+            float mx = sv[0];
+#pragma unroll
+            for (int j = 1; j < T / 4; ++j) mx = fmaxf(mx, sv[j]);
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+            const float mn = fmaxf(m_run, mx);
+            const float mref = mn == -INFINITY ? 0.f : mn;   // nothing visible yet: every 2^(-inf - 0) below is 0
+            const float corr = ex2(m_run - mref);
+            float ls = 0.f;
+#pragma unroll
+            for (int j = 0; j < T / 4; ++j) {
+                sv[j] = ex2(sv[j] - mref);
+                ls += sv[j];
+            }
+            ls += __shfl_xor_sync(0xffffffffu, ls, 1);
+            ls += __shfl_xor_sync(0xffffffffu, ls, 2);
+            l_run = l_run * corr + ls;
             m_run = mn;
-            if (lane == 0) corr_s[warp] = corr;
-        }
-        __syncthreads();
-        {   // O[head, 8-channel blocks of this warp] = corr * O + P V
-            const float cg_ = fr < G ? corr_s[fr] : 0.f;
 #pragma unroll
-            for (int t = 0; t < NTW; ++t) { acc[t][0] *= cg_; acc[t][1] *= cg_; }
+            for (int t = 0; t < NTW; ++t) { acc[t][0] *= corr; acc[t][1] *= corr; }
+            const int tn = min(T, nkeys - tile * T);
+            const __nv_bfloat16* vr = Vt + (lane & 15) * VROW;
 #pragma unroll
             for (int kk = 0; kk < T / 16; ++kk) {
                 if (kk * 16 < tn) {
-                    const uint32_t a0 = fr < G ? *reinterpret_cast<const uint32_t*>(Pb + fr * PROW + kk * 16 + fk) : 0u;
-                    const uint32_t a2 = fr < G ? *reinterpret_cast<const uint32_t*>(Pb + fr * PROW + kk * 16 + 8 + fk) : 0u;
+                    const uint32_t a0 = pack_bf16(sv[4 * kk], sv[4 * kk + 1]);
+                    const uint32_t a2 = pack_bf16(sv[4 * kk + 2], sv[4 * kk + 3]);
 #pragma unroll
                     for (int t = 0; t < NTW; ++t) {
-                        const int nt = warp + kDecWarps * t;
-                        if (nt < HD / 8) {
+                        if (warp + kDecWarps * t < HD / 8) {
                             uint32_t b0, b1;
-                            ldmatrix_x2_trans(b0, b1, Vt + (kk * 16 + (lane & 15)) * KROW + nt * 8);
+                            ldmatrix_x2_trans(b0, b1, vr + kk * 16 * VROW + vchunk(lane, warp + kDecWarps * t) * 8);
                             mma16816(acc[t], a0, 0u, a2, 0u, b0, b1);
                         }
                     }
@@ -309,7 +410,7 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
             }
         }
     }
-    if (warp < G && lane == 0) { r_ml[warp * 2] = m_run; r_ml[warp * 2 + 1] = l_run; }
+    if (warp == 0 && fr < G && fk == 0) { r_ml[fr * 2] = m_run; r_ml[fr * 2 + 1] = l_run; }
     // ---- merge the CTAs of the cluster into rank 0 (reads of the partners' shared memory)
     cluster.sync();
     if (rank == 0) {
@@ -321,12 +422,11 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
             float a0 = 0.f, a1 = 0.f, Lsum = 0.f;
             for (int r = 0; r < nsplit; ++r) {
                 const float* ml = cluster.map_shared_rank(r_ml, r);
-                const float mr = ml[g * 2];
-                const float f = mr == -INFINITY ? 0.f : __expf(mr - M);
+                const float f = ex2(ml[g * 2] - M);      // a partner without a visible key: 2^(-inf) = 0
                 const float2 v = *reinterpret_cast<const float2*>(cluster.map_shared_rank(r_o, r) + idx * 2);
                 a0 += f * v.x; a1 += f * v.y; Lsum += f * ml[g * 2 + 1];
             }
-            const float inv = 1.f / Lsum;               // key `slot` is always visible: Lsum > 0
+            const float inv = 1.f / Lsum;               // key `slot` is always visible: M is finite, Lsum > 0
             *reinterpret_cast<uint32_t*>(out + idx * 2) = pack_bf16(a0 * inv, a1 * inv);
         }
     }
@@ -334,17 +434,20 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
 }
 
 template <int HD, int G>
-static int launch_decode_attn(const DecodeAttnArgs& a, int nsplit, cudaStream_t stream) {
-    const size_t smem = DecSmem<HD, G>::bytes;
-    if (smem > 48 * 1024) {
+static int launch_decode_attn(const DecodeAttnArgs& a_in, int nsplit, cudaStream_t stream) {
+    DecodeAttnArgs a = a_in;
+    const int nloc = ((a.Smax + kDecTile - 1) / kDecTile + nsplit - 1) / nsplit;   // tiles of one CTA, at most
+    a.vm_bytes = nloc * kDecTile <= 32 * 1024 ? nloc * kDecTile : 0;
+    const size_t smem = static_cast<size_t>(DecSmem<HD, G>::fixed) + a.vm_bytes;
+    {   // opt in once per device to the largest size a launch can ask for
         static bool done[64] = {};
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev < 64 && !done[dev]) {
-            const cudaError_t e = cudaFuncSetAttribute(decode_attn_kernel<HD, G>,
-                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (dev < 0 || dev >= 64 || !done[dev]) {
+            const cudaError_t e = cudaFuncSetAttribute(decode_attn_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                       DecSmem<HD, G>::fixed + 32 * 1024);
             if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(decode_attn): %s", cudaGetErrorString(e)); return PT_ERR_CUDA; }
-            done[dev] = true;
+            if (dev >= 0 && dev < 64) done[dev] = true;
         }
     }
     cudaLaunchConfig_t cfg = {};

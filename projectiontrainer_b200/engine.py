@@ -1188,6 +1188,10 @@ class Stage1Engine:
         if splitk and "d_yacc" not in ws:
             ws["d_yacc"] = torch.zeros((B, h), dtype=F32, device=self.device)   # empty between uses, see the kernel
         yacc = ws.get("d_yacc")
+        # slices per 128-column tile so that the launch is about one CTA pair per SM pair (measured at B = 64 on
+        # Gemma3-1B: down 34.5 us unsplit, 14.9 with the generic wave-fill choice on 64-wide tiles, 11.7 this way)
+        sk = lambda K: max(2, min(K // 64, round(74 / -(-h // 128))))
+        sk_o, sk_down = sk(hq * hd), sk(ff)
         tabs = {}
         if fused:       # the kernel reads the table row g_pos[b] and masks from g_slot / g_valid itself
             for f in (True, False):
@@ -1217,7 +1221,7 @@ class Stage1Engine:
                                           m_full if full else m_slide, attn_o, B, Smax, ld, scale)
             last = li == len(Lm.layers) - 1
             if splitk:
-                ops.linear(attn_o, L["o_w"], out=yacc, ksplit=-1)
+                ops.linear(attn_o, L["o_w"], out=yacc, ksplit=sk_o, bn_hint=128)
                 ops.rmsnorm_residual_fwd_acc(yacc, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
             elif c.sandwich_norm:
                 ops.linear(attn_o, L["o_w"], out=y)
@@ -1231,7 +1235,7 @@ class Stage1Engine:
                 ops.linear(a, L["gu_w"], out=gu)
                 ops.geglu_fwd(gu, act, silu=c.silu)
             if splitk:
-                ops.linear(act, L["down_w"], out=yacc, ksplit=-1)
+                ops.linear(act, L["down_w"], out=yacc, ksplit=sk_down, bn_hint=128)
                 ops.rmsnorm_residual_fwd_acc(yacc, L["post_ffn_norm"], x1, x,
                                              None if last else Lm.layers[li + 1]["in_norm"],
                                              None if last else a, c.eps)

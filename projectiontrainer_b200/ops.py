@@ -113,7 +113,8 @@ def _seg2(M: int, N: int, a2, b2, b_mn: bool) -> dict:
 
 
 def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residual=None,
-           out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0, x2=None, w2=None, ksplit=0) -> torch.Tensor:
+           out=None, out_dtype=torch.bfloat16, c_pre=None, alpha=1.0, x2=None, w2=None, ksplit=0,
+           bn_hint=0) -> torch.Tensor:
     """y[M,N] = act(alpha * (x[M,K] @ w[N,K]^T (+ x2[M,K2] @ w2[N,K2]^T)) + bias) (+ residual).  bf16 row-major 2-D
     operands."""
     M, K = x.shape
@@ -124,7 +125,7 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, bias=None, act=ACT_NONE, residua
     gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w, ldb=w.stride(0), Cout=out,
              ldc=out.stride(0), bias=bias, residual=residual,
              ldr=0 if residual is None else residual.stride(0), act=act, alpha=alpha, c_pre=c_pre, ksplit=ksplit,
-             **_seg2(M, N, x2, w2, False))
+             bn_hint=bn_hint, **_seg2(M, N, x2, w2, False))
     return out
 
 

@@ -1,5 +1,6 @@
 """GPU probe: pt_decode_attn alone at the decode bench's geometry (Gemma3-1B: hq 4 / hkv 1 / hd 256; B samples,
 Smax-slot cache, this token at `slot`), per cluster size, against the HBM time of the K/V rows it reads."""
+import os
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -24,7 +25,7 @@ out = torch.empty(B, hq * hd, dtype=torch.bfloat16, device=dev)
 for window in (0, 512):
     keys = slot + 1 if window == 0 else min(window, slot + 1)
     mb = 2 * B * keys * hkv * hd * 2 / 1e6
-    for ns in (1, 2, 4, 8):
+    for ns in [int(v) for v in os.environ.get("PROBE_NSPLIT", "1,2,4,8").split(",")]:
         def run():
             for li in range(L):
                 ops.decode_attn(qkv, w, w, cos, sin, pos, slot_t, valid, Ks[li], Vs[li], out, hq, hkv, hd, window,
