@@ -105,6 +105,14 @@ def test_configs4_geometry_and_a_full_window(cuda_dev):
     _case(cuda_dev, B=8, hq=32, hkv=8, hd=128, Smax=640, slot=600, window=0, pads=False, seed=7)
 
 
+def test_cache_longer_than_the_visibility_table(cuda_dev):
+    """Past 32 K keys per CTA the key-visibility bytes are read from `valid` tile by tile instead of from the table in
+    shared memory (33 000 slots on one CTA); the same cache through 8 CTAs uses the table."""
+    for nsplit in (1, 8):
+        _case(cuda_dev, B=1, hq=2, hkv=1, hd=16, Smax=33000, slot=32990, window=0, pads=True, seed=11, nsplit=nsplit)
+    _case(cuda_dev, B=2, hq=4, hkv=2, hd=64, Smax=33000, slot=32999, window=4096, pads=False, seed=12, nsplit=1)
+
+
 def test_rejects_what_it_does_not_take(cuda_dev):
     from projectiontrainer_b200 import ops
     assert not ops.decode_attn_supported(6, 2, 256) and not ops.decode_attn_supported(4, 2, 96)
