@@ -83,6 +83,13 @@ const char* pt_last_error(void);
 int pt_version(void);
 /* 0 when a compute-capability 10.x device is current, PT_ERR_CUDA otherwise. */
 int pt_device_check(void);
+/* Programmatic dependent launch for the kernels that support it: `kinds` is a bit set — 1: pt_gemm_bf16, 2:
+ * pt_rmsnorm_residual_fwd[_acc] on rows of <= 4096, 4: pt_decode_attn.  A kernel of an enabled kind may become
+ * resident while its predecessor in the stream drains, its prologue (barrier init, TMEM allocation, tensor-map
+ * prefetch) overlapping the predecessor's tail; every such kernel waits for the predecessor's completion before its
+ * first dependent memory access, so results do not change.  Process-wide, 0 by default; returns the previous setting.
+ * No counterpart in the reference (CUDA launch plumbing). */
+int pt_set_dependent_launch(int kinds);
 
 /* ------------------------------------------------------------------------- *
  * Tensor-core GEMM (tcgen05.mma, TMEM accumulators, TMA-fed smem pipeline).

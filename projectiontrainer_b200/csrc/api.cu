@@ -35,7 +35,16 @@ int num_sms() {
     return cached;
 }
 
+static int g_pdl = 0;
+bool pdl_enabled(int kind) { return (g_pdl & kind) != 0; }
+
 }  // namespace pt
+
+extern "C" int pt_set_dependent_launch(int on) {   // bit set of kPdl* kinds
+    const int was = pt::g_pdl;
+    pt::g_pdl = on;
+    return was;
+}
 
 extern "C" const char* pt_last_error(void) { return pt::g_err; }
 

@@ -148,6 +148,8 @@ __global__ void __launch_bounds__(kDecThreads) decode_attn_kernel(const DecodeAt
     const int item = blockIdx.x / nsplit;
     const int b = item / p.hkv, kvh = item - b * p.hkv;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    pdl_trigger();
+    pdl_wait();                                          // everything read below was written by earlier kernels
     const int slot = static_cast<int>(*p.slot);
     long long trow = p.pos[b];
     if (slot < 0 || slot >= p.Smax) return;             // the whole grid reads the same slot: nobody waits below
@@ -455,13 +457,15 @@ static int launch_decode_attn(const DecodeAttnArgs& a_in, int nsplit, cudaStream
     cfg.blockDim = dim3(kDecThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = static_cast<unsigned>(nsplit);
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled(kPdlDecodeAttn) ? 2 : 1;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, decode_attn_kernel<HD, G>, a);
     if (e != cudaSuccess) { set_error("decode_attn launch: %s", cudaGetErrorString(e)); return PT_ERR_CUDA; }
     return check_launch("decode_attn");

@@ -326,6 +326,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int cid = static_cast<int>(ptx::cluster_id_x());
     const int ncl = static_cast<int>(ptx::num_clusters_x());
 
+    pdl_trigger();                                // the next kernel's prologue may overlap this one (pt_common.cuh)
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmB);
@@ -354,6 +355,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     ptx::cluster_sync_all();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                                   // operands and C belong to the kernels before this one until here
 
     auto decode = [&](int t, int& m_blk, int& n_blk, int (&z)[3]) {
         if (p.ksplit > 1) t %= tiles_per_split;
@@ -903,13 +905,16 @@ static int launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const CU
     cfg.blockDim = dim3(kGemm2Threads, 1, 1);
     cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    // (the delta epilogue's launch follows a memset of its output, not a kernel: launched the ordinary way)
+    cfg.numAttrs = pdl_enabled(kPdlGemm) && ACT != PT_ACT_ATTN_DELTA ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_bf16_kernel<BN, ACT>, ta, tb, t_aux, t_c, ta2, tb2, p);
     if (e != cudaSuccess) {
         set_error("gemm2_bf16_kernel<%d>: launch failed: %s", BN, cudaGetErrorString(e));

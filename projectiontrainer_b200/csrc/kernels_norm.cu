@@ -193,6 +193,8 @@ rmsnorm_residual_fwd_row_kernel(TY* __restrict__ y, const float* __restrict__ w_
     const bool on = i < D;
     float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, xi[8], g[8];
     float q = 0.f;
+    pdl_trigger();
+    pdl_wait();
     if (on) {
         load8(y + base + i, v); load8(x_in + base + i, xi); load8(w_post + i, g);
         if constexpr (sizeof(TY) == 4) {
@@ -411,10 +413,9 @@ extern "C" int pt_rmsnorm_residual_fwd(const void* y_bf16, const float* w_post, 
     PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0, "pt_rmsnorm_residual_fwd: D must be a positive multiple of 8");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
     if (D <= 4096)
-        rmsnorm_residual_fwd_row_kernel<const __nv_bfloat16><<<rows, ((D / 8 + 31) / 32) * 32, 0,
-                                                               static_cast<cudaStream_t>(stream)>>>(
-            static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
-            static_cast<__nv_bfloat16*>(next_bf16), D, eps);
+        launch_pdl(kPdlNorm, rmsnorm_residual_fwd_row_kernel<const __nv_bfloat16>, dim3(rows), dim3(((D / 8 + 31) / 32) * 32), 0,
+                   static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out,
+                   w_next, static_cast<__nv_bfloat16*>(next_bf16), D, eps);
     else
         rmsnorm_residual_fwd_kernel<<<row_blocks(rows), kWarpsPerBlock * 32, 0, static_cast<cudaStream_t>(stream)>>>(
             static_cast<const __nv_bfloat16*>(y_bf16), w_post, x_in, x_out, w_next,
@@ -430,8 +431,9 @@ extern "C" int pt_rmsnorm_residual_fwd_acc(float* y_acc, const float* w_post, co
     PT_REQUIRE(rows > 0 && D > 0 && D % 8 == 0 && D <= 4096,
                "pt_rmsnorm_residual_fwd_acc: D must be a positive multiple of 8, at most 4096");
     if (pt_device_check() != PT_OK) return PT_ERR_CUDA;
-    rmsnorm_residual_fwd_row_kernel<float><<<rows, ((D / 8 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        y_acc, w_post, x_in, x_out, w_next, static_cast<__nv_bfloat16*>(next_bf16), D, eps);
+    launch_pdl(kPdlNorm, rmsnorm_residual_fwd_row_kernel<float>, dim3(rows), dim3(((D / 8 + 31) / 32) * 32), 0,
+               static_cast<cudaStream_t>(stream), y_acc, w_post, x_in, x_out, w_next,
+               static_cast<__nv_bfloat16*>(next_bf16), D, eps);
     return check_launch("rmsnorm_residual_fwd_acc");
 }
 

@@ -27,6 +27,37 @@ int check_launch(const char* what);
 constexpr int kNumSMsFallback = 148;
 int num_sms();
 
+// ---- programmatic dependent launch (pt_set_dependent_launch) -----------------
+// A kernel launched through launch_pdl may become resident while the kernel before it in the stream is still running
+// (as soon as every CTA of that kernel has executed pdl_trigger() or exited): its prologue — barrier init, TMEM
+// allocation, tensor-map prefetch, index arithmetic — overlaps the predecessor's tail.  Such a kernel must execute
+// pdl_wait() in EVERY CTA before its first global-memory access that is not to its own parameters (the wait returns
+// once the predecessor grid has completed and its writes are visible), and before it exits.  Both instructions are
+// no-ops in a kernel that was launched the ordinary way.
+enum { kPdlGemm = 1, kPdlNorm = 2, kPdlDecodeAttn = 4 };   // bits of pt_set_dependent_launch
+bool pdl_enabled(int kind);
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int kind, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled(kind) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- small device helpers ---------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

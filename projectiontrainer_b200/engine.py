@@ -236,6 +236,10 @@ class Stage1Engine:
         # cross-entropy statistics (row max / sum exp partials) in the LM-head GEMM epilogue: the separate statistics
         # pass over the 2.1 GB of logits goes away
         self.fuse_ce_stats = self.lcfg.vocab >= 256 and os.environ.get("PT_STAGE1_FUSE_CE_STATS", "1") != "0"
+        # decode step: programmatic dependent launch (bit set of pt_set_dependent_launch: 1 GEMMs, 2 norm kernels,
+        # 4 attention).  A chain of dependent M = 64 GEMMs gains 1.5 us per launch (9.37 -> 7.86 us), but inside the
+        # step the A/B is box dependent (-6 % on one box, 0 .. +3 % on another, profiles/r02_decode_attn.txt): off.
+        self.decode_pdl = int(os.environ.get("PT_STAGE1_DECODE_PDL", "0"))
         # graphed decode step: q/k norm + RoPE, cache append and attention over the cache in one launch per layer
         # (0: pt_qknorm_rope_fwd, two cache row copies, score GEMM, softmax, P V GEMM)
         self.fuse_decode_attn = ops.decode_attn_supported(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
@@ -1132,7 +1136,7 @@ class Stage1Engine:
         if kc.get("g_tokens") is None or kc["g_tokens"].shape[0] != B:
             kc["g_tokens"] = torch.zeros(B, 1, dtype=torch.int64, device=self.device)
         kc["g_tokens"].copy_(tokens.to(self.device).view(B, 1), non_blocking=True)
-        variant = (self.fuse_decode_attn, self.decode_splitk)
+        variant = (self.fuse_decode_attn, self.decode_splitk, self.decode_pdl)
         if kc.get("g_variant") != variant:          # the captured graph belongs to one variant of the step
             kc.update(g_variant=variant, g_graph=None, g_calls=0)
         kc["g_calls"] += 1
@@ -1158,6 +1162,13 @@ class Stage1Engine:
         (pt_decode_attn: norm + RoPE, cache append, flash-decoding over a CTA cluster), or, for geometries it does not
         take, six (scores and P V over all Smax slots, masked in the softmax).  Ends by advancing g_slot / g_pos, so
         a captured graph serves every step."""
+        was = _lib.lib().pt_set_dependent_launch(self.decode_pdl)
+        try:
+            return self._decode_step_fixed_body()
+        finally:
+            _lib.lib().pt_set_dependent_launch(was)
+
+    def _decode_step_fixed_body(self) -> torch.Tensor:
         c, Lm, kc = self.lcfg, self.llm, self.cache
         B, Smax = kc["B"], kc["Smax"]
         h, hd, hq, hkv, ff = c.hidden, c.hd, c.hq, c.hkv, c.ff
