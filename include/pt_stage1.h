@@ -276,6 +276,18 @@ int pt_decode_attn(const void* qkv, const float* wq, const float* wk, const floa
                    int table_rows, const long long* pos, const long long* slot, const uint8_t* valid, void* K,
                    void* V, void* out_bf16, int B, int Smax, int hq, int hkv, int hd, int window, float eps,
                    float scale, int nsplit, void* stream);
+/* The next token of every row of `generate` in one launch (HF:generation/utils.py `_sample` with the logits
+ * processors / warpers of `_get_logits_processor`, as called at ref:Stage1/inference_stage1.py:176-186,
+ * ref:Stage1/projector_trainer.py:386-394): repetition penalty over prev[b, 0..nprev) (x < 0 ? x * rp : x / rp; NULL or
+ * rp == 1: none) -> / temperature -> top-k (values below the k-th largest go, ties with it stay; 1 <= top_k <= 1024)
+ * -> top-p (ascending cumulative probability <= 1 - top_p goes, the largest stays; >= 1: none) -> softmax -> one draw
+ * by inverse CDF over the surviving tokens in descending order at u[b] in [0, 1) (torch.multinomial's distribution,
+ * not its random stream); top_k == 0: argmax of the penalised logits (smallest index among ties).  Then HF's
+ * bookkeeping: a row with done[b] != 0 emits pad_id (if >= 0); out[b * ld_out] = token; next[b] = token (optional);
+ * done[b] |= token == eos_id (if >= 0).  logits f32 [B, ld >= V]. */
+int pt_sample_token(const float* logits, long long ld, int B, int V, const long long* prev, long long ld_prev, int nprev,
+                    float repetition_penalty, float temperature, int top_k, float top_p, const float* u, uint8_t* done,
+                    long long pad_id, long long eos_id, long long* out, long long ld_out, long long* next, void* stream);
 /* Fused backward of the same attention (autograd through HF:models/gemma3/modeling_gemma3.py:370-384, invoked at
  * ref:Stage1/projector_trainer.py:236-237), key/value stationary, P recomputed from q_rot, k_rot and lse:
  *   dV[b*S + k, kvh*hd ..] = sum_{heads of kvh} P^T dO          (bf16, row stride ld_dv elements)

@@ -244,6 +244,9 @@ class Stage1Engine:
         # (0: pt_qknorm_rope_fwd, two cache row copies, score GEMM, softmax, P V GEMM)
         self.fuse_decode_attn = ops.decode_attn_supported(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_FUSE_DECODE_ATTN", "1") != "0"
+        # generate(): the next-token choice (HF processors + draw + bookkeeping) as one launch per token
+        # (0: the same logic in torch ops on the [B, V] logits, also what top_k = 0 / > 1024 takes)
+        self.fuse_sampler = os.environ.get("PT_STAGE1_FUSE_SAMPLER", "1") != "0"
         # graphed decode step, sandwich-norm decoders: o- and down-projection as split-K GEMMs into an f32 accumulator
         # that the following norm kernel rounds, consumes and clears (0: one CTA pair per 64 output columns streams
         # the whole contraction)
@@ -1373,8 +1376,9 @@ class Stage1Engine:
         ref:Stage1/inference_stage1.py:176-187 / projector_trainer.py:386-393: returns the NEW tokens
         only, i64 [B, n<=max_new_tokens]; finished rows are filled with pad_token_id; stops early when
         every row has produced eos.  Token selection (HF logits processors: repetition penalty ->
-        temperature -> top-k -> top-p -> multinomial, or argmax) is control logic on a [B, V] tensor
-        and uses torch ops; all model arithmetic runs in the sm_100a kernels."""
+        temperature -> top-k -> top-p -> multinomial, or argmax) and the finished-row bookkeeping are one launch per
+        token (pt_sample_token; the draw has torch.multinomial's distribution, not its random stream); top_k = 0 or
+        > 1024 with sampling takes the torch restatement of the same logic below."""
         if self.lora is not None:
             # the decode loop reads the packed weights only: fold the adapters in for the length of this call
             kw = dict(max_new_tokens=max_new_tokens, do_sample=do_sample, temperature=temperature, top_p=top_p,
@@ -1393,8 +1397,30 @@ class Stage1Engine:
         dev = self.device
         out = torch.full((B, max_new_tokens), pad_token_id if pad_token_id is not None else 0,
                          dtype=torch.int64, device=dev)
-        done = torch.zeros(B, dtype=torch.bool, device=dev)
         n = 0
+        if self.fuse_sampler and (not do_sample or (top_k and 0 < top_k <= 1024)) and temperature > 0 and top_p > 0:
+            # one launch per token: processors, draw and finished-row bookkeeping (pt_sample_token); the uniform
+            # numbers of all steps come from `generator` up front
+            u = None
+            if do_sample:
+                on_dev = generator is None or generator.device.type == "cuda"
+                u = torch.rand((max_new_tokens, B), generator=generator, dtype=F32,
+                               device=dev if on_dev else "cpu").to(dev)
+            done8 = torch.zeros(B, dtype=torch.uint8, device=dev)
+            nxt = torch.empty(B, dtype=torch.int64, device=dev)
+            for step in range(max_new_tokens):
+                ops.sample_token(logits, out=out, step=step, next_tokens=nxt,
+                                 prev=out if repetition_penalty != 1.0 and step > 0 else None,
+                                 repetition_penalty=repetition_penalty, temperature=temperature,
+                                 top_k=top_k if do_sample else 0, top_p=top_p, u=None if u is None else u[step],
+                                 done=done8, pad_id=pad_token_id, eos_id=eos_token_id)
+                n = step + 1
+                if eos_token_id is not None and bool(done8.all()):
+                    break
+                if step + 1 < max_new_tokens:
+                    logits = self.decode_step(nxt)
+            return out[:, :n]
+        done = torch.zeros(B, dtype=torch.bool, device=dev)
         for step in range(max_new_tokens):
             sc = logits.float().clone()
             if repetition_penalty != 1.0 and step > 0:

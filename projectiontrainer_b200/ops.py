@@ -316,6 +316,26 @@ def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, win
               int(ld), int(heads_per_batch), int(causal), int(window), _stream())
 
 
+def sample_token(logits, *, out, step, next_tokens=None, prev=None, repetition_penalty=1.0, temperature=1.0, top_k=0,
+                 top_p=1.0, u=None, done=None, pad_id=None, eos_id=None):
+    """The next token of every row (HF's processor order: repetition penalty, temperature, top-k, top-p, one draw at
+    u[b]; top_k = 0: argmax) and HF's finished-row bookkeeping, written to out[:, step] (i64 [B, n]) and next_tokens.
+    logits f32 [B, V] (row stride >= V); prev = out: the tokens out[:, :step] are the penalised ones."""
+    _req_cuda(logits, out, next_tokens, prev, u, done)
+    B, V = logits.shape
+    if logits.dtype != torch.float32 or logits.stride(1) != 1 or out.dtype != torch.int64 or out.stride(1) != 1:
+        raise RuntimeError("sample_token: logits must be f32 rows, out int64 rows")
+    if (done is not None and done.dtype != torch.uint8) or (u is not None and (u.dtype != torch.float32 or u.numel() < B)):
+        raise RuntimeError("sample_token: done must be uint8 [B], u float32 [B]")
+    if prev is not None and (prev.dtype != torch.int64 or prev.stride(1) != 1):
+        raise RuntimeError("sample_token: prev must be int64 rows")
+    _lib.call("pt_sample_token", _ptr(logits), C.c_longlong(logits.stride(0)), int(B), int(V), _ptr(prev),
+              C.c_longlong(0 if prev is None else prev.stride(0)), int(step if prev is not None else 0),
+              _f(repetition_penalty), _f(temperature), int(top_k), _f(top_p), _ptr(u), _ptr(done),
+              C.c_longlong(-1 if pad_id is None else int(pad_id)), C.c_longlong(-1 if eos_id is None else int(eos_id)),
+              C.c_void_p(out.data_ptr() + 8 * int(step)), C.c_longlong(out.stride(0)), _ptr(next_tokens), _stream())
+
+
 def decode_attn_supported(hq: int, hkv: int, hd: int) -> bool:
     return bool(_lib.lib().pt_decode_attn_supported(int(hq), int(hkv), int(hd)))
 
