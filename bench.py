@@ -568,6 +568,22 @@ def aux_configs_1b(eng, vc, lc, dev, peak):
                              "prefill_ms": ms, "images_per_s": B / ms * 1e3, "tflops": tf,
                              "frac_of_sustained_peak": tf / peak, "decode_ms_per_token_step": msd,
                              "decode_tokens_per_s": B / msd * 1e3}
+        # `generate` end to end with the reference's sampling call (ref:Stage1/inference_stage1.py:176-186: do_sample,
+        # temperature 0.7, top_p 0.9, HF's default top_k 50), per generated token: difference of two lengths so that
+        # the prefill drops out; includes the token choice (pt_sample_token) and the host loop
+        import time
+
+        def gen(n):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            eng.generate(px, ids, max_new_tokens=n, do_sample=True, temperature=0.7, top_p=0.9, pad_token_id=0,
+                         eos_token_id=None, generator=g)
+            torch.cuda.synchronize()
+            return time.perf_counter() - t0
+        gen(nd), gen(8)
+        msg = min((gen(nd) - gen(8)) / (nd - 8) * 1e3 for _ in range(3))
+        out["configs[4]"].update({"generate_sampled_ms_per_token_step": msg,
+                                  "generate_sampled_tokens_per_s": B / msg * 1e3})
         eng.select_geometry(("default",))
     except Exception as e:
         out["error"] = f"{type(e).__name__}: {e}"
