@@ -276,6 +276,16 @@ int pt_decode_attn(const void* qkv, const float* wq, const float* wk, const floa
                    int table_rows, const long long* pos, const long long* slot, const uint8_t* valid, void* K,
                    void* V, void* out_bf16, int B, int Smax, int hq, int hkv, int hd, int window, float eps,
                    float scale, int nsplit, void* stream);
+/* Linear layer at small batch (M <= 16 rows; the decode step of the reference's one-image-at-a-time inference,
+ * ref:Stage1/inference_stage1.py:150-193 -> torch.nn.functional.linear in HF:models/gemma3/modeling_gemma3.py:127-129,
+ * 357-387, 652): out[m][n] = sum_k x[m][k] W[n][k], x bf16 [M, K] (row stride lda), W bf16 [N, K] (row stride ldb),
+ * K % 32 == 0, pure weight streaming on mma.sync with the weight rows as the MMA's M dimension.
+ * mode 0: out bf16 [M, N]; 1: out f32; 2: out f32 += (atomic; ksplit K slices, <= 0: chosen; the accumulator of
+ * pt_rmsnorm_residual_fwd_acc); 3 / 4: GeGLU / SwiGLU — W holds 2 N rows [gate rows ; up rows], out bf16 [M, N] =
+ * act(bf16(gate)) * bf16(up) like pt_gemm_bf16's PT_ACT_GEGLU / PT_ACT_SWIGLU epilogue (the pre-activations are not
+ * stored: inference). */
+int pt_gemv_small_m(const void* x, long long lda, int M, const void* W, long long ldb, int N, int K, void* out,
+                    long long ldc, int mode, int ksplit, void* stream);
 /* The next token of every row of `generate` in one launch (HF:generation/utils.py `_sample` with the logits
  * processors / warpers of `_get_logits_processor`, as called at ref:Stage1/inference_stage1.py:176-186,
  * ref:Stage1/projector_trainer.py:386-394): repetition penalty over prev[b, 0..nprev) (x < 0 ? x * rp : x / rp; NULL or

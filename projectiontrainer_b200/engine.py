@@ -244,6 +244,9 @@ class Stage1Engine:
         # (0: pt_qknorm_rope_fwd, two cache row copies, score GEMM, softmax, P V GEMM)
         self.fuse_decode_attn = ops.decode_attn_supported(self.lcfg.hq, self.lcfg.hkv, self.lcfg.hd) and \
             os.environ.get("PT_STAGE1_FUSE_DECODE_ATTN", "1") != "0"
+        # decode step at batch <= 16: the linear layers as weight-streaming mma.sync kernels (pt_gemv_small_m) instead
+        # of the 256-row tcgen05 tile
+        self.decode_gemv = os.environ.get("PT_STAGE1_DECODE_GEMV", "1") != "0"
         # generate(): the next-token choice (HF processors + draw + bookkeeping) as one launch per token
         # (0: the same logic in torch ops on the [B, V] logits, also what top_k = 0 / > 1024 takes)
         self.fuse_sampler = os.environ.get("PT_STAGE1_FUSE_SAMPLER", "1") != "0"
@@ -1111,13 +1114,16 @@ class Stage1Engine:
         x, _ = self._llm_stack(x0, keyvalid, B, S, save=False, cache=self.cache, pos_ids=pos_ids)
         return self._last_logits(x, B, S)
 
-    def _last_logits(self, x: torch.Tensor, B: int, S: int, buf=None) -> torch.Tensor:
+    def _last_logits(self, x: torch.Tensor, B: int, S: int, buf=None, skinny: bool = False) -> torch.Tensor:
         c, Lm = self.lcfg, self.llm
         buf = buf or self.buf
         yf = buf("i_yf", (B, c.hidden), BF16)
         ops.rmsnorm_fwd(x, Lm.final_norm, yf, c.eps, group=(1, S, S - 1))
         logits = buf("i_logits", (B, _pad8(c.vocab)), F32)[:, :c.vocab]
-        ops.linear(yf, Lm.lm_head, out=logits)
+        if skinny:
+            ops.gemv(yf, Lm.lm_head, logits, ops.GEMV_F32)
+        else:
+            ops.linear(yf, Lm.lm_head, out=logits)
         return logits
 
     @torch.no_grad()
@@ -1139,7 +1145,7 @@ class Stage1Engine:
         if kc.get("g_tokens") is None or kc["g_tokens"].shape[0] != B:
             kc["g_tokens"] = torch.zeros(B, 1, dtype=torch.int64, device=self.device)
         kc["g_tokens"].copy_(tokens.to(self.device).view(B, 1), non_blocking=True)
-        variant = (self.fuse_decode_attn, self.decode_splitk, self.decode_pdl)
+        variant = (self.fuse_decode_attn, self.decode_splitk, self.decode_pdl, self.decode_gemv)
         if kc.get("g_variant") != variant:          # the captured graph belongs to one variant of the step
             kc.update(g_variant=variant, g_graph=None, g_calls=0)
         kc["g_calls"] += 1
@@ -1199,6 +1205,7 @@ class Stage1Engine:
         act = dbuf("d_act", (B, ff), BF16)
         fused = self.fuse_decode_attn
         splitk = self.decode_splitk
+        skinny = self.decode_gemv and all(ops.gemv_ok(B, k) for k in (h, hq * hd, ff))
         if splitk and "d_yacc" not in ws:
             ws["d_yacc"] = torch.zeros((B, h), dtype=F32, device=self.device)   # empty between uses, see the kernel
         yacc = ws.get("d_yacc")
@@ -1225,7 +1232,10 @@ class Stage1Engine:
         ops.rmsnorm_fwd(x, Lm.layers[0]["in_norm"], a, c.eps)
         for li, L in enumerate(Lm.layers):
             full = c.is_full(li)
-            ops.linear(a, L["qkv_w"], out=qkv)
+            if skinny:
+                ops.gemv(a, L["qkv_w"], qkv)
+            else:
+                ops.linear(a, L["qkv_w"], out=qkv)
             K, V = kc["k"][li], kc["v"][li]
             if fused:
                 ops.decode_attn(qkv, L["q_norm"], L["k_norm"], tabs[full][0], tabs[full][1], posv, slot,
@@ -1235,7 +1245,10 @@ class Stage1Engine:
                                           m_full if full else m_slide, attn_o, B, Smax, ld, scale)
             last = li == len(Lm.layers) - 1
             if splitk:
-                ops.linear(attn_o, L["o_w"], out=yacc, ksplit=sk_o, bn_hint=128)
+                if skinny:
+                    ops.gemv(attn_o, L["o_w"], yacc, ops.GEMV_F32_ATOMIC)
+                else:
+                    ops.linear(attn_o, L["o_w"], out=yacc, ksplit=sk_o, bn_hint=128)
                 ops.rmsnorm_residual_fwd_acc(yacc, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
             elif c.sandwich_norm:
                 ops.linear(attn_o, L["o_w"], out=y)
@@ -1243,13 +1256,18 @@ class Stage1Engine:
             else:
                 ops.linear(attn_o, L["o_w"], out=x1, residual=x)
                 ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a, c.eps)
-            if self.fuse_geglu:
+            if skinny:
+                ops.gemv(a, L["gu_w"], act, ops.GEMV_SWIGLU if c.silu else ops.GEMV_GEGLU)
+            elif self.fuse_geglu:
                 ops.linear_geglu(a, L["gu_w"], gu, act, silu=c.silu)
             else:
                 ops.linear(a, L["gu_w"], out=gu)
                 ops.geglu_fwd(gu, act, silu=c.silu)
             if splitk:
-                ops.linear(act, L["down_w"], out=yacc, ksplit=sk_down, bn_hint=128)
+                if skinny:
+                    ops.gemv(act, L["down_w"], yacc, ops.GEMV_F32_ATOMIC)
+                else:
+                    ops.linear(act, L["down_w"], out=yacc, ksplit=sk_down, bn_hint=128)
                 ops.rmsnorm_residual_fwd_acc(yacc, L["post_ffn_norm"], x1, x,
                                              None if last else Lm.layers[li + 1]["in_norm"],
                                              None if last else a, c.eps)
@@ -1262,7 +1280,7 @@ class Stage1Engine:
                 ops.linear(act, L["down_w"], out=x, residual=x1)
                 if not last:
                     ops.rmsnorm_fwd(x, Lm.layers[li + 1]["in_norm"], a, c.eps)
-        logits = self._last_logits(x, B, 1, buf=dbuf)
+        logits = self._last_logits(x, B, 1, buf=dbuf, skinny=skinny)
         slot.add_(1)
         posv.add_(1)
         return logits

@@ -316,6 +316,28 @@ def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, win
               int(ld), int(heads_per_batch), int(causal), int(window), _stream())
 
 
+GEMV_BF16, GEMV_F32, GEMV_F32_ATOMIC, GEMV_GEGLU, GEMV_SWIGLU = range(5)
+
+
+def gemv_ok(M: int, K: int) -> bool:
+    return 1 <= M <= 16 and K >= 32 and K % 32 == 0
+
+
+def gemv(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor, mode: int = GEMV_BF16, ksplit: int = 0):
+    """out[M, N] = x[M, K] @ w[N, K]^T for M <= 16 (weight streaming; pt_gemv_small_m).  GLU modes: w holds
+    [gate rows ; up rows] (2 N rows) and out = act(gate) * up."""
+    _req_cuda(x, w, out)
+    M, K = x.shape
+    N = w.shape[0] // 2 if mode in (GEMV_GEGLU, GEMV_SWIGLU) else w.shape[0]
+    want = torch.float32 if mode in (GEMV_F32, GEMV_F32_ATOMIC) else torch.bfloat16
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or out.dtype != want or w.shape[1] != K or \
+            x.stride(1) != 1 or w.stride(1) != 1 or out.stride(1) != 1 or tuple(out.shape) != (M, N):
+        raise RuntimeError("gemv: bf16 row-major x [M, K], w [N, K]; out [M, N] bf16 (modes 0, 3, 4) or f32 (1, 2)")
+    _lib.call("pt_gemv_small_m", _ptr(x), C.c_longlong(x.stride(0)), int(M), _ptr(w), C.c_longlong(w.stride(0)), int(N),
+              int(K), _ptr(out), C.c_longlong(out.stride(0)), int(mode), int(ksplit), _stream())
+    return out
+
+
 def sample_token(logits, *, out, step, next_tokens=None, prev=None, repetition_penalty=1.0, temperature=1.0, top_k=0,
                  top_p=1.0, u=None, done=None, pad_id=None, eos_id=None):
     """The next token of every row (HF's processor order: repetition penalty, temperature, top-k, top-p, one draw at

@@ -109,7 +109,7 @@ def test_prefill_config5_shape_full_size_llm_head_last_position_only(cuda_dev):
     _close(lg2.cpu(), lg_ref.cpu(), "cached decode vs cache-free prefill")
 
 
-@pytest.mark.parametrize("variant", ["decode_attn+splitk", "decode_attn", "six_launches"])
+@pytest.mark.parametrize("variant", ["decode_attn+splitk", "decode_attn+splitk+tcgen05_gemm", "decode_attn", "six_launches"])
 @pytest.mark.parametrize("padded", [False, True], ids=["plain_prompt", "left_padded_prompt"])
 def test_graphed_decode_step_equals_eager_decode_step(cuda_dev, padded, variant, monkeypatch):
     """The decode step as one CUDA graph with the position on the device (eager warm-up, capture, replay, and a
@@ -131,8 +131,10 @@ def test_graphed_decode_step_equals_eager_decode_step(cuda_dev, padded, variant,
     eng = E.Stage1Engine(E.PackedSiglip(Wv, SiglipCfg(**vkw), cuda_dev), E.PackedGemma(Wl, GemmaCfg(**lkw), cuda_dev),
                          E.ProjectorState(P, cuda_dev), cuda_dev)
     assert eng.fuse_decode_attn and eng.decode_splitk
+    assert eng.decode_gemv                             # batch 3: the linear layers stream their weights (pt_gemv_small_m)
     eng.fuse_decode_attn = variant != "six_launches"
-    eng.decode_splitk = variant == "decode_attn+splitk"
+    eng.decode_splitk = variant.startswith("decode_attn+splitk")
+    eng.decode_gemv = variant in ("decode_attn+splitk", "decode_attn")   # six_launches: the eager step's arithmetic
     new = 7
 
     def run(seed, graph):
