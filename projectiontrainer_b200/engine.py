@@ -1254,7 +1254,11 @@ class Stage1Engine:
                 ops.linear(attn_o, L["o_w"], out=y)
                 ops.rmsnorm_residual_fwd(y, L["post_attn_norm"], x, x1, L["pre_ffn_norm"], a, c.eps)
             else:
-                ops.linear(attn_o, L["o_w"], out=x1, residual=x)
+                if skinny:      # x1 = x + attn_o W_o^T: the K slices add onto a copy of the residual stream
+                    x1.copy_(x)
+                    ops.gemv(attn_o, L["o_w"], x1, ops.GEMV_F32_ATOMIC)
+                else:
+                    ops.linear(attn_o, L["o_w"], out=x1, residual=x)
                 ops.rmsnorm_fwd(x1, L["pre_ffn_norm"], a, c.eps)
             if skinny:
                 ops.gemv(a, L["gu_w"], act, ops.GEMV_SWIGLU if c.silu else ops.GEMV_GEGLU)
@@ -1277,7 +1281,11 @@ class Stage1Engine:
                                          None if last else Lm.layers[li + 1]["in_norm"],
                                          None if last else a, c.eps)
             else:
-                ops.linear(act, L["down_w"], out=x, residual=x1)
+                if skinny:
+                    x.copy_(x1)
+                    ops.gemv(act, L["down_w"], x, ops.GEMV_F32_ATOMIC)
+                else:
+                    ops.linear(act, L["down_w"], out=x, residual=x1)
                 if not last:
                     ops.rmsnorm_fwd(x, Lm.layers[li + 1]["in_norm"], a, c.eps)
         logits = self._last_logits(x, B, 1, buf=dbuf, skinny=skinny)

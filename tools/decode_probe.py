@@ -6,15 +6,16 @@ from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import torch
 from projectiontrainer_b200 import ops
-from projectiontrainer_b200.config import GEMMA3_1B, SIGLIP_L
+from projectiontrainer_b200.config import GEMMA3_1B, GEMMA3_4B, QWEN3_8B, SIGLIP_L
 from projectiontrainer_b200.engine import build_engine
 
 dev = torch.device("cuda:0")
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
-eng = build_engine(SIGLIP_L, GEMMA3_1B, dev)
+LLM = {"gemma3_1b": GEMMA3_1B, "gemma3_4b": GEMMA3_4B, "qwen3_8b": QWEN3_8B}[sys.argv[2] if len(sys.argv) > 2 else "gemma3_1b"]
+eng = build_engine(SIGLIP_L, LLM, dev)
 g = torch.Generator(device=dev).manual_seed(1)
 px = torch.rand(B, 3, 384, 384, generator=g, device=dev) * 2 - 1
-ids = torch.randint(3, GEMMA3_1B.vocab, (B, 64), generator=g, device=dev)
+ids = torch.randint(3, LLM.vocab, (B, 64), generator=g, device=dev)
 nxt = eng.prefill(px, ids, max_new_tokens=40).argmax(-1)
 for _ in range(3):
     nxt = eng.decode_step(nxt).argmax(-1)
@@ -24,7 +25,7 @@ e0.record()
 for _ in range(20):
     nxt = eng.decode_step(nxt).argmax(-1)
 e1.record(); torch.cuda.synchronize()
-print(f"B={B}: graph replay {e0.elapsed_time(e1) / 20:.3f} ms per token step")
+print(f"{sys.argv[2] if len(sys.argv) > 2 else 'gemma3_1b'} B={B}: graph replay {e0.elapsed_time(e1) / 20:.3f} ms per token step")
 ops.GEMM_PROFILE = []
 e0.record()
 eng._decode_step_fixed()
