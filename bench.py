@@ -584,6 +584,19 @@ def aux_configs_1b(eng, vc, lc, dev, peak):
         msg = min((gen(nd) - gen(8)) / (nd - 8) * 1e3 for _ in range(3))
         out["configs[4]"].update({"generate_sampled_ms_per_token_step": msg,
                                   "generate_sampled_tokens_per_s": B / msg * 1e3})
+        # the reference's inference scripts run one image at a time: the same step at B = 1 (linear layers as weight
+        # streaming, pt_gemv_small_m)
+        nxt = eng.prefill(px[:1], ids[:1], max_new_tokens=nd).argmax(-1)
+        for _ in range(3):
+            nxt = eng.decode_step(nxt).argmax(-1)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(nd - 4):
+            nxt = eng.decode_step(nxt).argmax(-1)
+        e1.record()
+        torch.cuda.synchronize()
+        ms1 = e0.elapsed_time(e1) / (nd - 4)
+        out["configs[4]"].update({"decode_b1_ms_per_token_step": ms1, "decode_b1_tokens_per_s": 1e3 / ms1})
         eng.select_geometry(("default",))
     except Exception as e:
         out["error"] = f"{type(e).__name__}: {e}"
