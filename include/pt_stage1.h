@@ -276,7 +276,7 @@ int pt_decode_attn(const void* qkv, const float* wq, const float* wk, const floa
                    int table_rows, const long long* pos, const long long* slot, const uint8_t* valid, void* K,
                    void* V, void* out_bf16, int B, int Smax, int hq, int hkv, int hd, int window, float eps,
                    float scale, int nsplit, void* stream);
-/* Linear layer at small batch (M <= 16 rows; the decode step of the reference's one-image-at-a-time inference,
+/* Linear layer at small batch (M <= 32 rows; the decode step of the reference's one-image-at-a-time inference,
  * ref:Stage1/inference_stage1.py:150-193 -> torch.nn.functional.linear in HF:models/gemma3/modeling_gemma3.py:127-129,
  * 357-387, 652): out[m][n] = sum_k x[m][k] W[n][k], x bf16 [M, K] (row stride lda), W bf16 [N, K] (row stride ldb),
  * K % 32 == 0, pure weight streaming on mma.sync with the weight rows as the MMA's M dimension.

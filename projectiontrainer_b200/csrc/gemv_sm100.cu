@@ -154,7 +154,7 @@ using namespace pt;
 extern "C" int pt_gemv_small_m(const void* x, long long lda, int M, const void* W, long long ldb, int N, int K, void* out,
                                long long ldc, int mode, int ksplit, void* stream) {
     PT_REQUIRE(x && W && out, "pt_gemv_small_m: null pointer");
-    PT_REQUIRE(M >= 1 && M <= 16, "pt_gemv_small_m: M must be 1 .. 16 (larger batches take pt_gemm_bf16)");
+    PT_REQUIRE(M >= 1 && M <= 32, "pt_gemv_small_m: M must be 1 .. 32 (larger batches take pt_gemm_bf16)");
     PT_REQUIRE(N >= 1 && K >= 32 && K % 32 == 0, "pt_gemv_small_m: K must be a positive multiple of 32");
     PT_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= K && ldb >= K, "pt_gemv_small_m: row strides must be multiples of 8, >= K");
     PT_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(W)) % 16 == 0,
@@ -189,6 +189,6 @@ extern "C" int pt_gemv_small_m(const void* x, long long lda, int M, const void* 
         case GEMV_GEGLU: return launch_gemv<MT, GEMV_GEGLU>(a, slices, st);                      \
         default: return launch_gemv<MT, GEMV_SWIGLU>(a, slices, st);                             \
     }
-    if (M <= 8) { PT_GEMV(1) } else { PT_GEMV(2) }
+    if (M <= 8) { PT_GEMV(1) } else if (M <= 16) { PT_GEMV(2) } else { PT_GEMV(4) }
 #undef PT_GEMV
 }

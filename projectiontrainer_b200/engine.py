@@ -247,6 +247,7 @@ class Stage1Engine:
         # decode step at batch <= 16: the linear layers as weight-streaming mma.sync kernels (pt_gemv_small_m) instead
         # of the 256-row tcgen05 tile
         self.decode_gemv = os.environ.get("PT_STAGE1_DECODE_GEMV", "1") != "0"
+        self.decode_gemv_rows = int(os.environ.get("PT_STAGE1_DECODE_GEMV_ROWS", "16"))
         # generate(): the next-token choice (HF processors + draw + bookkeeping) as one launch per token
         # (0: the same logic in torch ops on the [B, V] logits, also what top_k = 0 / > 1024 takes)
         self.fuse_sampler = os.environ.get("PT_STAGE1_FUSE_SAMPLER", "1") != "0"
@@ -1205,7 +1206,7 @@ class Stage1Engine:
         act = dbuf("d_act", (B, ff), BF16)
         fused = self.fuse_decode_attn
         splitk = self.decode_splitk
-        skinny = self.decode_gemv and all(ops.gemv_ok(B, k) for k in (h, hq * hd, ff))
+        skinny = self.decode_gemv and all(ops.gemv_ok(B, k, self.decode_gemv_rows) for k in (h, hq * hd, ff))
         if splitk and "d_yacc" not in ws:
             ws["d_yacc"] = torch.zeros((B, h), dtype=F32, device=self.device)   # empty between uses, see the kernel
         yacc = ws.get("d_yacc")

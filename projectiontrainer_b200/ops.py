@@ -319,8 +319,11 @@ def softmax_fwd(scores, P, keyvalid, Z, Sq, Sk, ld, heads_per_batch, causal, win
 GEMV_BF16, GEMV_F32, GEMV_F32_ATOMIC, GEMV_GEGLU, GEMV_SWIGLU = range(5)
 
 
-def gemv_ok(M: int, K: int) -> bool:
-    return 1 <= M <= 16 and K >= 32 and K % 32 == 0
+GEMV_MAX_ROWS = 32
+
+
+def gemv_ok(M: int, K: int, max_rows: int = GEMV_MAX_ROWS) -> bool:
+    return 1 <= M <= min(max_rows, GEMV_MAX_ROWS) and K >= 32 and K % 32 == 0
 
 
 def gemv(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor, mode: int = GEMV_BF16, ksplit: int = 0):

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 SHAPES = [(1536, 1152), (1152, 1024), (1152, 6912), (64, 32), (1000, 96), (262144 // 16, 1152)]
 
 
-@pytest.mark.parametrize("M", [1, 3, 8, 9, 16])
+@pytest.mark.parametrize("M", [1, 3, 8, 9, 16, 17, 32])
 @pytest.mark.parametrize("N,K", SHAPES)
 def test_store_modes_match_the_fp32_product(cuda_dev, M, N, K):
     from projectiontrainer_b200 import ops
@@ -28,7 +28,7 @@ def test_store_modes_match_the_fp32_product(cuda_dev, M, N, K):
         assert float((ob.float() - ops.linear(x.contiguous(), w).float()).abs().max()) <= 2 ** -7 * float(ref.abs().max())
 
 
-@pytest.mark.parametrize("M", [1, 5, 16])
+@pytest.mark.parametrize("M", [1, 5, 16, 32])
 @pytest.mark.parametrize("ksplit", [0, 1, 3, 27])
 def test_atomic_slices_accumulate(cuda_dev, M, ksplit):
     from projectiontrainer_b200 import ops
@@ -45,7 +45,7 @@ def test_atomic_slices_accumulate(cuda_dev, M, ksplit):
 
 
 @pytest.mark.parametrize("silu", [False, True], ids=["geglu", "swiglu"])
-@pytest.mark.parametrize("M", [1, 7, 12])
+@pytest.mark.parametrize("M", [1, 7, 12, 29])
 def test_glu_modes_match_the_fused_gemm_epilogue(cuda_dev, M, silu):
     from projectiontrainer_b200 import ops
     g = torch.Generator(device=cuda_dev).manual_seed(M)
@@ -67,10 +67,10 @@ def test_glu_modes_match_the_fused_gemm_epilogue(cuda_dev, M, silu):
 
 def test_rejects(cuda_dev):
     from projectiontrainer_b200 import ops
-    x = torch.zeros(17, 64, device=cuda_dev, dtype=torch.bfloat16)
+    x = torch.zeros(33, 64, device=cuda_dev, dtype=torch.bfloat16)
     w = torch.zeros(32, 64, device=cuda_dev, dtype=torch.bfloat16)
-    with pytest.raises(RuntimeError, match="1 .. 16"):
-        ops.gemv(x, w, torch.empty(17, 32, device=cuda_dev, dtype=torch.bfloat16))
+    with pytest.raises(RuntimeError, match="1 .. 32"):
+        ops.gemv(x, w, torch.empty(33, 32, device=cuda_dev, dtype=torch.bfloat16))
     with pytest.raises(RuntimeError, match="multiple of 32"):
         ops.gemv(x[:4, :48].contiguous(), w[:, :48].contiguous(), torch.empty(4, 32, device=cuda_dev, dtype=torch.bfloat16))
-    assert ops.gemv_ok(16, 1152) and not ops.gemv_ok(17, 1152) and not ops.gemv_ok(4, 48)
+    assert ops.gemv_ok(32, 1152) and not ops.gemv_ok(33, 1152) and not ops.gemv_ok(4, 48) and not ops.gemv_ok(17, 1152, 16)
