@@ -79,8 +79,8 @@ def decode_pair(Bd=64, n=20, reps=3):
 
 
 if "--train" not in sys.argv:
-    decode_pair()
-    decode_pair(Bd=8)
+    for bd in [int(v) for v in sys.argv[1:] if v.isdigit()] or [64, 8]:
+        decode_pair(Bd=bd)
 else:
     for rep in range(2):
         for on in (0, 1):
