@@ -1087,8 +1087,11 @@ class Stage1Engine:
         kvd = c.hkv * c.hd
         key = (B, Smax)
         if getattr(self, "_cache_key", None) != key:
-            self.cache = dict(k=[torch.zeros(B, Smax, kvd, dtype=BF16, device=dev) for _ in range(c.layers)],
-                              v=[torch.zeros(B, Smax, kvd, dtype=BF16, device=dev) for _ in range(c.layers)])
+            # one tensor per operand, [layers, B, Smax, kvd]: a layer's cache is a contiguous slice of it, and beam
+            # search re-orders the rows of all layers in one pass
+            k_all = torch.zeros(c.layers, B, Smax, kvd, dtype=BF16, device=dev)
+            v_all = torch.zeros(c.layers, B, Smax, kvd, dtype=BF16, device=dev)
+            self.cache = dict(k=list(k_all.unbind(0)), v=list(v_all.unbind(0)), k_all=k_all, v_all=v_all)
             self._cache_key = key
         self.cache.update(pos=S, B=B, Smax=Smax, valid=None, next_pos=None)
         if keyvalid is not None:
@@ -1516,10 +1519,20 @@ class Stage1Engine:
             if do_sample:                                # HF's warpers, min_tokens_to_keep = 2 under beam search
                 if temperature != 1.0:
                     lp = lp / temperature
+                vals = None
                 if top_k and top_k > 0:
-                    kth = lp.topk(min(max(top_k, 2), V), dim=1).values[:, -1:]
-                    lp = lp.masked_fill(lp < kth, float("-inf"))
-                if top_p < 1.0:
+                    vals = lp.topk(min(max(top_k, 2), V), dim=1).values          # descending
+                    lp = lp.masked_fill(lp < vals[:, -1:], float("-inf"))
+                if top_p < 1.0 and vals is not None:
+                    # after top-k the finite entries of lp ARE `vals`: HF's ascending sort + cumulative sum over the
+                    # whole row sees -inf (probability 0) and then these values, so the tokens it removes are the
+                    # r smallest of them — everything below the value of rank r (no sort of the whole vocabulary)
+                    asc = vals.flip(1)
+                    rm = asc.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
+                    rm[:, -2:] = False
+                    thr = asc.gather(1, rm.sum(dim=1, keepdim=True))
+                    lp = lp.masked_fill(lp < thr, float("-inf"))
+                elif top_p < 1.0:
                     srt, idx = lp.sort(dim=1, descending=False)
                     rm = srt.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
                     rm[:, -2:] = False
@@ -1556,9 +1569,8 @@ class Stage1Engine:
                 break
             # KV rows follow their beams (in place: the decode graph holds the cache addresses)
             rows = (run_src + torch.arange(B, device=dev)[:, None] * nb).view(-1)
-            for li in range(len(kc["k"])):
-                kc["k"][li].copy_(kc["k"][li].index_select(0, rows))
-                kc["v"][li].copy_(kc["v"][li].index_select(0, rows))
+            kc["k_all"].copy_(kc["k_all"].index_select(1, rows))
+            kc["v_all"].copy_(kc["v_all"].index_select(1, rows))
             logits = self.decode_step(run_seq[:, :, cur].reshape(-1))
         out_len = int(fin_len[:, 0].max().item())
         return fin_seq[:, 0, :max(out_len, 1)]

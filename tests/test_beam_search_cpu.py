@@ -49,7 +49,8 @@ class _OracleEngine(SimpleNamespace):
             n_img = self.X0.shape[1] - prompt_ids.shape[1]
             self.attn0 = torch.cat([torch.ones(pixels.shape[0], n_img, dtype=torch.long), (prompt_ids != prompt_pad_id).long()], 1)
         R = pixels.shape[0]
-        self.cache = {"k": [torch.zeros(R, max_new_tokens + 1)], "v": [torch.zeros(R, 1)], "n": 0}
+        k_all, v_all = torch.zeros(1, R, max_new_tokens + 1), torch.zeros(1, R, 1)      # [layers, rows, ...] like the engine's
+        self.cache = {"k": list(k_all.unbind(0)), "v": list(v_all.unbind(0)), "k_all": k_all, "v_all": v_all, "n": 0}
         return self._logits()
 
     def decode_step(self, tokens):
@@ -89,3 +90,29 @@ def test_beam_sampling_draws_valid_sequences():
     c = _beam(eng, 1, generator=torch.Generator().manual_seed(4), **kw)
     assert torch.equal(a, b) and a.shape[0] == eng.pixels.shape[0] and 1 <= a.shape[1] <= eng.new
     assert a.min() >= 0 and a.max() < eng.lc.vocab and (a.shape != c.shape or not torch.equal(a, c))
+
+
+def test_top_p_on_the_top_k_candidates_equals_hf_warpers_on_the_whole_row():
+    """Beam sampling applies HF's TopKLogitsWarper then TopPLogitsWarper (min_tokens_to_keep = 2).  After top-k the
+    finite entries of a row are the k candidates, so top-p is evaluated on them alone (a threshold value) instead of
+    through a sort of the whole vocabulary: the surviving set must be the one HF's formulation leaves."""
+    g = torch.Generator().manual_seed(0)
+    for V, k, top_p, temp in ((5000, 50, 0.9, 1.0), (5000, 50, 0.5, 0.7), (300, 2, 0.9, 1.0), (40, 50, 0.3, 1.3)):
+        lp = torch.log_softmax(torch.randn(7, V, generator=g) * 3, dim=-1) / temp
+        # HF's formulation (the previous implementation)
+        kth = lp.topk(min(max(k, 2), V), dim=1).values[:, -1:]
+        ref = lp.masked_fill(lp < kth, float("-inf"))
+        srt, idx = ref.sort(dim=1, descending=False)
+        rm = srt.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
+        rm[:, -2:] = False
+        ref = ref.masked_fill(rm.scatter(1, idx, rm), float("-inf"))
+        # the engine's
+        vals = lp.topk(min(max(k, 2), V), dim=1).values
+        new = lp.masked_fill(lp < vals[:, -1:], float("-inf"))
+        asc = vals.flip(1)
+        rm2 = asc.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
+        rm2[:, -2:] = False
+        new = new.masked_fill(new < asc.gather(1, rm2.sum(dim=1, keepdim=True)), float("-inf"))
+        assert torch.equal(torch.isfinite(ref), torch.isfinite(new)), (V, k, top_p)
+        assert torch.equal(ref[torch.isfinite(ref)], new[torch.isfinite(new)])
+        assert int(torch.isfinite(new).sum(1).min()) >= 2
