@@ -1445,11 +1445,18 @@ class Stage1Engine:
                                  top_k=top_k if do_sample else 0, top_p=top_p, u=None if u is None else u[step],
                                  done=done8, pad_id=pad_token_id, eos_id=eos_token_id)
                 n = step + 1
-                if eos_token_id is not None and bool(done8.all()):
+                # "has every row emitted eos?" costs a host sync: asked every 8th token, the exact stopping point is
+                # recovered from the tokens below (finished rows only emit pad, the uniform numbers are per step)
+                if eos_token_id is not None and (n % 8 == 0 or n == max_new_tokens) and bool(done8.all()):
                     break
                 if step + 1 < max_new_tokens:
                     logits = self.decode_step(nxt)
-            return out[:, :n]
+            out = out[:, :n]
+            if eos_token_id is not None:
+                hit = out == eos_token_id
+                if bool(hit.any(dim=1).all()):       # HF stops after the step in which the last row emits eos
+                    out = out[:, :int(hit.float().argmax(dim=1).max()) + 1]
+            return out
         done = torch.zeros(B, dtype=torch.bool, device=dev)
         for step in range(max_new_tokens):
             sc = logits.float().clone()

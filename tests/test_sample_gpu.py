@@ -175,6 +175,23 @@ def test_generate_with_the_kernel_and_with_the_torch_restatement_agree_on_greedy
     b = eng.generate(px, ids, **kw)
     assert torch.equal(a, b)
     eng.fuse_sampler = True
+    a = eng.generate(px, ids, max_new_tokens=9, do_sample=False, pad_token_id=olc.pad_id, eos_token_id=None)
+    eng.fuse_sampler = True
+    # stopping: the kernel path asks "all rows done?" only every 8th token and trims to HF's stopping point afterwards
+    for row, at in ((0, 4), (1, 0), (2, 7)):
+        eos = int(a[row, at])
+        kw1 = dict(max_new_tokens=9, do_sample=False, pad_token_id=olc.pad_id, eos_token_id=eos)
+        one = eng.generate(px[row:row + 1], ids[row:row + 1], **kw1)
+        eng.fuse_sampler = False
+        ref = eng.generate(px[row:row + 1], ids[row:row + 1], **kw1)
+        eng.fuse_sampler = True
+        assert one.shape == ref.shape and torch.equal(one, ref), (row, at, one.tolist(), ref.tolist())
+        assert one.shape[1] <= 9 and int(one[0, -1]) == eos or one.shape[1] == 9
+    both = eng.generate(px, ids, max_new_tokens=9, do_sample=False, pad_token_id=olc.pad_id, eos_token_id=int(a[0, 3]))
+    eng.fuse_sampler = False
+    both_ref = eng.generate(px, ids, max_new_tokens=9, do_sample=False, pad_token_id=olc.pad_id, eos_token_id=int(a[0, 3]))
+    eng.fuse_sampler = True
+    assert both.shape == both_ref.shape and torch.equal(both, both_ref)
     s = eng.generate(px, ids, max_new_tokens=9, do_sample=True, temperature=0.7, top_p=0.9, pad_token_id=olc.pad_id,
                      eos_token_id=1, generator=torch.Generator(device=cuda_dev).manual_seed(1))
     s2 = eng.generate(px, ids, max_new_tokens=9, do_sample=True, temperature=0.7, top_p=0.9, pad_token_id=olc.pad_id,
