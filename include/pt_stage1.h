@@ -294,8 +294,9 @@ int pt_gemv_small_m(const void* x, long long lda, int M, const void* W, long lon
  * by inverse CDF over the surviving tokens in descending order at u[b] in [0, 1) (torch.multinomial's distribution,
  * not its random stream); top_k == 0: argmax of the penalised logits (smallest index among ties).  Then HF's
  * bookkeeping: a row with done[b] != 0 emits pad_id (if >= 0); out[b * ld_out] = token; next[b] = token (optional);
- * done[b] |= token == eos_id (if >= 0).  logits f32 [B, ld >= V]. */
-int pt_sample_token(const float* logits, long long ld, int B, int V, const long long* prev, long long ld_prev, int nprev,
+ * done[b] |= token == eos_id (if >= 0).  logits f32 [B, ld >= V]; with a repetition penalty the penalised entries of
+ * logits are overwritten with their penalised values (the selection then reads the row as it is). */
+int pt_sample_token(float* logits, long long ld, int B, int V, const long long* prev, long long ld_prev, int nprev,
                     float repetition_penalty, float temperature, int top_k, float top_p, const float* u, uint8_t* done,
                     long long pad_id, long long eos_id, long long* out, long long ld_out, long long* next, void* stream);
 /* Fused backward of the same attention (autograd through HF:models/gemma3/modeling_gemma3.py:370-384, invoked at

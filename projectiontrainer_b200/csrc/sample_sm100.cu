@@ -31,7 +31,7 @@ __device__ __forceinline__ uint32_t fkey(float x) {     // order-preserving floa
 }
 
 struct SampleArgs {
-    const float* logits;            // [B, ld]
+    float* logits;                  // [B, ld]; the repetition penalty is applied to it in place
     long long ld;
     int V;
     const long long* prev;          // [B, ld_prev]: tokens generated so far (repetition penalty), or null
@@ -56,35 +56,61 @@ __global__ void __launch_bounds__(kSampThreads) sample_token_kernel(const Sample
     __shared__ float sv[kCap];
     __shared__ int si[kCap];
     __shared__ int s_cnt, s_tok;
-    __shared__ float s_bound, s_kth;
+    __shared__ float s_bound;
     __shared__ uint32_t s_lo, s_hi;
     uint32_t* bitmap = reinterpret_cast<uint32_t*>(smem_raw);   // V bits: token was generated before
     const int b = blockIdx.x, tid = threadIdx.x;
-    const float* row = p.logits + static_cast<long long>(b) * p.ld;
+    float* row = p.logits + static_cast<long long>(b) * p.ld;
     const bool pen = p.prev != nullptr && p.nprev > 0 && p.rep != 1.f;
-    if (pen) {
+    if (pen) {      // the penalty is applied IN PLACE, once per distinct token (the bitmap only de-duplicates)
         for (int i = tid; i < (p.V + 31) / 32; i += kSampThreads) bitmap[i] = 0u;
         __syncthreads();
         const long long* pr = p.prev + static_cast<long long>(b) * p.ld_prev;
         for (int i = tid; i < p.nprev; i += kSampThreads) {
             const long long t = pr[i];
-            if (t >= 0 && t < p.V) atomicOr(&bitmap[t >> 5], 1u << (t & 31));
+            if (t >= 0 && t < p.V) {
+                const uint32_t bit = 1u << (t & 31);
+                if (!(atomicOr(&bitmap[t >> 5], bit) & bit)) {
+                    const float x = row[t];
+                    row[t] = x < 0.f ? x * p.rep : x / p.rep;
+                }
+            }
         }
         __syncthreads();
     }
     auto value = [&](int i) {
-        float x = row[i];
-        if (pen && ((bitmap[i >> 5] >> (i & 31)) & 1u)) x = x < 0.f ? x * p.rep : x / p.rep;
+        const float x = row[i];
         return x != x ? -INFINITY : x;                  // a NaN logit never wins
+    };
+    // every (index, value) of the row through fn: 16-byte loads, four per thread in flight
+    auto fix = [&](int, float x) { return x != x ? -INFINITY : x; };
+    const int n4 = reinterpret_cast<uintptr_t>(row) % 16 == 0 ? p.V / 4 : 0;
+    auto scan = [&](auto&& fn) {
+        constexpr int U = 4;
+        const float4* row4 = reinterpret_cast<const float4*>(row);
+        for (int j = tid; j < n4; j += kSampThreads * U) {
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (j + u * kSampThreads < n4) v[u] = row4[j + u * kSampThreads];   // (plain loads: the row was just patched)
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = 4 * (j + u * kSampThreads);
+                if (i < 4 * n4) {
+                    fn(i, fix(i, v[u].x)); fn(i + 1, fix(i + 1, v[u].y));
+                    fn(i + 2, fix(i + 2, v[u].z)); fn(i + 3, fix(i + 3, v[u].w));
+                }
+            }
+        }
+        for (int i = 4 * n4 + tid; i < p.V; i += kSampThreads) fn(i, fix(i, row[i]));
     };
 
     // pass 1: per-thread maximum (smallest index on ties)
     float m = -INFINITY;
     int am = p.V;
-    for (int i = tid; i < p.V; i += kSampThreads) {
-        const float x = value(i);
+    scan([&](int i, float x) {
         if (x > m || (x == m && i < am)) { m = x; am = i; }
-    }
+    });
     s_max[tid] = m;
     s_arg[tid] = am;
     __syncthreads();
@@ -104,24 +130,47 @@ __global__ void __launch_bounds__(kSampThreads) sample_token_kernel(const Sample
         // the k-th largest thread maximum is <= the k-th largest value (k <= 1024; beyond that: no bound)
         if (tid == 0) { s_bound = -INFINITY; s_cnt = 0; }
         __syncthreads();
-        if (k <= kSampThreads) {
-            int rank = 0;
-            for (int j = 0; j < kSampThreads; ++j) {
-                const float o = s_max[j];
-                rank += (o > m) || (o == m && j < tid);
+        if (k <= kSampThreads) {    // radix select over the 1024 ordered keys, 8 bits a pass
+            uint32_t* hist = reinterpret_cast<uint32_t*>(sv);    // 256 bins (sv is free until the ranking below)
+            const uint32_t key = fkey(m);
+            uint32_t prefix = 0;
+            int want = k;
+#pragma unroll 1
+            for (int pass = 0; pass < 4; ++pass) {
+                const int shift = 24 - 8 * pass;
+                if (tid < 256) hist[tid] = 0u;
+                __syncthreads();
+                if (pass == 0 || (key >> (shift + 8)) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+                __syncthreads();
+                if (tid == 0) {                          // the bin that holds the want-th largest of the matching keys
+                    int above = 0, bin = 255;
+                    for (; bin > 0; --bin) {
+                        const int c = static_cast<int>(hist[bin]);
+                        if (above + c >= want) break;
+                        above += c;
+                    }
+                    s_lo = static_cast<uint32_t>(bin);
+                    s_hi = static_cast<uint32_t>(above);
+                }
+                __syncthreads();
+                prefix = (prefix << 8) | s_lo;
+                want -= static_cast<int>(s_hi);
+                __syncthreads();
             }
-            if (rank == k - 1) s_bound = m;
+            if (tid == 0) {
+                const uint32_t u = prefix ^ ((prefix >> 31) ? 0x80000000u : 0xffffffffu);
+                s_bound = __uint_as_float(u);
+            }
         }
         __syncthreads();
         // pass 2: collect everything >= the bound; raise the bound by bisection while it lets too much through
         auto collect = [&](float bound) {
-            for (int i = tid; i < p.V; i += kSampThreads) {
-                const float x = value(i);
+            scan([&](int i, float x) {
                 if (x >= bound) {
                     const int at = atomicAdd(&s_cnt, 1);
                     if (at < kCap) { cv[at] = x; ci[at] = i; }
                 }
-            }
+            });
             __syncthreads();
         };
         collect(s_bound);
@@ -136,7 +185,7 @@ __global__ void __launch_bounds__(kSampThreads) sample_token_kernel(const Sample
                 if (tid == 0) s_cnt = 0;
                 __syncthreads();
                 int c = 0;
-                for (int i = tid; i < p.V; i += kSampThreads) c += fkey(value(i)) >= mid;
+                scan([&](int, float x) { c += fkey(x) >= mid; });
                 atomicAdd(&s_cnt, c);
                 __syncthreads();
                 const int tot = s_cnt;
@@ -148,13 +197,12 @@ __global__ void __launch_bounds__(kSampThreads) sample_token_kernel(const Sample
                 __syncthreads();
                 if (s_cnt == 0) {                         // collect at this bound
                     const uint32_t bk = s_lo;
-                    for (int i = tid; i < p.V; i += kSampThreads) {
-                        const float x = value(i);
+                    scan([&](int i, float x) {
                         if (fkey(x) >= bk) {
                             const int at = atomicAdd(&s_cnt, 1);
                             if (at < kCap) { cv[at] = x; ci[at] = i; }
                         }
-                    }
+                    });
                     __syncthreads();
                     break;
                 }
@@ -164,13 +212,12 @@ __global__ void __launch_bounds__(kSampThreads) sample_token_kernel(const Sample
                 if (tid == 0) s_cnt = 0;                 // equal logits has the same probability)
                 __syncthreads();
                 const uint32_t bk = s_lo;
-                for (int i = tid; i < p.V; i += kSampThreads) {
-                    const float x = value(i);
+                scan([&](int i, float x) {
                     if (fkey(x) > bk) {
                         const int at = atomicAdd(&s_cnt, 1);
                         if (at < kCap) { cv[at] = x; ci[at] = i; }
                     }
-                }
+                });
                 __syncthreads();
                 if (tid == 0) {
                     int n = s_cnt < kCap ? s_cnt : kCap;
@@ -240,7 +287,7 @@ __global__ void __launch_bounds__(kSampThreads) sample_token_kernel(const Sample
 
 using namespace pt;
 
-extern "C" int pt_sample_token(const float* logits, long long ld, int B, int V, const long long* prev, long long ld_prev,
+extern "C" int pt_sample_token(float* logits, long long ld, int B, int V, const long long* prev, long long ld_prev,
                                int nprev, float repetition_penalty, float temperature, int top_k, float top_p,
                                const float* u, uint8_t* done, long long pad_id, long long eos_id, long long* out,
                                long long ld_out, long long* next, void* stream) {

@@ -345,7 +345,8 @@ def sample_token(logits, *, out, step, next_tokens=None, prev=None, repetition_p
                  top_p=1.0, u=None, done=None, pad_id=None, eos_id=None):
     """The next token of every row (HF's processor order: repetition penalty, temperature, top-k, top-p, one draw at
     u[b]; top_k = 0: argmax) and HF's finished-row bookkeeping, written to out[:, step] (i64 [B, n]) and next_tokens.
-    logits f32 [B, V] (row stride >= V); prev = out: the tokens out[:, :step] are the penalised ones."""
+    logits f32 [B, V] (row stride >= V); prev = out: the tokens out[:, :step] are the penalised ones — their logits
+    are overwritten with the penalised values."""
     _req_cuda(logits, out, next_tokens, prev, u, done)
     B, V = logits.shape
     if logits.dtype != torch.float32 or logits.stride(1) != 1 or out.dtype != torch.int64 or out.stride(1) != 1:

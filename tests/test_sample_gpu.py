@@ -47,6 +47,9 @@ def _run(dev, logits, *, step, prev_tokens, rp, temperature, top_k, top_p, u, do
     if prev_tokens is not None:
         out[:, :step] = prev_tokens
     nxt = torch.full((B,), -1, dtype=torch.int64, device=dev)
+    hold = torch.empty(B, max(logits.stride(0), logits.shape[1]), device=dev)     # a repetition penalty is applied to
+    hold[:, :logits.shape[1]] = logits                                            # the logits in place: work on a copy
+    logits = hold[:, :logits.shape[1]]                                            # with the caller's row stride
     ops.sample_token(logits, out=out, step=step, next_tokens=nxt, prev=out if prev_tokens is not None else None,
                      repetition_penalty=rp, temperature=temperature, top_k=top_k, top_p=top_p, u=u, done=done,
                      pad_id=pad, eos_id=eos)
