@@ -8,20 +8,24 @@
 //   K[b, slot] = k_new, V[b, slot] = v_new                                     (the cache append)
 //   o_g  = softmax_k(scale * q_g . K[b, k]) V[b, k]   over  k in [lo, slot],  valid[b, k] != 0,
 //          lo = window > 0 ? max(0, slot - window + 1) : 0
-// Layout: the keys of one (sample, kv head) are split, in tiles of 64, over a CLUSTER of nsplit CTAs
-// (flash-decoding).  A CTA stages a K/V tile in shared memory with 16-byte cp.async (K rows padded by 16 bytes: the
-// per-key reads below are bank-conflict free), then
-//   scores: warp w takes keys 8w..8w+7 of the tile: S[G x 8] = Q[G x HD] K^T on mma.sync m16n8k16 (the G <= 8 query
-//           heads of the group are rows 0..G-1 of the 16-row A operand, kept in registers for the whole launch);
+// Layout: the keys of one (sample, kv head) are split, in tiles of 32, over a CLUSTER of nsplit CTAs
+// (flash-decoding).  A CTA stages K/V tiles in a two-stage shared-memory ring with 16-byte cp.async (unpadded rows,
+// chunks XOR-swizzled so that the fragment reads below are bank-conflict free), then, per tile,
+//   scores: warp w takes keys 8 (w & 3) .. + 7 and half of the contraction (w >> 2):
+//           S[G x 8] = Q[G x HD] K^T on mma.sync m16n8k16 (the G <= 8 query heads of the group are rows 0..G-1 of the
+//           16-row A operand, kept in registers for the whole launch; the contraction index is permuted inside each
+//           32-wide chunk so that a lane's K fragments of two k-steps are one 16-byte read);
 //   softmax + P V: every warp turns the scores of its lanes' query head into the A fragments of the P V product in
 //           registers (a quad of lanes holds the 32 scores of a head: two shuffle steps give the tile maximum and
 //           sum; every warp keeps the same running (max, sum)), then takes channel blocks of 8:
 //           O[G x 8] += P[G x 32] V[32 x 8], V fragments by ldmatrix.trans.  Two block barriers per tile.
-// (tcgen05 does not fit here: its M is 64+ rows and a decode step has G = 1..8 per K/V row — the kernel is bound by
-// the K/V bytes, the tensor cores only have to keep the arithmetic out of the way, which mma.sync does.)
+// (tcgen05 does not fit here: its M is 64+ rows and a decode step has G = 1..8 per K/V row; the tensor cores only
+// have to keep the arithmetic out of the way, which mma.sync does.)
 // The CTAs of the cluster merge their (max, sum, o) through distributed shared memory into rank 0, which writes
 // the bf16 output row.  The CTA that owns the tile containing `slot` appends this token's k / v to the cache.
-// HBM-bound by the K/V rows it reads: 2 * (slot - lo + 1) * HD * 2 bytes per (sample, kv head).
+// Algorithmic bytes: the K/V rows it reads, 2 * (slot - lo + 1) * HD * 2 per (sample, kv head) — and that is what it
+// reads (ncu: 42.22 MB against 42.0 MB at B = 64).  It runs at 2.8 of 7.7 TB/s there: bound by the instruction stream
+// of a tile at two warps per scheduler and by ~5.5 us that do not depend on the key count, not by HBM.
 // (Versions without tensor cores — a warp per key with shuffle reductions, then a thread per (key, head) — were
 // bound by latency / the FMA pipe at 0.65 and 1.6 TB/s; see profiles/r02_decode_attn.txt.)
 #include <cooperative_groups.h>
