@@ -69,7 +69,15 @@ typedef enum {
      * sum(exp(x - max)) of the bf16-ROUNDED logits (what a pass over the stored logits would see).
      * pt_ce_from_partials turns them into the row log-sum-exps: one 2.1 GB read of the logits less per step.
      * No bias / residual / C_pre / alpha, not batched; 256-wide tiles. */
-    PT_ACT_CE_STATS = 10
+    PT_ACT_CE_STATS = 10,
+    /* Per-head q/k RMSNorm + rotary embedding (pt_qknorm_rope_fwd, HF:models/gemma3/modeling_gemma3.py:362-368,233-263)
+     * in the epilogue of the fused q|k|v projection, head_dim 256 (a 256-wide tile IS one head): C [M, N] bf16
+     * receives the projection as usual (the backward reads it), aux [M, aux_i1 * 256] bf16 (row stride ld_aux)
+     * receives the rotated q heads and aux2 [M, hkv * 256] bf16 (dense) the rotated k heads, hkv = (N / 256 - aux_i1) / 2.
+     * bias = the norm gains f32 [512] = [q gains | k gains] (applied as 1 + w); residual = the rotary table f32
+     * [aux_i0, 256] = [cos (128) | sin (128)] per position, position of row r = r %% aux_i0; eps = the norm's epsilon.
+     * The sum of squares runs over the bf16-rounded projection, as the separate kernel's does.  Not batched. */
+    PT_ACT_QKNORM_ROPE = 11
 } pt_act;
 
 typedef enum {
@@ -180,6 +188,7 @@ typedef struct {
      * C_pre / band / K groups / K2.  For products with a long contraction and a small output (the adapters' weight
      * gradients); the summation order, hence the last bits of C, varies from run to run. */
     int32_t ksplit;
+    float eps;                /* PT_ACT_QKNORM_ROPE: RMSNorm epsilon */
 } pt_gemm_args;
 
 int pt_gemm_bf16(const pt_gemm_args* args, void* stream);

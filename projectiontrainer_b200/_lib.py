@@ -16,7 +16,7 @@ LIB_PATH = Path(os.environ.get("PT_STAGE1_LIB") or PKG / "libpt_stage1.so")
 PT_BF16, PT_F32, PT_I64, PT_I32 = 0, 1, 2, 3
 BAND_NONE, BAND_SCORES, BAND_K_BY_QUERY, BAND_K_BY_KEY = 0, 1, 2, 3
 ACT_NONE, ACT_GELU_TANH, ACT_GELU_ERF, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD = 0, 1, 2, 3, 4, 5
-ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GELU_ERF_BWD, ACT_ATTN_DELTA, ACT_CE_STATS = 6, 7, 8, 9, 10
+ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GELU_ERF_BWD, ACT_ATTN_DELTA, ACT_CE_STATS, ACT_QKNORM_ROPE = 6, 7, 8, 9, 10, 11
 
 
 class GemmArgs(C.Structure):
@@ -37,6 +37,7 @@ class GemmArgs(C.Structure):
         ("aux2", C.c_void_p), ("aux_i0", C.c_int32), ("aux_i1", C.c_int32),
         ("A2", C.c_void_p), ("lda2", C.c_int64), ("B2", C.c_void_p), ("ldb2", C.c_int64), ("K2", C.c_int32),
         ("ksplit", C.c_int32),
+        ("eps", C.c_float),
     ]
 
 

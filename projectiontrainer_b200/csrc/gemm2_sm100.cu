@@ -766,6 +766,85 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     o.C = static_cast<uint8_t*>(p.aux) + (static_cast<long long>(row0) * p.ld_aux + colg) * 2;
                     epi_chunk<PT_ACT_NONE>(vg, stg, lane, o);
                 }
+            } else if constexpr (ACT == PT_ACT_QKNORM_ROPE) {
+                // The 256-wide tile n_blk is head n_blk of the fused q|k|v row (q heads, then k heads, then v heads).
+                // A warp owns 32 rows (TMEM lanes) and may read every column of them: it sums the squares of the whole
+                // head itself (both warps of a row quadrant do: no exchange), then, like the GeGLU epilogue, takes two
+                // 32-column chunks of the first half together with their rotary partners 128 columns further on.
+                const bool live = rows_valid > row_lo;                                   // warp-uniform
+                const int hq_ = p.dl_hq, hkv_ = (p.N / 256 - hq_) / 2;
+                const bool rot = n_blk < hq_ + hkv_;
+                float rstd = 0.f;
+                if (live && rot) {
+                    float ssq = 0.f;
+#pragma unroll 1
+                    for (int c8 = 0; c8 < 8; ++c8) {
+                        uint32_t v[32];
+                        ptx::tmem_ld_32x32(taddr + c8 * 32, v);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float x = round_bf16(__uint_as_float(v[j]));   // what the stored projection holds
+                            ssq = fmaf(x, x, ssq);
+                        }
+                    }
+                    rstd = rsqrtf(ssq * (1.f / 256.f) + p.qn_eps);
+                }
+                const float* gw = p.bias + (n_blk < hq_ ? 0 : 256);
+                const float* cs = static_cast<const float*>(p.R) + static_cast<long long>((row0 + lane) % p.dl_S) * 256;
+#pragma unroll 1
+                for (int c2 = 0; c2 < 2; ++c2) {
+                    const int cg = (hf * 2 + c2) * 32;
+                    uint32_t v1[32], v2[32];
+                    if (live) {
+                        ptx::tmem_ld_32x32(taddr + cg, v1);
+                        ptx::tmem_ld_32x32(taddr + BNH + cg, v2);
+                        ptx::tmem_ld_wait();
+                    }
+                    if (c2 == 1) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty_bar[acc]), 0));
+                    }
+                    if (!live) continue;
+                    EpiArgs o;
+                    o.Cpre = nullptr; o.R = nullptr; o.bias = nullptr;
+                    o.p_row = 0; o.p_step = 0; o.r_row = 0; o.r_step = 0;
+                    o.c_f32 = 0; o.r_f32 = 0; o.alpha = 1.f; o.c_atomic = 0;
+                    o.rows_valid = rows_valid; o.row_lo = row_lo; o.cols_q = 32;
+                    o.c_row = p.ldc * 2; o.c_step = 4 * o.c_row;
+                    uint8_t* crow = static_cast<uint8_t*>(p.C) + (coff + static_cast<long long>(row0) * p.ldc) * 2;
+                    o.C = crow + static_cast<long long>(n_blk * 256 + cg) * 2;
+                    epi_chunk<PT_ACT_NONE>(v1, stg, lane, o);
+                    o.C = crow + static_cast<long long>(n_blk * 256 + BNH + cg) * 2;
+                    epi_chunk<PT_ACT_NONE>(v2, stg, lane, o);
+                    if (!rot) continue;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 c4 = *reinterpret_cast<const float4*>(cs + cg + j);
+                        const float4 s4 = *reinterpret_cast<const float4*>(cs + 128 + cg + j);
+                        const float4 g1 = *reinterpret_cast<const float4*>(gw + cg + j);
+                        const float4 g2 = *reinterpret_cast<const float4*>(gw + 128 + cg + j);
+                        const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+                        const float w1[4] = {g1.x, g1.y, g1.z, g1.w}, w2[4] = {g2.x, g2.y, g2.z, g2.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float n1 = round_bf16(__uint_as_float(v1[j + e])) * rstd * (1.f + w1[e]);
+                            const float n2 = round_bf16(__uint_as_float(v2[j + e])) * rstd * (1.f + w2[e]);
+                            v1[j + e] = __float_as_uint(n1 * cc[e] - n2 * ss[e]);
+                            v2[j + e] = __float_as_uint(n2 * cc[e] + n1 * ss[e]);
+                        }
+                    }
+                    const bool isq = n_blk < hq_;
+                    const long long ldo = isq ? p.ld_aux : static_cast<long long>(hkv_) * 256;
+                    uint8_t* orow = (isq ? static_cast<uint8_t*>(p.aux) : reinterpret_cast<uint8_t*>(p.delta)) +
+                                    (static_cast<long long>(row0) * ldo + (isq ? n_blk : n_blk - hq_) * 256) * 2;
+                    o.c_row = ldo * 2; o.c_step = 4 * o.c_row;
+                    o.C = orow + static_cast<long long>(cg) * 2;
+                    epi_chunk<PT_ACT_NONE>(v1, stg, lane, o);
+                    o.C = orow + static_cast<long long>(BNH + cg) * 2;
+                    epi_chunk<PT_ACT_NONE>(v2, stg, lane, o);
+                }
             } else {
             [[maybe_unused]] float ce_m = -INFINITY, ce_s = 0.f;       // PT_ACT_CE_STATS: this lane's row, this half tile
 #pragma unroll 1
@@ -953,6 +1032,10 @@ int launch_gemm2(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUt
     if (p.act == PT_ACT_CE_STATS) {
         if (bn != 256) { set_error("gemm2: the CE-statistics epilogue needs BN = 256"); return PT_ERR_INVALID; }
         return launch_gemm2_t<256, PT_ACT_CE_STATS>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);
+    }
+    if (p.act == PT_ACT_QKNORM_ROPE) {
+        if (bn != 256) { set_error("gemm2: the q/k-norm + RoPE epilogue needs BN = 256"); return PT_ERR_INVALID; }
+        return launch_gemm2_t<256, PT_ACT_QKNORM_ROPE>(ta, tb, t_aux, t_c, ta2, tb2, p, tiles, st);
     }
     if (p.act == PT_ACT_GEGLU) {
         if (bn != 256) { set_error("gemm2: the fused GeGLU epilogue needs BN = 256"); return PT_ERR_INVALID; }

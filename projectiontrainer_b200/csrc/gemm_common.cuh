@@ -54,6 +54,9 @@ struct GemmDev {
     // adds (vector atomics) into the f32 C — thin weight-gradient products whose output has fewer tiles than the
     // GPU has SM pairs (LoRA: dA [64, in], dB_i [out_i, r] contracted over all B*S rows)
     int ksplit, kb_per;
+    // PT_ACT_QKNORM_ROPE re-uses aux / ld_aux (rotated q), delta (rotated k, bf16), bias (gains [q | k]), R (rotary
+    // table [S][cos | sin]), dl_S (S) and dl_hq (query heads); its epsilon:
+    float qn_eps;
 };
 
 // K-block range [lo, hi) a tile must contract over, or skip = true when the whole tile is masked.

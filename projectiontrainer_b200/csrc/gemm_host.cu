@@ -196,7 +196,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     }
     PT_REQUIRE((a->N % 4) == 0 || ((!a->bias || a->act == PT_ACT_SOFTMAX_BWD) && !a->residual && !a->C_pre),
                "pt_gemm_bf16: bias / residual / C_pre need N %% 4 == 0 (N=%d)", a->N);
-    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_CE_STATS, "pt_gemm_bf16: bad act %d", a->act);
+    PT_REQUIRE(a->act >= PT_ACT_NONE && a->act <= PT_ACT_QKNORM_ROPE, "pt_gemm_bf16: bad act %d", a->act);
     if (a->act == PT_ACT_CE_STATS) {
         PT_REQUIRE(a->aux2 != nullptr && (reinterpret_cast<uintptr_t>(a->aux2) & 7) == 0,
                    "pt_gemm_bf16: PT_ACT_CE_STATS needs aux2 = the f32 partials buffer [2 * ceil(N / 256)][M][2]");
@@ -217,6 +217,19 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
                        a->N % a->aux_i1 == 0 && a->M % a->aux_i0 == 0,
                    "pt_gemm_bf16: PT_ACT_ATTN_DELTA needs aux2 = delta, aux_i0 = S (M %% S == 0), aux_i1 = head_dim "
                    "(%% 128 == 0) and N %% 256 == 0");
+    }
+    if (a->act == PT_ACT_QKNORM_ROPE) {
+        PT_REQUIRE(a->aux && a->aux2 && a->bias && a->residual && a->r_dtype == PT_F32 && a->aux_i0 > 0 && a->aux_i1 > 0,
+                   "pt_gemm_bf16: PT_ACT_QKNORM_ROPE needs aux = q out, aux2 = k out, bias = gains, residual = f32 rotary "
+                   "table, aux_i0 = table rows, aux_i1 = query heads");
+        PT_REQUIRE(a->N % 256 == 0 && a->N / 256 > a->aux_i1 && (a->N / 256 - a->aux_i1) % 2 == 0,
+                   "pt_gemm_bf16: PT_ACT_QKNORM_ROPE needs N = (hq + 2 hkv) * 256");
+        PT_REQUIRE(a->c_dtype == PT_BF16 && !a->C_pre && a->alpha == 1.0f && a->nz[0] * a->nz[1] * a->nz[2] == 1 &&
+                       kg == 1 && a->band == PT_BAND_NONE && a->ksplit <= 1,
+                   "pt_gemm_bf16: PT_ACT_QKNORM_ROPE takes bf16 C, no C_pre / alpha / batch / K groups / band / split-K");
+        PT_REQUIRE(a->ld_aux >= a->aux_i1 * 256 && a->ld_aux % 8 == 0 && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0 &&
+                       (reinterpret_cast<uintptr_t>(a->aux2) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->residual) & 15) == 0,
+                   "pt_gemm_bf16: PT_ACT_QKNORM_ROPE: aux / aux2 / table misaligned or ld_aux too small");
     }
     const bool silu = a->act == PT_ACT_SWIGLU || a->act == PT_ACT_SWIGLU_BWD;
     const bool geglu = a->act == PT_ACT_GEGLU || a->act == PT_ACT_SWIGLU;
@@ -287,6 +300,10 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
         p.dl_S = a->aux_i0; p.dl_hd = a->aux_i1; p.dl_hq = a->N / a->aux_i1;
     }
     if (a->act == PT_ACT_CE_STATS) p.delta = static_cast<float*>(a->aux2);
+    if (a->act == PT_ACT_QKNORM_ROPE) {
+        p.delta = static_cast<float*>(a->aux2);              // (bf16 rows: the kernel casts)
+        p.dl_S = a->aux_i0; p.dl_hq = a->aux_i1; p.dl_hd = 256; p.qn_eps = a->eps;
+    }
     PT_REQUIRE(a->band >= PT_BAND_NONE && a->band <= PT_BAND_K_BY_KEY && a->band_window >= 0,
                "pt_gemm_bf16: bad band %d / window %d", a->band, a->band_window);
     p.band = a->band; p.band_w = a->band_window;
@@ -295,7 +312,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_args* a, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUtensorMap ta, tb;
     // CTA-pair kernel (gemm2_sm100.cu): 256 x bn tiles, one per cluster of two SMs
-    const bool wide_only = geglu || a->act == PT_ACT_ATTN_DELTA || a->act == PT_ACT_CE_STATS;
+    const bool wide_only = geglu || a->act == PT_ACT_ATTN_DELTA || a->act == PT_ACT_CE_STATS || a->act == PT_ACT_QKNORM_ROPE;
     int bn = wide_only ? 256 : pick_bn2(a->M, a->N, nbatch, p.b_mn);
     if (!wide_only && a->bn_hint != 0) {
         PT_REQUIRE(a->bn_hint == 64 || a->bn_hint == 128 || a->bn_hint == 192 || a->bn_hint == 256,

@@ -248,6 +248,11 @@ class Stage1Engine:
         # of the 256-row tcgen05 tile
         self.decode_gemv = os.environ.get("PT_STAGE1_DECODE_GEMV", "1") != "0"
         self.decode_gemv_rows = int(os.environ.get("PT_STAGE1_DECODE_GEMV_ROWS", "16"))
+        # q/k RMSNorm + RoPE in the epilogue of the q|k|v projection (PT_ACT_QKNORM_ROPE, head_dim 256).  Built, pinned
+        # (tests/test_gemm_gpu.py) and measured: the epilogue of this short-K GEMM is already its bottleneck, and a second
+        # pass over TMEM for the sum of squares, the per-row rotary table reads and two more output chunks per pair make
+        # it 164 us against 127 us for the projection + pt_qknorm_rope_fwd (step +0.3 .. +2 ms): off
+        self.fuse_qknorm = os.environ.get("PT_STAGE1_FUSE_QKNORM", "0") != "0"
         # generate(): the next-token choice (HF processors + draw + bookkeeping) as one launch per token
         # (0: the same logic in torch ops on the [B, V] logits, also what top_k = 0 / > 1024 takes)
         self.fuse_sampler = os.environ.get("PT_STAGE1_FUSE_SAMPLER", "1") != "0"
@@ -447,6 +452,17 @@ class Stage1Engine:
             flat = pos_ids.reshape(-1)
             tabs = {f: (t[0].index_select(0, flat), t[1].index_select(0, flat)) for f, t in tabs.items()}
             rope_rows = M
+        cs_tabs = {}
+        if self.fuse_qknorm and hd == 256:      # [cos | sin] per position, as the q|k|v projection's epilogue reads it
+            for f, t in tabs.items():
+                key = ("cs", S, f)
+                if pos_ids is not None or key not in self._rope:
+                    cs = torch.cat([t[0], t[1]], dim=1).contiguous()
+                    if pos_ids is not None:
+                        cs_tabs[f] = cs
+                        continue
+                    self._rope[key] = cs
+                cs_tabs[f] = self._rope[key]
         for li, L in enumerate(Lm.layers):
             tag = f"l{li}_" if save else "l_"
             full = c.is_full(li)
@@ -477,9 +493,15 @@ class Stage1Engine:
                 _ts[g] = t
                 return dict(x2=t, w2=grp.B(lo.shadow))
 
-            ops.linear(a_in, L["qkv_w"], out=qkv, **adapter("qkv", a_in))
-            ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, rope_rows, hq,
-                                hkv, hd, c.eps)
+            if self.fuse_qknorm and hd == 256:
+                if "qk_gains" not in L:
+                    L["qk_gains"] = torch.cat([L["q_norm"], L["k_norm"]]).contiguous()
+                ops.linear_qknorm_rope(a_in, L["qkv_w"], qkv, q_post, k_post, L["qk_gains"], cs_tabs[full], hq, c.eps,
+                                       **adapter("qkv", a_in))
+            else:
+                ops.linear(a_in, L["qkv_w"], out=qkv, **adapter("qkv", a_in))
+                ops.qknorm_rope_fwd(qkv, L["q_norm"], L["k_norm"], cos_t, sin_t, q_post, k_post, rope_rows, hq,
+                                    hkv, hd, c.eps)
             if cache is not None:      # KV-cache fill: device-to-device copies (plumbing, no arithmetic)
                 cache["k"][li][:, :S].copy_(k_post.view(B, S, hkv * hd))
                 cache["v"][li][:, :S].copy_(qkv.view(B, S, QKV)[:, :, (hq + hkv) * hd:])

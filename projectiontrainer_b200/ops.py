@@ -12,7 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import BAND_K_BY_KEY, BAND_K_BY_QUERY, BAND_NONE, BAND_SCORES  # noqa: F401
-from ._lib import ACT_CE_STATS, ACT_ATTN_DELTA, ACT_GELU_ERF_BWD, ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
+from ._lib import ACT_QKNORM_ROPE, ACT_CE_STATS, ACT_ATTN_DELTA, ACT_GELU_ERF_BWD, ACT_SWIGLU, ACT_SWIGLU_BWD, ACT_GEGLU, ACT_GEGLU_BWD, ACT_SOFTMAX_BWD, ACT_GELU_ERF, ACT_GELU_TANH, ACT_NONE, PT_BF16, PT_F32, GemmArgs
 
 _DT = {torch.bfloat16: PT_BF16, torch.float32: PT_F32}
 
@@ -39,7 +39,7 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
              c_zs=(0, 0, 0), a_mn=False, b_mn=False, bias=None, residual=None, ldr=0,
              r_zs=(0, 0, 0), act=ACT_NONE, alpha=1.0, c_pre=None, kg=1, a_kgs=0, b_kgs=0,
              a_off=0, b_off=0, c_off=0, r_off=0, aux=None, ld_aux=0, band=0, band_window=0, bn_hint=0,
-             aux2=None, aux_i0=0, aux_i1=0, A2=None, lda2=0, B2=None, ldb2=0, K2=0, ksplit=0):
+             aux2=None, aux_i0=0, aux_i1=0, A2=None, lda2=0, B2=None, ldb2=0, K2=0, ksplit=0, eps=0.0):
     """Fully general launcher; A/B/Cout are tensors used only as base pointers
     (+ element offsets), all geometry comes from the explicit arguments."""
     _req_cuda(A, B, Cout, bias, residual, c_pre, aux)
@@ -90,6 +90,7 @@ def gemm_raw(*, M, N, K, A, lda, B, ldb, Cout, ldc, nz=(1, 1, 1), a_zs=(0, 0, 0)
             raise RuntimeError("gemm operands must be bf16")
         g.A2, g.lda2, g.B2, g.ldb2, g.K2 = A2.data_ptr(), int(lda2), B2.data_ptr(), int(ldb2), int(K2)
     g.ksplit = int(ksplit)
+    g.eps = float(eps)
     if GEMM_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -174,6 +175,23 @@ def linear_geglu(x: torch.Tensor, w_gu: torch.Tensor, gu: torch.Tensor, act: tor
     N = w_gu.shape[0]
     gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w_gu, ldb=w_gu.stride(0), Cout=gu, ldc=gu.stride(0),
              act=ACT_SWIGLU if silu else ACT_GEGLU, aux=act, ld_aux=act.stride(0), **_seg2(M, N, x2, w2, False))
+
+
+def linear_qknorm_rope(x: torch.Tensor, w_qkv: torch.Tensor, qkv: torch.Tensor, q_out: torch.Tensor, k_out: torch.Tensor,
+                       gains: torch.Tensor, table: torch.Tensor, hq: int, eps: float, x2=None, w2=None):
+    """qkv[M, (hq+2hkv)*256] = x @ w_qkv^T (kept for the backward) and, in the same epilogue, the per-head q/k RMSNorm +
+    rotary embedding of pt_qknorm_rope_fwd: q_out [M, hq*256], k_out [M, hkv*256].  gains f32 [512] = [q | k] norm
+    gains; table f32 [S, 256] = [cos | sin] per position (position of row r = r % S).  head_dim 256 only."""
+    M, K = x.shape
+    N = w_qkv.shape[0]
+    hkv = (N // 256 - hq) // 2
+    if gains.dtype != torch.float32 or gains.numel() != 512 or table.dtype != torch.float32 or table.shape[1] != 256 \
+            or not table.is_contiguous() or tuple(q_out.shape) != (M, hq * 256) or tuple(k_out.shape) != (M, hkv * 256) \
+            or not k_out.is_contiguous() or q_out.dtype != torch.bfloat16 or k_out.dtype != torch.bfloat16:
+        raise RuntimeError("linear_qknorm_rope: gains f32 [512], table f32 [S, 256], q_out / k_out bf16 [M, heads * 256]")
+    gemm_raw(M=M, N=N, K=K, A=x, lda=x.stride(0), B=w_qkv, ldb=w_qkv.stride(0), Cout=qkv, ldc=qkv.stride(0),
+             act=ACT_QKNORM_ROPE, aux=q_out, ld_aux=q_out.stride(0), aux2=k_out, aux_i0=table.shape[0], aux_i1=hq,
+             bias=gains, residual=table, ldr=256, eps=eps, **_seg2(M, N, x2, w2, False))
 
 
 def linear_dgrad_geglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, d_gu: torch.Tensor,

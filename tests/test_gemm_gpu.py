@@ -393,3 +393,39 @@ def test_gemm_split_k_accumulates_into_f32_output(cuda_dev, T, N, K):
         _check(out, ref, tol=2e-3, name=f"ksplit {ks}")
     with pytest.raises(RuntimeError, match="split-K"):
         ops.gemm_raw(M=N, N=K, K=T, A=a, lda=Tp, B=b, ldb=Tp, Cout=out.to(torch.bfloat16), ldc=K, ksplit=2)
+
+
+@pytest.mark.parametrize("M,S,K,hq,hkv,seg", [(1406, 703, 1152, 4, 1, False), (300, 100, 512, 8, 4, False),
+                                               (22496, 703, 1152, 4, 1, False), (831, 831, 1152, 4, 1, True)])
+def test_qknorm_rope_epilogue_equals_the_separate_kernel(cuda_dev, M, S, K, hq, hkv, seg):
+    """PT_ACT_QKNORM_ROPE: per-head q/k RMSNorm + RoPE in the epilogue of the q|k|v projection (a 256-wide tile is one
+    head) against the projection followed by pt_qknorm_rope_fwd.  The stored projection must be bit-identical; the
+    rotated heads differ only through the order of the 256-term sum of squares (one bf16 ulp at most)."""
+    from projectiontrainer_b200 import ops
+    hd = 256
+    N = (hq + 2 * hkv) * hd
+    g = torch.Generator(device=cuda_dev).manual_seed(M + K)
+    x = torch.randn(M, K, generator=g, device=cuda_dev).bfloat16()
+    w = (torch.randn(N, K, generator=g, device=cuda_dev) * K ** -0.5).bfloat16()
+    wq, wk = torch.randn(hd, generator=g, device=cuda_dev) * 0.3, torch.randn(hd, generator=g, device=cuda_dev) * 0.3
+    ang = torch.rand(S, hd // 2, generator=g, device=cuda_dev) * 6.28
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    kw = {}
+    if seg:
+        kw = dict(x2=torch.randn(M, 64, generator=g, device=cuda_dev).bfloat16(),
+                  w2=(torch.randn(N, 64, generator=g, device=cuda_dev) * 0.05).bfloat16())
+    qkv_ref = ops.linear(x, w, **kw)
+    q_ref = torch.empty(M, hq * hd, device=cuda_dev, dtype=torch.bfloat16)
+    k_ref = torch.empty(M, hkv * hd, device=cuda_dev, dtype=torch.bfloat16)
+    ops.qknorm_rope_fwd(qkv_ref, wq, wk, cos, sin, q_ref, k_ref, S, hq, hkv, hd, 1e-6)
+    qkv = torch.full((M, N), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    q = torch.full((M, hq * hd), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    k = torch.full((M, hkv * hd), float("nan"), device=cuda_dev, dtype=torch.bfloat16)
+    ops.linear_qknorm_rope(x, w, qkv, q, k, torch.cat([wq, wk]), torch.cat([cos, sin], 1).contiguous(), hq, 1e-6, **kw)
+    torch.cuda.synchronize()
+    assert torch.equal(qkv, qkv_ref)
+    for got, ref, name in ((q, q_ref, "q"), (k, k_ref, "k")):
+        assert bool(torch.isfinite(got.float()).all()), name
+        d = (got.float() - ref.float()).abs()
+        assert float(d.max()) <= 2 ** -7 * float(ref.float().abs().max()), name
+        assert float((d > 0).float().mean()) < 0.02, name          # almost every element is bit-identical
