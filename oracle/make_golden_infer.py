@@ -97,12 +97,22 @@ def run_case(name: str):
     beam_eos = [llm.generate(inputs_embeds=inputs_embeds, attention_mask=attention_mask, max_new_tokens=new,
                              pad_token_id=lc.pad_id, eos_token_id=e, do_sample=False, num_beams=3, temperature=None,
                              top_p=None, top_k=None, repetition_penalty=1.0) for e in beam_eos_ids]
-    print(f"[{name}] beam3 {beam.tolist()} | eos={beam_eos_ids}: {[b.tolist() for b in beam_eos]}")
+    # the Stage-2 inference scripts' call (ref:Stage2/inference_vqa_stage2.py:180-195, defaults :316-319): beams with a
+    # repetition penalty and a length penalty; also greedy with the penalty (ref:Stage1/inference_stage1.py:185)
+    beam_rep = llm.generate(inputs_embeds=inputs_embeds, attention_mask=attention_mask, max_new_tokens=new,
+                            pad_token_id=lc.pad_id, eos_token_id=beam_eos_ids[1], do_sample=False, num_beams=3,
+                            temperature=None, top_p=None, top_k=None, repetition_penalty=1.8, length_penalty=1.2)
+    greedy_rep = llm.generate(inputs_embeds=inputs_embeds, attention_mask=attention_mask, max_new_tokens=new,
+                              pad_token_id=lc.pad_id, eos_token_id=1, do_sample=False, temperature=None,
+                              top_p=None, top_k=None, repetition_penalty=1.8)
+    print(f"[{name}] beam3 {beam.tolist()} | eos={beam_eos_ids}: {[b.tolist() for b in beam_eos]} | "
+          f"rep 1.8 beams {beam_rep.tolist()} greedy {greedy_rep.tolist()}")
     np.savez_compressed(GOLDEN / f"{name}.npz", case=np.array(name), B=B, prompt_tokens=Tp, max_new_tokens=new,
                         prompt_ids=ids[:, :Tp].numpy(), prefill_logits=prefill_logits.numpy(),
                         generated=outputs.numpy(), eos_variant_id=first, generated_eos=outputs_eos.numpy(),
                         projected=projected.numpy(), beam3=beam.numpy(), beam3_eos_ids=np.array(beam_eos_ids),
-                        beam3_eos0=beam_eos[0].numpy(), beam3_eos1=beam_eos[1].numpy())
+                        beam3_eos0=beam_eos[0].numpy(), beam3_eos1=beam_eos[1].numpy(),
+                        beam3_rep=beam_rep.numpy(), greedy_rep=greedy_rep.numpy())
 
 
 if __name__ == "__main__":

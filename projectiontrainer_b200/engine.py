@@ -1442,6 +1442,7 @@ class Stage1Engine:
         if num_beams > 1:
             return self._beam_generate(pixels, prompt_ids, max_new_tokens=max_new_tokens, do_sample=do_sample,
                                        temperature=temperature, top_p=top_p, top_k=top_k,
+                                       repetition_penalty=repetition_penalty,
                                        pad_token_id=pad_token_id, eos_token_id=eos_token_id, generator=generator,
                                        prompt_pad_id=prompt_pad_id, num_beams=num_beams, length_penalty=length_penalty)
         logits = self.prefill(pixels, prompt_ids, max_new_tokens=max_new_tokens, prompt_pad_id=prompt_pad_id)
@@ -1515,7 +1516,8 @@ class Stage1Engine:
 
     @torch.no_grad()
     def _beam_generate(self, pixels, prompt_ids, *, max_new_tokens, do_sample, temperature, top_p, top_k,
-                       pad_token_id, eos_token_id, generator, prompt_pad_id, num_beams, length_penalty):
+                       pad_token_id, eos_token_id, generator, prompt_pad_id, num_beams, length_penalty,
+                       repetition_penalty=1.0):
         """HF `generate(num_beams=n)` (beam search, or beam sampling with do_sample=True: what the Stage-2 validation
         asks for, ref:Stage2/trainer.py:603-611 `num_beams=3, do_sample=True, top_p=0.9, top_k=50`), restated from
         `GenerationMixin._beam_search` of transformers 5.x with early_stopping=False and no prompt ids (generation
@@ -1545,6 +1547,10 @@ class Stage1Engine:
         kc = self.cache
         for cur in range(L):
             lp = torch.log_softmax(logits.float(), dim=-1)
+            if repetition_penalty != 1.0 and cur > 0:    # HF's processor runs on the log-probabilities of each beam,
+                prev = run_seq[:, :, :cur].reshape(B * nb, cur)      # over the tokens that beam has generated
+                gsel = lp.gather(1, prev)
+                lp = lp.scatter(1, prev, torch.where(gsel < 0, gsel * repetition_penalty, gsel / repetition_penalty))
             if do_sample:                                # HF's warpers, min_tokens_to_keep = 2 under beam search
                 if temperature != 1.0:
                     lp = lp / temperature

@@ -116,3 +116,20 @@ def test_top_p_on_the_top_k_candidates_equals_hf_warpers_on_the_whole_row():
         assert torch.equal(torch.isfinite(ref), torch.isfinite(new)), (V, k, top_p)
         assert torch.equal(ref[torch.isfinite(ref)], new[torch.isfinite(new)])
         assert int(torch.isfinite(new).sum(1).min()) >= 2
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_repetition_penalty_matches_hf_generate(name):
+    """The Stage-2 inference scripts' call: 3 beams with repetition_penalty 1.8 and length_penalty 1.2
+    (ref:Stage2/inference_vqa_stage2.py:180-195), and greedy decoding with the penalty — HF applies the penalty to the
+    log-probabilities of every beam over the tokens that beam has generated."""
+    from projectiontrainer_b200.engine import Stage1Engine
+    g = np.load(GOLDEN / f"{name}.npz")
+    eng = _OracleEngine(name)
+    pad = eng.lc.pad_id if name in LEFT_PADS else None
+    out = _beam(eng, int(g["beam3_eos_ids"][1]), prompt_pad_id=pad, repetition_penalty=1.8, length_penalty=1.2)
+    assert np.array_equal(out.numpy(), g["beam3_rep"]), (out.tolist(), g["beam3_rep"].tolist())
+    eng.fuse_sampler = False                   # the torch restatement of the token choice (the kernel needs a GPU)
+    out = Stage1Engine.generate(eng, eng.pixels, eng.prompt, max_new_tokens=eng.new, do_sample=False,
+                                repetition_penalty=1.8, pad_token_id=eng.lc.pad_id, eos_token_id=1, prompt_pad_id=pad)
+    assert np.array_equal(out.numpy(), g["greedy_rep"]), (out.tolist(), g["greedy_rep"].tolist())
