@@ -389,3 +389,14 @@ def test_vqa_trainer_dropin_end_to_end_tiny(cuda_dev, tmp_path):
     for k, p in proj.state_dict().items():
         assert torch.equal(back.state_dict()[k], p.cpu())
         assert not torch.equal(p.cpu(), P[k])                        # and it did train
+
+
+def test_inference_vqa_stage2_synthetic_runs_the_reference_generation_call(cuda_dev, capsys):
+    """`python -m projectiontrainer_b200.inference_vqa_stage2 --synthetic`: random-init SigLIP-L + Gemma3-1B with LoRA
+    adapters folded into the decoder once, three generated JPEGs + questions through the reference's loop and its
+    generation call (3 beams, sampling, repetition penalty 1.8, length penalty 1.2)."""
+    from projectiontrainer_b200 import inference_vqa_stage2 as I
+    preds = I.main(["--synthetic", "--max_new_tokens", "6", "--device", str(cuda_dev)])
+    assert len(preds) == 3 and all(p is not None and 1 <= len(p.split()) <= 6 for p in preds)
+    out = capsys.readouterr().out
+    assert out.count("Prediction:") == 3 and "Sample 3" in out

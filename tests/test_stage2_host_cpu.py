@@ -171,3 +171,24 @@ def test_stage1_dataset_token_cache_matches_lazy_tokenisation(tmp_path):
     for i in range(5):
         assert torch.equal(cached._tokens(i), lazy._tokens(i))
     assert WordTok.calls == 1 + 5
+
+
+def test_inference_vqa_stage2_flags_and_image_path_rules(tmp_path):
+    """The Stage-2 inference mirror keeps the reference's flags / defaults (ref:Stage2/inference_vqa_stage2.py:300-319)
+    and its image path rules (:222-241): plain entries under image_root, 'p.../s...' study directories under
+    image_root_2 with the first .jpg inside."""
+    from projectiontrainer_b200 import inference_vqa_stage2 as I
+    a = I.build_parser().parse_args([])
+    assert (a.max_new_tokens, a.do_sample, a.temperature, a.top_p, a.top_k, a.repetition_penalty, a.length_penalty,
+            a.num_beams) == (512, True, 0.3, 0.9, 50, 1.8, 1.2, 3)
+    assert a.vision_model_name == "StanfordAIMI/XraySigLIP__vit-l-16-siglip-384__webli" and a.image_root_2 is None
+    r1, r2 = tmp_path / "a", tmp_path / "b"
+    (r2 / "p10" / "s50").mkdir(parents=True)
+    (r2 / "p10" / "s50" / "x.JPG").write_bytes(b"")
+    (r2 / "p11" / "s51").mkdir(parents=True)
+    assert I.resolve_image_path("images_002/images/1.jpg", str(r1), str(r2)) == str(r1 / "images_002/images/1.jpg")
+    assert I.resolve_image_path("p10/s50", str(r1), str(r2)) == str(r2 / "p10" / "s50" / "x.JPG")
+    assert I.resolve_image_path("p11/s51", str(r1), str(r2)) is None              # a study directory without a .jpg
+    assert I.resolve_image_path("p10/s50", str(r1), None) == str(r1 / "p10/s50")    # no second root: the plain rule
+    # a sample without image / problem is skipped before any model work
+    assert I.process_sample({"image": "x.jpg"}, str(r1), None, 384, None, None, {}, 0, 1) is None
