@@ -114,6 +114,52 @@ def attach_adapters(engine: Stage1Engine, adapter_path: str) -> bool:
         return False
 
 
+def load_models(args, device):
+    """Processor, vision encoder, base LLM, tokenizer (adapter directory first), adapters, `projector_best.bin`
+    (ref:Stage2/inference_vqa_stage2.py:347-414, ref:Stage2/inference_generation.py:249-311) -> engine, image size,
+    tokenize(text) -> ids [1, n] without special tokens, decode(ids) -> text, pad id, eos id."""
+    logger.info("Loading models and processor...")
+    try:
+        from transformers import AutoModel, AutoModelForCausalLM, AutoProcessor, AutoTokenizer
+        processor = AutoProcessor.from_pretrained(args.vision_model_name)
+        vision_encoder = AutoModel.from_pretrained(args.vision_model_name, torch_dtype=torch.bfloat16)
+        vision_dim = vision_encoder.config.vision_config.hidden_size
+        logger.info(f"Loading base LLM: {args.base_llm_name}")
+        llm = AutoModelForCausalLM.from_pretrained(args.base_llm_name, torch_dtype=torch.bfloat16, trust_remote_code=True)
+        try:
+            tokenizer = AutoTokenizer.from_pretrained(args.adapter_path, trust_remote_code=True)
+            logger.info(f"Tokenizer loaded from adapter path: {args.adapter_path}")
+        except Exception:
+            logger.warning(f"Could not load tokenizer from adapter path '{args.adapter_path}'. Loading from base "
+                           f"model '{args.base_llm_name}'.")
+            tokenizer = AutoTokenizer.from_pretrained(args.base_llm_name, trust_remote_code=True)
+        tokenizer.padding_side = "left"
+        if tokenizer.pad_token is None:
+            tokenizer.pad_token = tokenizer.eos_token
+            logger.warning("pad_token was None. Set to eos_token.")
+        projection_layer = MLPProjector(vision_dim=vision_dim, llm_dim=llm.config.hidden_size)
+        weights_path = os.path.join(args.projector_path, "projector_best.bin")
+        if not os.path.exists(weights_path):
+            raise FileNotFoundError(f"Projector weights not found at {weights_path}")
+        projection_layer.load_state_dict(torch.load(weights_path, map_location="cpu"))
+        engine = Stage1Engine(
+            PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), device),
+            PackedGemma(*Wt.llm_from_hf(llm), device),
+            ProjectorState({k: v.detach().float() for k, v in projection_layer.state_dict().items()}, device), device)
+        attach_adapters(engine, args.adapter_path)
+        size = getattr(getattr(processor, "image_processor", processor), "size", {}) or {}
+        image_size = size["height"] if "height" in size else 384
+        logger.info("Models loaded successfully.")
+    except SystemExit:
+        raise
+    except Exception as e:
+        logger.error(f"Failed to load models: {e}", exc_info=True)
+        raise SystemExit(1)
+    tokenize = lambda text: tokenizer(text, return_tensors="pt", add_special_tokens=False).input_ids
+    decode = lambda ids: tokenizer.decode(ids, skip_special_tokens=True)
+    return engine, image_size, tokenize, decode, tokenizer.pad_token_id, tokenizer.eos_token_id
+
+
 def run(engine: Stage1Engine, data, args, image_size, tokenize, decode, pad_token_id, eos_token_id, generator=None):
     generation_args = dict(max_new_tokens=args.max_new_tokens, do_sample=args.do_sample, temperature=args.temperature,
                            top_p=args.top_p, top_k=args.top_k, repetition_penalty=args.repetition_penalty,
@@ -191,44 +237,7 @@ def main(argv=None):
         if not os.path.isdir(args.image_root):
             logger.error(f"Image root directory not found: {args.image_root}")
             raise SystemExit(1)
-        logger.info("Loading models and processor...")
-        try:
-            from transformers import AutoModel, AutoModelForCausalLM, AutoProcessor, AutoTokenizer
-            processor = AutoProcessor.from_pretrained(args.vision_model_name)
-            vision_encoder = AutoModel.from_pretrained(args.vision_model_name, torch_dtype=torch.bfloat16)
-            vision_dim = vision_encoder.config.vision_config.hidden_size
-            logger.info(f"Loading base LLM: {args.base_llm_name}")
-            llm = AutoModelForCausalLM.from_pretrained(args.base_llm_name, torch_dtype=torch.bfloat16,
-                                                       trust_remote_code=True)
-            try:
-                tokenizer = AutoTokenizer.from_pretrained(args.adapter_path, trust_remote_code=True)
-                logger.info(f"Tokenizer loaded from adapter path: {args.adapter_path}")
-            except Exception:
-                logger.warning(f"Could not load tokenizer from adapter path '{args.adapter_path}'. Loading from base "
-                               f"model '{args.base_llm_name}'.")
-                tokenizer = AutoTokenizer.from_pretrained(args.base_llm_name, trust_remote_code=True)
-            tokenizer.padding_side = "left"
-            if tokenizer.pad_token is None:
-                tokenizer.pad_token = tokenizer.eos_token
-                logger.warning("pad_token was None. Set to eos_token.")
-            projection_layer = MLPProjector(vision_dim=vision_dim, llm_dim=llm.config.hidden_size)
-            weights_path = os.path.join(args.projector_path, "projector_best.bin")
-            if not os.path.exists(weights_path):
-                raise FileNotFoundError(f"Projector weights not found at {weights_path}")
-            projection_layer.load_state_dict(torch.load(weights_path, map_location="cpu"))
-            engine = Stage1Engine(
-                PackedSiglip(*Wt.siglip_from_hf(getattr(vision_encoder, "vision_model", vision_encoder)), device),
-                PackedGemma(*Wt.llm_from_hf(llm), device),
-                ProjectorState({k: v.detach().float() for k, v in projection_layer.state_dict().items()}, device), device)
-            attach_adapters(engine, args.adapter_path)
-            size = getattr(getattr(processor, "image_processor", processor), "size", {}) or {}
-            image_size = size["height"] if "height" in size else 384
-            logger.info("Models loaded successfully.")
-        except SystemExit:
-            raise
-        except Exception as e:
-            logger.error(f"Failed to load models: {e}", exc_info=True)
-            raise SystemExit(1)
+        engine, image_size, tokenize, decode, pad_id, eos_id = load_models(args, device)
         try:
             with open(args.input_json, "r", encoding="utf-8") as f:
                 data = json.load(f)
@@ -236,9 +245,6 @@ def main(argv=None):
         except Exception as e:
             logger.error(f"Failed to load or parse JSON file {args.input_json}: {e}")
             raise SystemExit(1)
-        tokenize = lambda text: tokenizer(text, return_tensors="pt", add_special_tokens=False).input_ids
-        decode = lambda ids: tokenizer.decode(ids, skip_special_tokens=True)
-        pad_id, eos_id = tokenizer.pad_token_id, tokenizer.eos_token_id
     return run(engine, data, args, image_size, tokenize, decode, pad_id, eos_id)
 
 

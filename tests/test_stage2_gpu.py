@@ -400,3 +400,12 @@ def test_inference_vqa_stage2_synthetic_runs_the_reference_generation_call(cuda_
     assert len(preds) == 3 and all(p is not None and 1 <= len(p.split()) <= 6 for p in preds)
     out = capsys.readouterr().out
     assert out.count("Prediction:") == 3 and "Sample 3" in out
+
+
+def test_inference_generation_synthetic_runs_and_summarises(cuda_dev, capsys):
+    """`python -m projectiontrainer_b200.inference_generation --synthetic`: the fixed prompt, sampling at temperature
+    0.7 / top_p 0.9, substring scoring and the summary on three generated images."""
+    from projectiontrainer_b200 import inference_generation as G
+    s = G.main(["--synthetic", "--max_length", "6", "--device", str(cuda_dev)])
+    assert s["total"] == 3 and 0 <= s["correct"] <= 3 and sum(s["ground_truth"].values()) == 3
+    assert "SUMMARY OF RESULTS" in capsys.readouterr().out

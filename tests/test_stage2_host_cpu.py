@@ -192,3 +192,20 @@ def test_inference_vqa_stage2_flags_and_image_path_rules(tmp_path):
     assert I.resolve_image_path("p10/s50", str(r1), None) == str(r1 / "p10/s50")    # no second root: the plain rule
     # a sample without image / problem is skipped before any model work
     assert I.process_sample({"image": "x.jpg"}, str(r1), None, 384, None, None, {}, 0, 1) is None
+
+
+def test_inference_generation_summary_counts():
+    """ref:Stage2/inference_generation.py:94,129-199: a sample is correct when its ground-truth label occurs in the
+    generated text (case-insensitive); the summary counts per-label hits and candidate labels found in predictions."""
+    from projectiontrainer_b200 import inference_generation as G
+    a = G.build_parser().parse_args([])
+    assert a.max_length == 128 and not a.verbose and G.PROMPT.startswith("Identify the diseases in this chest X-ray")
+    res = [{"generated_text": "Likely ATELECTASIS with effusion", "normal_caption": "Atelectasis", "is_correct": True},
+           {"generated_text": "no finding", "normal_caption": "Atelectasis", "is_correct": False},
+           {"generated_text": "No Finding.", "normal_caption": "No Finding", "is_correct": True}]
+    s = G.summarise(res, ["Atelectasis", "No Finding", "Edema"])
+    assert (s["total"], s["correct"]) == (3, 2)
+    assert s["ground_truth"] == {"Atelectasis": 2, "No Finding": 1}
+    assert s["label_correct"]["Atelectasis"] == 1 and s["label_correct"]["No Finding"] == 1
+    assert s["predicted"] == {"Atelectasis": 1, "No Finding": 2}
+    assert G.summarise([], ["x"])["total"] == 0
