@@ -1545,6 +1545,10 @@ class Stage1Engine:
         improvable = torch.ones(B, 1, dtype=torch.bool, device=dev)
         gather = lambda t, idx: t.gather(1, idx.view(B, -1, *([1] * (t.dim() - 2))).expand(-1, -1, *t.shape[2:]))
         kc = self.cache
+        overlap = dev.type == "cuda"
+        if overlap:
+            stop_h = torch.zeros(1, dtype=torch.bool, pin_memory=True)
+            stop_ev = torch.cuda.Event()
         for cur in range(L):
             lp = torch.log_softmax(logits.float(), dim=-1)
             if repetition_penalty != 1.0 and cur > 0:    # HF's processor runs on the log-probabilities of each beam,
@@ -1600,13 +1604,22 @@ class Stage1Engine:
             best_run = run_score[:, :1] / float(cur + 1) ** length_penalty
             worst_fin = torch.where(finished, fin_score.min(dim=1, keepdim=True).values, torch.full_like(fin_score, -1e9))
             improvable = improvable & (best_run > worst_fin).any(dim=-1, keepdim=True)
-            if not bool(improvable.any()) or bool(hit.all()):
+            stop = (~improvable.any()) | hit.all()
+            if overlap:                                  # the answer travels to the host behind an event ...
+                stop_h.copy_(stop.view(1), non_blocking=True)
+                stop_ev.record()
+            elif bool(stop):
                 break
-            # KV rows follow their beams (in place: the decode graph holds the cache addresses)
-            rows = (run_src + torch.arange(B, device=dev)[:, None] * nb).view(-1)
-            kc["k_all"].copy_(kc["k_all"].index_select(1, rows))
-            kc["v_all"].copy_(kc["v_all"].index_select(1, rows))
-            logits = self.decode_step(run_seq[:, :, cur].reshape(-1))
+            if cur + 1 < L:
+                # KV rows follow their beams (in place: the decode graph holds the cache addresses)
+                rows = (run_src + torch.arange(B, device=dev)[:, None] * nb).view(-1)
+                kc["k_all"].copy_(kc["k_all"].index_select(1, rows))
+                kc["v_all"].copy_(kc["v_all"].index_select(1, rows))
+                logits = self.decode_step(run_seq[:, :, cur].reshape(-1))
+            if overlap:                                  # ... while the next decode step is already queued: the host
+                stop_ev.synchronize()                    # waits for the flag only and prepares the next step's
+                if bool(stop_h[0]):                      # bookkeeping during the decode (a step queued past the
+                    break                                # stop is never read)
         out_len = int(fin_len[:, 0].max().item())
         return fin_seq[:, 0, :max(out_len, 1)]
 
