@@ -1555,33 +1555,45 @@ class Stage1Engine:
                 prev = run_seq[:, :, :cur].reshape(B * nb, cur)      # over the tokens that beam has generated
                 gsel = lp.gather(1, prev)
                 lp = lp.scatter(1, prev, torch.where(gsel < 0, gsel * repetition_penalty, gsel / repetition_penalty))
-            if do_sample:                                # HF's warpers, min_tokens_to_keep = 2 under beam search
+            small = do_sample and bool(top_k) and top_k > 0
+            if small:
+                # HF's warpers (min_tokens_to_keep = 2 under beam search) on the top-k candidates only: after
+                # TopKLogitsWarper every other entry of the row is -inf (probability 0), so temperature, top-p, the joint
+                # softmax over the beams and the draw without replacement see exactly these values.  Nothing of size
+                # [rows, V] is touched after the top-k.  (Entries tied with the k-th value beyond the list are left out:
+                # HF keeps them; for float log-probabilities that is a set of measure zero.)
                 if temperature != 1.0:
                     lp = lp / temperature
-                vals = None
-                if top_k and top_k > 0:
-                    vals = lp.topk(min(max(top_k, 2), V), dim=1).values          # descending
-                    lp = lp.masked_fill(lp < vals[:, -1:], float("-inf"))
-                if top_p < 1.0 and vals is not None:
-                    # after top-k the finite entries of lp ARE `vals`: HF's ascending sort + cumulative sum over the
-                    # whole row sees -inf (probability 0) and then these values, so the tokens it removes are the
-                    # r smallest of them — everything below the value of rank r (no sort of the whole vocabulary)
+                kk = min(max(top_k, 2), V)
+                vals, tix = lp.topk(kk, dim=1)                                   # descending, [rows, kk]
+                if top_p < 1.0:
+                    # ascending cumulative probability <= 1 - top_p goes, the two largest stay
                     asc = vals.flip(1)
                     rm = asc.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
                     rm[:, -2:] = False
-                    thr = asc.gather(1, rm.sum(dim=1, keepdim=True))
-                    lp = lp.masked_fill(lp < thr, float("-inf"))
-                elif top_p < 1.0:
-                    srt, idx = lp.sort(dim=1, descending=False)
-                    rm = srt.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
-                    rm[:, -2:] = False
-                    lp = lp.masked_fill(rm.scatter(1, idx, rm), float("-inf"))
-            acc = (lp.view(B, nb, V) + run_score[:, :, None]).view(B, nb * V)
-            if do_sample:
-                cand = torch.multinomial(acc.softmax(dim=-1), keep, generator=generator)
-                cand_score = acc.gather(1, cand)
+                    vals = vals.masked_fill(rm.flip(1), float("-inf"))
+                acc = (vals.view(B, nb, kk) + run_score[:, :, None]).view(B, nb * kk)
+                pick = torch.multinomial(acc.softmax(dim=-1), keep, generator=generator)
+                cand_score = acc.gather(1, pick)
+                cand = (pick // kk) * V + tix.view(B, nb * kk).gather(1, pick)      # beam * V + token
             else:
-                cand_score, cand = acc.topk(keep, dim=1)
+                if do_sample:
+                    if temperature != 1.0:
+                        lp = lp / temperature
+                    if top_p < 1.0:
+                        srt, idx = lp.sort(dim=1, descending=False)
+                        rm = srt.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
+                        rm[:, -2:] = False
+                        lp = lp.masked_fill(rm.scatter(1, idx, rm), float("-inf"))
+                if do_sample:
+                    acc = (lp.view(B, nb, V) + run_score[:, :, None]).view(B, nb * V)
+                    cand = torch.multinomial(acc.softmax(dim=-1), keep, generator=generator)
+                    cand_score = acc.gather(1, cand)
+                else:       # the best `keep` of all beams' continuations are among each beam's own best `keep`
+                    vals, tix = lp.topk(keep, dim=1)
+                    acc = (vals.view(B, nb, keep) + run_score[:, :, None]).view(B, nb * keep)
+                    cand_score, pick = acc.topk(keep, dim=1)
+                    cand = (pick // keep) * V + tix.view(B, nb * keep).gather(1, pick)
             src_beam, tok = cand // V, cand % V
             cand_seq = gather(run_seq, src_beam)
             cand_seq[:, :, cur] = tok

@@ -106,13 +106,13 @@ def test_top_p_on_the_top_k_candidates_equals_hf_warpers_on_the_whole_row():
         rm = srt.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
         rm[:, -2:] = False
         ref = ref.masked_fill(rm.scatter(1, idx, rm), float("-inf"))
-        # the engine's
-        vals = lp.topk(min(max(k, 2), V), dim=1).values
-        new = lp.masked_fill(lp < vals[:, -1:], float("-inf"))
+        # the engine's: warp the top-k candidates only, nothing of size [rows, V] after the top-k
+        vals, tix = lp.topk(min(max(k, 2), V), dim=1)
         asc = vals.flip(1)
         rm2 = asc.softmax(dim=1).cumsum(dim=1) <= (1.0 - top_p)
         rm2[:, -2:] = False
-        new = new.masked_fill(new < asc.gather(1, rm2.sum(dim=1, keepdim=True)), float("-inf"))
+        vals = vals.masked_fill(rm2.flip(1), float("-inf"))
+        new = torch.full_like(lp, float("-inf")).scatter(1, tix, vals)
         assert torch.equal(torch.isfinite(ref), torch.isfinite(new)), (V, k, top_p)
         assert torch.equal(ref[torch.isfinite(ref)], new[torch.isfinite(new)])
         assert int(torch.isfinite(new).sum(1).min()) >= 2
