@@ -37,11 +37,13 @@ def build_parser():
     p.add_argument("--candidate_labels", type=str, default=None, help="comma-separated candidate labels of this run")
     p.add_argument("--device", type=str, default="cuda" if torch.cuda.is_available() else "cpu")
     p.add_argument("--synthetic", action="store_true", help="random-init models, generated images")
+    p.add_argument("--gpu_decode", action="store_true",
+                   help="decode baseline JPEG files and resize on the GPU (same pixel values as Pillow; not a reference flag)")
     return p
 
 
 def process_sample(sample, image_root, engine, image_size, tokenize, decode, pad_token_id, eos_token_id, max_length=128,
-                   generator=None):
+                   generator=None, gpu_decode=False):
     """ref:Stage2/inference_generation.py:24-107 on the engine: {generated_text, normal_caption, is_correct} or None."""
     image_rel_path = sample.get("image")
     normal_caption = sample.get("normal_caption", "")
@@ -51,7 +53,7 @@ def process_sample(sample, image_root, engine, image_size, tokenize, decode, pad
     text = V.process_sample({"image": image_rel_path, "problem": PROMPT}, image_root, engine, 384 if image_size is None
                             else image_size, tokenize, decode,
                             dict(max_new_tokens=max_length, do_sample=True, temperature=0.7, top_p=0.9, num_beams=1),
-                            pad_token_id, eos_token_id, generator=generator)
+                            pad_token_id, eos_token_id, generator=generator, gpu_decode=gpu_decode)
     if text is None:
         return None
     return {"generated_text": text, "normal_caption": normal_caption,
@@ -136,7 +138,7 @@ def main(argv=None):
     with engine.merged(engine.merge_adapters()):
         for sample in data:
             result = process_sample(sample, args.image_root, engine, image_size, tokenize, decode, pad_id, eos_id,
-                                    max_length=args.max_length)
+                                    max_length=args.max_length, gpu_decode=args.gpu_decode)
             if result is None:
                 skipped += 1
                 continue

@@ -409,3 +409,30 @@ def test_inference_generation_synthetic_runs_and_summarises(cuda_dev, capsys):
     s = G.main(["--synthetic", "--max_length", "6", "--device", str(cuda_dev)])
     assert s["total"] == 3 and 0 <= s["correct"] <= 3 and sum(s["ground_truth"].values()) == 3
     assert "SUMMARY OF RESULTS" in capsys.readouterr().out
+
+
+def test_inference_mirrors_gpu_decode_gives_pillows_pixel_values(cuda_dev, tmp_path):
+    """`--gpu_decode` of the Stage-2 inference mirrors: the file is only read on the host, a baseline JPEG is decoded
+    and bicubic-resized on the GPU — bit-identical pixel_values to Pillow's decode + resize + the processor arithmetic
+    (the default path); a PNG takes Pillow in both."""
+    import numpy as np
+    from PIL import Image
+    from oracle import stage1_oracle as O
+    from projectiontrainer_b200 import engine as E, inference_vqa_stage2 as I
+    from projectiontrainer_b200.config import GemmaCfg, SiglipCfg
+    vkw = dict(hidden=64, ff=128, layers=1, heads=1, image=64, patch=16)
+    lkw = dict(vocab=512, hidden=128, ff=128, layers=2, hq=2, hkv=1, hd=64, window=8, q_scalar=64.0)
+    ovc, olc = O.SiglipCfg(**vkw), O.GemmaCfg(**lkw)
+    eng = E.Stage1Engine(E.PackedSiglip(O.init_siglip(ovc), SiglipCfg(**vkw), cuda_dev),
+                         E.PackedGemma(O.init_gemma(olc), GemmaCfg(**lkw), cuda_dev),
+                         E.ProjectorState(O.init_projector(ovc.hidden, olc.hidden), cuda_dev), cuda_dev)
+    rng = np.random.default_rng(3)
+    img = (rng.random((301, 517, 3)) * 80 + np.linspace(0, 170, 517)[None, :, None]).astype(np.uint8)
+    jpg, png = tmp_path / "a.jpg", tmp_path / "b.png"
+    Image.fromarray(img).save(jpg, quality=88)
+    Image.fromarray(img).save(png)
+    for path in (jpg, png):
+        ref = I.load_pixel_values(eng, str(path), 64, gpu_decode=False)
+        got = I.load_pixel_values(eng, str(path), 64, gpu_decode=True)
+        torch.cuda.synchronize()
+        assert got.shape == (1, 3, 64, 64) and torch.equal(got, ref), path.name
