@@ -36,6 +36,9 @@ def parse_args(argv=None):
     p.add_argument("--repetition_penalty", type=float, default=1.0)
     p.add_argument("--do_sample", type=bool, default=True)
     p.add_argument("--synthetic", action="store_true", help="random-init SigLIP-L + Gemma3-1B, random image")
+    p.add_argument("--gpu_decode", action="store_true",
+                   help="decode a baseline JPEG and resize on the GPU (same pixel values as Pillow + the processor; not a "
+                        "reference flag)")
     return p.parse_args(argv)
 
 
@@ -127,8 +130,12 @@ def main(argv=None):
             raise SystemExit(1)
         engine = build_engine_from_hf(vision_encoder, llm_model, projection_layer, device)
         try:
-            image = Image.open(args.image_path).convert("RGB")
-            pixel_values = processor(images=image, return_tensors="pt").pixel_values
+            if args.gpu_decode:     # file bytes -> GPU decode + the processor's bicubic resize / rescale / normalise
+                from .inference_vqa_stage2 import load_pixel_values
+                pixel_values = load_pixel_values(engine, args.image_path, engine.vcfg.image, gpu_decode=True)
+            else:
+                image = Image.open(args.image_path).convert("RGB")
+                pixel_values = processor(images=image, return_tensors="pt").pixel_values
         except FileNotFoundError:
             logger.error(f"Image file not found: {args.image_path}")
             raise SystemExit(1)
